@@ -1,0 +1,284 @@
+"""Oracle graph interpreter -- TEST INFRASTRUCTURE ONLY.
+
+Evaluates (a) an un-partitioned ``tachikoma_b200.relay`` expression op by op, exactly like the
+reference's un-offloaded "llvm" build does after QNN canonicalization, and
+(b) a tachikoma JSON graph (composite nodes are evaluated by running the primitive oracle ops of
+the chain one after the other).  All arithmetic is done by oracle/libqnn_oracle.so
+(qnn_oracle.c); numpy is used for reshapes/transposes and trivial elementwise ops only.
+
+May be imported only by tests/, __graft_entry__.smoke() and bench.py (cpu_baseline /
+--impl reference).  The product package never imports this module.
+"""
+from __future__ import annotations
+
+import ctypes
+import json
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+DT = {"int8": 0, "uint8": 1, "int32": 2, "int16": 3, "int64": 4, "float32": 5}
+ROUNDING = {"UPWARD": 0, "TONEAREST": 1, "None": 0}
+COMPUTE = {"int64": 0, "float32": 1, "float64": 2, "None": 0}
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "libqnn_oracle.so")
+    src = os.path.join(_HERE, "qnn_oracle.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "clean", "all"])
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = ctypes.CDLL(build())
+        _LIB.tko_fixed_point_multiply.restype = ctypes.c_int32
+        _LIB.tko_fixed_point_multiply.argtypes = [ctypes.c_int32] * 3
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def _i64(v):
+    return (ctypes.c_int64 * len(v))(*[int(x) for x in v])
+
+
+def fixed_point_multiplier_shift(m):
+    s, e = ctypes.c_int32(), ctypes.c_int32()
+    lib().tko_fixed_point_multiplier_shift(ctypes.c_double(m), ctypes.byref(s), ctypes.byref(e))
+    return s.value, e.value
+
+
+def fixed_point_multiply(x, multiplier, shift):
+    x = np.asarray(x, dtype=np.int32)
+    f = lib().tko_fixed_point_multiply
+    return np.array([f(int(v), int(multiplier), int(shift)) for v in x.ravel()], dtype=np.int32).reshape(x.shape)
+
+
+def requantize(data, input_scale, input_zero_point, output_scale, output_zero_point, axis=-1,
+               rounding="None", compute_dtype="None", out_dtype="int8"):
+    data = np.asarray(data)
+    shape0 = data.shape
+    data = np.ascontiguousarray(data)
+    sc = np.ascontiguousarray(np.asarray(input_scale, dtype=np.float32).reshape(-1))
+    zp = np.ascontiguousarray(np.asarray(input_zero_point, dtype=np.int32).reshape(-1))
+    nd = data.ndim
+    ax = axis + nd if axis < 0 else axis
+    if nd == 0:
+        outer, C, inner = 1, 1, 1
+    else:
+        outer = int(np.prod(data.shape[:ax], dtype=np.int64))
+        C = int(data.shape[ax])
+        inner = int(np.prod(data.shape[ax + 1:], dtype=np.int64))
+    assert sc.size in (1, C) and zp.size in (1, C)
+    out = np.empty(shape0, dtype=out_dtype)
+    lib().tko_requantize(_p(data), DT[str(data.dtype)], ctypes.c_int64(outer), ctypes.c_int64(C),
+                         ctypes.c_int64(inner), _p(sc), int(sc.size), _p(zp), int(zp.size),
+                         ctypes.c_float(float(np.asarray(output_scale, dtype=np.float32).reshape(-1)[0])),
+                         ctypes.c_int32(int(np.asarray(output_zero_point).reshape(-1)[0])),
+                         ROUNDING[rounding], COMPUTE[compute_dtype], DT[out_dtype], _p(out))
+    return out
+
+
+def _strides(shape, layout, want):
+    st = [int(s) for s in (np.array(np.zeros(shape, dtype=np.int8).strides))]
+    return [st[layout.index(ch)] for ch in want]
+
+
+def conv2d(data, kernel, input_zero_point, kernel_zero_point, strides=(1, 1), padding=(0, 0, 0, 0),
+           dilation=(1, 1), groups=1, data_layout="NCHW", kernel_layout="OIHW", out_layout=""):
+    data, kernel = np.ascontiguousarray(data), np.ascontiguousarray(kernel)
+    if kernel_layout == "HWOI":  # depthwise NHWC convention: [H, W, C, multiplier] -> O = C*mult
+        kh, kw, c_, m_ = kernel.shape
+        kernel = np.ascontiguousarray(kernel.transpose(2, 3, 0, 1).reshape(c_ * m_, 1, kh, kw))
+        kernel_layout = "OIHW"
+    elif kernel_layout == "HWIO" and groups > 1 and kernel.shape[2] * groups != data.shape[data_layout.index("C")]:
+        # depthwise HWIO with I = in-channels, O = multiplier is not used by the reference tests
+        raise NotImplementedError("grouped HWIO kernel with I != C/groups")
+    N, C, H, W = [data.shape[data_layout.index(ch)] for ch in "NCHW"]
+    O, I, KH, KW = [kernel.shape[kernel_layout.index(ch)] for ch in "OIHW"]
+    assert I * groups == C, (I, groups, C)
+    pad = list(padding)
+    if len(pad) == 2:
+        pad = [pad[0], pad[1], pad[0], pad[1]]
+    sh, sw = strides
+    dh, dw = dilation
+    OH = (H + pad[0] + pad[2] - (KH - 1) * dh - 1) // sh + 1
+    OW = (W + pad[1] + pad[3] - (KW - 1) * dw - 1) // sw + 1
+    olay = out_layout or data_layout
+    oshape = [0] * 4
+    for ch, v in zip("NCHW", (N, O, OH, OW)):
+        oshape[olay.index(ch)] = v
+    out = np.empty(oshape, dtype=np.int32)
+    zw = np.ascontiguousarray(np.asarray(kernel_zero_point, dtype=np.int32).reshape(-1))
+    assert zw.size in (1, O)
+    L = ctypes.c_int64
+    lib().tko_conv2d(_p(data), DT[str(data.dtype)], _p(kernel), DT[str(kernel.dtype)], _p(out),
+                     L(N), L(C), L(H), L(W), L(O), L(KH), L(KW), L(groups), L(sh), L(sw), L(pad[0]), L(pad[1]),
+                     L(pad[2]), L(pad[3]), L(dh), L(dw), _i64(_strides(data.shape, data_layout, "NCHW")),
+                     _i64(_strides(kernel.shape, kernel_layout, "OIHW")), _i64(_strides(oshape, olay, "NCHW")),
+                     ctypes.c_int32(int(np.asarray(input_zero_point).reshape(-1)[0])), _p(zw), int(zw.size))
+    return out
+
+
+def dense(x, w, zp_x, zp_w):
+    x, w = np.ascontiguousarray(x), np.ascontiguousarray(w)
+    lead = x.shape[:-1]
+    M, K, N = int(np.prod(lead, dtype=np.int64)), x.shape[-1], w.shape[0]
+    out = np.empty((M, N), dtype=np.int32)
+    L = ctypes.c_int64
+    lib().tko_dense(_p(x), DT[str(x.dtype)], _p(w), DT[str(w.dtype)], _p(out), L(M), L(N), L(K),
+                    ctypes.c_int32(int(np.asarray(zp_x).reshape(-1)[0])),
+                    ctypes.c_int32(int(np.asarray(zp_w).reshape(-1)[0])))
+    return out.reshape(tuple(lead) + (N,))
+
+
+def batch_matmul(x, y, zp_x, zp_y):
+    x, y = np.ascontiguousarray(x), np.ascontiguousarray(y)
+    B, M, K = x.shape
+    By, N, _ = y.shape
+    out = np.empty((B, M, N), dtype=np.int32)
+    L = ctypes.c_int64
+    lib().tko_batch_matmul(_p(x), DT[str(x.dtype)], _p(y), DT[str(y.dtype)], _p(out), L(B), L(M), L(N), L(K),
+                           L(By), ctypes.c_int32(int(np.asarray(zp_x).reshape(-1)[0])),
+                           ctypes.c_int32(int(np.asarray(zp_y).reshape(-1)[0])))
+    return out
+
+
+def qnn_add(a, b, sa, zpa, sb, zpb, so, zpo):
+    a, b = np.ascontiguousarray(a), np.ascontiguousarray(b)
+    assert a.shape == b.shape and a.dtype == b.dtype
+    out = np.empty_like(a)
+    f = lambda v: ctypes.c_float(float(np.float32(np.asarray(v).reshape(-1)[0])))
+    z = lambda v: ctypes.c_int32(int(np.asarray(v).reshape(-1)[0]))
+    lib().tko_qnn_add(_p(a), _p(b), DT[str(a.dtype)], ctypes.c_int64(a.size), f(sa), z(zpa), f(sb), z(zpb),
+                      f(so), z(zpo), _p(out))
+    return out
+
+
+def pool2d(data, pool_size, strides, padding, layout="NCHW", is_avg=False, count_include_pad=False):
+    data = np.ascontiguousarray(data)
+    N, C, H, W = [data.shape[layout.index(ch)] for ch in "NCHW"]
+    pad = list(padding)
+    if len(pad) == 2:
+        pad = [pad[0], pad[1], pad[0], pad[1]]
+    OH = (H + pad[0] + pad[2] - pool_size[0]) // strides[0] + 1
+    OW = (W + pad[1] + pad[3] - pool_size[1]) // strides[1] + 1
+    oshape = [0] * 4
+    for ch, v in zip("NCHW", (N, C, OH, OW)):
+        oshape[layout.index(ch)] = v
+    out = np.empty(oshape, dtype=data.dtype)
+    L = ctypes.c_int64
+    lib().tko_pool2d(_p(data), DT[str(data.dtype)], _p(out), int(is_avg), int(count_include_pad), L(N), L(C),
+                     L(H), L(W), L(pool_size[0]), L(pool_size[1]), L(strides[0]), L(strides[1]), L(pad[0]),
+                     L(pad[1]), L(pad[2]), L(pad[3]), _i64(_strides(data.shape, layout, "NCHW")),
+                     _i64(_strides(oshape, layout, "NCHW")))
+    return out
+
+
+def dnnl_float_epilogue(acc, axis, bias_f, o_scl, act_scl, sum_t, sum_scl, dst_zp, out_dtype):
+    acc = np.ascontiguousarray(acc, dtype=np.int32)
+    outer = int(np.prod(acc.shape[:axis], dtype=np.int64))
+    C = acc.shape[axis]
+    inner = int(np.prod(acc.shape[axis + 1:], dtype=np.int64))
+    out = np.empty(acc.shape, dtype=out_dtype)
+    o_scl = np.ascontiguousarray(np.asarray(o_scl, dtype=np.float32).reshape(-1))
+    bias_p = None
+    if bias_f is not None:
+        bias_f = np.ascontiguousarray(np.broadcast_to(np.asarray(bias_f, dtype=np.float32).reshape(-1), (C,)))
+        bias_p = _p(bias_f)
+    sum_p, sum_dt = None, 0
+    if sum_t is not None:
+        sum_t = np.ascontiguousarray(sum_t)
+        sum_p, sum_dt = _p(sum_t), DT[str(sum_t.dtype)]
+    L = ctypes.c_int64
+    lib().tko_dnnl_float_epilogue(_p(acc), L(outer), L(C), L(inner), bias_p, _p(o_scl), int(o_scl.size),
+                                  ctypes.c_float(float(act_scl)), sum_p, sum_dt, ctypes.c_float(float(sum_scl)),
+                                  ctypes.c_float(float(dst_zp)), DT[out_dtype], _p(out))
+    return out
+
+
+# ----------------------------------------------------------------------------------------------
+# primitive-op dispatch shared by the expression and JSON interpreters
+# ----------------------------------------------------------------------------------------------
+
+def _wrap_add_i32(a, b):
+    return (a.astype(np.int64) + b.astype(np.int64)).astype(np.int32) if a.dtype == np.int32 else a + b
+
+
+def eval_op(op, attrs, args):
+    """Evaluate one Relay operator on numpy inputs (constants included in ``args``)."""
+    if op == "qnn.conv2d":
+        return conv2d(args[0], args[1], args[2], args[3], attrs["strides"], attrs["padding"], attrs["dilation"],
+                      attrs["groups"], attrs["data_layout"], attrs["kernel_layout"], attrs.get("out_layout", ""))
+    if op == "qnn.dense":
+        return dense(args[0], args[1], args[2], args[3])
+    if op == "qnn.batch_matmul":
+        return batch_matmul(args[0], args[1], args[2], args[3])
+    if op == "qnn.requantize":
+        return requantize(args[0], args[1], args[2], args[3], int(np.asarray(args[4]).reshape(-1)[0]),
+                          attrs.get("axis", -1), attrs.get("rounding", "None"), attrs.get("compute_dtype", "None"),
+                          attrs["out_dtype"])
+    if op == "qnn.add":
+        return qnn_add(*args[:8])
+    if op == "nn.bias_add":
+        ax = attrs.get("axis", 1)
+        shp = [1] * args[0].ndim
+        shp[ax] = -1
+        return _wrap_add_i32(args[0], np.asarray(args[1]).reshape(shp).astype(args[0].dtype))
+    if op == "add":
+        b = np.broadcast_to(np.asarray(args[1]), np.broadcast_shapes(args[0].shape, np.asarray(args[1]).shape))
+        return _wrap_add_i32(np.broadcast_to(args[0], b.shape), b.astype(args[0].dtype))
+    if op == "clip":
+        x = args[0]
+        if x.dtype.kind in "iu":  # relay clip on integers compares in the tensor dtype
+            lo = max(int(attrs["a_min"]), int(np.iinfo(x.dtype).min))
+            hi = min(int(attrs["a_max"]), int(np.iinfo(x.dtype).max))
+            return np.clip(x, lo, hi).astype(x.dtype)
+        return np.clip(x, attrs["a_min"], attrs["a_max"]).astype(x.dtype)
+    if op == "cast":
+        return args[0].astype(attrs["dtype"])  # truncating two's-complement cast, as LLVM trunc
+    if op in ("nn.max_pool2d", "nn.avg_pool2d"):
+        return pool2d(args[0], attrs["pool_size"], attrs["strides"], attrs["padding"], attrs["layout"],
+                      op == "nn.avg_pool2d", attrs.get("count_include_pad", False))
+    if op == "nn.global_avg_pool2d":
+        lay = attrs["layout"]
+        hw = [args[0].shape[lay.index("H")], args[0].shape[lay.index("W")]]
+        return pool2d(args[0], hw, [1, 1], [0, 0, 0, 0], lay, True, False)
+    if op == "nn.pad":
+        pv = np.asarray(args[1]).reshape(-1)[0]
+        return np.pad(args[0], attrs["pad_width"], mode="constant", constant_values=args[0].dtype.type(pv))
+    if op == "reshape":
+        return args[0].reshape(attrs["newshape"])
+    if op == "nn.batch_flatten":
+        return args[0].reshape(args[0].shape[0], -1)
+    if op == "transpose":
+        return np.ascontiguousarray(args[0].transpose(attrs["axes"]))
+    raise NotImplementedError(op)
+
+
+def run_expr(func, inputs):
+    """Evaluate an un-partitioned relay Function; returns (output, {node: value})."""
+    from tachikoma_b200 import relay as R
+
+    env = {}
+    for p in func.params:
+        env[id(p)] = np.ascontiguousarray(inputs[p.name]).astype(p.dtype, copy=False).reshape(p.shape)
+    for e in R.post_order(func.body):
+        if isinstance(e, R.Var):
+            assert id(e) in env, f"unbound var {e.name}"
+        elif isinstance(e, R.Constant):
+            env[id(e)] = e.data
+        else:
+            env[id(e)] = eval_op(e.op, e.attrs, [env[id(a)] for a in e.args])
+            assert tuple(env[id(e)].shape) == tuple(e.shape), (e.op, env[id(e)].shape, e.shape)
+            assert str(env[id(e)].dtype) == e.dtype, (e.op, env[id(e)].dtype, e.dtype)
+    return env[id(func.body)], env

@@ -1,0 +1,427 @@
+"""Generate golden fixtures by EXECUTING the reference's own Python QNN tests.
+
+Run in the build container only (needs /root/reference, which does not exist on the GPU box):
+
+    python tests/golden/gen_from_reference_tests.py
+
+TVM itself cannot be imported here, so a small shim ``tvm`` package is installed in
+``sys.modules`` whose ``relay.*`` constructors build ``tachikoma_b200.relay`` expressions.  The
+reference test files
+    tests/python/relay/test_op_qnn_requantize.py, test_op_qnn_dense.py, test_op_qnn_add.py,
+    tests/python/relay/test_op_qnn_batch_matmul.py, test_op_qnn_conv2d.py
+are then executed unmodified.  Whenever a test compares a QNN graph's output with a golden
+(``np.testing.assert_equal``) the triple (graph, inputs, golden) is captured.  For the conv2d
+property tests the golden is the test's own *reference function* (int32 nn.conv2d over
+zero-point-shifted operands, test_op_qnn_conv2d.py:35-81) evaluated by the plain-numpy
+evaluator in this file, on the random inputs the test drew.
+
+Output: tests/golden/qnn_reference_goldens.json (committed).
+"""
+import base64
+import contextlib
+import importlib.util
+import json
+import os
+import sys
+import types
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from tachikoma_b200 import relay as R  # noqa: E402
+
+REF_TESTS = "/root/reference/tests/python/relay"
+FILES = ["test_op_qnn_requantize.py", "test_op_qnn_dense.py", "test_op_qnn_add.py",
+         "test_op_qnn_batch_matmul.py", "test_op_qnn_conv2d.py"]
+
+CASES, SKIPPED = [], []
+CURRENT = {"name": ""}
+RQ_CFG = {"rounding": None, "compute_dtype": None}
+
+
+class Unsupported(Exception):
+    pass
+
+
+# ------------------------------------------------------------------------------ shim expressions
+class S:
+    """Shim expression node."""
+
+    def __init__(self, op, args=(), attrs=None, value=None, name=None, shape=None, dtype=None):
+        self.op, self.args, self.attrs = op, list(args), dict(attrs or {})
+        self.value, self.name, self.shape, self.dtype = value, name, shape, dtype
+
+    def __add__(self, o):
+        return S("add", [self, _lift(o)])
+
+    def __sub__(self, o):
+        return S("subtract", [self, _lift(o)])
+
+    def __mul__(self, o):
+        return S("multiply", [self, _lift(o)])
+
+
+def _lift(v):
+    return v if isinstance(v, S) else s_const(v)
+
+
+def s_var(name, shape=(), dtype="float32", **_):
+    return S("var", name=name, shape=tuple(int(x) for x in shape), dtype=dtype)
+
+
+def s_const(value, dtype=None):
+    arr = np.asarray(value)
+    if dtype is None:
+        dtype = {"float64": "float32", "int64": "int32"}.get(str(arr.dtype), str(arr.dtype))
+    return S("const", value=arr.astype(dtype), dtype=dtype)
+
+
+def walk(e, fn, seen=None):
+    seen = seen if seen is not None else set()
+    if id(e) in seen:
+        return
+    seen.add(id(e))
+    for a in e.args:
+        walk(a, fn, seen)
+    fn(e)
+
+
+def has_qnn(e):
+    found = []
+    walk(e, lambda n: found.append(1) if n.op.startswith("qnn.") else None)
+    return bool(found)
+
+
+def to_ir(e, memo):
+    """shim expression -> tachikoma_b200.relay expression"""
+    if id(e) in memo:
+        return memo[id(e)]
+    a = [to_ir(x, memo) for x in e.args]
+    at = e.attrs
+    if e.op == "var":
+        r = R.var(e.name, e.shape, e.dtype)
+    elif e.op == "const":
+        r = R.Constant(e.value)
+    elif e.op == "qnn.requantize":
+        r = R.qnn_requantize(a[0], a[1], a[2], a[3], a[4], **at)
+    elif e.op == "qnn.dense":
+        r = R.qnn_dense(a[0], a[1], a[2], a[3], a[4], a[5], **at)
+    elif e.op == "qnn.batch_matmul":
+        r = R.qnn_batch_matmul(a[0], a[1], a[2], a[3], a[4], a[5], **at)
+    elif e.op == "qnn.add":
+        r = R.qnn_add(*a, **at)
+    elif e.op == "qnn.conv2d":
+        for z in a[2:6]:
+            if not isinstance(z, R.Constant):
+                raise Unsupported("non-constant qnn parameter")
+        r = R.qnn_conv2d(a[0], a[1], a[2], a[3], a[4], a[5], **at)
+    elif e.op == "nn.bias_add":
+        r = R.bias_add(a[0], a[1], **at)
+    else:
+        raise Unsupported(f"op {e.op} in qnn graph")
+    memo[id(e)] = r
+    return r
+
+
+# ---------------------------------------------------------- plain numpy evaluator (reference funcs)
+def np_conv2d_int32(data, kernel, strides, padding, dilation, groups, data_layout, kernel_layout):
+    d = np.transpose(data, [data_layout.index(c) for c in "NCHW"]).astype(np.int64)
+    if kernel_layout == "HWOI":  # depthwise: [H,W,C,M] -> [C*M,1,H,W]
+        kh, kw, c_, m_ = kernel.shape
+        k = kernel.transpose(2, 3, 0, 1).reshape(c_ * m_, 1, kh, kw).astype(np.int64)
+    else:
+        k = np.transpose(kernel, [kernel_layout.index(c) for c in "OIHW"]).astype(np.int64)
+    pad = list(padding)
+    if len(pad) == 2:
+        pad = [pad[0], pad[1], pad[0], pad[1]]
+    d = np.pad(d, ((0, 0), (0, 0), (pad[0], pad[2]), (pad[1], pad[3])))
+    N, C, H, W = d.shape
+    O, I, KH, KW = k.shape
+    sh, sw = strides
+    dh, dw = dilation
+    OH = (H - (KH - 1) * dh - 1) // sh + 1
+    OW = (W - (KW - 1) * dw - 1) // sw + 1
+    out = np.zeros((N, O, OH, OW), dtype=np.int64)
+    og = O // groups
+    for o in range(O):
+        g = o // og
+        for r in range(KH):
+            for s in range(KW):
+                patch = d[:, g * I:(g + 1) * I, r * dh:r * dh + (OH - 1) * sh + 1:sh,
+                          s * dw:s * dw + (OW - 1) * sw + 1:sw]
+                out[:, o] += np.einsum("nchw,c->nhw", patch, k[o, :, r, s])
+    out = out.astype(np.int32)  # wraps like int32 arithmetic
+    return np.ascontiguousarray(np.transpose(out, ["NCHW".index(c) for c in data_layout]))
+
+
+def np_eval(e, env, memo):
+    if id(e) in memo:
+        return memo[id(e)]
+    a = [np_eval(x, env, memo) for x in e.args]
+    if e.op == "var":
+        r = np.asarray(env[e.name]).astype(e.dtype)
+    elif e.op == "const":
+        r = e.value
+    elif e.op == "cast":
+        r = a[0].astype(e.attrs["dtype"])
+    elif e.op == "subtract":
+        r = (a[0] - a[1]).astype(a[0].dtype)
+    elif e.op == "add":
+        r = (a[0] + a[1]).astype(a[0].dtype)
+    elif e.op == "multiply":
+        r = (a[0] * a[1]).astype(a[0].dtype)
+    elif e.op == "reshape":
+        r = a[0].reshape(e.attrs["newshape"])
+    elif e.op == "nn.conv2d":
+        at = e.attrs
+        r = np_conv2d_int32(a[0], a[1], at["strides"], at["padding"], at["dilation"], at["groups"],
+                            at["data_layout"], at["kernel_layout"])
+    else:
+        raise Unsupported(f"np_eval {e.op}")
+    memo[id(e)] = r
+    return r
+
+
+# -------------------------------------------------------------------------------- capture machinery
+class Sentinel:
+    def __init__(self, func, inputs):
+        self.func, self.inputs = func, inputs
+        self.dtype = func.body.dtype  # tests assert res.dtype == expected
+
+    def numpy(self):
+        return self
+
+
+def enc(arr):
+    arr = np.asarray(arr)
+    d = dict(shape=list(arr.shape), dtype=str(arr.dtype))
+    arr = np.ascontiguousarray(arr)
+    flat = arr.reshape(-1)
+    if flat.size and np.all(flat == flat[0]) and flat.size > 16:
+        d["fill"] = flat[0].item()
+    elif flat.size <= 64:
+        d["data"] = flat.tolist()
+    else:
+        d["b64"] = base64.b64encode(arr.tobytes()).decode()
+    return d
+
+
+def capture(sent, golden):
+    func = sent.func
+    golden = np.asarray(golden)
+    d = R.to_dict(func)
+    for n in d["nodes"]:
+        if n["kind"] == "const":
+            arr = np.array(n.pop("data"), dtype=n["dtype"]).reshape(n["shape"])
+            n.update({k: v for k, v in enc(arr).items() if k not in ("shape", "dtype")})
+    CASES.append(dict(source=CURRENT["name"], graph=d,
+                      inputs={k: enc(np.asarray(v)) for k, v in sent.inputs.items()},
+                      golden=enc(golden.astype(func.body.dtype).reshape(func.body.shape))))
+
+
+class Module:  # IRModule / Function stand-in
+    def __init__(self, params, body):
+        self.params, self.body = params, body
+
+    def __getitem__(self, _):
+        return self
+
+    def astext(self):
+        return ""
+
+
+class Executor:
+    def __init__(self, mod, bound):
+        self.mod, self.env = mod, dict(bound)
+
+    def set_input(self, *a, **kw):
+        if a:
+            self.env[a[0]] = np.asarray(a[1])
+        self.env.update({k: np.asarray(v) for k, v in kw.items()})
+
+    def run(self):
+        pass
+
+    def get_output(self, _):
+        return self._result()
+
+    def _result(self):
+        body = self.mod.body
+        if has_qnn(body):
+            memo = {}
+            ir_body = to_ir(body, memo)
+            params = [memo[id(p)] for p in self.mod.params if id(p) in memo]
+            func = R.Function(params, ir_body)
+            consts = {p.name: self.env[p.name] for p in params if p.name in ("kernel",) and p.name in self.env}
+            if consts:  # relay.build(params={"kernel": ...}) binds the weight as a constant
+                func = R.bind_params(func, consts)
+            inputs = {p.name: np.asarray(self.env[p.name]).astype(p.dtype) for p in func.params}
+            return Sentinel(func, inputs)
+        out = np_eval(body, self.env, {})
+
+        class _W:
+            def numpy(_s):
+                return out
+        return _W()
+
+    def evaluate(self, func):
+        def call(*vals):
+            for p, v in zip(func.params, vals):
+                self.env[p.name] = np.asarray(v)
+            self.mod = func
+            return self._result()
+        return call
+
+
+def install_shim():
+    tvm = types.ModuleType("tvm")
+    relay = types.ModuleType("tvm.relay")
+    tvm.relay = relay
+    tvm.te = types.ModuleType("tvm.te")
+    tvm.cpu = lambda *_: None
+
+    class IRModule:
+        @staticmethod
+        def from_expr(f):
+            return f
+    tvm.IRModule = IRModule
+    tvm.transform = types.SimpleNamespace(PassContext=lambda **kw: contextlib.nullcontext())
+
+    relay.var, relay.const = s_var, s_const
+    relay.Function = lambda params, body: Module(list(params), body)
+
+    def free_vars(e):
+        out = []
+        walk(e, lambda n: out.append(n) if n.op == "var" else None)
+        return out
+    relay.analysis = types.SimpleNamespace(free_vars=free_vars)
+    ident = lambda: (lambda m: m)
+    relay.transform = types.SimpleNamespace(InferType=ident, FoldConstant=ident)
+    relay.add = lambda a, b: S("add", [a, _lift(b)])
+    relay.reshape = lambda a, newshape: S("reshape", [a], dict(newshape=list(newshape)))
+
+    def build(mod, target=None, params=None):
+        return (mod, None, dict(params or {}))
+    relay.build = build
+
+    def create_executor(kind="graph", device=None, target=None, mod=None):
+        return Executor(None, {})
+    relay.create_executor = create_executor
+
+    def q_requantize(data, input_scale, input_zero_point, output_scale, output_zero_point, axis=-1,
+                     rounding="None", compute_dtype="None", out_dtype="int8"):
+        # src/relay/qnn/utils.cc:231-245 SelectRequntizeParameter: the op attribute wins, "None" takes the
+        # value of the enclosing requantize_config scope (defaults UPWARD / int64).
+        if rounding == "None" and RQ_CFG["rounding"] is not None:
+            rounding = RQ_CFG["rounding"]
+        if compute_dtype == "None" and RQ_CFG["compute_dtype"] is not None:
+            compute_dtype = RQ_CFG["compute_dtype"]
+        return S("qnn.requantize", [data, input_scale, input_zero_point, output_scale, output_zero_point],
+                 dict(axis=axis, rounding=rounding, compute_dtype=compute_dtype, out_dtype=out_dtype))
+
+    def q_dense(data, weight, input_zero_point, kernel_zero_point, input_scale, kernel_scale, units,
+                out_dtype="int32"):
+        return S("qnn.dense", [data, weight, input_zero_point, kernel_zero_point, input_scale, kernel_scale],
+                 dict(units=units, out_dtype=out_dtype))
+
+    def q_bmm(x, y, x_zero_point, y_zero_point, x_scale, y_scale, out_dtype="int32"):
+        return S("qnn.batch_matmul", [x, y, x_zero_point, y_zero_point, x_scale, y_scale], dict(out_dtype=out_dtype))
+
+    def q_add(lhs, rhs, lhs_scale, lhs_zero_point, rhs_scale, rhs_zero_point, output_scale, output_zero_point,
+              lhs_axis=-1, rhs_axis=-1):
+        return S("qnn.add", [lhs, rhs, lhs_scale, lhs_zero_point, rhs_scale, rhs_zero_point, output_scale,
+                             output_zero_point], dict(lhs_axis=lhs_axis, rhs_axis=rhs_axis))
+
+    def q_conv2d(data, kernel, input_zero_point, kernel_zero_point, input_scale, kernel_scale, kernel_size,
+                 channels, strides=(1, 1), padding=(0, 0), dilation=(1, 1), groups=1, data_layout="NCHW",
+                 kernel_layout="OIHW", out_layout="", out_dtype="int32"):
+        if channels is None:
+            ks = tuple(kernel.shape)
+            channels = ks[2] * ks[3] if kernel_layout == "HWOI" else ks[kernel_layout.index("O")]
+        return S("qnn.conv2d", [data, kernel, input_zero_point, kernel_zero_point, input_scale, kernel_scale],
+                 dict(kernel_size=list(kernel_size), channels=int(channels), strides=list(strides),
+                      padding=list(padding), dilation=list(dilation), groups=int(groups), data_layout=data_layout,
+                      kernel_layout=kernel_layout, out_layout=out_layout, out_dtype=out_dtype))
+
+    @contextlib.contextmanager
+    def requantize_config(rounding=None, compute_dtype=None):
+        old = dict(RQ_CFG)
+        RQ_CFG.update(rounding=rounding, compute_dtype=compute_dtype)
+        try:
+            yield
+        finally:
+            RQ_CFG.update(old)
+
+    qop = types.SimpleNamespace(requantize=q_requantize, dense=q_dense, batch_matmul=q_bmm, add=q_add,
+                                conv2d=q_conv2d, requantize_config=requantize_config)
+    relay.qnn = types.SimpleNamespace(op=qop, transform=types.SimpleNamespace(CanonicalizeOps=ident))
+
+    def nn_conv2d(data, weight, strides=(1, 1), padding=(0, 0), dilation=(1, 1), groups=1, channels=None,
+                  kernel_size=None, data_layout="NCHW", kernel_layout="OIHW", out_layout="", out_dtype=""):
+        return S("nn.conv2d", [data, weight], dict(strides=list(strides), padding=list(padding),
+                 dilation=list(dilation), groups=groups, data_layout=data_layout, kernel_layout=kernel_layout))
+    nn = types.SimpleNamespace(bias_add=lambda d, b, axis=1: S("nn.bias_add", [d, b], dict(axis=axis)),
+                               conv2d=nn_conv2d)
+    relay.nn = nn
+    relay.op = types.SimpleNamespace(cast=lambda d, dtype: S("cast", [d], dict(dtype=dtype)),
+                                     subtract=lambda a, b: S("subtract", [a, _lift(b)]),
+                                     multiply=lambda a, b: S("multiply", [a, _lift(b)]), nn=nn)
+    testing = types.ModuleType("tvm.relay.testing")
+    testing.run_infer_type = lambda e: e
+    toa = types.ModuleType("tvm.relay.testing.temp_op_attr")
+    toa.TempOpAttr = lambda *a, **k: contextlib.nullcontext()
+    testing.temp_op_attr = toa
+    relay.testing = testing
+    contrib = types.ModuleType("tvm.contrib")
+    ge = types.ModuleType("tvm.contrib.graph_executor")
+    ge.create = lambda graph, lib, device=None: Executor(graph, {})
+    contrib.graph_executor = ge
+    tvm.contrib = contrib
+    tvm.testing = types.SimpleNamespace(main=lambda: None)
+    for name, mod in {"tvm": tvm, "tvm.relay": relay, "tvm.te": tvm.te, "tvm.relay.testing": testing,
+                      "tvm.relay.testing.temp_op_attr": toa, "tvm.contrib": contrib,
+                      "tvm.contrib.graph_executor": ge, "tvm.relay.transform": types.ModuleType("tvm.relay.transform")}.items():
+        sys.modules[name] = mod
+    relay.transform_mod = sys.modules["tvm.relay.transform"]
+
+
+def main():
+    install_shim()
+    real_assert_equal = np.testing.assert_equal
+
+    def patched(actual, desired, *a, **k):
+        if isinstance(actual, Sentinel):
+            capture(actual, desired)
+            return
+        if isinstance(desired, Sentinel):
+            capture(desired, actual)
+            return
+        return real_assert_equal(actual, desired, *a, **k)
+    np.testing.assert_equal = patched
+    np.random.seed(20240229)
+    for fname in FILES:
+        spec = importlib.util.spec_from_file_location("ref_" + fname[:-3], os.path.join(REF_TESTS, fname))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        for tname in [n for n in dir(mod) if n.startswith("test_")]:
+            CURRENT["name"] = f"tests/python/relay/{fname}::{tname}"
+            before = len(CASES)
+            try:
+                getattr(mod, tname)()
+            except Unsupported as ex:
+                SKIPPED.append(dict(source=CURRENT["name"], why=str(ex), captured_before_skip=len(CASES) - before))
+            except Exception as ex:  # the shim does not cover everything; say so
+                SKIPPED.append(dict(source=CURRENT["name"], why=f"{type(ex).__name__}: {ex}",
+                                    captured_before_skip=len(CASES) - before))
+    out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "qnn_reference_goldens.json")
+    with open(out, "w") as f:
+        json.dump(dict(generator="tests/golden/gen_from_reference_tests.py", reference_commit="7cc8e9f",
+                       cases=CASES, skipped=SKIPPED), f)
+    print(f"{len(CASES)} cases, {len(SKIPPED)} tests skipped/partial -> {out}")
+    for s in SKIPPED:
+        print("  skipped:", s["source"], "|", s["why"][:100], "| kept", s["captured_before_skip"])
+
+
+if __name__ == "__main__":
+    main()

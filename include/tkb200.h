@@ -1,0 +1,118 @@
+/*
+ * tkb200.h -- C ABI of libtkb200.so, the B200-native drop-in for the tachikoma BYOC JSON runtime.
+ *
+ * Every entry point replaces one interface of the reference (paths relative to the
+ * CortexFoundation/tachikoma tree):
+ *
+ *   tkb_create            runtime.TachikomaJSONRuntimeCreate(symbol, graph_json, const_names)
+ *                         src/runtime/contrib/tachikoma/tachikoma_json_runtime.cc:900-906
+ *   tkb_load_binary       runtime.module.loadbinary_tachikoma_json          :908-909
+ *   tkb_save_binary       JSONRuntimeBase::SaveToBinary   src/runtime/contrib/json/json_runtime.h:105-115
+ *   tkb_get_symbol        PackedFunc "get_symbol"                           json_runtime.h:74-76
+ *   tkb_get_const_vars    PackedFunc "get_const_vars"                       json_runtime.h:77-79
+ *   tkb_init              PackedFunc "__init_<symbol>"(Array<NDArray>)      json_runtime.h:89-99,
+ *                         TachikomaJSONRuntime::Init + BuildEngine  tachikoma_json_runtime.cc:64-71,:240-290
+ *   tkb_run               PackedFunc "<symbol>"(in_0..in_k-1, out_0..out_m-1), thread-safe Run(args) const
+ *                         tachikoma_json_runtime.cc:77-106
+ *   tkb_last_error        TVMGetLastError()               include/tvm/runtime/c_runtime_api.h:238-249
+ *   tkb_packed_run        TVMBackendPackedCFunc-shaped shim include/tvm/runtime/c_backend_api.h:49-51
+ *   tkb_trace_*           the per-operator trace the reference describes (README.md:6) but does not
+ *                         ship; container = TVM NDArray-list blob, src/runtime/file_utils.cc:210-229,
+ *                         include/tvm/runtime/ndarray.h:449-494 (see DESIGN.md "Trace").
+ *
+ * Conventions (same as the reference's C API): every function returns 0 on success and -1 on
+ * failure; the message is available from tkb_last_error() (thread local).  Unsupported operators
+ * fail in tkb_init ("Unsupported op: <name>", tachikoma_json_runtime.cc:286) -- there is no CPU
+ * fallback.  Tensors are DLPack DLTensor (3rdparty/dlpack/include/dlpack/dlpack.h:187-200), must be
+ * compact (strides == NULL, tachikoma_json_runtime.cc:820) and may live on the host (kDLCPU,
+ * kDLCUDAHost) or on the current CUDA device (kDLCUDA); host tensors are staged through pinned
+ * buffers with cudaMemcpyAsync on the caller's stream.
+ */
+#ifndef TKB200_H_
+#define TKB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* --- DLPack (ABI-compatible restatement so that no TVM/DLPack header is needed) ------------- */
+typedef enum { tkbDLCPU = 1, tkbDLCUDA = 2, tkbDLCUDAHost = 3 } tkb_device_type;
+typedef struct { int32_t device_type; int32_t device_id; } tkb_DLDevice;
+typedef struct { uint8_t code; uint8_t bits; uint16_t lanes; } tkb_DLDataType; /* code: 0 int, 1 uint, 2 float */
+typedef struct {
+  void* data;
+  tkb_DLDevice device;
+  int32_t ndim;
+  tkb_DLDataType dtype;
+  int64_t* shape;
+  int64_t* strides; /* must be NULL (compact row-major) */
+  uint64_t byte_offset;
+} tkb_DLTensor;
+
+typedef struct tkb_runtime* tkb_handle;
+
+/* --- module life cycle ---------------------------------------------------------------------- */
+int tkb_create(const char* symbol, const char* graph_json, const char* const* const_names, int n_consts,
+               tkb_handle* out);
+int tkb_free(tkb_handle h);
+/* blob = dmlc stream {string symbol; string graph_json; vector<string> const_names} (u64 length prefixes) */
+int tkb_save_binary(tkb_handle h, const void** blob, size_t* len); /* blob owned by h */
+int tkb_load_binary(const void* blob, size_t len, tkb_handle* out);
+const char* tkb_type_key(void); /* "tachikoma_json" */
+
+/* --- module functions ------------------------------------------------------------------------ */
+const char* tkb_get_symbol(tkb_handle h);
+int tkb_get_const_vars(tkb_handle h, const char* const** names, int* n);
+int tkb_num_inputs(tkb_handle h);
+int tkb_num_outputs(tkb_handle h);
+/* Bind constants (in const_names order), build the execution plan, upload + repack weights.
+ * Idempotent and mutex-guarded like "__init_<symbol>". */
+int tkb_init(tkb_handle h, const tkb_DLTensor* const* consts, int n_consts);
+/* args = inputs (graph input order) followed by caller-allocated outputs; n_args must equal
+ * #inputs + #outputs.  cuda_stream is a cudaStream_t (NULL = default stream).  Re-entrant from
+ * several host threads provided each uses its own stream. */
+int tkb_run(tkb_handle h, const tkb_DLTensor* const* args, int n_args, void* cuda_stream);
+/* TVMBackendPackedCFunc-shaped entry: args[0] = module handle (void*), args[1..] = DLTensor*.
+ * type codes: 3 = kTVMOpaqueHandle, 7 = kTVMDLTensorHandle, 13 = kTVMNDArrayHandle. */
+int tkb_packed_run(void* args, int* type_codes, int num_args, void* out_ret_value, int* out_ret_tcode,
+                   void* resource_handle);
+
+const char* tkb_last_error(void);
+
+/* --- options / introspection ------------------------------------------------------------------ */
+/* Known keys: "conv_impl" = "auto"|"simt"|"tc" (tensor-core tcgen05 path vs CUDA-core path),
+ *             "trace_acc" = "0"|"1" (also record int32 accumulators of composites). */
+int tkb_set_option(tkb_handle h, const char* key, const char* value);
+/* Number of kernels this library launched on behalf of h since creation (bench.py "gpu_launches"). */
+int64_t tkb_launch_count(tkb_handle h);
+/* Human-readable plan: one line per kernel node with the kernel chosen and its algorithmic work. */
+const char* tkb_plan_summary(tkb_handle h);
+/* Total int8 multiply-accumulates and algorithmic HBM bytes of one run (roofline numerators). */
+int tkb_work(tkb_handle h, int64_t* macs, int64_t* hbm_bytes);
+
+/* --- per-operator trace ------------------------------------------------------------------------
+ * mode 0 = off, 1 = capture every kernel node's inputs/outputs into a device ring (D2D),
+ * 2 = additionally stream the ring to pinned host memory on a side stream.  After a run in mode 2,
+ * tkb_trace_save writes the NDArray-list blob; tkb_trace_bytes reports its payload size. */
+int tkb_trace_enable(tkb_handle h, int mode);
+int tkb_trace_sync(tkb_handle h);
+int tkb_trace_save(tkb_handle h, const char* path);
+int tkb_trace_blob(tkb_handle h, const void** blob, size_t* len); /* serialized in memory, owned by h */
+int64_t tkb_trace_bytes(tkb_handle h);
+
+/* --- stand-alone helpers (used by tests and tools) -------------------------------------------- */
+/* GetFixedPointMultiplierShift, src/relay/qnn/utils.cc:33-57 (host, double). */
+void tkb_fixed_point_multiplier_shift(double multiplier, int32_t* significand, int32_t* exponent);
+/* Dense int8 tcgen05 peak probe: issues back-to-back kind::i8 MMAs from resident smem tiles on all
+ * SMs; returns achieved tera-ops/s (2*MAC) in *tops.  Roofline denominator for conv/dense. */
+int tkb_probe_int8_peak(int iters, double* tops, void* cuda_stream);
+/* Library build info: "sm_100a;<n kernels>;..." */
+const char* tkb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TKB200_H_ */

@@ -1,0 +1,64 @@
+// Internal host-side launch API of the CUDA kernels (kernels_simt.cu, kernels_tc.cu).
+// All activations are channels-last ("NHWC") unless a stride array says otherwise.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "epilogue.cuh"
+
+namespace tkb {
+
+struct ConvGeom {
+  int N, H, W, C;          // input, channels-last
+  int O, KH, KW, groups;   // weights OHWI: [O][KH][KW][C/groups]
+  int sh, sw, pt, pl, pb, pr, dh, dw;
+  int OH, OW;
+  int a_dtype, w_dtype;    // kI8 / kU8
+  int32_t zp_a;            // input zero point (padding value)
+  const int32_t* zp_w;     // device [O] or nullptr -> zp_w0
+  int32_t zp_w0;
+};
+
+// ---- CUDA-core kernels (complete coverage; the fallback for every shape) ----------------------
+void launch_conv2d_simt(const void* x, const void* w, void* y, const ConvGeom& g, const EpiParams& e,
+                        cudaStream_t s);
+// Y[b,m,n] = sum_k (X[b,m,k]-zpx)(W[b?,n,k]-zpw); w_batched: W has a batch dim of B, else shared.
+void launch_gemm_simt(const void* x, const void* w, void* y, int B, int M, int N, int K, int w_batched,
+                      int x_dtype, int w_dtype, int32_t zpx, int32_t zpw, const EpiParams& e, cudaStream_t s);
+// elementwise over [outer][C][inner]
+void launch_requantize(const void* x, int x_dtype, void* y, int y_dtype, long long outer, int C, long long inner,
+                       const RqParams& p, cudaStream_t s);
+void launch_qnn_add(const void* a, const void* b, void* y, int dtype, long long n, const EpiParams& e,
+                    cudaStream_t s);
+void launch_clip(const void* x, void* y, int dtype, long long n, double lo, double hi, cudaStream_t s);
+void launch_cast(const void* x, int x_dtype, void* y, int y_dtype, long long n, cudaStream_t s);
+// y = x + b[c] (int32 wrap / same dtype) over [outer][C][inner]; b has C elements of dtype b_dtype
+void launch_bias_add(const void* x, const void* b, void* y, int dtype, long long outer, int C, long long inner,
+                     cudaStream_t s);
+void launch_add_same(const void* a, const void* b, void* y, int dtype, long long n, cudaStream_t s);
+// pooling with explicit element strides (n,c,h,w) for input and output
+void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_include_pad, int N, int C, int H, int W,
+                   int KH, int KW, int sh, int sw, int pt, int pl, int pb, int pr, const long long* xs,
+                   const long long* ys, cudaStream_t s);
+// generic 4-D permute copy: out[i0,i1,i2,i3] (dense) = in[... strides]; elem = 1/2/4 bytes
+void launch_permute4(const void* x, void* y, int elem, const long long* out_shape, const long long* in_strides,
+                     cudaStream_t s);
+// constant pad of a dense tensor up to rank 4 (shape padded to 4 dims)
+void launch_pad4(const void* x, void* y, int elem, const long long* in_shape, const long long* pad_before,
+                 const long long* out_shape, int32_t value, cudaStream_t s);
+
+// im2col into a [N*OH*OW][Kp] matrix (Kp >= KH*KW*C, multiple of 16) for the tensor-core GEMM path
+void launch_im2col(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream_t s);
+
+// ---- tcgen05 kernels ---------------------------------------------------------------------------
+// GEMM on the 5th-gen tensor cores: Y[M,N] = epilogue(X[M,K] . W[N,K]^T), X/W int8 or uint8, K-major.
+// Requirements (checked by tc_gemm_supported): K % 16 == 0, pointers 16B aligned, zp_w == 0.
+bool tc_gemm_supported(int M, int N, int K);
+int launch_gemm_tc(const void* x, const void* w, void* y, int B, int M, int N, int K, int w_batched, int x_dtype,
+                   int w_dtype, const EpiParams& e, cudaStream_t s);
+int probe_int8_peak(int iters, double* tops, cudaStream_t s);
+
+extern thread_local long long g_launches;  // kernels launched by this thread (summed per handle)
+
+}  // namespace tkb

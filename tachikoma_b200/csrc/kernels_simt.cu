@@ -1,0 +1,462 @@
+// CUDA-core kernels: complete-coverage implementations of every operator on the QNN hot path.
+// They are the path for shapes the tcgen05 kernels do not take (grouped / depthwise / dilated
+// convolutions, non-zero weight zero points, K not a multiple of 16) and for the HBM-bound
+// elementwise operators.  Arithmetic follows epilogue.cuh (bit-exact TVM integer lowering).
+#include <cstdio>
+
+#include "kernels.h"
+
+namespace tkb {
+
+thread_local long long g_launches = 0;
+
+static inline int blocks_for(long long n, int threads) {
+  long long b = (n + threads - 1) / threads;
+  const long long cap = 148LL * 32;  // grid-stride beyond 32 CTAs per SM
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+template <bool A_UNSIGNED, bool W_UNSIGNED>
+__device__ __forceinline__ int dp4a_mixed(uint32_t a, uint32_t w, int c) {
+  int d;
+  if (A_UNSIGNED && W_UNSIGNED) asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(w), "r"(c));
+  else if (A_UNSIGNED) asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(w), "r"(c));
+  else if (W_UNSIGNED) asm("dp4a.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(w), "r"(c));
+  else asm("dp4a.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(w), "r"(c));
+  return d;
+}
+
+// Direct convolution, one thread per output element (n, oy, ox, o), o fastest.
+// acc = sum over in-image taps of (a - zp_a)(w - zp_w)  (src/relay/qnn/op/convolution.cc:708-811;
+// out-of-image taps read zp_a and contribute 0, :227-253).
+template <bool AU, bool WU>
+__global__ void conv2d_simt_kernel(const uint8_t* __restrict__ x, const uint8_t* __restrict__ w, void* __restrict__ y,
+                                   ConvGeom g, EpiParams e) {
+  const int Cg = g.C / g.groups, Og = g.O / g.groups;
+  const long long total = (long long)g.N * g.OH * g.OW * g.O;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int o = (int)(idx % g.O);
+    long long t = idx / g.O;
+    const int ox = (int)(t % g.OW);
+    t /= g.OW;
+    const int oy = (int)(t % g.OH);
+    const int n = (int)(t / g.OH);
+    const int grp = o / Og;
+    const int32_t zw = g.zp_w ? g.zp_w[o] : g.zp_w0;
+    int raw = 0, sum_a = 0, sum_w = 0, taps = 0;
+    for (int r = 0; r < g.KH; ++r) {
+      const int iy = oy * g.sh + r * g.dh - g.pt;
+      if (iy < 0 || iy >= g.H) continue;
+      for (int s = 0; s < g.KW; ++s) {
+        const int ix = ox * g.sw + s * g.dw - g.pl;
+        if (ix < 0 || ix >= g.W) continue;
+        const uint8_t* ap = x + (((long long)n * g.H + iy) * g.W + ix) * g.C + grp * Cg;
+        const uint8_t* wp = w + (((long long)o * g.KH + r) * g.KW + s) * Cg;
+        int c = 0;
+        if ((Cg & 3) == 0 && ((((uintptr_t)ap) | ((uintptr_t)wp)) & 3) == 0) {
+          for (; c < Cg; c += 4) {
+            const uint32_t av = *(const uint32_t*)(ap + c), wv = *(const uint32_t*)(wp + c);
+            raw = dp4a_mixed<AU, WU>(av, wv, raw);
+            sum_a = dp4a_mixed<AU, false>(av, 0x01010101u, sum_a);
+            sum_w = dp4a_mixed<false, WU>(0x01010101u, wv, sum_w);
+          }
+        } else {
+          for (; c < Cg; ++c) {
+            const int av = AU ? (int)ap[c] : (int)(int8_t)ap[c];
+            const int wv = WU ? (int)wp[c] : (int)(int8_t)wp[c];
+            raw += av * wv;
+            sum_a += av;
+            sum_w += wv;
+          }
+        }
+        taps += Cg;
+      }
+    }
+    // sum (a-za)(w-zw) = raw - za*sum_w - zw*sum_a + taps*za*zw   (int32 ring arithmetic)
+    const uint32_t acc = (uint32_t)raw - (uint32_t)g.zp_a * (uint32_t)sum_w - (uint32_t)zw * (uint32_t)sum_a +
+                         (uint32_t)taps * (uint32_t)g.zp_a * (uint32_t)zw;
+    store_from_i32(y, e.out_dtype, idx, epilogue_one((int32_t)acc, o, idx, e));
+  }
+}
+
+void launch_conv2d_simt(const void* x, const void* w, void* y, const ConvGeom& g, const EpiParams& e,
+                        cudaStream_t s) {
+  const long long total = (long long)g.N * g.OH * g.OW * g.O;
+  const int th = 256, bl = blocks_for(total, th);
+  const uint8_t* xp = (const uint8_t*)x;
+  const uint8_t* wp = (const uint8_t*)w;
+  const bool au = g.a_dtype == kU8, wu = g.w_dtype == kU8;
+  if (au && wu) conv2d_simt_kernel<true, true><<<bl, th, 0, s>>>(xp, wp, y, g, e);
+  else if (au) conv2d_simt_kernel<true, false><<<bl, th, 0, s>>>(xp, wp, y, g, e);
+  else if (wu) conv2d_simt_kernel<false, true><<<bl, th, 0, s>>>(xp, wp, y, g, e);
+  else conv2d_simt_kernel<false, false><<<bl, th, 0, s>>>(xp, wp, y, g, e);
+  ++g_launches;
+}
+
+// GEMM fallback (qnn.dense dense.cc:160-205, qnn.batch_matmul batch_matmul.cc:161-200): one warp per
+// output row-tile would be faster; this is the correctness path for odd K / non-zero weight zp.
+template <bool AU, bool WU>
+__global__ void gemm_simt_kernel(const uint8_t* __restrict__ x, const uint8_t* __restrict__ w, void* __restrict__ y,
+                                 int B, int M, int N, int K, int w_batched, int32_t zpx, int32_t zpw, EpiParams e) {
+  const long long total = (long long)B * M * N;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(idx % N);
+    const long long bm = idx / N;
+    const int b = (int)(bm / M);
+    const uint8_t* ap = x + bm * K;
+    const uint8_t* wp = w + ((long long)(w_batched ? b : 0) * N + n) * K;
+    int raw = 0, sum_a = 0, sum_w = 0;
+    int k = 0;
+    if ((K & 3) == 0 && ((((uintptr_t)ap) | ((uintptr_t)wp)) & 3) == 0) {
+      for (; k < K; k += 4) {
+        const uint32_t av = *(const uint32_t*)(ap + k), wv = *(const uint32_t*)(wp + k);
+        raw = dp4a_mixed<AU, WU>(av, wv, raw);
+        sum_a = dp4a_mixed<AU, false>(av, 0x01010101u, sum_a);
+        sum_w = dp4a_mixed<false, WU>(0x01010101u, wv, sum_w);
+      }
+    } else {
+      for (; k < K; ++k) {
+        const int av = AU ? (int)ap[k] : (int)(int8_t)ap[k];
+        const int wv = WU ? (int)wp[k] : (int)(int8_t)wp[k];
+        raw += av * wv;
+        sum_a += av;
+        sum_w += wv;
+      }
+    }
+    const uint32_t acc = (uint32_t)raw - (uint32_t)zpx * (uint32_t)sum_w - (uint32_t)zpw * (uint32_t)sum_a +
+                         (uint32_t)K * (uint32_t)zpx * (uint32_t)zpw;
+    store_from_i32(y, e.out_dtype, idx, epilogue_one((int32_t)acc, n, idx, e));
+  }
+}
+
+void launch_gemm_simt(const void* x, const void* w, void* y, int B, int M, int N, int K, int w_batched,
+                      int x_dtype, int w_dtype, int32_t zpx, int32_t zpw, const EpiParams& e, cudaStream_t s) {
+  const long long total = (long long)B * M * N;
+  const int th = 256, bl = blocks_for(total, th);
+  const uint8_t* xp = (const uint8_t*)x;
+  const uint8_t* wp = (const uint8_t*)w;
+  const bool au = x_dtype == kU8, wu = w_dtype == kU8;
+  if (au && wu) gemm_simt_kernel<true, true><<<bl, th, 0, s>>>(xp, wp, y, B, M, N, K, w_batched, zpx, zpw, e);
+  else if (au) gemm_simt_kernel<true, false><<<bl, th, 0, s>>>(xp, wp, y, B, M, N, K, w_batched, zpx, zpw, e);
+  else if (wu) gemm_simt_kernel<false, true><<<bl, th, 0, s>>>(xp, wp, y, B, M, N, K, w_batched, zpx, zpw, e);
+  else gemm_simt_kernel<false, false><<<bl, th, 0, s>>>(xp, wp, y, B, M, N, K, w_batched, zpx, zpw, e);
+  ++g_launches;
+}
+
+__global__ void requantize_kernel(const void* __restrict__ x, int x_dtype, void* __restrict__ y, int y_dtype,
+                                  long long total, int C, long long inner, RqParams p) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)((i / inner) % C);
+    int32_t v;
+    if (x_dtype == kI64) v = (int32_t)((const long long*)x)[i];
+    else v = load_as_i32(x, x_dtype, i);
+    store_from_i32(y, y_dtype, i, requantize_one(v, c, p));
+  }
+}
+
+void launch_requantize(const void* x, int x_dtype, void* y, int y_dtype, long long outer, int C, long long inner,
+                       const RqParams& p, cudaStream_t s) {
+  const long long total = outer * C * inner;
+  if (total == 0) return;
+  requantize_kernel<<<blocks_for(total, 256), 256, 0, s>>>(x, x_dtype, y, y_dtype, total, C, inner, p);
+  ++g_launches;
+}
+
+// qnn.add, HBM-bound: 16 bytes per thread per operand for the 8-bit dtypes.
+__global__ void qnn_add_kernel(const void* __restrict__ a, const void* __restrict__ b, void* __restrict__ y,
+                               int dtype, long long n, EpiParams e) {
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  if ((dtype == kU8 || dtype == kI8) && (n & 15) == 0 &&
+      ((((uintptr_t)a) | ((uintptr_t)b) | ((uintptr_t)y)) & 15) == 0) {
+    const long long nv = n >> 4;
+    for (long long i = tid; i < nv; i += stride) {
+      const uint4 va = ((const uint4*)a)[i], vb = ((const uint4*)b)[i];
+      uint4 vo;
+      const uint32_t* pa = (const uint32_t*)&va;
+      const uint32_t* pb = (const uint32_t*)&vb;
+      uint32_t* po = (uint32_t*)&vo;
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        uint32_t o = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint32_t ba = (pa[w] >> (8 * k)) & 0xFF, bb = (pb[w] >> (8 * k)) & 0xFF;
+          const int32_t xa = dtype == kU8 ? (int32_t)ba : (int32_t)(int8_t)ba;
+          const int32_t xb = dtype == kU8 ? (int32_t)bb : (int32_t)(int8_t)bb;
+          o |= ((uint32_t)qnn_add_one(xa, xb, 0, e) & 0xFF) << (8 * k);
+        }
+        po[w] = o;
+      }
+      ((uint4*)y)[i] = vo;
+    }
+    return;
+  }
+  for (long long i = tid; i < n; i += stride)
+    store_from_i32(y, dtype, i, qnn_add_one(load_as_i32(a, dtype, i), load_as_i32(b, dtype, i), 0, e));
+}
+
+void launch_qnn_add(const void* a, const void* b, void* y, int dtype, long long n, const EpiParams& e,
+                    cudaStream_t s) {
+  if (n == 0) return;
+  const long long work = (dtype == kU8 || dtype == kI8) && (n & 15) == 0 ? n >> 4 : n;
+  qnn_add_kernel<<<blocks_for(work, 256), 256, 0, s>>>(a, b, y, dtype, n, e);
+  ++g_launches;
+}
+
+__global__ void clip_kernel(const void* __restrict__ x, void* __restrict__ y, int dtype, long long n, double lo,
+                            double hi) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    if (dtype == kF32) {
+      float v = ((const float*)x)[i];
+      ((float*)y)[i] = fminf(fmaxf(v, (float)lo), (float)hi);
+    } else {
+      // relay clip on an integer tensor clamps in that dtype (bounds already intersected on the host)
+      int32_t v = load_as_i32(x, dtype, i);
+      const int32_t l = (int32_t)lo, h = (int32_t)hi;
+      store_from_i32(y, dtype, i, v < l ? l : (v > h ? h : v));
+    }
+  }
+}
+
+void launch_clip(const void* x, void* y, int dtype, long long n, double lo, double hi, cudaStream_t s) {
+  if (n == 0) return;
+  clip_kernel<<<blocks_for(n, 256), 256, 0, s>>>(x, y, dtype, n, lo, hi);
+  ++g_launches;
+}
+
+__global__ void cast_kernel(const void* __restrict__ x, int xd, void* __restrict__ y, int yd, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    if (xd == kF32) {
+      float v = ((const float*)x)[i];
+      if (yd == kF32) ((float*)y)[i] = v;
+      else store_from_i32(y, yd, i, (int32_t)v);
+    } else {
+      int32_t v = load_as_i32(x, xd, i);
+      if (yd == kF32) ((float*)y)[i] = (float)v;
+      else store_from_i32(y, yd, i, v);  // truncating, like LLVM trunc / sext / zext
+    }
+  }
+}
+
+void launch_cast(const void* x, int x_dtype, void* y, int y_dtype, long long n, cudaStream_t s) {
+  if (n == 0) return;
+  cast_kernel<<<blocks_for(n, 256), 256, 0, s>>>(x, x_dtype, y, y_dtype, n);
+  ++g_launches;
+}
+
+__global__ void bias_add_kernel(const void* __restrict__ x, const void* __restrict__ b, void* __restrict__ y,
+                                int dtype, long long total, int C, long long inner) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)((i / inner) % C);
+    const uint32_t v = (uint32_t)load_as_i32(x, dtype, i) + (uint32_t)load_as_i32(b, dtype, c);
+    store_from_i32(y, dtype, i, (int32_t)v);
+  }
+}
+
+void launch_bias_add(const void* x, const void* b, void* y, int dtype, long long outer, int C, long long inner,
+                     cudaStream_t s) {
+  const long long total = outer * C * inner;
+  if (total == 0) return;
+  bias_add_kernel<<<blocks_for(total, 256), 256, 0, s>>>(x, b, y, dtype, total, C, inner);
+  ++g_launches;
+}
+
+__global__ void add_same_kernel(const void* __restrict__ a, const void* __restrict__ b, void* __restrict__ y,
+                                int dtype, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    store_from_i32(y, dtype, i, (int32_t)((uint32_t)load_as_i32(a, dtype, i) + (uint32_t)load_as_i32(b, dtype, i)));
+}
+
+void launch_add_same(const void* a, const void* b, void* y, int dtype, long long n, cudaStream_t s) {
+  if (n == 0) return;
+  add_same_kernel<<<blocks_for(n, 256), 256, 0, s>>>(a, b, y, dtype, n);
+  ++g_launches;
+}
+
+struct PoolArgs {
+  int N, C, H, W, KH, KW, sh, sw, pt, pl, pb, pr, OH, OW, is_avg, cip, dtype;
+  long long xs[4], ys[4];
+};
+
+// nn.max_pool2d / nn.avg_pool2d / global pooling on integer tensors
+// (include/tvm/topi/nn/pooling.h:389, :600-650: sum in the tensor dtype, truncating division).
+// Thread order follows the output's fastest-varying dimension so that stores coalesce for both
+// channels-last and NCHW tensors.
+__global__ void pool2d_kernel(const void* __restrict__ x, void* __restrict__ y, PoolArgs a) {
+  const long long total = (long long)a.N * a.C * a.OH * a.OW;
+  const bool c_fast = a.ys[1] == 1;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    int n, c, oy, ox;
+    long long t = idx;
+    if (c_fast) { c = (int)(t % a.C); t /= a.C; ox = (int)(t % a.OW); t /= a.OW; oy = (int)(t % a.OH); n = (int)(t / a.OH); }
+    else { ox = (int)(t % a.OW); t /= a.OW; oy = (int)(t % a.OH); t /= a.OH; c = (int)(t % a.C); n = (int)(t / a.C); }
+    const int y0 = oy * a.sh - a.pt, x0 = ox * a.sw - a.pl;
+    const int y1 = y0 + a.KH - 1, x1 = x0 + a.KW - 1;
+    int32_t best = a.dtype == kU8 ? 0 : a.dtype == kI8 ? -128 : a.dtype == kI16 ? -32768 : INT32_MIN;
+    uint32_t sum = 0;
+    int cnt = 0;
+    for (int iy = max(y0, 0); iy <= min(y1, a.H - 1); ++iy)
+      for (int ix = max(x0, 0); ix <= min(x1, a.W - 1); ++ix) {
+        const int32_t v = load_as_i32(x, a.dtype, n * a.xs[0] + c * a.xs[1] + iy * a.xs[2] + ix * a.xs[3]);
+        best = max(best, v);
+        sum += (uint32_t)v;
+        ++cnt;
+      }
+    int32_t r;
+    if (!a.is_avg) r = best;
+    else {
+      int div;
+      if (a.cip) {
+        const int ye = min(y1, a.H + a.pb - 1), xe = min(x1, a.W + a.pr - 1);
+        div = (ye - y0 + 1) * (xe - x0 + 1);
+      } else div = cnt > 1 ? cnt : 1;
+      r = (int32_t)sum / div;  // C division truncates toward zero
+    }
+    store_from_i32(y, a.dtype, n * a.ys[0] + c * a.ys[1] + oy * a.ys[2] + ox * a.ys[3], r);
+  }
+}
+
+void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_include_pad, int N, int C, int H, int W,
+                   int KH, int KW, int sh, int sw, int pt, int pl, int pb, int pr, const long long* xs,
+                   const long long* ys, cudaStream_t s) {
+  PoolArgs a;
+  a.N = N; a.C = C; a.H = H; a.W = W; a.KH = KH; a.KW = KW; a.sh = sh; a.sw = sw;
+  a.pt = pt; a.pl = pl; a.pb = pb; a.pr = pr; a.is_avg = is_avg; a.cip = count_include_pad; a.dtype = dtype;
+  a.OH = (H + pt + pb - KH) / sh + 1;
+  a.OW = (W + pl + pr - KW) / sw + 1;
+  for (int i = 0; i < 4; ++i) { a.xs[i] = xs[i]; a.ys[i] = ys[i]; }
+  const long long total = (long long)N * C * a.OH * a.OW;
+  if (total == 0) return;
+  pool2d_kernel<<<blocks_for(total, 256), 256, 0, s>>>(x, y, a);
+  ++g_launches;
+}
+
+struct Perm4 { long long shape[4], istr[4]; };
+
+// Tiled transpose of the two dims that swap fastest-varying roles would be the speed-of-light
+// version; graph-edge layout changes are small next to the convolutions, so this first version is a
+// plain gather with coalesced stores.
+template <typename T>
+__global__ void permute4_kernel(const T* __restrict__ x, T* __restrict__ y, Perm4 p) {
+  const long long total = p.shape[0] * p.shape[1] * p.shape[2] * p.shape[3];
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    long long t = idx;
+    const long long i3 = t % p.shape[3]; t /= p.shape[3];
+    const long long i2 = t % p.shape[2]; t /= p.shape[2];
+    const long long i1 = t % p.shape[1];
+    const long long i0 = t / p.shape[1];
+    y[idx] = x[i0 * p.istr[0] + i1 * p.istr[1] + i2 * p.istr[2] + i3 * p.istr[3]];
+  }
+}
+
+void launch_permute4(const void* x, void* y, int elem, const long long* out_shape, const long long* in_strides,
+                     cudaStream_t s) {
+  Perm4 p;
+  long long total = 1;
+  for (int i = 0; i < 4; ++i) { p.shape[i] = out_shape[i]; p.istr[i] = in_strides[i]; total *= out_shape[i]; }
+  if (total == 0) return;
+  const int bl = blocks_for(total, 256);
+  if (elem == 1) permute4_kernel<uint8_t><<<bl, 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, p);
+  else if (elem == 2) permute4_kernel<uint16_t><<<bl, 256, 0, s>>>((const uint16_t*)x, (uint16_t*)y, p);
+  else if (elem == 8) permute4_kernel<uint64_t><<<bl, 256, 0, s>>>((const uint64_t*)x, (uint64_t*)y, p);
+  else permute4_kernel<uint32_t><<<bl, 256, 0, s>>>((const uint32_t*)x, (uint32_t*)y, p);
+  ++g_launches;
+}
+
+struct Pad4 { long long ishape[4], before[4], oshape[4]; };
+
+template <typename T>
+__global__ void pad4_kernel(const T* __restrict__ x, T* __restrict__ y, Pad4 p, T value) {
+  const long long total = p.oshape[0] * p.oshape[1] * p.oshape[2] * p.oshape[3];
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    long long t = idx, i[4];
+    for (int d = 3; d >= 0; --d) { i[d] = t % p.oshape[d] - p.before[d]; t /= p.oshape[d]; }
+    bool in = true;
+    for (int d = 0; d < 4; ++d) in = in && i[d] >= 0 && i[d] < p.ishape[d];
+    y[idx] = in ? x[((i[0] * p.ishape[1] + i[1]) * p.ishape[2] + i[2]) * p.ishape[3] + i[3]] : value;
+  }
+}
+
+void launch_pad4(const void* x, void* y, int elem, const long long* in_shape, const long long* pad_before,
+                 const long long* out_shape, int32_t value, cudaStream_t s) {
+  Pad4 p;
+  long long total = 1;
+  for (int i = 0; i < 4; ++i) {
+    p.ishape[i] = in_shape[i]; p.before[i] = pad_before[i]; p.oshape[i] = out_shape[i];
+    total *= out_shape[i];
+  }
+  if (total == 0) return;
+  const int bl = blocks_for(total, 256);
+  if (elem == 1) pad4_kernel<uint8_t><<<bl, 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, p, (uint8_t)value);
+  else if (elem == 2) pad4_kernel<uint16_t><<<bl, 256, 0, s>>>((const uint16_t*)x, (uint16_t*)y, p, (uint16_t)value);
+  else pad4_kernel<uint32_t><<<bl, 256, 0, s>>>((const uint32_t*)x, (uint32_t*)y, p, (uint32_t)value);
+  ++g_launches;
+}
+
+// Explicit im2col for the tensor-core GEMM path: A[m][(r*KW+s)*C + c] = x[n, iy, ix, c]; taps that fall
+// outside the image read the INPUT ZERO POINT (convolution.cc:227-253 pads with zp_a), which makes the
+// zero-point correction  acc = raw - zp_a * sum_k W[o,k]  uniform over the whole output.  Columns
+// beyond KH*KW*C (K padded to a multiple of 16 for TMA) are zero and meet zero weights.
+__global__ void im2col_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ a, ConvGeom g, int Kp) {
+  const int K = g.KH * g.KW * g.C;
+  const long long M = (long long)g.N * g.OH * g.OW;
+  if ((g.C & 15) == 0) {
+    const int chunks = Kp >> 4, cpc = g.C >> 4;
+    const long long total = M * chunks;
+    const uint32_t z = (uint32_t)(g.zp_a & 0xFF) * 0x01010101u;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+      const int ch = (int)(idx % chunks);
+      long long m = idx / chunks;
+      const int tap = ch / cpc, c16 = ch % cpc;
+      const int r = tap / g.KW, s = tap % g.KW;
+      const int ox = (int)(m % g.OW);
+      long long t = m / g.OW;
+      const int oy = (int)(t % g.OH);
+      const int n = (int)(t / g.OH);
+      const int iy = oy * g.sh + r * g.dh - g.pt, ix = ox * g.sw + s * g.dw - g.pl;
+      uint4 v = make_uint4(z, z, z, z);
+      if (iy >= 0 && iy < g.H && ix >= 0 && ix < g.W)
+        v = *(const uint4*)(x + (((long long)n * g.H + iy) * g.W + ix) * g.C + c16 * 16);
+      *(uint4*)(a + m * Kp + ch * 16) = v;
+    }
+  } else {
+    const long long total = M * Kp;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+      const int k = (int)(idx % Kp);
+      long long m = idx / Kp;
+      uint8_t v = 0;
+      if (k < K) {
+        const int tap = k / g.C, c = k % g.C;
+        const int r = tap / g.KW, s = tap % g.KW;
+        const int ox = (int)(m % g.OW);
+        long long t = m / g.OW;
+        const int oy = (int)(t % g.OH);
+        const int n = (int)(t / g.OH);
+        const int iy = oy * g.sh + r * g.dh - g.pt, ix = ox * g.sw + s * g.dw - g.pl;
+        v = (uint8_t)g.zp_a;
+        if (iy >= 0 && iy < g.H && ix >= 0 && ix < g.W) v = x[(((long long)n * g.H + iy) * g.W + ix) * g.C + c];
+      }
+      a[idx] = v;
+    }
+  }
+}
+
+void launch_im2col(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream_t s) {
+  const long long M = (long long)g.N * g.OH * g.OW;
+  const long long total = (g.C & 15) == 0 ? M * (Kp >> 4) : M * Kp;
+  if (total == 0) return;
+  im2col_kernel<<<blocks_for(total, 256), 256, 0, s>>>((const uint8_t*)x, (uint8_t*)a, g, Kp);
+  ++g_launches;
+}
+
+}  // namespace tkb

@@ -1,0 +1,976 @@
+// libtkb200 runtime: the B200-native replacement of TachikomaJSONRuntime
+// (src/runtime/contrib/tachikoma/tachikoma_json_runtime.cc:52-124 Init/Run/GetFunction, :240-290
+// BuildEngine, :142-237 ParseAttrs) behind the C ABI declared in include/tkb200.h.
+//
+//   tkb_create : parse the JSON graph (graph.h)            <- TachikomaJSONRuntimeCreate
+//   tkb_init   : bind constants, build the launch plan      <- Init + BuildEngine
+//   tkb_run    : enqueue the plan on a CUDA stream          <- Run(args) const
+//
+// Internal tensor layout: 4-D activations of NCHW graphs are kept channels-last ("NHWC physical")
+// between spatial operators and converted at the subgraph boundary or where an operator needs the
+// logical layout (reshape / flatten / dense).  Every intermediate has its own slot in a per-stream
+// arena (no reuse inside a run, so trace capture can read any tensor after the fact).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <functional>
+#include <memory>
+#include <mutex>
+#include <regex>
+#include <sstream>
+#include <unordered_map>
+
+#include "../../include/tkb200.h"
+#include "graph.h"
+#include "kernels.h"
+
+namespace tkb {
+
+static thread_local std::string g_last_error;
+
+struct Error : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+
+[[noreturn]] static void fail(const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  throw Error(buf);
+}
+
+#define CUDA_OK(expr)                                                                      \
+  do {                                                                                     \
+    cudaError_t _e = (expr);                                                               \
+    if (_e != cudaSuccess) fail("CUDA error %s at %s:%d: %s", cudaGetErrorName(_e), __FILE__, __LINE__, \
+                                cudaGetErrorString(_e));                                   \
+  } while (0)
+
+static long long numel(const std::vector<int64_t>& s) {
+  long long n = 1;
+  for (auto d : s) n *= d;
+  return n;
+}
+
+enum Phys : int { kLogical = 0, kNHWC = 1 };  // kNHWC: logical NCHW tensor stored as N,H,W,C
+
+struct Entry {
+  std::vector<int64_t> shape;
+  int dtype = kI32;
+  bool is_input = false, is_const = false;
+  int input_index = -1;            // position among graph inputs
+  std::vector<uint8_t> host;       // constants: host copy (planner reads scales / zero points from it)
+  void* dev_const = nullptr;       // constants uploaded on demand (logical layout)
+  long long off[2] = {-1, -1};     // arena offsets per physical layout (intermediates, staged inputs)
+  int alias_of = -1;               // reshape / flatten: shares the buffer of another entry (logical)
+  long long bytes() const { return numel(shape) * dtype_size(dtype); }
+  bool nhwc_is_noop() const {      // NHWC and NCHW coincide in memory
+    return shape.size() == 4 && (shape[1] == 1 || shape[2] * shape[3] == 1);
+  }
+};
+
+struct RunCtx;
+struct Step {
+  std::function<void(RunCtx&)> fn;
+  std::string desc;
+  int nid = -1;  // JSON node this step belongs to (-1: boundary conversion)
+};
+
+struct TraceRec {
+  std::string name;
+  int eid;
+  int nid;
+};
+
+struct Workspace {
+  uint8_t* arena = nullptr;
+  long long arena_bytes = 0;
+  uint8_t* trace_ring = nullptr;    // device: logical copies of NHWC-physical tensors
+  uint8_t* trace_host = nullptr;    // pinned host mirror of every traced tensor
+  long long trace_ring_bytes = 0, trace_host_bytes = 0;
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev = nullptr;
+  std::vector<cudaEvent_t> node_events;
+  bool trace_valid = false;
+};
+
+}  // namespace tkb
+
+struct tkb_runtime {
+  std::string symbol, graph_json;
+  std::vector<std::string> const_names;
+  std::vector<const char*> const_name_ptrs;
+  tkb::Graph g;
+  std::vector<tkb::Entry> ent;
+  std::vector<tkb::Step> steps;
+  std::vector<void*> dev_allocs;  // freed in tkb_free
+  long long arena_bytes = 0;
+  bool initialized = false;
+  std::mutex init_mu, ws_mu;
+  std::unordered_map<cudaStream_t, std::unique_ptr<tkb::Workspace>> ws;
+  std::string conv_impl = "auto";
+  bool trace_acc = false;
+  int trace_mode = 0;
+  std::vector<tkb::TraceRec> trace_recs;        // in emission order
+  std::vector<long long> trace_host_off;        // per record
+  std::vector<long long> trace_ring_off;        // per record (-1: read the tensor in place)
+  long long trace_host_bytes = 0, trace_ring_bytes = 0;
+  std::vector<uint8_t> blob, trace_blob_buf;
+  std::string plan_text;
+  long long launches = 0;
+  long long macs = 0, hbm_bytes = 0;
+  cudaStream_t last_stream = nullptr;
+};
+
+namespace tkb {
+
+struct RunCtx {
+  tkb_runtime* rt;
+  Workspace* ws;
+  cudaStream_t s;
+  std::vector<void*> in_ptr;  // device pointer of each graph input (logical layout)
+  void* ptr(int eid, int phys) const {
+    const Entry* e = &rt->ent[eid];
+    while (e->alias_of >= 0) { e = &rt->ent[e->alias_of]; }
+    if (e->is_const) return e->dev_const;
+    if (e->is_input && phys == kLogical) return in_ptr[e->input_index];
+    if (e->off[phys] < 0) fail("internal: entry %d has no buffer in layout %d", eid, phys);
+    return ws->arena + e->off[phys];
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// planner helpers
+// ------------------------------------------------------------------------------------------------
+struct Planner {
+  tkb_runtime* rt;
+  Graph& g;
+  std::vector<Entry>& ent;
+  std::ostringstream plan;
+  int cur_nid = -1;
+
+  explicit Planner(tkb_runtime* r) : rt(r), g(r->g), ent(r->ent) {}
+
+  long long arena_alloc(long long bytes) {
+    long long off = (rt->arena_bytes + 255) & ~255LL;
+    rt->arena_bytes = off + std::max<long long>(bytes, 16);
+    return off;
+  }
+  void* dev_upload(const void* host, size_t bytes) {
+    void* d = nullptr;
+    CUDA_OK(cudaMalloc(&d, std::max<size_t>(bytes, 16)));
+    if (bytes) CUDA_OK(cudaMemcpy(d, host, bytes, cudaMemcpyHostToDevice));
+    rt->dev_allocs.push_back(d);
+    return d;
+  }
+  void add_step(const std::string& desc, std::function<void(RunCtx&)> fn) {
+    Step s;
+    s.fn = std::move(fn);
+    s.desc = desc;
+    s.nid = cur_nid;
+    rt->steps.push_back(std::move(s));
+    plan << "  [" << cur_nid << "] " << desc << "\n";
+  }
+  int root(int eid) const {
+    while (ent[eid].alias_of >= 0) eid = ent[eid].alias_of;
+    return eid;
+  }
+  bool has(int eid, int phys) const {
+    const Entry& e = ent[root(eid)];
+    if (e.is_const) return phys == kLogical;
+    if (e.is_input && phys == kLogical) return true;
+    return e.off[phys] >= 0;
+  }
+  // constants ------------------------------------------------------------------------------------
+  const Entry& cst(int eid, const char* what) const {
+    if (eid < 0) fail("missing %s input", what);
+    const Entry& e = ent[eid];
+    if (!e.is_const) fail("%s must be a constant", what);
+    return e;
+  }
+  std::vector<float> cfloats(int eid, const char* what) const {
+    const Entry& e = cst(eid, what);
+    if (e.dtype != kF32) fail("%s must be float32", what);
+    std::vector<float> v(numel(e.shape));
+    memcpy(v.data(), e.host.data(), v.size() * 4);
+    return v;
+  }
+  std::vector<int32_t> cints(int eid, const char* what) const {
+    const Entry& e = cst(eid, what);
+    const long long n = numel(e.shape);
+    std::vector<int32_t> v(n);
+    for (long long i = 0; i < n; ++i) {
+      switch (e.dtype) {
+        case kI32: v[i] = ((const int32_t*)e.host.data())[i]; break;
+        case kI8: v[i] = ((const int8_t*)e.host.data())[i]; break;
+        case kU8: v[i] = ((const uint8_t*)e.host.data())[i]; break;
+        case kI16: v[i] = ((const int16_t*)e.host.data())[i]; break;
+        case kI64: v[i] = (int32_t)((const int64_t*)e.host.data())[i]; break;
+        case kF32: v[i] = (int32_t)((const float*)e.host.data())[i]; break;
+        default: fail("%s: bad dtype", what);
+      }
+    }
+    return v;
+  }
+  void ensure_dev_const(int eid) {
+    Entry& e = ent[eid];
+    if (e.is_const && !e.dev_const) e.dev_const = dev_upload(e.host.data(), e.host.size());
+  }
+  // layout management ----------------------------------------------------------------------------
+  // Make sure entry `eid` is materialised in physical layout `phys`; emits a conversion if needed.
+  void need(int eid, int phys) {
+    const int r = root(eid);
+    Entry& e = ent[r];
+    if (e.is_const) {
+      if (phys != kLogical && !e.nhwc_is_noop()) fail("internal: constant activations must stay logical");
+      ensure_dev_const(r);
+      return;
+    }
+    if (has(r, phys)) return;
+    const int other = 1 - phys;
+    if (!has(r, other)) fail("internal: entry %d used before it is produced", r);
+    if (e.shape.size() != 4) fail("internal: layout conversion of a rank-%d tensor", (int)e.shape.size());
+    if (e.nhwc_is_noop() && !(e.is_input && other == kLogical)) {
+      e.off[phys] = e.off[other];
+      return;
+    }
+    e.off[phys] = arena_alloc(e.bytes());
+    const long long N = e.shape[0], C = e.shape[1], H = e.shape[2], W = e.shape[3];
+    const int elem = dtype_size(e.dtype);
+    std::array<long long, 4> oshape, istr;
+    if (phys == kNHWC) {  // out dims (N,H,W,C) reading logical NCHW
+      oshape = {N, H, W, C};
+      istr = {C * H * W, W, 1, H * W};
+    } else {  // out dims (N,C,H,W) reading NHWC
+      oshape = {N, C, H, W};
+      istr = {H * W * C, 1, W * C, C};
+    }
+    rt->hbm_bytes += 2 * e.bytes();
+    add_step(std::string("layout ") + (phys == kNHWC ? "NCHW->NHWC" : "NHWC->NCHW") + " e" + std::to_string(r),
+             [=](RunCtx& c) { launch_permute4(c.ptr(r, other), c.ptr(r, phys), elem, oshape.data(), istr.data(), c.s); });
+  }
+  void produce(int eid, int phys) {
+    Entry& e = ent[eid];
+    if (e.off[phys] < 0) e.off[phys] = arena_alloc(e.bytes());
+  }
+  int preferred(int eid) const {  // layout an elementwise consumer should work in
+    const int r = root(eid);
+    if (ent[r].is_const || ent[r].is_input) return has(r, kNHWC) ? kNHWC : kLogical;
+    return ent[r].off[kNHWC] >= 0 ? kNHWC : kLogical;
+  }
+};
+
+// (multiplier, shift) from double(float32 s_in) / double(float32 s_out): src/relay/qnn/utils.cc:33-57
+static void fixed_point_multiplier_shift(double m, int32_t* sig, int32_t* exp) {
+  if (m == 0.) { *sig = 0; *exp = 0; return; }
+  int e;
+  double s = std::frexp(m, &e);
+  s = std::round(s * (double)(1ll << 31));
+  long long s64 = (long long)s;
+  if (s64 == (1ll << 31)) { s64 /= 2; ++e; }
+  *sig = (int32_t)s64;
+  *exp = e;
+}
+
+static void dtype_range(int dt, int32_t* lo, int32_t* hi) {
+  switch (dt) {
+    case kI8: *lo = -128; *hi = 127; break;
+    case kU8: *lo = 0; *hi = 255; break;
+    case kI16: *lo = -32768; *hi = 32767; break;
+    default: *lo = INT32_MIN; *hi = INT32_MAX; break;
+  }
+}
+
+static int parse_rounding(const std::string& s) {
+  if (s == "UPWARD" || s == "None" || s.empty()) return kUpward;  // default config: requantize_config.h:53-73
+  if (s == "TONEAREST") return kToNearest;
+  fail("QNN requantize supports two rounding modes - UPWARD and TONEAREST (got %s)", s.c_str());
+}
+static int parse_compute(const std::string& s) {
+  if (s == "int64" || s == "None" || s.empty()) return kInt64;
+  if (s == "float32") return kFloat32;
+  if (s == "float64") return kFloat64;
+  fail("QNN requantize supports three compute_dtype variants (got %s)", s.c_str());
+}
+
+// Build a RqParams (RequantizeLower, requantize.cc:195-273).  C = channel count on the quantization axis.
+static RqParams make_rq(Planner& P, const std::vector<float>& in_scale, const std::vector<int32_t>& in_zp,
+                        float out_scale, int32_t out_zp, int rounding, int compute, int out_dtype, int C) {
+  RqParams p;
+  memset(&p, 0, sizeof(p));
+  if (in_scale.size() != 1 && (int)in_scale.size() != C) fail("requantize: %d scales for %d channels", (int)in_scale.size(), C);
+  if (in_zp.size() != 1 && (int)in_zp.size() != C) fail("requantize: %d zero points for %d channels", (int)in_zp.size(), C);
+  p.per_channel = in_scale.size() != 1;
+  p.rounding = rounding;
+  p.compute = compute;
+  p.zp_out = out_zp;
+  p.no_clamp = out_dtype == kI32;
+  dtype_range(out_dtype, &p.qmin, &p.qmax);
+  const size_t n = in_scale.size();
+  std::vector<int32_t> M(n), S(n);
+  std::vector<double> D(n);
+  for (size_t i = 0; i < n; ++i) {
+    D[i] = (double)in_scale[i] / (double)out_scale;
+    fixed_point_multiplier_shift(D[i], &M[i], &S[i]);
+  }
+  if (!p.per_channel) {
+    p.mult0 = M[0]; p.shift0 = S[0]; p.dmul0 = D[0];
+    p.skip_mul = in_scale[0] == out_scale;  // IsEqualScalar(input_scale, output_scale), requantize.cc:226
+  } else {
+    p.mult = (const int32_t*)P.dev_upload(M.data(), n * 4);
+    p.shift = (const int32_t*)P.dev_upload(S.data(), n * 4);
+    p.dmul = (const double*)P.dev_upload(D.data(), n * 8);
+  }
+  if (in_zp.size() == 1) p.zp_in0 = in_zp[0];
+  else p.zp_in = (const int32_t*)P.dev_upload(in_zp.data(), in_zp.size() * 4);
+  return p;
+}
+
+static void init_epi(EpiParams& e) {
+  memset(&e, 0, sizeof(e));
+  e.mode = kEpiRaw;
+  e.out_dtype = kI32;
+}
+
+// qnn.add parameters (add.cc:40-93, op_common.h:196-210) into e.lhs / e.rhs / sum_*
+static void make_qadd(Planner& P, EpiParams& e, float sa, int32_t zpa, float sb, int32_t zpb, float so, int32_t zpo,
+                      int dtype) {
+  e.lhs_identity = sa == so && zpa == zpo;
+  e.rhs_identity = sb == so && zpb == zpo;
+  e.lhs = make_rq(P, {sa}, {zpa}, so, zpo, kUpward, kInt64, kI32, 1);
+  e.rhs = make_rq(P, {sb}, {zpb}, so, zpo, kUpward, kInt64, kI32, 1);
+  e.sum_zp_out = zpo;
+  dtype_range(dtype, &e.sum_qmin, &e.sum_qmax);
+  e.sum_clip_lo = e.sum_qmin;
+  e.sum_clip_hi = e.sum_qmax;
+  e.sum_dtype = dtype;
+}
+
+static void clip_bounds(double a_min, double a_max, int dtype, int32_t* lo, int32_t* hi) {
+  int32_t qlo, qhi;
+  dtype_range(dtype, &qlo, &qhi);
+  const double l = std::max(a_min, (double)qlo), h = std::min(a_max, (double)qhi);
+  *lo = (int32_t)l;  // relay clip casts the bounds to the tensor dtype
+  *hi = (int32_t)h;
+}
+
+// ------------------------------------------------------------------------------------------------
+// composite epilogue (ParseAttrs equivalent, tachikoma_json_runtime.cc:142-237)
+// ------------------------------------------------------------------------------------------------
+struct CompositeInfo {
+  EpiParams epi;
+  int bias_eid = -1;      // runtime bias tensor (non-constant), int32 [channels]
+  int sum_eid = -1;       // residual input
+  std::vector<int32_t> bias_host;  // constant int32 bias (int mode), empty if none
+  bool has_const_bias = false;
+  int32_t zp_a = 0;
+  std::vector<int32_t> zp_w;
+  bool float_mode = false;
+};
+
+static int input_by_name(const Graph& g, const GNode& n, const char* key) {
+  if (!n.has(key)) return -1;
+  const int idx = (int)n.i64(key, -1);
+  if (idx < 0 || idx >= (int)n.inputs.size()) fail("%s: index %d out of range", key, idx);
+  return (int)g.eid(n.inputs[idx]);
+}
+
+// `channels`: size of the output channel axis; `axis_is_channel(axis)`: whether a requantize axis
+// (logical, may be negative) designates that axis.
+static CompositeInfo build_composite(Planner& P, const GNode& n, int nid, int channels, int out_rank, int channel_axis) {
+  const Graph& g = P.g;
+  CompositeInfo ci;
+  init_epi(ci.epi);
+  EpiParams& e = ci.epi;
+  const int out_eid = (int)g.eid(nid, 0);
+  const int out_dtype = P.ent[out_eid].dtype;
+  e.out_dtype = out_dtype;
+  ci.sum_eid = input_by_name(g, n, "sum_idx");
+  const int bias_in = input_by_name(g, n, "bias_idx");
+  if (n.has("rq_in_scl_idx")) {
+    // ---- integer mode: TVM's exact lowering --------------------------------------------------
+    e.mode = kEpiInt;
+    ci.zp_a = P.cints(input_by_name(g, n, "src_zp_idx"), "src_zp")[0];
+    ci.zp_w = P.cints(input_by_name(g, n, "wgh_zp_idx"), "wgh_zp");
+    if (bias_in >= 0) {
+      if (numel(P.ent[bias_in].shape) != channels) fail("bias has %lld elements, expected %d", numel(P.ent[bias_in].shape), channels);
+      if (P.ent[bias_in].dtype != kI32) fail("bias must be int32");
+      if (P.ent[bias_in].is_const) { ci.bias_host = P.cints(bias_in, "bias"); ci.has_const_bias = true; }
+      else ci.bias_eid = bias_in;
+    }
+    auto in_scl = P.cfloats(input_by_name(g, n, "rq_in_scl_idx"), "rq_in_scl");
+    auto in_zp = P.cints(input_by_name(g, n, "rq_in_zp_idx"), "rq_in_zp");
+    const float out_scl = P.cfloats(input_by_name(g, n, "rq_out_scl_idx"), "rq_out_scl")[0];
+    const int32_t out_zp = P.cints(input_by_name(g, n, "rq_out_zp_idx"), "rq_out_zp")[0];
+    int axis = (int)n.i64("rq_axis", -1);
+    if (axis < 0) axis += out_rank;
+    if ((in_scl.size() > 1 || in_zp.size() > 1) && axis != channel_axis)
+      fail("Unsupported op: %s with per-channel requantize on axis %d (channel axis is %d)", n.name.c_str(), axis, channel_axis);
+    const int rq_dtype = dtype_from_string(n.str("rq_out_dtype", "int32"));
+    e.rq = make_rq(P, in_scl, in_zp, out_scl, out_zp, parse_rounding(n.str("rounding", "None")),
+                   parse_compute(n.str("compute_dtype", "None")), rq_dtype, channels);
+    clip_bounds(n.f64("clip_a_min", -2147483648.0), n.f64("clip_a_max", 2147483647.0), rq_dtype, &e.clip_lo, &e.clip_hi);
+    const int cast_dtype = dtype_from_string(n.str("cast_dtype", n.str("rq_out_dtype", "int32")));
+    if (ci.sum_eid >= 0) {
+      const float sa = P.cfloats(input_by_name(g, n, "sum_lhs_scl_idx"), "sum_lhs_scl")[0];
+      const int32_t za = P.cints(input_by_name(g, n, "sum_lhs_zp_idx"), "sum_lhs_zp")[0];
+      const float sb = P.cfloats(input_by_name(g, n, "sum_rhs_scl_idx"), "sum_rhs_scl")[0];
+      const int32_t zb = P.cints(input_by_name(g, n, "sum_rhs_zp_idx"), "sum_rhs_zp")[0];
+      const float so = P.cfloats(input_by_name(g, n, "sum_out_scl_idx"), "sum_out_scl")[0];
+      const int32_t zo = P.cints(input_by_name(g, n, "sum_out_zp_idx"), "sum_out_zp")[0];
+      if (P.ent[ci.sum_eid].dtype != cast_dtype) fail("qnn.add operands must share a dtype");
+      make_qadd(P, e, sa, za, sb, zb, so, zo, cast_dtype);
+      clip_bounds(n.f64("sum_clip_a_min", -2147483648.0), n.f64("sum_clip_a_max", 2147483647.0), cast_dtype,
+                  &e.sum_clip_lo, &e.sum_clip_hi);
+      e.sum = (const void*)1;  // patched with the real pointer at run time
+    } else {
+      e.sum_dtype = cast_dtype;
+    }
+    if (ci.sum_eid < 0 && cast_dtype != out_dtype) fail("composite output dtype mismatch");
+  } else if (n.has("o_scl_idx")) {
+    // ---- oneDNN-style float post-ops (the reference's literal path B) -------------------------
+    e.mode = kEpiFloat;
+    ci.float_mode = true;
+    ci.zp_w = {0};
+    if (bias_in >= 0) {
+      auto bf = P.cfloats(bias_in, "bias");
+      std::vector<float> full(channels);
+      if ((int)bf.size() == channels) full = bf;
+      else if (bf.size() == 1) std::fill(full.begin(), full.end(), bf[0]);
+      else fail("float bias has %d elements, expected %d", (int)bf.size(), channels);
+      e.bias = (const int32_t*)P.dev_upload(full.data(), full.size() * 4);
+    }
+    auto oscl = P.cfloats(input_by_name(g, n, "o_scl_idx"), "o_scl");
+    if (oscl.size() != 1 && (int)oscl.size() != channels) fail("o_scl has %d elements", (int)oscl.size());
+    e.o_scl = (const float*)P.dev_upload(oscl.data(), oscl.size() * 4);
+    e.n_oscl = (int)oscl.size();
+    e.act_scl = 1.f;
+    if (n.has("activation")) {
+      auto& act = n.list("activation");
+      if (act[0] != "clip") fail("Unsupported op: activation %s", act[0].c_str());
+      const int ia = std::stoi(act[1]), il = std::stoi(act[2]), ih = std::stoi(act[3]);
+      e.act_scl = P.cfloats((int)g.eid(n.inputs[ia]), "act_scale")[0];
+      const float lo = P.cfloats((int)g.eid(n.inputs[il]), "alpha")[0], hi = P.cfloats((int)g.eid(n.inputs[ih]), "beta")[0];
+      if (lo != 0.f || hi != 255.f) fail("Unsupported op: clip(%g, %g) activation", lo, hi);
+    }
+    const int ss = input_by_name(g, n, "sum_scl_idx");
+    e.sum_scl = ss >= 0 ? P.cfloats(ss, "sum_scl")[0] : 0.f;
+    const int dz = input_by_name(g, n, "dst_zp_idx");
+    e.dst_zp = dz >= 0 ? P.cfloats(dz, "dst_zp")[0] : 0.f;
+    dtype_range(out_dtype, &e.f_qmin, &e.f_qmax);
+    if (ci.sum_eid >= 0) { e.sum = (const void*)1; e.sum_dtype = P.ent[ci.sum_eid].dtype; }
+  } else {
+    fail("Unsupported op: %s without quantization attributes", n.name.c_str());
+  }
+  return ci;
+}
+
+static std::vector<int32_t> add_vec(const std::vector<int32_t>& bias, const std::vector<int32_t>& corr, int n) {
+  std::vector<int32_t> out(n);
+  for (int i = 0; i < n; ++i)
+    out[i] = (int32_t)((uint32_t)(bias.empty() ? 0 : bias[i]) + (uint32_t)corr[i]);
+  return out;
+}
+
+static bool all_zero(const std::vector<int32_t>& v) {
+  for (auto x : v) if (x != 0) return false;
+  return true;
+}
+
+// ------------------------------------------------------------------------------------------------
+// convolution (Convolution builder, tachikoma_json_runtime.cc:292-388; arithmetic convolution.cc:708-811)
+// ------------------------------------------------------------------------------------------------
+static std::vector<uint8_t> repack_ohwi(const Entry& w, const std::string& layout, int O, int Cg, int KH, int KW) {
+  std::vector<uint8_t> out((size_t)O * KH * KW * Cg);
+  const uint8_t* src = w.host.data();
+  auto at = [&](int o, int i, int h, int x) -> uint8_t {
+    if (layout == "OIHW") return src[(((size_t)o * Cg + i) * KH + h) * KW + x];
+    if (layout == "HWIO") return src[(((size_t)h * KW + x) * Cg + i) * O + o];
+    if (layout == "OHWI") return src[(((size_t)o * KH + h) * KW + x) * Cg + i];
+    // HWOI depthwise: [H][W][C][mult], output channel = c*mult + m, one input channel per group
+    return src[((size_t)h * KW + x) * O + o];
+  };
+  for (int o = 0; o < O; ++o)
+    for (int h = 0; h < KH; ++h)
+      for (int x = 0; x < KW; ++x)
+        for (int i = 0; i < Cg; ++i) out[(((size_t)o * KH + h) * KW + x) * Cg + i] = at(o, i, h, x);
+  return out;
+}
+
+static void plan_conv(Planner& P, int nid, bool composite) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), w_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[P.root(x_eid)];
+  const Entry& Wt = P.cst(w_eid, "convolution weight");
+  Entry& Y = P.ent[y_eid];
+  const std::string dl = n.str("data_layout", "NCHW"), kl = n.str("kernel_layout", "OIHW");
+  std::string ol = n.str("out_layout", "");
+  if (ol.empty()) ol = dl;
+  if ((dl != "NCHW" && dl != "NHWC") || ol != dl) fail("Unsupported op: %s with data_layout %s / out_layout %s", n.name.c_str(), dl.c_str(), ol.c_str());
+  if (kl != "OIHW" && kl != "HWIO" && kl != "OHWI" && kl != "HWOI") fail("Unsupported op: %s with kernel_layout %s", n.name.c_str(), kl.c_str());
+  if (X.shape.size() != 4 || Wt.shape.size() != 4) fail("conv2d expects 4-D data and kernel");
+  ConvGeom g;
+  memset(&g, 0, sizeof(g));
+  auto dim = [&](const std::vector<int64_t>& shp, const std::string& lay, char c) { return (int)shp[lay.find(c)]; };
+  g.N = dim(X.shape, dl, 'N'); g.C = dim(X.shape, dl, 'C'); g.H = dim(X.shape, dl, 'H'); g.W = dim(X.shape, dl, 'W');
+  g.groups = (int)n.i64("groups", 1);
+  g.KH = dim(Wt.shape, kl, 'H'); g.KW = dim(Wt.shape, kl, 'W');
+  int Cg;
+  if (kl == "HWOI") {  // depthwise, channels-last convention
+    g.O = (int)(Wt.shape[2] * Wt.shape[3]);
+    Cg = 1;
+    if (g.groups != g.C || Wt.shape[2] != g.C) fail("Unsupported op: HWOI kernel layout is only valid for depthwise convolution");
+  } else {
+    g.O = dim(Wt.shape, kl, 'O');
+    Cg = dim(Wt.shape, kl, 'I');
+  }
+  if (Cg * g.groups != g.C || g.O % g.groups) fail("conv2d: channels %d, groups %d, kernel I %d do not agree", g.C, g.groups, Cg);
+  auto st = n.ints("strides"), pd = n.ints("padding"), di = n.ints("dilation");
+  if (st.size() != 2 || di.size() != 2) fail("conv2d: strides / dilation must have 2 elements");
+  g.sh = (int)st[0]; g.sw = (int)st[1]; g.dh = (int)di[0]; g.dw = (int)di[1];
+  if (pd.size() == 4) { g.pt = (int)pd[0]; g.pl = (int)pd[1]; g.pb = (int)pd[2]; g.pr = (int)pd[3]; }
+  else if (pd.size() == 2) { g.pt = g.pb = (int)pd[0]; g.pl = g.pr = (int)pd[1]; }
+  else if (pd.size() == 1) { g.pt = g.pb = g.pl = g.pr = (int)pd[0]; }
+  else fail("conv2d: bad padding");
+  g.OH = (g.H + g.pt + g.pb - (g.KH - 1) * g.dh - 1) / g.sh + 1;
+  g.OW = (g.W + g.pl + g.pr - (g.KW - 1) * g.dw - 1) / g.sw + 1;
+  if (dim(Y.shape, ol, 'N') != g.N || dim(Y.shape, ol, 'C') != g.O || dim(Y.shape, ol, 'H') != g.OH || dim(Y.shape, ol, 'W') != g.OW)
+    fail("conv2d: output shape in the graph does not match the attributes");
+  g.a_dtype = X.dtype; g.w_dtype = Wt.dtype;
+  if ((g.a_dtype != kI8 && g.a_dtype != kU8) || (g.w_dtype != kI8 && g.w_dtype != kU8))
+    fail("Unsupported op: %s with data/kernel dtypes other than int8/uint8", n.name.c_str());
+
+  CompositeInfo ci;
+  const int ch_axis = (int)ol.find('C');
+  if (composite) {
+    ci = build_composite(P, n, nid, g.O, 4, ch_axis);
+  } else {
+    init_epi(ci.epi);
+    if (Y.dtype != kI32) fail("qnn.conv2d out_dtype must be int32");
+    ci.zp_a = P.cints((int)P.g.eid(n.inputs[2]), "input_zero_point")[0];
+    ci.zp_w = P.cints((int)P.g.eid(n.inputs[3]), "kernel_zero_point");
+  }
+  if (ci.zp_w.size() != 1 && (int)ci.zp_w.size() != g.O) fail("kernel zero point must be a scalar or have one value per output channel");
+  g.zp_a = ci.float_mode ? 0 : ci.zp_a;
+  g.zp_w0 = ci.zp_w[0];
+  if (ci.zp_w.size() > 1) g.zp_w = (const int32_t*)P.dev_upload(ci.zp_w.data(), ci.zp_w.size() * 4);
+
+  const int phys = dl == "NCHW" ? kNHWC : kLogical;
+  P.need(x_eid, phys);
+  if (ci.sum_eid >= 0) P.need(ci.sum_eid, phys);
+  if (ci.bias_eid >= 0) P.need(ci.bias_eid, kLogical);
+  P.produce(y_eid, phys);
+
+  std::vector<uint8_t> w_ohwi = repack_ohwi(Wt, kl, g.O, Cg, g.KH, g.KW);
+  const int K = g.KH * g.KW * Cg;
+  const long long M = (long long)g.N * g.OH * g.OW;
+  const bool direct = g.KH == 1 && g.KW == 1 && g.sh == 1 && g.sw == 1 && !(g.pt | g.pl | g.pb | g.pr) && (g.C % 16) == 0;
+  const bool tc_ok = P.rt->conv_impl != "simt" && g.groups == 1 && all_zero(ci.zp_w) &&
+                     (g.zp_a == 0 || ci.bias_eid < 0) && M >= 1;
+  const bool use_tc = tc_ok && (P.rt->conv_impl == "tc" || M * g.O >= 4096);
+  P.rt->macs += M * g.O * K;
+  P.rt->hbm_bytes += X.bytes() + Y.bytes() + (long long)w_ohwi.size() + (ci.sum_eid >= 0 ? Y.bytes() : 0);
+
+  EpiParams epi = ci.epi;
+  const int bias_eid = ci.bias_eid, sum_eid = ci.sum_eid;
+  char desc[256];
+  if (use_tc) {
+    const int Kp = direct ? K : (K + 15) / 16 * 16;
+    std::vector<uint8_t> wp((size_t)g.O * Kp, 0);
+    std::vector<int32_t> corr(g.O, 0);
+    for (int o = 0; o < g.O; ++o) {
+      memcpy(&wp[(size_t)o * Kp], &w_ohwi[(size_t)o * K], K);
+      long long sum = 0;
+      for (int k = 0; k < K; ++k) sum += g.w_dtype == kU8 ? (int)w_ohwi[(size_t)o * K + k] : (int)(int8_t)w_ohwi[(size_t)o * K + k];
+      corr[o] = (int32_t)(0u - (uint32_t)g.zp_a * (uint32_t)(int32_t)sum);  // -zp_a * sum_k W[o,k]  (int32 ring)
+    }
+    void* wdev = P.dev_upload(wp.data(), wp.size());
+    if (!ci.float_mode) {
+      if (ci.has_const_bias || g.zp_a != 0) {
+        auto b = add_vec(ci.bias_host, corr, g.O);
+        epi.bias = (const int32_t*)P.dev_upload(b.data(), b.size() * 4);
+      }
+    }
+    long long scratch_off = -1;
+    if (!direct) scratch_off = P.arena_alloc(M * Kp);
+    snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 GEMM%s M=%lld N=%d K=%d (%dx%d s%d p%d) epi=%d", n.name.c_str(),
+             direct ? "" : " + im2col", M, g.O, Kp, g.KH, g.KW, g.sh, g.pt, epi.mode);
+    P.add_step(desc, [=](RunCtx& c) {
+      EpiParams e = epi;
+      if (bias_eid >= 0) e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
+      if (sum_eid >= 0) e.sum = c.ptr(sum_eid, phys);
+      const void* a = c.ptr(x_eid, phys);
+      if (!direct) {
+        void* col = c.ws->arena + scratch_off;
+        launch_im2col(a, col, g, Kp, c.s);
+        a = col;
+      }
+      if (launch_gemm_tc(a, wdev, c.ptr(y_eid, phys), 1, (int)M, g.O, Kp, 0, g.a_dtype, g.w_dtype, e, c.s) != 0)
+        fail("tcgen05 GEMM launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+    });
+  } else {
+    void* wdev = P.dev_upload(w_ohwi.data(), w_ohwi.size());
+    if (!ci.float_mode && ci.has_const_bias) epi.bias = (const int32_t*)P.dev_upload(ci.bias_host.data(), ci.bias_host.size() * 4);
+    snprintf(desc, sizeof(desc), "%s -> CUDA-core direct conv N=%d %dx%dx%d -> %dx%dx%d k%dx%d g%d epi=%d", n.name.c_str(),
+             g.N, g.H, g.W, g.C, g.OH, g.OW, g.O, g.KH, g.KW, g.groups, epi.mode);
+    P.add_step(desc, [=](RunCtx& c) {
+      EpiParams e = epi;
+      if (bias_eid >= 0) e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
+      if (sum_eid >= 0) e.sum = c.ptr(sum_eid, phys);
+      launch_conv2d_simt(c.ptr(x_eid, phys), wdev, c.ptr(y_eid, phys), g, e, c.s);
+    });
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// dense / batch_matmul (Dense :462-502, BatchMatMul :504-548; arithmetic dense.cc:160-205,
+// batch_matmul.cc:161-200)
+// ------------------------------------------------------------------------------------------------
+static void plan_dense(Planner& P, int nid, bool composite) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), w_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[x_eid];
+  const Entry& Wt = P.ent[w_eid];
+  Entry& Y = P.ent[y_eid];
+  if (Wt.shape.size() != 2 || X.shape.empty()) fail("dense expects a 2-D weight");
+  const int K = (int)Wt.shape[1], N = (int)Wt.shape[0];
+  if (X.shape.back() != K) fail("dense: input has %lld features, weight expects %d", (long long)X.shape.back(), K);
+  const long long M = numel(X.shape) / K;
+  if ((X.dtype != kI8 && X.dtype != kU8) || (Wt.dtype != kI8 && Wt.dtype != kU8))
+    fail("Unsupported op: %s with data/kernel dtypes other than int8/uint8", n.name.c_str());
+  CompositeInfo ci;
+  if (composite) {
+    ci = build_composite(P, n, nid, N, (int)Y.shape.size(), (int)Y.shape.size() - 1);
+  } else {
+    init_epi(ci.epi);
+    if (Y.dtype != kI32) fail("qnn.dense out_dtype must be int32");
+    ci.zp_a = P.cints((int)P.g.eid(n.inputs[2]), "input_zero_point")[0];
+    ci.zp_w = P.cints((int)P.g.eid(n.inputs[3]), "kernel_zero_point");
+  }
+  if (ci.zp_w.size() != 1) fail("Unsupported op: qnn.dense with a per-channel kernel zero point");
+  const int32_t zpx = ci.float_mode ? 0 : ci.zp_a, zpw = ci.zp_w[0];
+  P.need(x_eid, kLogical);
+  P.need(w_eid, kLogical);
+  if (ci.sum_eid >= 0) P.need(ci.sum_eid, kLogical);
+  if (ci.bias_eid >= 0) P.need(ci.bias_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->macs += M * N * K;
+  P.rt->hbm_bytes += X.bytes() + Wt.bytes() + Y.bytes() + (ci.sum_eid >= 0 ? Y.bytes() : 0);
+  EpiParams epi = ci.epi;
+  const int bias_eid = ci.bias_eid, sum_eid = ci.sum_eid, xd = X.dtype, wd = Wt.dtype;
+  const bool foldable = zpx == 0 || (Wt.is_const && bias_eid < 0);
+  const bool use_tc = P.rt->conv_impl != "simt" && tc_gemm_supported((int)M, N, K) && zpw == 0 && foldable &&
+                      (P.rt->conv_impl == "tc" || M * N >= 4096);
+  char desc[256];
+  if (use_tc) {
+    if (!ci.float_mode && (ci.has_const_bias || zpx != 0)) {
+      std::vector<int32_t> corr(N, 0);
+      if (zpx != 0)
+        for (int o = 0; o < N; ++o) {
+          long long sum = 0;
+          for (int k = 0; k < K; ++k) sum += wd == kU8 ? (int)Wt.host[(size_t)o * K + k] : (int)(int8_t)Wt.host[(size_t)o * K + k];
+          corr[o] = (int32_t)(0u - (uint32_t)zpx * (uint32_t)(int32_t)sum);
+        }
+      auto b = add_vec(ci.bias_host, corr, N);
+      epi.bias = (const int32_t*)P.dev_upload(b.data(), b.size() * 4);
+    }
+    snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 GEMM M=%lld N=%d K=%d epi=%d", n.name.c_str(), M, N, K, epi.mode);
+    P.add_step(desc, [=](RunCtx& c) {
+      EpiParams e = epi;
+      if (bias_eid >= 0) e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
+      if (sum_eid >= 0) e.sum = c.ptr(sum_eid, kLogical);
+      if (launch_gemm_tc(c.ptr(x_eid, kLogical), c.ptr(w_eid, kLogical), c.ptr(y_eid, kLogical), 1, (int)M, N, K, 0, xd, wd,
+                         e, c.s) != 0)
+        fail("tcgen05 GEMM launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+    });
+  } else {
+    if (!ci.float_mode && ci.has_const_bias) epi.bias = (const int32_t*)P.dev_upload(ci.bias_host.data(), ci.bias_host.size() * 4);
+    snprintf(desc, sizeof(desc), "%s -> CUDA-core GEMM M=%lld N=%d K=%d epi=%d", n.name.c_str(), M, N, K, epi.mode);
+    P.add_step(desc, [=](RunCtx& c) {
+      EpiParams e = epi;
+      if (bias_eid >= 0) e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
+      if (sum_eid >= 0) e.sum = c.ptr(sum_eid, kLogical);
+      launch_gemm_simt(c.ptr(x_eid, kLogical), c.ptr(w_eid, kLogical), c.ptr(y_eid, kLogical), 1, (int)M, N, K, 0, xd, wd,
+                       zpx, zpw, e, c.s);
+    });
+  }
+}
+
+static void plan_batch_matmul(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), w_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[x_eid];
+  const Entry& Wt = P.ent[w_eid];
+  if (X.shape.size() != 3 || Wt.shape.size() != 3 || X.shape[2] != Wt.shape[2])
+    fail("qnn.batch_matmul expects x [B,M,K] and y [B,N,K] (transpose_b only, batch_matmul.cc:83-87)");
+  if (n.i64("transpose_a", 0) != 0 || n.i64("transpose_b", 1) != 1) fail("Unsupported op: qnn.batch_matmul transpose flags");
+  const int B = (int)std::max(X.shape[0], Wt.shape[0]), M = (int)X.shape[1], N = (int)Wt.shape[1], K = (int)X.shape[2];
+  if (X.shape[0] != B) fail("Unsupported op: qnn.batch_matmul broadcasting the first operand");
+  const int wb = Wt.shape[0] == B && B > 1 ? 1 : 0;
+  if ((X.dtype != kI8 && X.dtype != kU8) || (Wt.dtype != kI8 && Wt.dtype != kU8)) fail("Unsupported op: batch_matmul dtypes");
+  const int32_t zpx = P.cints((int)P.g.eid(n.inputs[2]), "x_zero_point")[0];
+  const int32_t zpw = P.cints((int)P.g.eid(n.inputs[3]), "y_zero_point")[0];
+  P.need(x_eid, kLogical);
+  P.need(w_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->macs += (long long)B * M * N * K;
+  P.rt->hbm_bytes += X.bytes() + Wt.bytes() + P.ent[y_eid].bytes();
+  EpiParams epi;
+  init_epi(epi);
+  const int xd = X.dtype, wd = Wt.dtype;
+  const bool use_tc = P.rt->conv_impl != "simt" && tc_gemm_supported(M, N, K) && zpx == 0 && zpw == 0 &&
+                      (P.rt->conv_impl == "tc" || (long long)B * M * N >= 4096);
+  char desc[256];
+  snprintf(desc, sizeof(desc), "qnn.batch_matmul -> %s B=%d M=%d N=%d K=%d", use_tc ? "tcgen05 i8 GEMM" : "CUDA-core GEMM", B, M, N, K);
+  P.add_step(desc, [=](RunCtx& c) {
+    if (use_tc) {
+      if (launch_gemm_tc(c.ptr(x_eid, kLogical), c.ptr(w_eid, kLogical), c.ptr(y_eid, kLogical), B, M, N, K, wb, xd, wd, epi, c.s) != 0)
+        fail("tcgen05 GEMM launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+    } else {
+      launch_gemm_simt(c.ptr(x_eid, kLogical), c.ptr(w_eid, kLogical), c.ptr(y_eid, kLogical), B, M, N, K, wb, xd, wd, zpx, zpw, epi, c.s);
+    }
+  });
+}
+
+// ------------------------------------------------------------------------------------------------
+// elementwise / pooling / data-movement operators
+// ------------------------------------------------------------------------------------------------
+// (outer, C, inner) decomposition of a tensor around logical axis `axis` in physical layout `phys`.
+static void axis_split(const Entry& e, int axis, int phys, long long* outer, int* C, long long* inner) {
+  const int rank = (int)e.shape.size();
+  if (rank == 0) { *outer = 1; *C = 1; *inner = 1; return; }
+  if (axis < 0) axis += rank;
+  if (axis < 0 || axis >= rank) fail("axis %d out of range for rank %d", axis, rank);
+  std::vector<int64_t> shp = e.shape;
+  int ax = axis;
+  if (phys == kNHWC && rank == 4) {
+    shp = {e.shape[0], e.shape[2], e.shape[3], e.shape[1]};
+    static const int map[4] = {0, 3, 1, 2};  // logical axis -> physical position
+    ax = map[axis];
+  }
+  *outer = 1; *inner = 1;
+  for (int i = 0; i < ax; ++i) *outer *= shp[i];
+  *C = (int)shp[ax];
+  for (int i = ax + 1; i < rank; ++i) *inner *= shp[i];
+}
+
+static void plan_requantize(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[x_eid];
+  const int phys = P.preferred(x_eid);
+  auto in_scl = P.cfloats((int)P.g.eid(n.inputs[1]), "input_scale");
+  auto in_zp = P.cints((int)P.g.eid(n.inputs[2]), "input_zero_point");
+  const float out_scl = P.cfloats((int)P.g.eid(n.inputs[3]), "output_scale")[0];
+  const int32_t out_zp = P.cints((int)P.g.eid(n.inputs[4]), "output_zero_point")[0];
+  long long outer, inner;
+  int C;
+  axis_split(X, (int)n.i64("axis", -1), phys, &outer, &C, &inner);
+  if (in_scl.size() == 1 && in_zp.size() == 1) { outer *= (long long)C * inner; C = 1; inner = 1; }
+  const int ydt = P.ent[y_eid].dtype, xdt = X.dtype;
+  RqParams rq = make_rq(P, in_scl, in_zp, out_scl, out_zp, parse_rounding(n.str("rounding", "None")),
+                        parse_compute(n.str("compute_dtype", "None")), ydt, C);
+  P.need(x_eid, phys);
+  P.produce(y_eid, phys);
+  P.rt->hbm_bytes += X.bytes() + P.ent[y_eid].bytes();
+  P.add_step("qnn.requantize -> elementwise kernel", [=](RunCtx& c) {
+    launch_requantize(c.ptr(x_eid, phys), xdt, c.ptr(y_eid, phys), ydt, outer, C, inner, rq, c.s);
+  });
+}
+
+static void plan_qnn_add(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int a_eid = (int)P.g.eid(n.inputs[0]), b_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& A = P.ent[a_eid];
+  if (A.shape != P.ent[b_eid].shape || A.dtype != P.ent[b_eid].dtype) fail("Unsupported op: qnn.add with broadcasting operands");
+  const int phys = (P.preferred(a_eid) == kNHWC || P.preferred(b_eid) == kNHWC) && A.shape.size() == 4 &&
+                           !P.ent[P.root(a_eid)].is_const && !P.ent[P.root(b_eid)].is_const ? kNHWC : kLogical;
+  EpiParams e;
+  init_epi(e);
+  make_qadd(P, e, P.cfloats((int)P.g.eid(n.inputs[2]), "lhs_scale")[0], P.cints((int)P.g.eid(n.inputs[3]), "lhs_zero_point")[0],
+            P.cfloats((int)P.g.eid(n.inputs[4]), "rhs_scale")[0], P.cints((int)P.g.eid(n.inputs[5]), "rhs_zero_point")[0],
+            P.cfloats((int)P.g.eid(n.inputs[6]), "output_scale")[0], P.cints((int)P.g.eid(n.inputs[7]), "output_zero_point")[0],
+            A.dtype);
+  P.need(a_eid, phys);
+  P.need(b_eid, phys);
+  P.produce(y_eid, phys);
+  const long long cnt = numel(A.shape);
+  const int dt = A.dtype;
+  P.rt->hbm_bytes += 3 * A.bytes();
+  P.add_step("qnn.add -> vectorised elementwise kernel", [=](RunCtx& c) {
+    launch_qnn_add(c.ptr(a_eid, phys), c.ptr(b_eid, phys), c.ptr(y_eid, phys), dt, cnt, e, c.s);
+  });
+}
+
+static void plan_unary(Planner& P, int nid) {  // clip, cast
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[x_eid];
+  const int phys = P.preferred(x_eid);
+  P.need(x_eid, phys);
+  P.produce(y_eid, phys);
+  const long long cnt = numel(X.shape);
+  const int xdt = X.dtype, ydt = P.ent[y_eid].dtype;
+  P.rt->hbm_bytes += X.bytes() + P.ent[y_eid].bytes();
+  if (n.name == "clip") {
+    double lo = n.f64("a_min"), hi = n.f64("a_max");
+    if (xdt != kF32) {
+      int32_t l, h;
+      clip_bounds(lo, hi, xdt, &l, &h);
+      lo = l; hi = h;
+    }
+    P.add_step("clip -> elementwise kernel", [=](RunCtx& c) { launch_clip(c.ptr(x_eid, phys), c.ptr(y_eid, phys), xdt, cnt, lo, hi, c.s); });
+  } else {
+    P.add_step("cast -> elementwise kernel", [=](RunCtx& c) { launch_cast(c.ptr(x_eid, phys), xdt, c.ptr(y_eid, phys), ydt, cnt, c.s); });
+  }
+}
+
+static void plan_add(Planner& P, int nid) {  // nn.bias_add, add
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), b_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[x_eid];
+  const Entry& Bv = P.ent[b_eid];
+  if (X.dtype != Bv.dtype || X.dtype == kF32 || X.dtype == kI64) fail("Unsupported op: %s on dtypes other than matching integers", n.name.c_str());
+  if (P.ent[y_eid].shape != X.shape) fail("Unsupported op: %s broadcasting the first operand", n.name.c_str());
+  const int dt = X.dtype;
+  const int rank = (int)X.shape.size();
+  P.rt->hbm_bytes += 2 * X.bytes();
+  if (n.name == "add" && Bv.shape == X.shape) {
+    const int phys = P.preferred(x_eid);
+    P.need(x_eid, phys);
+    P.need(b_eid, phys);
+    P.produce(y_eid, phys);
+    const long long cnt = numel(X.shape);
+    P.add_step("add -> elementwise kernel", [=](RunCtx& c) { launch_add_same(c.ptr(x_eid, phys), c.ptr(b_eid, phys), c.ptr(y_eid, phys), dt, cnt, c.s); });
+    return;
+  }
+  // broadcast of a vector along one axis: nn.bias_add(axis) or add(x, const[C,1,1] / [C] / scalar)
+  int axis;
+  if (n.name == "nn.bias_add") {
+    axis = (int)n.i64("axis", 1);
+    if (axis < 0) axis += rank;
+  } else {
+    const int br = (int)Bv.shape.size();
+    axis = -1;
+    for (int i = 0; i < br; ++i) {
+      if (Bv.shape[i] == 1) continue;
+      if (axis >= 0) fail("Unsupported op: add with a multi-axis broadcast operand");
+      axis = rank - br + i;
+    }
+    if (axis < 0) axis = rank > 0 ? rank - 1 : 0;  // scalar: broadcast over everything
+  }
+  const int phys = P.preferred(x_eid);
+  long long outer, inner;
+  int C;
+  axis_split(X, axis, phys, &outer, &C, &inner);
+  const long long bn = numel(Bv.shape);
+  if (bn == 1) { outer *= (long long)C * inner; C = 1; inner = 1; }
+  else if (bn != C) fail("%s: operand has %lld elements, axis has %d", n.name.c_str(), bn, C);
+  P.need(x_eid, phys);
+  P.need(b_eid, kLogical);
+  P.produce(y_eid, phys);
+  P.add_step(n.name + " -> elementwise kernel", [=](RunCtx& c) {
+    launch_bias_add(c.ptr(x_eid, phys), c.ptr(b_eid, kLogical), c.ptr(y_eid, phys), dt, outer, C, inner, c.s);
+  });
+}
+
+static void plan_pool(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[P.root(x_eid)];
+  const Entry& Y = P.ent[y_eid];
+  const std::string lay = n.str("layout", "NCHW");
+  if ((lay != "NCHW" && lay != "NHWC") || X.shape.size() != 4) fail("Unsupported op: %s with layout %s", n.name.c_str(), lay.c_str());
+  if (X.dtype == kF32 || X.dtype == kI64) fail("Unsupported op: %s on non-integer tensors", n.name.c_str());
+  const int N = (int)X.shape[lay.find('N')], C = (int)X.shape[lay.find('C')], H = (int)X.shape[lay.find('H')], W = (int)X.shape[lay.find('W')];
+  int KH, KW, sh = 1, sw = 1, pt = 0, pl = 0, pb = 0, pr = 0, cip = 0;
+  const bool global = n.name == "nn.global_avg_pool2d";
+  const bool is_avg = global || n.name == "nn.avg_pool2d";
+  if (global) { KH = H; KW = W; }
+  else {
+    auto ps = n.ints("pool_size"), st = n.ints("strides"), pd = n.ints("padding"), di = n.ints("dilation");
+    if (ps.size() != 2 || st.size() != 2) fail("%s: pool_size / strides must have 2 elements", n.name.c_str());
+    for (auto d : di) if (d != 1) fail("Unsupported op: dilated pooling");
+    if (n.i64("ceil_mode", 0)) fail("Unsupported op: pooling with ceil_mode");
+    KH = (int)ps[0]; KW = (int)ps[1]; sh = (int)st[0]; sw = (int)st[1];
+    if (pd.size() == 4) { pt = (int)pd[0]; pl = (int)pd[1]; pb = (int)pd[2]; pr = (int)pd[3]; }
+    else if (pd.size() == 2) { pt = pb = (int)pd[0]; pl = pr = (int)pd[1]; }
+    else if (pd.size() == 1) { pt = pb = pl = pr = (int)pd[0]; }
+    cip = (int)n.i64("count_include_pad", 0);
+  }
+  const int OH = (H + pt + pb - KH) / sh + 1, OW = (W + pl + pr - KW) / sw + 1;
+  if (Y.shape[lay.find('H')] != OH || Y.shape[lay.find('W')] != OW) fail("%s: output shape mismatch", n.name.c_str());
+  const int phys = lay == "NCHW" ? kNHWC : kLogical;  // channels-last in memory either way
+  P.need(x_eid, phys);
+  P.produce(y_eid, phys);
+  const int dt = X.dtype;
+  std::array<long long, 4> xs = {(long long)H * W * C, 1, (long long)W * C, C}, ys = {(long long)OH * OW * C, 1, (long long)OW * C, C};
+  P.rt->hbm_bytes += X.bytes() + Y.bytes();
+  P.add_step(n.name + " -> pooling kernel (channels-last)", [=](RunCtx& c) {
+    launch_pool2d(c.ptr(x_eid, phys), c.ptr(y_eid, phys), dt, is_avg, cip, N, C, H, W, KH, KW, sh, sw, pt, pl, pb, pr, xs.data(), ys.data(), c.s);
+  });
+}
+
+static void plan_pad(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[x_eid];
+  const int rank = (int)X.shape.size();
+  if (rank > 4 || n.str("pad_mode", "constant") != "constant") fail("Unsupported op: nn.pad (rank %d, mode %s)", rank, n.str("pad_mode").c_str());
+  auto pw = n.ints("pad_width");
+  if ((int)pw.size() != 2 * rank) fail("nn.pad: pad_width must have 2*rank entries");
+  const Entry& V = P.cst((int)P.g.eid(n.inputs[1]), "pad_value");
+  const int32_t value = V.dtype == kF32 ? (int32_t)((const float*)V.host.data())[0] : P.cints((int)P.g.eid(n.inputs[1]), "pad_value")[0];
+  std::array<long long, 4> ishape = {1, 1, 1, 1}, before = {0, 0, 0, 0}, oshape = {1, 1, 1, 1};
+  for (int i = 0; i < rank; ++i) {
+    const int d = 4 - rank + i;
+    ishape[d] = X.shape[i]; before[d] = pw[2 * i]; oshape[d] = X.shape[i] + pw[2 * i] + pw[2 * i + 1];
+  }
+  P.need(x_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  const int elem = dtype_size(X.dtype);
+  P.rt->hbm_bytes += X.bytes() + P.ent[y_eid].bytes();
+  P.add_step("nn.pad -> pad kernel", [=](RunCtx& c) {
+    launch_pad4(c.ptr(x_eid, kLogical), c.ptr(y_eid, kLogical), elem, ishape.data(), before.data(), oshape.data(), value, c.s);
+  });
+}
+
+static void plan_reshape(Planner& P, int nid) {  // reshape, nn.batch_flatten: alias, no kernel
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  if (numel(P.ent[x_eid].shape) != numel(P.ent[y_eid].shape)) fail("%s: element count changes", n.name.c_str());
+  P.need(x_eid, kLogical);
+  P.ent[y_eid].alias_of = P.root(x_eid);
+  P.plan << "  [" << nid << "] " << n.name << " -> alias of e" << P.root(x_eid) << " (no kernel)\n";
+}
+
+static void plan_transpose(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[x_eid];
+  const int rank = (int)X.shape.size();
+  auto axes = n.ints("axes");
+  if (rank > 4 || (int)axes.size() != rank) fail("Unsupported op: transpose of rank %d", rank);
+  std::vector<long long> istr(rank, 1);
+  for (int i = rank - 2; i >= 0; --i) istr[i] = istr[i + 1] * X.shape[i + 1];
+  std::array<long long, 4> oshape = {1, 1, 1, 1}, ostr = {0, 0, 0, 0};
+  for (int i = 0; i < rank; ++i) {
+    int a = (int)axes[i];
+    if (a < 0) a += rank;
+    oshape[4 - rank + i] = X.shape[a];
+    ostr[4 - rank + i] = istr[a];
+  }
+  P.need(x_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  const int elem = dtype_size(X.dtype);
+  P.rt->hbm_bytes += 2 * X.bytes();
+  P.add_step("transpose -> permute kernel", [=](RunCtx& c) {
+    launch_permute4(c.ptr(x_eid, kLogical), c.ptr(y_eid, kLogical), elem, oshape.data(), ostr.data(), c.s);
+  });
+}

@@ -282,3 +282,208 @@ def run_expr(func, inputs):
             assert tuple(env[id(e)].shape) == tuple(e.shape), (e.op, env[id(e)].shape, e.shape)
             assert str(env[id(e)].dtype) == e.dtype, (e.op, env[id(e)].dtype, e.dtype)
     return env[id(func.body)], env
+
+
+# ----------------------------------------------------------------------------------------------
+# tachikoma JSON graph interpreter (composites evaluated as their primitive chain) + trace writer
+# ----------------------------------------------------------------------------------------------
+
+def _attr(node, key, default=None):
+    v = node.get("attrs", {}).get(key)
+    return default if v is None else v[0]
+
+
+def _ints(node, key):
+    return [int(x) for x in _attr(node, key, [])]
+
+
+def _conv_attrs(node):
+    return dict(strides=_ints(node, "strides"), padding=_ints(node, "padding"), dilation=_ints(node, "dilation"),
+                groups=int(_attr(node, "groups", ["1"])[0]), data_layout=_attr(node, "data_layout", ["NCHW"])[0],
+                kernel_layout=_attr(node, "kernel_layout", ["OIHW"])[0], out_layout=_attr(node, "out_layout", [""])[0])
+
+
+def _eval_composite(node, ins):
+    """tachikoma.qnn.conv2d / tachikoma.qnn.dense: run the fused chain op by op."""
+    is_conv = node["name"].endswith("conv2d")
+
+    def arg(key):
+        v = _attr(node, key)
+        return None if v is None else ins[int(v[0])]
+
+    if _attr(node, "rq_in_scl_idx") is not None:  # integer mode (path A)
+        if is_conv:
+            acc = eval_op("qnn.conv2d", _conv_attrs(node), [ins[0], ins[1], arg("src_zp_idx"), arg("wgh_zp_idx")])
+            ch_axis = (_conv_attrs(node)["out_layout"] or _conv_attrs(node)["data_layout"]).index("C")
+        else:
+            acc = dense(ins[0], ins[1], arg("src_zp_idx"), arg("wgh_zp_idx"))
+            ch_axis = acc.ndim - 1
+        bias = arg("bias_idx")
+        if bias is not None:
+            shp = [1] * acc.ndim
+            shp[ch_axis] = -1
+            acc = _wrap_add_i32(acc, np.asarray(bias).reshape(shp).astype(np.int32))
+        y = requantize(acc, arg("rq_in_scl_idx"), arg("rq_in_zp_idx"), arg("rq_out_scl_idx"),
+                       int(np.asarray(arg("rq_out_zp_idx")).reshape(-1)[0]), int(_attr(node, "rq_axis", ["-1"])[0]),
+                       _attr(node, "rounding", ["None"])[0], _attr(node, "compute_dtype", ["None"])[0],
+                       _attr(node, "rq_out_dtype", ["int32"])[0])
+        y = eval_op("clip", dict(a_min=float(_attr(node, "clip_a_min")[0]), a_max=float(_attr(node, "clip_a_max")[0])), [y])
+        y = y.astype(_attr(node, "cast_dtype")[0])
+        s = arg("sum_idx")
+        if s is not None:
+            y = qnn_add(y, s, arg("sum_lhs_scl_idx"), arg("sum_lhs_zp_idx"), arg("sum_rhs_scl_idx"), arg("sum_rhs_zp_idx"),
+                        arg("sum_out_scl_idx"), arg("sum_out_zp_idx"))
+            y = eval_op("clip", dict(a_min=float(_attr(node, "sum_clip_a_min")[0]),
+                                     a_max=float(_attr(node, "sum_clip_a_max")[0])), [y])
+        return y
+    # float mode (path B): zero zero-points, float post-ops
+    if is_conv:
+        acc = eval_op("qnn.conv2d", _conv_attrs(node), [ins[0], ins[1], np.int32(0), np.int32(0)])
+        ch_axis = (_conv_attrs(node)["out_layout"] or _conv_attrs(node)["data_layout"]).index("C")
+    else:
+        acc = dense(ins[0], ins[1], 0, 0)
+        ch_axis = acc.ndim - 1
+    act = _attr(node, "activation")
+    act_scl = float(np.asarray(ins[int(act[1])]).reshape(-1)[0]) if act else 1.0
+    sum_scl = arg("sum_scl_idx")
+    dst_zp = arg("dst_zp_idx")
+    out_dtype = node["attrs"]["dtype"][0][0]
+    return dnnl_float_epilogue(acc, ch_axis, arg("bias_idx"), arg("o_scl_idx"), act_scl, arg("sum_idx"),
+                               0.0 if sum_scl is None else float(np.asarray(sum_scl).reshape(-1)[0]),
+                               0.0 if dst_zp is None else float(np.asarray(dst_zp).reshape(-1)[0]), out_dtype)
+
+
+def _plain_attrs(node):
+    a = {}
+    for k, v in node.get("attrs", {}).items():
+        if k in ("shape", "dtype", "num_inputs", "num_outputs"):
+            continue
+        a[k] = v[0]
+    return a
+
+
+def _eval_json_node(node, ins):
+    op = node["name"]
+    if op.startswith("tachikoma.qnn."):
+        return _eval_composite(node, ins)
+    a = _plain_attrs(node)
+    g = lambda k, d=None: a[k][0] if k in a else d
+    if op == "qnn.conv2d":
+        return eval_op(op, _conv_attrs(node), ins)
+    if op == "qnn.requantize":
+        return eval_op(op, dict(axis=int(g("axis", -1)), rounding=g("rounding", "None"),
+                                compute_dtype=g("compute_dtype", "None"), out_dtype=g("out_dtype")), ins)
+    if op == "clip":
+        return eval_op(op, dict(a_min=float(g("a_min")), a_max=float(g("a_max"))), ins)
+    if op == "cast":
+        # the cast's own "dtype" attribute is shadowed by the node's type list (codegen_json.h:228-231)
+        return eval_op(op, dict(dtype=node["attrs"]["dtype"][0][0]), ins)
+    if op == "nn.bias_add":
+        return eval_op(op, dict(axis=int(g("axis", 1))), ins)
+    if op in ("nn.max_pool2d", "nn.avg_pool2d"):
+        return eval_op(op, dict(pool_size=[int(x) for x in a["pool_size"]], strides=[int(x) for x in a["strides"]],
+                                padding=[int(x) for x in a["padding"]], layout=g("layout", "NCHW"),
+                                count_include_pad=bool(int(g("count_include_pad", 0)))), ins)
+    if op == "nn.global_avg_pool2d":
+        return eval_op(op, dict(layout=g("layout", "NCHW")), ins)
+    if op == "nn.pad":
+        pw = [int(x) for x in a["pad_width"]]
+        return eval_op(op, dict(pad_width=[[pw[2 * i], pw[2 * i + 1]] for i in range(len(pw) // 2)]), ins)
+    if op == "reshape":
+        return ins[0].reshape(node["attrs"]["shape"][0][0])
+    if op == "transpose":
+        return eval_op(op, dict(axes=[int(x) for x in a["axes"]]), ins)
+    return eval_op(op, {}, ins)  # qnn.dense, qnn.batch_matmul, qnn.add, add, nn.batch_flatten
+
+
+def run_json(graph_json, consts, inputs, want_trace=False):
+    """Evaluate a tachikoma JSON graph.  ``consts``: arrays in const order; ``inputs``: arrays in graph
+    input order.  Returns (outputs, trace) with trace = ordered list of (name, array) records in the
+    runtime's naming (``{op}____topo-index:{nid}____input-num:{i}`` / ``____output-num:0``)."""
+    g = json.loads(graph_json)
+    nodes = g["nodes"]
+    vals = {}
+    ci = ii = 0
+    for nid in g["arg_nodes"]:
+        n = nodes[nid]
+        shape, dtype = n["attrs"]["shape"][0][0], n["attrs"]["dtype"][0][0]
+        if n["op"] == "const":
+            vals[(nid, 0)] = np.ascontiguousarray(consts[ci]).astype(dtype).reshape(shape)
+            ci += 1
+        else:
+            vals[(nid, 0)] = np.ascontiguousarray(inputs[ii]).astype(dtype).reshape(shape)
+            ii += 1
+    trace = []
+    for nid, n in enumerate(nodes):
+        if n["op"] != "kernel":
+            continue
+        ins = [vals[(e[0], e[1])] for e in n["inputs"]]
+        out = _eval_json_node(n, ins)
+        shape, dtype = n["attrs"]["shape"][0][0], n["attrs"]["dtype"][0][0]
+        assert list(out.shape) == list(shape) and str(out.dtype) == dtype, (n["name"], out.shape, shape, out.dtype, dtype)
+        vals[(nid, 0)] = np.ascontiguousarray(out)
+        if want_trace:
+            for i, a in enumerate(ins):
+                trace.append((f"{n['name']}____topo-index:{nid}____input-num:{i}", a))
+            trace.append((f"{n['name']}____topo-index:{nid}____output-num:0", vals[(nid, 0)]))
+    outs = [vals[(h[0], h[1])] for h in g["heads"]]
+    return outs, trace
+
+
+_DL = {"int8": (0, 8), "uint8": (1, 8), "int16": (0, 16), "int32": (0, 32), "int64": (0, 64), "float32": (2, 32)}
+
+
+def save_ndarray_list(records):
+    """TVM NDArray-list blob (src/runtime/file_utils.cc:210-229 SaveParams; per-array layout
+    include/tvm/runtime/ndarray.h:449-494 SaveDLTensor), written independently of the CUDA library."""
+    import struct
+
+    out = bytearray()
+    out += struct.pack("<QQ", 0xF7E58D4F05049CB7, 0)
+    out += struct.pack("<Q", len(records))
+    for name, _ in records:
+        b = name.encode()
+        out += struct.pack("<Q", len(b)) + b
+    out += struct.pack("<Q", len(records))
+    for _, arr in records:
+        arr = np.asarray(arr)
+        shape = arr.shape
+        arr = np.ascontiguousarray(arr)
+        code, bits = _DL[str(arr.dtype)]
+        out += struct.pack("<QQ", 0xDD5E40F096B4A13F, 0)
+        out += struct.pack("<iii", 1, 0, len(shape))
+        out += struct.pack("<BBH", code, bits, 1)
+        for d in shape:
+            out += struct.pack("<q", d)
+        out += struct.pack("<q", arr.nbytes)
+        out += arr.tobytes()
+    return bytes(out)
+
+
+def load_ndarray_list(blob):
+    """Inverse of save_ndarray_list (src/runtime/file_utils.cc:184-208 LoadParams)."""
+    import struct
+
+    pos = 0
+    magic, _ = struct.unpack_from("<QQ", blob, pos); pos += 16
+    assert magic == 0xF7E58D4F05049CB7
+    (n,) = struct.unpack_from("<Q", blob, pos); pos += 8
+    names = []
+    for _ in range(n):
+        (ln,) = struct.unpack_from("<Q", blob, pos); pos += 8
+        names.append(blob[pos:pos + ln].decode()); pos += ln
+    (m,) = struct.unpack_from("<Q", blob, pos); pos += 8
+    assert m == n
+    inv = {v: k for k, v in _DL.items()}
+    recs = []
+    for i in range(n):
+        magic, _ = struct.unpack_from("<QQ", blob, pos); pos += 16
+        assert magic == 0xDD5E40F096B4A13F
+        _dev, _id, ndim = struct.unpack_from("<iii", blob, pos); pos += 12
+        code, bits, _lanes = struct.unpack_from("<BBH", blob, pos); pos += 4
+        shape = struct.unpack_from("<" + "q" * ndim, blob, pos); pos += 8 * ndim
+        (nbytes,) = struct.unpack_from("<q", blob, pos); pos += 8
+        arr = np.frombuffer(blob, dtype=inv[(code, bits)], count=nbytes // (bits // 8), offset=pos).reshape(shape)
+        pos += nbytes
+        recs.append((names[i], arr))
+    return recs

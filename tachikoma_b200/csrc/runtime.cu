@@ -974,3 +974,508 @@ static void plan_transpose(Planner& P, int nid) {
     launch_permute4(c.ptr(x_eid, kLogical), c.ptr(y_eid, kLogical), elem, oshape.data(), ostr.data(), c.s);
   });
 }
+
+// ------------------------------------------------------------------------------------------------
+// BuildEngine (tachikoma_json_runtime.cc:240-290): walk the nodes, dispatch on the operator name
+// ------------------------------------------------------------------------------------------------
+static void build_plan(tkb_runtime* rt) {
+  Planner P(rt);
+  Graph& g = rt->g;
+  rt->steps.clear();
+  rt->arena_bytes = 0;
+  rt->macs = rt->hbm_bytes = 0;
+  rt->trace_recs.clear();
+  for (auto& e : rt->ent) { e.off[0] = e.off[1] = -1; e.alias_of = -1; }
+  for (uint32_t eid : g.input_eids) rt->ent[eid].off[kLogical] = P.arena_alloc(rt->ent[eid].bytes());  // H2D staging
+  P.plan << "plan for " << rt->symbol << " (conv_impl=" << rt->conv_impl << ")\n";
+  static const std::regex conv_pat(".*conv2d.*"), dense_pat(".*dense.*");
+  for (size_t nid = 0; nid < g.nodes.size(); ++nid) {
+    const GNode& n = g.nodes[nid];
+    if (n.op_type != "kernel") continue;
+    P.cur_nid = (int)nid;
+    const std::string& op = n.name;
+    if (n.num_outputs != 1) fail("Unsupported op: %s with %u outputs", op.c_str(), n.num_outputs);
+    if (op == "tachikoma.qnn.conv2d") plan_conv(P, (int)nid, true);
+    else if (op == "tachikoma.qnn.dense") plan_dense(P, (int)nid, true);
+    else if (op == "qnn.conv2d") plan_conv(P, (int)nid, false);
+    else if (op == "qnn.dense") plan_dense(P, (int)nid, false);
+    else if (op == "qnn.batch_matmul") plan_batch_matmul(P, (int)nid);
+    else if (op == "qnn.requantize") plan_requantize(P, (int)nid);
+    else if (op == "qnn.add") plan_qnn_add(P, (int)nid);
+    else if (op == "clip" || op == "cast") plan_unary(P, (int)nid);
+    else if (op == "nn.bias_add" || op == "add") plan_add(P, (int)nid);
+    else if (op == "nn.max_pool2d" || op == "nn.avg_pool2d" || op == "nn.global_avg_pool2d") plan_pool(P, (int)nid);
+    else if (op == "nn.pad") plan_pad(P, (int)nid);
+    else if (op == "reshape" || op == "nn.batch_flatten") plan_reshape(P, (int)nid);
+    else if (op == "transpose") plan_transpose(P, (int)nid);
+    else fail("Unsupported op: %s", op.c_str());  // same message as tachikoma_json_runtime.cc:286
+    // trace records of this node: inputs then outputs, in the logical layout
+    for (size_t i = 0; i < n.inputs.size(); ++i)
+      rt->trace_recs.push_back({n.name + "____topo-index:" + std::to_string(nid) + "____input-num:" + std::to_string(i),
+                                (int)g.eid(n.inputs[i]), (int)nid});
+    rt->trace_recs.push_back({n.name + "____topo-index:" + std::to_string(nid) + "____output-num:0", (int)g.eid((uint32_t)nid, 0), (int)nid});
+  }
+  // graph outputs are delivered in the logical layout
+  P.cur_nid = -1;
+  for (auto& h : g.heads) P.need((int)g.eid(h), kLogical);
+  // trace staging plan: tensors that exist in logical layout are copied in place; NHWC-physical ones
+  // are permuted into a device ring first
+  rt->trace_host_off.assign(rt->trace_recs.size(), 0);
+  rt->trace_ring_off.assign(rt->trace_recs.size(), -1);
+  long long hoff = 0, roff = 0;
+  for (size_t i = 0; i < rt->trace_recs.size(); ++i) {
+    const int r = P.root(rt->trace_recs[i].eid);
+    const Entry& e = rt->ent[r];
+    rt->trace_host_off[i] = hoff;
+    hoff += (rt->ent[rt->trace_recs[i].eid].bytes() + 63) & ~63LL;
+    if (!e.is_const && !P.has(r, kLogical)) {
+      rt->trace_ring_off[i] = roff;
+      roff += (e.bytes() + 255) & ~255LL;
+    }
+  }
+  rt->trace_host_bytes = hoff;
+  rt->trace_ring_bytes = roff;
+  P.plan << "arena " << rt->arena_bytes << " B, int8 MACs " << rt->macs << ", algorithmic HBM bytes " << rt->hbm_bytes
+         << ", trace payload " << hoff << " B\n";
+  rt->plan_text = P.plan.str();
+}
+
+// ------------------------------------------------------------------------------------------------
+// run
+// ------------------------------------------------------------------------------------------------
+static Workspace* get_workspace(tkb_runtime* rt, cudaStream_t s) {
+  std::lock_guard<std::mutex> lk(rt->ws_mu);
+  auto& slot = rt->ws[s];
+  if (!slot) {
+    slot.reset(new Workspace());
+    slot->arena_bytes = rt->arena_bytes + 256;
+    CUDA_OK(cudaMalloc((void**)&slot->arena, slot->arena_bytes));
+  }
+  return slot.get();
+}
+
+static void ensure_trace_buffers(tkb_runtime* rt, Workspace* ws) {
+  if (!ws->side) {
+    CUDA_OK(cudaStreamCreateWithFlags(&ws->side, cudaStreamNonBlocking));
+    CUDA_OK(cudaEventCreateWithFlags(&ws->ev, cudaEventDisableTiming));
+  }
+  if (ws->trace_ring_bytes < rt->trace_ring_bytes) {
+    if (ws->trace_ring) cudaFree(ws->trace_ring);
+    CUDA_OK(cudaMalloc((void**)&ws->trace_ring, rt->trace_ring_bytes + 256));
+    ws->trace_ring_bytes = rt->trace_ring_bytes;
+  }
+  if (rt->trace_mode >= 2 && ws->trace_host_bytes < rt->trace_host_bytes) {
+    if (ws->trace_host) cudaFreeHost(ws->trace_host);
+    CUDA_OK(cudaMallocHost((void**)&ws->trace_host, rt->trace_host_bytes + 256));
+    ws->trace_host_bytes = rt->trace_host_bytes;
+  }
+}
+
+// Stage the trace records of node `nid` (records [lo, hi)): D2D permute for NHWC-physical tensors,
+// then (mode 2) D2H on the side stream, ordered after the producing kernels by an event.
+static void trace_node(RunCtx& c, size_t lo, size_t hi) {
+  tkb_runtime* rt = c.rt;
+  for (size_t i = lo; i < hi; ++i) {
+    if (rt->trace_ring_off[i] < 0) continue;
+    const int eid = rt->trace_recs[i].eid;
+    int r = eid;
+    while (rt->ent[r].alias_of >= 0) r = rt->ent[r].alias_of;
+    const Entry& e = rt->ent[r];
+    const long long N = e.shape[0], C = e.shape[1], H = e.shape[2], W = e.shape[3];
+    long long oshape[4] = {N, C, H, W}, istr[4] = {H * W * C, 1, W * C, C};
+    launch_permute4(c.ptr(r, kNHWC), c.ws->trace_ring + rt->trace_ring_off[i], dtype_size(e.dtype), oshape, istr, c.s);
+  }
+  if (rt->trace_mode < 2) return;
+  CUDA_OK(cudaEventRecord(c.ws->ev, c.s));
+  CUDA_OK(cudaStreamWaitEvent(c.ws->side, c.ws->ev, 0));
+  for (size_t i = lo; i < hi; ++i) {
+    const int eid = rt->trace_recs[i].eid;
+    int r = eid;
+    while (rt->ent[r].alias_of >= 0) r = rt->ent[r].alias_of;
+    const Entry& e = rt->ent[r];
+    uint8_t* dst = c.ws->trace_host + rt->trace_host_off[i];
+    const long long bytes = rt->ent[eid].bytes();
+    if (e.is_const) { memcpy(dst, e.host.data(), bytes); continue; }  // constants never leave the host
+    const void* src = rt->trace_ring_off[i] >= 0 ? (const void*)(c.ws->trace_ring + rt->trace_ring_off[i]) : c.ptr(r, kLogical);
+    CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.ws->side));
+  }
+}
+
+static void check_arg(const Entry& e, const tkb_DLTensor* t, int i) {
+  if (!t || !t->data) fail("argument %d is null", i);
+  if (t->strides != nullptr) fail("argument %d: only compact tensors are supported (strides must be NULL)", i);
+  if (t->ndim != (int)e.shape.size()) fail("argument %d: rank %d, expected %d", i, t->ndim, (int)e.shape.size());
+  for (int d = 0; d < t->ndim; ++d)
+    if (t->shape[d] != e.shape[d]) fail("argument %d: dim %d is %lld, expected %lld", i, d, (long long)t->shape[d], (long long)e.shape[d]);
+  if (t->dtype.bits / 8 != dtype_size(e.dtype) || t->dtype.lanes != 1) fail("argument %d: dtype width mismatch", i);
+  if (t->device.device_type != tkbDLCPU && t->device.device_type != tkbDLCUDA && t->device.device_type != tkbDLCUDAHost)
+    fail("argument %d: unsupported device type %d", i, t->device.device_type);
+}
+
+static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_args, cudaStream_t s) {
+  if (!rt->initialized) fail("The module has not been initialized");
+  Graph& g = rt->g;
+  const int n_in = (int)g.input_eids.size(), n_out = (int)g.heads.size();
+  if (n_args != n_in + n_out) fail("Found mismatch in the number of provided data entries and required.");
+  RunCtx c;
+  c.rt = rt;
+  c.s = s;
+  c.ws = get_workspace(rt, s);
+  c.in_ptr.resize(n_in);
+  const long long before = g_launches;
+  // inputs: device tensors are used in place, host tensors are staged (H2D on the caller's stream)
+  for (int i = 0; i < n_in; ++i) {
+    Entry& e = rt->ent[g.input_eids[i]];
+    check_arg(e, args[i], i);
+    uint8_t* p = (uint8_t*)args[i]->data + args[i]->byte_offset;
+    if (args[i]->device.device_type == tkbDLCUDA) {
+      c.in_ptr[i] = p;
+    } else {
+      void* stage = c.ws->arena + rt->ent[g.input_eids[i]].off[kLogical];
+      CUDA_OK(cudaMemcpyAsync(stage, p, e.bytes(), cudaMemcpyHostToDevice, s));
+      c.in_ptr[i] = stage;
+    }
+  }
+  if (rt->trace_mode > 0) ensure_trace_buffers(rt, c.ws);
+  size_t rec = 0;
+  for (size_t si = 0; si < rt->steps.size(); ++si) {
+    rt->steps[si].fn(c);
+    const int nid = rt->steps[si].nid;
+    const bool last_of_node = si + 1 == rt->steps.size() || rt->steps[si + 1].nid != nid;
+    if (rt->trace_mode > 0 && nid >= 0 && last_of_node) {
+      // records are grouped per node in node order; nodes without steps (reshape aliases) in between
+      size_t hi = rec;
+      while (hi < rt->trace_recs.size() && rt->trace_recs[hi].nid <= nid) ++hi;
+      trace_node(c, rec, hi);
+      rec = hi;
+    }
+  }
+  if (rt->trace_mode > 0 && rec < rt->trace_recs.size()) trace_node(c, rec, rt->trace_recs.size());
+  bool host_out = false;
+  for (int j = 0; j < n_out; ++j) {
+    const int eid = (int)g.eid(g.heads[j]);
+    const Entry& e = rt->ent[eid];
+    check_arg(e, args[n_in + j], n_in + j);
+    uint8_t* p = (uint8_t*)args[n_in + j]->data + args[n_in + j]->byte_offset;
+    const bool dev = args[n_in + j]->device.device_type == tkbDLCUDA;
+    CUDA_OK(cudaMemcpyAsync(p, c.ptr(eid, kLogical), e.bytes(), dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+    host_out = host_out || !dev;
+  }
+  CUDA_OK(cudaGetLastError());
+  if (host_out) CUDA_OK(cudaStreamSynchronize(s));  // host results are valid on return, like the reference
+  c.ws->trace_valid = rt->trace_mode >= 2;
+  rt->last_stream = s;
+  {
+    std::lock_guard<std::mutex> lk(rt->ws_mu);
+    rt->launches += g_launches - before;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// serialisation: dmlc stream encoding (u64 length prefixes, 3rdparty/dmlc-core serializer.h:128-193)
+// ------------------------------------------------------------------------------------------------
+static void put_u64(std::vector<uint8_t>& b, uint64_t v) { for (int i = 0; i < 8; ++i) b.push_back((uint8_t)(v >> (8 * i))); }
+static void put_i32(std::vector<uint8_t>& b, int32_t v) { for (int i = 0; i < 4; ++i) b.push_back((uint8_t)((uint32_t)v >> (8 * i))); }
+static void put_str(std::vector<uint8_t>& b, const std::string& s) { put_u64(b, s.size()); b.insert(b.end(), s.begin(), s.end()); }
+
+struct Reader {
+  const uint8_t* p;
+  size_t n, pos = 0;
+  uint64_t u64() {
+    if (pos + 8 > n) fail("binary blob truncated");
+    uint64_t v = 0;
+    for (int i = 0; i < 8; ++i) v |= (uint64_t)p[pos + i] << (8 * i);
+    pos += 8;
+    return v;
+  }
+  std::string str() {
+    uint64_t len = u64();
+    if (pos + len > n) fail("binary blob truncated");
+    std::string s((const char*)p + pos, len);
+    pos += len;
+    return s;
+  }
+};
+
+static void dl_dtype(int dt, uint8_t* code, uint8_t* bits) {
+  switch (dt) {
+    case kI8: *code = 0; *bits = 8; break;
+    case kU8: *code = 1; *bits = 8; break;
+    case kI16: *code = 0; *bits = 16; break;
+    case kI32: *code = 0; *bits = 32; break;
+    case kI64: *code = 0; *bits = 64; break;
+    default: *code = 2; *bits = 32; break;
+  }
+}
+
+// NDArray-list blob: src/runtime/file_utils.cc:210-229 (SaveParams) + include/tvm/runtime/ndarray.h:449-494
+// (SaveDLTensor): magic, reserved, names, count, then per tensor {magic, reserved, DLDevice(cpu,0), ndim,
+// dtype, shape[i64], nbytes(i64), data}.
+static void serialize_trace(tkb_runtime* rt, Workspace* ws, std::vector<uint8_t>& out) {
+  out.clear();
+  out.reserve((size_t)rt->trace_host_bytes + rt->trace_recs.size() * 128 + 64);
+  put_u64(out, 0xF7E58D4F05049CB7ull);
+  put_u64(out, 0);
+  put_u64(out, rt->trace_recs.size());
+  for (auto& r : rt->trace_recs) put_str(out, r.name);
+  put_u64(out, rt->trace_recs.size());
+  for (size_t i = 0; i < rt->trace_recs.size(); ++i) {
+    const Entry& e = rt->ent[rt->trace_recs[i].eid];
+    put_u64(out, 0xDD5E40F096B4A13Full);
+    put_u64(out, 0);
+    put_i32(out, 1);  // kDLCPU
+    put_i32(out, 0);
+    put_i32(out, (int32_t)e.shape.size());
+    uint8_t code, bits;
+    dl_dtype(e.dtype, &code, &bits);
+    out.push_back(code);
+    out.push_back(bits);
+    out.push_back(1);
+    out.push_back(0);  // lanes = 1 (u16 LE)
+    for (auto d : e.shape) put_u64(out, (uint64_t)d);
+    const long long bytes = e.bytes();
+    put_u64(out, (uint64_t)bytes);
+    const uint8_t* src = ws->trace_host + rt->trace_host_off[i];
+    out.insert(out.end(), src, src + bytes);
+  }
+}
+
+static tkb_runtime* create_impl(const std::string& symbol, const std::string& json, const std::vector<std::string>& names) {
+  std::unique_ptr<tkb_runtime> rt(new tkb_runtime());
+  rt->symbol = symbol;
+  rt->graph_json = json;
+  rt->const_names = names;
+  for (auto& s : rt->const_names) rt->const_name_ptrs.push_back(s.c_str());
+  rt->g = parse_graph(json, names);
+  rt->ent.resize(rt->g.num_entries());
+  for (size_t nid = 0; nid < rt->g.nodes.size(); ++nid) {
+    const GNode& n = rt->g.nodes[nid];
+    if (n.shapes.size() != rt->g.node_row_ptr[nid + 1] - rt->g.node_row_ptr[nid])
+      fail("node %s: %d shapes for %d entries", n.name.c_str(), (int)n.shapes.size(),
+           (int)(rt->g.node_row_ptr[nid + 1] - rt->g.node_row_ptr[nid]));
+    for (size_t j = 0; j < n.shapes.size(); ++j) {
+      Entry& e = rt->ent[rt->g.eid((uint32_t)nid, (uint32_t)j)];
+      e.shape = n.shapes[j];
+      e.dtype = dtype_from_string(n.dtypes[j]);
+      e.is_const = n.op_type == "const";
+      e.is_input = n.op_type == "input";
+    }
+  }
+  for (size_t i = 0; i < rt->g.input_eids.size(); ++i) rt->ent[rt->g.input_eids[i]].input_index = (int)i;
+  return rt.release();
+}
+
+}  // namespace tkb
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+using namespace tkb;
+
+#define TKB_TRY try {
+#define TKB_CATCH                                   \
+  }                                                 \
+  catch (const std::exception& ex) {                \
+    g_last_error = ex.what();                       \
+    return -1;                                      \
+  }                                                 \
+  return 0;
+
+extern "C" {
+
+const char* tkb_last_error(void) { return g_last_error.c_str(); }
+const char* tkb_type_key(void) { return "tachikoma_json"; }
+const char* tkb_version(void) { return "tkb200 0.1 sm_100a tcgen05.kind::i8+TMA"; }
+
+int tkb_create(const char* symbol, const char* graph_json, const char* const* const_names, int n_consts, tkb_handle* out) {
+  TKB_TRY
+  if (!symbol || !graph_json || !out) fail("tkb_create: null argument");
+  std::vector<std::string> names;
+  for (int i = 0; i < n_consts; ++i) names.emplace_back(const_names[i]);
+  *out = create_impl(symbol, graph_json, names);
+  TKB_CATCH
+}
+
+int tkb_free(tkb_handle h) {
+  TKB_TRY
+  if (!h) return 0;
+  for (auto& kv : h->ws) {
+    Workspace* w = kv.second.get();
+    if (w->arena) cudaFree(w->arena);
+    if (w->trace_ring) cudaFree(w->trace_ring);
+    if (w->trace_host) cudaFreeHost(w->trace_host);
+    if (w->side) cudaStreamDestroy(w->side);
+    if (w->ev) cudaEventDestroy(w->ev);
+  }
+  for (void* p : h->dev_allocs) cudaFree(p);
+  delete h;
+  TKB_CATCH
+}
+
+int tkb_save_binary(tkb_handle h, const void** blob, size_t* len) {
+  TKB_TRY
+  h->blob.clear();
+  put_str(h->blob, h->symbol);
+  put_str(h->blob, h->graph_json);
+  put_u64(h->blob, h->const_names.size());
+  for (auto& s : h->const_names) put_str(h->blob, s);
+  *blob = h->blob.data();
+  *len = h->blob.size();
+  TKB_CATCH
+}
+
+int tkb_load_binary(const void* blob, size_t len, tkb_handle* out) {
+  TKB_TRY
+  Reader r{(const uint8_t*)blob, len};
+  std::string symbol = r.str(), json = r.str();
+  uint64_t n = r.u64();
+  std::vector<std::string> names;
+  for (uint64_t i = 0; i < n; ++i) names.push_back(r.str());
+  *out = create_impl(symbol, json, names);
+  TKB_CATCH
+}
+
+const char* tkb_get_symbol(tkb_handle h) { return h->symbol.c_str(); }
+
+int tkb_get_const_vars(tkb_handle h, const char* const** names, int* n) {
+  *names = h->const_name_ptrs.data();
+  *n = (int)h->const_name_ptrs.size();
+  return 0;
+}
+
+int tkb_num_inputs(tkb_handle h) { return (int)h->g.input_eids.size(); }
+int tkb_num_outputs(tkb_handle h) { return (int)h->g.heads.size(); }
+
+int tkb_init(tkb_handle h, const tkb_DLTensor* const* consts, int n_consts) {
+  TKB_TRY
+  std::lock_guard<std::mutex> guard(h->init_mu);
+  if (h->initialized) return 0;
+  if (n_consts != (int)h->g.const_nids.size()) fail("The number of input constants must match the number of required.");
+  for (int i = 0; i < n_consts; ++i) {
+    Entry& e = h->ent[h->g.eid(h->g.const_nids[i], 0)];
+    check_arg(e, consts[i], i);
+    e.host.resize((size_t)e.bytes());
+    const uint8_t* p = (const uint8_t*)consts[i]->data + consts[i]->byte_offset;
+    if (consts[i]->device.device_type == tkbDLCUDA) CUDA_OK(cudaMemcpy(e.host.data(), p, e.host.size(), cudaMemcpyDeviceToHost));
+    else memcpy(e.host.data(), p, e.host.size());
+  }
+  build_plan(h);
+  h->initialized = true;
+  TKB_CATCH
+}
+
+int tkb_run(tkb_handle h, const tkb_DLTensor* const* args, int n_args, void* cuda_stream) {
+  TKB_TRY
+  run_impl(h, args, n_args, (cudaStream_t)cuda_stream);
+  TKB_CATCH
+}
+
+int tkb_packed_run(void* args, int* type_codes, int num_args, void* out_ret_value, int* out_ret_tcode, void* resource_handle) {
+  TKB_TRY
+  (void)out_ret_value; (void)out_ret_tcode; (void)resource_handle;
+  union Value { int64_t v_int64; double v_float64; void* v_handle; const char* v_str; };
+  Value* a = (Value*)args;
+  if (num_args < 1 || type_codes[0] != 3) fail("tkb_packed_run: args[0] must be the module handle");
+  std::vector<const tkb_DLTensor*> ts;
+  for (int i = 1; i < num_args; ++i) {
+    if (type_codes[i] != 7 && type_codes[i] != 13) fail("Expect NDArray or DLTensor as inputs");
+    ts.push_back((const tkb_DLTensor*)a[i].v_handle);  // an NDArray handle points at its DLTensor
+  }
+  run_impl((tkb_handle)a[0].v_handle, ts.data(), (int)ts.size(), nullptr);
+  TKB_CATCH
+}
+
+int tkb_set_option(tkb_handle h, const char* key, const char* value) {
+  TKB_TRY
+  const std::string k = key, v = value;
+  if (k == "conv_impl") {
+    if (v != "auto" && v != "simt" && v != "tc") fail("conv_impl must be auto|simt|tc");
+    if (h->initialized && v != h->conv_impl) {
+      h->conv_impl = v;
+      std::lock_guard<std::mutex> guard(h->init_mu);
+      for (auto& kv : h->ws) {  // arena layout changes: drop the workspaces
+        cudaFree(kv.second->arena);
+        if (kv.second->trace_ring) cudaFree(kv.second->trace_ring);
+        if (kv.second->trace_host) cudaFreeHost(kv.second->trace_host);
+      }
+      h->ws.clear();
+      build_plan(h);
+    }
+    h->conv_impl = v;
+  } else {
+    fail("unknown option %s", key);
+  }
+  TKB_CATCH
+}
+
+int64_t tkb_launch_count(tkb_handle h) { return h->launches; }
+const char* tkb_plan_summary(tkb_handle h) { return h->plan_text.c_str(); }
+int tkb_work(tkb_handle h, int64_t* macs, int64_t* hbm_bytes) {
+  if (macs) *macs = h->macs;
+  if (hbm_bytes) *hbm_bytes = h->hbm_bytes;
+  return 0;
+}
+
+int tkb_trace_enable(tkb_handle h, int mode) {
+  TKB_TRY
+  if (mode < 0 || mode > 2) fail("trace mode must be 0, 1 or 2");
+  h->trace_mode = mode;
+  TKB_CATCH
+}
+
+static Workspace* last_ws(tkb_handle h) {
+  std::lock_guard<std::mutex> lk(h->ws_mu);
+  auto it = h->ws.find(h->last_stream);
+  if (it == h->ws.end()) fail("no run has been executed yet");
+  return it->second.get();
+}
+
+int tkb_trace_sync(tkb_handle h) {
+  TKB_TRY
+  Workspace* ws = last_ws(h);
+  if (ws->side) CUDA_OK(cudaStreamSynchronize(ws->side));
+  TKB_CATCH
+}
+
+int tkb_trace_blob(tkb_handle h, const void** blob, size_t* len) {
+  TKB_TRY
+  Workspace* ws = last_ws(h);
+  if (!ws->trace_valid) fail("no trace captured: call tkb_trace_enable(h, 2) before tkb_run");
+  CUDA_OK(cudaStreamSynchronize(ws->side));
+  serialize_trace(h, ws, h->trace_blob_buf);
+  *blob = h->trace_blob_buf.data();
+  *len = h->trace_blob_buf.size();
+  TKB_CATCH
+}
+
+int tkb_trace_save(tkb_handle h, const char* path) {
+  TKB_TRY
+  const void* blob;
+  size_t len;
+  if (tkb_trace_blob(h, &blob, &len) != 0) fail("%s", g_last_error.c_str());
+  FILE* f = fopen(path, "wb");
+  if (!f) fail("cannot open %s for writing", path);
+  const size_t w = fwrite(blob, 1, len, f);
+  fclose(f);
+  if (w != len) fail("short write to %s", path);
+  TKB_CATCH
+}
+
+int64_t tkb_trace_bytes(tkb_handle h) {
+  int64_t n = 0;
+  for (auto& r : h->trace_recs) n += h->ent[r.eid].bytes();
+  return n;
+}
+
+void tkb_fixed_point_multiplier_shift(double multiplier, int32_t* significand, int32_t* exponent) {
+  fixed_point_multiplier_shift(multiplier, significand, exponent);
+}
+
+int tkb_probe_int8_peak(int iters, double* tops, void* cuda_stream) {
+  TKB_TRY
+  if (probe_int8_peak(iters, tops, (cudaStream_t)cuda_stream) != 0)
+    fail("peak probe failed: %s", cudaGetErrorString(cudaGetLastError()));
+  TKB_CATCH
+}
+
+}  // extern "C"

@@ -1,0 +1,215 @@
+"""Synthetic integer-only QNN models for the BASELINE.json configs (random-init quantized weights).
+
+The graphs have exactly the operator chain the reference's PyTorch frontend emits for prequantized
+models (python/tvm/relay/frontend/qnn_torch.py:649-682): qnn.conv2d / qnn.dense (uint8 activations,
+int8 weights, per-output-channel weight scales) -> nn.bias_add (int32) -> qnn.requantize(axis=1,
+int32) -> clip -> cast(uint8); residual joins are qnn.add -> clip (quantized::add_relu); average
+pooling is done on int32 (apply_with_upcast, qnn_torch.py:587-590).  Explicit zero-point padding is
+expressed through the convolution's padding attribute, which is what the reference's SimplifyExpr
+(FoldExplicitPadding) leaves after partition_for_tachikoma (tests/python/contrib/test_tachikoma.py:88).
+
+Output scales are calibrated once on one seeded sample with a float simulation (torch CPU conv used
+as a calculator only) and rounded to 4 significant digits, so that activations keep spanning the
+uint8 range through the whole depth instead of collapsing to the zero point.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import relay as R
+
+
+def _round_sig(x, sig=4):
+    x = float(x)
+    if x == 0:
+        return 0.0
+    from math import floor, log10
+    return round(x, sig - int(floor(log10(abs(x)))) - 1)
+
+
+class _Builder:
+    """Tracks (expr, scale, zero_point) and a float shadow activation used for calibration."""
+
+    def __init__(self, seed, calib_input, in_scale, in_zp):
+        self.rng = np.random.default_rng(seed)
+        self.n_layers = 0
+        import torch
+        self.torch = torch
+        self.shadow = torch.from_numpy(calib_input.astype(np.float32))  # quantized values as floats
+
+    def weights(self, shape, k):
+        w = self.rng.integers(-127, 128, size=shape).astype(np.int8)
+        s_w = (self.rng.uniform(0.5, 1.5, size=shape[0]) / (127.0 * np.sqrt(k))).astype(np.float32)
+        b = self.rng.integers(-(1 << 12), 1 << 12, size=shape[0]).astype(np.int32)
+        return w, s_w, b
+
+    def _calibrate(self, acc, s_x, s_w, relu, ch_axis):
+        """acc: float tensor of int32 accumulators (+bias).  Returns (s_out, zp_out, next shadow)."""
+        torch = self.torch
+        shp = [1] * acc.dim()
+        shp[ch_axis] = -1
+        real = acc * torch.from_numpy((s_x * s_w).astype(np.float32)).reshape(shp)
+        std = float(real.std()) + 1e-12
+        zp_out = 0 if relu else 128
+        s_out = _round_sig(std / (50.0 if relu else 40.0))
+        q = torch.floor(real / s_out + 0.5) + zp_out
+        q = torch.clamp(q, float(zp_out if relu else 0), 255.0)
+        return np.float32(s_out), zp_out, q
+
+    def conv(self, x, s_x, zp_x, oc, ksize, stride=1, pad=0, groups=1, relu=True, residual=None):
+        """x: expr NCHW uint8.  residual: (expr, scale, zp, shadow) joined with qnn.add + relu."""
+        torch = self.torch
+        ic = x.shape[1]
+        w, s_w, b = self.weights((oc, ic // groups, ksize, ksize), ksize * ksize * ic // groups)
+        acc = torch.nn.functional.conv2d(
+            torch.nn.functional.pad(self.shadow - zp_x, (pad, pad, pad, pad)), torch.from_numpy(w.astype(np.float32)),
+            stride=stride, groups=groups) + torch.from_numpy(b.astype(np.float32)).reshape(1, -1, 1, 1)
+        s_out, zp_out, q = self._calibrate(acc, s_x, s_w, relu and residual is None, 1)
+        e = R.qnn_conv2d(x, R.const(w), zp_x, 0, np.float32(s_x), R.const(s_w), (ksize, ksize), oc,
+                         strides=(stride, stride), padding=(pad, pad), groups=groups)
+        e = R.bias_add(e, R.const(b))
+        e = R.qnn_requantize(e, R.const((np.float32(s_x) * s_w).astype(np.float32)), 0, s_out, zp_out, axis=1,
+                             out_dtype="int32")
+        e = R.cast(R.clip(e, float(zp_out if (relu and residual is None) else 0), 255.0), "uint8")
+        self.shadow = q
+        if residual is not None:
+            r_e, r_s, r_zp, r_shadow = residual
+            real = (q - zp_out) * float(s_out) + (r_shadow - r_zp) * float(r_s)
+            so = np.float32(_round_sig(float(real.std()) / 50.0))
+            zo = 0
+            e = R.qnn_add(e, r_e, s_out, zp_out, np.float32(r_s), r_zp, so, zo)
+            e = R.clip(e, float(zo), 255.0)
+            self.shadow = torch.clamp(torch.floor(real / float(so) + 0.5) + zo, float(zo), 255.0)
+            s_out, zp_out = so, zo
+        self.n_layers += 1
+        return e, s_out, zp_out
+
+    def dense(self, x, s_x, zp_x, units, relu=True):
+        torch = self.torch
+        k = x.shape[-1]
+        w, s_w, b = self.weights((units, k), k)
+        acc = (self.shadow - zp_x) @ torch.from_numpy(w.astype(np.float32)).T + torch.from_numpy(b.astype(np.float32))
+        s_out, zp_out, q = self._calibrate(acc, s_x, s_w, relu, acc.dim() - 1)
+        e = R.qnn_dense(x, R.const(w), zp_x, 0, np.float32(s_x), R.const(s_w), units)
+        e = R.bias_add(e, R.const(b), axis=1 if len(x.shape) == 2 else -1)
+        e = R.qnn_requantize(e, R.const((np.float32(s_x) * s_w).astype(np.float32)), 0, s_out, zp_out, axis=-1,
+                             out_dtype="int32")
+        e = R.cast(R.clip(e, float(zp_out if relu else 0), 255.0), "uint8")
+        self.shadow = q
+        self.n_layers += 1
+        return e, s_out, zp_out
+
+    def max_pool(self, x, k, stride, pad):
+        self.shadow = self.torch.nn.functional.max_pool2d(self.shadow, k, stride, pad)
+        return R.max_pool2d(x, (k, k), (stride, stride), (pad, pad))
+
+    def avg_pool_upcast(self, x, k=None, stride=None):
+        """apply_with_upcast: cast int32 -> avg pool (truncating) -> cast uint8."""
+        e = R.cast(x, "int32")
+        if k is None:
+            e = R.global_avg_pool2d(e)
+            self.shadow = self.torch.trunc(self.shadow.mean(dim=(2, 3), keepdim=True))
+        else:
+            e = R.avg_pool2d(e, (k, k), (stride, stride))
+            self.shadow = self.torch.trunc(self.torch.nn.functional.avg_pool2d(self.shadow, k, stride))
+        return R.cast(e, "uint8")
+
+
+def _input(shape, seed=1):
+    return np.random.default_rng(seed).integers(0, 256, size=shape).astype(np.uint8)
+
+
+def synthetic_input(name, batch, seed=1):
+    shape = {"mlp": (batch, 784), "lenet5": (batch, 1, 28, 28), "resnet18": (batch, 3, 224, 224),
+             "mobilenetv2": (batch, 3, 224, 224)}[name]
+    return _input(shape, seed)
+
+
+IN_SCALE, IN_ZP = np.float32(1.0 / 64), 128
+
+
+def mlp(batch=256, seed=0):
+    """C1: int8 MLP 784-128-10 (qnn.dense + requantize)."""
+    x = R.var("data", (batch, 784), "uint8")
+    b = _Builder(seed, _input((4, 784), 7), IN_SCALE, IN_ZP)
+    e, s, zp = b.dense(x, IN_SCALE, IN_ZP, 128, relu=True)
+    e, s, zp = b.dense(e, s, zp, 10, relu=False)
+    return R.Function([x], e)
+
+
+def lenet5(batch=256, seed=0):
+    """C2: LeNet-5: conv5x5x6 -> pool -> conv5x5x16 -> pool -> 120 -> 84 -> 10."""
+    x = R.var("data", (batch, 1, 28, 28), "uint8")
+    b = _Builder(seed, _input((4, 1, 28, 28), 7), IN_SCALE, IN_ZP)
+    e, s, zp = b.conv(x, IN_SCALE, IN_ZP, 6, 5, pad=2)
+    e = b.max_pool(e, 2, 2, 0)
+    e, s, zp = b.conv(e, s, zp, 16, 5)
+    e = b.max_pool(e, 2, 2, 0)
+    e = R.batch_flatten(e)
+    b.shadow = b.shadow.reshape(b.shadow.shape[0], -1)
+    e, s, zp = b.dense(e, s, zp, 120)
+    e, s, zp = b.dense(e, s, zp, 84)
+    e, s, zp = b.dense(e, s, zp, 10, relu=False)
+    return R.Function([x], e)
+
+
+def resnet18(batch=64, seed=0, image=224, num_classes=1000):
+    """C3: ResNet-18 (torchvision topology, quantized::conv2d_relu / add_relu chain)."""
+    x = R.var("data", (batch, 3, image, image), "uint8")
+    b = _Builder(seed, _input((1, 3, image, image), 7), IN_SCALE, IN_ZP)
+    e, s, zp = b.conv(x, IN_SCALE, IN_ZP, 64, 7, stride=2, pad=3)
+    e = b.max_pool(e, 3, 2, 1)
+    for stage, (oc, stride) in enumerate([(64, 1), (128, 2), (256, 2), (512, 2)]):
+        for blk in range(2):
+            st = stride if blk == 0 else 1
+            ident, ident_s, ident_zp, ident_shadow = e, s, zp, b.shadow
+            y, ys, yzp = b.conv(e, s, zp, oc, 3, stride=st, pad=1)
+            main_shadow = b.shadow
+            if st != 1 or ident.shape[1] != oc:
+                b.shadow = ident_shadow
+                ident, ident_s, ident_zp = b.conv(ident, ident_s, ident_zp, oc, 1, stride=st, relu=False)
+                ident_shadow = b.shadow
+            b.shadow = main_shadow
+            e, s, zp = b.conv(y, ys, yzp, oc, 3, pad=1, relu=True, residual=(ident, ident_s, ident_zp, ident_shadow))
+    e = b.avg_pool_upcast(e)
+    e = R.batch_flatten(e)
+    b.shadow = b.shadow.reshape(b.shadow.shape[0], -1)
+    e, s, zp = b.dense(e, s, zp, num_classes, relu=False)
+    return R.Function([x], e)
+
+
+def mobilenetv2(batch=128, seed=0, image=224, num_classes=1000):
+    """C4: MobileNetV2 (depthwise 3x3 + pointwise 1x1 qnn.conv2d, ReLU6 folded into the clip)."""
+    x = R.var("data", (batch, 3, image, image), "uint8")
+    b = _Builder(seed, _input((1, 3, image, image), 7), IN_SCALE, IN_ZP)
+    e, s, zp = b.conv(x, IN_SCALE, IN_ZP, 32, 3, stride=2, pad=1)
+    cfg = [(1, 16, 1, 1), (6, 24, 2, 2), (6, 32, 3, 2), (6, 64, 4, 2), (6, 96, 3, 1), (6, 160, 3, 2), (6, 320, 1, 1)]
+    ic = 32
+    for t, c, n, st0 in cfg:
+        for i in range(n):
+            st = st0 if i == 0 else 1
+            ident, ident_s, ident_zp, ident_shadow = e, s, zp, b.shadow
+            y, ys, yzp = e, s, zp
+            if t != 1:
+                y, ys, yzp = b.conv(y, ys, yzp, ic * t, 1)
+            y, ys, yzp = b.conv(y, ys, yzp, ic * t, 3, stride=st, pad=1, groups=ic * t)
+            if st == 1 and ic == c:
+                # linear bottleneck joined with quantized::add (no relu): qnn.add -> clip(0, 255)
+                y, ys, yzp = b.conv(y, ys, yzp, c, 1, relu=False)
+                real = (b.shadow - yzp) * float(ys) + (ident_shadow - ident_zp) * float(ident_s)
+                so, zo = np.float32(_round_sig(float(real.std()) / 40.0)), 128
+                y = R.qnn_add(y, ident, ys, yzp, np.float32(ident_s), ident_zp, so, zo)
+                b.shadow = b.torch.clamp(b.torch.floor(real / float(so) + 0.5) + zo, 0.0, 255.0)
+                ys, yzp = so, zo
+            else:
+                y, ys, yzp = b.conv(y, ys, yzp, c, 1, relu=False)
+            e, s, zp, ic = y, ys, yzp, c
+    e, s, zp = b.conv(e, s, zp, 1280, 1)
+    e = b.avg_pool_upcast(e)
+    e = R.batch_flatten(e)
+    b.shadow = b.shadow.reshape(b.shadow.shape[0], -1)
+    e, s, zp = b.dense(e, s, zp, num_classes, relu=False)
+    return R.Function([x], e)
+
+
+MODELS = {"mlp": mlp, "lenet5": lenet5, "resnet18": resnet18, "mobilenetv2": mobilenetv2}

@@ -1,0 +1,282 @@
+"""ctypes binding of libtkb200.so -- plays the role the GraphExecutor / ConstLoaderModule play for the
+reference's TachikomaJSONRuntime (src/runtime/graph_executor/graph_executor.cc:524-562,
+src/runtime/const_loader_module.cc:124-131): create the module from (symbol, graph_json,
+const_names), bind the constants once through ``__init_<symbol>``, then call ``<symbol>`` with the
+inputs followed by caller-allocated outputs.
+
+There is no CPU fallback: if the CUDA library is missing or no CUDA device is present the calls
+raise.  PyTorch is used only to own device memory / streams in the convenience helpers."""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+kDLCPU, kDLCUDA, kDLCUDAHost = 1, 2, 3
+
+
+class DLDevice(ctypes.Structure):
+    _fields_ = [("device_type", ctypes.c_int32), ("device_id", ctypes.c_int32)]
+
+
+class DLDataType(ctypes.Structure):
+    _fields_ = [("code", ctypes.c_uint8), ("bits", ctypes.c_uint8), ("lanes", ctypes.c_uint16)]
+
+
+class DLTensor(ctypes.Structure):
+    _fields_ = [("data", ctypes.c_void_p), ("device", DLDevice), ("ndim", ctypes.c_int32), ("dtype", DLDataType),
+                ("shape", ctypes.POINTER(ctypes.c_int64)), ("strides", ctypes.POINTER(ctypes.c_int64)),
+                ("byte_offset", ctypes.c_uint64)]
+
+
+_DT = {"int8": (0, 8), "uint8": (1, 8), "int16": (0, 16), "int32": (0, 32), "int64": (0, 64), "float32": (2, 32)}
+
+
+class TachikomaError(RuntimeError):
+    """Raised with the message of tkb_last_error(), the analogue of tvm.error.TVMError."""
+
+
+def lib_path():
+    return os.path.join(_HERE, "libtkb200.so")
+
+
+def load_library():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = lib_path()
+    if not os.path.exists(path):
+        raise TachikomaError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                             "(there is no CPU fallback for the tachikoma CUDA runtime)")
+    L = ctypes.CDLL(path)
+    H = ctypes.c_void_p
+    L.tkb_last_error.restype = ctypes.c_char_p
+    L.tkb_type_key.restype = ctypes.c_char_p
+    L.tkb_version.restype = ctypes.c_char_p
+    L.tkb_get_symbol.restype = ctypes.c_char_p
+    L.tkb_get_symbol.argtypes = [H]
+    L.tkb_plan_summary.restype = ctypes.c_char_p
+    L.tkb_plan_summary.argtypes = [H]
+    L.tkb_create.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(ctypes.c_char_p), ctypes.c_int,
+                             ctypes.POINTER(H)]
+    L.tkb_free.argtypes = [H]
+    L.tkb_save_binary.argtypes = [H, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t)]
+    L.tkb_load_binary.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(H)]
+    L.tkb_get_const_vars.argtypes = [H, ctypes.POINTER(ctypes.POINTER(ctypes.c_char_p)), ctypes.POINTER(ctypes.c_int)]
+    L.tkb_num_inputs.argtypes = [H]
+    L.tkb_num_outputs.argtypes = [H]
+    L.tkb_init.argtypes = [H, ctypes.POINTER(ctypes.POINTER(DLTensor)), ctypes.c_int]
+    L.tkb_run.argtypes = [H, ctypes.POINTER(ctypes.POINTER(DLTensor)), ctypes.c_int, ctypes.c_void_p]
+    L.tkb_set_option.argtypes = [H, ctypes.c_char_p, ctypes.c_char_p]
+    L.tkb_launch_count.restype = ctypes.c_int64
+    L.tkb_launch_count.argtypes = [H]
+    L.tkb_work.argtypes = [H, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)]
+    L.tkb_trace_enable.argtypes = [H, ctypes.c_int]
+    L.tkb_trace_sync.argtypes = [H]
+    L.tkb_trace_save.argtypes = [H, ctypes.c_char_p]
+    L.tkb_trace_blob.argtypes = [H, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t)]
+    L.tkb_trace_bytes.restype = ctypes.c_int64
+    L.tkb_trace_bytes.argtypes = [H]
+    L.tkb_fixed_point_multiplier_shift.argtypes = [ctypes.c_double, ctypes.POINTER(ctypes.c_int32),
+                                                   ctypes.POINTER(ctypes.c_int32)]
+    L.tkb_fixed_point_multiplier_shift.restype = None
+    L.tkb_probe_int8_peak.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.c_void_p]
+    _LIB = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise TachikomaError(load_library().tkb_last_error().decode())
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+class _Arg:
+    """A DLTensor view of a numpy array (host) or torch tensor (host or CUDA); keeps the owner alive."""
+
+    def __init__(self, x):
+        if _is_torch(x):
+            if not x.is_contiguous():
+                raise TachikomaError("only compact tensors are supported (strides must be NULL)")
+            self.owner = x
+            dtype = str(x.dtype).replace("torch.", "")
+            shape = tuple(x.shape)
+            ptr = x.data_ptr()
+            if x.is_cuda:
+                dev = (kDLCUDA, x.device.index or 0)
+            else:
+                dev = (kDLCUDAHost if x.is_pinned() else kDLCPU, 0)
+        else:
+            x = np.asarray(x)
+            if not x.flags["C_CONTIGUOUS"]:
+                raise TachikomaError("only compact tensors are supported (strides must be NULL)")
+            self.owner = x
+            dtype, shape, ptr, dev = str(x.dtype), x.shape, x.ctypes.data, (kDLCPU, 0)
+        code, bits = _DT[dtype]
+        self.shape = (ctypes.c_int64 * max(len(shape), 1))(*shape)
+        self.t = DLTensor(ctypes.c_void_p(ptr), DLDevice(*dev), len(shape), DLDataType(code, bits, 1), self.shape, None, 0)
+
+
+def _tensor_array(xs):
+    args = [_Arg(x) for x in xs]
+    arr = (ctypes.POINTER(DLTensor) * max(len(args), 1))(*[ctypes.pointer(a.t) for a in args])
+    return args, arr
+
+
+class TachikomaJSONRuntime:
+    """runtime.TachikomaJSONRuntimeCreate(symbol, graph_json, const_names)
+    (src/runtime/contrib/tachikoma/tachikoma_json_runtime.cc:900-906)."""
+
+    type_key = "tachikoma_json"
+
+    def __init__(self, symbol, graph_json, const_names, _handle=None):
+        self._lib = load_library()
+        self._h = ctypes.c_void_p()
+        if _handle is not None:
+            self._h = _handle
+        else:
+            names = (ctypes.c_char_p * max(len(const_names), 1))(*[n.encode() for n in const_names])
+            _check(self._lib.tkb_create(symbol.encode(), graph_json.encode(), names, len(const_names),
+                                        ctypes.byref(self._h)))
+        self._keep = []
+
+    def __del__(self):
+        try:
+            if self._h:
+                self._lib.tkb_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    # -- module functions (json_runtime.h:73-103) ------------------------------------------------
+    def get_symbol(self):
+        return self._lib.tkb_get_symbol(self._h).decode()
+
+    def get_const_vars(self):
+        names = ctypes.POINTER(ctypes.c_char_p)()
+        n = ctypes.c_int()
+        _check(self._lib.tkb_get_const_vars(self._h, ctypes.byref(names), ctypes.byref(n)))
+        return [names[i].decode() for i in range(n.value)]
+
+    def get_function(self, name):
+        sym = self.get_symbol()
+        if name == "get_symbol":
+            return self.get_symbol
+        if name == "get_const_vars":
+            return self.get_const_vars
+        if name == sym:
+            return self.run
+        if name == "__init_" + sym:
+            return self.init
+        return None  # PackedFunc(nullptr)
+
+    __getitem__ = get_function
+
+    @property
+    def num_inputs(self):
+        return self._lib.tkb_num_inputs(self._h)
+
+    @property
+    def num_outputs(self):
+        return self._lib.tkb_num_outputs(self._h)
+
+    def init(self, consts):
+        """``__init_<symbol>``: bind the constants (const_names order) and build the plan."""
+        args, arr = _tensor_array(consts)
+        _check(self._lib.tkb_init(self._h, arr, len(args)))
+        return 0
+
+    def run(self, *tensors, stream=None):
+        """``<symbol>``(inputs..., outputs...): outputs are caller-allocated."""
+        args, arr = _tensor_array(tensors)
+        _check(self._lib.tkb_run(self._h, arr, len(args), ctypes.c_void_p(stream or 0)))
+
+    # -- persistence (json_runtime.h:105-135) ------------------------------------------------------
+    def save_to_binary(self):
+        p, n = ctypes.c_void_p(), ctypes.c_size_t()
+        _check(self._lib.tkb_save_binary(self._h, ctypes.byref(p), ctypes.byref(n)))
+        return ctypes.string_at(p.value, n.value)
+
+    @classmethod
+    def load_from_binary(cls, blob):
+        L = load_library()
+        h = ctypes.c_void_p()
+        buf = ctypes.create_string_buffer(blob, len(blob))
+        _check(L.tkb_load_binary(buf, len(blob), ctypes.byref(h)))
+        return cls(None, None, None, _handle=h)
+
+    # -- options / introspection ---------------------------------------------------------------------
+    def set_option(self, key, value):
+        _check(self._lib.tkb_set_option(self._h, key.encode(), str(value).encode()))
+
+    def plan_summary(self):
+        return self._lib.tkb_plan_summary(self._h).decode()
+
+    def launch_count(self):
+        return int(self._lib.tkb_launch_count(self._h))
+
+    def work(self):
+        macs, hbm = ctypes.c_int64(), ctypes.c_int64()
+        self._lib.tkb_work(self._h, ctypes.byref(macs), ctypes.byref(hbm))
+        return macs.value, hbm.value
+
+    # -- trace -------------------------------------------------------------------------------------------
+    def trace_enable(self, mode):
+        _check(self._lib.tkb_trace_enable(self._h, int(mode)))
+
+    def trace_sync(self):
+        _check(self._lib.tkb_trace_sync(self._h))
+
+    def trace_blob(self):
+        p, n = ctypes.c_void_p(), ctypes.c_size_t()
+        _check(self._lib.tkb_trace_blob(self._h, ctypes.byref(p), ctypes.byref(n)))
+        return ctypes.string_at(p.value, n.value)
+
+    def trace_save(self, path):
+        _check(self._lib.tkb_trace_save(self._h, path.encode()))
+
+    def trace_bytes(self):
+        return int(self._lib.tkb_trace_bytes(self._h))
+
+
+def fixed_point_multiplier_shift(m):
+    s, e = ctypes.c_int32(), ctypes.c_int32()
+    load_library().tkb_fixed_point_multiplier_shift(float(m), ctypes.byref(s), ctypes.byref(e))
+    return s.value, e.value
+
+
+def probe_int8_peak(iters=2000):
+    t = ctypes.c_double()
+    _check(load_library().tkb_probe_int8_peak(int(iters), ctypes.byref(t), None))
+    return t.value
+
+
+def create_executor(func, params=None, mode="int", conv_impl="auto"):
+    """Partition + codegen + create + init in one call; returns (module, run) where
+    ``run(**inputs) -> numpy array`` uses host buffers (the reference's graph-executor usage)."""
+    from . import tachikoma as T
+
+    part = T.partition_for_tachikoma(func, params, mode=mode)
+    symbol, graph_json, const_names, consts = T.serialize(part)
+    mod = TachikomaJSONRuntime(symbol, graph_json, const_names)
+    mod.set_option("conv_impl", conv_impl)
+    mod.init(consts)
+    out_shape, out_dtype = part.body.shape, part.body.dtype
+    names = [p.name for p in part.params]
+    dtypes = {p.name: p.dtype for p in part.params}
+    shapes = {p.name: p.shape for p in part.params}
+
+    def run(**inputs):
+        ins = [np.ascontiguousarray(np.asarray(inputs[n]).astype(dtypes[n]).reshape(shapes[n])) for n in names]
+        out = np.empty(out_shape, dtype=out_dtype)
+        mod.run(*ins, out)
+        return out
+
+    return mod, run

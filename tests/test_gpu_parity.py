@@ -1,0 +1,202 @@
+"""GPU parity tests (run with -m gpu on the B200 box): the CUDA path, called through the C ABI
+(libtkb200.so), against the CPU oracle on the same inputs.  Bit-exact for the integer path
+(np.testing.assert_equal); the oneDNN-style float epilogue mode is judged at +-1 like the
+reference's own test (tests/python/contrib/test_tachikoma.py:1615-1616)."""
+import numpy as np
+import pytest
+
+from golden_util import load_cases
+from oracle import interp
+from tachikoma_b200 import models, relay as R, runtime as RT, tachikoma as T
+
+pytestmark = pytest.mark.gpu
+CASES = load_cases()
+
+
+def run_gpu(func, inputs, mode="int", conv_impl="auto", trace=False):
+    part = T.partition_for_tachikoma(func, mode=mode)
+    sym, js, names, consts = T.serialize(part)
+    mod = RT.TachikomaJSONRuntime(sym, js, names)
+    mod.set_option("conv_impl", conv_impl)
+    mod.init(consts)
+    if trace:
+        mod.trace_enable(2)
+    ins = [np.ascontiguousarray(np.asarray(inputs[p.name]).astype(p.dtype).reshape(p.shape)) for p in part.params]
+    out = np.empty(part.body.shape, dtype=part.body.dtype)
+    mod.run(*ins, out)
+    return out, mod, (js, consts, ins)
+
+
+@pytest.mark.parametrize("impl", ["auto", "tc"])
+@pytest.mark.parametrize("case", CASES, ids=[c["id"] for c in CASES])
+def test_reference_goldens_on_gpu(case, impl):
+    out, mod, _ = run_gpu(case["func"], case["inputs"], conv_impl=impl)
+    np.testing.assert_equal(out, case["golden"])
+
+
+# ---- tests/python/contrib/test_tachikoma.py:1422-1522 QNN conv profiles, replayed -------------------
+def _conv_profile(shape=(1, 8, 5, 5), ker=(3, 3), pad=(1, 1), dil=(1, 1), oc=16, gr=1, nhwc=False, bias=True,
+                  with_sum=False, asym=False):
+    np.random.seed(0)
+    n, ic, ih, iw = shape
+    d_zp, rq_zp, rq_scl, o_zp = (3, 10, 0.1, 4) if asym else (0, 30, 0.2, 5)
+    oh = (ih + 2 * pad[0] - (ker[0] - 1) * dil[0] - 1) + 1
+    ow = (iw + 2 * pad[1] - (ker[1] - 1) * dil[1] - 1) + 1
+    dl, kl = ("NHWC", "HWIO") if nhwc else ("NCHW", "OIHW")
+    d_shape = (n, ih, iw, ic) if nhwc else shape
+    w_shape = (ker[0], ker[1], ic // gr, oc) if nhwc else (oc, ic // gr, ker[0], ker[1])
+    s_shape = (n, oh, ow, oc) if nhwc else (n, oc, oh, ow)
+    b_shape = (oc,) if nhwc else (oc, 1, 1)
+    data = R.var("in_0", d_shape, "uint8")
+    args = {"in_0": np.random.uniform(0, 20, d_shape).astype("uint8")}
+    wgh = R.const(np.random.uniform(-20, 20, w_shape).astype("int8"))
+    op = R.qnn_conv2d(data, wgh, d_zp, 0, 0.2, 0.1, ker, oc, padding=pad, dilation=dil, groups=gr, data_layout=dl,
+                      kernel_layout=kl)
+    if bias:
+        op = R.add(op, R.const(np.random.uniform(-50, 50, b_shape).astype("int32")))
+    op = R.qnn_requantize(op, np.float32(0.2 * 0.1), 0, rq_scl, rq_zp, out_dtype="int32")
+    op = R.cast(R.clip(op, 0.0, 255.0), "uint8")
+    params = [data]
+    if with_sum:
+        s = R.var("in_1", s_shape, "uint8")
+        args["in_1"] = np.random.uniform(0, 10, s_shape).astype("uint8")
+        params.append(s)
+        op = R.clip(R.qnn_add(op, s, rq_scl, rq_zp, 0.3, 15, 0.2, o_zp), 0.0, 255.0)
+    return R.Function(params, op), args
+
+
+CONV_PROFILES = {
+    "Base": dict(), "NHWC": dict(nhwc=True), "Group": dict(pad=(0, 0), gr=2, asym=True),
+    "DW": dict(shape=(1, 16, 5, 5), pad=(0, 0), gr=16, asym=True), "NoBias": dict(bias=False),
+    "AsymmetricInput": dict(pad=(0, 0), asym=True), "AsymmetricInput_NHWC": dict(pad=(0, 0), asym=True, nhwc=True),
+    "WithSum": dict(pad=(0, 0), asym=True, with_sum=True), "WithSum_NHWC": dict(pad=(0, 0), asym=True, with_sum=True, nhwc=True),
+    "WithSum_NoBias": dict(pad=(0, 0), asym=True, with_sum=True, bias=False),
+    "Dilated": dict(pad=(2, 2), dil=(2, 2)), "AsymmetricPadded": dict(asym=True),
+}
+
+
+@pytest.mark.parametrize("impl", ["simt", "tc"])
+@pytest.mark.parametrize("name", list(CONV_PROFILES))
+def test_qnn_conv2d_profiles(name, impl):
+    func, args = _conv_profile(**CONV_PROFILES[name])
+    ref, _ = interp.run_expr(func, args)
+    out, mod, _ = run_gpu(func, args, mode="int", conv_impl=impl)
+    assert "tachikoma.qnn.conv2d" in mod.plan_summary()
+    np.testing.assert_equal(out, ref)
+    if name != "AsymmetricPadded":  # "Input ZP is not compatible with padding" in the float legalization
+        outf, _, _ = run_gpu(func, args, mode="dnnl_float", conv_impl=impl)
+        # atol=1: int values should match with +-1 quantum value tolerance (test_tachikoma.py:1615)
+        assert np.abs(outf.astype(np.int32) - ref.astype(np.int32)).max() <= 1
+
+
+@pytest.mark.parametrize("impl", ["simt", "tc"])
+@pytest.mark.parametrize("profile", ["Base", "AsymmetricInput", "AsymmetricInput_Sum"])
+def test_qnn_dense_profiles(profile, impl):
+    # tests/python/contrib/test_tachikoma.py:1690-1762: N=2, IC=10, OC=16 (IC=16 added for the TMA path)
+    for ic in (10, 16):
+        np.random.seed(0)
+        asym = profile != "Base"
+        d_zp, rq_zp, rq_scl, o_zp = (3, 10, 0.1, 4) if asym else (0, 30, 0.2, 5)
+        data = R.var("in_0", (2, ic), "uint8")
+        args = {"in_0": np.random.uniform(0, 20, (2, ic)).astype("uint8")}
+        op = R.qnn_dense(data, R.const(np.random.uniform(-20, 20, (16, ic)).astype("int8")), d_zp, 0, 0.2, 0.1, 16)
+        op = R.add(op, R.const(np.random.uniform(-50, 50, (16,)).astype("int32")))
+        op = R.qnn_requantize(op, np.float32(0.02), 0, rq_scl, rq_zp, out_dtype="int32")
+        op = R.cast(R.clip(op, 0.0, 255.0), "uint8")
+        params = [data]
+        if profile.endswith("Sum"):
+            s = R.var("in_1", (2, 16), "uint8")
+            args["in_1"] = np.random.uniform(0, 10, (2, 16)).astype("uint8")
+            params.append(s)
+            op = R.clip(R.qnn_add(op, s, rq_scl, rq_zp, 0.3, 15, 0.2, o_zp), 0.0, 255.0)
+        func = R.Function(params, op)
+        ref, _ = interp.run_expr(func, args)
+        out, _, _ = run_gpu(func, args, conv_impl=impl)
+        np.testing.assert_equal(out, ref)
+        outf, _, _ = run_gpu(func, args, mode="dnnl_float", conv_impl=impl)
+        assert np.abs(outf.astype(np.int32) - ref.astype(np.int32)).max() <= 1
+
+
+GEMM_SHAPES = [(1, 8, 16), (128, 64, 128), (130, 72, 144), (257, 10, 784), (300, 300, 1024), (64, 1000, 512),
+               (1024, 128, 2304), (77, 200, 48)]
+
+
+@pytest.mark.parametrize("mnk", GEMM_SHAPES, ids=[f"{m}x{n}x{k}" for m, n, k in GEMM_SHAPES])
+@pytest.mark.parametrize("xdt", ["uint8", "int8"])
+def test_tcgen05_gemm_vs_oracle(mnk, xdt):
+    m, n, k = mnk
+    rng = np.random.default_rng(m * 7 + n * 3 + k)
+    lo, hi = (0, 256) if xdt == "uint8" else (-128, 128)
+    x = rng.integers(lo, hi, (m, k)).astype(xdt)
+    w = rng.integers(-128, 128, (n, k)).astype("int8")
+    zp = 7 if xdt == "uint8" else -3
+    f = R.Function([R.var("x", (m, k), xdt)], R.qnn_dense(R.var("x", (m, k), xdt), R.const(w), zp, 0, 1.0, 1.0, n))
+    xv = R.var("x", (m, k), xdt)
+    f = R.Function([xv], R.qnn_dense(xv, R.const(w), zp, 0, 1.0, 1.0, n))
+    ref, _ = interp.run_expr(f, {"x": x})
+    out, mod, _ = run_gpu(f, {"x": x}, conv_impl="tc")
+    assert "tcgen05" in mod.plan_summary()
+    np.testing.assert_equal(out, ref)
+
+
+def test_tcgen05_batch_matmul_vs_oracle():
+    rng = np.random.default_rng(5)
+    for (b, m, n, k, yb) in [(3, 128, 64, 64, 3), (4, 50, 130, 32, 1), (12, 128, 128, 64, 12)]:
+        x = rng.integers(-128, 128, (b, m, k)).astype("int8")
+        y = rng.integers(-128, 128, (yb, n, k)).astype("int8")
+        xv, yv = R.var("x", x.shape, "int8"), R.var("y", y.shape, "int8")
+        f = R.Function([xv, yv], R.qnn_batch_matmul(xv, yv, 0, 0, 1.0, 1.0))
+        ref, _ = interp.run_expr(f, {"x": x, "y": y})
+        for impl in ("tc", "simt"):
+            out, _, _ = run_gpu(f, {"x": x, "y": y}, conv_impl=impl)
+            np.testing.assert_equal(out, ref)
+
+
+MODEL_CASES = [("mlp", dict(batch=64)), ("lenet5", dict(batch=8)), ("resnet18", dict(batch=2, image=64, num_classes=100)),
+               ("mobilenetv2", dict(batch=2, image=64, num_classes=100))]
+
+
+@pytest.mark.parametrize("impl", ["simt", "tc"])
+@pytest.mark.parametrize("name,kw", MODEL_CASES, ids=[c[0] for c in MODEL_CASES])
+def test_models_bit_exact_with_trace(name, kw, impl):
+    func = models.MODELS[name](**kw)
+    x = models.synthetic_input(name, kw["batch"])
+    if "image" in kw:
+        x = np.ascontiguousarray(x[:, :, :kw["image"], :kw["image"]])
+    ref, _ = interp.run_expr(func, {"data": x})  # un-partitioned, op by op
+    out, mod, (js, consts, ins) = run_gpu(func, {"data": x}, conv_impl=impl, trace=True)
+    np.testing.assert_equal(out, ref)
+    # serialized trace bytes: GPU-produced blob == oracle-produced blob
+    _, recs = interp.run_json(js, consts, ins, want_trace=True)
+    want = interp.save_ndarray_list(recs)
+    got = mod.trace_blob()
+    assert len(got) == len(want)
+    assert got == want
+    assert mod.launch_count() > 0
+
+
+def test_resnet18_full_size_properties():
+    """Full BASELINE size (224x224, batch 8 here to bound oracle time): GPU tc == GPU simt bit for bit, and the
+    first image equals the oracle."""
+    func = models.resnet18(batch=8)
+    x = models.synthetic_input("resnet18", 8)
+    a, _, _ = run_gpu(func, {"data": x}, conv_impl="tc")
+    b, _, _ = run_gpu(func, {"data": x}, conv_impl="simt")
+    np.testing.assert_equal(a, b)
+    f1 = models.resnet18(batch=1)
+    ref, _ = interp.run_expr(f1, {"data": x[:1]})
+    np.testing.assert_equal(a[:1], ref)
+
+
+def test_int8_peak_probe_runs():
+    tops = RT.probe_int8_peak(2000)
+    assert tops > 100.0, tops
+
+
+def test_unsupported_op_fails_at_init_not_run():
+    xv = R.var("x", (1, 4), "float32")
+    part = R.Function([xv], R.Call("nn.softmax", [xv], {}, (1, 4), "float32"))
+    sym, js, names, consts = T.serialize(part)
+    mod = RT.TachikomaJSONRuntime(sym, js, names)
+    with pytest.raises(RT.TachikomaError, match="Unsupported op: nn.softmax"):
+        mod.init(consts)

@@ -1,0 +1,148 @@
+"""CPU-only tests: host logic, C-ABI symbol table, JSON schema, binary module blob, trace container."""
+import ctypes
+import json
+import os
+import re
+import struct
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import interp
+from tachikoma_b200 import models, relay as R, runtime as RT, tachikoma as T
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _small_graph():
+    np.random.seed(0)
+    x = R.var("in_0", (1, 8, 5, 5), "uint8")
+    w = R.const(np.random.randint(-20, 20, (16, 8, 3, 3)).astype("int8"))
+    c = R.qnn_conv2d(x, w, 0, 0, 0.2, 0.1, (3, 3), 16, padding=(1, 1))
+    c = R.add(c, R.const(np.random.randint(-50, 50, (16, 1, 1)).astype("int32")))
+    c = R.qnn_requantize(c, np.float32(0.02), 0, 0.2, 30, out_dtype="int32")
+    c = R.cast(R.clip(c, 0.0, 255.0), "uint8")
+    s = R.var("in_1", (1, 16, 5, 5), "uint8")
+    c = R.clip(R.qnn_add(c, s, 0.2, 30, 0.3, 15, 0.2, 5), 0.0, 255.0)
+    f = R.Function([x, s], c)
+    ins = {"in_0": np.random.randint(0, 20, (1, 8, 5, 5)).astype("uint8"),
+           "in_1": np.random.randint(0, 10, (1, 16, 5, 5)).astype("uint8")}
+    return f, ins
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "tkb200.h")).read()
+    declared = set(re.findall(r"\b(tkb_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    lib = ctypes.CDLL(RT.lib_path())
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in include/tkb200.h but not exported"
+
+
+def test_pattern_table_names():
+    names = T.pattern_table()
+    assert names[:2] == ["tachikoma.qnn.conv2d", "tachikoma.qnn.dense"]
+    assert "tachikoma.conv2d_bias_relu" in names and "tachikoma.dense_bias_gelu" in names
+    assert len(names) == 4 + 6 * 2 * 8  # tachikoma.py:418-458
+
+
+def test_partition_fuses_chain_and_keeps_argpacker_order():
+    f, _ = _small_graph()
+    part = T.partition_for_tachikoma(f)
+    sym, js, names, consts = T.serialize(part)
+    g = json.loads(js)
+    assert set(g) == {"nodes", "arg_nodes", "heads", "node_row_ptr"}
+    kern = [n for n in g["nodes"] if n["op"] == "kernel"]
+    assert [k["name"] for k in kern] == ["tachikoma.qnn.conv2d"]
+    a = kern[0]["attrs"]
+    assert a["bias_idx"] == [["2"]] and a["sum_idx"] == [["3"]]
+    assert a["PartitionedFromPattern"] == [["qnn.conv2d_add_qnn.requantize_clip_cast_qnn.add_clip_"]]
+    assert a["padding"] == [["1", "1", "1", "1"]] and a["kernel_layout"] == [["OIHW"]]
+    assert names == [f"tachikoma_{sym}_const_{i}" for i in range(len(names))]
+    # float mode follows comp_op_matcher.h:140-156
+    partf = T.partition_for_tachikoma(f, mode="dnnl_float")
+    _, jsf, _, _ = T.serialize(partf)
+    af = [n for n in json.loads(jsf)["nodes"] if n["op"] == "kernel"][0]["attrs"]
+    assert af["o_scl_idx"] == [["4"]] and af["act_scl_idx"] == [["5"]] and af["sum_scl_idx"] == [["6"]]
+    assert af["dst_zp_idx"] == [["7"]] and af["activation"] == [["clip", "8", "9", "10"]]
+
+
+def test_fused_json_equals_unfused_expression_on_oracle():
+    f, ins = _small_graph()
+    ref, _ = interp.run_expr(f, ins)
+    part = T.partition_for_tachikoma(f)
+    _, js, _, consts = T.serialize(part)
+    outs, _ = interp.run_json(js, consts, [ins["in_0"], ins["in_1"]])
+    np.testing.assert_equal(outs[0], ref)
+    partf = T.partition_for_tachikoma(f, mode="dnnl_float")
+    _, jsf, _, constsf = T.serialize(partf)
+    outf, _ = interp.run_json(jsf, constsf, [ins["in_0"], ins["in_1"]])
+    assert np.abs(outf[0].astype(int) - ref.astype(int)).max() <= 1
+
+
+def test_create_symbols_binary_roundtrip_and_errors():
+    f, ins = _small_graph()
+    sym, js, names, consts = T.serialize(T.partition_for_tachikoma(f))
+    mod = RT.TachikomaJSONRuntime(sym, js, names)
+    assert mod.get_symbol() == sym and mod.get_const_vars() == names
+    assert mod.num_inputs == 2 and mod.num_outputs == 1 and mod.type_key == "tachikoma_json"
+    assert mod.get_function("nope") is None and mod.get_function("__init_" + sym) is not None
+    blob = mod.save_to_binary()
+    # dmlc stream: u64 len + symbol, u64 len + json, u64 count + strings
+    (n0,) = struct.unpack_from("<Q", blob, 0)
+    assert blob[8:8 + n0].decode() == sym
+    mod2 = RT.TachikomaJSONRuntime.load_from_binary(blob)
+    assert mod2.get_symbol() == sym and mod2.get_const_vars() == names
+    with pytest.raises(RT.TachikomaError, match="has not been initialized"):
+        mod.run(ins["in_0"], ins["in_1"], np.zeros((1, 16, 5, 5), "uint8"))
+    with pytest.raises(RT.TachikomaError, match="non-existent constant|mismatch"):
+        RT.TachikomaJSONRuntime(sym, js, names[:-1])
+    with pytest.raises(RT.TachikomaError):
+        RT.TachikomaJSONRuntime(sym, "{not json", [])
+
+
+def test_fixed_point_multiplier_matches_oracle_and_reference_pairs():
+    # tests/python/contrib/test_hexagon/test_fixed_point_multiply.py:96-100
+    for (m, s), v in {(1288490240, -2): 0.15, (1395864320, 1): 1.3, (1288490188, 0): 0.6}.items():
+        got = RT.fixed_point_multiplier_shift(v)
+        assert got[1] == s and abs(got[0] - m) <= 64
+    rng = np.random.default_rng(0)
+    for v in list(rng.uniform(1e-6, 8.0, 200)) + [0.0, 0.5, 1.0, 2.0, 1 / 16, 1 / 3, 3.0]:
+        assert RT.fixed_point_multiplier_shift(v) == interp.fixed_point_multiplier_shift(v)
+
+
+def test_trace_container_roundtrip_and_layout():
+    recs = [("a____topo-index:3____output-num:0", np.arange(6, dtype=np.uint8).reshape(2, 3)),
+            ("b", np.array(-5, dtype=np.int32))]
+    blob = interp.save_ndarray_list(recs)
+    assert struct.unpack_from("<Q", blob, 0)[0] == 0xF7E58D4F05049CB7  # file_utils.h:107
+    back = interp.load_ndarray_list(blob)
+    assert [n for n, _ in back] == [n for n, _ in recs]
+    for (_, a), (_, b) in zip(recs, back):
+        assert a.dtype == b.dtype and a.shape == b.shape and (a == b).all()
+
+
+def test_models_partition_fully_and_match_unfused_oracle():
+    for name, kw in [("mlp", dict(batch=4)), ("lenet5", dict(batch=2)), ("resnet18", dict(batch=1, image=32, num_classes=10))]:
+        f = models.MODELS[name](**kw)
+        x = models.synthetic_input(name, kw["batch"])
+        if "image" in kw:
+            x = np.ascontiguousarray(x[:, :, :kw["image"], :kw["image"]])
+        ref, _ = interp.run_expr(f, {"data": x})
+        part = T.partition_for_tachikoma(f)
+        _, js, _, consts = T.serialize(part)
+        ops = [n["name"] for n in json.loads(js)["nodes"] if n["op"] == "kernel"]
+        assert not any(o.startswith("qnn.") for o in ops), ops  # every QNN chain landed in a composite
+        outs, _ = interp.run_json(js, consts, [x])
+        np.testing.assert_equal(outs[0], ref)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "tachikoma_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h", ".cc")):
+                src = open(os.path.join(dirpath, fn)).read()
+                assert "oracle" not in src.replace("test oracle", ""), f"{fn} mentions the oracle"

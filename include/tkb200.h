@@ -84,12 +84,14 @@ const char* tkb_last_error(void);
 
 /* --- options / introspection ------------------------------------------------------------------ */
 /* Known keys: "conv_impl" = "auto"|"simt"|"tc" (tensor-core tcgen05 path vs CUDA-core path),
- *             "trace_acc" = "0"|"1" (also record int32 accumulators of composites). */
+ *             "time_tc"   = "0"|"1" (bracket every tcgen05 GEMM launch with CUDA events). */
 int tkb_set_option(tkb_handle h, const char* key, const char* value);
 /* Number of kernels this library launched on behalf of h since creation (bench.py "gpu_launches"). */
 int64_t tkb_launch_count(tkb_handle h);
 /* Human-readable plan: one line per kernel node with the kernel chosen and its algorithmic work. */
 const char* tkb_plan_summary(tkb_handle h);
+/* With option time_tc=1: summed device time (ms) and count of the tcgen05 GEMM launches of the last run. */
+int tkb_tc_time(tkb_handle h, double* ms, int* launches);
 /* Total int8 multiply-accumulates and algorithmic HBM bytes of one run (roofline numerators). */
 int tkb_work(tkb_handle h, int64_t* macs, int64_t* hbm_bytes);
 

@@ -96,7 +96,8 @@ struct Workspace {
   long long trace_ring_bytes = 0, trace_host_bytes = 0;
   cudaStream_t side = nullptr;
   cudaEvent_t ev = nullptr;
-  std::vector<cudaEvent_t> node_events;
+  std::vector<cudaEvent_t> tc_events;  // begin/end pairs around tcgen05 GEMM launches (option time_tc)
+  size_t tc_used = 0;
   bool trace_valid = false;
 };
 
@@ -115,7 +116,7 @@ struct tkb_runtime {
   std::mutex init_mu, ws_mu;
   std::unordered_map<cudaStream_t, std::unique_ptr<tkb::Workspace>> ws;
   std::string conv_impl = "auto";
-  bool trace_acc = false;
+  bool time_tc = false;
   int trace_mode = 0;
   std::vector<tkb::TraceRec> trace_recs;        // in emission order
   std::vector<long long> trace_host_off;        // per record
@@ -135,6 +136,15 @@ struct RunCtx {
   Workspace* ws;
   cudaStream_t s;
   std::vector<void*> in_ptr;  // device pointer of each graph input (logical layout)
+  void tc_mark() {  // records an event on the compute stream when kernel timing is on
+    if (!rt->time_tc) return;
+    if (ws->tc_used == ws->tc_events.size()) {
+      cudaEvent_t ev;
+      cudaEventCreate(&ev);
+      ws->tc_events.push_back(ev);
+    }
+    cudaEventRecord(ws->tc_events[ws->tc_used++], s);
+  }
   void* ptr(int eid, int phys) const {
     const Entry* e = &rt->ent[eid];
     while (e->alias_of >= 0) { e = &rt->ent[e->alias_of]; }
@@ -611,8 +621,10 @@ static void plan_conv(Planner& P, int nid, bool composite) {
         launch_im2col(a, col, g, Kp, c.s);
         a = col;
       }
+      c.tc_mark();
       if (launch_gemm_tc(a, wdev, c.ptr(y_eid, phys), 1, (int)M, g.O, Kp, 0, g.a_dtype, g.w_dtype, e, c.s) != 0)
         fail("tcgen05 GEMM launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+      c.tc_mark();
     });
   } else {
     void* wdev = P.dev_upload(w_ohwi.data(), w_ohwi.size());
@@ -685,9 +697,11 @@ static void plan_dense(Planner& P, int nid, bool composite) {
       EpiParams e = epi;
       if (bias_eid >= 0) e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
       if (sum_eid >= 0) e.sum = c.ptr(sum_eid, kLogical);
+      c.tc_mark();
       if (launch_gemm_tc(c.ptr(x_eid, kLogical), c.ptr(w_eid, kLogical), c.ptr(y_eid, kLogical), 1, (int)M, N, K, 0, xd, wd,
                          e, c.s) != 0)
         fail("tcgen05 GEMM launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+      c.tc_mark();
     });
   } else {
     if (!ci.float_mode && ci.has_const_bias) epi.bias = (const int32_t*)P.dev_upload(ci.bias_host.data(), ci.bias_host.size() * 4);
@@ -730,8 +744,10 @@ static void plan_batch_matmul(Planner& P, int nid) {
   snprintf(desc, sizeof(desc), "qnn.batch_matmul -> %s B=%d M=%d N=%d K=%d", use_tc ? "tcgen05 i8 GEMM" : "CUDA-core GEMM", B, M, N, K);
   P.add_step(desc, [=](RunCtx& c) {
     if (use_tc) {
+      c.tc_mark();
       if (launch_gemm_tc(c.ptr(x_eid, kLogical), c.ptr(w_eid, kLogical), c.ptr(y_eid, kLogical), B, M, N, K, wb, xd, wd, epi, c.s) != 0)
         fail("tcgen05 GEMM launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+      c.tc_mark();
     } else {
       launch_gemm_simt(c.ptr(x_eid, kLogical), c.ptr(w_eid, kLogical), c.ptr(y_eid, kLogical), B, M, N, K, wb, xd, wd, zpx, zpw, epi, c.s);
     }
@@ -1122,6 +1138,7 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
   c.s = s;
   c.ws = get_workspace(rt, s);
   c.in_ptr.resize(n_in);
+  c.ws->tc_used = 0;
   const long long before = g_launches;
   // inputs: device tensors are used in place, host tensors are staged (H2D on the caller's stream)
   for (int i = 0; i < n_in; ++i) {
@@ -1402,6 +1419,8 @@ int tkb_set_option(tkb_handle h, const char* key, const char* value) {
       build_plan(h);
     }
     h->conv_impl = v;
+  } else if (k == "time_tc") {
+    h->time_tc = v == "1";
   } else {
     fail("unknown option %s", key);
   }
@@ -1416,18 +1435,33 @@ int tkb_work(tkb_handle h, int64_t* macs, int64_t* hbm_bytes) {
   return 0;
 }
 
-int tkb_trace_enable(tkb_handle h, int mode) {
-  TKB_TRY
-  if (mode < 0 || mode > 2) fail("trace mode must be 0, 1 or 2");
-  h->trace_mode = mode;
-  TKB_CATCH
-}
-
 static Workspace* last_ws(tkb_handle h) {
   std::lock_guard<std::mutex> lk(h->ws_mu);
   auto it = h->ws.find(h->last_stream);
   if (it == h->ws.end()) fail("no run has been executed yet");
   return it->second.get();
+}
+
+int tkb_tc_time(tkb_handle h, double* ms, int* launches) {
+  TKB_TRY
+  Workspace* ws = last_ws(h);
+  double total = 0;
+  for (size_t i = 0; i + 1 < ws->tc_used; i += 2) {
+    CUDA_OK(cudaEventSynchronize(ws->tc_events[i + 1]));
+    float t = 0;
+    CUDA_OK(cudaEventElapsedTime(&t, ws->tc_events[i], ws->tc_events[i + 1]));
+    total += t;
+  }
+  *ms = total;
+  *launches = (int)(ws->tc_used / 2);
+  TKB_CATCH
+}
+
+int tkb_trace_enable(tkb_handle h, int mode) {
+  TKB_TRY
+  if (mode < 0 || mode > 2) fail("trace mode must be 0, 1 or 2");
+  h->trace_mode = mode;
+  TKB_CATCH
 }
 
 int tkb_trace_sync(tkb_handle h) {

@@ -75,6 +75,7 @@ def load_library():
     L.tkb_launch_count.restype = ctypes.c_int64
     L.tkb_launch_count.argtypes = [H]
     L.tkb_work.argtypes = [H, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)]
+    L.tkb_tc_time.argtypes = [H, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)]
     L.tkb_trace_enable.argtypes = [H, ctypes.c_int]
     L.tkb_trace_sync.argtypes = [H]
     L.tkb_trace_save.argtypes = [H, ctypes.c_char_p]
@@ -227,6 +228,12 @@ class TachikomaJSONRuntime:
         self._lib.tkb_work(self._h, ctypes.byref(macs), ctypes.byref(hbm))
         return macs.value, hbm.value
 
+    def tc_time(self):
+        """(milliseconds, launches) of the tcgen05 GEMM kernels in the last run (needs option time_tc=1)."""
+        ms, n = ctypes.c_double(), ctypes.c_int()
+        _check(self._lib.tkb_tc_time(self._h, ctypes.byref(ms), ctypes.byref(n)))
+        return ms.value, n.value
+
     # -- trace -------------------------------------------------------------------------------------------
     def trace_enable(self, mode):
         _check(self._lib.tkb_trace_enable(self._h, int(mode)))
@@ -274,7 +281,7 @@ def create_executor(func, params=None, mode="int", conv_impl="auto"):
     shapes = {p.name: p.shape for p in part.params}
 
     def run(**inputs):
-        ins = [np.ascontiguousarray(np.asarray(inputs[n]).astype(dtypes[n]).reshape(shapes[n])) for n in names]
+        ins = [np.asarray(np.asarray(inputs[n]).astype(dtypes[n]).reshape(shapes[n]), order="C") for n in names]
         out = np.empty(out_shape, dtype=out_dtype)
         mod.run(*ins, out)
         return out

@@ -21,7 +21,7 @@ def run_gpu(func, inputs, mode="int", conv_impl="auto", trace=False):
     mod.init(consts)
     if trace:
         mod.trace_enable(2)
-    ins = [np.ascontiguousarray(np.asarray(inputs[p.name]).astype(p.dtype).reshape(p.shape)) for p in part.params]
+    ins = [np.asarray(np.asarray(inputs[p.name]).astype(p.dtype).reshape(p.shape), order="C") for p in part.params]
     out = np.empty(part.body.shape, dtype=part.body.dtype)
     mod.run(*ins, out)
     return out, mod, (js, consts, ins)

@@ -1,0 +1,278 @@
+#!/usr/bin/env python
+"""bench.py -- traced int8 inferences/s of the tachikoma QNN hot path on B200 (BASELINE.json metric).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU algorithm (oracle port)
+
+Workload (N=1): BASELINE.json configs[2], int8 ResNet-18 224x224, integer-only, batch 64 per GPU, full
+per-op trace, synthetic uint8 images and random-init quantized weights (tachikoma_b200/models.py).
+A "step" is one batch of 64 images through partition -> JSON runtime -> kernels.  N>1: one process per
+GPU (torchrun), the batch shards by rank (weak scaling, no data-path collective); torch.distributed is
+used only for the barrier and the max-over-ranks of the device time.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "traced int8 inferences/sec"
+UNIT = "inferences/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--model", default="resnet18")
+    ap.add_argument("--batch", type=int, default=64, help="images per GPU per step")
+    ap.add_argument("--conv-impl", default="tc")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def build_model(name, batch):
+    from tachikoma_b200 import models, tachikoma as T
+    func = models.MODELS[name](batch=batch)
+    part = T.partition_for_tachikoma(func)
+    symbol, graph_json, const_names, consts = T.serialize(part)
+    return part, symbol, graph_json, const_names, consts
+
+
+def cpu_oracle_rate(name, sample, repeats=1):
+    """images/s of the oracle (CPU port of the reference algorithm) on `sample` images, all host threads."""
+    from oracle import interp
+    from tachikoma_b200 import models
+    part, symbol, graph_json, const_names, consts = build_model(name, sample)
+    x = models.synthetic_input(name, sample)
+    interp.run_json(graph_json, consts, [x[:sample]])  # warm-up (library load, page faults)
+    t0 = time.perf_counter()
+    for _ in range(repeats):
+        interp.run_json(graph_json, consts, [x], want_trace=True)
+    return sample * repeats / (time.perf_counter() - t0)
+
+
+def run_reference(args, rank):
+    """Reference arm: the reference's own CPU implementation is not buildable here (no LLVM/oneDNN), so this
+    times the oracle port of its algorithm on the host cores; rank 0 only."""
+    if rank != 0:
+        return
+    from oracle import interp
+    from tachikoma_b200 import models
+    cores = os.cpu_count()
+    t0 = time.perf_counter()
+    probe = cpu_oracle_rate(args.model, 1)
+    # bounded sample per step so that (steps + warmup) * sample images finish within ~2 minutes
+    sample = int(max(1, min(args.batch, 120.0 * probe / max(1, args.steps + args.warmup))))
+    part, symbol, graph_json, const_names, consts = build_model(args.model, sample)
+    x = models.synthetic_input(args.model, sample)
+    for _ in range(args.warmup):
+        interp.run_json(graph_json, consts, [x], want_trace=True)
+    t1 = time.perf_counter()
+    for _ in range(args.steps):
+        interp.run_json(graph_json, consts, [x], want_trace=True)
+    dt = time.perf_counter() - t1
+    value = sample * args.steps / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8*s8->s32", "data": "synthetic",
+        "config": {"workload": f"int8 {args.model} 224x224 integer-only, full per-op trace, CPU oracle port of the "
+                               f"reference lowering, {sample} images per step (bounded sample of batch {args.batch})"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{sample} images/step x {args.steps} steps, OpenMP on {cores} threads"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": time.perf_counter() - t0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from tachikoma_b200 import models, runtime as RT
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    part, symbol, graph_json, const_names, consts = build_model(args.model, args.batch)
+    mod = RT.TachikomaJSONRuntime(symbol, graph_json, const_names)
+    mod.set_option("conv_impl", args.conv_impl)
+    mod.init(consts)
+    macs, hbm_bytes = mod.work()
+    x_np = models.synthetic_input(args.model, args.batch, seed=1 + rank)
+    x_host = torch.from_numpy(x_np).pin_memory()
+    x_dev = x_host.cuda()
+    out_shape = tuple(part.body.shape)
+    out_dev = torch.empty(out_shape, dtype=torch.uint8, device="cuda")
+    out_host = torch.empty(out_shape, dtype=torch.uint8).pin_memory()
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def timed(n_warm, n_steps, fn):
+        for _ in range(n_warm):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = mod.launch_count()
+        e0.record()
+        for _ in range(n_steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, mod.launch_count() - l0
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+
+    # (i) compute only: device-resident input, no trace
+    mod.trace_enable(0)
+    ms_compute, _ = timed(args.warmup, args.steps, lambda: mod.run(x_dev, out_dev, stream=stream))
+    # (ii) headline `value`: device-resident input, every operator's tensors captured on the device
+    mod.trace_enable(1)
+    ms_value, launches = timed(args.warmup, args.steps, lambda: mod.run(x_dev, out_dev, stream=stream))
+    # (iii) e2e through the C ABI with HOST buffers: H2D of the batch, trace streamed to pinned host, D2H of the logits
+    mod.trace_enable(2)
+
+    def e2e_step():
+        mod.run(x_host, out_host, stream=stream)
+        mod.trace_sync()
+
+    ms_e2e, _ = timed(args.warmup, args.steps, e2e_step)
+    trace_bytes = mod.trace_bytes()
+    clocks = sampler.stop() if rank == 0 else None
+
+    # roofline of the dominant kernel (tcgen05 int8 GEMM): CUDA events around every launch, same stream
+    mod.trace_enable(0)
+    mod.set_option("time_tc", "1")
+    tc_ms, tc_n = 0.0, 0
+    for _ in range(max(3, args.steps // 4)):
+        mod.run(x_dev, out_dev, stream=stream)
+        torch.cuda.synchronize()
+        a, b = mod.tc_time()
+        tc_ms += a
+        tc_n += b
+    mod.set_option("time_tc", "0")
+    runs = max(3, args.steps // 4)
+    peak_tops = RT.probe_int8_peak(4000)
+    achieved_tops = 2.0 * macs * runs / (tc_ms * 1e-3) / 1e12 if tc_ms > 0 else 0.0
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    total_images = args.batch * world
+    value = total_images * args.steps / (ms_value * 1e-3)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_value / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8*s8->s32", "data": "synthetic",
+        "config": {
+            "workload": f"int8 {args.model} 224x224 integer-only, batch {args.batch} per GPU, full per-op trace "
+                        "(BASELINE.json configs[2])",
+            "value_mode": "inputs resident in HBM, per-op trace captured on the device",
+            "compute_only": total_images * args.steps / (ms_compute * 1e-3),
+            "trace_to_host_e2e": total_images * args.steps / (ms_e2e * 1e-3),
+            "trace_bytes_per_step": trace_bytes,
+            "l2": "no explicit flush: each step streams its whole activation arena (> 126 MB L2) through HBM",
+            "conv_impl": args.conv_impl, "int8_macs_per_step": macs,
+        },
+        "e2e": {"value": total_images * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": int(x_np.nbytes), "d2h_bytes_per_step": int(trace_bytes + np.prod(out_shape))},
+        "gpu_launches": int(launches),
+        "roofline": {
+            "bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05.mma kind::i8)", "achieved": achieved_tops,
+            "peak": peak_tops, "unit": "TFLOP/s", "frac": achieved_tops / peak_tops if peak_tops else None, "traffic": None,
+            "note": "int8 ops (2*MAC) counted as FLOPs; peak = this run's tcgen05 kind::i8 issue-rate probe "
+                    "(MEASURED_PEAKS.json has no int8 entry; 2x its bf16 burst = %.0f)" % (2 * peaks.get("bf16_tflops", 0)),
+            "avg_launch_us": 1e3 * tc_ms / tc_n if tc_n else None, "launches_per_step": tc_n // runs if runs else None,
+        },
+        "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count()
+        sample = 8
+        rate = cpu_oracle_rate(args.model, sample)
+        line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"{sample} images of the same workload, oracle (C + OpenMP) with trace"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

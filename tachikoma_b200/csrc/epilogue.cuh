@@ -209,4 +209,42 @@ __device__ __forceinline__ int32_t epilogue_one(int32_t acc, int n, long long id
   return cast_trunc(y, e.out_dtype);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Fast fixed-point epilogue (tensor-core kernels).  Exactly the same integers as epilogue_one for the
+// default configuration (UPWARD rounding, int64 compute, multiplier <= 1 i.e. no left shift), with all
+// per-channel work folded on the host into one 64-bit multiply-add and two shifts per element:
+//
+//   reference:  t = acc + bias - zp_in  (int32 ring)       v = int64(t) * M + 2^(T-1)
+//               y = int32(v >> T) + zp_out                   y = clamp(y, qmin, qmax); y = clip(y, lo, hi)
+//   here:       t = acc + b2[c]                              v = int64(t) * M[c] + C[c],  C = 2^(T-1) + (zp_out << T)
+//               y = int32(v >> T[c])  (funnel shift s1 = min(T,32), then arithmetic shift s2 = max(T-32,0))
+//               y = clamp(y, max(qmin,lo), min(qmax,hi))
+//
+// floor((v + r)/2^T) + z == floor((v + r + z*2^T)/2^T), and |t*M| < 2^62, so the fold is exact; the
+// host only enables this path when every channel satisfies the preconditions (runtime.cu fast_epi()).
+// The residual qnn.add is folded the same way: each side is one multiply-add and a shift with
+// per-tensor constants (its operands are 8-bit, so nothing can overflow).
+struct FastSide {        // q' = int32((int64(q << ls) * M + C) >> T)
+  int32_t M, ls, s1, s2;
+  long long C;
+};
+struct FastEpi {
+  int enabled;
+  const int4* tabA;      // [N] {b2, M, C_lo, C_hi}
+  const int2* tabS;      // [N] {s1, s2}
+  int32_t lo, hi;        // merged clamp of the requantize out_dtype and the relay clip
+  int has_sum, sum_unsigned;
+  FastSide lhs, rhs;     // qnn.add sides; lhs.C also carries "- zp_out" of the add
+  int32_t sum_lo, sum_hi;
+};
+
+__device__ __forceinline__ int32_t fast_shift(long long v, int32_t s1, int32_t s2) {
+  int32_t d;
+  asm("shf.r.clamp.b32 %0, %1, %2, %3;" : "=r"(d) : "r"((uint32_t)v), "r"((uint32_t)((unsigned long long)v >> 32)), "r"(s1));
+  return d >> s2;
+}
+__device__ __forceinline__ int32_t fast_side(int32_t q, const FastSide& f) {
+  return fast_shift((long long)(q << f.ls) * f.M + f.C, f.s1, f.s2);
+}
+
 }  // namespace tkb

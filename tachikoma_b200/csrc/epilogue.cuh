@@ -211,40 +211,31 @@ __device__ __forceinline__ int32_t epilogue_one(int32_t acc, int n, long long id
 
 // ------------------------------------------------------------------------------------------------
 // Fast fixed-point epilogue (tensor-core kernels).  Exactly the same integers as epilogue_one for the
-// default configuration (UPWARD rounding, int64 compute, multiplier <= 1 i.e. no left shift), with all
-// per-channel work folded on the host into one 64-bit multiply-add and two shifts per element:
+// default configuration (UPWARD rounding, int64 compute, requantize multiplier < 0.5 so that the total
+// right shift T = 31 - exponent is >= 32), with all per-channel work folded on the host into ONE 64-bit
+// multiply-add and one 32-bit shift per element:
 //
 //   reference:  t = acc + bias - zp_in  (int32 ring)       v = int64(t) * M + 2^(T-1)
 //               y = int32(v >> T) + zp_out                   y = clamp(y, qmin, qmax); y = clip(y, lo, hi)
-//   here:       t = acc + b2[c]                              v = int64(t) * M[c] + C[c],  C = 2^(T-1) + (zp_out << T)
-//               y = int32(v >> T[c])  (funnel shift s1 = min(T,32), then arithmetic shift s2 = max(T-32,0))
-//               y = clamp(y, max(qmin,lo), min(qmax,hi))
+//   here:       v = int64(acc) * M[c] + C[c],   C = (bias - zp_in) * M + 2^(T-1) + (zp_out << T)
+//               y = hi32(v) >> (T[c] - 32);     y = clamp(y, max(qmin,lo), min(qmax,hi))
 //
-// floor((v + r)/2^T) + z == floor((v + r + z*2^T)/2^T), and |t*M| < 2^62, so the fold is exact; the
-// host only enables this path when every channel satisfies the preconditions (runtime.cu fast_epi()).
-// The residual qnn.add is folded the same way: each side is one multiply-add and a shift with
-// per-tensor constants (its operands are 8-bit, so nothing can overflow).
-struct FastSide {        // q' = int32((int64(q << ls) * M + C) >> T)
-  int32_t M, ls, s1, s2;
+// floor((v + r)/2^T) + z == floor((v + r + z*2^T)/2^T); the host (runtime.cu build_fast_epi) proves from
+// sum_k |w[c][k]| that neither the reference's int32 ring nor the 64-bit fold can overflow for any input,
+// and only then enables this path -- otherwise the kernel runs epilogue_one.  The residual qnn.add is
+// folded the same way: each side is one multiply-add and a 64-bit shift with per-tensor constants (its
+// operands are 8-bit, so nothing can overflow); an identity side is M = 1, T = 0.
+struct FastSide {        // q' = int32((int64(q << ls) * M + C) >> s1)
+  int32_t M, ls, s1, pad;
   long long C;
 };
 struct FastEpi {
   int enabled;
-  const int4* tabA;      // [N] {b2, M, C_lo, C_hi}
-  const int2* tabS;      // [N] {s1, s2}
+  const int4* tabA;      // [N] {M, T - 32, C_lo, C_hi}
   int32_t lo, hi;        // merged clamp of the requantize out_dtype and the relay clip
   int has_sum, sum_unsigned;
   FastSide lhs, rhs;     // qnn.add sides; lhs.C also carries "- zp_out" of the add
   int32_t sum_lo, sum_hi;
 };
-
-__device__ __forceinline__ int32_t fast_shift(long long v, int32_t s1, int32_t s2) {
-  int32_t d;
-  asm("shf.r.clamp.b32 %0, %1, %2, %3;" : "=r"(d) : "r"((uint32_t)v), "r"((uint32_t)((unsigned long long)v >> 32)), "r"(s1));
-  return d >> s2;
-}
-__device__ __forceinline__ int32_t fast_side(int32_t q, const FastSide& f) {
-  return fast_shift((long long)(q << f.ls) * f.M + f.C, f.s1, f.s2);
-}
 
 }  // namespace tkb

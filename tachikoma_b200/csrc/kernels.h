@@ -52,11 +52,30 @@ void launch_pad4(const void* x, void* y, int elem, const long long* in_shape, co
 void launch_im2col(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream_t s);
 
 // ---- tcgen05 kernels ---------------------------------------------------------------------------
-// GEMM on the 5th-gen tensor cores: Y[M,N] = epilogue(X[M,K] . W[N,K]^T), X/W int8 or uint8, K-major.
-// Requirements (checked by tc_gemm_supported): K % 16 == 0, pointers 16B aligned, zp_w == 0.
+// Persistent GEMM / implicit-GEMM convolution on the 5th-gen tensor cores:
+//   Y[b][M][N] = epilogue(A[b][M][K] . W[b?][N][K]^T), A/W int8 or uint8, K-major, zp_w == 0.
+// implicit != 0: `a` is the NHWC activation tensor of geometry `g` and the A operand is gathered by an
+// im2col-mode TMA tensor map (K = KH*KW*C ordered tap-major, i.e. OHWI weights); taps in the padding read
+// 0, so the caller supplies the per-border-class zero-point correction `delta` (see runtime.cu).
+struct TcArgs {
+  const void* a;
+  const void* w;
+  void* y;
+  int B, M, N, K, w_batched, a_dtype, w_dtype;
+  int implicit;
+  ConvGeom g;
+  const int32_t* delta;   // [n_classes][N] int32, class 0 = interior (all zeros, never read); or nullptr
+  const uint8_t* cls_h;   // [OH] class of each output row
+  const uint8_t* cls_w;   // [OW] class of each output column
+  int ncls_w;
+  EpiParams e;
+  FastEpi f;
+};
+// Requirements of the plain-GEMM form: K % 16 == 0, pointers 16B aligned.
 bool tc_gemm_supported(int M, int N, int K);
-int launch_gemm_tc(const void* x, const void* w, void* y, int B, int M, int N, int K, int w_batched, int x_dtype,
-                   int w_dtype, const EpiParams& e, cudaStream_t s);
+// Requirements of the implicit form: groups == 1, C % 32 == 0, TMA corner / offset ranges.
+bool tc_implicit_conv_supported(const ConvGeom& g);
+int launch_tc(const TcArgs& a, cudaStream_t s);
 int probe_int8_peak(int iters, double* tops, cudaStream_t s);
 
 extern thread_local long long g_launches;  // kernels launched by this thread (summed per handle)

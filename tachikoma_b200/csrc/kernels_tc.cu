@@ -1,214 +1,173 @@
-// tcgen05 (5th-gen tensor core) kernels for sm_100a: int8 GEMM with the fused QNN epilogue and the
-// dense-int8 peak probe.  Warp-specialised: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA
-// issuer (one elected thread issues tcgen05.mma kind::i8), warps 2..5 = epilogue (tcgen05.ld from
-// TMEM -> requantize -> global).  Operands are staged by TMA into 128-byte-swizzled K-major tiles;
-// accumulators (int32) live in TMEM.
-#include <cstdio>
+// tcgen05 (5th-gen tensor core) kernels for sm_100a: persistent int8 GEMM / implicit-GEMM convolution
+// with the fused QNN epilogue, and the dense-int8 peak probe.
+//
+// One CTA per SM, looping over 128 x BN output tiles (static round-robin schedule).  Warp roles:
+//   warp 0      TMA producer.  A tile: activations, either a plain K-major matrix (tiled tensor map) or
+//               the NHWC activation tensor read through an IM2COL-mode tensor map (implicit GEMM: one
+//               filter tap x one channel chunk per pipeline stage; out-of-image taps are zero-filled by
+//               the TMA unit and corrected for the input zero point in the epilogue).  B tile: weights
+//               [N][K] K-major.  Both land in swizzled shared memory (swizzle span = bytes of K per stage).
+//   warp 1      TMEM allocator + MMA issuer: one thread issues tcgen05.mma.kind::i8 (u8/s8 x u8/s8 ->
+//               s32) into one of two TMEM accumulator stages, tcgen05.commit frees the smem slot.
+//   warps 2..5  epilogue: tcgen05.ld (TMEM -> registers, software-pipelined 32 columns at a time) ->
+//               requantize / clip / residual qnn.add -> 16-byte global stores.  While they drain one
+//               accumulator stage the MMA warp already fills the other.
+// The arithmetic contract of the epilogue is in epilogue.cuh (reference: requantize.cc:195-273,
+// intrin_rule.cc:165-250, add.cc:40-93).
 #include <mutex>
 
-#include "kernels.h"
-#include "tc_ptx.cuh"
+#include "tc_kernel.cuh"
 
 namespace tkb {
-
-using namespace ptx;
-
-static constexpr int BM = 128;       // UMMA M (rows = TMEM lanes)
-static constexpr int BK = 128;       // bytes of K per stage = one 128B swizzle row
-static constexpr int UMMA_K = 32;    // int8 elements per tcgen05.mma
-
-template <int BN, int STAGES>
-struct GemmSmem {
-  static constexpr int A_BYTES = BM * BK;
-  static constexpr int B_BYTES = BN * BK;
-  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
-  static constexpr int TOTAL = BAR_OFF + (2 * STAGES + 1) * 8 + 16 + 1024 /* alignment slack */;
-};
-
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(192) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                      const __grid_constant__ CUtensorMap tmB, void* __restrict__ y,
-                                                      int M, int N, int K, int w_batched, uint32_t idesc,
-                                                      EpiParams e) {
-  using L = GemmSmem<BN, STAGES>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* full = (uint64_t*)(smem + L::BAR_OFF);
-  uint64_t* empty = full + STAGES;
-  uint64_t* tmem_full = empty + STAGES;
-  uint32_t* tmem_ptr = (uint32_t*)(tmem_full + 1);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM, b = blockIdx.z;
-  const int num_kb = (K + BK - 1) / BK;
-
-  if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tmA);
-    prefetch_tmap(&tmB);
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    mbar_init(tmem_full, 1);
-    fence_barrier_init();
-  }
-  if (warp == 1) tmem_alloc<BN>(tmem_ptr);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr;
-
-  if (warp == 0) {
-    if (lane == 0) {
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int st = kb % STAGES;
-        mbar_wait(&empty[st], ((kb / STAGES) & 1) ^ 1);
-        mbar_expect_tx(&full[st], L::STAGE_BYTES);
-        tma_load_3d(smem + st * L::STAGE_BYTES, &tmA, &full[st], kb * BK, m0, b);
-        tma_load_3d(smem + st * L::STAGE_BYTES + L::A_BYTES, &tmB, &full[st], kb * BK, n0, w_batched ? b : 0);
-      }
-    }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int st = kb % STAGES;
-        mbar_wait(&full[st], (kb / STAGES) & 1);
-        tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + st * L::STAGE_BYTES);
-        const uint32_t b_addr = a_addr + L::A_BYTES;
-#pragma unroll
-        for (int k = 0; k < BK / UMMA_K; ++k) {
-          // K-major, 128B swizzle: 8-row groups are 1024 B apart (SBO); advancing K inside the
-          // swizzle row is a plain start-address offset.
-          const uint64_t da = smem_desc(a_addr + k * UMMA_K, 16, 1024, 2);
-          const uint64_t db = smem_desc(b_addr + k * UMMA_K, 16, 1024, 2);
-          mma_i8(tmem_base, da, db, idesc, (kb | k) != 0);
-        }
-        tc_commit(&empty[st]);  // frees the smem slot once the MMAs above have read it
-      }
-      tc_commit(tmem_full);
-    }
-  } else {
-    // epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31
-    const int q = warp & 3;
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
-    const int row = m0 + q * 32 + lane;
-    const long long row_off = ((long long)b * M + row) * N;
-    const bool vec8 = (e.out_dtype == kU8 || e.out_dtype == kI8) && (N & 15) == 0 && (((uintptr_t)y) & 15) == 0;
-    const bool vec32 = e.out_dtype == kI32 && (N & 3) == 0 && (((uintptr_t)y) & 15) == 0;
-#pragma unroll 1
-    for (int c = 0; c < BN; c += 16) {
-      if (n0 + c >= N) break;  // warp-uniform
-      uint32_t r[16];
-      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + c, r);
-      tmem_ld_wait();
-      if (row < M) {
-        int32_t v[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int col = n0 + c + j;
-          v[j] = col < N ? epilogue_one((int32_t)r[j], col, row_off + col, e) : 0;
-        }
-        if (vec8 && n0 + c + 16 <= N) {
-          uint4 o;
-          uint32_t* po = (uint32_t*)&o;
-#pragma unroll
-          for (int w = 0; w < 4; ++w)
-            po[w] = (v[4 * w] & 0xFF) | ((v[4 * w + 1] & 0xFF) << 8) | ((v[4 * w + 2] & 0xFF) << 16) |
-                    ((uint32_t)(v[4 * w + 3] & 0xFF) << 24);
-          *(uint4*)((uint8_t*)y + row_off + n0 + c) = o;
-        } else if (vec32 && n0 + c + 16 <= N) {
-          int32_t* yp = (int32_t*)y + row_off + n0 + c;
-#pragma unroll
-          for (int w = 0; w < 4; ++w) *(int4*)(yp + 4 * w) = make_int4(v[4 * w], v[4 * w + 1], v[4 * w + 2], v[4 * w + 3]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (n0 + c + j < N) store_from_i32(y, e.out_dtype, row_off + n0 + c + j, v[j]);
-        }
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc<BN>(tmem_base);
-}
 
 // ---- host side -----------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*,
+                                   CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                   CUtensorMapFloatOOBfill);
 
+static void* driver_entry(const char* name) {
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult qr;
+  if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess)
+    return p;
+  return nullptr;
+}
 static EncodeTiledFn encode_tiled() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qr;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess &&
-        qr == cudaDriverEntryPointSuccess)
-      fn = (EncodeTiledFn)p;
-  });
+  static EncodeTiledFn fn = (EncodeTiledFn)driver_entry("cuTensorMapEncodeTiled");
+  return fn;
+}
+static EncodeIm2colFn encode_im2col() {
+  static EncodeIm2colFn fn = (EncodeIm2colFn)driver_entry("cuTensorMapEncodeIm2col");
   return fn;
 }
 
-// 3-D uint8 tensor map [batch][rows][k] (k innermost), box = {128 bytes of k, box_rows, 1}, 128B swizzle
-static bool make_tmap_3d(CUtensorMap* tm, const void* base, long long k, long long rows, long long batch, int box_rows) {
+static CUtensorMapSwizzle swizzle_for(int bk) {
+  return bk == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : bk == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+}
+
+// 3-D uint8 tensor map [batch][rows][k] (k innermost), box = {bk bytes of k, box_rows, 1}, swizzle span = bk
+static bool make_tmap_3d(CUtensorMap* tm, const void* base, long long k, long long rows, long long batch, int box_rows,
+                         int bk) {
   EncodeTiledFn fn = encode_tiled();
   if (!fn) return false;
   cuuint64_t dims[3] = {(cuuint64_t)k, (cuuint64_t)rows, (cuuint64_t)batch};
   cuuint64_t strides[2] = {(cuuint64_t)k, (cuuint64_t)(k * rows)};
-  cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)box_rows, 1};
+  cuuint32_t box[3] = {(cuuint32_t)bk, (cuuint32_t)box_rows, 1};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(bk), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;
 }
 
-bool tc_gemm_supported(int M, int N, int K) { return M > 0 && N > 0 && K > 0 && (K % 16) == 0; }
-
-template <int BN, int STAGES>
-static int launch_gemm_tc_t(const CUtensorMap& ta, const CUtensorMap& tb, void* y, int B, int M, int N, int K,
-                            int w_batched, uint32_t idesc, const EpiParams& e, cudaStream_t s) {
-  using L = GemmSmem<BN, STAGES>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL) !=
-        cudaSuccess)
-      return -1;
-    attr_set = true;
-  }
-  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, B);
-  gemm_tc_kernel<BN, STAGES><<<grid, 192, L::TOTAL, s>>>(ta, tb, y, M, N, K, w_batched, idesc, e);
-  ++g_launches;
-  return cudaGetLastError() == cudaSuccess ? 0 : -1;
+// IM2COL-mode map over the NHWC activation tensor {C, W, H, N}: the TMA unit walks 128 consecutive output
+// pixels (q fastest, then p, then n) starting at the base pixel given to the instruction, stepping by the
+// convolution stride inside the bounding box [lower corner, dim + upper corner); the filter tap is an
+// instruction-time offset.  Elements outside the tensor are zero-filled.
+static bool make_tmap_im2col(CUtensorMap* tm, const void* base, const ConvGeom& g, int bk) {
+  EncodeIm2colFn fn = encode_im2col();
+  if (!fn) return false;
+  cuuint64_t dims[4] = {(cuuint64_t)g.C, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
+  cuuint64_t strides[3] = {(cuuint64_t)g.C, (cuuint64_t)g.C * g.W, (cuuint64_t)g.C * g.W * g.H};
+  int lower[2] = {-g.pl, -g.pt};
+  int upper[2] = {g.pr - (g.KW - 1) * g.dw, g.pb - (g.KH - 1) * g.dh};
+  cuuint32_t estr[4] = {1, (cuuint32_t)g.sw, (cuuint32_t)g.sh, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void*>(base), dims, strides, lower, upper,
+                  (cuuint32_t)bk, (cuuint32_t)BM, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(bk),
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return false;
+  // Drivers up to 13.1 mis-encode im2col maps of tensors smaller than 128 KiB (same work-around as
+  // cute/atom/copy_traits_sm90_im2col.hpp make_im2col_tma_copy_desc).
+  int drv = 0;
+  cudaDriverGetVersion(&drv);
+  if (drv <= 13010 && (long long)g.C * g.W * g.H * g.N < 131072) reinterpret_cast<uint64_t*>(tm)[1] &= ~(1ull << 21);
+  return true;
 }
 
-int launch_gemm_tc(const void* x, const void* w, void* y, int B, int M, int N, int K, int w_batched, int x_dtype,
-                   int w_dtype, const EpiParams& e, cudaStream_t s) {
-  if (!tc_gemm_supported(M, N, K)) return -1;
-  if ((((uintptr_t)x) | ((uintptr_t)w)) & 15) return -1;
-  const int bn = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+bool tc_gemm_supported(int M, int N, int K) { return M > 0 && N > 0 && K > 0 && (K % 16) == 0; }
+
+bool tc_implicit_conv_supported(const ConvGeom& g) {
+  if (g.groups != 1 || (g.C % 32) != 0) return false;
+  const int lo_w = -g.pl, lo_h = -g.pt, up_w = g.pr - (g.KW - 1) * g.dw, up_h = g.pb - (g.KH - 1) * g.dh;
+  for (int v : {lo_w, lo_h, up_w, up_h})
+    if (v < -128 || v > 127) return false;
+  if ((g.KW - 1) * g.dw > 255 || (g.KH - 1) * g.dh > 255) return false;
+  if (g.sw < 1 || g.sw > 8 || g.sh < 1 || g.sh > 8) return false;
+  return true;
+}
+
+static int pick_bn(long long mtiles, int N) {
+  const int cand[3] = {256, 128, 64};
+  int best = 64;
+  long long best_cost = -1;
+  const int sms = num_sms();
+  for (int bn : cand) {
+    if (bn > 64 && bn >= 2 * ((N + 63) / 64 * 64)) continue;  // mostly padding
+    const long long tiles = mtiles * ((N + bn - 1) / bn);
+    const long long cost = ((tiles + sms - 1) / sms) * (bn + 32);
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bn; }
+  }
+  return best;
+}
+
+int launch_tc(const TcArgs& a, cudaStream_t s) {
+  if ((((uintptr_t)a.a) | ((uintptr_t)a.w)) & 15) return -1;
+  TcKernelParams p;
+  memset(&p, 0, sizeof(p));
+  p.y = a.y;
+  p.sum = a.e.sum;
+  p.M = a.M; p.N = a.N; p.K = a.K;
+  p.batches = a.B; p.w_batched = a.w_batched;
+  p.e = a.e;
+  p.f = a.f;
+  p.delta = a.delta; p.cls_h = a.cls_h; p.cls_w = a.cls_w; p.ncls_w = a.ncls_w;
+  int bk;
+  if (a.implicit) {
+    const ConvGeom& g = a.g;
+    if (!tc_implicit_conv_supported(g)) return -1;
+    bk = g.C % 128 == 0 ? 128 : (g.C % 64 == 0 ? 64 : 32);
+    p.implicit = 1;
+    p.C = g.C; p.KH = g.KH; p.KW = g.KW; p.OH = g.OH; p.OW = g.OW;
+    p.sh = g.sh; p.sw = g.sw; p.dh = g.dh; p.dw = g.dw; p.pt = g.pt; p.pl = g.pl;
+  } else {
+    if (!tc_gemm_supported(a.M, a.N, a.K)) return -1;
+    bk = a.K >= 128 ? 128 : (a.K > 32 ? 64 : 32);
+  }
+  p.bk = bk;
+  const uint32_t layout = bk == 128 ? 2u : (bk == 64 ? 4u : 6u);
+  p.desc_hi = (uint32_t)(smem_desc(0, 16, 8 * bk, layout) >> 32);
+  p.idesc = ((a.a_dtype == kI8 ? 1u : 0u) << 7) | ((a.w_dtype == kI8 ? 1u : 0u) << 10);
+  const long long mtiles = (a.M + BM - 1) / BM;
+  const int bn = pick_bn(mtiles * a.B, a.N);
   CUtensorMap ta, tb;
-  if (!make_tmap_3d(&ta, x, K, M, B, BM)) return -1;
-  if (!make_tmap_3d(&tb, w, K, N, w_batched ? B : 1, bn)) return -1;
-  const uint32_t idesc = idesc_i8(BM, bn, x_dtype == kI8, w_dtype == kI8);
-  if (bn == 64) return launch_gemm_tc_t<64, 4>(ta, tb, y, B, M, N, K, w_batched, idesc, e, s);
-  if (bn == 128) return launch_gemm_tc_t<128, 3>(ta, tb, y, B, M, N, K, w_batched, idesc, e, s);
-  return launch_gemm_tc_t<256, 4>(ta, tb, y, B, M, N, K, w_batched, idesc, e, s);
+  if (a.implicit) {
+    if (!make_tmap_im2col(&ta, a.a, a.g, bk)) return -1;
+  } else {
+    if (!make_tmap_3d(&ta, a.a, a.K, a.M, a.B, BM, bk)) return -1;
+  }
+  if (!make_tmap_3d(&tb, a.w, a.K, a.N, a.w_batched ? a.B : 1, bn, bk)) return -1;
+  const bool fast = a.f.enabled != 0;
+  if (!fast) return launch_tc_generic(bn, ta, tb, p, s);
+  if (bn == 64) return launch_t<64, true>(ta, tb, p, s);
+  if (bn == 128) return launch_t<128, true>(ta, tb, p, s);
+  return launch_t<256, true>(ta, tb, p, s);
 }
 
 // ---- dense int8 peak probe -------------------------------------------------------------------------
-// One CTA per SM issues `iters` x 4 tcgen05.mma (128 x 256 x 32, int8) from resident (uninitialised)
-// smem tiles into two TMEM accumulators; nothing is loaded or stored, so the time is the tensor
-// pipe's issue floor.  This is the measured denominator for the conv/dense roofline.
+// One CTA per SM issues `iters` x 4 tcgen05.mma (128 x 256 x 32, int8) from resident smem tiles into two
+// TMEM accumulators; nothing is loaded or stored, so the time is the tensor pipe's issue floor.  This is
+// the measured denominator for the conv/dense roofline.
 __global__ void __launch_bounds__(128) probe_i8_kernel(int iters, uint32_t idesc) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   __shared__ uint64_t done;
   __shared__ uint32_t tmem_ptr;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int i = threadIdx.x; i < (BM * BK + 256 * BK) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0x01010101u;
+  for (int i = threadIdx.x; i < (BM * 128 + 256 * 128) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0x01010101u;
   if (threadIdx.x == 0) { mbar_init(&done, 1); fence_barrier_init(); }
   if (warp == 0) tmem_alloc<512>(&tmem_ptr);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -217,7 +176,7 @@ __global__ void __launch_bounds__(128) probe_i8_kernel(int iters, uint32_t idesc
   tc_fence_after();
   const uint32_t tmem_base = tmem_ptr;
   if (warp == 0 && lane == 0) {
-    const uint32_t a_addr = smem_u32(smem), b_addr = a_addr + BM * BK;
+    const uint32_t a_addr = smem_u32(smem), b_addr = a_addr + BM * 128;
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
@@ -235,11 +194,9 @@ __global__ void __launch_bounds__(128) probe_i8_kernel(int iters, uint32_t idesc
 }
 
 int probe_int8_peak(int iters, double* tops, cudaStream_t s) {
-  const int smem = BM * BK + 256 * BK + 1024;
+  const int smem = BM * 128 + 256 * 128 + 1024;
   if (cudaFuncSetAttribute(probe_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int sms = num_sms();
   const uint32_t idesc = idesc_i8(128, 256, true, true);
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0);

@@ -310,8 +310,13 @@ static int parse_compute(const std::string& s) {
 }
 
 // Build a RqParams (RequantizeLower, requantize.cc:195-273).  C = channel count on the quantization axis.
+struct RqHost {  // host copy of the fixed-point constants of one requantize (for build_fast_epi)
+  std::vector<int32_t> M, S, zp_in;
+};
+
 static RqParams make_rq(Planner& P, const std::vector<float>& in_scale, const std::vector<int32_t>& in_zp,
-                        float out_scale, int32_t out_zp, int rounding, int compute, int out_dtype, int C) {
+                        float out_scale, int32_t out_zp, int rounding, int compute, int out_dtype, int C,
+                        RqHost* host = nullptr) {
   RqParams p;
   memset(&p, 0, sizeof(p));
   if (in_scale.size() != 1 && (int)in_scale.size() != C) fail("requantize: %d scales for %d channels", (int)in_scale.size(), C);
@@ -339,6 +344,7 @@ static RqParams make_rq(Planner& P, const std::vector<float>& in_scale, const st
   }
   if (in_zp.size() == 1) p.zp_in0 = in_zp[0];
   else p.zp_in = (const int32_t*)P.dev_upload(in_zp.data(), in_zp.size() * 4);
+  if (host) { host->M = M; host->S = S; host->zp_in = in_zp; }
   return p;
 }
 
@@ -350,11 +356,11 @@ static void init_epi(EpiParams& e) {
 
 // qnn.add parameters (add.cc:40-93, op_common.h:196-210) into e.lhs / e.rhs / sum_*
 static void make_qadd(Planner& P, EpiParams& e, float sa, int32_t zpa, float sb, int32_t zpb, float so, int32_t zpo,
-                      int dtype) {
+                      int dtype, RqHost* lhs_host = nullptr, RqHost* rhs_host = nullptr) {
   e.lhs_identity = sa == so && zpa == zpo;
   e.rhs_identity = sb == so && zpb == zpo;
-  e.lhs = make_rq(P, {sa}, {zpa}, so, zpo, kUpward, kInt64, kI32, 1);
-  e.rhs = make_rq(P, {sb}, {zpb}, so, zpo, kUpward, kInt64, kI32, 1);
+  e.lhs = make_rq(P, {sa}, {zpa}, so, zpo, kUpward, kInt64, kI32, 1, lhs_host);
+  e.rhs = make_rq(P, {sb}, {zpb}, so, zpo, kUpward, kInt64, kI32, 1, rhs_host);
   e.sum_zp_out = zpo;
   dtype_range(dtype, &e.sum_qmin, &e.sum_qmax);
   e.sum_clip_lo = e.sum_qmin;
@@ -382,6 +388,7 @@ struct CompositeInfo {
   int32_t zp_a = 0;
   std::vector<int32_t> zp_w;
   bool float_mode = false;
+  RqHost rq_host, lhs_host, rhs_host;
 };
 
 static int input_by_name(const Graph& g, const GNode& n, const char* key) {
@@ -424,7 +431,7 @@ static CompositeInfo build_composite(Planner& P, const GNode& n, int nid, int ch
       fail("Unsupported op: %s with per-channel requantize on axis %d (channel axis is %d)", n.name.c_str(), axis, channel_axis);
     const int rq_dtype = dtype_from_string(n.str("rq_out_dtype", "int32"));
     e.rq = make_rq(P, in_scl, in_zp, out_scl, out_zp, parse_rounding(n.str("rounding", "None")),
-                   parse_compute(n.str("compute_dtype", "None")), rq_dtype, channels);
+                   parse_compute(n.str("compute_dtype", "None")), rq_dtype, channels, &ci.rq_host);
     clip_bounds(n.f64("clip_a_min", -2147483648.0), n.f64("clip_a_max", 2147483647.0), rq_dtype, &e.clip_lo, &e.clip_hi);
     const int cast_dtype = dtype_from_string(n.str("cast_dtype", n.str("rq_out_dtype", "int32")));
     if (ci.sum_eid >= 0) {
@@ -435,7 +442,7 @@ static CompositeInfo build_composite(Planner& P, const GNode& n, int nid, int ch
       const float so = P.cfloats(input_by_name(g, n, "sum_out_scl_idx"), "sum_out_scl")[0];
       const int32_t zo = P.cints(input_by_name(g, n, "sum_out_zp_idx"), "sum_out_zp")[0];
       if (P.ent[ci.sum_eid].dtype != cast_dtype) fail("qnn.add operands must share a dtype");
-      make_qadd(P, e, sa, za, sb, zb, so, zo, cast_dtype);
+      make_qadd(P, e, sa, za, sb, zb, so, zo, cast_dtype, &ci.lhs_host, &ci.rhs_host);
       clip_bounds(n.f64("sum_clip_a_min", -2147483648.0), n.f64("sum_clip_a_max", 2147483647.0), cast_dtype,
                   &e.sum_clip_lo, &e.sum_clip_hi);
       e.sum = (const void*)1;  // patched with the real pointer at run time
@@ -490,6 +497,171 @@ static std::vector<int32_t> add_vec(const std::vector<int32_t>& bias, const std:
 
 static bool all_zero(const std::vector<int32_t>& v) {
   for (auto x : v) if (x != 0) return false;
+  return true;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host-side folding for the tensor-core kernels
+// ------------------------------------------------------------------------------------------------
+static bool fits_i63(__int128 v) { return v < ((__int128)1 << 62) && v > -((__int128)1 << 62); }
+
+// One side of the residual qnn.add (RequantizeOrUpcast, op_common.h:196-210) as q' = ((q << ls) * M + C) >> T.
+// `p`/`h`: the requantize of this side towards the add's output qparams.  Returns false when the side
+// cannot be expressed (absurd scale ratios); the caller then keeps the generic epilogue.
+static bool fold_side(const RqParams& p, const RqHost& h, bool identity, FastSide* f) {
+  memset(f, 0, sizeof(*f));
+  const long long zin = h.zp_in[0], zo = p.zp_out;
+  if (identity) { f->M = 1; return true; }
+  if (p.skip_mul) { f->M = 1; f->C = zo - zin; return true; }
+  const int32_t M = h.M[0], S = h.S[0];
+  if (M <= 0) return false;
+  if (M == (1 << 30)) {  // power-of-two shortcut of the per-tensor UPWARD path, intrin_rule.cc:221-239
+    const int e = S - 1;
+    if (e > 16 || e < -30) return false;
+    f->M = 1;
+    if (e > 0) { f->ls = e; f->C = -zin * (1ll << e) + zo; }
+    else if (e == 0) { f->C = zo - zin; }
+    else { f->s1 = -e; f->C = -zin + (1ll << (-e - 1)) + zo * (1ll << -e); }
+    return true;
+  }
+  const int ls = S > 0 ? S : 0, rs = S > 0 ? 0 : -S, T = rs + 31;
+  if (ls > 8 || T > 62) return false;
+  const __int128 C = -(__int128)zin * ((__int128)M << ls) + ((__int128)1 << (T - 1)) + (__int128)zo * ((__int128)1 << T);
+  if (!fits_i63(C)) return false;
+  f->M = M; f->ls = ls; f->s1 = T; f->C = (long long)C;
+  return true;
+}
+
+// Fold bias, zero points, rounding constant and the two clamps of the int-mode composite into FastEpi
+// (see epilogue.cuh).  bias2[c]: constant int32 bias plus the uniform zero-point correction; wabs[c]:
+// sum_k |w[c][k]| (bounds every accumulator the kernel or the reference can form for channel c).
+static bool build_fast_epi(Planner& P, const CompositeInfo& ci, const std::vector<int32_t>& bias2,
+                           const std::vector<long long>& wabs, int channels, int out_dtype, FastEpi* out) {
+  memset(out, 0, sizeof(*out));
+  const EpiParams& e = ci.epi;
+  if (e.mode != kEpiInt || ci.bias_eid >= 0) return false;
+  const RqParams& rq = e.rq;
+  if (rq.compute != kInt64 || rq.rounding != kUpward || rq.skip_mul) return false;
+  const RqHost& h = ci.rq_host;
+  if (h.M.empty()) return false;
+  const bool has_sum = ci.sum_eid >= 0;
+  const int mid_dtype = has_sum ? e.sum_dtype : out_dtype;  // dtype of the cast that follows the clip
+  int32_t dlo, dhi;
+  dtype_range(mid_dtype, &dlo, &dhi);
+  const int32_t lo = std::max(rq.no_clamp ? INT32_MIN : rq.qmin, e.clip_lo);
+  const int32_t hi = std::min(rq.no_clamp ? INT32_MAX : rq.qmax, e.clip_hi);
+  if (lo > hi || lo < dlo || hi > dhi) return false;  // the cast must be the identity on [lo, hi]
+  std::vector<int32_t> tab((size_t)channels * 4);
+  for (int c = 0; c < channels; ++c) {
+    const int32_t M = h.M[h.M.size() == 1 ? 0 : c], S = h.S[h.S.size() == 1 ? 0 : c];
+    const long long zin = h.zp_in[h.zp_in.size() == 1 ? 0 : c];
+    if (M <= 0 || S > -1) return false;  // T = 31 - S must be >= 32 (multiplier < 0.5)
+    const int T = 31 - S;
+    if (T > 62) return false;
+    const long long b = bias2.empty() ? 0 : bias2[c];
+    // every |acc|, |acc + delta|, |acc + bias|, |acc + bias - zp_in| stays below 2^31: the reference's int32
+    // ring arithmetic equals plain integer arithmetic
+    const __int128 amax = (__int128)2 * 255 * wabs[c] + (b < 0 ? -b : b) + (zin < 0 ? -zin : zin) + 1;
+    if (amax >= ((__int128)1 << 31)) return false;
+    if (h.M.size() == 1 && M == (1 << 30) && (-S > 29 || amax >= ((__int128)1 << 30))) return false;  // shortcut branch
+    const __int128 C = (__int128)(b - zin) * M + ((__int128)1 << (T - 1)) + (__int128)rq.zp_out * ((__int128)1 << T);
+    if (!fits_i63(C) || !fits_i63(amax * M + (C < 0 ? -C : C))) return false;
+    const long long C64 = (long long)C;
+    tab[4 * c + 0] = M;
+    tab[4 * c + 1] = T - 32;
+    tab[4 * c + 2] = (int32_t)(uint32_t)(C64 & 0xFFFFFFFFll);
+    tab[4 * c + 3] = (int32_t)(C64 >> 32);
+  }
+  out->lo = lo;
+  out->hi = hi;
+  if (has_sum) {
+    if (e.sum_dtype != kU8 && e.sum_dtype != kI8) return false;
+    if (!fold_side(e.lhs, ci.lhs_host, e.lhs_identity != 0, &out->lhs)) return false;
+    if (!fold_side(e.rhs, ci.rhs_host, e.rhs_identity != 0, &out->rhs)) return false;
+    const __int128 Cl = (__int128)out->lhs.C - (__int128)e.sum_zp_out * ((__int128)1 << out->lhs.s1);
+    if (!fits_i63(Cl)) return false;
+    out->lhs.C = (long long)Cl;
+    out->has_sum = 1;
+    out->sum_unsigned = e.sum_dtype == kU8;
+    out->sum_lo = std::max(e.sum_qmin, e.sum_clip_lo);
+    out->sum_hi = std::min(e.sum_qmax, e.sum_clip_hi);
+    int32_t olo, ohi;
+    dtype_range(out_dtype, &olo, &ohi);
+    if (out->sum_lo > out->sum_hi || out->sum_lo < olo || out->sum_hi > ohi) return false;
+  }
+  out->tabA = (const int4*)P.dev_upload(tab.data(), tab.size() * 4);
+  out->enabled = 1;
+  return true;
+}
+
+// sum_k |w[o][k]| of an [O][K] int8/uint8 matrix
+static std::vector<long long> abs_row_sums(const uint8_t* w, int O, int K, int w_dtype) {
+  std::vector<long long> out(O, 0);
+  for (int o = 0; o < O; ++o) {
+    long long s = 0;
+    for (int k = 0; k < K; ++k) {
+      const int v = w_dtype == kU8 ? (int)w[(size_t)o * K + k] : (int)(int8_t)w[(size_t)o * K + k];
+      s += v < 0 ? -v : v;
+    }
+    out[o] = s;
+  }
+  return out;
+}
+
+// Implicit-GEMM convolution reads 0 (TMA out-of-bounds fill) where the reference pads with the input zero
+// point (convolution.cc:227-253), so  acc_ref = raw - zp_a * sum_{valid taps} W.  The uniform part
+// (-zp_a * sum_{all taps} W) goes into the bias; an output pixel whose window overlaps the padding gets
+// +zp_a * sum_{taps in the padding} W back.  Pixels are classified per axis by their set of valid taps;
+// class 0 is "all taps valid".  Returns false if the geometry has too many classes for uint8 tables.
+struct BorderPlan {
+  std::vector<uint8_t> cls_h, cls_w;
+  std::vector<int32_t> delta;  // [nh*nw][O]
+  int nh = 1, nw = 1;
+};
+static bool axis_classes(int in, int out, int k, int stride, int dil, int pad, std::vector<uint8_t>* cls,
+                         std::vector<uint64_t>* masks) {
+  if (k > 63) return false;
+  masks->assign(1, (1ull << k) - 1);
+  cls->resize(out);
+  for (int p = 0; p < out; ++p) {
+    uint64_t m = 0;
+    for (int r = 0; r < k; ++r) {
+      const int i = p * stride + r * dil - pad;
+      if (i >= 0 && i < in) m |= 1ull << r;
+    }
+    size_t id = 0;
+    for (; id < masks->size(); ++id) if ((*masks)[id] == m) break;
+    if (id == masks->size()) masks->push_back(m);
+    if (id > 255) return false;
+    (*cls)[p] = (uint8_t)id;
+  }
+  return true;
+}
+static bool border_plan(const ConvGeom& g, const std::vector<uint8_t>& w_ohwi, int Cg, BorderPlan* bp) {
+  std::vector<uint64_t> mh, mw;
+  if (!axis_classes(g.H, g.OH, g.KH, g.sh, g.dh, g.pt, &bp->cls_h, &mh)) return false;
+  if (!axis_classes(g.W, g.OW, g.KW, g.sw, g.dw, g.pl, &bp->cls_w, &mw)) return false;
+  bp->nh = (int)mh.size();
+  bp->nw = (int)mw.size();
+  if (bp->nh * bp->nw == 1 || g.zp_a == 0) { bp->delta.clear(); return true; }
+  std::vector<long long> tap((size_t)g.O * g.KH * g.KW, 0);  // sum over channels of each tap
+  for (int o = 0; o < g.O; ++o)
+    for (int t = 0; t < g.KH * g.KW; ++t) {
+      long long s = 0;
+      const uint8_t* src = &w_ohwi[((size_t)o * g.KH * g.KW + t) * Cg];
+      for (int c = 0; c < Cg; ++c) s += g.w_dtype == kU8 ? (int)src[c] : (int)(int8_t)src[c];
+      tap[(size_t)o * g.KH * g.KW + t] = s;
+    }
+  bp->delta.assign((size_t)bp->nh * bp->nw * g.O, 0);
+  for (int ch = 0; ch < bp->nh; ++ch)
+    for (int cw = 0; cw < bp->nw; ++cw)
+      for (int o = 0; o < g.O; ++o) {
+        long long s = 0;
+        for (int r = 0; r < g.KH; ++r)
+          for (int x = 0; x < g.KW; ++x)
+            if (!((mh[ch] >> r) & 1) || !((mw[cw] >> x) & 1)) s += tap[((size_t)o * g.KH + r) * g.KW + x];
+        bp->delta[((size_t)ch * bp->nw + cw) * g.O + o] = (int32_t)((uint32_t)g.zp_a * (uint32_t)(int32_t)s);
+      }
   return true;
 }
 
@@ -583,7 +755,8 @@ static void plan_conv(Planner& P, int nid, bool composite) {
   const bool direct = g.KH == 1 && g.KW == 1 && g.sh == 1 && g.sw == 1 && !(g.pt | g.pl | g.pb | g.pr) && (g.C % 16) == 0;
   const bool tc_ok = P.rt->conv_impl != "simt" && g.groups == 1 && all_zero(ci.zp_w) &&
                      (g.zp_a == 0 || ci.bias_eid < 0) && M >= 1;
-  const bool use_tc = tc_ok && (P.rt->conv_impl == "tc" || M * g.O >= 4096);
+  const bool force_tc = P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit";
+  const bool use_tc = tc_ok && (force_tc || M * g.O >= 4096);
   P.rt->macs += M * g.O * K;
   P.rt->hbm_bytes += X.bytes() + Y.bytes() + (long long)w_ohwi.size() + (ci.sum_eid >= 0 ? Y.bytes() : 0);
 
@@ -591,7 +764,13 @@ static void plan_conv(Planner& P, int nid, bool composite) {
   const int bias_eid = ci.bias_eid, sum_eid = ci.sum_eid;
   char desc[256];
   if (use_tc) {
-    const int Kp = direct ? K : (K + 15) / 16 * 16;
+    // A-operand source: (1) the activation tensor itself for 1x1/stride-1/unpadded convolutions, (2) the
+    // activation tensor through an im2col-mode TMA map (implicit GEMM), (3) an explicit im2col matrix for
+    // channel counts TMA cannot address (C % 32 != 0, e.g. the 3-channel stem).
+    BorderPlan bp;
+    const bool implicit = !direct && P.rt->conv_impl != "tc_explicit" && tc_implicit_conv_supported(g) &&
+                          border_plan(g, w_ohwi, Cg, &bp);
+    const int Kp = (direct || implicit) ? K : (K + 15) / 16 * 16;
     std::vector<uint8_t> wp((size_t)g.O * Kp, 0);
     std::vector<int32_t> corr(g.O, 0);
     for (int o = 0; o < g.O; ++o) {
@@ -601,29 +780,47 @@ static void plan_conv(Planner& P, int nid, bool composite) {
       corr[o] = (int32_t)(0u - (uint32_t)g.zp_a * (uint32_t)(int32_t)sum);  // -zp_a * sum_k W[o,k]  (int32 ring)
     }
     void* wdev = P.dev_upload(wp.data(), wp.size());
+    std::vector<int32_t> bias2;
     if (!ci.float_mode) {
       if (ci.has_const_bias || g.zp_a != 0) {
-        auto b = add_vec(ci.bias_host, corr, g.O);
-        epi.bias = (const int32_t*)P.dev_upload(b.data(), b.size() * 4);
+        bias2 = add_vec(ci.bias_host, corr, g.O);
+        epi.bias = (const int32_t*)P.dev_upload(bias2.data(), bias2.size() * 4);
       }
     }
+    TcArgs ta;
+    memset(&ta, 0, sizeof(ta));
+    ta.w = wdev;
+    ta.B = 1; ta.M = (int)M; ta.N = g.O; ta.K = Kp;
+    ta.a_dtype = g.a_dtype; ta.w_dtype = g.w_dtype;
+    ta.implicit = implicit ? 1 : 0;
+    ta.g = g;
+    if (implicit && !bp.delta.empty()) {
+      ta.delta = (const int32_t*)P.dev_upload(bp.delta.data(), bp.delta.size() * 4);
+      ta.cls_h = (const uint8_t*)P.dev_upload(bp.cls_h.data(), bp.cls_h.size());
+      ta.cls_w = (const uint8_t*)P.dev_upload(bp.cls_w.data(), bp.cls_w.size());
+      ta.ncls_w = bp.nw;
+    }
+    if (composite && !ci.float_mode)
+      build_fast_epi(P, ci, bias2, abs_row_sums(w_ohwi.data(), g.O, K, g.w_dtype), g.O, Y.dtype, &ta.f);
     long long scratch_off = -1;
-    if (!direct) scratch_off = P.arena_alloc(M * Kp);
-    snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 GEMM%s M=%lld N=%d K=%d (%dx%d s%d p%d) epi=%d", n.name.c_str(),
-             direct ? "" : " + im2col", M, g.O, Kp, g.KH, g.KW, g.sh, g.pt, epi.mode);
+    if (!direct && !implicit) scratch_off = P.arena_alloc(M * Kp);
+    snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 %s M=%lld N=%d K=%d (%dx%d s%d p%d) epi=%s", n.name.c_str(),
+             direct ? "GEMM" : (implicit ? "implicit-GEMM conv (TMA im2col)" : "GEMM + explicit im2col"), M, g.O, Kp, g.KH,
+             g.KW, g.sh, g.pt, ta.f.enabled ? "fast" : (epi.mode == kEpiInt ? "int" : (epi.mode == kEpiFloat ? "float" : "raw")));
     P.add_step(desc, [=](RunCtx& c) {
-      EpiParams e = epi;
-      if (bias_eid >= 0) e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
-      if (sum_eid >= 0) e.sum = c.ptr(sum_eid, phys);
-      const void* a = c.ptr(x_eid, phys);
-      if (!direct) {
+      TcArgs t = ta;
+      t.e = epi;
+      if (bias_eid >= 0) t.e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
+      if (sum_eid >= 0) t.e.sum = c.ptr(sum_eid, phys);
+      t.a = c.ptr(x_eid, phys);
+      if (!direct && !implicit) {
         void* col = c.ws->arena + scratch_off;
-        launch_im2col(a, col, g, Kp, c.s);
-        a = col;
+        launch_im2col(t.a, col, g, Kp, c.s);
+        t.a = col;
       }
+      t.y = c.ptr(y_eid, phys);
       c.tc_mark();
-      if (launch_gemm_tc(a, wdev, c.ptr(y_eid, phys), 1, (int)M, g.O, Kp, 0, g.a_dtype, g.w_dtype, e, c.s) != 0)
-        fail("tcgen05 GEMM launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+      if (launch_tc(t, c.s) != 0) fail("tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
       c.tc_mark();
     });
   } else {
@@ -678,9 +875,10 @@ static void plan_dense(Planner& P, int nid, bool composite) {
   const int bias_eid = ci.bias_eid, sum_eid = ci.sum_eid, xd = X.dtype, wd = Wt.dtype;
   const bool foldable = zpx == 0 || (Wt.is_const && bias_eid < 0);
   const bool use_tc = P.rt->conv_impl != "simt" && tc_gemm_supported((int)M, N, K) && zpw == 0 && foldable &&
-                      (P.rt->conv_impl == "tc" || M * N >= 4096);
+                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || M * N >= 4096);
   char desc[256];
   if (use_tc) {
+    std::vector<int32_t> bias2;
     if (!ci.float_mode && (ci.has_const_bias || zpx != 0)) {
       std::vector<int32_t> corr(N, 0);
       if (zpx != 0)
@@ -689,18 +887,27 @@ static void plan_dense(Planner& P, int nid, bool composite) {
           for (int k = 0; k < K; ++k) sum += wd == kU8 ? (int)Wt.host[(size_t)o * K + k] : (int)(int8_t)Wt.host[(size_t)o * K + k];
           corr[o] = (int32_t)(0u - (uint32_t)zpx * (uint32_t)(int32_t)sum);
         }
-      auto b = add_vec(ci.bias_host, corr, N);
-      epi.bias = (const int32_t*)P.dev_upload(b.data(), b.size() * 4);
+      bias2 = add_vec(ci.bias_host, corr, N);
+      epi.bias = (const int32_t*)P.dev_upload(bias2.data(), bias2.size() * 4);
     }
-    snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 GEMM M=%lld N=%d K=%d epi=%d", n.name.c_str(), M, N, K, epi.mode);
+    TcArgs ta;
+    memset(&ta, 0, sizeof(ta));
+    ta.B = 1; ta.M = (int)M; ta.N = N; ta.K = K;
+    ta.a_dtype = xd; ta.w_dtype = wd;
+    if (composite && !ci.float_mode && Wt.is_const)
+      build_fast_epi(P, ci, bias2, abs_row_sums(Wt.host.data(), N, K, wd), N, Y.dtype, &ta.f);
+    snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 GEMM M=%lld N=%d K=%d epi=%s", n.name.c_str(), M, N, K,
+             ta.f.enabled ? "fast" : (epi.mode == kEpiInt ? "int" : (epi.mode == kEpiFloat ? "float" : "raw")));
     P.add_step(desc, [=](RunCtx& c) {
-      EpiParams e = epi;
-      if (bias_eid >= 0) e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
-      if (sum_eid >= 0) e.sum = c.ptr(sum_eid, kLogical);
+      TcArgs t = ta;
+      t.e = epi;
+      if (bias_eid >= 0) t.e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
+      if (sum_eid >= 0) t.e.sum = c.ptr(sum_eid, kLogical);
+      t.a = c.ptr(x_eid, kLogical);
+      t.w = c.ptr(w_eid, kLogical);
+      t.y = c.ptr(y_eid, kLogical);
       c.tc_mark();
-      if (launch_gemm_tc(c.ptr(x_eid, kLogical), c.ptr(w_eid, kLogical), c.ptr(y_eid, kLogical), 1, (int)M, N, K, 0, xd, wd,
-                         e, c.s) != 0)
-        fail("tcgen05 GEMM launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+      if (launch_tc(t, c.s) != 0) fail("tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
       c.tc_mark();
     });
   } else {
@@ -739,14 +946,18 @@ static void plan_batch_matmul(Planner& P, int nid) {
   init_epi(epi);
   const int xd = X.dtype, wd = Wt.dtype;
   const bool use_tc = P.rt->conv_impl != "simt" && tc_gemm_supported(M, N, K) && zpx == 0 && zpw == 0 &&
-                      (P.rt->conv_impl == "tc" || (long long)B * M * N >= 4096);
+                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || (long long)B * M * N >= 4096);
   char desc[256];
   snprintf(desc, sizeof(desc), "qnn.batch_matmul -> %s B=%d M=%d N=%d K=%d", use_tc ? "tcgen05 i8 GEMM" : "CUDA-core GEMM", B, M, N, K);
   P.add_step(desc, [=](RunCtx& c) {
     if (use_tc) {
+      TcArgs t;
+      memset(&t, 0, sizeof(t));
+      t.a = c.ptr(x_eid, kLogical); t.w = c.ptr(w_eid, kLogical); t.y = c.ptr(y_eid, kLogical);
+      t.B = B; t.M = M; t.N = N; t.K = K; t.w_batched = wb; t.a_dtype = xd; t.w_dtype = wd;
+      t.e = epi;
       c.tc_mark();
-      if (launch_gemm_tc(c.ptr(x_eid, kLogical), c.ptr(w_eid, kLogical), c.ptr(y_eid, kLogical), B, M, N, K, wb, xd, wd, epi, c.s) != 0)
-        fail("tcgen05 GEMM launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+      if (launch_tc(t, c.s) != 0) fail("tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
       c.tc_mark();
     } else {
       launch_gemm_simt(c.ptr(x_eid, kLogical), c.ptr(w_eid, kLogical), c.ptr(y_eid, kLogical), B, M, N, K, wb, xd, wd, zpx, zpw, epi, c.s);
@@ -1406,7 +1617,7 @@ int tkb_set_option(tkb_handle h, const char* key, const char* value) {
   TKB_TRY
   const std::string k = key, v = value;
   if (k == "conv_impl") {
-    if (v != "auto" && v != "simt" && v != "tc") fail("conv_impl must be auto|simt|tc");
+    if (v != "auto" && v != "simt" && v != "tc" && v != "tc_explicit") fail("conv_impl must be auto|simt|tc|tc_explicit");
     if (h->initialized && v != h->conv_impl) {
       h->conv_impl = v;
       std::lock_guard<std::mutex> guard(h->init_mu);

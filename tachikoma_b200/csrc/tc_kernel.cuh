@@ -1,0 +1,369 @@
+// Shared between kernels_tc.cu (folded "fast" epilogue instantiations, host-side tensor maps) and
+// kernels_tc_generic.cu (generic epilogue instantiations): the persistent tcgen05 GEMM / implicit-GEMM
+// convolution kernel.  See kernels_tc.cu for the design notes.
+#pragma once
+#include <cstdio>
+#include <cstring>
+
+#include "kernels.h"
+#include "tc_ptx.cuh"
+
+namespace tkb {
+
+using namespace ptx;
+
+static constexpr int BM = 128;       // UMMA M (rows = TMEM lanes)
+static constexpr int UMMA_K = 32;    // int8 elements per tcgen05.mma
+static constexpr int MAX_STAGES = 12;
+static constexpr int EPI_THREADS = 128;
+
+struct TcKernelParams {
+  void* y;
+  const void* sum;        // residual tensor (same shape as y) or nullptr
+  int M, N, K;            // GEMM view; implicit conv: K = KH*KW*C
+  int batches, w_batched; // batched GEMM (qnn.batch_matmul): tensor-map z coordinate
+  int bk;                 // bytes of K per pipeline stage: 128 / 64 / 32 (= swizzle span)
+  int stages;
+  uint32_t idesc;
+  uint32_t desc_hi;       // upper 32 bits of the UMMA smem descriptors (SBO, version, swizzle mode)
+  // implicit convolution
+  int implicit, C, KH, KW, OH, OW, sh, sw, dh, dw, pt, pl;
+  // zero-point correction of taps that fall into the padding (see runtime.cu border_classes())
+  const int32_t* delta;   // [n_classes][N] or nullptr
+  const uint8_t* cls_h;   // [OH]
+  const uint8_t* cls_w;   // [OW]
+  int ncls_w;
+  EpiParams e;            // generic epilogue (any rounding / compute dtype / float mode / raw int32)
+  FastEpi f;              // host-folded fixed-point epilogue (default QNN configuration)
+};
+
+__device__ __forceinline__ void tma_load_im2col_4d(void* dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h,
+                                                   int n, uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], "
+      "[%2], {%7, %8};" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+
+// 32 lanes x 32 columns of 32-bit: thread i of the warp gets lane (base_lane + i), columns c..c+31
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+// tcgen05.wait::ld with a register dependency on the loaded values, so that no consumer of r[] can be
+// scheduled above the wait.
+__device__ __forceinline__ void tmem_ld_wait32(uint32_t (&r)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                 "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                 "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
+                 "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+               :
+               : "memory");
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory"); }
+
+__device__ __forceinline__ uint4 ldg_nc_16(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
+// ---- epilogue of 32 accumulator columns of one output row ---------------------------------------
+// r: raw TMEM accumulators; row_valid: row < M; ncols: valid columns of this chunk (1..32);
+// col0: absolute first column; idx0: linear output index of (row, col0).
+template <bool FAST>
+__device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const TcKernelParams& p, const int4* tab_s,
+                                               int tab_off, bool row_valid, int ncols, int col0, long long idx0,
+                                               const int32_t* drow, bool vec_ok) {
+  if (!row_valid) return;
+  int32_t v[32];
+  const bool full = ncols == 32;
+  if constexpr (FAST) {
+    const FastEpi& f = p.f;
+    uint32_t sraw[8];
+    const bool vec_sum = f.has_sum && vec_ok && full;
+    if (vec_sum) {
+      const uint4 s0 = ldg_nc_16((const uint8_t*)p.sum + idx0), s1 = ldg_nc_16((const uint8_t*)p.sum + idx0 + 16);
+      sraw[0] = s0.x; sraw[1] = s0.y; sraw[2] = s0.z; sraw[3] = s0.w;
+      sraw[4] = s1.x; sraw[5] = s1.y; sraw[6] = s1.z; sraw[7] = s1.w;
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const int4 t = tab_s[tab_off + j];  // {M, s2, C_lo, C_hi}: same address for the whole warp (broadcast)
+      int32_t a = (int32_t)r[j];
+      if (drow) a += (j < ncols) ? __ldg(drow + col0 + j) : 0;
+      const long long c = ((long long)t.w << 32) | (unsigned long long)(uint32_t)t.z;
+      const long long acc = (long long)a * (long long)t.x + c;
+      int32_t y = (int32_t)(acc >> 32) >> t.y;
+      y = min(max(y, f.lo), f.hi);
+      if (f.has_sum) {
+        int32_t b;
+        if (vec_sum) {
+          const uint32_t w = sraw[j >> 2] >> (8 * (j & 3));
+          b = f.sum_unsigned ? (int32_t)(w & 0xFF) : (int32_t)(int8_t)(w & 0xFF);
+        } else {
+          b = (j < ncols) ? (f.sum_unsigned ? (int32_t)((const uint8_t*)p.sum)[idx0 + j]
+                                            : (int32_t)((const int8_t*)p.sum)[idx0 + j])
+                          : 0;
+        }
+        const int32_t qa = (int32_t)(((long long)(y << f.lhs.ls) * f.lhs.M + f.lhs.C) >> f.lhs.s1);
+        const int32_t qb = (int32_t)(((long long)(b << f.rhs.ls) * f.rhs.M + f.rhs.C) >> f.rhs.s1);
+        y = min(max(qa + qb, f.sum_lo), f.sum_hi);
+      }
+      v[j] = y;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      int32_t a = (int32_t)r[j];
+      if (j < ncols) {
+        if (drow) a = (int32_t)((uint32_t)a + (uint32_t)__ldg(drow + col0 + j));
+        v[j] = epilogue_one(a, col0 + j, idx0 + j, p.e);
+      } else {
+        v[j] = 0;
+      }
+    }
+  }
+  const int odt = p.e.out_dtype;
+  if (odt == kU8 || odt == kI8) {
+    if (vec_ok && full) {
+      uint32_t w[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        w[i] = (v[4 * i] & 0xFF) | ((v[4 * i + 1] & 0xFF) << 8) | ((v[4 * i + 2] & 0xFF) << 16) |
+               ((uint32_t)(v[4 * i + 3] & 0xFF) << 24);
+      uint4* dst = (uint4*)((uint8_t*)p.y + idx0);
+      dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+      dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < ncols) ((uint8_t*)p.y)[idx0 + j] = (uint8_t)v[j];
+    }
+  } else if (odt == kI32) {
+    int32_t* dst = (int32_t*)p.y + idx0;
+    if (vec_ok && full) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) ((int4*)dst)[i] = make_int4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < ncols) dst[j] = v[j];
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < ncols) store_from_i32(p.y, odt, idx0 + j, v[j]);
+  }
+}
+
+template <int BN, bool FAST>
+__global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                         const __grid_constant__ CUtensorMap tmB,
+                                                         const __grid_constant__ TcKernelParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int a_bytes = BM * p.bk, b_bytes = BN * p.bk, stage_bytes = a_bytes + b_bytes;
+  int4* tab_s = (int4*)(smem + p.stages * stage_bytes);
+  uint64_t* full = (uint64_t*)(tab_s + BN);
+  uint64_t* empty = full + MAX_STAGES;
+  uint64_t* tfull = empty + MAX_STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_ptr = (uint32_t*)(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int mtiles = (p.M + BM - 1) / BM, ntiles = (p.N + BN - 1) / BN;
+  const long long total_tiles = (long long)mtiles * ntiles * p.batches;
+  const int cchunks = p.implicit ? p.C / p.bk : 0;
+  const int num_kb = p.implicit ? p.KH * p.KW * cchunks : (p.K + p.bk - 1) / p.bk;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int i = 0; i < p.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<2 * BN>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int st = 0;
+      uint32_t ph = 0;
+      for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int nt = (int)(tile % ntiles);
+        const long long t2 = tile / ntiles;
+        const int mt = (int)(t2 % mtiles), b = (int)(t2 / mtiles);
+        const int n0 = nt * BN, m0 = mt * BM;
+        int cw = 0, chh = 0, cn = 0;
+        if (p.implicit) {
+          const int q0 = m0 % p.OW, t3 = m0 / p.OW;
+          cw = q0 * p.sw - p.pl;
+          chh = (t3 % p.OH) * p.sh - p.pt;
+          cn = t3 / p.OH;
+        }
+        int r = 0, s = 0, cc = 0;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty[st], ph ^ 1);
+          uint8_t* sa = smem + st * stage_bytes;
+          mbar_expect_tx(&full[st], (uint32_t)stage_bytes);
+          if (p.implicit) {
+            tma_load_im2col_4d(sa, &tmA, &full[st], cc * p.bk, cw, chh, cn, (uint16_t)(s * p.dw), (uint16_t)(r * p.dh));
+            if (++cc == cchunks) { cc = 0; if (++s == p.KW) { s = 0; ++r; } }
+          } else {
+            tma_load_3d(sa, &tmA, &full[st], kb * p.bk, m0, b);
+          }
+          tma_load_3d(sa + a_bytes, &tmB, &full[st], kb * p.bk, n0, p.w_batched ? b : 0);
+          if (++st == p.stages) { st = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      int st = 0;
+      uint32_t ph = 0, lt = 0;
+      const int kper = p.bk / UMMA_K;
+      for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+        const uint32_t as = lt & 1;
+        mbar_wait(&tempty[as], ((lt >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full[st], ph);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + st * stage_bytes);
+          const uint32_t b_addr = a_addr + a_bytes;
+          for (int k = 0; k < kper; ++k) {
+            // K-major swizzled tiles: 8-row groups are 8*bk bytes apart (SBO, in desc_hi); advancing K inside
+            // the swizzle row is a plain start-address offset.
+            const uint64_t da = ((uint64_t)p.desc_hi << 32) | (uint64_t)((((a_addr + k * UMMA_K) >> 4) & 0x3FFF) | (1u << 16));
+            const uint64_t db = ((uint64_t)p.desc_hi << 32) | (uint64_t)((((b_addr + k * UMMA_K) >> 4) & 0x3FFF) | (1u << 16));
+            mma_i8(d_tmem, da, db, p.idesc, (kb | k) != 0);
+          }
+          tc_commit(&empty[st]);  // frees the smem slot once the MMAs above have read it
+          if (++st == p.stages) { st = 0; ph ^= 1; }
+        }
+        tc_commit(&tfull[as]);
+      }
+    }
+  } else {
+    // ===== epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31 =====
+    const int q = warp & 3;
+    const int et = threadIdx.x - 64;  // 0..127
+    const int esz = dtype_size(p.e.out_dtype);
+    const bool vec_ok = ((long long)p.N * esz) % 16 == 0 && (((uintptr_t)p.y) & 15) == 0 &&
+                        (p.sum == nullptr || (((uintptr_t)p.sum) & 15) == 0);
+    uint32_t lt = 0;
+    int tab_n0 = -1;
+    for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int nt = (int)(tile % ntiles);
+      const long long t2 = tile / ntiles;
+      const int mt = (int)(t2 % mtiles), b = (int)(t2 / mtiles);
+      const int n0 = nt * BN, m0 = mt * BM;
+      if (FAST && n0 != tab_n0) {  // stage this n-tile's per-channel constants (uniform over the 4 warps)
+        epi_bar_sync();
+        for (int i = et; i < BN; i += EPI_THREADS) tab_s[i] = n0 + i < p.N ? p.f.tabA[n0 + i] : make_int4(0, 0, 0, 0);
+        epi_bar_sync();
+        tab_n0 = n0;
+      }
+      const int row = m0 + q * 32 + lane;
+      const bool row_valid = row < p.M;
+      const long long row_off = ((long long)b * p.M + row) * p.N;
+      const int32_t* drow = nullptr;
+      if (p.delta != nullptr && row_valid) {
+        const int qq = row % p.OW, pp = (row / p.OW) % p.OH;
+        const int cls = (int)p.cls_h[pp] * p.ncls_w + (int)p.cls_w[qq];
+        if (cls) drow = p.delta + (long long)cls * p.N;
+      }
+      const uint32_t as = lt & 1;
+      mbar_wait(&tfull[as], (lt >> 1) & 1);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
+      const int ncol_tile = min(BN, p.N - n0);
+      uint32_t ra[32], rb[32];
+      tmem_ld32(t_addr, ra);
+#pragma unroll 1
+      for (int c = 0; c < BN; c += 64) {
+        tmem_ld_wait32(ra);
+        const bool more_b = c + 32 < ncol_tile;
+        if (more_b) tmem_ld32(t_addr + c + 32, rb);
+        else {  // all TMEM reads of this tile are complete: hand the accumulator stage back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[as]);
+        }
+        epilogue_chunk<FAST>(ra, p, tab_s, c, row_valid, min(32, ncol_tile - c), n0 + c, row_off + n0 + c, drow, vec_ok);
+        if (!more_b) break;
+        tmem_ld_wait32(rb);
+        const bool more_a = c + 64 < ncol_tile;
+        if (more_a) tmem_ld32(t_addr + c + 64, ra);
+        else {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[as]);
+        }
+        epilogue_chunk<FAST>(rb, p, tab_s, c + 32, row_valid, min(32, ncol_tile - c - 32), n0 + c + 32,
+                             row_off + n0 + c + 32, drow, vec_ok);
+        if (!more_a) break;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
+}
+
+inline int num_sms() {
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+  }
+  return sms;
+}
+
+template <int BN, bool FAST>
+static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s) {
+  const int stage_bytes = (BM + BN) * p.bk;
+  const int fixed = BN * 16 + (2 * MAX_STAGES + 4) * 8 + 16 + 1024 /* alignment slack */;
+  int stages = (227 * 1024 - fixed) / stage_bytes;
+  stages = stages > MAX_STAGES ? MAX_STAGES : stages;
+  if (stages < 2) return -1;
+  p.stages = stages;
+  const int smem = stages * stage_bytes + fixed;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(tc_gemm_kernel<BN, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
+        cudaSuccess)
+      return -1;
+    attr_set = true;
+  }
+  const long long tiles = (long long)((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN) * p.batches;
+  const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
+  tc_gemm_kernel<BN, FAST><<<grid, 192, smem, s>>>(ta, tb, p);
+  ++g_launches;
+  return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+// generic-epilogue instantiations live in their own translation unit (compile time)
+int launch_tc_generic(int bn, const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s);
+
+}  // namespace tkb

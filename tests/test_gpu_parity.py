@@ -152,6 +152,122 @@ def test_tcgen05_batch_matmul_vs_oracle():
             np.testing.assert_equal(out, ref)
 
 
+# ---- implicit-GEMM convolution (TMA im2col mode) and the folded epilogue ----------------------------
+def _chain_conv(n, ic, h, w, oc, k, stride, pad, dil, zp_a, per_channel, relu, with_sum, seed, nhwc=False,
+                out_scale=None, raw=False, rounding="None", xdt="uint8", sum_scales=(0.3, 15, 0.2, 4)):
+    rng = np.random.default_rng(seed)
+    dl, kl = ("NHWC", "HWIO") if nhwc else ("NCHW", "OIHW")
+    d_shape = (n, h, w, ic) if nhwc else (n, ic, h, w)
+    w_shape = (k, k, ic, oc) if nhwc else (oc, ic, k, k)
+    lo, hi = (0, 256) if xdt == "uint8" else (-128, 128)
+    x = rng.integers(lo, hi, d_shape).astype(xdt)
+    wt = rng.integers(-127, 128, w_shape).astype("int8")
+    s_x = np.float32(0.02)
+    s_w = (rng.uniform(0.5, 1.5, oc) / (127.0 * np.sqrt(k * k * ic))).astype("float32") if per_channel \
+        else np.float32(1.0 / (127.0 * np.sqrt(k * k * ic)))
+    data = R.var("data", d_shape, xdt)
+    e = R.qnn_conv2d(data, R.const(wt), zp_a, 0, s_x, R.const(s_w) if per_channel else s_w, (k, k), oc,
+                     strides=(stride, stride), padding=(pad, pad), dilation=(dil, dil), data_layout=dl, kernel_layout=kl)
+    args = {"data": x}
+    params = [data]
+    if not raw:
+        b = rng.integers(-(1 << 12), 1 << 12, oc).astype("int32")
+        e = R.bias_add(e, R.const(b), axis=3 if nhwc else 1)
+        zp_out = 0 if relu else 128
+        so = np.float32(out_scale if out_scale is not None else 0.02 * 1.2)
+        e = R.qnn_requantize(e, R.const((s_x * s_w).astype("float32")) if per_channel else np.float32(s_x * s_w), 0, so,
+                             zp_out, axis=3 if nhwc else 1, out_dtype="int32", rounding=rounding)
+        e = R.cast(R.clip(e, float(zp_out if relu else 0), 255.0), "uint8")
+        if with_sum:
+            sv = R.var("res", e.shape, "uint8")
+            args["res"] = rng.integers(0, 256, e.shape).astype("uint8")
+            params.append(sv)
+            rs, rz, os_, oz = sum_scales
+            e = R.clip(R.qnn_add(e, sv, so, zp_out, rs, rz, os_, oz), 0.0, 255.0)
+    return R.Function(params, e), args
+
+
+IMPLICIT_CASES = {
+    # name: (n, ic, h, w, oc, k, stride, pad, dil, zp_a, per_channel, relu, with_sum)
+    "c64_3x3_p1": (2, 64, 12, 12, 64, 3, 1, 1, 1, 0, True, True, False),
+    "c64_3x3_p1_zp": (2, 64, 12, 12, 64, 3, 1, 1, 1, 128, True, True, False),
+    "c64_3x3_p1_zp_sum": (2, 64, 9, 11, 64, 3, 1, 1, 1, 7, True, False, True),
+    "c128_3x3_s2": (3, 128, 14, 14, 128, 3, 2, 1, 1, 5, True, True, False),
+    "c64_1x1_s2": (2, 64, 16, 16, 128, 1, 2, 0, 1, 9, True, False, False),
+    "c32_3x3_p1_pt": (1, 32, 7, 7, 48, 3, 1, 1, 1, 3, False, True, True),
+    "c96_3x3_dil2": (1, 96, 13, 13, 40, 3, 1, 2, 2, 11, True, True, False),
+    "c256_3x3_n512": (1, 256, 7, 7, 512, 3, 1, 1, 1, 0, True, True, True),
+    "c32_7x7_s2_p3": (2, 32, 30, 30, 64, 7, 2, 3, 1, 128, True, True, False),
+    "c64_5x5_p2_big": (4, 64, 31, 29, 72, 5, 1, 2, 1, 1, True, True, False),
+    "c512_1x1": (2, 512, 7, 7, 1000, 1, 1, 0, 1, 4, True, False, False),
+    "c64_3x3_p0_s8": (2, 64, 12, 12, 64, 3, 1, 0, 1, 128, True, True, False),
+}
+
+
+@pytest.mark.parametrize("nhwc", [False, True], ids=["nchw", "nhwc"])
+@pytest.mark.parametrize("name", list(IMPLICIT_CASES))
+def test_implicit_conv_vs_oracle(name, nhwc):
+    cfg = IMPLICIT_CASES[name]
+    func, args = _chain_conv(*cfg, seed=len(name) * 13 + cfg[1], nhwc=nhwc, xdt="int8" if name.endswith("s8") else "uint8")
+    ref, _ = interp.run_expr(func, args)
+    out, mod, _ = run_gpu(func, args, conv_impl="tc")
+    plan = mod.plan_summary()
+    assert "tcgen05" in plan and "epi=fast" in plan, plan
+    if cfg[5] > 1 or cfg[6] > 1:
+        assert "implicit-GEMM" in plan, plan
+    np.testing.assert_equal(out, ref)
+    # the explicit-im2col route and the CUDA-core route agree bit for bit
+    out2, _, _ = run_gpu(func, args, conv_impl="tc_explicit")
+    np.testing.assert_equal(out2, ref)
+
+
+def test_implicit_conv_raw_int32_and_generic_epilogue():
+    # plain qnn.conv2d (int32 accumulators out) through the implicit path with border correction
+    func, args = _chain_conv(2, 64, 10, 10, 64, 3, 1, 1, 1, 77, True, True, False, seed=3, raw=True)
+    ref, _ = interp.run_expr(func, args)
+    out, mod, _ = run_gpu(func, args, conv_impl="tc")
+    assert "implicit-GEMM" in mod.plan_summary() and "epi=raw" in mod.plan_summary()
+    np.testing.assert_equal(out, ref)
+    # TONEAREST rounding and multipliers >= 0.5 are outside the folded epilogue: generic path, same bits
+    for kw in (dict(rounding="TONEAREST"), dict(out_scale=0.02 / (127.0 * 24) * 1.1)):
+        func, args = _chain_conv(2, 64, 10, 10, 64, 3, 1, 1, 1, 77, True, True, True, seed=4, **kw)
+        ref, _ = interp.run_expr(func, args)
+        out, mod, _ = run_gpu(func, args, conv_impl="tc")
+        assert "epi=int" in mod.plan_summary(), mod.plan_summary()
+        np.testing.assert_equal(out, ref)
+
+
+@pytest.mark.parametrize("sum_scales", [(0.3, 15, 0.2, 4), (0.024, 0, 0.024, 0), (0.024, 3, 0.024, 9), (0.012, 0, 0.024, 0),
+                                        (0.05, 200, 0.0125, 30), (0.024, 0, 0.04, 0)])
+def test_fast_epilogue_residual_variants(sum_scales):
+    """qnn.add sides: generic multiplier, identity, equal scales with different zero points, power-of-two
+    ratios (the intrin_rule.cc:221-239 shortcut), ratios > 1 (left shift)."""
+    func, args = _chain_conv(2, 64, 8, 8, 64, 3, 1, 1, 1, 0, True, True, True, seed=11, sum_scales=sum_scales)
+    ref, _ = interp.run_expr(func, args)
+    out, mod, _ = run_gpu(func, args, conv_impl="tc")
+    assert "epi=fast" in mod.plan_summary(), mod.plan_summary()
+    np.testing.assert_equal(out, ref)
+    out2, _, _ = run_gpu(func, args, conv_impl="simt")
+    np.testing.assert_equal(out2, ref)
+
+
+def test_fast_epilogue_saturating_accumulators():
+    """All-255 activations x all-(+/-127) weights: the largest accumulators the shapes allow."""
+    for sign in (1, -1):
+        n, ic, h, w, oc, k = 1, 512, 6, 6, 64, 3
+        x = np.full((n, ic, h, w), 255, "uint8")
+        wt = np.full((oc, ic, k, k), 127 * sign, "int8")
+        data = R.var("data", x.shape, "uint8")
+        e = R.qnn_conv2d(data, R.const(wt), 0, 0, 0.02, 0.001, (k, k), oc, padding=(1, 1))
+        e = R.bias_add(e, R.const(np.full(oc, sign * (1 << 20), "int32")))
+        e = R.qnn_requantize(e, np.float32(2e-5), 0, np.float32(2.0), 128, axis=1, out_dtype="int32")
+        e = R.cast(R.clip(e, 0.0, 255.0), "uint8")
+        func = R.Function([data], e)
+        ref, _ = interp.run_expr(func, {"data": x})
+        out, mod, _ = run_gpu(func, {"data": x}, conv_impl="tc")
+        np.testing.assert_equal(out, ref)
+
+
 MODEL_CASES = [("mlp", dict(batch=64)), ("lenet5", dict(batch=8)), ("resnet18", dict(batch=2, image=64, num_classes=100)),
                ("mobilenetv2", dict(batch=2, image=64, num_classes=100))]
 

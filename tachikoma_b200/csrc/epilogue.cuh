@@ -225,7 +225,7 @@ __device__ __forceinline__ int32_t epilogue_one(int32_t acc, int n, long long id
 // and only then enables this path -- otherwise the kernel runs epilogue_one.  The residual qnn.add is
 // folded the same way: each side is one multiply-add and a 64-bit shift with per-tensor constants (its
 // operands are 8-bit, so nothing can overflow); an identity side is M = 1, T = 0.
-struct FastSide {        // q' = int32((int64(q << ls) * M + C) >> s1)
+struct FastSide {        // q' = hi32(int64(q << ls) * M + C) >> s1   (host-normalised so that the shift is >= 32)
   int32_t M, ls, s1, pad;
   long long C;
 };
@@ -233,7 +233,8 @@ struct FastEpi {
   int enabled;
   const int4* tabA;      // [N] {M, T - 32, C_lo, C_hi}
   int32_t lo, hi;        // merged clamp of the requantize out_dtype and the relay clip
-  int has_sum, sum_unsigned;
+  int has_sum;
+  uint32_t sum_xor;      // 0x80808080 for an int8 residual (b = (u ^ 0x80) - 128, the -128 is folded into rhs.C)
   FastSide lhs, rhs;     // qnn.add sides; lhs.C also carries "- zp_out" of the add
   int32_t sum_lo, sum_hi;
 };

@@ -150,11 +150,18 @@ int launch_tc(const TcArgs& a, cudaStream_t s) {
     if (!make_tmap_3d(&ta, a.a, a.K, a.M, a.B, BM, bk)) return -1;
   }
   if (!make_tmap_3d(&tb, a.w, a.K, a.N, a.w_batched ? a.B : 1, bn, bk)) return -1;
-  const bool fast = a.f.enabled != 0;
-  if (!fast) return launch_tc_generic(bn, ta, tb, p, s);
-  if (bn == 64) return launch_t<64, true>(ta, tb, p, s);
-  if (bn == 128) return launch_t<128, true>(ta, tb, p, s);
-  return launch_t<256, true>(ta, tb, p, s);
+  int mode = kModeGeneric;
+  if (a.f.enabled) mode = a.f.has_sum ? kModeFastSum : kModeFast;
+  else if (a.e.mode == kEpiRaw) mode = kModeRaw;
+  if (mode == kModeGeneric || mode == kModeRaw) return launch_tc_other(bn, mode, ta, tb, p, s);
+  if (mode == kModeFast) {
+    if (bn == 64) return launch_t<64, kModeFast>(ta, tb, p, s);
+    if (bn == 128) return launch_t<128, kModeFast>(ta, tb, p, s);
+    return launch_t<256, kModeFast>(ta, tb, p, s);
+  }
+  if (bn == 64) return launch_t<64, kModeFastSum>(ta, tb, p, s);
+  if (bn == 128) return launch_t<128, kModeFastSum>(ta, tb, p, s);
+  return launch_t<256, kModeFastSum>(ta, tb, p, s);
 }
 
 // ---- dense int8 peak probe -------------------------------------------------------------------------

@@ -1,13 +1,19 @@
-// Generic-epilogue instantiations of the persistent tcgen05 kernel (tc_kernel.cuh): every rounding mode,
-// compute dtype, the oneDNN-style float post-ops and raw int32 output, through epilogue_one().
+// Generic- and raw-epilogue instantiations of the persistent tcgen05 kernel (tc_kernel.cuh): every
+// rounding mode, compute dtype and the oneDNN-style float post-ops go through epilogue_one(); plain
+// qnn.conv2d / qnn.dense / qnn.batch_matmul (int32 accumulators out) use the vectorised raw path.
 #include "tc_kernel.cuh"
 
 namespace tkb {
 
-int launch_tc_generic(int bn, const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s) {
-  if (bn == 64) return launch_t<64, false>(ta, tb, p, s);
-  if (bn == 128) return launch_t<128, false>(ta, tb, p, s);
-  return launch_t<256, false>(ta, tb, p, s);
+int launch_tc_other(int bn, int mode, const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s) {
+  if (mode == kModeRaw) {
+    if (bn == 64) return launch_t<64, kModeRaw>(ta, tb, p, s);
+    if (bn == 128) return launch_t<128, kModeRaw>(ta, tb, p, s);
+    return launch_t<256, kModeRaw>(ta, tb, p, s);
+  }
+  if (bn == 64) return launch_t<64, kModeGeneric>(ta, tb, p, s);
+  if (bn == 128) return launch_t<128, kModeGeneric>(ta, tb, p, s);
+  return launch_t<256, kModeGeneric>(ta, tb, p, s);
 }
 
 }  // namespace tkb

@@ -532,6 +532,30 @@ static bool fold_side(const RqParams& p, const RqHost& h, bool identity, FastSid
   return true;
 }
 
+// Rewrite q' = ((q << ls) * M + C) >> T  (T in f->s1) as  hi32((q << ls') * M' + C') >> s  so that the kernel
+// needs one IMAD.WIDE and one 32-bit shift: scale by 2^(32-T) when T < 32, split between the left shift
+// of q (|q| <= 255, so ls' <= 22 keeps q << ls' inside int32) and the multiplier.
+static bool normalize_side(FastSide* f) {
+  int T = f->s1;
+  __int128 C = f->C;
+  long long M = f->M;
+  int ls = f->ls;
+  if (T < 32) {
+    int k = 32 - T;
+    const int k1 = std::min(k, 22 - ls);
+    if (k1 < 0) return false;
+    ls += k1;
+    k -= k1;
+    M <<= k;
+    if (M > INT32_MAX) return false;
+    C <<= (32 - T);
+    T = 32;
+  }
+  if (ls > 22 || !fits_i63(C) || !fits_i63(((__int128)256 << ls) * M + (C < 0 ? -C : C))) return false;
+  f->M = (int32_t)M; f->ls = ls; f->s1 = T - 32; f->C = (long long)C;
+  return true;
+}
+
 // Fold bias, zero points, rounding constant and the two clamps of the int-mode composite into FastEpi
 // (see epilogue.cuh).  bias2[c]: constant int32 bias plus the uniform zero-point correction; wabs[c]:
 // sum_k |w[c][k]| (bounds every accumulator the kernel or the reference can form for channel c).
@@ -582,7 +606,13 @@ static bool build_fast_epi(Planner& P, const CompositeInfo& ci, const std::vecto
     if (!fits_i63(Cl)) return false;
     out->lhs.C = (long long)Cl;
     out->has_sum = 1;
-    out->sum_unsigned = e.sum_dtype == kU8;
+    if (e.sum_dtype == kI8) {  // the kernel reads the residual bytes as u' = u ^ 0x80, i.e. b = u' - 128
+      out->sum_xor = 0x80808080u;
+      const __int128 Cr = (__int128)out->rhs.C - ((__int128)128 << out->rhs.ls) * out->rhs.M;
+      if (!fits_i63(Cr)) return false;
+      out->rhs.C = (long long)Cr;
+    }
+    if (!normalize_side(&out->lhs) || !normalize_side(&out->rhs)) return false;
     out->sum_lo = std::max(e.sum_qmin, e.sum_clip_lo);
     out->sum_hi = std::min(e.sum_qmax, e.sum_clip_hi);
     int32_t olo, ohi;

@@ -77,96 +77,106 @@ __device__ __forceinline__ uint4 ldg_nc_16(const void* p) {
   return v;
 }
 
-// ---- epilogue of 32 accumulator columns of one output row ---------------------------------------
-// r: raw TMEM accumulators; row_valid: row < M; ncols: valid columns of this chunk (1..32);
-// col0: absolute first column; idx0: linear output index of (row, col0).
-template <bool FAST>
-__device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const TcKernelParams& p, const int4* tab_s,
-                                               int tab_off, bool row_valid, int ncols, int col0, long long idx0,
+// ---- epilogue -------------------------------------------------------------------------------------
+// MODE selects the inlined hot path of the epilogue warps; everything unusual (ragged N tails, outputs
+// whose rows are not 16-byte multiples, border rows that need the zero-point delta, the generic
+// rounding / compute-dtype / float variants) goes element by element through one out-of-line function,
+// which keeps the hot loop small enough to stay in the instruction cache.
+enum TcMode : int { kModeGeneric = 0, kModeFast = 1, kModeFastSum = 2, kModeRaw = 3 };
+
+__device__ __forceinline__ int4 lds128(uint32_t addr) {
+  int4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, int4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+__device__ __forceinline__ int32_t fast_requant(int32_t a, const int4& t, int32_t lo, int32_t hi) {
+  const long long c = ((long long)t.w << 32) | (unsigned long long)(uint32_t)t.z;
+  const long long v = (long long)a * (long long)t.x + c;
+  const int32_t y = (int32_t)(v >> 32) >> t.y;
+  return min(max(y, lo), hi);
+}
+__device__ __forceinline__ int32_t fast_side(int32_t q, const FastSide& f) {
+  const long long v = (long long)(q << f.ls) * (long long)f.M + f.C;
+  return (int32_t)(v >> 32) >> f.s1;
+}
+
+// one element, any configuration
+static __device__ __noinline__ void epi_slow_elem(int32_t acc, int col, long long idx, const int32_t* drow,
+                                           const TcKernelParams* p, int mode) {
+  if (drow) acc = (int32_t)((uint32_t)acc + (uint32_t)__ldg(drow + col));
+  int32_t v;
+  if (mode == kModeFast || mode == kModeFastSum) {
+    const FastEpi& f = p->f;
+    v = fast_requant(acc, __ldg(f.tabA + col), f.lo, f.hi);
+    if (mode == kModeFastSum) {
+      const int32_t b = (int32_t)(((const uint8_t*)p->sum)[idx] ^ (uint8_t)f.sum_xor);
+      v = min(max(fast_side(v, f.lhs) + fast_side(b, f.rhs), f.sum_lo), f.sum_hi);
+    }
+  } else {
+    v = epilogue_one(acc, col, idx, p->e);
+  }
+  store_from_i32(p->y, p->e.out_dtype, idx, v);
+}
+
+// 32 columns of one output row.  r: raw TMEM accumulators; ncols: valid columns (1..32); col0: absolute
+// first column; idx0: linear output index of (row, col0); tab_addr: shared address of this chunk's table.
+template <int MODE>
+__device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const TcKernelParams& p, uint32_t tab_addr,
+                                               bool row_valid, int ncols, int col0, long long idx0,
                                                const int32_t* drow, bool vec_ok) {
   if (!row_valid) return;
-  int32_t v[32];
-  const bool full = ncols == 32;
-  if constexpr (FAST) {
-    const FastEpi& f = p.f;
-    uint32_t sraw[8];
-    const bool vec_sum = f.has_sum && vec_ok && full;
-    if (vec_sum) {
-      const uint4 s0 = ldg_nc_16((const uint8_t*)p.sum + idx0), s1 = ldg_nc_16((const uint8_t*)p.sum + idx0 + 16);
-      sraw[0] = s0.x; sraw[1] = s0.y; sraw[2] = s0.z; sraw[3] = s0.w;
-      sraw[4] = s1.x; sraw[5] = s1.y; sraw[6] = s1.z; sraw[7] = s1.w;
-    }
-#pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      const int4 t = tab_s[tab_off + j];  // {M, s2, C_lo, C_hi}: same address for the whole warp (broadcast)
-      int32_t a = (int32_t)r[j];
-      if (drow) a += (j < ncols) ? __ldg(drow + col0 + j) : 0;
-      const long long c = ((long long)t.w << 32) | (unsigned long long)(uint32_t)t.z;
-      const long long acc = (long long)a * (long long)t.x + c;
-      int32_t y = (int32_t)(acc >> 32) >> t.y;
-      y = min(max(y, f.lo), f.hi);
-      if (f.has_sum) {
-        int32_t b;
-        if (vec_sum) {
-          const uint32_t w = sraw[j >> 2] >> (8 * (j & 3));
-          b = f.sum_unsigned ? (int32_t)(w & 0xFF) : (int32_t)(int8_t)(w & 0xFF);
-        } else {
-          b = (j < ncols) ? (f.sum_unsigned ? (int32_t)((const uint8_t*)p.sum)[idx0 + j]
-                                            : (int32_t)((const int8_t*)p.sum)[idx0 + j])
-                          : 0;
-        }
-        const int32_t qa = (int32_t)(((long long)(y << f.lhs.ls) * f.lhs.M + f.lhs.C) >> f.lhs.s1);
-        const int32_t qb = (int32_t)(((long long)(b << f.rhs.ls) * f.rhs.M + f.rhs.C) >> f.rhs.s1);
-        y = min(max(qa + qb, f.sum_lo), f.sum_hi);
-      }
-      v[j] = y;
-    }
-  } else {
-#pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      int32_t a = (int32_t)r[j];
-      if (j < ncols) {
-        if (drow) a = (int32_t)((uint32_t)a + (uint32_t)__ldg(drow + col0 + j));
-        v[j] = epilogue_one(a, col0 + j, idx0 + j, p.e);
-      } else {
-        v[j] = 0;
-      }
-    }
-  }
-  const int odt = p.e.out_dtype;
-  if (odt == kU8 || odt == kI8) {
-    if (vec_ok && full) {
-      uint32_t w[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
-        w[i] = (v[4 * i] & 0xFF) | ((v[4 * i + 1] & 0xFF) << 8) | ((v[4 * i + 2] & 0xFF) << 16) |
-               ((uint32_t)(v[4 * i + 3] & 0xFF) << 24);
-      uint4* dst = (uint4*)((uint8_t*)p.y + idx0);
-      dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
-      dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (j < ncols) ((uint8_t*)p.y)[idx0 + j] = (uint8_t)v[j];
-    }
-  } else if (odt == kI32) {
-    int32_t* dst = (int32_t*)p.y + idx0;
-    if (vec_ok && full) {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) ((int4*)dst)[i] = make_int4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (j < ncols) dst[j] = v[j];
-    }
-  } else {
+  const bool hot = MODE != kModeGeneric && ncols == 32 && vec_ok && drow == nullptr;
+  if (!hot) {
 #pragma unroll
     for (int j = 0; j < 32; ++j)
-      if (j < ncols) store_from_i32(p.y, odt, idx0 + j, v[j]);
+      if (j < ncols) epi_slow_elem((int32_t)r[j], col0 + j, idx0 + j, drow, &p, MODE);
+    return;
+  }
+  if constexpr (MODE == kModeRaw) {
+    int32_t* dst = (int32_t*)p.y + idx0;
+    const int32_t* bias = p.e.bias;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      int4 b = make_int4(0, 0, 0, 0);
+      if (bias) b = __ldg((const int4*)(bias + col0) + i);
+      ((int4*)dst)[i] = make_int4((int32_t)(r[4 * i] + (uint32_t)b.x), (int32_t)(r[4 * i + 1] + (uint32_t)b.y),
+                                  (int32_t)(r[4 * i + 2] + (uint32_t)b.z), (int32_t)(r[4 * i + 3] + (uint32_t)b.w));
+    }
+  } else if constexpr (MODE == kModeFast || MODE == kModeFastSum) {
+    const FastEpi& f = p.f;
+    uint32_t sraw[8];
+    if constexpr (MODE == kModeFastSum) {
+      const uint4 s0 = ldg_nc_16((const uint8_t*)p.sum + idx0), s1 = ldg_nc_16((const uint8_t*)p.sum + idx0 + 16);
+      sraw[0] = s0.x ^ f.sum_xor; sraw[1] = s0.y ^ f.sum_xor; sraw[2] = s0.z ^ f.sum_xor; sraw[3] = s0.w ^ f.sum_xor;
+      sraw[4] = s1.x ^ f.sum_xor; sraw[5] = s1.y ^ f.sum_xor; sraw[6] = s1.z ^ f.sum_xor; sraw[7] = s1.w ^ f.sum_xor;
+    }
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      uint32_t word = 0;
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+        const int j = 4 * i + jj;
+        int32_t y = fast_requant((int32_t)r[j], lds128(tab_addr + j * 16), f.lo, f.hi);
+        if constexpr (MODE == kModeFastSum) {
+          const int32_t b = (int32_t)((sraw[i] >> (8 * jj)) & 0xFFu);
+          y = min(max(fast_side(y, f.lhs) + fast_side(b, f.rhs), f.sum_lo), f.sum_hi);
+        }
+        word |= (uint32_t)(y & 0xFF) << (8 * jj);
+      }
+      w[i] = word;
+    }
+    uint4* dst = (uint4*)((uint8_t*)p.y + idx0);
+    dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
   }
 }
 
-template <int BN, bool FAST>
+template <int BN, int MODE>
 __global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
                                                          const __grid_constant__ CUtensorMap tmB,
                                                          const __grid_constant__ TcKernelParams p) {
@@ -267,7 +277,10 @@ __global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__
     const int et = threadIdx.x - 64;  // 0..127
     const int esz = dtype_size(p.e.out_dtype);
     const bool vec_ok = ((long long)p.N * esz) % 16 == 0 && (((uintptr_t)p.y) & 15) == 0 &&
-                        (p.sum == nullptr || (((uintptr_t)p.sum) & 15) == 0);
+                        (p.sum == nullptr || (((uintptr_t)p.sum) & 15) == 0) &&
+                        (MODE == kModeRaw ? (p.e.out_dtype == kI32 && (p.e.bias == nullptr || (((uintptr_t)p.e.bias) & 15) == 0))
+                                          : (p.e.out_dtype == kU8 || p.e.out_dtype == kI8));
+    const uint32_t tab_base = smem_u32(tab_s);
     uint32_t lt = 0;
     int tab_n0 = -1;
     for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
@@ -275,9 +288,11 @@ __global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__
       const long long t2 = tile / ntiles;
       const int mt = (int)(t2 % mtiles), b = (int)(t2 / mtiles);
       const int n0 = nt * BN, m0 = mt * BM;
-      if (FAST && n0 != tab_n0) {  // stage this n-tile's per-channel constants (uniform over the 4 warps)
+      if ((MODE == kModeFast || MODE == kModeFastSum) && n0 != tab_n0) {
+        // stage this n-tile's per-channel constants (the condition is uniform over the 4 epilogue warps)
         epi_bar_sync();
-        for (int i = et; i < BN; i += EPI_THREADS) tab_s[i] = n0 + i < p.N ? p.f.tabA[n0 + i] : make_int4(0, 0, 0, 0);
+        for (int i = et; i < BN; i += EPI_THREADS)
+          sts128(tab_base + i * 16, n0 + i < p.N ? __ldg(p.f.tabA + n0 + i) : make_int4(0, 0, 0, 0));
         epi_bar_sync();
         tab_n0 = n0;
       }
@@ -307,7 +322,8 @@ __global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[as]);
         }
-        epilogue_chunk<FAST>(ra, p, tab_s, c, row_valid, min(32, ncol_tile - c), n0 + c, row_off + n0 + c, drow, vec_ok);
+        epilogue_chunk<MODE>(ra, p, tab_base + c * 16, row_valid, min(32, ncol_tile - c), n0 + c, row_off + n0 + c, drow,
+                             vec_ok);
         if (!more_b) break;
         tmem_ld_wait32(rb);
         const bool more_a = c + 64 < ncol_tile;
@@ -317,7 +333,7 @@ __global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[as]);
         }
-        epilogue_chunk<FAST>(rb, p, tab_s, c + 32, row_valid, min(32, ncol_tile - c - 32), n0 + c + 32,
+        epilogue_chunk<MODE>(rb, p, tab_base + (c + 32) * 16, row_valid, min(32, ncol_tile - c - 32), n0 + c + 32,
                              row_off + n0 + c + 32, drow, vec_ok);
         if (!more_a) break;
       }
@@ -339,7 +355,7 @@ inline int num_sms() {
   return sms;
 }
 
-template <int BN, bool FAST>
+template <int BN, int MODE>
 static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s) {
   const int stage_bytes = (BM + BN) * p.bk;
   const int fixed = BN * 16 + (2 * MAX_STAGES + 4) * 8 + 16 + 1024 /* alignment slack */;
@@ -350,7 +366,7 @@ static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams
   const int smem = stages * stage_bytes + fixed;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(tc_gemm_kernel<BN, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
+    if (cudaFuncSetAttribute(tc_gemm_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
         cudaSuccess)
       return -1;
     attr_set = true;
@@ -358,12 +374,12 @@ static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams
   const long long tiles = (long long)((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN) * p.batches;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
-  tc_gemm_kernel<BN, FAST><<<grid, 192, smem, s>>>(ta, tb, p);
+  tc_gemm_kernel<BN, MODE><<<grid, 192, smem, s>>>(ta, tb, p);
   ++g_launches;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
-// generic-epilogue instantiations live in their own translation unit (compile time)
-int launch_tc_generic(int bn, const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s);
+// generic / raw epilogue instantiations live in their own translation unit (compile time)
+int launch_tc_other(int bn, int mode, const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s);
 
 }  // namespace tkb

@@ -50,6 +50,8 @@ void launch_pad4(const void* x, void* y, int elem, const long long* in_shape, co
 
 // im2col into a [N*OH*OW][Kp] matrix (Kp >= KH*KW*C, multiple of 16) for the tensor-core GEMM path
 void launch_im2col(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream_t s);
+// same matrix built from a logical NCHW tensor, K ordered (c, r, s) like OIHW weights; KH, KW <= 255
+void launch_im2col_nchw(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream_t s);
 
 // ---- tcgen05 kernels ---------------------------------------------------------------------------
 // Persistent GEMM / implicit-GEMM convolution on the 5th-gen tensor cores:

@@ -322,6 +322,35 @@ __global__ void pool2d_kernel(const void* __restrict__ x, void* __restrict__ y, 
   }
 }
 
+// 8-bit max pooling on channels-last tensors: one thread owns 16 consecutive channels of one output
+// pixel (128-bit loads / stores, byte-wise SIMD max), threads of a warp cover consecutive channel groups.
+template <bool UNSIGNED>
+__global__ void maxpool8_nhwc_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y, PoolArgs a) {
+  const int cg = a.C >> 4;
+  const long long total = (long long)a.N * a.OH * a.OW * cg;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(idx % cg);
+    long long t = idx / cg;
+    const int ox = (int)(t % a.OW); t /= a.OW;
+    const int oy = (int)(t % a.OH);
+    const int n = (int)(t / a.OH);
+    const int y0 = max(oy * a.sh - a.pt, 0), y1 = min(oy * a.sh - a.pt + a.KH - 1, a.H - 1);
+    const int x0 = max(ox * a.sw - a.pl, 0), x1 = min(ox * a.sw - a.pl + a.KW - 1, a.W - 1);
+    const uint32_t init = UNSIGNED ? 0u : 0x80808080u;
+    uint4 m = make_uint4(init, init, init, init);
+    for (int iy = y0; iy <= y1; ++iy) {
+      const uint8_t* row = x + (((long long)n * a.H + iy) * a.W) * a.C + g * 16;
+      for (int ix = x0; ix <= x1; ++ix) {
+        const uint4 v = __ldg((const uint4*)(row + (long long)ix * a.C));
+        if (UNSIGNED) { m.x = __vmaxu4(m.x, v.x); m.y = __vmaxu4(m.y, v.y); m.z = __vmaxu4(m.z, v.z); m.w = __vmaxu4(m.w, v.w); }
+        else { m.x = __vmaxs4(m.x, v.x); m.y = __vmaxs4(m.y, v.y); m.z = __vmaxs4(m.z, v.z); m.w = __vmaxs4(m.w, v.w); }
+      }
+    }
+    *(uint4*)(y + (((long long)n * a.OH + oy) * a.OW + ox) * a.C + g * 16) = m;
+  }
+}
+
 void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_include_pad, int N, int C, int H, int W,
                    int KH, int KW, int sh, int sw, int pt, int pl, int pb, int pr, const long long* xs,
                    const long long* ys, cudaStream_t s) {
@@ -333,6 +362,16 @@ void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_incl
   for (int i = 0; i < 4; ++i) { a.xs[i] = xs[i]; a.ys[i] = ys[i]; }
   const long long total = (long long)N * C * a.OH * a.OW;
   if (total == 0) return;
+  const bool dense_nhwc = xs[1] == 1 && ys[1] == 1 && xs[3] == C && ys[3] == C && xs[2] == (long long)W * C &&
+                          ys[2] == (long long)a.OW * C && xs[0] == (long long)H * W * C && ys[0] == (long long)a.OH * a.OW * C;
+  if (!is_avg && (dtype == kU8 || dtype == kI8) && (C % 16) == 0 && dense_nhwc &&
+      ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0) {
+    const long long work = total / 16;
+    if (dtype == kU8) maxpool8_nhwc_kernel<true><<<blocks_for(work, 256), 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
+    else maxpool8_nhwc_kernel<false><<<blocks_for(work, 256), 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
+    ++g_launches;
+    return;
+  }
   pool2d_kernel<<<blocks_for(total, 256), 256, 0, s>>>(x, y, a);
   ++g_launches;
 }
@@ -449,6 +488,59 @@ __global__ void im2col_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict
       a[idx] = v;
     }
   }
+}
+
+// im2col straight from a logical NCHW tensor (few input channels, e.g. the 3-channel network stem):
+// A[m][(c*KH + r)*KW + s] = x[n, c, iy, ix], i.e. K is ordered like OIHW weights.  One thread produces 16
+// consecutive bytes of a row, so a warp writes 512 contiguous bytes; the (c, r, s) decomposition of k comes
+// from a small shared-memory table.  Out-of-image taps read the input zero point.
+__global__ void im2col_nchw_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ a, ConvGeom g, int Kp) {
+  extern __shared__ uint32_t ktab[];  // [Kp] c << 16 | r << 8 | s, 0xFFFFFFFF for the zero tail
+  const int K = g.C * g.KH * g.KW;
+  for (int k = threadIdx.x; k < Kp; k += blockDim.x) {
+    const int c = k / (g.KH * g.KW), rs = k % (g.KH * g.KW);
+    ktab[k] = k < K ? ((uint32_t)c << 16) | ((uint32_t)(rs / g.KW) << 8) | (uint32_t)(rs % g.KW) : 0xFFFFFFFFu;
+  }
+  __syncthreads();
+  const int chunks = Kp >> 4;
+  const long long M = (long long)g.N * g.OH * g.OW, total = M * chunks;
+  const long long plane = (long long)g.H * g.W;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int ch = (int)(idx % chunks);
+    const long long m = idx / chunks;
+    const int ox = (int)(m % g.OW);
+    const long long t = m / g.OW;
+    const int oy = (int)(t % g.OH);
+    const long long n = t / g.OH;
+    const int iy0 = oy * g.sh - g.pt, ix0 = ox * g.sw - g.pl;
+    const uint8_t* img = x + n * g.C * plane;
+    uint32_t w[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint32_t word = 0;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const uint32_t e = ktab[ch * 16 + q * 4 + b];
+        uint32_t v = 0;
+        if (e != 0xFFFFFFFFu) {
+          const int iy = iy0 + (int)((e >> 8) & 0xFF) * g.dh, ix = ix0 + (int)(e & 0xFF) * g.dw;
+          v = (uint32_t)(g.zp_a & 0xFF);
+          if (iy >= 0 && iy < g.H && ix >= 0 && ix < g.W) v = __ldg(img + (long long)(e >> 16) * plane + (long long)iy * g.W + ix);
+        }
+        word |= v << (8 * b);
+      }
+      w[q] = word;
+    }
+    *(uint4*)(a + m * Kp + ch * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+void launch_im2col_nchw(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream_t s) {
+  const long long total = (long long)g.N * g.OH * g.OW * (Kp >> 4);
+  if (total == 0) return;
+  im2col_nchw_kernel<<<blocks_for(total, 256), 256, Kp * 4, s>>>((const uint8_t*)x, (uint8_t*)a, g, Kp);
+  ++g_launches;
 }
 
 void launch_im2col(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream_t s) {

@@ -774,11 +774,6 @@ static void plan_conv(Planner& P, int nid, bool composite) {
   if (ci.zp_w.size() > 1) g.zp_w = (const int32_t*)P.dev_upload(ci.zp_w.data(), ci.zp_w.size() * 4);
 
   const int phys = dl == "NCHW" ? kNHWC : kLogical;
-  P.need(x_eid, phys);
-  if (ci.sum_eid >= 0) P.need(ci.sum_eid, phys);
-  if (ci.bias_eid >= 0) P.need(ci.bias_eid, kLogical);
-  P.produce(y_eid, phys);
-
   std::vector<uint8_t> w_ohwi = repack_ohwi(Wt, kl, g.O, Cg, g.KH, g.KW);
   const int K = g.KH * g.KW * Cg;
   const long long M = (long long)g.N * g.OH * g.OW;
@@ -787,6 +782,16 @@ static void plan_conv(Planner& P, int nid, bool composite) {
                      (g.zp_a == 0 || ci.bias_eid < 0) && M >= 1;
   const bool force_tc = P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit";
   const bool use_tc = tc_ok && (force_tc || M * g.O >= 4096);
+  const bool want_implicit = use_tc && !direct && P.rt->conv_impl != "tc_explicit" && tc_implicit_conv_supported(g) &&
+                             g.KH <= 63 && g.KW <= 63;
+  // Explicit im2col of a tensor that still lives in its logical NCHW form (the network stem): gather from
+  // NCHW directly instead of permuting to channels-last first.
+  const bool from_nchw = use_tc && !direct && !want_implicit && phys == kNHWC && P.has(x_eid, kLogical) &&
+                         !P.has(x_eid, kNHWC) && !X.nhwc_is_noop() && g.KH <= 255 && g.KW <= 255;
+  P.need(x_eid, from_nchw ? kLogical : phys);
+  if (ci.sum_eid >= 0) P.need(ci.sum_eid, phys);
+  if (ci.bias_eid >= 0) P.need(ci.bias_eid, kLogical);
+  P.produce(y_eid, phys);
   P.rt->macs += M * g.O * K;
   P.rt->hbm_bytes += X.bytes() + Y.bytes() + (long long)w_ohwi.size() + (ci.sum_eid >= 0 ? Y.bytes() : 0);
 
@@ -798,13 +803,17 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     // activation tensor through an im2col-mode TMA map (implicit GEMM), (3) an explicit im2col matrix for
     // channel counts TMA cannot address (C % 32 != 0, e.g. the 3-channel stem).
     BorderPlan bp;
-    const bool implicit = !direct && P.rt->conv_impl != "tc_explicit" && tc_implicit_conv_supported(g) &&
-                          border_plan(g, w_ohwi, Cg, &bp);
+    const bool implicit = want_implicit && border_plan(g, w_ohwi, Cg, &bp);
     const int Kp = (direct || implicit) ? K : (K + 15) / 16 * 16;
     std::vector<uint8_t> wp((size_t)g.O * Kp, 0);
     std::vector<int32_t> corr(g.O, 0);
     for (int o = 0; o < g.O; ++o) {
-      memcpy(&wp[(size_t)o * Kp], &w_ohwi[(size_t)o * K], K);
+      if (from_nchw) {  // K ordered (c, r, s) to match launch_im2col_nchw
+        for (int c = 0; c < Cg; ++c)
+          for (int t = 0; t < g.KH * g.KW; ++t) wp[(size_t)o * Kp + (size_t)c * g.KH * g.KW + t] = w_ohwi[((size_t)o * g.KH * g.KW + t) * Cg + c];
+      } else {
+        memcpy(&wp[(size_t)o * Kp], &w_ohwi[(size_t)o * K], K);
+      }
       long long sum = 0;
       for (int k = 0; k < K; ++k) sum += g.w_dtype == kU8 ? (int)w_ohwi[(size_t)o * K + k] : (int)(int8_t)w_ohwi[(size_t)o * K + k];
       corr[o] = (int32_t)(0u - (uint32_t)g.zp_a * (uint32_t)(int32_t)sum);  // -zp_a * sum_k W[o,k]  (int32 ring)
@@ -835,17 +844,18 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     long long scratch_off = -1;
     if (!direct && !implicit) scratch_off = P.arena_alloc(M * Kp);
     snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 %s M=%lld N=%d K=%d (%dx%d s%d p%d) epi=%s", n.name.c_str(),
-             direct ? "GEMM" : (implicit ? "implicit-GEMM conv (TMA im2col)" : "GEMM + explicit im2col"), M, g.O, Kp, g.KH,
+             direct ? "GEMM" : (implicit ? "implicit-GEMM conv (TMA im2col)" : (from_nchw ? "GEMM + explicit im2col from NCHW" : "GEMM + explicit im2col")), M, g.O, Kp, g.KH,
              g.KW, g.sh, g.pt, ta.f.enabled ? "fast" : (epi.mode == kEpiInt ? "int" : (epi.mode == kEpiFloat ? "float" : "raw")));
     P.add_step(desc, [=](RunCtx& c) {
       TcArgs t = ta;
       t.e = epi;
       if (bias_eid >= 0) t.e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
       if (sum_eid >= 0) t.e.sum = c.ptr(sum_eid, phys);
-      t.a = c.ptr(x_eid, phys);
+      t.a = c.ptr(x_eid, from_nchw ? kLogical : phys);
       if (!direct && !implicit) {
         void* col = c.ws->arena + scratch_off;
-        launch_im2col(t.a, col, g, Kp, c.s);
+        if (from_nchw) launch_im2col_nchw(t.a, col, g, Kp, c.s);
+        else launch_im2col(t.a, col, g, Kp, c.s);
         t.a = col;
       }
       t.y = c.ptr(y_eid, phys);

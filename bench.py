@@ -209,6 +209,7 @@ def main():
 
     ms_e2e, _ = timed(args.warmup, args.steps, e2e_step)
     trace_bytes = mod.trace_bytes()
+    trace_d2h = mod.trace_d2h_bytes()
     clocks = sampler.stop() if rank == 0 else None
 
     # roofline of the dominant kernel (tcgen05 int8 GEMM): CUDA events around every launch, same stream
@@ -247,12 +248,12 @@ def main():
             "value_mode": "inputs resident in HBM, per-op trace captured on the device",
             "compute_only": total_images * args.steps / (ms_compute * 1e-3),
             "trace_to_host_e2e": total_images * args.steps / (ms_e2e * 1e-3),
-            "trace_bytes_per_step": trace_bytes,
+            "trace_bytes_per_step": trace_bytes, "trace_d2h_bytes_per_step": trace_d2h,
             "l2": "no explicit flush: each step streams its whole activation arena (> 126 MB L2) through HBM",
             "conv_impl": args.conv_impl, "int8_macs_per_step": macs,
         },
         "e2e": {"value": total_images * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
-                "h2d_bytes_per_step": int(x_np.nbytes), "d2h_bytes_per_step": int(trace_bytes + np.prod(out_shape))},
+                "h2d_bytes_per_step": int(x_np.nbytes), "d2h_bytes_per_step": int(trace_d2h + np.prod(out_shape))},
         "gpu_launches": int(launches),
         "roofline": {
             "bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05.mma kind::i8)", "achieved": achieved_tops,

@@ -104,6 +104,9 @@ int tkb_trace_sync(tkb_handle h);
 int tkb_trace_save(tkb_handle h, const char* path);
 int tkb_trace_blob(tkb_handle h, const void** blob, size_t* len); /* serialized in memory, owned by h */
 int64_t tkb_trace_bytes(tkb_handle h);
+/* Bytes copied device -> host per traced run: every distinct activation once (a tensor that is one node's
+ * output and another node's input is staged once and serialized twice); constants stay on the host. */
+int64_t tkb_trace_d2h_bytes(tkb_handle h);
 
 /* --- stand-alone helpers (used by tests and tools) -------------------------------------------- */
 /* GetFixedPointMultiplierShift, src/relay/qnn/utils.cc:33-57 (host, double). */

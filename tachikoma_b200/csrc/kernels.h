@@ -44,6 +44,8 @@ void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_incl
 // generic 4-D permute copy: out[i0,i1,i2,i3] (dense) = in[... strides]; elem = 1/2/4 bytes
 void launch_permute4(const void* x, void* y, int elem, const long long* out_shape, const long long* in_strides,
                      cudaStream_t s);
+// tiled 8-bit channels-last -> NCHW transpose; returns false (nothing launched) if the shape needs launch_permute4
+bool launch_nhwc_to_nchw8(const void* x, void* y, long long N, long long HW, long long C, cudaStream_t s);
 // constant pad of a dense tensor up to rank 4 (shape padded to 4 dims)
 void launch_pad4(const void* x, void* y, int elem, const long long* in_shape, const long long* pad_before,
                  const long long* out_shape, int32_t value, cudaStream_t s);

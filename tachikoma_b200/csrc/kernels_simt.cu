@@ -376,6 +376,45 @@ void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_incl
   ++g_launches;
 }
 
+// 8-bit [N][HW][C] (channels-last) -> [N][C][HW] transpose through a 64 x 64 shared-memory tile: 32-bit
+// coalesced loads along C, 32-bit coalesced stores along HW.  Used for the logical-layout copies of the
+// per-operator trace and for subgraph outputs.  Requires C % 4 == 0, HW % 4 == 0, 4-byte aligned bases.
+__global__ void __launch_bounds__(256) nhwc_to_nchw8_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y, int HW, int C) {
+  __shared__ uint8_t tile[64][68];
+  const int n = blockIdx.z, hw0 = blockIdx.x * 64, c0 = blockIdx.y * 64;
+  const uint8_t* xin = x + (long long)n * HW * C;
+  uint8_t* yout = y + (long long)n * HW * C;
+  const int t = threadIdx.x;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int idx = t + i * 256;      // 0..1023: row = hw, 16 words along C
+    const int r = idx >> 4, w = idx & 15;
+    uint32_t v = 0;
+    if (hw0 + r < HW && c0 + 4 * w < C) v = __ldg((const uint32_t*)(xin + (long long)(hw0 + r) * C + c0 + 4 * w));
+    *(uint32_t*)&tile[r][4 * w] = v;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int idx = t + i * 256;      // row = c, 16 words along HW
+    const int c = idx >> 4, w = idx & 15;
+    if (c0 + c < C && hw0 + 4 * w < HW) {
+      const uint32_t v = (uint32_t)tile[4 * w][c] | ((uint32_t)tile[4 * w + 1][c] << 8) | ((uint32_t)tile[4 * w + 2][c] << 16) |
+                         ((uint32_t)tile[4 * w + 3][c] << 24);
+      *(uint32_t*)(yout + (long long)(c0 + c) * HW + hw0 + 4 * w) = v;
+    }
+  }
+}
+
+bool launch_nhwc_to_nchw8(const void* x, void* y, long long N, long long HW, long long C, cudaStream_t s) {
+  if ((C & 3) || (HW & 3) || ((((uintptr_t)x) | ((uintptr_t)y)) & 3) || N > 65535 || (C + 63) / 64 > 65535) return false;
+  if (N * HW * C == 0) return true;
+  dim3 grid((unsigned)((HW + 63) / 64), (unsigned)((C + 63) / 64), (unsigned)N);
+  nhwc_to_nchw8_kernel<<<grid, 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, (int)HW, (int)C);
+  ++g_launches;
+  return true;
+}
+
 struct Perm4 { long long shape[4], istr[4]; };
 
 // Tiled transpose of the two dims that swap fastest-varying roles would be the speed-of-light

@@ -86,6 +86,7 @@ struct TraceRec {
   std::string name;
   int eid;
   int nid;
+  bool logical = false;  // a logical-layout copy of the tensor exists once node `nid` has run
 };
 
 struct Workspace {
@@ -121,6 +122,8 @@ struct tkb_runtime {
   std::vector<tkb::TraceRec> trace_recs;        // in emission order
   std::vector<long long> trace_host_off;        // per record
   std::vector<long long> trace_ring_off;        // per record (-1: read the tensor in place)
+  std::vector<int> trace_dup_of;                // per record: earlier record holding the same tensor, or -1
+  long long trace_d2h_bytes = 0;                // bytes copied device -> host per run (each tensor once)
   long long trace_host_bytes = 0, trace_ring_bytes = 0;
   std::vector<uint8_t> blob, trace_blob_buf;
   std::string plan_text;
@@ -263,7 +266,10 @@ struct Planner {
     }
     rt->hbm_bytes += 2 * e.bytes();
     add_step(std::string("layout ") + (phys == kNHWC ? "NCHW->NHWC" : "NHWC->NCHW") + " e" + std::to_string(r),
-             [=](RunCtx& c) { launch_permute4(c.ptr(r, other), c.ptr(r, phys), elem, oshape.data(), istr.data(), c.s); });
+             [=](RunCtx& c) {
+               if (phys == kLogical && elem == 1 && launch_nhwc_to_nchw8(c.ptr(r, other), c.ptr(r, phys), N, H * W, C, c.s)) return;
+               launch_permute4(c.ptr(r, other), c.ptr(r, phys), elem, oshape.data(), istr.data(), c.s);
+             });
   }
   void produce(int eid, int phys) {
     Entry& e = ent[eid];
@@ -1277,25 +1283,45 @@ static void build_plan(tkb_runtime* rt) {
     else if (op == "transpose") plan_transpose(P, (int)nid);
     else fail("Unsupported op: %s", op.c_str());  // same message as tachikoma_json_runtime.cc:286
     // trace records of this node: inputs then outputs, in the logical layout
+    auto add_rec = [&](const std::string& name, int eid) {
+      TraceRec tr;
+      tr.name = name; tr.eid = eid; tr.nid = (int)nid;
+      const int r = P.root(eid);
+      tr.logical = rt->ent[r].is_const || P.has(r, kLogical);  // as of this node: later conversions do not count
+      rt->trace_recs.push_back(tr);
+    };
     for (size_t i = 0; i < n.inputs.size(); ++i)
-      rt->trace_recs.push_back({n.name + "____topo-index:" + std::to_string(nid) + "____input-num:" + std::to_string(i),
-                                (int)g.eid(n.inputs[i]), (int)nid});
-    rt->trace_recs.push_back({n.name + "____topo-index:" + std::to_string(nid) + "____output-num:0", (int)g.eid((uint32_t)nid, 0), (int)nid});
+      add_rec(n.name + "____topo-index:" + std::to_string(nid) + "____input-num:" + std::to_string(i), (int)g.eid(n.inputs[i]));
+    add_rec(n.name + "____topo-index:" + std::to_string(nid) + "____output-num:0", (int)g.eid((uint32_t)nid, 0));
   }
   // graph outputs are delivered in the logical layout
   P.cur_nid = -1;
   for (auto& h : g.heads) P.need((int)g.eid(h), kLogical);
   // trace staging plan: tensors that exist in logical layout are copied in place; NHWC-physical ones
   // are permuted into a device ring first
+  // Every tensor is staged ONCE per run: an activation appears as the output of its producer and again as
+  // an input of each consumer; the later records alias the first one's host slot (the serializer reads the
+  // same bytes), so neither the D2D permute nor the D2H copy is repeated.
   rt->trace_host_off.assign(rt->trace_recs.size(), 0);
   rt->trace_ring_off.assign(rt->trace_recs.size(), -1);
+  rt->trace_dup_of.assign(rt->trace_recs.size(), -1);
+  rt->trace_d2h_bytes = 0;
   long long hoff = 0, roff = 0;
+  std::unordered_map<int, int> first_of_root;
   for (size_t i = 0; i < rt->trace_recs.size(); ++i) {
     const int r = P.root(rt->trace_recs[i].eid);
     const Entry& e = rt->ent[r];
+    auto it = first_of_root.find(r);
+    if (it != first_of_root.end()) {
+      rt->trace_dup_of[i] = it->second;
+      rt->trace_host_off[i] = rt->trace_host_off[it->second];
+      continue;
+    }
+    first_of_root[r] = (int)i;
     rt->trace_host_off[i] = hoff;
     hoff += (rt->ent[rt->trace_recs[i].eid].bytes() + 63) & ~63LL;
-    if (!e.is_const && !P.has(r, kLogical)) {
+    if (!e.is_const) rt->trace_d2h_bytes += e.bytes();
+    if (!e.is_const && !rt->trace_recs[i].logical) {
       rt->trace_ring_off[i] = roff;
       roff += (e.bytes() + 255) & ~255LL;
     }
@@ -1335,6 +1361,13 @@ static void ensure_trace_buffers(tkb_runtime* rt, Workspace* ws) {
     if (ws->trace_host) cudaFreeHost(ws->trace_host);
     CUDA_OK(cudaMallocHost((void**)&ws->trace_host, rt->trace_host_bytes + 256));
     ws->trace_host_bytes = rt->trace_host_bytes;
+    for (size_t i = 0; i < rt->trace_recs.size(); ++i) {  // constants never change: written once, never copied again
+      if (rt->trace_dup_of[i] >= 0) continue;
+      int r = rt->trace_recs[i].eid;
+      while (rt->ent[r].alias_of >= 0) r = rt->ent[r].alias_of;
+      const Entry& e = rt->ent[r];
+      if (e.is_const) memcpy(ws->trace_host + rt->trace_host_off[i], e.host.data(), (size_t)rt->ent[rt->trace_recs[i].eid].bytes());
+    }
   }
 }
 
@@ -1343,14 +1376,15 @@ static void ensure_trace_buffers(tkb_runtime* rt, Workspace* ws) {
 static void trace_node(RunCtx& c, size_t lo, size_t hi) {
   tkb_runtime* rt = c.rt;
   for (size_t i = lo; i < hi; ++i) {
-    if (rt->trace_ring_off[i] < 0) continue;
+    if (rt->trace_ring_off[i] < 0 || rt->trace_dup_of[i] >= 0) continue;
     const int eid = rt->trace_recs[i].eid;
     int r = eid;
     while (rt->ent[r].alias_of >= 0) r = rt->ent[r].alias_of;
     const Entry& e = rt->ent[r];
     const long long N = e.shape[0], C = e.shape[1], H = e.shape[2], W = e.shape[3];
     long long oshape[4] = {N, C, H, W}, istr[4] = {H * W * C, 1, W * C, C};
-    launch_permute4(c.ptr(r, kNHWC), c.ws->trace_ring + rt->trace_ring_off[i], dtype_size(e.dtype), oshape, istr, c.s);
+    if (dtype_size(e.dtype) != 1 || !launch_nhwc_to_nchw8(c.ptr(r, kNHWC), c.ws->trace_ring + rt->trace_ring_off[i], N, H * W, C, c.s))
+      launch_permute4(c.ptr(r, kNHWC), c.ws->trace_ring + rt->trace_ring_off[i], dtype_size(e.dtype), oshape, istr, c.s);
   }
   if (rt->trace_mode < 2) return;
   CUDA_OK(cudaEventRecord(c.ws->ev, c.s));
@@ -1362,7 +1396,7 @@ static void trace_node(RunCtx& c, size_t lo, size_t hi) {
     const Entry& e = rt->ent[r];
     uint8_t* dst = c.ws->trace_host + rt->trace_host_off[i];
     const long long bytes = rt->ent[eid].bytes();
-    if (e.is_const) { memcpy(dst, e.host.data(), bytes); continue; }  // constants never leave the host
+    if (e.is_const || rt->trace_dup_of[i] >= 0) continue;  // constants were written once; duplicates alias a slot
     const void* src = rt->trace_ring_off[i] >= 0 ? (const void*)(c.ws->trace_ring + rt->trace_ring_off[i]) : c.ptr(r, kLogical);
     CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.ws->side));
   }
@@ -1745,6 +1779,8 @@ int tkb_trace_save(tkb_handle h, const char* path) {
   if (w != len) fail("short write to %s", path);
   TKB_CATCH
 }
+
+int64_t tkb_trace_d2h_bytes(tkb_handle h) { return h->trace_d2h_bytes; }
 
 int64_t tkb_trace_bytes(tkb_handle h) {
   int64_t n = 0;

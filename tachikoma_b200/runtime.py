@@ -82,6 +82,8 @@ def load_library():
     L.tkb_trace_blob.argtypes = [H, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t)]
     L.tkb_trace_bytes.restype = ctypes.c_int64
     L.tkb_trace_bytes.argtypes = [H]
+    L.tkb_trace_d2h_bytes.restype = ctypes.c_int64
+    L.tkb_trace_d2h_bytes.argtypes = [H]
     L.tkb_fixed_point_multiplier_shift.argtypes = [ctypes.c_double, ctypes.POINTER(ctypes.c_int32),
                                                    ctypes.POINTER(ctypes.c_int32)]
     L.tkb_fixed_point_multiplier_shift.restype = None
@@ -251,6 +253,10 @@ class TachikomaJSONRuntime:
 
     def trace_bytes(self):
         return int(self._lib.tkb_trace_bytes(self._h))
+
+    def trace_d2h_bytes(self):
+        """Bytes copied device -> host per traced run (each distinct activation once)."""
+        return int(self._lib.tkb_trace_d2h_bytes(self._h))
 
 
 def fixed_point_multiplier_shift(m):

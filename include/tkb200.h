@@ -114,6 +114,9 @@ void tkb_fixed_point_multiplier_shift(double multiplier, int32_t* significand, i
 /* Dense int8 tcgen05 peak probe: issues back-to-back kind::i8 MMAs from resident smem tiles on all
  * SMs; returns achieved tera-ops/s (2*MAC) in *tops.  Roofline denominator for conv/dense. */
 int tkb_probe_int8_peak(int iters, double* tops, void* cuda_stream);
+/* Same probe with UMMA N = n (multiple of 16, <= 256) and a tcgen05.commit every `commit_every` groups of 4 MMAs
+ * (0 = never): how the issue rate depends on the instruction shape and on per-stage commits. */
+int tkb_probe_int8_shape(int iters, int n, int commit_every, double* tops, void* cuda_stream);
 /* Library build info: "sm_100a;<n kernels>;..." */
 const char* tkb_version(void);
 

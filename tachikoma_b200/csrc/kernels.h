@@ -81,6 +81,7 @@ bool tc_gemm_supported(int M, int N, int K);
 bool tc_implicit_conv_supported(const ConvGeom& g);
 int launch_tc(const TcArgs& a, cudaStream_t s);
 int probe_int8_peak(int iters, double* tops, cudaStream_t s);
+int probe_int8_shape(int iters, int n, int commit_every, double* tops, cudaStream_t s);
 
 extern thread_local long long g_launches;  // kernels launched by this thread (summed per handle)
 

@@ -14,6 +14,7 @@
 //               accumulator stage the MMA warp already fills the other.
 // The arithmetic contract of the epilogue is in epilogue.cuh (reference: requantize.cc:195-273,
 // intrin_rule.cc:165-250, add.cc:40-93).
+#include <cstdlib>
 #include <mutex>
 
 #include "tc_kernel.cuh"
@@ -124,6 +125,7 @@ int launch_tc(const TcArgs& a, cudaStream_t s) {
   p.batches = a.B; p.w_batched = a.w_batched;
   p.e = a.e;
   p.f = a.f;
+  if (const char* d = getenv("TKB_DBG")) p.dbg = atoi(d);
   p.delta = a.delta; p.cls_h = a.cls_h; p.cls_w = a.cls_w; p.ncls_w = a.ncls_w;
   int bk;
   if (a.implicit) {
@@ -168,31 +170,47 @@ int launch_tc(const TcArgs& a, cudaStream_t s) {
 // One CTA per SM issues `iters` x 4 tcgen05.mma (128 x 256 x 32, int8) from resident smem tiles into two
 // TMEM accumulators; nothing is loaded or stored, so the time is the tensor pipe's issue floor.  This is
 // the measured denominator for the conv/dense roofline.
-__global__ void __launch_bounds__(128) probe_i8_kernel(int iters, uint32_t idesc) {
+__global__ void __launch_bounds__(128) probe_i8_kernel(int iters, uint32_t idesc, int commit_every) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   __shared__ uint64_t done;
+  __shared__ uint64_t kb_bar[2];
   __shared__ uint32_t tmem_ptr;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < (BM * 128 + 256 * 128) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0x01010101u;
-  if (threadIdx.x == 0) { mbar_init(&done, 1); fence_barrier_init(); }
+  if (threadIdx.x == 0) { mbar_init(&done, 1); mbar_init(&kb_bar[0], 1); mbar_init(&kb_bar[1], 1); fence_barrier_init(); }
   if (warp == 0) tmem_alloc<512>(&tmem_ptr);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_ptr;
-  if (warp == 0 && lane == 0) {
-    const uint32_t a_addr = smem_u32(smem), b_addr = a_addr + BM * 128;
+  if (warp == 0) {
+    // the whole warp runs the loop; one elected lane issues (elect.sync lets the compiler emit the
+    // uniform-datapath UTCIMMA / UTCBAR directly instead of a per-active-thread serialisation loop)
+    const uint32_t a_lo = ((smem_u32(smem) >> 4) & 0x3FFF) | (1u << 16);
+    const uint32_t b_lo = (((smem_u32(smem) + BM * 128) >> 4) & 0x3FFF) | (1u << 16);
+    const uint32_t hi = (uint32_t)(smem_desc(0, 16, 1024, 2) >> 32);
+    // commit_every is a bit mask of per-iteration extras: 1 = tcgen05.commit to a scratch mbarrier,
+    // 2 = tcgen05.fence::after_thread_sync, 4 = wait for the commit of the iteration two back (what a
+    // TMA producer does before it refills a slot), 8 = wait for the commit of THIS iteration (no overlap)
+    uint32_t phase[2] = {0, 0};
     for (int it = 0; it < iters; ++it) {
+      if (commit_every & 2) tc_fence_after();
+      if (elect_one()) {
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const uint64_t da = smem_desc(a_addr + k * UMMA_K, 16, 1024, 2);
-        const uint64_t db = smem_desc(b_addr + k * UMMA_K, 16, 1024, 2);
-        mma_i8(tmem_base + (it & 1) * 256, da, db, idesc, 1);
+        for (int k = 0; k < 4; ++k)
+          mma_i8(tmem_base + (it & 1) * 256, ((uint64_t)hi << 32) | (a_lo + 2 * k), ((uint64_t)hi << 32) | (b_lo + 2 * k), idesc, 1);
+        if (commit_every & 1) tc_commit(&kb_bar[it & 1]);
       }
+      __syncwarp();
+      if ((commit_every & 5) == 5 && it >= 2) { mbar_wait(&kb_bar[it & 1], phase[it & 1]); phase[it & 1] ^= 1; }
+      if ((commit_every & 9) == 9) { mbar_wait(&kb_bar[it & 1], phase[it & 1]); phase[it & 1] ^= 1; }
     }
-    tc_commit(&done);
+    if (elect_one()) {
+      tc_commit(&done);
+    }
+    __syncwarp();
     mbar_wait(&done, 0);
   }
   tc_fence_before();
@@ -200,17 +218,17 @@ __global__ void __launch_bounds__(128) probe_i8_kernel(int iters, uint32_t idesc
   if (warp == 0) tmem_dealloc<512>(tmem_base);
 }
 
-int probe_int8_peak(int iters, double* tops, cudaStream_t s) {
+int probe_int8_shape(int iters, int n, int commit_every, double* tops, cudaStream_t s) {
   const int smem = BM * 128 + 256 * 128 + 1024;
   if (cudaFuncSetAttribute(probe_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
   const int sms = num_sms();
-  const uint32_t idesc = idesc_i8(128, 256, true, true);
+  const uint32_t idesc = idesc_i8(128, n, true, true);
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0);
   cudaEventCreate(&e1);
-  probe_i8_kernel<<<sms, 128, smem, s>>>(iters / 8 + 1, idesc);  // warm-up
+  probe_i8_kernel<<<sms, 128, smem, s>>>(iters / 8 + 1, idesc, commit_every);  // warm-up
   cudaEventRecord(e0, s);
-  probe_i8_kernel<<<sms, 128, smem, s>>>(iters, idesc);
+  probe_i8_kernel<<<sms, 128, smem, s>>>(iters, idesc, commit_every);
   cudaEventRecord(e1, s);
   g_launches += 2;
   if (cudaEventSynchronize(e1) != cudaSuccess) return -1;
@@ -218,9 +236,11 @@ int probe_int8_peak(int iters, double* tops, cudaStream_t s) {
   cudaEventElapsedTime(&ms, e0, e1);
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
-  const double ops = 2.0 * 128 * 256 * 32 * 4.0 * (double)iters * sms;
+  const double ops = 2.0 * 128 * n * 32 * 4.0 * (double)iters * sms;
   *tops = ops / (ms * 1e-3) / 1e12;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
+
+int probe_int8_peak(int iters, double* tops, cudaStream_t s) { return probe_int8_shape(iters, 256, 0, tops, s); }
 
 }  // namespace tkb

@@ -1792,6 +1792,14 @@ void tkb_fixed_point_multiplier_shift(double multiplier, int32_t* significand, i
   fixed_point_multiplier_shift(multiplier, significand, exponent);
 }
 
+int tkb_probe_int8_shape(int iters, int n, int commit_every, double* tops, void* cuda_stream) {
+  TKB_TRY
+  if (n < 16 || n > 256 || (n % 16)) fail("probe: N must be a multiple of 16 in [16, 256]");
+  if (probe_int8_shape(iters, n, commit_every, tops, (cudaStream_t)cuda_stream) != 0)
+    fail("peak probe failed: %s", cudaGetErrorString(cudaGetLastError()));
+  TKB_CATCH
+}
+
 int tkb_probe_int8_peak(int iters, double* tops, void* cuda_stream) {
   TKB_TRY
   if (probe_int8_peak(iters, tops, (cudaStream_t)cuda_stream) != 0)

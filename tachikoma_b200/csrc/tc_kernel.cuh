@@ -15,7 +15,9 @@ using namespace ptx;
 static constexpr int BM = 128;       // UMMA M (rows = TMEM lanes)
 static constexpr int UMMA_K = 32;    // int8 elements per tcgen05.mma
 static constexpr int MAX_STAGES = 12;
-static constexpr int EPI_THREADS = 128;
+static constexpr int EPI_WARPS = 8;        // two per TMEM lane quadrant, each draining half of the tile's columns
+static constexpr int EPI_THREADS = EPI_WARPS * 32;
+static constexpr int TC_THREADS = 64 + EPI_THREADS;
 
 struct TcKernelParams {
   void* y;
@@ -24,6 +26,7 @@ struct TcKernelParams {
   int batches, w_batched; // batched GEMM (qnn.batch_matmul): tensor-map z coordinate
   int bk;                 // bytes of K per pipeline stage: 128 / 64 / 32 (= swizzle span)
   int stages;
+  int kps;                // k-blocks per pipeline stage: one mbarrier round trip covers kps * bk/32 MMAs
   uint32_t idesc;
   uint32_t desc_hi;       // upper 32 bits of the UMMA smem descriptors (SBO, version, swizzle mode)
   // implicit convolution
@@ -33,6 +36,7 @@ struct TcKernelParams {
   const uint8_t* cls_h;   // [OH]
   const uint8_t* cls_w;   // [OW]
   int ncls_w;
+  int dbg;                // timing experiments only (TKB_DBG): 1 = no epilogue work, 2 = no B loads, 4 = no A loads
   EpiParams e;            // generic epilogue (any rounding / compute dtype / float mode / raw int32)
   FastEpi f;              // host-folded fixed-point epilogue (default QNN configuration)
 };
@@ -177,12 +181,12 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const Tc
 }
 
 template <int BN, int MODE>
-__global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
+__global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
                                                          const __grid_constant__ CUtensorMap tmB,
                                                          const __grid_constant__ TcKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  const int a_bytes = BM * p.bk, b_bytes = BN * p.bk, stage_bytes = a_bytes + b_bytes;
+  const int a_bytes = BM * p.bk, b_bytes = BN * p.bk, sub_bytes = a_bytes + b_bytes, stage_bytes = p.kps * sub_bytes;
   int4* tab_s = (int4*)(smem + p.stages * stage_bytes);
   uint64_t* full = (uint64_t*)(tab_s + BN);
   uint64_t* empty = full + MAX_STAGES;
@@ -200,7 +204,7 @@ __global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
     for (int i = 0; i < p.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], EPI_WARPS); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<2 * BN>(tmem_ptr);
@@ -209,72 +213,93 @@ __global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
+  // Producer and MMA warps run their loops with the whole warp converged (all lanes poll the mbarriers) and
+  // guard only the issuing instructions with elect.sync: the compiler then emits the uniform-datapath
+  // UTMALDG / UTCIMMA / UTCBAR directly.  (An `if (lane == 0)` around the loop makes it wrap each of them
+  // in a per-active-thread serialisation loop, which cost ~300 cycles per MMA in the first version.)
   if (warp == 0) {
     // ===== TMA producer =====
-    if (lane == 0) {
-      int st = 0;
-      uint32_t ph = 0;
-      for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int nt = (int)(tile % ntiles);
-        const long long t2 = tile / ntiles;
-        const int mt = (int)(t2 % mtiles), b = (int)(t2 / mtiles);
-        const int n0 = nt * BN, m0 = mt * BM;
-        int cw = 0, chh = 0, cn = 0;
-        if (p.implicit) {
-          const int q0 = m0 % p.OW, t3 = m0 / p.OW;
-          cw = q0 * p.sw - p.pl;
-          chh = (t3 % p.OH) * p.sh - p.pt;
-          cn = t3 / p.OH;
-        }
-        int r = 0, s = 0, cc = 0;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&empty[st], ph ^ 1);
-          uint8_t* sa = smem + st * stage_bytes;
-          mbar_expect_tx(&full[st], (uint32_t)stage_bytes);
-          if (p.implicit) {
-            tma_load_im2col_4d(sa, &tmA, &full[st], cc * p.bk, cw, chh, cn, (uint16_t)(s * p.dw), (uint16_t)(r * p.dh));
-            if (++cc == cchunks) { cc = 0; if (++s == p.KW) { s = 0; ++r; } }
-          } else {
-            tma_load_3d(sa, &tmA, &full[st], kb * p.bk, m0, b);
+    int st = 0;
+    uint32_t ph = 0;
+    const bool ld_a = !(p.dbg & 4), ld_b = !(p.dbg & 2);
+    const uint32_t tx_bytes = (uint32_t)((ld_a ? a_bytes : 0) + (ld_b ? b_bytes : 0));
+    for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int nt = (int)(tile % ntiles);
+      const long long t2 = tile / ntiles;
+      const int mt = (int)(t2 % mtiles), b = (int)(t2 / mtiles);
+      const int n0 = nt * BN, m0 = mt * BM;
+      int cw = 0, chh = 0, cn = 0;
+      if (p.implicit) {
+        const int q0 = m0 % p.OW, t3 = m0 / p.OW;
+        cw = q0 * p.sw - p.pl;
+        chh = (t3 % p.OH) * p.sh - p.pt;
+        cn = t3 / p.OH;
+      }
+      int r = 0, s = 0, cc = 0;
+      for (int kb0 = 0; kb0 < num_kb; kb0 += p.kps) {
+        const int nsub = min(p.kps, num_kb - kb0);
+        mbar_wait(&empty[st], ph ^ 1);
+        if (elect_one()) {
+          mbar_expect_tx(&full[st], (uint32_t)nsub * tx_bytes);
+          for (int j = 0; j < nsub; ++j) {
+            uint8_t* sa = smem + st * stage_bytes + j * sub_bytes;
+            const int kb = kb0 + j;
+            if (ld_a) {
+              if (p.implicit) {
+                tma_load_im2col_4d(sa, &tmA, &full[st], cc * p.bk, cw, chh, cn, (uint16_t)(s * p.dw), (uint16_t)(r * p.dh));
+                if (++cc == cchunks) { cc = 0; if (++s == p.KW) { s = 0; ++r; } }
+              } else {
+                tma_load_3d(sa, &tmA, &full[st], kb * p.bk, m0, b);
+              }
+            }
+            if (ld_b) tma_load_3d(sa + a_bytes, &tmB, &full[st], kb * p.bk, n0, p.w_batched ? b : 0);
           }
-          tma_load_3d(sa + a_bytes, &tmB, &full[st], kb * p.bk, n0, p.w_batched ? b : 0);
-          if (++st == p.stages) { st = 0; ph ^= 1; }
         }
+        // the tap / chunk counters live in the elected lane only; every lane needs them for the next group
+        r = __shfl_sync(0xffffffffu, r, 0); s = __shfl_sync(0xffffffffu, s, 0); cc = __shfl_sync(0xffffffffu, cc, 0);
+        if (++st == p.stages) { st = 0; ph ^= 1; }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
-    if (lane == 0) {
-      int st = 0;
-      uint32_t ph = 0, lt = 0;
-      const int kper = p.bk / UMMA_K;
-      for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-        const uint32_t as = lt & 1;
-        mbar_wait(&tempty[as], ((lt >> 1) & 1) ^ 1);
+    int st = 0;
+    uint32_t ph = 0, lt = 0;
+    const int kper = p.bk / UMMA_K;
+    const uint32_t smem_base = smem_u32(smem);
+    for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const uint32_t as = lt & 1;
+      mbar_wait(&tempty[as], ((lt >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BN;
+      for (int kb0 = 0; kb0 < num_kb; kb0 += p.kps) {
+        const int nsub = min(p.kps, num_kb - kb0);
+        mbar_wait(&full[st], ph);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&full[st], ph);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem + st * stage_bytes);
-          const uint32_t b_addr = a_addr + a_bytes;
-          for (int k = 0; k < kper; ++k) {
-            // K-major swizzled tiles: 8-row groups are 8*bk bytes apart (SBO, in desc_hi); advancing K inside
-            // the swizzle row is a plain start-address offset.
-            const uint64_t da = ((uint64_t)p.desc_hi << 32) | (uint64_t)((((a_addr + k * UMMA_K) >> 4) & 0x3FFF) | (1u << 16));
-            const uint64_t db = ((uint64_t)p.desc_hi << 32) | (uint64_t)((((b_addr + k * UMMA_K) >> 4) & 0x3FFF) | (1u << 16));
-            mma_i8(d_tmem, da, db, p.idesc, (kb | k) != 0);
+        if (elect_one()) {
+          // K-major swizzled tiles: 8-row groups are 8*bk bytes apart (SBO, in desc_hi); advancing K inside the
+          // swizzle row is a plain start-address offset (+32 B = +2 in the descriptor's 16-byte units).
+          const uint64_t hi = (uint64_t)p.desc_hi << 32;
+          uint32_t acc = kb0 != 0;
+          for (int j = 0; j < nsub; ++j) {
+            const uint32_t a_addr = smem_base + st * stage_bytes + j * sub_bytes;
+            const uint32_t a_lo = ((a_addr >> 4) & 0x3FFF) | (1u << 16);
+            const uint32_t b_lo = (((a_addr + a_bytes) >> 4) & 0x3FFF) | (1u << 16);
+            for (int k = 0; k < kper; ++k) {
+              mma_i8(d_tmem, hi | (a_lo + 2 * k), hi | (b_lo + 2 * k), p.idesc, acc);
+              acc = 1;
+            }
           }
           tc_commit(&empty[st]);  // frees the smem slot once the MMAs above have read it
-          if (++st == p.stages) { st = 0; ph ^= 1; }
+          if (kb0 + nsub >= num_kb) tc_commit(&tfull[as]);
         }
-        tc_commit(&tfull[as]);
+        __syncwarp();
+        if (++st == p.stages) { st = 0; ph ^= 1; }
       }
     }
   } else {
     // ===== epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31 =====
-    const int q = warp & 3;
-    const int et = threadIdx.x - 64;  // 0..127
+    const int q = warp & 3, half = (warp - 2) >> 2;
+    const int et = threadIdx.x - 64;  // 0..EPI_THREADS-1
     const int esz = dtype_size(p.e.out_dtype);
     const bool vec_ok = ((long long)p.N * esz) % 16 == 0 && (((uintptr_t)p.y) & 15) == 0 &&
                         (p.sum == nullptr || (((uintptr_t)p.sum) & 15) == 0) &&
@@ -289,7 +314,7 @@ __global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__
       const int mt = (int)(t2 % mtiles), b = (int)(t2 / mtiles);
       const int n0 = nt * BN, m0 = mt * BM;
       if ((MODE == kModeFast || MODE == kModeFastSum) && n0 != tab_n0) {
-        // stage this n-tile's per-channel constants (the condition is uniform over the 4 epilogue warps)
+        // stage this n-tile's per-channel constants (the condition is uniform over the epilogue warps)
         epi_bar_sync();
         for (int i = et; i < BN; i += EPI_THREADS)
           sts128(tab_base + i * 16, n0 + i < p.N ? __ldg(p.f.tabA + n0 + i) : make_int4(0, 0, 0, 0));
@@ -310,30 +335,42 @@ __global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
       const int ncol_tile = min(BN, p.N - n0);
+      const int cbeg = half * (BN / 2), cend = min(cbeg + BN / 2, ncol_tile);
+      if (cbeg >= cend) {  // nothing to drain for this warp (ragged N tail): just release the stage
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[as]);
+        continue;
+      }
+      if (p.dbg & 1) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[as]);
+        continue;
+      }
       uint32_t ra[32], rb[32];
-      tmem_ld32(t_addr, ra);
+      tmem_ld32(t_addr + cbeg, ra);
 #pragma unroll 1
-      for (int c = 0; c < BN; c += 64) {
+      for (int c = cbeg;; c += 64) {
         tmem_ld_wait32(ra);
-        const bool more_b = c + 32 < ncol_tile;
+        const bool more_b = c + 32 < cend;
         if (more_b) tmem_ld32(t_addr + c + 32, rb);
-        else {  // all TMEM reads of this tile are complete: hand the accumulator stage back to the MMA warp
+        else {  // all TMEM reads of this warp are complete: hand the accumulator stage back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[as]);
         }
-        epilogue_chunk<MODE>(ra, p, tab_base + c * 16, row_valid, min(32, ncol_tile - c), n0 + c, row_off + n0 + c, drow,
-                             vec_ok);
+        epilogue_chunk<MODE>(ra, p, tab_base + c * 16, row_valid, min(32, cend - c), n0 + c, row_off + n0 + c, drow, vec_ok);
         if (!more_b) break;
         tmem_ld_wait32(rb);
-        const bool more_a = c + 64 < ncol_tile;
+        const bool more_a = c + 64 < cend;
         if (more_a) tmem_ld32(t_addr + c + 64, ra);
         else {
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[as]);
         }
-        epilogue_chunk<MODE>(rb, p, tab_base + (c + 32) * 16, row_valid, min(32, ncol_tile - c - 32), n0 + c + 32,
+        epilogue_chunk<MODE>(rb, p, tab_base + (c + 32) * 16, row_valid, min(32, cend - c - 32), n0 + c + 32,
                              row_off + n0 + c + 32, drow, vec_ok);
         if (!more_a) break;
       }
@@ -357,9 +394,19 @@ inline int num_sms() {
 
 template <int BN, int MODE>
 static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s) {
-  const int stage_bytes = (BM + BN) * p.bk;
+  const int sub_bytes = (BM + BN) * p.bk;
   const int fixed = BN * 16 + (2 * MAX_STAGES + 4) * 8 + 16 + 1024 /* alignment slack */;
-  int stages = (227 * 1024 - fixed) / stage_bytes;
+  const int budget = 227 * 1024 - fixed;
+  const int num_kb = p.implicit ? p.KH * p.KW * (p.C / p.bk) : (p.K + p.bk - 1) / p.bk;
+  // Group k-blocks so that one mbarrier round trip (~100+ cycles on the single issuing thread for each of
+  // wait / elect / commit) covers enough MMAs: stages of up to 64 KB, at least 3 of them.
+  int kps = (64 * 1024) / sub_bytes;
+  kps = kps < 1 ? 1 : (kps > 8 ? 8 : kps);
+  if (kps > num_kb) kps = num_kb;
+  while (kps > 1 && budget / (kps * sub_bytes) < 3) --kps;
+  p.kps = kps;
+  const int stage_bytes = kps * sub_bytes;
+  int stages = budget / stage_bytes;
   stages = stages > MAX_STAGES ? MAX_STAGES : stages;
   if (stages < 2) return -1;
   p.stages = stages;
@@ -374,7 +421,7 @@ static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams
   const long long tiles = (long long)((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN) * p.batches;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
-  tc_gemm_kernel<BN, MODE><<<grid, 192, smem, s>>>(ta, tb, p);
+  tc_gemm_kernel<BN, MODE><<<grid, TC_THREADS, smem, s>>>(ta, tb, p);
   ++g_launches;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

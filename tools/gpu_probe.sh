@@ -1,0 +1,6 @@
+#!/bin/bash
+for cfg in "64 56 64 3 1" "128 28 128 3 1" "256 14 256 3 1" "512 7 512 3 1"; do
+  for dbg in 0 1 2 4 6 7; do
+    TKB_DBG=$dbg timeout 120 python tools/conv_probe.py $cfg 2>&1 | tail -1
+  done
+done

@@ -55,6 +55,9 @@ void launch_im2col(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream
 // same matrix built from a logical NCHW tensor, K ordered (c, r, s) like OIHW weights; KH, KW <= 255
 void launch_im2col_nchw(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream_t s);
 
+// vertical unfold of an NCHW tensor with C*KH <= 32 into [N][OH][W][32] (see kernels_simt.cu)
+void launch_unfold_rows_nchw(const void* x, void* y, const ConvGeom& g, cudaStream_t s);
+
 // ---- tcgen05 kernels ---------------------------------------------------------------------------
 // Persistent GEMM / implicit-GEMM convolution on the 5th-gen tensor cores:
 //   Y[b][M][N] = epilogue(A[b][M][K] . W[b?][N][K]^T), A/W int8 or uint8, K-major, zp_w == 0.

@@ -582,6 +582,80 @@ void launch_im2col_nchw(const void* x, void* a, const ConvGeom& g, int Kp, cudaS
   ++g_launches;
 }
 
+// "Vertical unfold" of a few-channel NCHW tensor (network stem):
+//   X3[n][p][pl + w][r*C + c] = x[n, c, p*sh - pt + r*dh, w]      (CP = 32 bytes per pixel)
+// for the KH vertical taps of output row p; rows are physically padded with pl / pr extra pixels.  Taps and
+// pixels outside the image hold the input zero point (exactly the reference's pad-with-zp,
+// convolution.cc:227-253), bytes beyond KH*C are zero.  The im2col row of output pixel (p, q) is then the
+// CONTIGUOUS window of KW pixels starting at pixel q*sw of row (n, p): a tiled tensor map with an overlapping
+// row stride of sw*CP bytes presents X3 as the [M][KW*CP] GEMM operand without materialising it.
+// One thread per (n, p, padded w): loads coalesce along w, the CP bytes are stored as 16-byte vectors.
+template <int C_, int KH_>
+__global__ void unfold_rows_nchw_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y, ConvGeom g) {
+  constexpr int CP = 32;
+  const int C = C_ ? C_ : g.C, KH = KH_ ? KH_ : g.KH;
+  const int WP = g.W + g.pl + g.pr;
+  const long long total = (long long)g.N * g.OH * WP;
+  const long long plane = (long long)g.H * g.W;
+  const uint32_t zp = (uint32_t)(g.zp_a & 0xFF);
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int wp = (int)(idx % WP);
+    const long long t = idx / WP;
+    const int p = (int)(t % g.OH);
+    const long long n = t / g.OH;
+    const int w = wp - g.pl;
+    const bool win = w >= 0 && w < g.W;
+    const uint8_t* img = x + n * g.C * plane + (win ? w : 0);
+    const int iy0 = p * g.sh - g.pt;
+    uint32_t words[CP / 4];
+#pragma unroll
+    for (int i = 0; i < CP / 4; ++i) words[i] = 0;
+    if (C_ && KH_) {
+#pragma unroll
+      for (int r = 0; r < KH_; ++r) {
+        const int iy = iy0 + r * g.dh;
+        const bool in = win && iy >= 0 && iy < g.H;
+#pragma unroll
+        for (int c = 0; c < C_; ++c) {
+          const int k = r * C_ + c;
+          const uint32_t v = in ? (uint32_t)__ldg(img + c * plane + (long long)iy * g.W) : zp;
+          words[k >> 2] |= v << (8 * (k & 3));
+        }
+      }
+    } else {
+      int k = 0;
+      for (int r = 0; r < KH; ++r) {
+        const int iy = iy0 + r * g.dh;
+        const bool in = win && iy >= 0 && iy < g.H;
+        for (int c = 0; c < C; ++c, ++k) {
+          const uint32_t v = in ? (uint32_t)__ldg(img + c * plane + (long long)iy * g.W) : zp;
+#pragma unroll
+          for (int i = 0; i < CP / 4; ++i)
+            if ((k >> 2) == i) words[i] |= v << (8 * (k & 3));
+        }
+      }
+    }
+    uint4* dst = (uint4*)(y + idx * CP);
+    dst[0] = make_uint4(words[0], words[1], words[2], words[3]);
+    dst[1] = make_uint4(words[4], words[5], words[6], words[7]);
+  }
+}
+
+void launch_unfold_rows_nchw(const void* x, void* y, const ConvGeom& g, cudaStream_t s) {
+  const long long total = (long long)g.N * g.OH * (g.W + g.pl + g.pr);
+  if (total == 0) return;
+  const int nb = blocks_for(total, 256);
+  const uint8_t* xi = (const uint8_t*)x;
+  uint8_t* yo = (uint8_t*)y;
+  if (g.C == 3 && g.KH == 7) unfold_rows_nchw_kernel<3, 7><<<nb, 256, 0, s>>>(xi, yo, g);
+  else if (g.C == 3 && g.KH == 3) unfold_rows_nchw_kernel<3, 3><<<nb, 256, 0, s>>>(xi, yo, g);
+  else if (g.C == 1 && g.KH == 5) unfold_rows_nchw_kernel<1, 5><<<nb, 256, 0, s>>>(xi, yo, g);
+  else if (g.C == 1 && g.KH == 3) unfold_rows_nchw_kernel<1, 3><<<nb, 256, 0, s>>>(xi, yo, g);
+  else unfold_rows_nchw_kernel<0, 0><<<nb, 256, 0, s>>>(xi, yo, g);
+  ++g_launches;
+}
+
 void launch_im2col(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream_t s) {
   const long long M = (long long)g.N * g.OH * g.OW;
   const long long total = (g.C & 15) == 0 ? M * (Kp >> 4) : M * Kp;

@@ -65,6 +65,21 @@ static bool make_tmap_3d(CUtensorMap* tm, const void* base, long long k, long lo
   return r == CUDA_SUCCESS;
 }
 
+// [outer][rows][k] uint8 map with explicit byte strides: stride_row may be SMALLER than k (overlapping rows)
+static bool make_tmap_rows(CUtensorMap* tm, const void* base, long long k, long long rows, long long outer,
+                           long long stride_row, long long stride_outer, int box_rows, int bk) {
+  EncodeTiledFn fn = encode_tiled();
+  if (!fn || (stride_row & 15) || (stride_outer & 15)) return false;
+  cuuint64_t dims[3] = {(cuuint64_t)k, (cuuint64_t)rows, (cuuint64_t)outer};
+  cuuint64_t strides[2] = {(cuuint64_t)stride_row, (cuuint64_t)stride_outer};
+  cuuint32_t box[3] = {(cuuint32_t)bk, (cuuint32_t)box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(bk), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
 // IM2COL-mode map over the NHWC activation tensor {C, W, H, N}: the TMA unit walks 128 consecutive output
 // pixels (q fastest, then p, then n) starting at the base pixel given to the instruction, stepping by the
 // convolution stride inside the bounding box [lower corner, dim + upper corner); the filter tap is an
@@ -128,7 +143,15 @@ int launch_tc(const TcArgs& a, cudaStream_t s) {
   if (const char* d = getenv("TKB_DBG")) p.dbg = atoi(d);
   p.delta = a.delta; p.cls_h = a.cls_h; p.cls_w = a.cls_w; p.ncls_w = a.ncls_w;
   int bk;
-  if (a.implicit) {
+  if (a.implicit == 2) {  // windowed rows over the unfolded tensor X3 (see launch_unfold_rows_nchw)
+    const ConvGeom& g = a.g;
+    if (a.K != g.KW * 32 || a.M != g.N * g.OH * g.OW) return -1;
+    bk = a.K >= 128 ? 128 : (a.K > 32 ? 64 : 32);
+    p.win = 1;
+    p.win_rows = g.N * g.OH;
+    p.win_qt = (g.OW + BM - 1) / BM;
+    p.OW = g.OW; p.OH = g.OH;
+  } else if (a.implicit) {
     const ConvGeom& g = a.g;
     if (!tc_implicit_conv_supported(g)) return -1;
     bk = g.C % 128 == 0 ? 128 : (g.C % 64 == 0 ? 64 : 32);
@@ -143,10 +166,14 @@ int launch_tc(const TcArgs& a, cudaStream_t s) {
   const uint32_t layout = bk == 128 ? 2u : (bk == 64 ? 4u : 6u);
   p.desc_hi = (uint32_t)(smem_desc(0, 16, 8 * bk, layout) >> 32);
   p.idesc = ((a.a_dtype == kI8 ? 1u : 0u) << 7) | ((a.w_dtype == kI8 ? 1u : 0u) << 10);
-  const long long mtiles = (a.M + BM - 1) / BM;
+  const long long mtiles = p.win ? (long long)p.win_rows * p.win_qt : (a.M + BM - 1) / BM;
   const int bn = pick_bn(mtiles * a.B, a.N);
   CUtensorMap ta, tb;
-  if (a.implicit) {
+  if (a.implicit == 2) {
+    const ConvGeom& g = a.g;
+    const long long wp = g.W + g.pl + g.pr;
+    if (!make_tmap_rows(&ta, a.a, a.K, g.OW, (long long)g.N * g.OH, (long long)g.sw * 32, wp * 32, BM, bk)) return -1;
+  } else if (a.implicit) {
     if (!make_tmap_im2col(&ta, a.a, a.g, bk)) return -1;
   } else {
     if (!make_tmap_3d(&ta, a.a, a.K, a.M, a.B, BM, bk)) return -1;

@@ -788,13 +788,33 @@ static void plan_conv(Planner& P, int nid, bool composite) {
                      (g.zp_a == 0 || ci.bias_eid < 0) && M >= 1;
   const bool force_tc = P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit";
   const bool use_tc = tc_ok && (force_tc || M * g.O >= 4096);
-  const bool want_implicit = use_tc && !direct && P.rt->conv_impl != "tc_explicit" && tc_implicit_conv_supported(g) &&
-                             g.KH <= 63 && g.KW <= 63;
-  // Explicit im2col of a tensor that still lives in its logical NCHW form (the network stem): gather from
-  // NCHW directly instead of permuting to channels-last first.
-  const bool from_nchw = use_tc && !direct && !want_implicit && phys == kNHWC && P.has(x_eid, kLogical) &&
+  // "Kernel view" of the convolution.  A few-channel convolution whose input still lives in logical NCHW
+  // form (the network stem) is rewritten as a 1 x KW convolution over the vertically unfolded tensor
+  // X3[n][p][w][r*C + c] (32 bytes per pixel, launch_unfold_rows_nchw): same integers, but addressable by the
+  // TMA im2col path and 2.4x fewer bytes than an explicit im2col matrix.
+  std::vector<uint8_t> wk;
+  int Cgk = Cg, Kk = K;
+  const bool unfold = use_tc && !direct && P.rt->conv_impl != "tc_explicit" && g.groups == 1 && phys == kNHWC &&
+                      P.has(x_eid, kLogical) && !P.has(x_eid, kNHWC) && !X.nhwc_is_noop() && (g.C % 32) != 0 &&
+                      g.C * g.KH <= 32 && g.KW <= 63 && g.dw == 1;
+  if (unfold) {
+    Cgk = 32; Kk = g.KW * 32;
+    wk.assign((size_t)g.O * Kk, 0);
+    for (int o = 0; o < g.O; ++o)
+      for (int r = 0; r < g.KH; ++r)
+        for (int x = 0; x < g.KW; ++x)
+          for (int c = 0; c < Cg; ++c)
+            wk[((size_t)o * g.KW + x) * 32 + r * Cg + c] = w_ohwi[(((size_t)o * g.KH + r) * g.KW + x) * Cg + c];
+  } else {
+    wk = w_ohwi;
+  }
+  const bool want_implicit = use_tc && !direct && !unfold && P.rt->conv_impl != "tc_explicit" &&
+                             tc_implicit_conv_supported(g) && g.KH <= 63 && g.KW <= 63;
+  // Explicit im2col of a tensor that still lives in its logical NCHW form: gather from NCHW directly instead
+  // of permuting to channels-last first.
+  const bool from_nchw = use_tc && !direct && !want_implicit && !unfold && phys == kNHWC && P.has(x_eid, kLogical) &&
                          !P.has(x_eid, kNHWC) && !X.nhwc_is_noop() && g.KH <= 255 && g.KW <= 255;
-  P.need(x_eid, from_nchw ? kLogical : phys);
+  P.need(x_eid, (from_nchw || unfold) ? kLogical : phys);
   if (ci.sum_eid >= 0) P.need(ci.sum_eid, phys);
   if (ci.bias_eid >= 0) P.need(ci.bias_eid, kLogical);
   P.produce(y_eid, phys);
@@ -809,19 +829,20 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     // activation tensor through an im2col-mode TMA map (implicit GEMM), (3) an explicit im2col matrix for
     // channel counts TMA cannot address (C % 32 != 0, e.g. the 3-channel stem).
     BorderPlan bp;
-    const bool implicit = want_implicit && border_plan(g, w_ohwi, Cg, &bp);
-    const int Kp = (direct || implicit) ? K : (K + 15) / 16 * 16;
+    const bool implicit = want_implicit && border_plan(g, wk, Cgk, &bp);
+    const int K = Kk;  // from here on: the kernel view
+    const int Kp = (direct || implicit || unfold) ? K : (K + 15) / 16 * 16;
     std::vector<uint8_t> wp((size_t)g.O * Kp, 0);
     std::vector<int32_t> corr(g.O, 0);
     for (int o = 0; o < g.O; ++o) {
       if (from_nchw) {  // K ordered (c, r, s) to match launch_im2col_nchw
         for (int c = 0; c < Cg; ++c)
-          for (int t = 0; t < g.KH * g.KW; ++t) wp[(size_t)o * Kp + (size_t)c * g.KH * g.KW + t] = w_ohwi[((size_t)o * g.KH * g.KW + t) * Cg + c];
+          for (int t = 0; t < g.KH * g.KW; ++t) wp[(size_t)o * Kp + (size_t)c * g.KH * g.KW + t] = wk[((size_t)o * g.KH * g.KW + t) * Cg + c];
       } else {
-        memcpy(&wp[(size_t)o * Kp], &w_ohwi[(size_t)o * K], K);
+        memcpy(&wp[(size_t)o * Kp], &wk[(size_t)o * K], K);
       }
       long long sum = 0;
-      for (int k = 0; k < K; ++k) sum += g.w_dtype == kU8 ? (int)w_ohwi[(size_t)o * K + k] : (int)(int8_t)w_ohwi[(size_t)o * K + k];
+      for (int k = 0; k < K; ++k) sum += g.w_dtype == kU8 ? (int)wk[(size_t)o * K + k] : (int)(int8_t)wk[(size_t)o * K + k];
       corr[o] = (int32_t)(0u - (uint32_t)g.zp_a * (uint32_t)(int32_t)sum);  // -zp_a * sum_k W[o,k]  (int32 ring)
     }
     void* wdev = P.dev_upload(wp.data(), wp.size());
@@ -837,7 +858,7 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     ta.w = wdev;
     ta.B = 1; ta.M = (int)M; ta.N = g.O; ta.K = Kp;
     ta.a_dtype = g.a_dtype; ta.w_dtype = g.w_dtype;
-    ta.implicit = implicit ? 1 : 0;
+    ta.implicit = unfold ? 2 : (implicit ? 1 : 0);
     ta.g = g;
     if (implicit && !bp.delta.empty()) {
       ta.delta = (const int32_t*)P.dev_upload(bp.delta.data(), bp.delta.size() * 4);
@@ -846,19 +867,25 @@ static void plan_conv(Planner& P, int nid, bool composite) {
       ta.ncls_w = bp.nw;
     }
     if (composite && !ci.float_mode)
-      build_fast_epi(P, ci, bias2, abs_row_sums(w_ohwi.data(), g.O, K, g.w_dtype), g.O, Y.dtype, &ta.f);
+      build_fast_epi(P, ci, bias2, abs_row_sums(wk.data(), g.O, K, g.w_dtype), g.O, Y.dtype, &ta.f);
     long long scratch_off = -1;
-    if (!direct && !implicit) scratch_off = P.arena_alloc(M * Kp);
+    if (unfold) scratch_off = P.arena_alloc((long long)g.N * g.OH * (g.W + g.pl + g.pr) * 32 + 256);
+    else if (!direct && !implicit) scratch_off = P.arena_alloc(M * Kp);
     snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 %s M=%lld N=%d K=%d (%dx%d s%d p%d) epi=%s", n.name.c_str(),
-             direct ? "GEMM" : (implicit ? "implicit-GEMM conv (TMA im2col)" : (from_nchw ? "GEMM + explicit im2col from NCHW" : "GEMM + explicit im2col")), M, g.O, Kp, g.KH,
+             direct ? "GEMM" : (unfold ? "conv as windowed-row GEMM over vertically unfolded NCHW input" : implicit ? "implicit-GEMM conv (TMA im2col)" : (from_nchw ? "GEMM + explicit im2col from NCHW" : "GEMM + explicit im2col")), M, g.O, Kp, g.KH,
              g.KW, g.sh, g.pt, ta.f.enabled ? "fast" : (epi.mode == kEpiInt ? "int" : (epi.mode == kEpiFloat ? "float" : "raw")));
     P.add_step(desc, [=](RunCtx& c) {
       TcArgs t = ta;
       t.e = epi;
       if (bias_eid >= 0) t.e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
       if (sum_eid >= 0) t.e.sum = c.ptr(sum_eid, phys);
-      t.a = c.ptr(x_eid, from_nchw ? kLogical : phys);
-      if (!direct && !implicit) {
+      t.a = c.ptr(x_eid, (from_nchw || unfold) ? kLogical : phys);
+      if (unfold) {
+        void* x3 = c.ws->arena + scratch_off;
+        launch_unfold_rows_nchw(t.a, x3, g, c.s);
+        t.a = x3;
+      }
+      if (!direct && !implicit && !unfold) {
         void* col = c.ws->arena + scratch_off;
         if (from_nchw) launch_im2col_nchw(t.a, col, g, Kp, c.s);
         else launch_im2col(t.a, col, g, Kp, c.s);

@@ -31,6 +31,8 @@ struct TcKernelParams {
   uint32_t desc_hi;       // upper 32 bits of the UMMA smem descriptors (SBO, version, swizzle mode)
   // implicit convolution
   int implicit, C, KH, KW, OH, OW, sh, sw, dh, dw, pt, pl;
+  // windowed rows (A = overlapping windows of an unfolded tensor): tile = 128 pixels of ONE output row
+  int win, win_rows, win_qt;  // rows = N*OH, qt = ceil(OW / 128)
   // zero-point correction of taps that fall into the padding (see runtime.cu border_classes())
   const int32_t* delta;   // [n_classes][N] or nullptr
   const uint8_t* cls_h;   // [OH]
@@ -195,8 +197,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
   uint32_t* tmem_ptr = (uint32_t*)(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int mtiles = (p.M + BM - 1) / BM, ntiles = (p.N + BN - 1) / BN;
-  const long long total_tiles = (long long)mtiles * ntiles * p.batches;
+  const int mtiles = p.win ? p.win_rows * p.win_qt : (p.M + BM - 1) / BM, ntiles = (p.N + BN - 1) / BN;
+  const long long total_tiles = (p.dbg & 8) ? 0 : (long long)mtiles * ntiles * p.batches;  // dbg 8: launch + prologue + teardown only
   const int cchunks = p.implicit ? p.C / p.bk : 0;
   const int num_kb = p.implicit ? p.KH * p.KW * cchunks : (p.K + p.bk - 1) / p.bk;
 
@@ -248,6 +250,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
               if (p.implicit) {
                 tma_load_im2col_4d(sa, &tmA, &full[st], cc * p.bk, cw, chh, cn, (uint16_t)(s * p.dw), (uint16_t)(r * p.dh));
                 if (++cc == cchunks) { cc = 0; if (++s == p.KW) { s = 0; ++r; } }
+              } else if (p.win) {
+                tma_load_3d(sa, &tmA, &full[st], kb * p.bk, (mt % p.win_qt) * BM, mt / p.win_qt);
               } else {
                 tma_load_3d(sa, &tmA, &full[st], kb * p.bk, m0, b);
               }
@@ -321,8 +325,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         epi_bar_sync();
         tab_n0 = n0;
       }
-      const int row = m0 + q * 32 + lane;
-      const bool row_valid = row < p.M;
+      int row = m0 + q * 32 + lane;
+      bool row_valid = row < p.M;
+      if (p.win) {
+        const int qp = (mt % p.win_qt) * BM + q * 32 + lane;
+        row_valid = qp < p.OW;
+        row = (mt / p.win_qt) * p.OW + qp;
+      }
       const long long row_off = ((long long)b * p.M + row) * p.N;
       const int32_t* drow = nullptr;
       if (p.delta != nullptr && row_valid) {
@@ -418,7 +427,8 @@ static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams
       return -1;
     attr_set = true;
   }
-  const long long tiles = (long long)((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN) * p.batches;
+  const long long mt_host = p.win ? (long long)p.win_rows * p.win_qt : (p.M + BM - 1) / BM;
+  const long long tiles = mt_host * ((p.N + BN - 1) / BN) * p.batches;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
   tc_gemm_kernel<BN, MODE><<<grid, TC_THREADS, smem, s>>>(ta, tb, p);

@@ -46,6 +46,8 @@ void launch_permute4(const void* x, void* y, int elem, const long long* out_shap
                      cudaStream_t s);
 // tiled 8-bit channels-last -> NCHW transpose; returns false (nothing launched) if the shape needs launch_permute4
 bool launch_nhwc_to_nchw8(const void* x, void* y, long long N, long long HW, long long C, cudaStream_t s);
+// [N][A][B] -> [N][B][A] for 1/2/4-byte elements (32 x 32 tiles); false if nothing could be launched
+bool launch_transpose_tile(const void* x, void* y, int elem, long long N, long long A, long long B, cudaStream_t s);
 // constant pad of a dense tensor up to rank 4 (shape padded to 4 dims)
 void launch_pad4(const void* x, void* y, int elem, const long long* in_shape, const long long* pad_before,
                  const long long* out_shape, int32_t value, cudaStream_t s);

@@ -415,6 +415,38 @@ bool launch_nhwc_to_nchw8(const void* x, void* y, long long N, long long HW, lon
   return true;
 }
 
+// Generic [N][A][B] -> [N][B][A] transpose of 1/2/4-byte elements through a padded 32 x 32 tile (element-wise
+// accesses, both sides coalesced).  Fallback of nhwc_to_nchw8 for odd spatial sizes and wider dtypes.
+template <typename T>
+__global__ void __launch_bounds__(256) transpose_tile_kernel(const T* __restrict__ x, T* __restrict__ y, int A, int B) {
+  __shared__ T tile[32][33];
+  const long long base = (long long)blockIdx.z * A * B;
+  const int a0 = blockIdx.x * 32, b0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int a = a0 + ty + 8 * i, b = b0 + tx;
+    if (a < A && b < B) tile[ty + 8 * i][tx] = x[base + (long long)a * B + b];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int b = b0 + ty + 8 * i, a = a0 + tx;
+    if (a < A && b < B) y[base + (long long)b * A + a] = tile[tx][ty + 8 * i];
+  }
+}
+
+bool launch_transpose_tile(const void* x, void* y, int elem, long long N, long long A, long long B, cudaStream_t s) {
+  if (N > 65535 || (B + 31) / 32 > 65535 || N * A * B == 0) return N * A * B == 0;
+  dim3 grid((unsigned)((A + 31) / 32), (unsigned)((B + 31) / 32), (unsigned)N);
+  if (elem == 1) transpose_tile_kernel<uint8_t><<<grid, 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, (int)A, (int)B);
+  else if (elem == 2) transpose_tile_kernel<uint16_t><<<grid, 256, 0, s>>>((const uint16_t*)x, (uint16_t*)y, (int)A, (int)B);
+  else if (elem == 4) transpose_tile_kernel<uint32_t><<<grid, 256, 0, s>>>((const uint32_t*)x, (uint32_t*)y, (int)A, (int)B);
+  else return false;
+  ++g_launches;
+  return true;
+}
+
 struct Perm4 { long long shape[4], istr[4]; };
 
 // Tiled transpose of the two dims that swap fastest-varying roles would be the speed-of-light

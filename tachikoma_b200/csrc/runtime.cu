@@ -268,6 +268,10 @@ struct Planner {
     add_step(std::string("layout ") + (phys == kNHWC ? "NCHW->NHWC" : "NHWC->NCHW") + " e" + std::to_string(r),
              [=](RunCtx& c) {
                if (phys == kLogical && elem == 1 && launch_nhwc_to_nchw8(c.ptr(r, other), c.ptr(r, phys), N, H * W, C, c.s)) return;
+               // NHWC -> NCHW is [N][HW][C] -> [N][C][HW]; NCHW -> NHWC is [N][C][HW] -> [N][HW][C]
+               if (phys == kLogical ? launch_transpose_tile(c.ptr(r, other), c.ptr(r, phys), elem, N, H * W, C, c.s)
+                                    : launch_transpose_tile(c.ptr(r, other), c.ptr(r, phys), elem, N, C, H * W, c.s))
+                 return;
                launch_permute4(c.ptr(r, other), c.ptr(r, phys), elem, oshape.data(), istr.data(), c.s);
              });
   }
@@ -1410,8 +1414,10 @@ static void trace_node(RunCtx& c, size_t lo, size_t hi) {
     const Entry& e = rt->ent[r];
     const long long N = e.shape[0], C = e.shape[1], H = e.shape[2], W = e.shape[3];
     long long oshape[4] = {N, C, H, W}, istr[4] = {H * W * C, 1, W * C, C};
-    if (dtype_size(e.dtype) != 1 || !launch_nhwc_to_nchw8(c.ptr(r, kNHWC), c.ws->trace_ring + rt->trace_ring_off[i], N, H * W, C, c.s))
-      launch_permute4(c.ptr(r, kNHWC), c.ws->trace_ring + rt->trace_ring_off[i], dtype_size(e.dtype), oshape, istr, c.s);
+    void* dstp = c.ws->trace_ring + rt->trace_ring_off[i];
+    if (dtype_size(e.dtype) == 1 && launch_nhwc_to_nchw8(c.ptr(r, kNHWC), dstp, N, H * W, C, c.s)) continue;
+    if (launch_transpose_tile(c.ptr(r, kNHWC), dstp, dtype_size(e.dtype), N, H * W, C, c.s)) continue;
+    launch_permute4(c.ptr(r, kNHWC), c.ws->trace_ring + rt->trace_ring_off[i], dtype_size(e.dtype), oshape, istr, c.s);
   }
   if (rt->trace_mode < 2) return;
   CUDA_OK(cudaEventRecord(c.ws->ev, c.s));

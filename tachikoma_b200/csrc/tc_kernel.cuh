@@ -3,6 +3,7 @@
 // convolution kernel.  See kernels_tc.cu for the design notes.
 #pragma once
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "kernels.h"
@@ -202,6 +203,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
   const int cchunks = p.implicit ? p.C / p.bk : 0;
   const int num_kb = p.implicit ? p.KH * p.KW * cchunks : (p.K + p.bk - 1) / p.bk;
 
+  // Programmatic dependent launch: let the next kernel of the stream start its own prologue as soon as SMs
+  // free up; everything this kernel reads or writes in global memory comes after griddepcontrol.wait below.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
@@ -214,6 +218,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  // wait for the preceding kernel(s) of the stream to complete and flush (no-op without the PDL launch attribute)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 
   // Producer and MMA warps run their loops with the whole warp converged (all lanes poll the mbarriers) and
   // guard only the issuing instructions with elect.sync: the compiler then emits the uniform-datapath
@@ -431,7 +437,17 @@ static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams
   const long long tiles = mt_host * ((p.N + BN - 1) / BN) * p.batches;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
-  tc_gemm_kernel<BN, MODE><<<grid, TC_THREADS, smem, s>>>(ta, tb, p);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(TC_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = getenv("TKB_NO_PDL") ? 0 : 1;
+  if (cudaLaunchKernelEx(&cfg, tc_gemm_kernel<BN, MODE>, ta, tb, p) != cudaSuccess) return -1;
   ++g_launches;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

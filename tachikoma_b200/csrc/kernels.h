@@ -79,7 +79,15 @@ struct TcArgs {
   int ncls_w;
   EpiParams e;
   FastEpi f;
+  // Constant weights may be handed over pre-tiled ("packed"): for every (n-tile, k-block) the BN x bk tile in
+  // its final swizzled shared-memory image, so that the kernel fetches it with one bulk copy instead of one
+  // TMA request per row.  w_packed != 0: `w` points at tc_pack_weights() output made for (pack_bn, pack_bk).
+  int w_packed, pack_bn, pack_bk;
 };
+// Tile configuration launch_tc will use for this problem (bn: N tile, bk: bytes of K per k-block).
+void tc_tile_config(const TcArgs& a, int* bn, int* bk);
+// [N][K] K-major weights -> packed tiles for (bn, bk); returns the byte size (dst may be nullptr to query).
+size_t tc_pack_weights(const uint8_t* w, int N, int K, int bn, int bk, uint8_t* dst);
 // Requirements of the plain-GEMM form: K % 16 == 0, pointers 16B aligned.
 bool tc_gemm_supported(int M, int N, int K);
 // Requirements of the implicit form: groups == 1, C % 32 == 0, TMA corner / offset ranges.

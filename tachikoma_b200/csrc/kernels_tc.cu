@@ -130,6 +130,42 @@ static int pick_bn(long long mtiles, int N) {
   return best;
 }
 
+static int pick_bk(const TcArgs& a) {
+  if (a.implicit == 1) return a.g.C % 128 == 0 ? 128 : (a.g.C % 64 == 0 ? 64 : 32);
+  return a.K >= 128 ? 128 : (a.K > 32 ? 64 : 32);
+}
+
+void tc_tile_config(const TcArgs& a, int* bn, int* bk) {
+  const long long mtiles = a.implicit == 2 ? (long long)a.g.N * a.g.OH * ((a.g.OW + BM - 1) / BM) : (a.M + BM - 1) / BM;
+  *bn = pick_bn(mtiles * a.B, a.N);
+  *bk = pick_bk(a);
+}
+
+// 16-byte chunk c of row n goes to chunk c ^ f(n) (the 128 / 64 / 32-byte TMA + UMMA swizzle patterns,
+// Swizzle<3,4,3> / <2,4,3> / <1,4,3> over byte offsets with a row pitch of bk bytes).
+size_t tc_pack_weights(const uint8_t* w, int N, int K, int bn, int bk, uint8_t* dst) {
+  const int ntiles = (N + bn - 1) / bn, num_kb = (K + bk - 1) / bk;
+  const size_t tile = (size_t)bn * bk, total = tile * ntiles * num_kb;
+  if (!dst) return total;
+  memset(dst, 0, total);
+  for (int nt = 0; nt < ntiles; ++nt)
+    for (int kb = 0; kb < num_kb; ++kb) {
+      uint8_t* d = dst + ((size_t)nt * num_kb + kb) * tile;
+      for (int r = 0; r < bn; ++r) {
+        const int n = nt * bn + r;
+        if (n >= N) break;
+        const int x = bk == 128 ? (r & 7) : (bk == 64 ? ((r >> 1) & 3) : ((r >> 2) & 1));
+        for (int c = 0; c < bk / 16; ++c) {
+          const int k0 = kb * bk + c * 16;
+          if (k0 >= K) break;
+          const int len = K - k0 < 16 ? K - k0 : 16;
+          memcpy(d + (size_t)r * bk + ((c ^ x) * 16), w + (size_t)n * K + k0, len);
+        }
+      }
+    }
+  return total;
+}
+
 int launch_tc(const TcArgs& a, cudaStream_t s) {
   if ((((uintptr_t)a.a) | ((uintptr_t)a.w)) & 15) return -1;
   TcKernelParams p;
@@ -142,11 +178,10 @@ int launch_tc(const TcArgs& a, cudaStream_t s) {
   p.f = a.f;
   if (const char* d = getenv("TKB_DBG")) p.dbg = atoi(d);
   p.delta = a.delta; p.cls_h = a.cls_h; p.cls_w = a.cls_w; p.ncls_w = a.ncls_w;
-  int bk;
+  const int bk = pick_bk(a);
   if (a.implicit == 2) {  // windowed rows over the unfolded tensor X3 (see launch_unfold_rows_nchw)
     const ConvGeom& g = a.g;
     if (a.K != g.KW * 32 || a.M != g.N * g.OH * g.OW) return -1;
-    bk = a.K >= 128 ? 128 : (a.K > 32 ? 64 : 32);
     p.win = 1;
     p.win_rows = g.N * g.OH;
     p.win_qt = (g.OW + BM - 1) / BM;
@@ -154,20 +189,22 @@ int launch_tc(const TcArgs& a, cudaStream_t s) {
   } else if (a.implicit) {
     const ConvGeom& g = a.g;
     if (!tc_implicit_conv_supported(g)) return -1;
-    bk = g.C % 128 == 0 ? 128 : (g.C % 64 == 0 ? 64 : 32);
     p.implicit = 1;
     p.C = g.C; p.KH = g.KH; p.KW = g.KW; p.OH = g.OH; p.OW = g.OW;
     p.sh = g.sh; p.sw = g.sw; p.dh = g.dh; p.dw = g.dw; p.pt = g.pt; p.pl = g.pl;
   } else {
     if (!tc_gemm_supported(a.M, a.N, a.K)) return -1;
-    bk = a.K >= 128 ? 128 : (a.K > 32 ? 64 : 32);
   }
   p.bk = bk;
   const uint32_t layout = bk == 128 ? 2u : (bk == 64 ? 4u : 6u);
   p.desc_hi = (uint32_t)(smem_desc(0, 16, 8 * bk, layout) >> 32);
   p.idesc = ((a.a_dtype == kI8 ? 1u : 0u) << 7) | ((a.w_dtype == kI8 ? 1u : 0u) << 10);
-  const long long mtiles = p.win ? (long long)p.win_rows * p.win_qt : (a.M + BM - 1) / BM;
-  const int bn = pick_bn(mtiles * a.B, a.N);
+  int bn, bk2;
+  tc_tile_config(a, &bn, &bk2);
+  if (a.w_packed) {
+    if (a.pack_bn != bn || a.pack_bk != bk || a.w_batched) return -1;
+    p.wpack = (const uint8_t*)a.w;
+  }
   CUtensorMap ta, tb;
   if (a.implicit == 2) {
     const ConvGeom& g = a.g;
@@ -178,7 +215,8 @@ int launch_tc(const TcArgs& a, cudaStream_t s) {
   } else {
     if (!make_tmap_3d(&ta, a.a, a.K, a.M, a.B, BM, bk)) return -1;
   }
-  if (!make_tmap_3d(&tb, a.w, a.K, a.N, a.w_batched ? a.B : 1, bn, bk)) return -1;
+  if (a.w_packed) tb = ta;  // never dereferenced: B tiles come from p.wpack with bulk copies
+  else if (!make_tmap_3d(&tb, a.w, a.K, a.N, a.w_batched ? a.B : 1, bn, bk)) return -1;
   int mode = kModeGeneric;
   if (a.f.enabled) mode = a.f.has_sum ? kModeFastSum : kModeFast;
   else if (a.e.mode == kEpiRaw) mode = kModeRaw;
@@ -205,14 +243,15 @@ __global__ void __launch_bounds__(128) probe_i8_kernel(int iters, uint32_t idesc
   __shared__ uint32_t tmem_ptr;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < (BM * 128 + 256 * 128) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0x01010101u;
-  if (threadIdx.x == 0) { mbar_init(&done, 1); mbar_init(&kb_bar[0], 1); mbar_init(&kb_bar[1], 1); fence_barrier_init(); }
+  if (threadIdx.x == 0) { mbar_init(&done, (commit_every & 16) ? 2 : 1); mbar_init(&kb_bar[0], 1); mbar_init(&kb_bar[1], 1); fence_barrier_init(); }
   if (warp == 0) tmem_alloc<512>(&tmem_ptr);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_ptr;
-  if (warp == 0) {
+  const int issuers = (commit_every & 16) ? 2 : 1;
+  if (warp < issuers) {
     // the whole warp runs the loop; one elected lane issues (elect.sync lets the compiler emit the
     // uniform-datapath UTCIMMA / UTCBAR directly instead of a per-active-thread serialisation loop)
     const uint32_t a_lo = ((smem_u32(smem) >> 4) & 0x3FFF) | (1u << 16);
@@ -227,7 +266,7 @@ __global__ void __launch_bounds__(128) probe_i8_kernel(int iters, uint32_t idesc
       if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-          mma_i8(tmem_base + (it & 1) * 256, ((uint64_t)hi << 32) | (a_lo + 2 * k), ((uint64_t)hi << 32) | (b_lo + 2 * k), idesc, 1);
+          mma_i8(tmem_base + (issuers == 2 ? warp * 256 : (it & 1) * 256), ((uint64_t)hi << 32) | (a_lo + 2 * k), ((uint64_t)hi << 32) | (b_lo + 2 * k), idesc, 1);
         if (commit_every & 1) tc_commit(&kb_bar[it & 1]);
       }
       __syncwarp();
@@ -263,7 +302,7 @@ int probe_int8_shape(int iters, int n, int commit_every, double* tops, cudaStrea
   cudaEventElapsedTime(&ms, e0, e1);
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
-  const double ops = 2.0 * 128 * n * 32 * 4.0 * (double)iters * sms;
+  const double ops = 2.0 * 128 * n * 32 * 4.0 * (double)iters * sms * ((commit_every & 16) ? 2 : 1);
   *tops = ops / (ms * 1e-3) / 1e12;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

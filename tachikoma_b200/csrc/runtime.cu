@@ -849,7 +849,6 @@ static void plan_conv(Planner& P, int nid, bool composite) {
       for (int k = 0; k < K; ++k) sum += g.w_dtype == kU8 ? (int)wk[(size_t)o * K + k] : (int)(int8_t)wk[(size_t)o * K + k];
       corr[o] = (int32_t)(0u - (uint32_t)g.zp_a * (uint32_t)(int32_t)sum);  // -zp_a * sum_k W[o,k]  (int32 ring)
     }
-    void* wdev = P.dev_upload(wp.data(), wp.size());
     std::vector<int32_t> bias2;
     if (!ci.float_mode) {
       if (ci.has_const_bias || g.zp_a != 0) {
@@ -859,11 +858,17 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     }
     TcArgs ta;
     memset(&ta, 0, sizeof(ta));
-    ta.w = wdev;
     ta.B = 1; ta.M = (int)M; ta.N = g.O; ta.K = Kp;
     ta.a_dtype = g.a_dtype; ta.w_dtype = g.w_dtype;
     ta.implicit = unfold ? 2 : (implicit ? 1 : 0);
     ta.g = g;
+    {  // constant weights: pre-tile into the swizzled shared-memory image (one bulk copy per tile at run time)
+      tc_tile_config(ta, &ta.pack_bn, &ta.pack_bk);
+      std::vector<uint8_t> packed(tc_pack_weights(wp.data(), g.O, Kp, ta.pack_bn, ta.pack_bk, nullptr));
+      tc_pack_weights(wp.data(), g.O, Kp, ta.pack_bn, ta.pack_bk, packed.data());
+      ta.w = P.dev_upload(packed.data(), packed.size());
+      ta.w_packed = 1;
+    }
     if (implicit && !bp.delta.empty()) {
       ta.delta = (const int32_t*)P.dev_upload(bp.delta.data(), bp.delta.size() * 4);
       ta.cls_h = (const uint8_t*)P.dev_upload(bp.cls_h.data(), bp.cls_h.size());
@@ -973,6 +978,14 @@ static void plan_dense(Planner& P, int nid, bool composite) {
     ta.a_dtype = xd; ta.w_dtype = wd;
     if (composite && !ci.float_mode && Wt.is_const)
       build_fast_epi(P, ci, bias2, abs_row_sums(Wt.host.data(), N, K, wd), N, Y.dtype, &ta.f);
+    const void* wpacked = nullptr;
+    if (Wt.is_const) {
+      tc_tile_config(ta, &ta.pack_bn, &ta.pack_bk);
+      std::vector<uint8_t> packed(tc_pack_weights(Wt.host.data(), N, K, ta.pack_bn, ta.pack_bk, nullptr));
+      tc_pack_weights(Wt.host.data(), N, K, ta.pack_bn, ta.pack_bk, packed.data());
+      wpacked = P.dev_upload(packed.data(), packed.size());
+      ta.w_packed = 1;
+    }
     snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 GEMM M=%lld N=%d K=%d epi=%s", n.name.c_str(), M, N, K,
              ta.f.enabled ? "fast" : (epi.mode == kEpiInt ? "int" : (epi.mode == kEpiFloat ? "float" : "raw")));
     P.add_step(desc, [=](RunCtx& c) {
@@ -981,7 +994,7 @@ static void plan_dense(Planner& P, int nid, bool composite) {
       if (bias_eid >= 0) t.e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
       if (sum_eid >= 0) t.e.sum = c.ptr(sum_eid, kLogical);
       t.a = c.ptr(x_eid, kLogical);
-      t.w = c.ptr(w_eid, kLogical);
+      t.w = wpacked ? wpacked : c.ptr(w_eid, kLogical);
       t.y = c.ptr(y_eid, kLogical);
       c.tc_mark();
       if (launch_tc(t, c.s) != 0) fail("tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));

@@ -39,6 +39,7 @@ struct TcKernelParams {
   const uint8_t* cls_h;   // [OH]
   const uint8_t* cls_w;   // [OW]
   int ncls_w;
+  const uint8_t* wpack;   // packed weight tiles (tc_pack_weights) or nullptr: B comes through tmB
   int dbg;                // timing experiments only (TKB_DBG): 1 = no epilogue work, 2 = no B loads, 4 = no A loads
   EpiParams e;            // generic epilogue (any rounding / compute dtype / float mode / raw int32)
   FastEpi f;              // host-folded fixed-point epilogue (default QNN configuration)
@@ -262,7 +263,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                 tma_load_3d(sa, &tmA, &full[st], kb * p.bk, m0, b);
               }
             }
-            if (ld_b) tma_load_3d(sa + a_bytes, &tmB, &full[st], kb * p.bk, n0, p.w_batched ? b : 0);
+            if (ld_b) {
+              if (p.wpack) bulk_load(sa + a_bytes, p.wpack + ((size_t)nt * num_kb + kb) * b_bytes, (uint32_t)b_bytes, &full[st]);
+              else tma_load_3d(sa + a_bytes, &tmB, &full[st], kb * p.bk, n0, p.w_batched ? b : 0);
+            }
           }
         }
         // the tap / chunk counters live in the elected lane only; every lane needs them for the next group

@@ -216,14 +216,15 @@ def main():
     mod.trace_enable(0)
     mod.set_option("time_tc", "1")
     tc_ms, tc_n = 0.0, 0
-    for _ in range(max(3, args.steps // 4)):
+    runs = max(3, args.steps // 4)
+    for _ in range(runs):
+        RT.spin(3000.0, stream)  # the host queues the whole step while the GPU spins: events see device time only
         mod.run(x_dev, out_dev, stream=stream)
         torch.cuda.synchronize()
         a, b = mod.tc_time()
         tc_ms += a
         tc_n += b
     mod.set_option("time_tc", "0")
-    runs = max(3, args.steps // 4)
     peak_tops = RT.probe_int8_peak(4000)
     achieved_tops = 2.0 * macs * runs / (tc_ms * 1e-3) / 1e12 if tc_ms > 0 else 0.0
 
@@ -256,7 +257,7 @@ def main():
                 "h2d_bytes_per_step": int(x_np.nbytes), "d2h_bytes_per_step": int(trace_d2h + np.prod(out_shape))},
         "gpu_launches": int(launches),
         "roofline": {
-            "bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05.mma kind::i8)", "achieved": achieved_tops,
+            "bound": "tensor", "kernel": "tc_gemm_kernel<BN,MODE> (tcgen05.mma kind::i8, all conv/dense launches of a step)", "achieved": achieved_tops,
             "peak": peak_tops, "unit": "TFLOP/s", "frac": achieved_tops / peak_tops if peak_tops else None, "traffic": None,
             "note": "int8 ops (2*MAC) counted as FLOPs; peak = this run's tcgen05 kind::i8 issue-rate probe "
                     "(MEASURED_PEAKS.json has no int8 entry; 2x its bf16 burst = %.0f)" % (2 * peaks.get("bf16_tflops", 0)),

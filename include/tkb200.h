@@ -117,6 +117,9 @@ int tkb_probe_int8_peak(int iters, double* tops, void* cuda_stream);
 /* Same probe with UMMA N = n (multiple of 16, <= 256) and a tcgen05.commit every `commit_every` groups of 4 MMAs
  * (0 = never): how the issue rate depends on the instruction shape and on per-stage commits. */
 int tkb_probe_int8_shape(int iters, int n, int commit_every, double* tops, void* cuda_stream);
+/* Measurement aid: enqueue a device busy-wait of about `microseconds` on the stream, so that a host can queue a
+ * whole step behind it and per-kernel CUDA events then see device time only. */
+int tkb_spin(double microseconds, void* cuda_stream);
 /* Library build info: "sm_100a;<n kernels>;..." */
 const char* tkb_version(void);
 

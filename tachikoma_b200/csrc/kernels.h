@@ -92,9 +92,15 @@ size_t tc_pack_weights(const uint8_t* w, int N, int K, int bn, int bk, uint8_t* 
 bool tc_gemm_supported(int M, int N, int K);
 // Requirements of the implicit form: groups == 1, C % 32 == 0, TMA corner / offset ranges.
 bool tc_implicit_conv_supported(const ConvGeom& g);
+// halo-reuse convolution kernel (kernels_tc_halo.cu): TcArgs.implicit == 3
+bool tc_halo_supported(const ConvGeom& g, int N);
+void tc_halo_tile_config(const ConvGeom& g, int N, int* bn, int* bk);
+int launch_tc_halo(const TcArgs& a, cudaStream_t s);
 int launch_tc(const TcArgs& a, cudaStream_t s);
 int probe_int8_peak(int iters, double* tops, cudaStream_t s);
 int probe_int8_shape(int iters, int n, int commit_every, double* tops, cudaStream_t s);
+
+void launch_spin(double us, cudaStream_t s);  // device busy-wait (measurement aid)
 
 extern thread_local long long g_launches;  // kernels launched by this thread (summed per handle)
 

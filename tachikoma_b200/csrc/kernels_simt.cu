@@ -447,6 +447,19 @@ bool launch_transpose_tile(const void* x, void* y, int elem, long long N, long l
   return true;
 }
 
+// Busy-wait on the device for about `us` microseconds (one thread).  bench.py queues it in front of a timed
+// step so that the host enqueues the whole step while the GPU is still busy: the CUDA events recorded around
+// every tensor-core launch then measure device time only, not host launch overhead.
+__global__ void spin_kernel(long long ns) {
+  unsigned long long t0, t1;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  do { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1)); } while ((long long)(t1 - t0) < ns);
+}
+void launch_spin(double us, cudaStream_t s) {
+  spin_kernel<<<1, 1, 0, s>>>((long long)(us * 1e3));
+  ++g_launches;
+}
+
 struct Perm4 { long long shape[4], istr[4]; };
 
 // Tiled transpose of the two dims that swap fastest-varying roles would be the speed-of-light

@@ -136,6 +136,7 @@ static int pick_bk(const TcArgs& a) {
 }
 
 void tc_tile_config(const TcArgs& a, int* bn, int* bk) {
+  if (a.implicit == 3) { tc_halo_tile_config(a.g, a.N, bn, bk); return; }
   const long long mtiles = a.implicit == 2 ? (long long)a.g.N * a.g.OH * ((a.g.OW + BM - 1) / BM) : (a.M + BM - 1) / BM;
   *bn = pick_bn(mtiles * a.B, a.N);
   *bk = pick_bk(a);
@@ -167,6 +168,7 @@ size_t tc_pack_weights(const uint8_t* w, int N, int K, int bn, int bk, uint8_t* 
 }
 
 int launch_tc(const TcArgs& a, cudaStream_t s) {
+  if (a.implicit == 3) return launch_tc_halo(a, s);
   if ((((uintptr_t)a.a) | ((uintptr_t)a.w)) & 15) return -1;
   TcKernelParams p;
   memset(&p, 0, sizeof(p));

@@ -790,7 +790,7 @@ static void plan_conv(Planner& P, int nid, bool composite) {
   const bool direct = g.KH == 1 && g.KW == 1 && g.sh == 1 && g.sw == 1 && !(g.pt | g.pl | g.pb | g.pr) && (g.C % 16) == 0;
   const bool tc_ok = P.rt->conv_impl != "simt" && g.groups == 1 && all_zero(ci.zp_w) &&
                      (g.zp_a == 0 || ci.bias_eid < 0) && M >= 1;
-  const bool force_tc = P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit";
+  const bool force_tc = P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col";
   const bool use_tc = tc_ok && (force_tc || M * g.O >= 4096);
   // "Kernel view" of the convolution.  A few-channel convolution whose input still lives in logical NCHW
   // form (the network stem) is rewritten as a 1 x KW convolution over the vertically unfolded tensor
@@ -862,6 +862,10 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     ta.a_dtype = g.a_dtype; ta.w_dtype = g.w_dtype;
     ta.implicit = unfold ? 2 : (implicit ? 1 : 0);
     ta.g = g;
+    if (composite && !ci.float_mode)
+      build_fast_epi(P, ci, bias2, abs_row_sums(wk.data(), g.O, K, g.w_dtype), g.O, Y.dtype, &ta.f);
+    const bool halo = implicit && ta.f.enabled && P.rt->conv_impl != "tc_im2col" && tc_halo_supported(g, g.O);
+    if (halo) ta.implicit = 3;
     {  // constant weights: pre-tile into the swizzled shared-memory image (one bulk copy per tile at run time)
       tc_tile_config(ta, &ta.pack_bn, &ta.pack_bk);
       std::vector<uint8_t> packed(tc_pack_weights(wp.data(), g.O, Kp, ta.pack_bn, ta.pack_bk, nullptr));
@@ -875,13 +879,11 @@ static void plan_conv(Planner& P, int nid, bool composite) {
       ta.cls_w = (const uint8_t*)P.dev_upload(bp.cls_w.data(), bp.cls_w.size());
       ta.ncls_w = bp.nw;
     }
-    if (composite && !ci.float_mode)
-      build_fast_epi(P, ci, bias2, abs_row_sums(wk.data(), g.O, K, g.w_dtype), g.O, Y.dtype, &ta.f);
     long long scratch_off = -1;
     if (unfold) scratch_off = P.arena_alloc((long long)g.N * g.OH * (g.W + g.pl + g.pr) * 32 + 256);
     else if (!direct && !implicit) scratch_off = P.arena_alloc(M * Kp);
     snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 %s M=%lld N=%d K=%d (%dx%d s%d p%d) epi=%s", n.name.c_str(),
-             direct ? "GEMM" : (unfold ? "conv as windowed-row GEMM over vertically unfolded NCHW input" : implicit ? "implicit-GEMM conv (TMA im2col)" : (from_nchw ? "GEMM + explicit im2col from NCHW" : "GEMM + explicit im2col")), M, g.O, Kp, g.KH,
+             direct ? "GEMM" : (unfold ? "conv as windowed-row GEMM over vertically unfolded NCHW input" : halo ? "halo-reuse conv (TMA patch, resident weights)" : implicit ? "implicit-GEMM conv (TMA im2col)" : (from_nchw ? "GEMM + explicit im2col from NCHW" : "GEMM + explicit im2col")), M, g.O, Kp, g.KH,
              g.KW, g.sh, g.pt, ta.f.enabled ? "fast" : (epi.mode == kEpiInt ? "int" : (epi.mode == kEpiFloat ? "float" : "raw")));
     P.add_step(desc, [=](RunCtx& c) {
       TcArgs t = ta;
@@ -957,7 +959,7 @@ static void plan_dense(Planner& P, int nid, bool composite) {
   const int bias_eid = ci.bias_eid, sum_eid = ci.sum_eid, xd = X.dtype, wd = Wt.dtype;
   const bool foldable = zpx == 0 || (Wt.is_const && bias_eid < 0);
   const bool use_tc = P.rt->conv_impl != "simt" && tc_gemm_supported((int)M, N, K) && zpw == 0 && foldable &&
-                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || M * N >= 4096);
+                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" || M * N >= 4096);
   char desc[256];
   if (use_tc) {
     std::vector<int32_t> bias2;
@@ -1036,7 +1038,7 @@ static void plan_batch_matmul(Planner& P, int nid) {
   init_epi(epi);
   const int xd = X.dtype, wd = Wt.dtype;
   const bool use_tc = P.rt->conv_impl != "simt" && tc_gemm_supported(M, N, K) && zpx == 0 && zpw == 0 &&
-                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || (long long)B * M * N >= 4096);
+                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" || (long long)B * M * N >= 4096);
   char desc[256];
   snprintf(desc, sizeof(desc), "qnn.batch_matmul -> %s B=%d M=%d N=%d K=%d", use_tc ? "tcgen05 i8 GEMM" : "CUDA-core GEMM", B, M, N, K);
   P.add_step(desc, [=](RunCtx& c) {
@@ -1737,7 +1739,8 @@ int tkb_set_option(tkb_handle h, const char* key, const char* value) {
   TKB_TRY
   const std::string k = key, v = value;
   if (k == "conv_impl") {
-    if (v != "auto" && v != "simt" && v != "tc" && v != "tc_explicit") fail("conv_impl must be auto|simt|tc|tc_explicit");
+    if (v != "auto" && v != "simt" && v != "tc" && v != "tc_explicit" && v != "tc_im2col")
+      fail("conv_impl must be auto|simt|tc|tc_explicit|tc_im2col");
     if (h->initialized && v != h->conv_impl) {
       h->conv_impl = v;
       std::lock_guard<std::mutex> guard(h->init_mu);
@@ -1836,6 +1839,14 @@ int64_t tkb_trace_bytes(tkb_handle h) {
 
 void tkb_fixed_point_multiplier_shift(double multiplier, int32_t* significand, int32_t* exponent) {
   fixed_point_multiplier_shift(multiplier, significand, exponent);
+}
+
+int tkb_spin(double microseconds, void* cuda_stream) {
+  TKB_TRY
+  if (microseconds < 0 || microseconds > 1e6) fail("tkb_spin: 0 .. 1e6 microseconds");
+  launch_spin(microseconds, (cudaStream_t)cuda_stream);
+  CUDA_OK(cudaGetLastError());
+  TKB_CATCH
 }
 
 int tkb_probe_int8_shape(int iters, int n, int commit_every, double* tops, void* cuda_stream) {

@@ -39,6 +39,9 @@ struct TcKernelParams {
   const uint8_t* cls_h;   // [OH]
   const uint8_t* cls_w;   // [OW]
   int ncls_w;
+  // halo-reuse convolution (tc_halo_kernel): tile = hR output rows of one image, A = one (hR+KH-1) x hWp pixel
+  // patch per channel chunk, taps = shifted UMMA descriptors into the patch, weights resident in shared memory
+  int hR, hWp, hRows, hTpi, a_slot, a_stages;
   const uint8_t* wpack;   // packed weight tiles (tc_pack_weights) or nullptr: B comes through tmB
   int dbg;                // timing experiments only (TKB_DBG): 1 = no epilogue work, 2 = no B loads, 4 = no A loads
   EpiParams e;            // generic epilogue (any rounding / compute dtype / float mode / raw int32)
@@ -181,6 +184,65 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const Tc
     uint4* dst = (uint4*)((uint8_t*)p.y + idx0);
     dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
     dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  }
+}
+
+// Drain one accumulator stage: the calling epilogue warp owns TMEM lanes 32*q .. +31 and columns
+// [half*BN/2, +BN/2) of the tile; `row` is the output row (pixel) of this lane.
+template <int BN, int MODE>
+__device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t tmem_base, uint32_t lt, int q, int half,
+                                               int lane, int row, bool row_valid, int b, int n0, uint32_t tab_base,
+                                               bool vec_ok, uint64_t* tempty, uint64_t* tfull) {
+  const long long row_off = ((long long)b * p.M + row) * p.N;
+  const int32_t* drow = nullptr;
+  if (p.delta != nullptr && row_valid) {
+    const int qq = row % p.OW, pp = (row / p.OW) % p.OH;
+    const int cls = (int)p.cls_h[pp] * p.ncls_w + (int)p.cls_w[qq];
+    if (cls) drow = p.delta + (long long)cls * p.N;
+  }
+  const uint32_t as = lt & 1;
+  mbar_wait(&tfull[as], (lt >> 1) & 1);
+  tc_fence_after();
+  const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
+  const int ncol_tile = min(BN, p.N - n0);
+  const int cbeg = half * (BN / 2), cend = min(cbeg + BN / 2, ncol_tile);
+  if (cbeg >= cend) {  // nothing to drain for this warp (ragged N tail): just release the stage
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&tempty[as]);
+    return;
+  }
+  if (p.dbg & 1) {
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&tempty[as]);
+    return;
+  }
+  uint32_t ra[32], rb[32];
+  tmem_ld32(t_addr + cbeg, ra);
+#pragma unroll 1
+  for (int c = cbeg;; c += 64) {
+    tmem_ld_wait32(ra);
+    const bool more_b = c + 32 < cend;
+    if (more_b) tmem_ld32(t_addr + c + 32, rb);
+    else {  // all TMEM reads of this warp are complete: hand the accumulator stage back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[as]);
+    }
+    epilogue_chunk<MODE>(ra, p, tab_base + c * 16, row_valid, min(32, cend - c), n0 + c, row_off + n0 + c, drow, vec_ok);
+    if (!more_b) break;
+    tmem_ld_wait32(rb);
+    const bool more_a = c + 64 < cend;
+    if (more_a) tmem_ld32(t_addr + c + 64, ra);
+    else {
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[as]);
+    }
+    epilogue_chunk<MODE>(rb, p, tab_base + (c + 32) * 16, row_valid, min(32, cend - c - 32), n0 + c + 32,
+                         row_off + n0 + c + 32, drow, vec_ok);
+    if (!more_a) break;
   }
 }
 
@@ -342,57 +404,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         row_valid = qp < p.OW;
         row = (mt / p.win_qt) * p.OW + qp;
       }
-      const long long row_off = ((long long)b * p.M + row) * p.N;
-      const int32_t* drow = nullptr;
-      if (p.delta != nullptr && row_valid) {
-        const int qq = row % p.OW, pp = (row / p.OW) % p.OH;
-        const int cls = (int)p.cls_h[pp] * p.ncls_w + (int)p.cls_w[qq];
-        if (cls) drow = p.delta + (long long)cls * p.N;
-      }
-      const uint32_t as = lt & 1;
-      mbar_wait(&tfull[as], (lt >> 1) & 1);
-      tc_fence_after();
-      const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
-      const int ncol_tile = min(BN, p.N - n0);
-      const int cbeg = half * (BN / 2), cend = min(cbeg + BN / 2, ncol_tile);
-      if (cbeg >= cend) {  // nothing to drain for this warp (ragged N tail): just release the stage
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[as]);
-        continue;
-      }
-      if (p.dbg & 1) {
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[as]);
-        continue;
-      }
-      uint32_t ra[32], rb[32];
-      tmem_ld32(t_addr + cbeg, ra);
-#pragma unroll 1
-      for (int c = cbeg;; c += 64) {
-        tmem_ld_wait32(ra);
-        const bool more_b = c + 32 < cend;
-        if (more_b) tmem_ld32(t_addr + c + 32, rb);
-        else {  // all TMEM reads of this warp are complete: hand the accumulator stage back to the MMA warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty[as]);
-        }
-        epilogue_chunk<MODE>(ra, p, tab_base + c * 16, row_valid, min(32, cend - c), n0 + c, row_off + n0 + c, drow, vec_ok);
-        if (!more_b) break;
-        tmem_ld_wait32(rb);
-        const bool more_a = c + 64 < cend;
-        if (more_a) tmem_ld32(t_addr + c + 64, ra);
-        else {
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty[as]);
-        }
-        epilogue_chunk<MODE>(rb, p, tab_base + (c + 32) * 16, row_valid, min(32, cend - c - 32), n0 + c + 32,
-                             row_off + n0 + c + 32, drow, vec_ok);
-        if (!more_a) break;
-      }
+      epi_drain_tile<BN, MODE>(p, tmem_base, lt, q, half, lane, row, row_valid, b, n0, tab_base, vec_ok, tempty, tfull);
     }
   }
   tc_fence_before();

@@ -265,6 +265,13 @@ def fixed_point_multiplier_shift(m):
     return s.value, e.value
 
 
+def spin(microseconds, stream=None):
+    """Enqueue a device busy-wait (measurement aid, see tkb_spin)."""
+    L = load_library()
+    L.tkb_spin.argtypes = [ctypes.c_double, ctypes.c_void_p]
+    _check(L.tkb_spin(float(microseconds), ctypes.c_void_p(stream) if stream else None))
+
+
 def probe_int8_peak(iters=2000):
     t = ctypes.c_double()
     _check(load_library().tkb_probe_int8_peak(int(iters), ctypes.byref(t), None))

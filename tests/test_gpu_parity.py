@@ -214,11 +214,37 @@ def test_implicit_conv_vs_oracle(name, nhwc):
     plan = mod.plan_summary()
     assert "tcgen05" in plan and "epi=fast" in plan, plan
     if cfg[5] > 1 or cfg[6] > 1:
-        assert "implicit-GEMM" in plan, plan
+        assert "implicit-GEMM" in plan or "halo-reuse" in plan, plan
     np.testing.assert_equal(out, ref)
-    # the explicit-im2col route and the CUDA-core route agree bit for bit
-    out2, _, _ = run_gpu(func, args, conv_impl="tc_explicit")
+    # the TMA-im2col route (halo kernel off) and the explicit-im2col route agree bit for bit
+    out2, mod2, _ = run_gpu(func, args, conv_impl="tc_im2col")
+    assert "halo-reuse" not in mod2.plan_summary()
     np.testing.assert_equal(out2, ref)
+    out3, _, _ = run_gpu(func, args, conv_impl="tc_explicit")
+    np.testing.assert_equal(out3, ref)
+
+
+HALO_CASES = {
+    # stride-1 convolutions that take the halo-reuse kernel (patch loads, taps as shifted descriptors, resident weights)
+    "h_c64_56": (2, 64, 56, 56, 64, 3, 1, 1, 1, 3, True, True, False),            # ResNet-18 layer1 geometry
+    "h_c128_28_sum": (3, 128, 28, 28, 128, 3, 1, 1, 1, 128, True, False, True),  # layer2 geometry + residual
+    "h_c64_ragged_n48": (2, 64, 13, 20, 48, 3, 1, 1, 1, 5, True, True, True),    # last tile of an image is partial
+    "h_c64_5x5": (1, 64, 17, 17, 32, 5, 1, 2, 1, 9, False, True, False),
+    "h_c192_3chunks": (2, 192, 14, 14, 64, 3, 1, 1, 1, 77, True, True, False),   # 3 channel chunks of 64
+    "h_c256_2chunks": (1, 256, 14, 14, 64, 3, 1, 1, 1, 200, True, False, True),  # 2 channel chunks of 128
+    "h_c64_p0_s8": (5, 64, 30, 30, 96, 3, 1, 0, 1, 0, True, True, False),        # no padding, 150 tiles > 148 SMs
+}
+
+
+@pytest.mark.parametrize("nhwc", [False, True], ids=["nchw", "nhwc"])
+@pytest.mark.parametrize("name", list(HALO_CASES))
+def test_halo_conv_vs_oracle(name, nhwc):
+    cfg = HALO_CASES[name]
+    func, args = _chain_conv(*cfg, seed=len(name) * 7 + cfg[2], nhwc=nhwc, xdt="int8" if name.endswith("s8") else "uint8")
+    ref, _ = interp.run_expr(func, args)
+    out, mod, _ = run_gpu(func, args, conv_impl="tc")
+    assert "halo-reuse" in mod.plan_summary(), mod.plan_summary()
+    np.testing.assert_equal(out, ref)
 
 
 def test_implicit_conv_raw_int32_and_generic_epilogue():

@@ -19,7 +19,11 @@ namespace tkb {
 
 static constexpr int MAX_A_STAGES = 8;
 
-template <int BN, int MODE>
+// KH_ = 0: any KH x KW / chunk size, loops with run-time bounds.  Otherwise KH_ x KW_ taps with BK_ bytes per pixel
+// chunk, fully unrolled -- a straight line of UTCIMMAs with one uniform add per descriptor.  (The run-time loop
+// costs ~110 cycles per MMA on the single issuing thread -- LDCU / R2UR / UIMAD chains between the MMAs -- which
+// for N = 64 tiles is 3x the tensor pipe's own time per instruction; unrolled it is ~57.)
+template <int BN, int MODE, int KH_, int KW_, int BK_>
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ TcKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -71,8 +75,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
       for (int cc = 0; cc < cchunks; ++cc) {
         mbar_wait(&a_empty[st], ph ^ 1);
         if (elect_one()) {
-          mbar_expect_tx(&a_full[st], patch_bytes);
-          tma_load_4d(smem_a + (size_t)st * p.a_slot, &tmA, &a_full[st], cc * p.bk, -p.pl, oh0 - p.pt, n);
+          if (p.dbg & 4) mbar_arrive(&a_full[st]);  // timing experiment: no patch traffic
+          else {
+            mbar_expect_tx(&a_full[st], patch_bytes);
+            tma_load_4d(smem_a + (size_t)st * p.a_slot, &tmA, &a_full[st], cc * p.bk, -p.pl, oh0 - p.pt, n);
+          }
         }
         __syncwarp();
         if (++st == p.a_stages) { st = 0; ph ^= 1; }
@@ -97,22 +104,40 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
         if (elect_one()) {
           const uint32_t slot = a_base + st * p.a_slot;
           uint32_t acc = cc != 0;
-          int t = 0;
-          for (int r = 0; r < p.KH; ++r)
-            for (int s = 0; s < p.KW; ++s, ++t) {
-              const uint32_t a_addr = slot + (uint32_t)((r * p.hWp + s) * p.bk);
-              const uint32_t b_addr = b_base + (uint32_t)((t * cchunks + cc) * b_bytes);
-              // The swizzle XOR is applied to absolute shared-memory address bits, so a start address that is
-              // not a multiple of the 8-row pattern needs nothing else: measured on B200, the descriptor's
-              // "matrix base offset" field must stay 0 here (setting it to (addr >> 7) & 7 gives wrong sums).
-              const uint64_t hi_a = (uint64_t)p.desc_hi << 32, hi_b = hi_a;
-              const uint32_t a_lo = ((a_addr >> 4) & 0x3FFF) | (1u << 16);
-              const uint32_t b_lo = ((b_addr >> 4) & 0x3FFF) | (1u << 16);
-              for (int k = 0; k < kper; ++k) {
-                mma_i8(d_tmem, hi_a | (a_lo + 2 * k), hi_b | (b_lo + 2 * k), p.idesc, acc);
-                acc = 1;
-              }
+          // The swizzle XOR is applied to absolute shared-memory address bits, so a start address that is not a
+          // multiple of the 8-row pattern needs nothing else: measured on B200, the descriptor's "matrix base
+          // offset" field must stay 0 here (setting it to (addr >> 7) & 7 gives wrong sums).
+          const uint64_t hi = (uint64_t)p.desc_hi << 32;
+          if constexpr (KH_ != 0) {
+            const uint32_t a_lo0 = ((slot >> 4) & 0x3FFF) | (1u << 16);
+            const uint32_t b_lo0 = (((b_base + (uint32_t)(cc * b_bytes)) >> 4) & 0x3FFF) | (1u << 16);
+            const uint32_t b_step = (uint32_t)(cchunks * b_bytes) >> 4, row_step = (uint32_t)(p.hWp * BK_) >> 4;
+            if (!(p.dbg & 32)) {
+#pragma unroll
+              for (int r = 0; r < KH_; ++r)
+#pragma unroll
+                for (int s = 0; s < KW_; ++s)
+#pragma unroll
+                  for (int k = 0; k < BK_ / UMMA_K; ++k) {
+                    mma_i8(d_tmem, hi | (a_lo0 + r * row_step + s * (BK_ / 16) + 2 * k),
+                           hi | (b_lo0 + (r * KW_ + s) * b_step + 2 * k), p.idesc, acc);
+                    acc = 1;
+                  }
             }
+          } else {
+            int t = 0;
+            for (int r = 0; r < ((p.dbg & 32) ? 0 : p.KH); ++r)  // dbg 32: timing experiment without MMAs
+              for (int s = 0; s < p.KW; ++s, ++t) {
+                const uint32_t a_addr = slot + (uint32_t)((r * p.hWp + s) * p.bk);
+                const uint32_t b_addr = b_base + (uint32_t)((t * cchunks + cc) * b_bytes);
+                const uint32_t a_lo = ((a_addr >> 4) & 0x3FFF) | (1u << 16);
+                const uint32_t b_lo = ((b_addr >> 4) & 0x3FFF) | (1u << 16);
+                for (int k = 0; k < kper; ++k) {
+                  mma_i8(d_tmem, hi | (a_lo + 2 * k), hi | (b_lo + 2 * k), p.idesc, acc);
+                  acc = 1;
+                }
+              }
+          }
           tc_commit(&a_empty[st]);
           if (cc == cchunks - 1) tc_commit(&tfull[as]);
         }
@@ -205,11 +230,11 @@ void tc_halo_tile_config(const ConvGeom& g, int N, int* bn, int* bk) {
   if (halo_config(g, N, &c)) { *bn = c.bn; *bk = c.bk; }
 }
 
-template <int BN, int MODE>
+template <int BN, int MODE, int KH_, int KW_, int BK_>
 static int launch_halo_t(const CUtensorMap& ta, TcKernelParams& p, int smem, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(tc_halo_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
+    if (cudaFuncSetAttribute(tc_halo_kernel<BN, MODE, KH_, KW_, BK_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
         cudaSuccess)
       return -1;
     attr_set = true;
@@ -226,7 +251,7 @@ static int launch_halo_t(const CUtensorMap& ta, TcKernelParams& p, int smem, cud
   cfg.attrs = attr;
   cfg.numAttrs = getenv("TKB_NO_PDL") ? 0 : 1;
   p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
-  if (cudaLaunchKernelEx(&cfg, tc_halo_kernel<BN, MODE>, ta, p) != cudaSuccess) return -1;
+  if (cudaLaunchKernelEx(&cfg, tc_halo_kernel<BN, MODE, KH_, KW_, BK_>, ta, p) != cudaSuccess) return -1;
   ++g_launches;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
@@ -266,9 +291,16 @@ int launch_tc_halo(const TcArgs& a, cudaStream_t s) {
          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
     return -1;
   const bool sum = a.f.has_sum != 0;
-  if (c.bn == 64) return sum ? launch_halo_t<64, kModeFastSum>(ta, p, c.smem, s) : launch_halo_t<64, kModeFast>(ta, p, c.smem, s);
-  if (c.bn == 128) return sum ? launch_halo_t<128, kModeFastSum>(ta, p, c.smem, s) : launch_halo_t<128, kModeFast>(ta, p, c.smem, s);
-  return sum ? launch_halo_t<256, kModeFastSum>(ta, p, c.smem, s) : launch_halo_t<256, kModeFast>(ta, p, c.smem, s);
+  const bool k33 = g.KH == 3 && g.KW == 3, k14 = g.KH == 1 && g.KW == 4;
+#define TKB_HALO(COND_, BN_, KH_, KW_, BK_)                                                        \
+  if ((COND_) && c.bn == BN_ && (BK_ == 0 || c.bk == BK_))                                         \
+    return sum ? launch_halo_t<BN_, kModeFastSum, KH_, KW_, BK_>(ta, p, c.smem, s)                 \
+               : launch_halo_t<BN_, kModeFast, KH_, KW_, BK_>(ta, p, c.smem, s);
+  TKB_HALO(k33, 64, 3, 3, 64) TKB_HALO(k33, 64, 3, 3, 128) TKB_HALO(k33, 128, 3, 3, 64) TKB_HALO(k33, 128, 3, 3, 128)
+  TKB_HALO(k14, 64, 1, 4, 64)  // the stride-2 7x7 stem as a 1x4 convolution over pixel pairs of the unfolded input
+  TKB_HALO(true, 64, 0, 0, 0) TKB_HALO(true, 128, 0, 0, 0) TKB_HALO(true, 256, 0, 0, 0)
+#undef TKB_HALO
+  return -1;
 }
 
 }  // namespace tkb

@@ -864,12 +864,33 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     ta.g = g;
     if (composite && !ci.float_mode)
       build_fast_epi(P, ci, bias2, abs_row_sums(wk.data(), g.O, K, g.w_dtype), g.O, Y.dtype, &ta.f);
-    const bool halo = implicit && ta.f.enabled && P.rt->conv_impl != "tc_im2col" && tc_halo_supported(g, g.O);
+    bool halo = implicit && ta.f.enabled && P.rt->conv_impl != "tc_im2col" && tc_halo_supported(g, g.O);
     if (halo) ta.implicit = 3;
+    // Stride-2 stem over the unfolded tensor: two horizontally adjacent 32-byte pixels of X3 form one 64-byte
+    // "pair pixel", output column q reads pair pixels q .. q + ceil(KW/2) - 1: a stride-1 1 x ceil(KW/2)
+    // convolution with 64 channels, which the halo-reuse kernel runs with one window load per output row
+    // (each X3 byte enters shared memory once instead of KW/2 times) and the weights resident.
+    if (unfold && g.sw == 2 && (g.W + g.pl + g.pr) % 2 == 0 && ta.f.enabled && P.rt->conv_impl != "tc_im2col") {
+      ConvGeom g2 = g;
+      g2.C = 64; g2.H = g.OH; g2.W = (g.W + g.pl + g.pr) / 2; g2.KH = 1; g2.KW = (g.KW + 1) / 2;
+      g2.sh = g2.sw = g2.dh = g2.dw = 1;
+      g2.pt = g2.pb = g2.pl = g2.pr = 0;
+      if (g2.W - g2.KW + 1 == g.OW && tc_halo_supported(g2, g.O)) {
+        const int K2 = g2.KW * 64;
+        std::vector<uint8_t> w2((size_t)g.O * K2, 0);
+        for (int o = 0; o < g.O; ++o) memcpy(&w2[(size_t)o * K2], &wp[(size_t)o * Kp], Kp);
+        wp.swap(w2);
+        ta.g = g2;
+        ta.K = K2;
+        ta.implicit = 3;
+        halo = true;
+      }
+    }
+    const int Kw = ta.K;  // row length of wp
     {  // constant weights: pre-tile into the swizzled shared-memory image (one bulk copy per tile at run time)
       tc_tile_config(ta, &ta.pack_bn, &ta.pack_bk);
-      std::vector<uint8_t> packed(tc_pack_weights(wp.data(), g.O, Kp, ta.pack_bn, ta.pack_bk, nullptr));
-      tc_pack_weights(wp.data(), g.O, Kp, ta.pack_bn, ta.pack_bk, packed.data());
+      std::vector<uint8_t> packed(tc_pack_weights(wp.data(), g.O, Kw, ta.pack_bn, ta.pack_bk, nullptr));
+      tc_pack_weights(wp.data(), g.O, Kw, ta.pack_bn, ta.pack_bk, packed.data());
       ta.w = P.dev_upload(packed.data(), packed.size());
       ta.w_packed = 1;
     }
@@ -883,7 +904,7 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     if (unfold) scratch_off = P.arena_alloc((long long)g.N * g.OH * (g.W + g.pl + g.pr) * 32 + 256);
     else if (!direct && !implicit) scratch_off = P.arena_alloc(M * Kp);
     snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 %s M=%lld N=%d K=%d (%dx%d s%d p%d) epi=%s", n.name.c_str(),
-             direct ? "GEMM" : (unfold ? "conv as windowed-row GEMM over vertically unfolded NCHW input" : halo ? "halo-reuse conv (TMA patch, resident weights)" : implicit ? "implicit-GEMM conv (TMA im2col)" : (from_nchw ? "GEMM + explicit im2col from NCHW" : "GEMM + explicit im2col")), M, g.O, Kp, g.KH,
+             direct ? "GEMM" : (unfold ? (halo ? "halo-reuse conv over pixel pairs of the vertically unfolded NCHW input" : "conv as windowed-row GEMM over vertically unfolded NCHW input") : halo ? "halo-reuse conv (TMA patch, resident weights)" : implicit ? "implicit-GEMM conv (TMA im2col)" : (from_nchw ? "GEMM + explicit im2col from NCHW" : "GEMM + explicit im2col")), M, g.O, Kp, g.KH,
              g.KW, g.sh, g.pt, ta.f.enabled ? "fast" : (epi.mode == kEpiInt ? "int" : (epi.mode == kEpiFloat ? "float" : "raw")));
     P.add_step(desc, [=](RunCtx& c) {
       TcArgs t = ta;

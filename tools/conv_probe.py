@@ -37,6 +37,7 @@ mod.set_option("time_tc", "1")
 n = 10
 tot = 0.0
 for _ in range(n):
+    RT.spin(300.0, st)  # host queues the launch behind the spin: the events see device time only
     mod.run(xd, out, stream=st)
     torch.cuda.synchronize()
     ms, cnt = mod.tc_time()

@@ -1,4 +1,5 @@
 #!/bin/bash
+cd "$(dirname "$0")/.."
 for cfg in "64 56 64 3 1" "128 28 128 3 1"; do
-  for dbg in 0 1 2 4 5 6 7 8; do TKB_DBG=$dbg timeout 120 python tools/conv_probe.py $cfg 2>&1 | tail -1 | cut -c1-80; done
+  for dbg in 0 1 4 5 32 33 36 37 8; do TKB_DBG=$dbg timeout 120 python tools/conv_probe.py $cfg 2>&1 | tail -1 | cut -c1-90; done
 done

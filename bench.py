@@ -137,6 +137,16 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def _ncu_traffic():
+    """DRAM bytes per tcgen05 launch (read + write) from the committed ncu --set full capture of the same step,
+    profiles/r01_tc_traffic.json; None when the file is absent."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_tc_traffic.json")) as f:
+            return float(json.load(f)["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -257,8 +267,8 @@ def main():
                 "h2d_bytes_per_step": int(x_np.nbytes), "d2h_bytes_per_step": int(trace_d2h + np.prod(out_shape))},
         "gpu_launches": int(launches),
         "roofline": {
-            "bound": "tensor", "kernel": "tc_gemm_kernel<BN,MODE> (tcgen05.mma kind::i8, all conv/dense launches of a step)", "achieved": achieved_tops,
-            "peak": peak_tops, "unit": "TFLOP/s", "frac": achieved_tops / peak_tops if peak_tops else None, "traffic": None,
+            "bound": "tensor", "kernel": "tc_halo_kernel / tc_gemm_kernel (tcgen05.mma kind::i8; all %d conv/dense launches of a step)" % (tc_n // runs if runs else 0), "achieved": achieved_tops,
+            "peak": peak_tops, "unit": "TFLOP/s", "frac": achieved_tops / peak_tops if peak_tops else None, "traffic": _ncu_traffic(),
             "note": "int8 ops (2*MAC) counted as FLOPs; peak = this run's tcgen05 kind::i8 issue-rate probe "
                     "(MEASURED_PEAKS.json has no int8 entry; 2x its bf16 burst = %.0f)" % (2 * peaks.get("bf16_tflops", 0)),
             "avg_launch_us": 1e3 * tc_ms / tc_n if tc_n else None, "launches_per_step": tc_n // runs if runs else None,

@@ -93,6 +93,7 @@ def cpu_oracle_rate(name, sample, repeats=1):
     """images/s of the oracle (CPU port of the reference algorithm) on `sample` images, all host threads."""
     from oracle import interp
     from tachikoma_b200 import models
+    interp.set_threads(os.cpu_count())  # torchrun exports OMP_NUM_THREADS=1
     part, symbol, graph_json, const_names, consts = build_model(name, sample)
     x = models.synthetic_input(name, sample)
     interp.run_json(graph_json, consts, [x[:sample]])  # warm-up (library load, page faults)
@@ -109,7 +110,7 @@ def run_reference(args, rank):
         return
     from oracle import interp
     from tachikoma_b200 import models
-    cores = os.cpu_count()
+    cores = interp.set_threads(os.cpu_count())  # torchrun exports OMP_NUM_THREADS=1
     t0 = time.perf_counter()
     probe = cpu_oracle_rate(args.model, 1)
     # bounded sample per step so that (steps + warmup) * sample images finish within ~2 minutes

@@ -43,6 +43,11 @@ def lib():
     return _LIB
 
 
+def set_threads(n=0):
+    """Set (n > 0) and return the OpenMP thread count the oracle kernels run with."""
+    return int(lib().tko_set_threads(int(n)))
+
+
 def _p(a):
     return a.ctypes.data_as(ctypes.c_void_p)
 

@@ -15,6 +15,9 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 /* dtype codes shared with oracle/interp.py */
 enum { TKO_I8 = 0, TKO_U8 = 1, TKO_I32 = 2, TKO_I16 = 3, TKO_I64 = 4, TKO_F32 = 5 };
@@ -375,4 +378,16 @@ void tko_dnnl_float_epilogue(const int32_t* acc, int64_t outer, int64_t C, int64
     int64_t y = r < (float)lo ? lo : (r > (float)hi ? hi : (int64_t)r);
     store_int(out, out_dtype, idx, y);
   }
+}
+
+/* Thread control for the timed CPU-baseline legs of bench.py: launchers such as torchrun export
+ * OMP_NUM_THREADS=1, which would silently turn the "all host cores" baseline into a single-thread one. */
+int tko_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  (void)n;
+  return 1;
+#endif
 }

@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nimg = p.M / (p.OH * p.OW);
-  const long long total_tiles = (long long)nimg * p.hTpi;
+  const long long total_tiles = (p.dbg & 8) ? 0 : (long long)nimg * p.hTpi;  // dbg 8: launch + prologue + teardown only
 
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (warp == 0 && lane == 0) {

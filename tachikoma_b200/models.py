@@ -121,7 +121,7 @@ def _input(shape, seed=1):
 
 def synthetic_input(name, batch, seed=1):
     shape = {"mlp": (batch, 784), "lenet5": (batch, 1, 28, 28), "resnet18": (batch, 3, 224, 224),
-             "mobilenetv2": (batch, 3, 224, 224)}[name]
+             "mobilenetv2": (batch, 3, 224, 224), "bert_encoder": (batch * 128, 768)}[name]
     return _input(shape, seed)
 
 
@@ -212,4 +212,88 @@ def mobilenetv2(batch=128, seed=0, image=224, num_classes=1000):
     return R.Function([x], e)
 
 
-MODELS = {"mlp": mlp, "lenet5": lenet5, "resnet18": resnet18, "mobilenetv2": mobilenetv2}
+def bert_encoder(batch=8, seed=0, seq=128, hidden=768, heads=12, ffn=3072, layers=1):
+    """C5: the integer chain of a BERT-base encoder layer (seq 128, hidden 768, 12 heads, FFN 3072): Q/K/V
+    qnn.dense -> requantize to int8 (symmetric) -> head split (reshape / transpose) -> qnn.batch_matmul Q.K^T ->
+    requantize -> uint8 "P" (zero point 0) -> qnn.batch_matmul P.V^T-form -> requantize -> head merge -> output
+    qnn.dense -> qnn.add residual -> FFN qnn.dense x2 -> qnn.add residual.  Softmax and LayerNorm are float
+    operators outside the integer path and are not modelled: P is the
+    requantized, clipped score matrix, which keeps every integer operator at its BERT-base shape."""
+    import torch
+    rng = np.random.default_rng(seed)
+    d = hidden // heads
+    x = R.var("data", (batch * seq, hidden), "uint8")
+    shadow = torch.from_numpy(_input((2 * seq, hidden), 7).astype(np.float32))  # calibration sample: 2 sequences
+    cb = 2
+
+    def calib(real, kind):
+        std = float(real.std()) + 1e-12
+        if kind == "i8":
+            s_out = np.float32(_round_sig(std / 40.0))
+            return s_out, 0, torch.clamp(torch.floor(real / float(s_out) + 0.5), -128.0, 127.0)
+        zp = 0 if kind == "relu" else 128
+        s_out = np.float32(_round_sig(std / (50.0 if kind == "relu" else 40.0)))
+        return s_out, zp, torch.clamp(torch.floor(real / float(s_out) + 0.5) + zp, 0.0, 255.0)
+
+    def dense(e, sh, s_x, zp_x, units, kind):
+        k = e.shape[-1]
+        w = rng.integers(-127, 128, size=(units, k)).astype(np.int8)
+        s_w = (rng.uniform(0.5, 1.5, size=units) / (127.0 * np.sqrt(k))).astype(np.float32)
+        b = rng.integers(-(1 << 12), 1 << 12, size=units).astype(np.int32)
+        acc = (sh - zp_x) @ torch.from_numpy(w.astype(np.float32)).T + torch.from_numpy(b.astype(np.float32))
+        real = acc * torch.from_numpy((np.float32(s_x) * s_w).astype(np.float32))
+        s_out, zp_out, q = calib(real, kind)
+        y = R.qnn_dense(e, R.const(w), zp_x, 0, np.float32(s_x), R.const(s_w), units)
+        y = R.bias_add(y, R.const(b), axis=1)
+        y = R.qnn_requantize(y, R.const((np.float32(s_x) * s_w).astype(np.float32)), 0, s_out, zp_out, axis=-1,
+                             out_dtype="int32")
+        if kind == "i8":
+            y = R.cast(R.clip(y, -128.0, 127.0), "int8")
+        else:
+            y = R.cast(R.clip(y, float(zp_out if kind == "relu" else 0), 255.0), "uint8")
+        return y, s_out, zp_out, q
+
+    def split_heads(e, sh, nb):  # [nb*seq, hidden] -> [nb*heads, seq, d]
+        e = R.reshape(R.transpose(R.reshape(e, (nb, seq, heads, d)), (0, 2, 1, 3)), (nb * heads, seq, d))
+        sh = sh.reshape(cb, seq, heads, d).permute(0, 2, 1, 3).reshape(cb * heads, seq, d)
+        return e, sh
+
+    def bmm(a, a_sh, s_a, b_, b_sh, s_b, kind):
+        real = (a_sh @ b_sh.transpose(1, 2)) * float(s_a) * float(s_b)
+        s_out, zp_out, q = calib(real, kind)
+        y = R.qnn_batch_matmul(a, b_, 0, 0, np.float32(s_a), np.float32(s_b))
+        y = R.qnn_requantize(y, np.float32(np.float32(s_a) * np.float32(s_b)), 0, s_out, zp_out, axis=-1, out_dtype="int32")
+        if kind == "i8":
+            y = R.cast(R.clip(y, -128.0, 127.0), "int8")
+        else:
+            y = R.cast(R.clip(y, 0.0, 255.0), "uint8")
+        return y, s_out, zp_out, q
+
+    def residual(a, a_sh, s_a, zp_a, b_, b_sh, s_b, zp_b):
+        real = (a_sh - zp_a) * float(s_a) + (b_sh - zp_b) * float(s_b)
+        so, zo = np.float32(_round_sig(float(real.std()) / 40.0)), 128
+        y = R.clip(R.qnn_add(a, b_, np.float32(s_a), zp_a, np.float32(s_b), zp_b, so, zo), 0.0, 255.0)
+        return y, so, zo, torch.clamp(torch.floor(real / float(so) + 0.5) + zo, 0.0, 255.0)
+
+    e, s, zp = x, IN_SCALE, IN_ZP
+    for _ in range(layers):
+        q, s_q, _, q_sh = dense(e, shadow, s, zp, hidden, "i8")
+        k, s_k, _, k_sh = dense(e, shadow, s, zp, hidden, "i8")
+        v, s_v, _, v_sh = dense(e, shadow, s, zp, hidden, "i8")
+        q, q_sh = split_heads(q, q_sh, batch)
+        k, k_sh = split_heads(k, k_sh, batch)
+        v, v_sh = split_heads(v, v_sh, batch)
+        p, s_p, _, p_sh = bmm(q, q_sh, s_q, k, k_sh, s_k, "relu")            # [B*h, S, S] uint8, zero point 0
+        vt, vt_sh = R.transpose(v, (0, 2, 1)), v_sh.transpose(1, 2)           # [B*h, d, S]
+        c, s_c, _, c_sh = bmm(p, p_sh, s_p, vt, vt_sh, s_v, "i8")            # [B*h, S, d]
+        c = R.reshape(R.transpose(R.reshape(c, (batch, heads, seq, d)), (0, 2, 1, 3)), (batch * seq, hidden))
+        c_sh = c_sh.reshape(cb, heads, seq, d).permute(0, 2, 1, 3).reshape(cb * seq, hidden)
+        o, s_o, zp_o, o_sh = dense(c, c_sh, s_c, 0, hidden, "u8")
+        e, s, zp, shadow = residual(o, o_sh, s_o, zp_o, e, shadow, s, zp)
+        f, s_f, zp_f, f_sh = dense(e, shadow, s, zp, ffn, "relu")
+        g, s_g, zp_g, g_sh = dense(f, f_sh, s_f, zp_f, hidden, "u8")
+        e, s, zp, shadow = residual(g, g_sh, s_g, zp_g, e, shadow, s, zp)
+    return R.Function([x], e)
+
+
+MODELS = {"mlp": mlp, "lenet5": lenet5, "resnet18": resnet18, "mobilenetv2": mobilenetv2, "bert_encoder": bert_encoder}

@@ -295,7 +295,8 @@ def test_fast_epilogue_saturating_accumulators():
 
 
 MODEL_CASES = [("mlp", dict(batch=64)), ("lenet5", dict(batch=8)), ("resnet18", dict(batch=2, image=64, num_classes=100)),
-               ("mobilenetv2", dict(batch=2, image=64, num_classes=100))]
+               ("mobilenetv2", dict(batch=2, image=64, num_classes=100)),
+               ("bert_encoder", dict(batch=2, seq=32, hidden=128, heads=4, ffn=256))]
 
 
 @pytest.mark.parametrize("impl", ["simt", "tc"])
@@ -305,6 +306,8 @@ def test_models_bit_exact_with_trace(name, kw, impl):
     x = models.synthetic_input(name, kw["batch"])
     if "image" in kw:
         x = np.ascontiguousarray(x[:, :, :kw["image"], :kw["image"]])
+    if name == "bert_encoder":
+        x = np.random.default_rng(1).integers(0, 256, (kw["batch"] * kw["seq"], kw["hidden"])).astype("uint8")
     ref, _ = interp.run_expr(func, {"data": x})  # un-partitioned, op by op
     out, mod, (js, consts, ins) = run_gpu(func, {"data": x}, conv_impl=impl, trace=True)
     np.testing.assert_equal(out, ref)
@@ -328,6 +331,22 @@ def test_resnet18_full_size_properties():
     f1 = models.resnet18(batch=1)
     ref, _ = interp.run_expr(f1, {"data": x[:1]})
     np.testing.assert_equal(a[:1], ref)
+
+
+def test_bert_base_layer_full_size():
+    """C5 at BASELINE size (seq 128, hidden 768, 12 heads, FFN 3072; 2 sequences to bound oracle time): dense and
+    batch_matmul run on tcgen05 and the output and the serialized trace equal the oracle's byte for byte."""
+    func = models.bert_encoder(batch=2)
+    x = models.synthetic_input("bert_encoder", 2)
+    ref, _ = interp.run_expr(func, {"data": x})
+    out, mod, (js, consts, ins) = run_gpu(func, {"data": x}, conv_impl="tc", trace=True)
+    plan = mod.plan_summary()
+    assert plan.count("tcgen05") >= 8, plan  # 6 dense + 2 batch_matmul
+    np.testing.assert_equal(out, ref)
+    _, recs = interp.run_json(js, consts, ins, want_trace=True)
+    assert mod.trace_blob() == interp.save_ndarray_list(recs)
+    out2, _, _ = run_gpu(func, {"data": x}, conv_impl="simt")
+    np.testing.assert_equal(out2, ref)
 
 
 def test_int8_peak_probe_runs():

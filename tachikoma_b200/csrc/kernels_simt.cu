@@ -687,12 +687,110 @@ __global__ void unfold_rows_nchw_kernel(const uint8_t* __restrict__ x, uint8_t* 
   }
 }
 
+// Vectorised variant for W % 4 == 0: one warp produces 128 consecutive interior pixels of one (n, p) row.
+// Lane l loads, for each of the KH*C (row, channel) lines, the 32-bit word holding input columns w0+4l .. +3
+// (128 contiguous bytes per warp load), transposes bytes in registers (4x4 byte transposes with PRMT) into its
+// four 32-byte pixels, and the warp then re-orders the 4 KB through a padded shared-memory slab so that every
+// global store instruction writes 512 contiguous bytes.  The pl + pr padding pixels of the row are written by
+// the first lanes of segment 0.
+template <int C_, int KH_>
+__global__ void __launch_bounds__(256) unfold_rows_nchw_vec_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y,
+                                                                   ConvGeom g) {
+  constexpr int CP = 32, KC = KH_ * C_, NG = (KC + 3) / 4;  // NG groups of 4 source lines -> output word NG-1 max
+  __shared__ uint4 slab[8][32 * 9];                          // per warp: 32 lanes x (128 + 16) bytes
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int segs = (g.W + 127) / 128;
+  const int WP = g.W + g.pl + g.pr;
+  const long long plane = (long long)g.H * g.W;
+  const uint32_t zp = (uint32_t)(g.zp_a & 0xFF), zp4 = zp * 0x01010101u;
+  const long long nwarps = (long long)g.N * g.OH * segs;
+  for (long long wi = blockIdx.x * 8LL + warp; wi < nwarps; wi += gridDim.x * 8LL) {
+    const int seg = (int)(wi % segs);
+    const long long t = wi / segs;
+    const int p = (int)(t % g.OH);
+    const long long n = t / g.OH;
+    const int w0 = seg * 128, w = w0 + 4 * lane;
+    const bool act = w < g.W;
+    const uint8_t* img = x + n * C_ * plane + w;
+    const int iy0 = p * g.sh - g.pt;
+    uint32_t L[NG * 4];
+#pragma unroll
+    for (int k = 0; k < NG * 4; ++k) {
+      uint32_t v = 0;
+      if (k < KC) {
+        const int r = k / C_, c = k % C_;
+        const int iy = iy0 + r * g.dh;
+        v = zp4;
+        if (act && iy >= 0 && iy < g.H) v = __ldg((const uint32_t*)(img + c * plane + (long long)iy * g.W));
+      }
+      L[k] = v;
+    }
+    // 4x4 byte transposes: out[j][i] = bytes j of L[4i .. 4i+3]
+    uint32_t out[4][8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) out[j][i] = 0;
+#pragma unroll
+    for (int i = 0; i < NG; ++i) {
+      const uint32_t a = __byte_perm(L[4 * i], L[4 * i + 1], 0x5140), b = __byte_perm(L[4 * i], L[4 * i + 1], 0x7362);
+      const uint32_t c2 = __byte_perm(L[4 * i + 2], L[4 * i + 3], 0x5140), d = __byte_perm(L[4 * i + 2], L[4 * i + 3], 0x7362);
+      out[0][i] = __byte_perm(a, c2, 0x5410);
+      out[1][i] = __byte_perm(a, c2, 0x7632);
+      out[2][i] = __byte_perm(b, d, 0x5410);
+      out[3][i] = __byte_perm(b, d, 0x7632);
+    }
+    uint4* mine = &slab[warp][lane * 9];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      mine[2 * j] = make_uint4(out[j][0], out[j][1], out[j][2], out[j][3]);
+      mine[2 * j + 1] = make_uint4(out[j][4], out[j][5], out[j][6], out[j][7]);
+    }
+    __syncwarp();
+    uint8_t* row = y + ((n * g.OH + p) * (long long)WP) * CP;
+    uint4* dst = (uint4*)(row + (long long)(g.pl + w0) * CP);
+    const int npx = min(128, g.W - w0);  // pixels of this segment
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int chunk = 32 * i + lane;   // 16-byte chunk of the segment's contiguous 4 KB
+      if (chunk < npx * 2) dst[chunk] = slab[warp][(chunk >> 3) * 9 + (chunk & 7)];
+    }
+    if (seg == 0 && lane < g.pl + g.pr) {  // padding pixels: zero-point bytes in the first KH*C positions
+      uint32_t wz[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        uint32_t v = 0;
+#pragma unroll
+        for (int bb = 0; bb < 4; ++bb)
+          if (4 * i + bb < KC) v |= zp << (8 * bb);
+        wz[i] = v;
+      }
+      const int px = lane < g.pl ? lane : g.pl + g.W + (lane - g.pl);
+      uint4* pd = (uint4*)(row + (long long)px * CP);
+      pd[0] = make_uint4(wz[0], wz[1], wz[2], wz[3]);
+      pd[1] = make_uint4(wz[4], wz[5], wz[6], wz[7]);
+    }
+    __syncwarp();
+  }
+}
+
 void launch_unfold_rows_nchw(const void* x, void* y, const ConvGeom& g, cudaStream_t s) {
   const long long total = (long long)g.N * g.OH * (g.W + g.pl + g.pr);
   if (total == 0) return;
   const int nb = blocks_for(total, 256);
   const uint8_t* xi = (const uint8_t*)x;
   uint8_t* yo = (uint8_t*)y;
+  if ((g.W & 3) == 0 && (((uintptr_t)x) & 3) == 0 && (((uintptr_t)y) & 15) == 0 && g.pl + g.pr <= 32) {
+    const long long nwarps = (long long)g.N * g.OH * ((g.W + 127) / 128);
+    const int nbv = (int)std::min<long long>((nwarps + 7) / 8, 148LL * 64);
+    bool done = true;
+    if (g.C == 3 && g.KH == 7) unfold_rows_nchw_vec_kernel<3, 7><<<nbv, 256, 0, s>>>(xi, yo, g);
+    else if (g.C == 3 && g.KH == 3) unfold_rows_nchw_vec_kernel<3, 3><<<nbv, 256, 0, s>>>(xi, yo, g);
+    else if (g.C == 1 && g.KH == 5) unfold_rows_nchw_vec_kernel<1, 5><<<nbv, 256, 0, s>>>(xi, yo, g);
+    else if (g.C == 1 && g.KH == 3) unfold_rows_nchw_vec_kernel<1, 3><<<nbv, 256, 0, s>>>(xi, yo, g);
+    else done = false;
+    if (done) { ++g_launches; return; }
+  }
   if (g.C == 3 && g.KH == 7) unfold_rows_nchw_kernel<3, 7><<<nb, 256, 0, s>>>(xi, yo, g);
   else if (g.C == 3 && g.KH == 3) unfold_rows_nchw_kernel<3, 3><<<nb, 256, 0, s>>>(xi, yo, g);
   else if (g.C == 1 && g.KH == 5) unfold_rows_nchw_kernel<1, 5><<<nb, 256, 0, s>>>(xi, yo, g);

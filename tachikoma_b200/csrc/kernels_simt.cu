@@ -351,6 +351,53 @@ __global__ void maxpool8_nhwc_kernel(const uint8_t* __restrict__ x, uint8_t* __r
   }
 }
 
+// 3x3 / stride 2 specialisation (ResNet stem pool): one thread owns 16 channels of TWO vertically adjacent
+// outputs (5 input rows x 3 columns, the middle row shared), no 64-bit index arithmetic (3-D grid), all 15
+// 128-bit loads issued back to back.  Taps outside the image are replaced by a clamped in-window tap: max is
+// idempotent, so re-reading a valid element changes nothing and no predication is needed.
+template <bool UNSIGNED>
+__global__ void __launch_bounds__(256) maxpool8_nhwc_3x3s2_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y,
+                                                                  PoolArgs a) {
+  const int cg = a.C >> 4;
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t >= a.OW * cg) return;
+  const int ox = t / cg, g = t - ox * cg;
+  const int oy = blockIdx.y * 2, n = blockIdx.z;
+  const bool two = oy + 1 < a.OH;
+  const uint8_t* img = x + (long long)n * a.H * a.W * a.C + g * 16;
+  int cx[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) cx[j] = min(max(ox * 2 - a.pl + j, 0), a.W - 1) * a.C;
+  const int ylo0 = max(oy * 2 - a.pt, 0), yhi0 = min(oy * 2 - a.pt + 2, a.H - 1);
+  const int ylo1 = two ? max(oy * 2 + 2 - a.pt, 0) : ylo0, yhi1 = two ? min(oy * 2 + 4 - a.pt, a.H - 1) : yhi0;
+  uint4 v[5][3];
+#pragma unroll
+  for (int r = 0; r < 5; ++r) {
+    // rows 0..2 belong to output 0 (row 2 also to output 1), rows 3..4 to output 1; clamp each into its window
+    int iy = oy * 2 - a.pt + r;
+    iy = r < 2 ? min(max(iy, ylo0), yhi0) : (r == 2 ? min(max(iy, ylo0), yhi0) : min(max(iy, ylo1), yhi1));
+    const uint8_t* row = img + (long long)iy * a.W * a.C;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) v[r][j] = __ldg((const uint4*)(row + cx[j]));
+  }
+  auto vmax = [](uint4 p, uint4 q) {
+    if (UNSIGNED) return make_uint4(__vmaxu4(p.x, q.x), __vmaxu4(p.y, q.y), __vmaxu4(p.z, q.z), __vmaxu4(p.w, q.w));
+    return make_uint4(__vmaxs4(p.x, q.x), __vmaxs4(p.y, q.y), __vmaxs4(p.z, q.z), __vmaxs4(p.w, q.w));
+  };
+  uint4 rm[5];
+#pragma unroll
+  for (int r = 0; r < 5; ++r) rm[r] = vmax(vmax(v[r][0], v[r][1]), v[r][2]);
+  uint8_t* out = y + (((long long)n * a.OH + oy) * a.OW + ox) * a.C + g * 16;
+  *(uint4*)out = vmax(vmax(rm[0], rm[1]), rm[2]);
+  // row 2 of the pair lies in output 1's window only when it is not clamped away (always true for pt <= 2)
+  if (two) {
+    const int iy2 = oy * 2 - a.pt + 2;
+    uint4 m1 = vmax(rm[3], rm[4]);
+    if (iy2 >= ylo1 && iy2 <= yhi1) m1 = vmax(m1, rm[2]);
+    *(uint4*)(out + (long long)a.OW * a.C) = m1;
+  }
+}
+
 void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_include_pad, int N, int C, int H, int W,
                    int KH, int KW, int sh, int sw, int pt, int pl, int pb, int pr, const long long* xs,
                    const long long* ys, cudaStream_t s) {
@@ -367,6 +414,13 @@ void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_incl
   if (!is_avg && (dtype == kU8 || dtype == kI8) && (C % 16) == 0 && dense_nhwc &&
       ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0) {
     const long long work = total / 16;
+    if (KH == 3 && KW == 3 && sh == 2 && sw == 2 && pt <= 2 && pl <= 2 && N <= 65535 && a.OH <= 131070 && H >= 2 && W >= 2) {
+      dim3 grid((unsigned)((a.OW * (C / 16) + 255) / 256), (unsigned)((a.OH + 1) / 2), (unsigned)N);
+      if (dtype == kU8) maxpool8_nhwc_3x3s2_kernel<true><<<grid, 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
+      else maxpool8_nhwc_3x3s2_kernel<false><<<grid, 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
+      ++g_launches;
+      return;
+    }
     if (dtype == kU8) maxpool8_nhwc_kernel<true><<<blocks_for(work, 256), 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
     else maxpool8_nhwc_kernel<false><<<blocks_for(work, 256), 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
     ++g_launches;

@@ -349,6 +349,28 @@ def test_bert_base_layer_full_size():
     np.testing.assert_equal(out2, ref)
 
 
+POOL_CASES = [
+    # (n, h, w, c, k, stride, pad, dtype)
+    (2, 16, 16, 64, 3, 2, 1, "uint8"), (3, 13, 9, 32, 3, 2, 1, "uint8"), (1, 7, 7, 16, 3, 2, 1, "int8"),
+    (2, 15, 14, 48, 3, 2, 0, "int8"), (1, 2, 2, 16, 3, 2, 1, "uint8"), (2, 12, 12, 32, 3, 2, 2, "uint8"),
+    (2, 12, 10, 32, 2, 2, 0, "uint8"), (1, 9, 9, 16, 3, 1, 1, "int8"),
+]
+
+
+@pytest.mark.parametrize("cfg", POOL_CASES, ids=["x".join(str(v) for v in c) for c in POOL_CASES])
+def test_max_pool_nhwc_8bit_vs_oracle(cfg):
+    n, h, w, c, k, st, pad, dt = cfg
+    rng = np.random.default_rng(h * 31 + w)
+    lo, hi = (0, 256) if dt == "uint8" else (-128, 128)
+    x = rng.integers(lo, hi, (n, h, w, c)).astype(dt)
+    x[0, 0, 0, :] = lo  # minimum of the dtype in a corner window: padding must never win
+    data = R.var("data", x.shape, dt)
+    func = R.Function([data], R.max_pool2d(data, (k, k), (st, st), (pad, pad), layout="NHWC"))
+    ref, _ = interp.run_expr(func, {"data": x})
+    out, _, _ = run_gpu(func, {"data": x})
+    np.testing.assert_equal(out, ref)
+
+
 def test_int8_peak_probe_runs():
     tops = RT.probe_int8_peak(2000)
     assert tops > 100.0, tops

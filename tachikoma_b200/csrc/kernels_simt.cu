@@ -242,8 +242,40 @@ __global__ void cast_kernel(const void* __restrict__ x, int xd, void* __restrict
   }
 }
 
+// 8-bit -> 32-bit integer widening, 4 elements per thread (32-bit load, 128-bit store)
+template <bool SIGNED>
+__global__ void cast_8_to_32_kernel(const uint32_t* __restrict__ x, int4* __restrict__ y, unsigned n4) {
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  const uint32_t w = __ldg(x + i);
+  if (SIGNED) y[i] = make_int4((int8_t)(w & 0xFF), (int8_t)((w >> 8) & 0xFF), (int8_t)((w >> 16) & 0xFF), (int8_t)(w >> 24));
+  else y[i] = make_int4((int)(w & 0xFF), (int)((w >> 8) & 0xFF), (int)((w >> 16) & 0xFF), (int)(w >> 24));
+}
+// 32-bit -> 8-bit truncation (LLVM trunc), 4 elements per thread
+__global__ void cast_32_to_8_kernel(const int4* __restrict__ x, uint32_t* __restrict__ y, unsigned n4) {
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  const int4 v = __ldg(x + i);
+  y[i] = ((uint32_t)v.x & 0xFF) | (((uint32_t)v.y & 0xFF) << 8) | (((uint32_t)v.z & 0xFF) << 16) | ((uint32_t)v.w << 24);
+}
+
 void launch_cast(const void* x, int x_dtype, void* y, int y_dtype, long long n, cudaStream_t s) {
   if (n == 0) return;
+  const bool x8 = x_dtype == kU8 || x_dtype == kI8, y8 = y_dtype == kU8 || y_dtype == kI8;
+  if ((n & 3) == 0 && n / 4 < (1LL << 31) && ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0) {
+    const unsigned n4 = (unsigned)(n / 4), nb = (n4 + 255) / 256;
+    if (x8 && y_dtype == kI32) {
+      if (x_dtype == kI8) cast_8_to_32_kernel<true><<<nb, 256, 0, s>>>((const uint32_t*)x, (int4*)y, n4);
+      else cast_8_to_32_kernel<false><<<nb, 256, 0, s>>>((const uint32_t*)x, (int4*)y, n4);
+      ++g_launches;
+      return;
+    }
+    if (x_dtype == kI32 && y8) {
+      cast_32_to_8_kernel<<<nb, 256, 0, s>>>((const int4*)x, (uint32_t*)y, n4);
+      ++g_launches;
+      return;
+    }
+  }
   cast_kernel<<<blocks_for(n, 256), 256, 0, s>>>(x, x_dtype, y, y_dtype, n);
   ++g_launches;
 }
@@ -398,6 +430,26 @@ __global__ void __launch_bounds__(256) maxpool8_nhwc_3x3s2_kernel(const uint8_t*
   }
 }
 
+// Global average pool of a dense channels-last int32 tensor: one thread per (n, c), the HW loads are independent
+// (unrolled by 7) so several are in flight; sum wraps in int32 and the division truncates toward zero, as the
+// reference's topi pool (include/tvm/topi/nn/pooling.h:389, :624-650).
+__global__ void global_avgpool_nhwc_i32_kernel(const int32_t* __restrict__ x, int32_t* __restrict__ y, int HW, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, n = blockIdx.y;
+  if (c >= C) return;
+  const int32_t* p = x + (long long)n * HW * C + c;
+  uint32_t sum = 0;
+  int i = 0;
+  for (; i + 7 <= HW; i += 7) {
+    uint32_t v[7];
+#pragma unroll
+    for (int j = 0; j < 7; ++j) v[j] = (uint32_t)__ldg(p + (long long)(i + j) * C);
+#pragma unroll
+    for (int j = 0; j < 7; ++j) sum += v[j];
+  }
+  for (; i < HW; ++i) sum += (uint32_t)__ldg(p + (long long)i * C);
+  y[(long long)n * C + c] = (int32_t)sum / HW;
+}
+
 void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_include_pad, int N, int C, int H, int W,
                    int KH, int KW, int sh, int sw, int pt, int pl, int pb, int pr, const long long* xs,
                    const long long* ys, cudaStream_t s) {
@@ -423,6 +475,12 @@ void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_incl
     }
     if (dtype == kU8) maxpool8_nhwc_kernel<true><<<blocks_for(work, 256), 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
     else maxpool8_nhwc_kernel<false><<<blocks_for(work, 256), 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
+    ++g_launches;
+    return;
+  }
+  if (is_avg && dtype == kI32 && dense_nhwc && KH == H && KW == W && pt + pb + pl + pr == 0 && N <= 65535 && H * W > 0) {
+    dim3 grid((unsigned)((C + 127) / 128), (unsigned)N);
+    global_avgpool_nhwc_i32_kernel<<<grid, 128, 0, s>>>((const int32_t*)x, (int32_t*)y, H * W, C);
     ++g_launches;
     return;
   }

@@ -96,6 +96,8 @@ struct Workspace {
   uint8_t* trace_host = nullptr;    // pinned host mirror of every traced tensor
   long long trace_ring_bytes = 0, trace_host_bytes = 0;
   cudaStream_t side = nullptr;
+  cudaEvent_t ev_join = nullptr;
+  bool side_dirty = false;
   cudaEvent_t ev = nullptr;
   std::vector<cudaEvent_t> tc_events;  // begin/end pairs around tcgen05 GEMM launches (option time_tc)
   size_t tc_used = 0;
@@ -1418,6 +1420,7 @@ static void ensure_trace_buffers(tkb_runtime* rt, Workspace* ws) {
   if (!ws->side) {
     CUDA_OK(cudaStreamCreateWithFlags(&ws->side, cudaStreamNonBlocking));
     CUDA_OK(cudaEventCreateWithFlags(&ws->ev, cudaEventDisableTiming));
+    CUDA_OK(cudaEventCreateWithFlags(&ws->ev_join, cudaEventDisableTiming));
   }
   if (ws->trace_ring_bytes < rt->trace_ring_bytes) {
     if (ws->trace_ring) cudaFree(ws->trace_ring);
@@ -1442,6 +1445,20 @@ static void ensure_trace_buffers(tkb_runtime* rt, Workspace* ws) {
 // then (mode 2) D2H on the side stream, ordered after the producing kernels by an event.
 static void trace_node(RunCtx& c, size_t lo, size_t hi) {
   tkb_runtime* rt = c.rt;
+  // All trace work runs on the side stream, ordered after the producing kernels by an event: the layout
+  // transposes are HBM-bound and overlap with the following tensor-core kernels instead of delaying them.
+  bool any = false;
+  for (size_t i = lo; i < hi && !any; ++i) {
+    if (rt->trace_dup_of[i] >= 0) continue;
+    int r = rt->trace_recs[i].eid;
+    while (rt->ent[r].alias_of >= 0) r = rt->ent[r].alias_of;
+    any = rt->trace_ring_off[i] >= 0 || (rt->trace_mode >= 2 && !rt->ent[r].is_const);
+  }
+  if (!any) return;
+  cudaStream_t side = c.ws->side;
+  CUDA_OK(cudaEventRecord(c.ws->ev, c.s));
+  CUDA_OK(cudaStreamWaitEvent(side, c.ws->ev, 0));
+  c.ws->side_dirty = true;
   for (size_t i = lo; i < hi; ++i) {
     if (rt->trace_ring_off[i] < 0 || rt->trace_dup_of[i] >= 0) continue;
     const int eid = rt->trace_recs[i].eid;
@@ -1451,13 +1468,11 @@ static void trace_node(RunCtx& c, size_t lo, size_t hi) {
     const long long N = e.shape[0], C = e.shape[1], H = e.shape[2], W = e.shape[3];
     long long oshape[4] = {N, C, H, W}, istr[4] = {H * W * C, 1, W * C, C};
     void* dstp = c.ws->trace_ring + rt->trace_ring_off[i];
-    if (dtype_size(e.dtype) == 1 && launch_nhwc_to_nchw8(c.ptr(r, kNHWC), dstp, N, H * W, C, c.s)) continue;
-    if (launch_transpose_tile(c.ptr(r, kNHWC), dstp, dtype_size(e.dtype), N, H * W, C, c.s)) continue;
-    launch_permute4(c.ptr(r, kNHWC), c.ws->trace_ring + rt->trace_ring_off[i], dtype_size(e.dtype), oshape, istr, c.s);
+    if (dtype_size(e.dtype) == 1 && launch_nhwc_to_nchw8(c.ptr(r, kNHWC), dstp, N, H * W, C, side)) continue;
+    if (launch_transpose_tile(c.ptr(r, kNHWC), dstp, dtype_size(e.dtype), N, H * W, C, side)) continue;
+    launch_permute4(c.ptr(r, kNHWC), c.ws->trace_ring + rt->trace_ring_off[i], dtype_size(e.dtype), oshape, istr, side);
   }
   if (rt->trace_mode < 2) return;
-  CUDA_OK(cudaEventRecord(c.ws->ev, c.s));
-  CUDA_OK(cudaStreamWaitEvent(c.ws->side, c.ws->ev, 0));
   for (size_t i = lo; i < hi; ++i) {
     const int eid = rt->trace_recs[i].eid;
     int r = eid;
@@ -1467,8 +1482,17 @@ static void trace_node(RunCtx& c, size_t lo, size_t hi) {
     const long long bytes = rt->ent[eid].bytes();
     if (e.is_const || rt->trace_dup_of[i] >= 0) continue;  // constants were written once; duplicates alias a slot
     const void* src = rt->trace_ring_off[i] >= 0 ? (const void*)(c.ws->trace_ring + rt->trace_ring_off[i]) : c.ptr(r, kLogical);
-    CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.ws->side));
+    CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, side));
   }
+}
+
+// Join the side stream back into the caller's stream: everything enqueued on `s` after a traced run (the next
+// run's kernels, which overwrite the arena and the ring; the caller's own work) is ordered after the trace work.
+static void trace_join(RunCtx& c) {
+  if (!c.ws->side || !c.ws->side_dirty) return;
+  CUDA_OK(cudaEventRecord(c.ws->ev_join, c.ws->side));
+  CUDA_OK(cudaStreamWaitEvent(c.s, c.ws->ev_join, 0));
+  c.ws->side_dirty = false;
 }
 
 static void check_arg(const Entry& e, const tkb_DLTensor* t, int i) {
@@ -1522,6 +1546,7 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
     }
   }
   if (rt->trace_mode > 0 && rec < rt->trace_recs.size()) trace_node(c, rec, rt->trace_recs.size());
+  trace_join(c);
   bool host_out = false;
   for (int j = 0; j < n_out; ++j) {
     const int eid = (int)g.eid(g.heads[j]);
@@ -1677,6 +1702,7 @@ int tkb_free(tkb_handle h) {
     if (w->trace_host) cudaFreeHost(w->trace_host);
     if (w->side) cudaStreamDestroy(w->side);
     if (w->ev) cudaEventDestroy(w->ev);
+    if (w->ev_join) cudaEventDestroy(w->ev_join);
   }
   for (void* p : h->dev_allocs) cudaFree(p);
   delete h;

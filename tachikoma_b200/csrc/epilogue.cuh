@@ -237,6 +237,9 @@ struct FastEpi {
   uint32_t sum_xor;      // 0x80808080 for an int8 residual (b = (u ^ 0x80) - 128, the -128 is folded into rhs.C)
   FastSide lhs, rhs;     // qnn.add sides; lhs.C also carries "- zp_out" of the add
   int32_t sum_lo, sum_hi;
+  // 1 / 2: the final clamp equals the uint8 / int8 range, so the saturating pack (cvt.pack.sat) performs it;
+  // `sat` for the plain composite ([lo, hi]), `sum_sat` for the residual form ([sum_lo, sum_hi])
+  int sat, sum_sat;
 };
 
 }  // namespace tkb

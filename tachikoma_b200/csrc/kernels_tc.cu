@@ -220,17 +220,24 @@ int launch_tc(const TcArgs& a, cudaStream_t s) {
   if (a.w_packed) tb = ta;  // never dereferenced: B tiles come from p.wpack with bulk copies
   else if (!make_tmap_3d(&tb, a.w, a.K, a.N, a.w_batched ? a.B : 1, bn, bk)) return -1;
   int mode = kModeGeneric;
-  if (a.f.enabled) mode = a.f.has_sum ? kModeFastSum : kModeFast;
+  // the saturating-pack epilogue needs more registers; at BN >= 128 (two TMEM chunks in flight) it spills under the
+  // 168-register cap and is slower than the explicit clamps, so it is used for 64-column tiles only
+  const bool sat_ok = bn == 64;
+  if (a.f.enabled)
+    mode = a.f.has_sum ? (a.f.sum_sat && sat_ok ? kModeFastSumSat : kModeFastSum) : (a.f.sat && sat_ok ? kModeFastSat : kModeFast);
   else if (a.e.mode == kEpiRaw) mode = kModeRaw;
   if (mode == kModeGeneric || mode == kModeRaw) return launch_tc_other(bn, mode, ta, tb, p, s);
-  if (mode == kModeFast) {
-    if (bn == 64) return launch_t<64, kModeFast>(ta, tb, p, s);
-    if (bn == 128) return launch_t<128, kModeFast>(ta, tb, p, s);
-    return launch_t<256, kModeFast>(ta, tb, p, s);
+  if (mode == kModeFastSat) return launch_t<64, kModeFastSat>(ta, tb, p, s);
+  if (mode == kModeFastSumSat) return launch_t<64, kModeFastSumSat>(ta, tb, p, s);
+#define TKB_GEMM(MODE_)                                                    \
+  if (mode == MODE_) {                                                     \
+    if (bn == 64) return launch_t<64, MODE_>(ta, tb, p, s);                \
+    if (bn == 128) return launch_t<128, MODE_>(ta, tb, p, s);              \
+    return launch_t<256, MODE_>(ta, tb, p, s);                             \
   }
-  if (bn == 64) return launch_t<64, kModeFastSum>(ta, tb, p, s);
-  if (bn == 128) return launch_t<128, kModeFastSum>(ta, tb, p, s);
-  return launch_t<256, kModeFastSum>(ta, tb, p, s);
+  TKB_GEMM(kModeFast) TKB_GEMM(kModeFastSum)
+#undef TKB_GEMM
+  return -1;
 }
 
 // ---- dense int8 peak probe -------------------------------------------------------------------------

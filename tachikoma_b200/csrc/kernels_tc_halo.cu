@@ -291,11 +291,15 @@ int launch_tc_halo(const TcArgs& a, cudaStream_t s) {
          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
     return -1;
   const bool sum = a.f.has_sum != 0;
+  // saturating-pack epilogue (kModeFastSat): spills at BN = 128 without the residual, so 64-column tiles only there
+  const bool sat = a.f.sat && c.bn == 64, sum_sat = a.f.sum_sat != 0;
   const bool k33 = g.KH == 3 && g.KW == 3, k14 = g.KH == 1 && g.KW == 4;
 #define TKB_HALO(COND_, BN_, KH_, KW_, BK_)                                                        \
   if ((COND_) && c.bn == BN_ && (BK_ == 0 || c.bk == BK_))                                         \
-    return sum ? launch_halo_t<BN_, kModeFastSum, KH_, KW_, BK_>(ta, p, c.smem, s)                 \
-               : launch_halo_t<BN_, kModeFast, KH_, KW_, BK_>(ta, p, c.smem, s);
+    return sum ? (sum_sat ? launch_halo_t<BN_, kModeFastSumSat, KH_, KW_, BK_>(ta, p, c.smem, s)  \
+                              : launch_halo_t<BN_, kModeFastSum, KH_, KW_, BK_>(ta, p, c.smem, s))     \
+               : (sat ? launch_halo_t<BN_, kModeFastSat, KH_, KW_, BK_>(ta, p, c.smem, s)          \
+                          : launch_halo_t<BN_, kModeFast, KH_, KW_, BK_>(ta, p, c.smem, s));
   TKB_HALO(k33, 64, 3, 3, 64) TKB_HALO(k33, 64, 3, 3, 128) TKB_HALO(k33, 128, 3, 3, 64) TKB_HALO(k33, 128, 3, 3, 128)
   TKB_HALO(k14, 64, 1, 4, 64)  // the stride-2 7x7 stem as a 1x4 convolution over pixel pairs of the unfolded input
   TKB_HALO(true, 64, 0, 0, 0) TKB_HALO(true, 128, 0, 0, 0) TKB_HALO(true, 256, 0, 0, 0)

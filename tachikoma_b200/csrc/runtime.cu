@@ -631,6 +631,11 @@ static bool build_fast_epi(Planner& P, const CompositeInfo& ci, const std::vecto
     dtype_range(out_dtype, &olo, &ohi);
     if (out->sum_lo > out->sum_hi || out->sum_lo < olo || out->sum_hi > ohi) return false;
   }
+  auto sat_code = [](int dtype, int32_t l, int32_t h) {
+    return dtype == kU8 && l == 0 && h == 255 ? 1 : (dtype == kI8 && l == -128 && h == 127 ? 2 : 0);
+  };
+  out->sat = has_sum ? 0 : sat_code(out_dtype, lo, hi);
+  out->sum_sat = has_sum ? sat_code(out_dtype, out->sum_lo, out->sum_hi) : 0;
   out->tabA = (const int4*)P.dev_upload(tab.data(), tab.size() * 4);
   out->enabled = 1;
   return true;

@@ -93,7 +93,12 @@ __device__ __forceinline__ uint4 ldg_nc_16(const void* p) {
 // whose rows are not 16-byte multiples, border rows that need the zero-point delta, the generic
 // rounding / compute-dtype / float variants) goes element by element through one out-of-line function,
 // which keeps the hot loop small enough to stay in the instruction cache.
-enum TcMode : int { kModeGeneric = 0, kModeFast = 1, kModeFastSum = 2, kModeRaw = 3 };
+// kModeFastSat / kModeFastSumSat: same arithmetic, the final clamp is the output dtype's own range and is done by
+// the saturating pack (separate instantiations keep each kernel's hot loop small: instruction cache)
+enum TcMode : int { kModeGeneric = 0, kModeFast = 1, kModeFastSum = 2, kModeRaw = 3, kModeFastSat = 5, kModeFastSumSat = 6 };
+__host__ __device__ constexpr bool mode_is_fast(int m) { return (m & 3) == kModeFast || (m & 3) == kModeFastSum; }
+__host__ __device__ constexpr bool mode_is_sum(int m) { return (m & 3) == kModeFastSum; }
+__host__ __device__ constexpr bool mode_is_sat(int m) { return (m & 4) != 0; }
 
 __device__ __forceinline__ int4 lds128(uint32_t addr) {
   int4 v;
@@ -115,15 +120,35 @@ __device__ __forceinline__ int32_t fast_side(int32_t q, const FastSide& f) {
   return (int32_t)(v >> 32) >> f.s1;
 }
 
+// cvt.pack.sat: two int32 -> two saturated 8-bit values in the low half of d, the low half of c moved up:
+// d = (c << 16) | (sat8(a) << 8) | sat8(b).  Saturation to the full range of the output dtype IS the final clamp
+// whenever the clip bounds are the dtype's own range, which saves two min/max and the shift/or packing per element.
+template <bool UNSIGNED>
+__device__ __forceinline__ uint32_t pack4_sat8(int32_t v0, int32_t v1, int32_t v2, int32_t v3) {
+  uint32_t t, d;
+  if (UNSIGNED) {
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(t) : "r"(v3), "r"(v2), "r"(0));
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(v1), "r"(v0), "r"(t));
+  } else {
+    asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(t) : "r"(v3), "r"(v2), "r"(0));
+    asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(v1), "r"(v0), "r"(t));
+  }
+  return d;
+}
+__device__ __forceinline__ int32_t fast_requant_raw(int32_t a, const int4& t) {
+  const long long c = ((long long)t.w << 32) | (unsigned long long)(uint32_t)t.z;
+  return (int32_t)(((long long)a * (long long)t.x + c) >> 32) >> t.y;
+}
+
 // one element, any configuration
 static __device__ __noinline__ void epi_slow_elem(int32_t acc, int col, long long idx, const int32_t* drow,
                                            const TcKernelParams* p, int mode) {
   if (drow) acc = (int32_t)((uint32_t)acc + (uint32_t)__ldg(drow + col));
   int32_t v;
-  if (mode == kModeFast || mode == kModeFastSum) {
+  if (mode_is_fast(mode)) {
     const FastEpi& f = p->f;
     v = fast_requant(acc, __ldg(f.tabA + col), f.lo, f.hi);
-    if (mode == kModeFastSum) {
+    if (mode_is_sum(mode)) {
       const int32_t b = (int32_t)(((const uint8_t*)p->sum)[idx] ^ (uint8_t)f.sum_xor);
       v = min(max(fast_side(v, f.lhs) + fast_side(b, f.rhs), f.sum_lo), f.sum_hi);
     }
@@ -157,29 +182,50 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const Tc
       ((int4*)dst)[i] = make_int4((int32_t)(r[4 * i] + (uint32_t)b.x), (int32_t)(r[4 * i + 1] + (uint32_t)b.y),
                                   (int32_t)(r[4 * i + 2] + (uint32_t)b.z), (int32_t)(r[4 * i + 3] + (uint32_t)b.w));
     }
-  } else if constexpr (MODE == kModeFast || MODE == kModeFastSum) {
+  } else if constexpr (mode_is_fast(MODE)) {
     const FastEpi& f = p.f;
     uint32_t sraw[8];
-    if constexpr (MODE == kModeFastSum) {
+    if constexpr (mode_is_sum(MODE)) {
       const uint4 s0 = ldg_nc_16((const uint8_t*)p.sum + idx0), s1 = ldg_nc_16((const uint8_t*)p.sum + idx0 + 16);
       sraw[0] = s0.x ^ f.sum_xor; sraw[1] = s0.y ^ f.sum_xor; sraw[2] = s0.z ^ f.sum_xor; sraw[3] = s0.w ^ f.sum_xor;
       sraw[4] = s1.x ^ f.sum_xor; sraw[5] = s1.y ^ f.sum_xor; sraw[6] = s1.z ^ f.sum_xor; sraw[7] = s1.w ^ f.sum_xor;
     }
     uint32_t w[8];
+    // sat: 0 = explicit clamps, 1 = final clamp is the uint8 range, 2 = final clamp is the int8 range
+    if constexpr (mode_is_sat(MODE)) {
+      const int sat = mode_is_sum(MODE) ? f.sum_sat : f.sat;  // 1: uint8 range, 2: int8 range
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      uint32_t word = 0;
+      for (int i = 0; i < 8; ++i) {
+        int32_t v[4];
 #pragma unroll
-      for (int jj = 0; jj < 4; ++jj) {
-        const int j = 4 * i + jj;
-        int32_t y = fast_requant((int32_t)r[j], lds128(tab_addr + j * 16), f.lo, f.hi);
-        if constexpr (MODE == kModeFastSum) {
-          const int32_t b = (int32_t)((sraw[i] >> (8 * jj)) & 0xFFu);
-          y = min(max(fast_side(y, f.lhs) + fast_side(b, f.rhs), f.sum_lo), f.sum_hi);
+        for (int jj = 0; jj < 4; ++jj) {
+          const int j = 4 * i + jj;
+          int32_t y = fast_requant_raw((int32_t)r[j], lds128(tab_addr + j * 16));
+          if constexpr (mode_is_sum(MODE)) {
+            y = min(max(y, f.lo), f.hi);
+            const int32_t b = (int32_t)((sraw[i] >> (8 * jj)) & 0xFFu);
+            y = fast_side(y, f.lhs) + fast_side(b, f.rhs);
+          }
+          v[jj] = y;
         }
-        word |= (uint32_t)(y & 0xFF) << (8 * jj);
+        w[i] = sat == 1 ? pack4_sat8<true>(v[0], v[1], v[2], v[3]) : pack4_sat8<false>(v[0], v[1], v[2], v[3]);
       }
-      w[i] = word;
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        uint32_t word = 0;
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          const int j = 4 * i + jj;
+          int32_t y = fast_requant((int32_t)r[j], lds128(tab_addr + j * 16), f.lo, f.hi);
+          if constexpr (mode_is_sum(MODE)) {
+            const int32_t b = (int32_t)((sraw[i] >> (8 * jj)) & 0xFFu);
+            y = min(max(fast_side(y, f.lhs) + fast_side(b, f.rhs), f.sum_lo), f.sum_hi);
+          }
+          word |= (uint32_t)(y & 0xFF) << (8 * jj);
+        }
+        w[i] = word;
+      }
     }
     uint4* dst = (uint4*)((uint8_t*)p.y + idx0);
     dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
@@ -389,7 +435,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
       const long long t2 = tile / ntiles;
       const int mt = (int)(t2 % mtiles), b = (int)(t2 / mtiles);
       const int n0 = nt * BN, m0 = mt * BM;
-      if ((MODE == kModeFast || MODE == kModeFastSum) && n0 != tab_n0) {
+      if (mode_is_fast(MODE) && n0 != tab_n0) {
         // stage this n-tile's per-channel constants (the condition is uniform over the epilogue warps)
         epi_bar_sync();
         for (int i = et; i < BN; i += EPI_THREADS)

@@ -154,7 +154,8 @@ def test_tcgen05_batch_matmul_vs_oracle():
 
 # ---- implicit-GEMM convolution (TMA im2col mode) and the folded epilogue ----------------------------
 def _chain_conv(n, ic, h, w, oc, k, stride, pad, dil, zp_a, per_channel, relu, with_sum, seed, nhwc=False,
-                out_scale=None, raw=False, rounding="None", xdt="uint8", sum_scales=(0.3, 15, 0.2, 4)):
+                out_scale=None, raw=False, rounding="None", xdt="uint8", sum_scales=(0.3, 15, 0.2, 4), zp_relu=0,
+                out_dt="uint8", clip=None):
     rng = np.random.default_rng(seed)
     dl, kl = ("NHWC", "HWIO") if nhwc else ("NCHW", "OIHW")
     d_shape = (n, h, w, ic) if nhwc else (n, ic, h, w)
@@ -173,11 +174,13 @@ def _chain_conv(n, ic, h, w, oc, k, stride, pad, dil, zp_a, per_channel, relu, w
     if not raw:
         b = rng.integers(-(1 << 12), 1 << 12, oc).astype("int32")
         e = R.bias_add(e, R.const(b), axis=3 if nhwc else 1)
-        zp_out = 0 if relu else 128
+        zp_out = zp_relu if relu else (128 if out_dt == "uint8" else 0)
         so = np.float32(out_scale if out_scale is not None else 0.02 * 1.2)
         e = R.qnn_requantize(e, R.const((s_x * s_w).astype("float32")) if per_channel else np.float32(s_x * s_w), 0, so,
                              zp_out, axis=3 if nhwc else 1, out_dtype="int32", rounding=rounding)
-        e = R.cast(R.clip(e, float(zp_out if relu else 0), 255.0), "uint8")
+        dlo, dhi = (0.0, 255.0) if out_dt == "uint8" else (-128.0, 127.0)
+        c_lo, c_hi = clip if clip is not None else (float(zp_out) if relu else dlo, dhi)
+        e = R.cast(R.clip(e, c_lo, c_hi), out_dt)
         if with_sum:
             sv = R.var("res", e.shape, "uint8")
             args["res"] = rng.integers(0, 256, e.shape).astype("uint8")
@@ -244,6 +247,33 @@ def test_halo_conv_vs_oracle(name, nhwc):
     ref, _ = interp.run_expr(func, args)
     out, mod, _ = run_gpu(func, args, conv_impl="tc")
     assert "halo-reuse" in mod.plan_summary(), mod.plan_summary()
+    np.testing.assert_equal(out, ref)
+
+
+CLAMP_CASES = {
+    # (oc, relu, zp_relu, out_dt, clip): which epilogue clamp the tile takes
+    "u8_full_range_sat": (64, True, 0, "uint8", None),
+    "u8_relu_zp10_explicit": (64, True, 10, "uint8", None),
+    "u8_clip_20_200_explicit": (64, False, 0, "uint8", (20.0, 200.0)),
+    "s8_full_range_sat": (64, False, 0, "int8", None),
+    "s8_clip_explicit": (48, False, 0, "int8", (-100.0, 90.0)),
+    "u8_n128_full_range": (128, True, 0, "uint8", None),
+    "s8_n128_full_range": (128, False, 0, "int8", None),
+}
+
+
+@pytest.mark.parametrize("stride", [1, 2], ids=["halo", "im2col"])
+@pytest.mark.parametrize("name", list(CLAMP_CASES))
+def test_fast_epilogue_clamp_variants(name, stride):
+    """Saturating-pack epilogue (clip == dtype range) and explicit-clamp epilogue, uint8 and int8 outputs, on the
+    halo kernel (stride 1) and the implicit-GEMM kernel (stride 2); accumulators span far beyond the clamp."""
+    oc, relu, zp_relu, out_dt, clip = CLAMP_CASES[name]
+    func, args = _chain_conv(2, 64, 14, 14, oc, 3, stride, 1, 1, 9, True, relu, False, seed=len(name), zp_relu=zp_relu,
+                             out_dt=out_dt, clip=clip, out_scale=0.004)
+    ref, _ = interp.run_expr(func, args)
+    assert ref.min() == (clip[0] if clip else (zp_relu if relu else (0 if out_dt == "uint8" else -128)))
+    out, mod, _ = run_gpu(func, args, conv_impl="tc")
+    assert "epi=fast" in mod.plan_summary(), mod.plan_summary()
     np.testing.assert_equal(out, ref)
 
 

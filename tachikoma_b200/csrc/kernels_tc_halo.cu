@@ -23,7 +23,7 @@ static constexpr int MAX_A_STAGES = 8;
 // chunk, fully unrolled -- a straight line of UTCIMMAs with one uniform add per descriptor.  (The run-time loop
 // costs ~110 cycles per MMA on the single issuing thread -- LDCU / R2UR / UIMAD chains between the MMAs -- which
 // for N = 64 tiles is 3x the tensor pipe's own time per instruction; unrolled it is ~57.)
-template <int BN, int MODE, int KH_, int KW_, int BK_>
+template <int BN, int MODE, int KH_, int KW_, int BK_, bool SPLIT>
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ TcKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     for (int i = 0; i < p.a_stages; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], EPI_WARPS); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], SPLIT ? EPI_GROUP_WARPS : EPI_WARPS); }
     mbar_init(b_full, 1);
     fence_barrier_init();
   }
@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
   } else {
     // ===== epilogue =====
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    const int q = warp & 3, half = (warp - 2) >> 2;
+    const int q = warp & 3, grp = (warp - 2) >> 2;  // group g drains the tiles of TMEM stage g (see tc_kernel.cuh)
     const int et = threadIdx.x - 64;
     const bool vec_ok = (p.N % 16) == 0 && (((uintptr_t)p.y) & 15) == 0 &&
                         (p.sum == nullptr || (((uintptr_t)p.sum) & 15) == 0) &&
@@ -160,12 +160,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
     const int m = q * 32 + lane;
     const int prow = m / p.hWp, pcol = m - prow * p.hWp;
     const bool slot_valid = prow < p.hR && pcol < p.OW;
-    uint32_t lt = 0;
-    for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+    constexpr int tstep = SPLIT ? 2 : 1, cspan = SPLIT ? BN : BN / 2;
+    const int cbeg0 = SPLIT ? 0 : grp * (BN / 2);
+    uint32_t lt = SPLIT ? grp : 0;
+    for (long long tile = blockIdx.x + (long long)lt * gridDim.x; tile < total_tiles; tile += (long long)tstep * gridDim.x, lt += tstep) {
       const int n = (int)(tile / p.hTpi), oh = (int)(tile % p.hTpi) * p.hR + prow;
       const bool row_valid = slot_valid && oh < p.OH;
       const int row = (n * p.OH + oh) * p.OW + pcol;
-      epi_drain_tile<BN, MODE>(p, tmem_base, lt, q, half, lane, row, row_valid, 0, 0, tab_base, vec_ok, tempty, tfull);
+      epi_drain_tile<BN, MODE>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, 0, 0, tab_base, vec_ok, tempty, tfull);
     }
   }
   tc_fence_before();
@@ -230,11 +232,11 @@ void tc_halo_tile_config(const ConvGeom& g, int N, int* bn, int* bk) {
   if (halo_config(g, N, &c)) { *bn = c.bn; *bk = c.bk; }
 }
 
-template <int BN, int MODE, int KH_, int KW_, int BK_>
-static int launch_halo_t(const CUtensorMap& ta, TcKernelParams& p, int smem, cudaStream_t s) {
+template <int BN, int MODE, int KH_, int KW_, int BK_, bool SPLIT>
+static int launch_halo_ts(const CUtensorMap& ta, TcKernelParams& p, int smem, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(tc_halo_kernel<BN, MODE, KH_, KW_, BK_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
+    if (cudaFuncSetAttribute(tc_halo_kernel<BN, MODE, KH_, KW_, BK_, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
         cudaSuccess)
       return -1;
     attr_set = true;
@@ -251,9 +253,19 @@ static int launch_halo_t(const CUtensorMap& ta, TcKernelParams& p, int smem, cud
   cfg.attrs = attr;
   cfg.numAttrs = getenv("TKB_NO_PDL") ? 0 : 1;
   p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
-  if (cudaLaunchKernelEx(&cfg, tc_halo_kernel<BN, MODE, KH_, KW_, BK_>, ta, p) != cudaSuccess) return -1;
+  if (cudaLaunchKernelEx(&cfg, tc_halo_kernel<BN, MODE, KH_, KW_, BK_, SPLIT>, ta, p) != cudaSuccess) return -1;
   ++g_launches;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+// epilogue partition (see launch_t in tc_kernel.cuh): tile split for 64-column tiles of multi-tile CTAs
+template <int BN, int MODE, int KH_, int KW_, int BK_>
+static int launch_halo_t(const CUtensorMap& ta, TcKernelParams& p, int smem, cudaStream_t s) {
+  if constexpr (BN == 64) {
+    const long long tiles = (long long)(p.M / (p.OH * p.OW)) * p.hTpi;
+    if (tiles >= 2LL * num_sms()) return launch_halo_ts<BN, MODE, KH_, KW_, BK_, true>(ta, p, smem, s);
+  }
+  return launch_halo_ts<BN, MODE, KH_, KW_, BK_, false>(ta, p, smem, s);
 }
 
 int launch_tc_halo(const TcArgs& a, cudaStream_t s) {

@@ -16,7 +16,12 @@ using namespace ptx;
 static constexpr int BM = 128;       // UMMA M (rows = TMEM lanes)
 static constexpr int UMMA_K = 32;    // int8 elements per tcgen05.mma
 static constexpr int MAX_STAGES = 12;
-static constexpr int EPI_WARPS = 8;        // two per TMEM lane quadrant, each draining half of the tile's columns
+static constexpr int EPI_WARPS = 8;        // two GROUPS of four (one warp per TMEM lane quadrant): group g drains the
+                                           // tiles whose accumulator lives in TMEM stage g, so two tiles are in the
+                                           // epilogue at once (one tile's TMEM-load / barrier latency hides behind
+                                           // the other's arithmetic)
+static constexpr int EPI_GROUP_WARPS = 4;
+static constexpr int EPI_GROUP_THREADS = EPI_GROUP_WARPS * 32;
 static constexpr int EPI_THREADS = EPI_WARPS * 32;
 static constexpr int TC_THREADS = 64 + EPI_THREADS;
 
@@ -81,6 +86,10 @@ __device__ __forceinline__ void tmem_ld_wait32(uint32_t (&r)[32]) {
                : "memory");
 }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory"); }
+// named barrier of one epilogue group (ids 2 and 3)
+__device__ __forceinline__ void epi_group_sync(int grp) {
+  asm volatile("bar.sync %0, %1;" ::"r"(2 + grp), "n"(EPI_GROUP_THREADS) : "memory");
+}
 
 __device__ __forceinline__ uint4 ldg_nc_16(const void* p) {
   uint4 v;
@@ -234,9 +243,9 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const Tc
 }
 
 // Drain one accumulator stage: the calling epilogue warp owns TMEM lanes 32*q .. +31 and columns
-// [half*BN/2, +BN/2) of the tile; `row` is the output row (pixel) of this lane.
+// [cbeg0, cbeg0 + cspan) of the tile; `row` is the output row (pixel) of this lane.
 template <int BN, int MODE>
-__device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t tmem_base, uint32_t lt, int q, int half,
+__device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t tmem_base, uint32_t lt, int q, int cbeg0, int cspan,
                                                int lane, int row, bool row_valid, int b, int n0, uint32_t tab_base,
                                                bool vec_ok, uint64_t* tempty, uint64_t* tfull) {
   const long long row_off = ((long long)b * p.M + row) * p.N;
@@ -251,7 +260,7 @@ __device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t
   tc_fence_after();
   const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
   const int ncol_tile = min(BN, p.N - n0);
-  const int cbeg = half * (BN / 2), cend = min(cbeg + BN / 2, ncol_tile);
+  const int cbeg = cbeg0, cend = min(cbeg + cspan, ncol_tile);
   if (cbeg >= cend) {  // nothing to drain for this warp (ragged N tail): just release the stage
     tc_fence_before();
     __syncwarp();
@@ -292,15 +301,15 @@ __device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t
   }
 }
 
-template <int BN, int MODE>
+template <int BN, int MODE, bool SPLIT>
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
                                                          const __grid_constant__ CUtensorMap tmB,
                                                          const __grid_constant__ TcKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int a_bytes = BM * p.bk, b_bytes = BN * p.bk, sub_bytes = a_bytes + b_bytes, stage_bytes = p.kps * sub_bytes;
-  int4* tab_s = (int4*)(smem + p.stages * stage_bytes);
-  uint64_t* full = (uint64_t*)(tab_s + BN);
+  int4* tab_s = (int4*)(smem + p.stages * stage_bytes);  // one table of BN entries per epilogue group
+  uint64_t* full = (uint64_t*)(tab_s + 2 * BN);
   uint64_t* empty = full + MAX_STAGES;
   uint64_t* tfull = empty + MAX_STAGES;
   uint64_t* tempty = tfull + 2;
@@ -319,7 +328,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
     for (int i = 0; i < p.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], EPI_WARPS); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], SPLIT ? EPI_GROUP_WARPS : EPI_WARPS); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<2 * BN>(tmem_ptr);
@@ -420,27 +429,30 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     }
   } else {
     // ===== epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31 =====
-    const int q = warp & 3, half = (warp - 2) >> 2;
-    const int et = threadIdx.x - 64;  // 0..EPI_THREADS-1
+    const int q = warp & 3, grp = (warp - 2) >> 2;
+    const int et = threadIdx.x - 64 - grp * EPI_GROUP_THREADS;  // 0..EPI_GROUP_THREADS-1 within the group
     const int esz = dtype_size(p.e.out_dtype);
     const bool vec_ok = ((long long)p.N * esz) % 16 == 0 && (((uintptr_t)p.y) & 15) == 0 &&
                         (p.sum == nullptr || (((uintptr_t)p.sum) & 15) == 0) &&
                         (MODE == kModeRaw ? (p.e.out_dtype == kI32 && (p.e.bias == nullptr || (((uintptr_t)p.e.bias) & 15) == 0))
                                           : (p.e.out_dtype == kU8 || p.e.out_dtype == kI8));
-    const uint32_t tab_base = smem_u32(tab_s);
-    uint32_t lt = 0;
+    const uint32_t tab_base = smem_u32(tab_s) + grp * BN * 16;
     int tab_n0 = -1;
-    for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+    // tile split: group g takes the CTA's tiles g, g + 2, ...: exactly those whose accumulator is TMEM stage g
+    constexpr int tstep = SPLIT ? 2 : 1, cspan = SPLIT ? BN : BN / 2;
+    const int cbeg0 = SPLIT ? 0 : grp * (BN / 2);
+    uint32_t lt = SPLIT ? grp : 0;
+    for (long long tile = blockIdx.x + (long long)lt * gridDim.x; tile < total_tiles; tile += (long long)tstep * gridDim.x, lt += tstep) {
       const int nt = (int)(tile % ntiles);
       const long long t2 = tile / ntiles;
       const int mt = (int)(t2 % mtiles), b = (int)(t2 / mtiles);
       const int n0 = nt * BN, m0 = mt * BM;
       if (mode_is_fast(MODE) && n0 != tab_n0) {
-        // stage this n-tile's per-channel constants (the condition is uniform over the epilogue warps)
-        epi_bar_sync();
-        for (int i = et; i < BN; i += EPI_THREADS)
+        // stage this n-tile's per-channel constants (the condition is uniform over the group's warps)
+        epi_group_sync(grp);
+        for (int i = et; i < BN; i += EPI_GROUP_THREADS)
           sts128(tab_base + i * 16, n0 + i < p.N ? __ldg(p.f.tabA + n0 + i) : make_int4(0, 0, 0, 0));
-        epi_bar_sync();
+        epi_group_sync(grp);
         tab_n0 = n0;
       }
       int row = m0 + q * 32 + lane;
@@ -450,7 +462,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         row_valid = qp < p.OW;
         row = (mt / p.win_qt) * p.OW + qp;
       }
-      epi_drain_tile<BN, MODE>(p, tmem_base, lt, q, half, lane, row, row_valid, b, n0, tab_base, vec_ok, tempty, tfull);
+      epi_drain_tile<BN, MODE>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, b, n0, tab_base, vec_ok, tempty, tfull);
     }
   }
   tc_fence_before();
@@ -469,10 +481,13 @@ inline int num_sms() {
   return sms;
 }
 
-template <int BN, int MODE>
-static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s) {
+// SPLIT (epilogue partition, template parameter of the kernels): true = the two epilogue groups take alternate
+// TILES, all columns each (64-column tiles of CTAs that have several tiles: two tiles are in the epilogue at once);
+// false = both groups work on every tile, half of its columns each.
+template <int BN, int MODE, bool SPLIT>
+static int launch_ts(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s) {
   const int sub_bytes = (BM + BN) * p.bk;
-  const int fixed = BN * 16 + (2 * MAX_STAGES + 4) * 8 + 16 + 1024 /* alignment slack */;
+  const int fixed = 2 * BN * 16 + (2 * MAX_STAGES + 4) * 8 + 16 + 1024 /* alignment slack */;
   const int budget = 227 * 1024 - fixed;
   const int num_kb = p.implicit ? p.KH * p.KW * (p.C / p.bk) : (p.K + p.bk - 1) / p.bk;
   // Group k-blocks so that one mbarrier round trip (~100+ cycles on the single issuing thread for each of
@@ -490,7 +505,7 @@ static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams
   const int smem = stages * stage_bytes + fixed;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(tc_gemm_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
+    if (cudaFuncSetAttribute(tc_gemm_kernel<BN, MODE, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
         cudaSuccess)
       return -1;
     attr_set = true;
@@ -509,9 +524,19 @@ static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = getenv("TKB_NO_PDL") ? 0 : 1;
-  if (cudaLaunchKernelEx(&cfg, tc_gemm_kernel<BN, MODE>, ta, tb, p) != cudaSuccess) return -1;
+  if (cudaLaunchKernelEx(&cfg, tc_gemm_kernel<BN, MODE, SPLIT>, ta, tb, p) != cudaSuccess) return -1;
   ++g_launches;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+template <int BN, int MODE>
+static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s) {
+  if constexpr (BN == 64 && mode_is_fast(MODE)) {
+    const long long mt_host = p.win ? (long long)p.win_rows * p.win_qt : (p.M + BM - 1) / BM;
+    const long long tiles = mt_host * ((p.N + BN - 1) / BN) * p.batches;
+    if (tiles >= 2LL * num_sms()) return launch_ts<BN, MODE, true>(ta, tb, p, s);
+  }
+  return launch_ts<BN, MODE, false>(ta, tb, p, s);
 }
 
 // generic / raw epilogue instantiations live in their own translation unit (compile time)

@@ -83,8 +83,11 @@ int tkb_packed_run(void* args, int* type_codes, int num_args, void* out_ret_valu
 const char* tkb_last_error(void);
 
 /* --- options / introspection ------------------------------------------------------------------ */
-/* Known keys: "conv_impl" = "auto"|"simt"|"tc" (tensor-core tcgen05 path vs CUDA-core path),
- *             "time_tc"   = "0"|"1" (bracket every tcgen05 GEMM launch with CUDA events). */
+/* Known keys: "conv_impl" = "auto" (tensor cores where they pay) | "simt" (CUDA-core kernels only) | "tc" (tensor
+ *                           cores wherever supported) | "tc_im2col" (as "tc" without the halo-reuse convolution
+ *                           kernel: TMA-im2col implicit GEMM) | "tc_explicit" (as "tc" with an explicit im2col
+ *                           matrix) -- all routes produce identical bits, the last two exist for A/B tests;
+ *             "time_tc"   = "0"|"1" (bracket every tcgen05 launch with CUDA events, see tkb_tc_time). */
 int tkb_set_option(tkb_handle h, const char* key, const char* value);
 /* Number of kernels this library launched on behalf of h since creation (bench.py "gpu_launches"). */
 int64_t tkb_launch_count(tkb_handle h);

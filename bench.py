@@ -81,6 +81,11 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+SHAPES = {"mlp": "784-128-10 MLP (configs[0])", "lenet5": "LeNet-5 28x28 (configs[1])",
+          "resnet18": "resnet18 224x224 (configs[2])", "mobilenetv2": "mobilenetv2 224x224 (configs[3])",
+          "bert_encoder": "BERT-base encoder layer, seq 128, hidden 768 (configs[4]; batch = sequences)"}
+
+
 def build_model(name, batch):
     from tachikoma_b200 import models, tachikoma as T
     func = models.MODELS[name](batch=batch)
@@ -96,7 +101,7 @@ def cpu_oracle_rate(name, sample, repeats=1):
     interp.set_threads(os.cpu_count())  # torchrun exports OMP_NUM_THREADS=1
     part, symbol, graph_json, const_names, consts = build_model(name, sample)
     x = models.synthetic_input(name, sample)
-    interp.run_json(graph_json, consts, [x[:sample]])  # warm-up (library load, page faults)
+    interp.run_json(graph_json, consts, [x])  # warm-up (library load, page faults)
     t0 = time.perf_counter()
     for _ in range(repeats):
         interp.run_json(graph_json, consts, [x], want_trace=True)
@@ -128,7 +133,7 @@ def run_reference(args, rank):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8*s8->s32", "data": "synthetic",
-        "config": {"workload": f"int8 {args.model} 224x224 integer-only, full per-op trace, CPU oracle port of the "
+        "config": {"workload": f"int8 {SHAPES.get(args.model, args.model)} integer-only, full per-op trace, CPU oracle port of the "
                                f"reference lowering, {sample} images per step (bounded sample of batch {args.batch})"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{sample} images/step x {args.steps} steps, OpenMP on {cores} threads"},
@@ -255,7 +260,7 @@ def main():
         "ms_per_step": ms_value / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8*s8->s32", "data": "synthetic",
         "config": {
-            "workload": f"int8 {args.model} 224x224 integer-only, batch {args.batch} per GPU, full per-op trace "
+            "workload": f"int8 {SHAPES.get(args.model, args.model)} integer-only, batch {args.batch} per GPU, full per-op trace "
                         "(BASELINE.json configs[2])",
             "value_mode": "inputs resident in HBM, per-op trace captured on the device",
             "compute_only": total_images * args.steps / (ms_compute * 1e-3),
@@ -278,7 +283,7 @@ def main():
     }
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count()
-        sample = 8
+        sample = min(8, args.batch)
         rate = cpu_oracle_rate(args.model, sample)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{sample} images of the same workload, oracle (C + OpenMP) with trace"}

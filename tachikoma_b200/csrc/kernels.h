@@ -23,6 +23,10 @@ struct ConvGeom {
 // ---- CUDA-core kernels (complete coverage; the fallback for every shape) ----------------------
 void launch_conv2d_simt(const void* x, const void* w, void* y, const ConvGeom& g, const EpiParams& e,
                         cudaStream_t s);
+// depthwise convolution on dense channels-last 8-bit tensors; w_tap: [KH*KW][C] (tap-major), corr[c] = -zp_a*sum_taps w
+bool dwconv_nhwc_supported(const ConvGeom& g);
+void launch_dwconv_nhwc(const void* x, const void* w_tap, const int32_t* corr, void* y, const ConvGeom& g,
+                        const EpiParams& e, const FastEpi& f, cudaStream_t s);
 // Y[b,m,n] = sum_k (X[b,m,k]-zpx)(W[b?,n,k]-zpw); w_batched: W has a batch dim of B, else shared.
 void launch_gemm_simt(const void* x, const void* w, void* y, int B, int M, int N, int K, int w_batched,
                       int x_dtype, int w_dtype, int32_t zpx, int32_t zpw, const EpiParams& e, cudaStream_t s);

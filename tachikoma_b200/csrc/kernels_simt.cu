@@ -94,6 +94,90 @@ void launch_conv2d_simt(const void* x, const void* w, void* y, const ConvGeom& g
   ++g_launches;
 }
 
+// Depthwise KH x KW convolution (groups == C == O, one input channel per filter: MobileNet-class layers; arithmetic
+// src/relay/qnn/op/convolution.cc:272-413 of the reference) on dense channels-last 8-bit tensors.  One thread owns
+// 16 consecutive channels of one output pixel: per tap one 128-bit activation load and one 128-bit load of the
+// tap-major weights [KH*KW][C] (L1-resident), 16 integer MACs.  Taps outside the image read the zero point, so
+// that  acc = sum_taps x' * w  and the per-channel constant  corr[c] = -zp_a * sum_taps w[c]  (int32 ring, added
+// by the epilogue) give exactly  sum_{in-image taps} (x - zp_a) * w .  3-D grid: no 64-bit index arithmetic.
+// Epilogue: the host-folded FastEpi form when available (corr is then already inside its table), else the
+// generic epilogue_one.
+template <bool AU, bool WU>
+__global__ void __launch_bounds__(256) dwconv_nhwc_kernel(const uint8_t* __restrict__ x, const uint8_t* __restrict__ w,
+                                                          const int32_t* __restrict__ corr, void* __restrict__ y,
+                                                          ConvGeom g, EpiParams e, FastEpi f) {
+  const int cg = g.C >> 4;
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t >= g.OW * cg) return;
+  const int ox = t / cg, c0 = (t - ox * cg) * 16;
+  const int oy = blockIdx.y, n = blockIdx.z;
+  const uint32_t zp4 = (uint32_t)(g.zp_a & 0xFF) * 0x01010101u;
+  int32_t acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) acc[i] = 0;
+  const uint8_t* img = x + (long long)n * g.H * g.W * g.C + c0;
+  for (int r = 0; r < g.KH; ++r) {
+    const int iy = oy * g.sh + r * g.dh - g.pt;
+    const bool yin = iy >= 0 && iy < g.H;
+    for (int q = 0; q < g.KW; ++q) {
+      const int ix = ox * g.sw + q * g.dw - g.pl;
+      uint4 a = make_uint4(zp4, zp4, zp4, zp4);
+      if (yin && ix >= 0 && ix < g.W) a = __ldg((const uint4*)(img + ((long long)iy * g.W + ix) * g.C));
+      const uint4 b = __ldg((const uint4*)(w + (long long)(r * g.KW + q) * g.C + c0));
+      const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const uint32_t ab = (aw[i >> 2] >> (8 * (i & 3))) & 0xFFu, bb = (bw[i >> 2] >> (8 * (i & 3))) & 0xFFu;
+        const int av = AU ? (int)ab : (int)(int8_t)ab, bv = WU ? (int)bb : (int)(int8_t)bb;
+        acc[i] += av * bv;
+      }
+    }
+  }
+  const long long idx0 = (((long long)n * g.OH + oy) * g.OW + ox) * g.C + c0;
+  const bool out8 = e.out_dtype == kU8 || e.out_dtype == kI8;
+  if (f.enabled && !f.has_sum && out8) {
+    uint32_t o4[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t word = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int4 tb = __ldg(f.tabA + c0 + 4 * i + j);
+        const long long cc = ((long long)tb.w << 32) | (unsigned long long)(uint32_t)tb.z;
+        const int32_t v = (int32_t)(((long long)acc[4 * i + j] * (long long)tb.x + cc) >> 32) >> tb.y;
+        word |= (uint32_t)(min(max(v, f.lo), f.hi) & 0xFF) << (8 * j);
+      }
+      o4[i] = word;
+    }
+    *(uint4*)((uint8_t*)y + idx0) = make_uint4(o4[0], o4[1], o4[2], o4[3]);
+  } else {
+#pragma unroll 1
+    for (int i = 0; i < 16; ++i) {
+      const int32_t a = (int32_t)((uint32_t)acc[i] + (corr ? (uint32_t)corr[c0 + i] : 0u));
+      store_from_i32(y, e.out_dtype, idx0 + i, epilogue_one(a, c0 + i, idx0 + i, e));
+    }
+  }
+}
+
+bool dwconv_nhwc_supported(const ConvGeom& g) {
+  return g.groups == g.C && g.O == g.C && (g.C % 16) == 0 && g.N <= 65535 && g.OH <= 65535 && g.zp_w == nullptr &&
+         g.zp_w0 == 0 && g.KH * g.KW <= 49;
+}
+
+void launch_dwconv_nhwc(const void* x, const void* w_tap, const int32_t* corr, void* y, const ConvGeom& g,
+                        const EpiParams& e, const FastEpi& f, cudaStream_t s) {
+  if ((long long)g.N * g.OH * g.OW == 0) return;
+  dim3 grid((unsigned)((g.OW * (g.C / 16) + 255) / 256), (unsigned)g.OH, (unsigned)g.N);
+  const uint8_t* xp = (const uint8_t*)x;
+  const uint8_t* wp = (const uint8_t*)w_tap;
+  const bool au = g.a_dtype == kU8, wu = g.w_dtype == kU8;
+  if (au && wu) dwconv_nhwc_kernel<true, true><<<grid, 256, 0, s>>>(xp, wp, corr, y, g, e, f);
+  else if (au) dwconv_nhwc_kernel<true, false><<<grid, 256, 0, s>>>(xp, wp, corr, y, g, e, f);
+  else if (wu) dwconv_nhwc_kernel<false, true><<<grid, 256, 0, s>>>(xp, wp, corr, y, g, e, f);
+  else dwconv_nhwc_kernel<false, false><<<grid, 256, 0, s>>>(xp, wp, corr, y, g, e, f);
+  ++g_launches;
+}
+
 // GEMM fallback (qnn.dense dense.cc:160-205, qnn.batch_matmul batch_matmul.cc:161-200): one warp per
 // output row-tile would be faster; this is the correctness path for odd K / non-zero weight zp.
 template <bool AU, bool WU>

@@ -935,6 +935,38 @@ static void plan_conv(Planner& P, int nid, bool composite) {
       if (launch_tc(t, c.s) != 0) fail("tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
       c.tc_mark();
     });
+  } else if (P.rt->conv_impl != "simt" && phys == kNHWC && Cg == 1 && all_zero(ci.zp_w) && dwconv_nhwc_supported(g)) {
+    // depthwise: dedicated channels-last kernel (16 channels per thread), tap-major weights
+    const int KK = g.KH * g.KW;
+    std::vector<uint8_t> w_tap((size_t)KK * g.C);
+    std::vector<int32_t> corr(g.C, 0);
+    for (int c = 0; c < g.C; ++c) {
+      long long sum = 0;
+      for (int t = 0; t < KK; ++t) {
+        const uint8_t b = w_ohwi[(size_t)c * KK + t];
+        w_tap[(size_t)t * g.C + c] = b;
+        sum += g.w_dtype == kU8 ? (int)b : (int)(int8_t)b;
+      }
+      corr[c] = (int32_t)(0u - (uint32_t)g.zp_a * (uint32_t)(int32_t)sum);
+    }
+    void* wdev = P.dev_upload(w_tap.data(), w_tap.size());
+    const int32_t* corr_dev = g.zp_a != 0 ? (const int32_t*)P.dev_upload(corr.data(), corr.size() * 4) : nullptr;
+    FastEpi fe;
+    memset(&fe, 0, sizeof(fe));
+    if (composite && !ci.float_mode) {
+      std::vector<int32_t> bias2;
+      if (ci.has_const_bias || g.zp_a != 0) bias2 = add_vec(ci.bias_host, corr, g.O);
+      build_fast_epi(P, ci, bias2, abs_row_sums(w_ohwi.data(), g.O, KK, g.w_dtype), g.O, Y.dtype, &fe);
+    }
+    if (!ci.float_mode && ci.has_const_bias) epi.bias = (const int32_t*)P.dev_upload(ci.bias_host.data(), ci.bias_host.size() * 4);
+    snprintf(desc, sizeof(desc), "%s -> CUDA-core depthwise conv (NHWC, 16 ch/thread) N=%d %dx%dx%d -> %dx%d k%dx%d s%d epi=%s",
+             n.name.c_str(), g.N, g.H, g.W, g.C, g.OH, g.OW, g.KH, g.KW, g.sh, fe.enabled && !fe.has_sum ? "fast" : "generic");
+    P.add_step(desc, [=](RunCtx& c) {
+      EpiParams e = epi;
+      if (bias_eid >= 0) e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
+      if (sum_eid >= 0) e.sum = c.ptr(sum_eid, phys);
+      launch_dwconv_nhwc(c.ptr(x_eid, phys), wdev, corr_dev, c.ptr(y_eid, phys), g, e, fe, c.s);
+    });
   } else {
     void* wdev = P.dev_upload(w_ohwi.data(), w_ohwi.size());
     if (!ci.float_mode && ci.has_const_bias) epi.bias = (const int32_t*)P.dev_upload(ci.bias_host.data(), ci.bias_host.size() * 4);

@@ -155,11 +155,14 @@ def test_tcgen05_batch_matmul_vs_oracle():
 # ---- implicit-GEMM convolution (TMA im2col mode) and the folded epilogue ----------------------------
 def _chain_conv(n, ic, h, w, oc, k, stride, pad, dil, zp_a, per_channel, relu, with_sum, seed, nhwc=False,
                 out_scale=None, raw=False, rounding="None", xdt="uint8", sum_scales=(0.3, 15, 0.2, 4), zp_relu=0,
-                out_dt="uint8", clip=None):
+                out_dt="uint8", clip=None, groups=1):
     rng = np.random.default_rng(seed)
     dl, kl = ("NHWC", "HWIO") if nhwc else ("NCHW", "OIHW")
     d_shape = (n, h, w, ic) if nhwc else (n, ic, h, w)
-    w_shape = (k, k, ic, oc) if nhwc else (oc, ic, k, k)
+    w_shape = (k, k, ic // groups, oc) if nhwc else (oc, ic // groups, k, k)
+    if groups > 1 and nhwc:
+        kl = "HWOI" if groups == ic else kl
+        w_shape = (k, k, oc, 1) if groups == ic else w_shape
     lo, hi = (0, 256) if xdt == "uint8" else (-128, 128)
     x = rng.integers(lo, hi, d_shape).astype(xdt)
     wt = rng.integers(-127, 128, w_shape).astype("int8")
@@ -168,7 +171,8 @@ def _chain_conv(n, ic, h, w, oc, k, stride, pad, dil, zp_a, per_channel, relu, w
         else np.float32(1.0 / (127.0 * np.sqrt(k * k * ic)))
     data = R.var("data", d_shape, xdt)
     e = R.qnn_conv2d(data, R.const(wt), zp_a, 0, s_x, R.const(s_w) if per_channel else s_w, (k, k), oc,
-                     strides=(stride, stride), padding=(pad, pad), dilation=(dil, dil), data_layout=dl, kernel_layout=kl)
+                     strides=(stride, stride), padding=(pad, pad), dilation=(dil, dil), data_layout=dl, kernel_layout=kl,
+                     groups=groups)
     args = {"data": x}
     params = [data]
     if not raw:
@@ -275,6 +279,33 @@ def test_fast_epilogue_clamp_variants(name, stride):
     out, mod, _ = run_gpu(func, args, conv_impl="tc")
     assert "epi=fast" in mod.plan_summary(), mod.plan_summary()
     np.testing.assert_equal(out, ref)
+
+
+DEPTHWISE_CASES = {
+    # name: (n, c, h, w, k, stride, pad, zp_a, per_channel, relu, xdt, raw)
+    "dw_c32_3x3_s1": (2, 32, 14, 14, 3, 1, 1, 0, True, True, "uint8", False),
+    "dw_c96_3x3_s2_zp": (2, 96, 15, 13, 3, 2, 1, 128, True, True, "uint8", False),
+    "dw_c16_5x5_p2": (1, 16, 9, 9, 5, 1, 2, 7, True, False, "uint8", False),
+    "dw_c48_3x3_s8": (3, 48, 10, 10, 3, 1, 1, 0, False, True, "int8", False),
+    "dw_c64_3x3_raw": (2, 64, 8, 8, 3, 1, 1, 77, True, True, "uint8", True),
+    "dw_c144_3x3_p0": (1, 144, 12, 12, 3, 2, 0, 5, True, True, "uint8", False),
+}
+
+
+@pytest.mark.parametrize("name", list(DEPTHWISE_CASES))
+def test_depthwise_conv_vs_oracle(name):
+    """Depthwise qnn.conv2d (groups == channels) through the dedicated channels-last kernel, the generic CUDA-core
+    kernel ("simt") and the oracle: identical bits."""
+    n, c, h, w, k, stride, pad, zp_a, per_channel, relu, xdt, raw = DEPTHWISE_CASES[name]
+    func, args = _chain_conv(n, c, h, w, c, k, stride, pad, 1, zp_a, per_channel, relu, False, seed=len(name) + c, xdt=xdt,
+                             raw=raw, groups=c, out_scale=0.003)
+    ref, _ = interp.run_expr(func, args)
+    out, mod, _ = run_gpu(func, args)
+    assert "depthwise conv" in mod.plan_summary(), mod.plan_summary()
+    np.testing.assert_equal(out, ref)
+    out2, mod2, _ = run_gpu(func, args, conv_impl="simt")
+    assert "depthwise conv" not in mod2.plan_summary()
+    np.testing.assert_equal(out2, ref)
 
 
 def test_implicit_conv_raw_int32_and_generic_epilogue():

@@ -283,9 +283,49 @@ __global__ void qnn_add_kernel(const void* __restrict__ a, const void* __restric
     store_from_i32(y, dtype, i, qnn_add_one(load_as_i32(a, dtype, i), load_as_i32(b, dtype, i), 0, e));
 }
 
+// 8-bit qnn.add through two 256-entry tables: both operands are bytes, so each side's requantize (add.cc:40-93,
+// the exact requantize_one) is tabulated once per block in shared memory and the per-element work is two lookups,
+// one ring add and the clamp -- the kernel is then HBM-bound instead of bound by two int64 fixed-point multiplies.
+__global__ void __launch_bounds__(256) qnn_add_lut_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
+                                                          uint4* __restrict__ y, int dtype, long long nv, EpiParams e) {
+  __shared__ int32_t tl[256], tr[256];
+  {
+    const int i = threadIdx.x;
+    const int32_t v = dtype == kU8 ? i : (int32_t)(int8_t)i;
+    tl[i] = e.lhs_identity ? v : requantize_one(v, 0, e.lhs);
+    const int32_t qb = e.rhs_identity ? v : requantize_one(v, 0, e.rhs);
+    tr[i] = (int32_t)((uint32_t)qb - (uint32_t)e.sum_zp_out);
+  }
+  __syncthreads();
+  for (long long i = blockIdx.x * 256LL + threadIdx.x; i < nv; i += (long long)gridDim.x * 256) {
+    const uint4 va = __ldg(a + i), vb = __ldg(b + i);
+    const uint32_t pa[4] = {va.x, va.y, va.z, va.w}, pb[4] = {vb.x, vb.y, vb.z, vb.w};
+    uint32_t po[4];
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      uint32_t o = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int32_t s = (int32_t)((uint32_t)tl[(pa[w] >> (8 * k)) & 0xFF] + (uint32_t)tr[(pb[w] >> (8 * k)) & 0xFF]);
+        o |= ((uint32_t)min(max(s, e.sum_qmin), e.sum_qmax) & 0xFF) << (8 * k);
+      }
+      po[w] = o;
+    }
+    y[i] = make_uint4(po[0], po[1], po[2], po[3]);
+  }
+}
+
 void launch_qnn_add(const void* a, const void* b, void* y, int dtype, long long n, const EpiParams& e,
                     cudaStream_t s) {
   if (n == 0) return;
+  if ((dtype == kU8 || dtype == kI8) && (n & 15) == 0 && n >= 4096 &&
+      ((((uintptr_t)a) | ((uintptr_t)b) | ((uintptr_t)y)) & 15) == 0) {
+    const long long nv = n >> 4;
+    const int nb = (int)std::min<long long>((nv + 255) / 256, 148LL * 8);
+    qnn_add_lut_kernel<<<nb, 256, 0, s>>>((const uint4*)a, (const uint4*)b, (uint4*)y, dtype, nv, e);
+    ++g_launches;
+    return;
+  }
   const long long work = (dtype == kU8 || dtype == kI8) && (n & 15) == 0 ? n >> 4 : n;
   qnn_add_kernel<<<blocks_for(work, 256), 256, 0, s>>>(a, b, y, dtype, n, e);
   ++g_launches;

@@ -308,6 +308,34 @@ def test_depthwise_conv_vs_oracle(name):
     np.testing.assert_equal(out2, ref)
 
 
+QADD_CASES = [
+    # (dtype, lhs_scale, lhs_zp, rhs_scale, rhs_zp, out_scale, out_zp)
+    ("uint8", 0.02, 128, 0.03, 127, 0.05, 128), ("uint8", 0.5, 3, 0.5, 3, 0.5, 3), ("uint8", 0.25, 0, 0.5, 10, 0.125, 20),
+    ("int8", 0.02, -5, 0.013, 7, 0.031, -3), ("int8", 1.0, 0, 0.5, 0, 0.25, 0), ("uint8", 0.001, 255, 7.5, 0, 0.9, 1),
+]
+
+
+@pytest.mark.parametrize("cfg", QADD_CASES, ids=[str(i) for i in range(len(QADD_CASES))])
+def test_qnn_add_standalone_vs_oracle(cfg):
+    """Un-fused qnn.add on 8-bit tensors (table-lookup kernel for >= 4096 elements, generic kernel below): every byte
+    pair of the full 256 x 256 input space appears."""
+    dt, ls, lz, rs, rz, os_, oz = cfg
+    lo = 0 if dt == "uint8" else -128
+    a = (np.arange(65536) % 256 + lo).astype(dt).reshape(4, 64, 256)
+    b = (np.arange(65536) // 256 + lo).astype(dt).reshape(4, 64, 256)
+    va, vb = R.var("a", a.shape, dt), R.var("b", b.shape, dt)
+    func = R.Function([va, vb], R.qnn_add(va, vb, ls, lz, rs, rz, os_, oz))
+    ref, _ = interp.run_expr(func, {"a": a, "b": b})
+    out, mod, _ = run_gpu(func, {"a": a, "b": b})
+    np.testing.assert_equal(out, ref)
+    wa, wb = R.var("a", (3, 5), dt), R.var("b", (3, 5), dt)
+    small = R.Function([wa, wb], R.qnn_add(wa, wb, ls, lz, rs, rz, os_, oz))
+    sa, sb = a.reshape(-1)[1000:1015].reshape(3, 5), b.reshape(-1)[5000:5015].reshape(3, 5)
+    ref2, _ = interp.run_expr(small, {"a": sa, "b": sb})
+    out2, _, _ = run_gpu(small, {"a": sa, "b": sb})
+    np.testing.assert_equal(out2, ref2)
+
+
 def test_implicit_conv_raw_int32_and_generic_epilogue():
     # plain qnn.conv2d (int32 accumulators out) through the implicit path with border correction
     func, args = _chain_conv(2, 64, 10, 10, 64, 3, 1, 1, 1, 77, True, True, False, seed=3, raw=True)

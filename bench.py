@@ -168,6 +168,9 @@ def main():
 
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # NCCL prints its version banner (NCCL_DEBUG=VERSION/INFO) on stdout, where the ONE JSON line goes: send it
+        # to stderr instead
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():

@@ -140,7 +140,7 @@ def run_reference(args, rank):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": time.perf_counter() - t0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
 
 
 def _ncu_traffic():
@@ -153,8 +153,21 @@ def _ncu_traffic():
         return None
 
 
+_JSON_OUT = sys.stdout
+
+
+def _claim_stdout():
+    """stdout carries exactly ONE JSON line: keep a private handle to it and point file descriptor 1 at stderr, so
+    that nothing a library prints (NCCL's version banner, for one) can land beside the line."""
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
 def main():
     args = parse()
+    _claim_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -168,9 +181,6 @@ def main():
 
     torch.cuda.set_device(local_rank)
     if world > 1:
-        # NCCL prints its version banner (NCCL_DEBUG=VERSION/INFO) on stdout, where the ONE JSON line goes: send it
-        # to stderr instead
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
@@ -290,7 +300,7 @@ def main():
         rate = cpu_oracle_rate(args.model, sample)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{sample} images of the same workload, oracle (C + OpenMP) with trace"}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 

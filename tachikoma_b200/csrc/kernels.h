@@ -25,8 +25,9 @@ void launch_conv2d_simt(const void* x, const void* w, void* y, const ConvGeom& g
                         cudaStream_t s);
 // depthwise convolution on dense channels-last 8-bit tensors; w_tap: [KH*KW][C] (tap-major), corr[c] = -zp_a*sum_taps w
 bool dwconv_nhwc_supported(const ConvGeom& g);
-void launch_dwconv_nhwc(const void* x, const void* w_tap, const int32_t* corr, void* y, const ConvGeom& g,
-                        const EpiParams& e, const FastEpi& f, cudaStream_t s);
+// w_row3 (3x3 kernels, may be null): [3][C] words {w(r,0), w(r,1), w(r,2), 0} for the dp4a kernel
+void launch_dwconv_nhwc(const void* x, const void* w_tap, const void* w_row3, const int32_t* corr, void* y,
+                        const ConvGeom& g, const EpiParams& e, const FastEpi& f, cudaStream_t s);
 // Y[b,m,n] = sum_k (X[b,m,k]-zpx)(W[b?,n,k]-zpw); w_batched: W has a batch dim of B, else shared.
 void launch_gemm_simt(const void* x, const void* w, void* y, int B, int M, int N, int K, int w_batched,
                       int x_dtype, int w_dtype, int32_t zpx, int32_t zpw, const EpiParams& e, cudaStream_t s);

@@ -950,6 +950,14 @@ static void plan_conv(Planner& P, int nid, bool composite) {
       corr[c] = (int32_t)(0u - (uint32_t)g.zp_a * (uint32_t)(int32_t)sum);
     }
     void* wdev = P.dev_upload(w_tap.data(), w_tap.size());
+    void* wrow_dev = nullptr;
+    if (g.KH == 3 && g.KW == 3) {  // row-packed weights for the dp4a kernel: word (r, c) = {w(r,0), w(r,1), w(r,2), 0}
+      std::vector<uint8_t> w_row((size_t)3 * g.C * 4, 0);
+      for (int c = 0; c < g.C; ++c)
+        for (int rr = 0; rr < 3; ++rr)
+          for (int q = 0; q < 3; ++q) w_row[((size_t)rr * g.C + c) * 4 + q] = w_ohwi[(size_t)c * KK + rr * 3 + q];
+      wrow_dev = P.dev_upload(w_row.data(), w_row.size());
+    }
     const int32_t* corr_dev = g.zp_a != 0 ? (const int32_t*)P.dev_upload(corr.data(), corr.size() * 4) : nullptr;
     FastEpi fe;
     memset(&fe, 0, sizeof(fe));
@@ -965,7 +973,7 @@ static void plan_conv(Planner& P, int nid, bool composite) {
       EpiParams e = epi;
       if (bias_eid >= 0) e.bias = (const int32_t*)c.ptr(bias_eid, kLogical);
       if (sum_eid >= 0) e.sum = c.ptr(sum_eid, phys);
-      launch_dwconv_nhwc(c.ptr(x_eid, phys), wdev, corr_dev, c.ptr(y_eid, phys), g, e, fe, c.s);
+      launch_dwconv_nhwc(c.ptr(x_eid, phys), wdev, wrow_dev, corr_dev, c.ptr(y_eid, phys), g, e, fe, c.s);
     });
   } else {
     void* wdev = P.dev_upload(w_ohwi.data(), w_ohwi.size());

@@ -1131,8 +1131,24 @@ void launch_unfold_rows_nchw(const void* x, void* y, const ConvGeom& g, cudaStre
   ++g_launches;
 }
 
+// 1x1 / stride-1 / unpadded convolution whose channel count is not a multiple of 16 (e.g. 24): the im2col matrix is
+// the activation matrix with every row zero-padded from C to Kp bytes; 8 bytes per thread, 32-bit indices.
+__global__ void pad_rows8_kernel(const uint2* __restrict__ x, uint2* __restrict__ a, unsigned total, int c8, int k8) {
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const unsigned m = i / (unsigned)k8, ch = i - m * (unsigned)k8;
+  a[i] = ch < (unsigned)c8 ? __ldg(x + (size_t)m * c8 + ch) : make_uint2(0u, 0u);
+}
+
 void launch_im2col(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream_t s) {
   const long long M = (long long)g.N * g.OH * g.OW;
+  if (g.KH == 1 && g.KW == 1 && g.sh == 1 && g.sw == 1 && !(g.pt | g.pl | g.pb | g.pr) && (g.C & 15) != 0 && (g.C & 7) == 0 &&
+      (Kp & 7) == 0 && M * (Kp >> 3) < (1LL << 31) && M > 0 && ((((uintptr_t)x) | ((uintptr_t)a)) & 7) == 0) {
+    const unsigned total = (unsigned)(M * (Kp >> 3));
+    pad_rows8_kernel<<<(total + 255) / 256, 256, 0, s>>>((const uint2*)x, (uint2*)a, total, g.C >> 3, Kp >> 3);
+    ++g_launches;
+    return;
+  }
   const long long total = (g.C & 15) == 0 ? M * (Kp >> 4) : M * Kp;
   if (total == 0) return;
   im2col_kernel<<<blocks_for(total, 256), 256, 0, s>>>((const uint8_t*)x, (uint8_t*)a, g, Kp);

@@ -208,6 +208,8 @@ IMPLICIT_CASES = {
     "c64_5x5_p2_big": (4, 64, 31, 29, 72, 5, 1, 2, 1, 1, True, True, False),
     "c512_1x1": (2, 512, 7, 7, 1000, 1, 1, 0, 1, 4, True, False, False),
     "c64_3x3_p0_s8": (2, 64, 12, 12, 64, 3, 1, 0, 1, 128, True, True, False),
+    "c24_1x1_rowpad": (2, 24, 9, 9, 40, 1, 1, 0, 1, 6, True, True, False),   # K = 24 padded to 32 by pad_rows8_kernel
+    "c40_1x1_rowpad_sum": (1, 40, 7, 5, 24, 1, 1, 0, 1, 200, False, False, True),
 }
 
 

@@ -117,6 +117,10 @@ bool tc_implicit_conv_supported(const ConvGeom& g) {
 }
 
 static int pick_bn(long long mtiles, int N) {
+  if (const char* f = getenv("TKB_BN")) {  // tuning experiments only
+    const int v = atoi(f);
+    if (v == 64 || v == 128 || v == 256) return v;
+  }
   const int cand[3] = {256, 128, 64};
   int best = 64;
   long long best_cost = -1;

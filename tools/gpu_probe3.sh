@@ -1,5 +1,5 @@
 #!/bin/bash
 cd "$(dirname "$0")/.."
-for cfg in "64 56 64 3 1"; do
-  for dbg in 0 1 4 5 32 33 36 37 8; do TKB_DBG=$dbg timeout 120 python tools/conv_probe.py $cfg 2>&1 | tail -1 | cut -c1-90; done
+for cfg in "256 14 256 3 1" "512 7 512 3 1" "128 28 256 3 2" "256 14 512 3 2" "64 56 128 3 2"; do
+  for bn in 64 128 256; do TKB_BN=$bn timeout 120 python tools/conv_probe.py $cfg 2>&1 | tail -1 | cut -c1-70 | sed "s/^/bn=$bn /"; done
 done

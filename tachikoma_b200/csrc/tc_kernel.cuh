@@ -169,7 +169,7 @@ static __device__ __noinline__ void epi_slow_elem(int32_t acc, int col, long lon
 
 // 32 columns of one output row.  r: raw TMEM accumulators; ncols: valid columns (1..32); col0: absolute
 // first column; idx0: linear output index of (row, col0); tab_addr: shared address of this chunk's table.
-template <int MODE>
+template <int MODE, bool AL8 = false>
 __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const TcKernelParams& p, uint32_t tab_addr,
                                                bool row_valid, int ncols, int col0, long long idx0,
                                                const int32_t* drow, bool vec_ok) {
@@ -236,15 +236,23 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const Tc
         w[i] = word;
       }
     }
-    uint4* dst = (uint4*)((uint8_t*)p.y + idx0);
-    dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
-    dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    uint8_t* dst8 = (uint8_t*)p.y + idx0;
+    if ((p.dbg & 64) && w[0] != 0x9e3779b9u) return;  // timing experiment: no global stores
+    if (!AL8 || (((uintptr_t)dst8) & 15) == 0) {
+      uint4* dst = (uint4*)dst8;
+      dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+      dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    } else {  // rows that are 8- but not 16-byte multiples (e.g. 1000 classes)
+      uint2* dst = (uint2*)dst8;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dst[i] = make_uint2(w[2 * i], w[2 * i + 1]);
+    }
   }
 }
 
 // Drain one accumulator stage: the calling epilogue warp owns TMEM lanes 32*q .. +31 and columns
 // [cbeg0, cbeg0 + cspan) of the tile; `row` is the output row (pixel) of this lane.
-template <int BN, int MODE>
+template <int BN, int MODE, bool AL8 = false>
 __device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t tmem_base, uint32_t lt, int q, int cbeg0, int cspan,
                                                int lane, int row, bool row_valid, int b, int n0, uint32_t tab_base,
                                                bool vec_ok, uint64_t* tempty, uint64_t* tfull) {
@@ -285,7 +293,7 @@ __device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[as]);
     }
-    epilogue_chunk<MODE>(ra, p, tab_base + c * 16, row_valid, min(32, cend - c), n0 + c, row_off + n0 + c, drow, vec_ok);
+    epilogue_chunk<MODE, AL8>(ra, p, tab_base + c * 16, row_valid, min(32, cend - c), n0 + c, row_off + n0 + c, drow, vec_ok);
     if (!more_b) break;
     tmem_ld_wait32(rb);
     const bool more_a = c + 64 < cend;
@@ -295,7 +303,7 @@ __device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[as]);
     }
-    epilogue_chunk<MODE>(rb, p, tab_base + (c + 32) * 16, row_valid, min(32, cend - c - 32), n0 + c + 32,
+    epilogue_chunk<MODE, AL8>(rb, p, tab_base + (c + 32) * 16, row_valid, min(32, cend - c - 32), n0 + c + 32,
                          row_off + n0 + c + 32, drow, vec_ok);
     if (!more_a) break;
   }
@@ -432,7 +440,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     const int q = warp & 3, grp = (warp - 2) >> 2;
     const int et = threadIdx.x - 64 - grp * EPI_GROUP_THREADS;  // 0..EPI_GROUP_THREADS-1 within the group
     const int esz = dtype_size(p.e.out_dtype);
-    const bool vec_ok = ((long long)p.N * esz) % 16 == 0 && (((uintptr_t)p.y) & 15) == 0 &&
+    // 8-bit outputs without a residual only need 8-byte row alignment (the chunk store picks 16- or 8-byte vectors)
+    constexpr bool AL8 = BN == 64 && mode_is_fast(MODE) && !mode_is_sum(MODE);
+    constexpr int row_align = AL8 ? 8 : 16;
+    const bool vec_ok = ((long long)p.N * esz) % row_align == 0 && (((uintptr_t)p.y) & 15) == 0 &&
                         (p.sum == nullptr || (((uintptr_t)p.sum) & 15) == 0) &&
                         (MODE == kModeRaw ? (p.e.out_dtype == kI32 && (p.e.bias == nullptr || (((uintptr_t)p.e.bias) & 15) == 0))
                                           : (p.e.out_dtype == kU8 || p.e.out_dtype == kI8));
@@ -462,7 +473,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         row_valid = qp < p.OW;
         row = (mt / p.win_qt) * p.OW + qp;
       }
-      epi_drain_tile<BN, MODE>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, b, n0, tab_base, vec_ok, tempty, tfull);
+      epi_drain_tile<BN, MODE, AL8>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, b, n0, tab_base, vec_ok, tempty, tfull);
     }
   }
   tc_fence_before();

@@ -411,6 +411,16 @@ def test_models_bit_exact_with_trace(name, kw, impl):
     assert mod.launch_count() > 0
 
 
+def test_gpu_trace_passes_record_by_record_replay():
+    """the GPU-produced trace is a valid witness -- every record re-computed on the oracle
+    from the recorded inputs alone, chain and constants checked (oracle/replay.py)."""
+    from oracle import replay
+    func = models.resnet18(batch=2, image=64, num_classes=100)
+    x = np.ascontiguousarray(models.synthetic_input("resnet18", 2)[:, :, :64, :64])
+    _, mod, (js, consts, _ins) = run_gpu(func, {"data": x}, conv_impl="tc", trace=True)
+    assert replay.verify_trace(js, mod.trace_blob(), consts) == []
+
+
 def test_resnet18_full_size_properties():
     """Full BASELINE size (224x224, batch 8 here to bound oracle time): GPU tc == GPU simt bit for bit, and the
     first image equals the oracle."""

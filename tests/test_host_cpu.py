@@ -146,3 +146,54 @@ def test_product_never_imports_oracle():
             if fn.endswith((".py", ".cu", ".cuh", ".h", ".cc")):
                 src = open(os.path.join(dirpath, fn)).read()
                 assert "oracle" not in src.replace("test oracle", ""), f"{fn} mentions the oracle"
+
+
+# ---- trace reader / verifier: record-by-record replay on the oracle ---------------
+def _oracle_trace(func, ins):
+    part = T.partition_for_tachikoma(func)
+    sym, js, names, consts = T.serialize(part)
+    _, recs = interp.run_json(js, consts, [ins[p.name] for p in part.params], want_trace=True)
+    return js, consts, recs
+
+
+def test_trace_replay_accepts_a_valid_trace_and_pinpoints_tampering():
+    from oracle import replay
+    func, ins = _small_graph()
+    js, consts, recs = _oracle_trace(func, ins)
+    blob = interp.save_ndarray_list(recs)
+    assert replay.verify_trace(js, blob, consts) == []
+    # flip one output element of one record: exactly that node (and its consumers' chain check) is reported
+    out_idx = [i for i, (n, _) in enumerate(recs) if n.endswith("____output-num:0")]
+    i = out_idx[0]
+    name, arr = recs[i]
+    bad = arr.copy()
+    bad.reshape(-1)[3] ^= 1
+    tampered = list(recs)
+    tampered[i] = (name, bad)
+    problems = replay.verify_trace(js, interp.save_ndarray_list(tampered), consts)
+    nid = int(re.search(r"topo-index:(\d+)", name).group(1))
+    assert any(p.startswith("node %d " % nid) and "differ from the oracle" in p for p in problems), problems
+    # a tampered weight is caught against the module's constants
+    w_idx = next(i for i, (n, a) in enumerate(recs) if "input-num:1" in n)
+    name, arr = recs[w_idx]
+    bad = arr.copy()
+    bad.reshape(-1)[0] += 1
+    tampered = list(recs)
+    tampered[w_idx] = (name, bad)
+    problems = replay.verify_trace(js, interp.save_ndarray_list(tampered), consts)
+    assert any("differs from constant node" in p for p in problems), problems
+    # a dropped record is reported, not skipped
+    problems = replay.verify_trace(js, interp.save_ndarray_list(recs[:-1]), consts)
+    assert problems and "expected" in problems[-1] or "no records" in problems[-1]
+
+
+@pytest.mark.parametrize("name,kw", [("mlp", dict(batch=4)), ("lenet5", dict(batch=2)),
+                                     ("resnet18", dict(batch=1, image=32, num_classes=10))])
+def test_trace_replay_models(name, kw):
+    from oracle import replay
+    func = models.MODELS[name](**kw)
+    x = models.synthetic_input(name, kw["batch"])
+    if "image" in kw:
+        x = np.ascontiguousarray(x[:, :, :kw["image"], :kw["image"]])
+    js, consts, recs = _oracle_trace(func, {"data": x})
+    assert replay.verify_trace(js, interp.save_ndarray_list(recs), consts) == []

@@ -27,6 +27,8 @@ def build(force=False, verbose=False):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
+    if os.environ.get("TKB_BUILD_TIMELINE"):  # device timeline stamps in the tcgen05 kernels (tc_kernel.cuh tl_stamp)
+        flags.append("-DTKB_TIMELINE")
     objs = []
     procs = []
     for src in SOURCES:

@@ -42,9 +42,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nimg = p.M / (p.OH * p.OW);
-  const long long total_tiles = (p.dbg & 8) ? 0 : (long long)nimg * p.hTpi;  // dbg 8: launch + prologue + teardown only
+  const int total_tiles = (p.dbg & 8) ? 0 : nimg * p.hTpi;  // host: < 2^30  // dbg 8: launch + prologue + teardown only
 
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  TKB_TL_IF(threadIdx.x == 0, p, 0);
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     for (int i = 0; i < p.a_stages; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
@@ -57,6 +58,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  TKB_TL_IF(threadIdx.x == 0, p, 1);
 
   if (warp == 0) {
     // ===== producer: weights once (constants: they do not depend on the preceding kernel), then patches =====
@@ -70,8 +72,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
     const uint32_t patch_bytes = (uint32_t)(p.hRows * p.hWp * p.bk);
     int st = 0;
     uint32_t ph = 0;
-    for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int n = (int)(tile / p.hTpi), oh0 = (int)(tile % p.hTpi) * p.hR;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int n = tile / p.hTpi, oh0 = (tile % p.hTpi) * p.hR;
       for (int cc = 0; cc < cchunks; ++cc) {
         mbar_wait(&a_empty[st], ph ^ 1);
         if (elect_one()) {
@@ -88,12 +90,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
   } else if (warp == 1) {
     // ===== MMA issuer =====
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    TKB_TL_IF(lane == 0, p, 2);
     int st = 0;
     uint32_t ph = 0, lt = 0;
     const int kper = p.bk / UMMA_K;
     const uint32_t a_base = smem_u32(smem_a), b_base = smem_u32(smem_b);
     mbar_wait(b_full, 0);
-    for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const uint32_t as = lt & 1;
       mbar_wait(&tempty[as], ((lt >> 1) & 1) ^ 1);
       tc_fence_after();
@@ -101,6 +104,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
       for (int cc = 0; cc < cchunks; ++cc) {
         mbar_wait(&a_full[st], ph);
         tc_fence_after();
+        TKB_TL_IF(lt == 0 && cc == 0 && lane == 0, p, 3);
         if (elect_one()) {
           const uint32_t slot = a_base + st * p.a_slot;
           uint32_t acc = cc != 0;
@@ -140,11 +144,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
           }
           tc_commit(&a_empty[st]);
           if (cc == cchunks - 1) tc_commit(&tfull[as]);
+          TKB_TL_IF(lt < 48 && cc == cchunks - 1, p, 16 + lt);  // per TILE here
         }
         __syncwarp();
         if (++st == p.a_stages) { st = 0; ph ^= 1; }
       }
+      TKB_TL_IF(lt == 0 && lane == 0, p, 4);
     }
+    TKB_TL_IF(lane == 0, p, 5);
   } else {
     // ===== epilogue =====
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -163,15 +170,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
     constexpr int tstep = SPLIT ? 2 : 1, cspan = SPLIT ? BN : BN / 2;
     const int cbeg0 = SPLIT ? 0 : grp * (BN / 2);
     uint32_t lt = SPLIT ? grp : 0;
-    for (long long tile = blockIdx.x + (long long)lt * gridDim.x; tile < total_tiles; tile += (long long)tstep * gridDim.x, lt += tstep) {
-      const int n = (int)(tile / p.hTpi), oh = (int)(tile % p.hTpi) * p.hR + prow;
+    for (int tile = blockIdx.x + (int)lt * gridDim.x; tile < total_tiles; tile += tstep * gridDim.x, lt += tstep) {
+      const int n = tile / p.hTpi, oh = (tile % p.hTpi) * p.hR + prow;
       const bool row_valid = slot_valid && oh < p.OH;
       const int row = (n * p.OH + oh) * p.OW + pcol;
       epi_drain_tile<BN, MODE>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, 0, 0, tab_base, vec_ok, tempty, tfull);
+      TKB_TL_IF(lt == 0 && warp == 2 && lane == 0, p, 7);
     }
+    TKB_TL_IF(warp == 2 && lane == 0, p, 8);
   }
   tc_fence_before();
   __syncthreads();
+  TKB_TL_IF(threadIdx.x == 0, p, 9);
   if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
 }
 
@@ -242,6 +252,7 @@ static int launch_halo_ts(const CUtensorMap& ta, TcKernelParams& p, int smem, cu
     attr_set = true;
   }
   const long long tiles = (long long)(p.M / (p.OH * p.OW)) * p.hTpi;
+  if (tiles > 0x3fffffffLL) return -1;  // the kernel decodes tiles in 32-bit arithmetic
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(tiles < num_sms() ? tiles : num_sms()));
   cfg.blockDim = dim3(TC_THREADS);
@@ -253,7 +264,9 @@ static int launch_halo_ts(const CUtensorMap& ta, TcKernelParams& p, int smem, cu
   cfg.attrs = attr;
   cfg.numAttrs = getenv("TKB_NO_PDL") ? 0 : 1;
   p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
+  p.tl = timeline_buf();
   if (cudaLaunchKernelEx(&cfg, tc_halo_kernel<BN, MODE, KH_, KW_, BK_, SPLIT>, ta, p) != cudaSuccess) return -1;
+  timeline_print("tc_halo", p.tl, s);
   ++g_launches;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

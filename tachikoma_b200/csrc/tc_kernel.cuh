@@ -48,10 +48,47 @@ struct TcKernelParams {
   // patch per channel chunk, taps = shifted UMMA descriptors into the patch, weights resident in shared memory
   int hR, hWp, hRows, hTpi, a_slot, a_stages;
   const uint8_t* wpack;   // packed weight tiles (tc_pack_weights) or nullptr: B comes through tmB
+  long long* tl;          // TKB_TIMELINE: clock64 stamps of CTA 0 (see tl_stamp) or nullptr
   int dbg;                // timing experiments only (TKB_DBG): 1 = no epilogue work, 2 = no B loads, 4 = no A loads
   EpiParams e;            // generic epilogue (any rounding / compute dtype / float mode / raw int32)
   FastEpi f;              // host-folded fixed-point epilogue (default QNN configuration)
 };
+
+// Device timeline of CTA 0 (TKB_TIMELINE=1, tools/conv_probe.py): slot -> clock64.  0 entry, 1 prologue done,
+// 2 griddepcontrol.wait passed, 3 first operands landed (MMA warp), 4 first tile issued, 5 all tiles issued,
+// 6 first accumulator ready (epilogue), 7 first tile drained, 8 all tiles drained, 9 teardown; 16.. = issue of the
+// first tile's k-groups (GEMM kernel) / of the CTA's tiles (halo kernel).
+// Compiled in only with -DTKB_TIMELINE (TKB_BUILD_TIMELINE=1 python -m tachikoma_b200.build --force): the stamps
+// cost ~2 % of a ResNet-18 step even when disabled at run time (hot-loop instructions, instruction cache).
+__device__ __forceinline__ void tl_stamp(const TcKernelParams& p, int slot) {
+  if (p.tl != nullptr && blockIdx.x == 0) p.tl[slot] = clock64();
+}
+#ifdef TKB_TIMELINE
+#define TKB_TL_IF(cond, p, slot) do { if (cond) tl_stamp(p, slot); } while (0)
+#else
+#define TKB_TL_IF(cond, p, slot) do { } while (0)
+#endif
+inline long long* timeline_buf() {
+  static long long* buf = [] {
+    long long* b = nullptr;
+#ifdef TKB_TIMELINE
+    if (getenv("TKB_TIMELINE") && cudaMalloc(&b, 64 * sizeof(long long)) != cudaSuccess) b = nullptr;
+#endif
+    return b;
+  }();
+  if (buf) cudaMemset(buf, 0, 64 * sizeof(long long));
+  return buf;
+}
+inline void timeline_print(const char* what, long long* buf, cudaStream_t s) {
+  if (!buf) return;
+  long long h[64];
+  if (cudaStreamSynchronize(s) != cudaSuccess || cudaMemcpy(h, buf, sizeof(h), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+  fprintf(stderr, "timeline %s (cycles since entry):", what);
+  for (int i = 1; i < 10; ++i) fprintf(stderr, " [%d]%lld", i, h[i] ? h[i] - h[0] : -1);
+  fprintf(stderr, " | issue stamps (cycles since [3]):");
+  for (int i = 16; i < 64 && h[i]; ++i) fprintf(stderr, " %lld", h[i] - h[3]);
+  fprintf(stderr, "\n");
+}
 
 __device__ __forceinline__ void tma_load_im2col_4d(void* dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h,
                                                    int n, uint16_t off_w, uint16_t off_h) {
@@ -237,7 +274,6 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const Tc
       }
     }
     uint8_t* dst8 = (uint8_t*)p.y + idx0;
-    if ((p.dbg & 64) && w[0] != 0x9e3779b9u) return;  // timing experiment: no global stores
     if (!AL8 || (((uintptr_t)dst8) & 15) == 0) {
       uint4* dst = (uint4*)dst8;
       dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
@@ -266,6 +302,7 @@ __device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t
   const uint32_t as = lt & 1;
   mbar_wait(&tfull[as], (lt >> 1) & 1);
   tc_fence_after();
+  TKB_TL_IF(lt == 0 && q == 2 && lane == 0 && cbeg0 == 0, p, 6);
   const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
   const int ncol_tile = min(BN, p.N - n0);
   const int cbeg = cbeg0, cend = min(cbeg + cspan, ncol_tile);
@@ -325,13 +362,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mtiles = p.win ? p.win_rows * p.win_qt : (p.M + BM - 1) / BM, ntiles = (p.N + BN - 1) / BN;
-  const long long total_tiles = (p.dbg & 8) ? 0 : (long long)mtiles * ntiles * p.batches;  // dbg 8: launch + prologue + teardown only
+  const int total_tiles = (p.dbg & 8) ? 0 : mtiles * ntiles * p.batches;  // (host: < 2^30) dbg 8: launch + prologue + teardown only
   const int cchunks = p.implicit ? p.C / p.bk : 0;
   const int num_kb = p.implicit ? p.KH * p.KW * cchunks : (p.K + p.bk - 1) / p.bk;
 
   // Programmatic dependent launch: let the next kernel of the stream start its own prologue as soon as SMs
   // free up; everything this kernel reads or writes in global memory comes after griddepcontrol.wait below.
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  TKB_TL_IF(threadIdx.x == 0, p, 0);
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
@@ -344,8 +382,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  TKB_TL_IF(threadIdx.x == 0, p, 1);
   // wait for the preceding kernel(s) of the stream to complete and flush (no-op without the PDL launch attribute)
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  TKB_TL_IF(threadIdx.x == 0, p, 2);
 
   // Producer and MMA warps run their loops with the whole warp converged (all lanes poll the mbarriers) and
   // guard only the issuing instructions with elect.sync: the compiler then emits the uniform-datapath
@@ -357,10 +397,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     uint32_t ph = 0;
     const bool ld_a = !(p.dbg & 4), ld_b = !(p.dbg & 2);
     const uint32_t tx_bytes = (uint32_t)((ld_a ? a_bytes : 0) + (ld_b ? b_bytes : 0));
-    for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int nt = (int)(tile % ntiles);
-      const long long t2 = tile / ntiles;
-      const int mt = (int)(t2 % mtiles), b = (int)(t2 / mtiles);
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {  // 32-bit tile decode (64-bit divisions: ~200 cycles each)
+      const int nt = tile % ntiles;
+      const int t2 = tile / ntiles;
+      const int mt = t2 % mtiles, b = t2 / mtiles;
       const int n0 = nt * BN, m0 = mt * BM;
       int cw = 0, chh = 0, cn = 0;
       if (p.implicit) {
@@ -405,7 +445,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     uint32_t ph = 0, lt = 0;
     const int kper = p.bk / UMMA_K;
     const uint32_t smem_base = smem_u32(smem);
-    for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const uint32_t as = lt & 1;
       mbar_wait(&tempty[as], ((lt >> 1) & 1) ^ 1);
       tc_fence_after();
@@ -414,6 +454,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         const int nsub = min(p.kps, num_kb - kb0);
         mbar_wait(&full[st], ph);
         tc_fence_after();
+        TKB_TL_IF(lt == 0 && kb0 == 0 && lane == 0, p, 3);
         if (elect_one()) {
           // K-major swizzled tiles: 8-row groups are 8*bk bytes apart (SBO, in desc_hi); advancing K inside the
           // swizzle row is a plain start-address offset (+32 B = +2 in the descriptor's 16-byte units).
@@ -430,11 +471,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
           }
           tc_commit(&empty[st]);  // frees the smem slot once the MMAs above have read it
           if (kb0 + nsub >= num_kb) tc_commit(&tfull[as]);
+          TKB_TL_IF(lt == 0 && kb0 / p.kps < 48, p, 16 + kb0 / p.kps);
         }
         __syncwarp();
         if (++st == p.stages) { st = 0; ph ^= 1; }
       }
+      TKB_TL_IF(lt == 0 && lane == 0, p, 4);
     }
+    TKB_TL_IF(lane == 0, p, 5);
   } else {
     // ===== epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31 =====
     const int q = warp & 3, grp = (warp - 2) >> 2;
@@ -453,10 +497,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     constexpr int tstep = SPLIT ? 2 : 1, cspan = SPLIT ? BN : BN / 2;
     const int cbeg0 = SPLIT ? 0 : grp * (BN / 2);
     uint32_t lt = SPLIT ? grp : 0;
-    for (long long tile = blockIdx.x + (long long)lt * gridDim.x; tile < total_tiles; tile += (long long)tstep * gridDim.x, lt += tstep) {
-      const int nt = (int)(tile % ntiles);
-      const long long t2 = tile / ntiles;
-      const int mt = (int)(t2 % mtiles), b = (int)(t2 / mtiles);
+    for (int tile = blockIdx.x + (int)lt * gridDim.x; tile < total_tiles; tile += tstep * gridDim.x, lt += tstep) {
+      const int nt = tile % ntiles;
+      const int t2 = tile / ntiles;
+      const int mt = t2 % mtiles, b = t2 / mtiles;
       const int n0 = nt * BN, m0 = mt * BM;
       if (mode_is_fast(MODE) && n0 != tab_n0) {
         // stage this n-tile's per-channel constants (the condition is uniform over the group's warps)
@@ -474,10 +518,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         row = (mt / p.win_qt) * p.OW + qp;
       }
       epi_drain_tile<BN, MODE, AL8>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, b, n0, tab_base, vec_ok, tempty, tfull);
+      TKB_TL_IF(lt == 0 && warp == 2 && lane == 0, p, 7);
     }
+    TKB_TL_IF(warp == 2 && lane == 0, p, 8);
   }
   tc_fence_before();
   __syncthreads();
+  TKB_TL_IF(threadIdx.x == 0, p, 9);
   if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
 }
 
@@ -523,6 +570,7 @@ static int launch_ts(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParam
   }
   const long long mt_host = p.win ? (long long)p.win_rows * p.win_qt : (p.M + BM - 1) / BM;
   const long long tiles = mt_host * ((p.N + BN - 1) / BN) * p.batches;
+  if (tiles > 0x3fffffffLL) return -1;  // the kernel decodes tiles in 32-bit arithmetic
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
   cudaLaunchConfig_t cfg = {};
@@ -535,7 +583,9 @@ static int launch_ts(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParam
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = getenv("TKB_NO_PDL") ? 0 : 1;
+  p.tl = timeline_buf();
   if (cudaLaunchKernelEx(&cfg, tc_gemm_kernel<BN, MODE, SPLIT>, ta, tb, p) != cudaSuccess) return -1;
+  timeline_print("tc_gemm", p.tl, s);
   ++g_launches;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

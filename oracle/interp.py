@@ -257,7 +257,7 @@ def eval_op(op, attrs, args):
     if op == "nn.global_avg_pool2d":
         lay = attrs["layout"]
         hw = [args[0].shape[lay.index("H")], args[0].shape[lay.index("W")]]
-        return pool2d(args[0], hw, [1, 1], [0, 0, 0, 0], lay, True, False)
+        return pool2d(args[0], hw, [1, 1], [0, 0, 0, 0], lay, 2, False)  # 2: adaptive form, divisor in the tensor dtype
     if op == "nn.pad":
         pv = np.asarray(args[1]).reshape(-1)[0]
         return np.pad(args[0], attrs["pad_width"], mode="constant", constant_values=args[0].dtype.type(pv))

@@ -309,10 +309,24 @@ void tko_qnn_add(const void* a, const void* b, int dtype, int64_t n, float sa, i
   }
 }
 
-/* nn.max_pool2d / nn.avg_pool2d on integer tensors: include/tvm/topi/nn/pooling.h:389 (adaptive,
- * used by global pooling), :600-650 (windowed).  Sum in the tensor dtype (int32 after the
- * frontend's upcast, python/tvm/relay/frontend/qnn_torch.py:587-590) and TRUNCATING division.
- * Max-pool padding reads the dtype minimum.  Strides describe (n,c,h,w) for in and out. */
+/* nn.max_pool2d / nn.avg_pool2d on integer tensors: include/tvm/topi/nn/pooling.h:384-389 (adaptive,
+ * used by global pooling: is_avg == 2), :585-650 (windowed: is_avg == 1).  The window sum is reduced
+ * IN THE TENSOR DTYPE (tvm::sum(temp(indices), daxis), :599; int32 after the frontend's upcast,
+ * python/tvm/relay/frontend/qnn_torch.py:587-590), i.e. it wraps at 8 / 16 / 32 bits.  The windowed
+ * form divides by an int32 element count (the narrow sum is promoted to int32 first, :612-648); the
+ * adaptive form multiplies its divisor up in the tensor dtype (:384-387), so the divisor wraps too
+ * (a zero divisor is a division by zero in the reference: reported here as 0, rejected by the product
+ * at init).  TRUNCATING division.  Max-pool padding reads the dtype minimum.  Strides describe
+ * (n,c,h,w) for in and out. */
+static int64_t wrap_dtype(int64_t v, int dtype) {
+  switch (dtype) {
+    case 0: return (int8_t)v;
+    case 1: return (uint8_t)v;
+    case 3: return (int16_t)v;
+    case 4: return v;
+    default: return (int32_t)v;
+  }
+}
 void tko_pool2d(const void* in, int dtype, void* out, int is_avg, int count_include_pad, int64_t N,
                 int64_t C, int64_t H, int64_t W, int64_t KH, int64_t KW, int64_t sh, int64_t sw,
                 int64_t pt, int64_t pl, int64_t pb, int64_t pr, const int64_t* is,
@@ -334,18 +348,20 @@ void tko_pool2d(const void* in, int dtype, void* out, int is_avg, int count_incl
               if (iy < 0 || iy >= H || ix < 0 || ix >= W) continue;
               int64_t v = load_int(in, dtype, n * is[0] + c * is[1] + iy * is[2] + ix * is[3]);
               if (v > best) best = v;
-              sum = wrap32((int64_t)sum + v);
+              sum = (int32_t)wrap_dtype((int64_t)sum + v, dtype);
               ++cnt;
             }
           int64_t r;
           if (!is_avg) r = best;
           else {
             int64_t div;
-            if (count_include_pad) {
+            if (is_avg == 2) {
+              div = wrap_dtype(wrap_dtype(KH, dtype) * wrap_dtype(KW, dtype), dtype);
+            } else if (count_include_pad) {
               int64_t ye = y1 < H + pb - 1 ? y1 : H + pb - 1, xe = x1 < W + pr - 1 ? x1 : W + pr - 1;
               div = (ye - y0 + 1) * (xe - x0 + 1);
             } else div = cnt > 1 ? cnt : 1;
-            r = (int32_t)sum / (int32_t)div; /* C division truncates toward zero */
+            r = div == 0 ? 0 : (int32_t)sum / (int32_t)div; /* C division truncates toward zero */
           }
           store_int(out, dtype, n * os[0] + c * os[1] + y * os[2] + x * os[3], r);
         }

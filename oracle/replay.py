@@ -109,3 +109,44 @@ def verify_trace(graph_json, blob, consts=None, stop_at_first=False):
     if extra:
         bad("records for node ids that are not kernel nodes of the graph: %s" % extra)
     return problems
+
+
+# ---- debug-executor-compatible dump (python/tvm/contrib/debugger/debug_result.py:25, :114-149, :191-202) -------------
+def load_debug_dump(directory):
+    """Read the pair the debug executor writes: ``_tvmdbg_graph_dump.json`` (nodes carry ``op``, ``name``, ``inputs``
+    as producer NAMES, ``attrs`` incl. ``T``, ``shape``) and ``output_tensors.params`` (NDArray-list blob keyed
+    ``{name}____topo-index:{i}____output-num:{j}`` over ALL nodes).  Returns (graph dict, {key: array})."""
+    import os
+    with open(os.path.join(str(directory), "_tvmdbg_graph_dump.json")) as f:
+        graph = json.load(f)
+    with open(os.path.join(str(directory), "output_tensors.params"), "rb") as f:
+        tensors = dict(interp.load_ndarray_list(f.read()))
+    return graph, tensors
+
+
+def verify_debug_dump(graph_json, directory, consts=None):
+    """Replay a debug dump against the module's tachikoma JSON graph: the dump holds one tensor per node output, so the
+    per-node input records of the trace format are rebuilt from the producers' outputs and handed to verify_trace."""
+    graph, tensors = load_debug_dump(directory)
+    g = json.loads(graph_json)
+    problems = []
+    if [n["name"] for n in graph["nodes"]] != [n["name"] for n in g["nodes"]]:
+        return ["debug dump and graph disagree on the node list"]
+    recs = []
+    for nid, n in enumerate(g["nodes"]):
+        if n["op"] != "kernel":
+            continue
+        for i, e in enumerate(n["inputs"]):
+            key = "%s____topo-index:%d____output-num:%d" % (g["nodes"][e[0]]["name"], e[0], e[1])
+            if key not in tensors:
+                problems.append("debug dump lacks %s" % key)
+                continue
+            recs.append(("%s____topo-index:%d____input-num:%d" % (n["name"], nid, i), tensors[key]))
+        key = "%s____topo-index:%d____output-num:0" % (n["name"], nid)
+        if key not in tensors:
+            problems.append("debug dump lacks %s" % key)
+            continue
+        recs.append((key, tensors[key]))
+    if problems:
+        return problems
+    return verify_trace(graph_json, interp.save_ndarray_list(recs), consts)

@@ -42,7 +42,8 @@ void launch_cast(const void* x, int x_dtype, void* y, int y_dtype, long long n, 
 void launch_bias_add(const void* x, const void* b, void* y, int dtype, long long outer, int C, long long inner,
                      cudaStream_t s);
 void launch_add_same(const void* a, const void* b, void* y, int dtype, long long n, cudaStream_t s);
-// pooling with explicit element strides (n,c,h,w) for input and output
+// pooling with explicit element strides (n,c,h,w) for input and output; is_avg: 0 max, 1 windowed average,
+// 2 adaptive / global average (divisor cast to the tensor dtype, include/tvm/topi/nn/pooling.h:384-389)
 void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_include_pad, int N, int C, int H, int W,
                    int KH, int KW, int sh, int sw, int pt, int pl, int pb, int pr, const long long* xs,
                    const long long* ys, cudaStream_t s);

@@ -535,8 +535,10 @@ struct PoolArgs {
   long long xs[4], ys[4];
 };
 
-// nn.max_pool2d / nn.avg_pool2d / global pooling on integer tensors
-// (include/tvm/topi/nn/pooling.h:389, :600-650: sum in the tensor dtype, truncating division).
+// nn.max_pool2d / nn.avg_pool2d / global pooling on integer tensors (include/tvm/topi/nn/pooling.h).  The window sum is
+// reduced IN THE TENSOR DTYPE (tvm::sum(temp(indices), daxis), :599): it wraps at 8 / 16 / 32 bits.  Windowed pooling
+// divides by an int32 element count (:612-648; the 8/16-bit sum is promoted to int32 first); adaptive / global
+// pooling (is_avg == 2) casts the divisor to the tensor dtype as well (:384-389).  Division truncates toward zero.
 // Thread order follows the output's fastest-varying dimension so that stores coalesce for both
 // channels-last and NCHW tensors.
 __global__ void pool2d_kernel(const void* __restrict__ x, void* __restrict__ y, PoolArgs a) {
@@ -557,14 +559,16 @@ __global__ void pool2d_kernel(const void* __restrict__ x, void* __restrict__ y, 
       for (int ix = max(x0, 0); ix <= min(x1, a.W - 1); ++ix) {
         const int32_t v = load_as_i32(x, a.dtype, n * a.xs[0] + c * a.xs[1] + iy * a.xs[2] + ix * a.xs[3]);
         best = max(best, v);
-        sum += (uint32_t)v;
+        sum = (uint32_t)cast_trunc((int32_t)(sum + (uint32_t)v), a.dtype);
         ++cnt;
       }
     int32_t r;
     if (!a.is_avg) r = best;
     else {
       int div;
-      if (a.cip) {
+      if (a.is_avg == 2) {  // adaptive pool: divisor multiplied up in the tensor dtype (host rejects a zero divisor)
+        div = cast_trunc(cast_trunc(a.KH, a.dtype) * cast_trunc(a.KW, a.dtype), a.dtype);
+      } else if (a.cip) {
         const int ye = min(y1, a.H + a.pb - 1), xe = min(x1, a.W + a.pr - 1);
         div = (ye - y0 + 1) * (xe - x0 + 1);
       } else div = cnt > 1 ? cnt : 1;
@@ -699,6 +703,7 @@ void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_incl
     return;
   }
   if (is_avg && dtype == kI32 && dense_nhwc && KH == H && KW == W && pt + pb + pl + pr == 0 && N <= 65535 && H * W > 0) {
+    // int32: the adaptive (is_avg == 2) and the windowed divisor are both H * W
     dim3 grid((unsigned)((C + 127) / 128), (unsigned)N);
     global_avgpool_nhwc_i32_kernel<<<grid, 128, 0, s>>>((const int32_t*)x, (int32_t*)y, H * W, C);
     ++g_launches;

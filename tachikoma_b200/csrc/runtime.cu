@@ -13,6 +13,8 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <array>
+#include <atomic>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -22,6 +24,7 @@
 #include <mutex>
 #include <regex>
 #include <sstream>
+#include <thread>
 #include <unordered_map>
 
 #include "../../include/tkb200.h"
@@ -89,11 +92,14 @@ struct TraceRec {
   bool logical = false;  // a logical-layout copy of the tensor exists once node `nid` has run
 };
 
+// Everything one run touches lives here, one Workspace per caller stream: the plan is immutable after tkb_init and
+// the handle carries no per-call state (tachikoma_json_runtime.cc:76-90: "Run(args) const", instance immutable), so
+// host threads that use distinct streams never share mutable memory.
 struct Workspace {
   uint8_t* arena = nullptr;
   long long arena_bytes = 0;
   uint8_t* trace_ring = nullptr;    // device: logical copies of NHWC-physical tensors
-  uint8_t* trace_host = nullptr;    // pinned host mirror of every traced tensor
+  uint8_t* trace_host = nullptr;    // pinned host image of the serialized NDArray-list blob (headers written once)
   long long trace_ring_bytes = 0, trace_host_bytes = 0;
   cudaStream_t side = nullptr;
   cudaEvent_t ev_join = nullptr;
@@ -101,7 +107,12 @@ struct Workspace {
   cudaEvent_t ev = nullptr;
   std::vector<cudaEvent_t> tc_events;  // begin/end pairs around tcgen05 GEMM launches (option time_tc)
   size_t tc_used = 0;
-  bool trace_valid = false;
+  int trace_mode = 0;               // trace mode of the LAST run on this stream (0 = nothing captured)
+  bool payload_on_host = false;     // first occurrence of every traced tensor has been copied into trace_host
+  bool dups_filled = false;         // repeated records (a tensor that is also a consumer's input) have been filled in
+  std::vector<void*> in_ptr;        // device pointers of the last run's graph inputs (deferred read-out, mode 1)
+  int* chain_flags = nullptr;       // device: per-(layer, image) completion counters of the chained tcgen05 launches
+  unsigned chain_epoch = 0;         // runs executed on this workspace (the counters are never reset)
 };
 
 }  // namespace tkb
@@ -119,19 +130,20 @@ struct tkb_runtime {
   std::mutex init_mu, ws_mu;
   std::unordered_map<cudaStream_t, std::unique_ptr<tkb::Workspace>> ws;
   std::string conv_impl = "auto";
-  bool time_tc = false;
-  int trace_mode = 0;
+  std::atomic<bool> time_tc{false};
+  std::atomic<int> trace_mode{0};               // DEFAULT mode of tkb_run; tkb_run_traced passes its own per call
   std::vector<tkb::TraceRec> trace_recs;        // in emission order
-  std::vector<long long> trace_host_off;        // per record
+  std::vector<long long> trace_host_off;        // per record: payload offset inside the serialized blob
   std::vector<long long> trace_ring_off;        // per record (-1: read the tensor in place)
   std::vector<int> trace_dup_of;                // per record: earlier record holding the same tensor, or -1
   long long trace_d2h_bytes = 0;                // bytes copied device -> host per run (each tensor once)
   long long trace_host_bytes = 0, trace_ring_bytes = 0;
-  std::vector<uint8_t> blob, trace_blob_buf;
+  std::vector<std::pair<long long, std::vector<uint8_t>>> blob_headers;  // (offset, bytes): everything but payloads
+  std::vector<uint8_t> blob;
   std::string plan_text;
-  long long launches = 0;
+  std::atomic<long long> launches{0};
   long long macs = 0, hbm_bytes = 0;
-  cudaStream_t last_stream = nullptr;
+  cudaStream_t last_stream = nullptr;           // guarded by ws_mu; only the stream-less convenience calls read it
 };
 
 namespace tkb {
@@ -140,9 +152,11 @@ struct RunCtx {
   tkb_runtime* rt;
   Workspace* ws;
   cudaStream_t s;
+  int mode = 0;               // trace mode of THIS call
+  bool time_tc = false;
   std::vector<void*> in_ptr;  // device pointer of each graph input (logical layout)
   void tc_mark() {  // records an event on the compute stream when kernel timing is on
-    if (!rt->time_tc) return;
+    if (!time_tc) return;
     if (ws->tc_used == ws->tc_events.size()) {
       cudaEvent_t ev;
       cudaEventCreate(&ev);
@@ -1297,10 +1311,20 @@ static void plan_pool(Planner& P, int nid) {
   P.need(x_eid, phys);
   P.produce(y_eid, phys);
   const int dt = X.dtype;
+  // The reference reduces in the tensor dtype and, for the adaptive (global) form, multiplies the divisor up in that
+  // dtype too (include/tvm/topi/nn/pooling.h:384-389, :599): a divisor that wraps to zero is a division by zero there.
+  const int avg_kind = global ? 2 : (is_avg ? 1 : 0);
+  if (global) {
+    auto wrap = [&](long long v) -> long long {
+      return dt == kI8 ? (int8_t)v : dt == kU8 ? (uint8_t)v : dt == kI16 ? (int16_t)v : (int32_t)v;
+    };
+    if (wrap(wrap(KH) * wrap(KW)) == 0)
+      fail("Unsupported op: %s over %dx%d on a %d-bit tensor (the divisor wraps to zero in the tensor dtype)", n.name.c_str(), KH, KW, 8 * dtype_size(dt));
+  }
   std::array<long long, 4> xs = {(long long)H * W * C, 1, (long long)W * C, C}, ys = {(long long)OH * OW * C, 1, (long long)OW * C, C};
   P.rt->hbm_bytes += X.bytes() + Y.bytes();
   P.add_step(n.name + " -> pooling kernel (channels-last)", [=](RunCtx& c) {
-    launch_pool2d(c.ptr(x_eid, phys), c.ptr(y_eid, phys), dt, is_avg, cip, N, C, H, W, KH, KW, sh, sw, pt, pl, pb, pr, xs.data(), ys.data(), c.s);
+    launch_pool2d(c.ptr(x_eid, phys), c.ptr(y_eid, phys), dt, avg_kind, cip, N, C, H, W, KH, KW, sh, sw, pt, pl, pb, pr, xs.data(), ys.data(), c.s);
   });
 }
 
@@ -1363,6 +1387,27 @@ static void plan_transpose(Planner& P, int nid) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// serialisation helpers: dmlc stream encoding (u64 length prefixes, 3rdparty/dmlc-core serializer.h:128-193)
+// ------------------------------------------------------------------------------------------------
+static void put_u64(std::vector<uint8_t>& b, uint64_t v) { for (int i = 0; i < 8; ++i) b.push_back((uint8_t)(v >> (8 * i))); }
+static void put_i32(std::vector<uint8_t>& b, int32_t v) { for (int i = 0; i < 4; ++i) b.push_back((uint8_t)((uint32_t)v >> (8 * i))); }
+static void put_str(std::vector<uint8_t>& b, const std::string& s) { put_u64(b, s.size()); b.insert(b.end(), s.begin(), s.end()); }
+
+static void dl_dtype(int dt, uint8_t* code, uint8_t* bits) {
+  switch (dt) {
+    case kI8: *code = 0; *bits = 8; break;
+    case kU8: *code = 1; *bits = 8; break;
+    case kI16: *code = 0; *bits = 16; break;
+    case kI32: *code = 0; *bits = 32; break;
+    case kI64: *code = 0; *bits = 64; break;
+    default: *code = 2; *bits = 32; break;
+  }
+}
+
+
+static int dl_code(int dt) { return dt == kU8 ? 1 : (dt == kF32 ? 2 : 0); }
+
+// ------------------------------------------------------------------------------------------------
 // BuildEngine (tachikoma_json_runtime.cc:240-290): walk the nodes, dispatch on the operator name
 // ------------------------------------------------------------------------------------------------
 static void build_plan(tkb_runtime* rt) {
@@ -1416,24 +1461,53 @@ static void build_plan(tkb_runtime* rt) {
   // Every tensor is staged ONCE per run: an activation appears as the output of its producer and again as
   // an input of each consumer; the later records alias the first one's host slot (the serializer reads the
   // same bytes), so neither the D2D permute nor the D2H copy is repeated.
+  // The pinned host buffer of a traced run IS the serialized NDArray-list blob (src/runtime/file_utils.cc:210-229,
+  // include/tvm/runtime/ndarray.h:449-494): names and per-array headers are written once when the buffer is
+  // allocated, the device -> host copies land directly at the payload offsets, and tkb_trace_blob hands the buffer out
+  // without another pass over the data (repeated records are filled by a parallel host copy on request).
   rt->trace_host_off.assign(rt->trace_recs.size(), 0);
   rt->trace_ring_off.assign(rt->trace_recs.size(), -1);
   rt->trace_dup_of.assign(rt->trace_recs.size(), -1);
   rt->trace_d2h_bytes = 0;
+  rt->blob_headers.clear();
   long long hoff = 0, roff = 0;
+  {
+    std::vector<uint8_t> pre;
+    put_u64(pre, 0xF7E58D4F05049CB7ull);
+    put_u64(pre, 0);
+    put_u64(pre, rt->trace_recs.size());
+    for (auto& r : rt->trace_recs) put_str(pre, r.name);
+    put_u64(pre, rt->trace_recs.size());
+    hoff = (long long)pre.size();
+    rt->blob_headers.emplace_back(0, std::move(pre));
+  }
   std::unordered_map<int, int> first_of_root;
   for (size_t i = 0; i < rt->trace_recs.size(); ++i) {
+    const Entry& re = rt->ent[rt->trace_recs[i].eid];  // shape / dtype as this record sees the tensor (reshape aliases)
+    std::vector<uint8_t> hd;
+    put_u64(hd, 0xDD5E40F096B4A13Full);
+    put_u64(hd, 0);
+    put_i32(hd, 1);  // kDLCPU
+    put_i32(hd, 0);
+    put_i32(hd, (int32_t)re.shape.size());
+    uint8_t code, bits;
+    dl_dtype(re.dtype, &code, &bits);
+    hd.push_back(code); hd.push_back(bits); hd.push_back(1); hd.push_back(0);  // lanes = 1 (u16 LE)
+    for (auto d : re.shape) put_u64(hd, (uint64_t)d);
+    put_u64(hd, (uint64_t)re.bytes());
+    const long long hlen = (long long)hd.size();
+    rt->blob_headers.emplace_back(hoff, std::move(hd));
+    hoff += hlen;
+    rt->trace_host_off[i] = hoff;
+    hoff += re.bytes();
     const int r = P.root(rt->trace_recs[i].eid);
     const Entry& e = rt->ent[r];
     auto it = first_of_root.find(r);
     if (it != first_of_root.end()) {
       rt->trace_dup_of[i] = it->second;
-      rt->trace_host_off[i] = rt->trace_host_off[it->second];
       continue;
     }
     first_of_root[r] = (int)i;
-    rt->trace_host_off[i] = hoff;
-    hoff += (rt->ent[rt->trace_recs[i].eid].bytes() + 63) & ~63LL;
     if (!e.is_const) rt->trace_d2h_bytes += e.bytes();
     if (!e.is_const && !rt->trace_recs[i].logical) {
       rt->trace_ring_off[i] = roff;
@@ -1443,7 +1517,7 @@ static void build_plan(tkb_runtime* rt) {
   rt->trace_host_bytes = hoff;
   rt->trace_ring_bytes = roff;
   P.plan << "arena " << rt->arena_bytes << " B, int8 MACs " << rt->macs << ", algorithmic HBM bytes " << rt->hbm_bytes
-         << ", trace payload " << hoff << " B\n";
+         << ", serialized trace " << hoff << " B (" << rt->trace_d2h_bytes << " B of distinct activations)\n";
   rt->plan_text = P.plan.str();
 }
 
@@ -1461,37 +1535,57 @@ static Workspace* get_workspace(tkb_runtime* rt, cudaStream_t s) {
   return slot.get();
 }
 
-static void ensure_trace_buffers(tkb_runtime* rt, Workspace* ws) {
-  if (!ws->side) {
-    // The trace stream gets the highest priority: its transpose blocks are then placed ahead of the next tensor-core
-    // kernel's (programmatically launched) CTAs whenever SMs free up instead of starving behind them
-    // (traced ResNet-18: 144.7k -> 149.1k img/s; TKB_SIDE_PRIO=0 restores the default priority)
-    int prio_lo = 0, prio_hi = 0;
-    const char* sp = getenv("TKB_SIDE_PRIO");
-    if (!(sp && atoi(sp) == 0) && cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi) == cudaSuccess)
-      CUDA_OK(cudaStreamCreateWithPriority(&ws->side, cudaStreamNonBlocking, prio_hi));
-    else
-      CUDA_OK(cudaStreamCreateWithFlags(&ws->side, cudaStreamNonBlocking));
-    CUDA_OK(cudaEventCreateWithFlags(&ws->ev, cudaEventDisableTiming));
-    CUDA_OK(cudaEventCreateWithFlags(&ws->ev_join, cudaEventDisableTiming));
+static void ensure_trace_stream(Workspace* ws) {
+  if (ws->side) return;
+  // The trace stream gets the highest priority: its transpose blocks are then placed ahead of the next tensor-core
+  // kernel's (programmatically launched) CTAs whenever SMs free up instead of starving behind them
+  // (traced ResNet-18: 144.7k -> 149.1k img/s; TKB_SIDE_PRIO=0 restores the default priority)
+  int prio_lo = 0, prio_hi = 0;
+  const char* sp = getenv("TKB_SIDE_PRIO");
+  if (!(sp && atoi(sp) == 0) && cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi) == cudaSuccess)
+    CUDA_OK(cudaStreamCreateWithPriority(&ws->side, cudaStreamNonBlocking, prio_hi));
+  else
+    CUDA_OK(cudaStreamCreateWithFlags(&ws->side, cudaStreamNonBlocking));
+  CUDA_OK(cudaEventCreateWithFlags(&ws->ev, cudaEventDisableTiming));
+  CUDA_OK(cudaEventCreateWithFlags(&ws->ev_join, cudaEventDisableTiming));
+}
+
+// Pinned host image of the blob: headers and constant payloads are written here once per workspace.
+static void ensure_trace_host(tkb_runtime* rt, Workspace* ws) {
+  if (ws->trace_host && ws->trace_host_bytes >= rt->trace_host_bytes) return;
+  if (ws->trace_host) cudaFreeHost(ws->trace_host);
+  ws->trace_host = nullptr;
+  CUDA_OK(cudaMallocHost((void**)&ws->trace_host, (size_t)rt->trace_host_bytes + 256));
+  ws->trace_host_bytes = rt->trace_host_bytes;
+  for (auto& h : rt->blob_headers) memcpy(ws->trace_host + h.first, h.second.data(), h.second.size());
+  for (size_t i = 0; i < rt->trace_recs.size(); ++i) {  // constants never change: every record of one is final
+    int r = rt->trace_recs[i].eid;
+    while (rt->ent[r].alias_of >= 0) r = rt->ent[r].alias_of;
+    const Entry& e = rt->ent[r];
+    if (e.is_const) memcpy(ws->trace_host + rt->trace_host_off[i], e.host.data(), (size_t)rt->ent[rt->trace_recs[i].eid].bytes());
   }
-  if (ws->trace_ring_bytes < rt->trace_ring_bytes) {
+}
+
+static void ensure_trace_buffers(tkb_runtime* rt, Workspace* ws, int mode) {
+  ensure_trace_stream(ws);
+  if (ws->trace_ring_bytes < rt->trace_ring_bytes || !ws->trace_ring) {
     if (ws->trace_ring) cudaFree(ws->trace_ring);
+    ws->trace_ring = nullptr;
     CUDA_OK(cudaMalloc((void**)&ws->trace_ring, rt->trace_ring_bytes + 256));
     ws->trace_ring_bytes = rt->trace_ring_bytes;
   }
-  if (rt->trace_mode >= 2 && ws->trace_host_bytes < rt->trace_host_bytes) {
-    if (ws->trace_host) cudaFreeHost(ws->trace_host);
-    CUDA_OK(cudaMallocHost((void**)&ws->trace_host, rt->trace_host_bytes + 256));
-    ws->trace_host_bytes = rt->trace_host_bytes;
-    for (size_t i = 0; i < rt->trace_recs.size(); ++i) {  // constants never change: written once, never copied again
-      if (rt->trace_dup_of[i] >= 0) continue;
-      int r = rt->trace_recs[i].eid;
-      while (rt->ent[r].alias_of >= 0) r = rt->ent[r].alias_of;
-      const Entry& e = rt->ent[r];
-      if (e.is_const) memcpy(ws->trace_host + rt->trace_host_off[i], e.host.data(), (size_t)rt->ent[rt->trace_recs[i].eid].bytes());
-    }
-  }
+  if (mode >= 2) ensure_trace_host(rt, ws);
+}
+
+// Device address a trace record is read from after the run: the ring for NHWC-physical tensors, else the tensor itself.
+static const void* trace_src(tkb_runtime* rt, Workspace* ws, const std::vector<void*>& in_ptr, size_t i) {
+  if (rt->trace_ring_off[i] >= 0) return ws->trace_ring + rt->trace_ring_off[i];
+  int r = rt->trace_recs[i].eid;
+  while (rt->ent[r].alias_of >= 0) r = rt->ent[r].alias_of;
+  const Entry& e = rt->ent[r];
+  if (e.is_input) return in_ptr[e.input_index];
+  if (e.off[kLogical] < 0) fail("internal: trace record %d has no logical copy", (int)i);
+  return ws->arena + e.off[kLogical];
 }
 
 // Stage the trace records of node `nid` (records [lo, hi)): D2D permute for NHWC-physical tensors,
@@ -1505,7 +1599,7 @@ static void trace_node(RunCtx& c, size_t lo, size_t hi) {
     if (rt->trace_dup_of[i] >= 0) continue;
     int r = rt->trace_recs[i].eid;
     while (rt->ent[r].alias_of >= 0) r = rt->ent[r].alias_of;
-    any = rt->trace_ring_off[i] >= 0 || (rt->trace_mode >= 2 && !rt->ent[r].is_const);
+    any = rt->trace_ring_off[i] >= 0 || (c.mode >= 2 && !rt->ent[r].is_const);
   }
   if (!any) return;
   cudaStream_t side = c.ws->side;
@@ -1525,7 +1619,7 @@ static void trace_node(RunCtx& c, size_t lo, size_t hi) {
     if (launch_transpose_tile(c.ptr(r, kNHWC), dstp, dtype_size(e.dtype), N, H * W, C, side)) continue;
     launch_permute4(c.ptr(r, kNHWC), c.ws->trace_ring + rt->trace_ring_off[i], dtype_size(e.dtype), oshape, istr, side);
   }
-  if (rt->trace_mode < 2) return;
+  if (c.mode < 2) return;
   for (size_t i = lo; i < hi; ++i) {
     const int eid = rt->trace_recs[i].eid;
     int r = eid;
@@ -1534,8 +1628,7 @@ static void trace_node(RunCtx& c, size_t lo, size_t hi) {
     uint8_t* dst = c.ws->trace_host + rt->trace_host_off[i];
     const long long bytes = rt->ent[eid].bytes();
     if (e.is_const || rt->trace_dup_of[i] >= 0) continue;  // constants were written once; duplicates alias a slot
-    const void* src = rt->trace_ring_off[i] >= 0 ? (const void*)(c.ws->trace_ring + rt->trace_ring_off[i]) : c.ptr(r, kLogical);
-    CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, side));
+    CUDA_OK(cudaMemcpyAsync(dst, trace_src(rt, c.ws, c.in_ptr, i), bytes, cudaMemcpyDeviceToHost, side));
   }
 }
 
@@ -1555,12 +1648,16 @@ static void check_arg(const Entry& e, const tkb_DLTensor* t, int i) {
   for (int d = 0; d < t->ndim; ++d)
     if (t->shape[d] != e.shape[d]) fail("argument %d: dim %d is %lld, expected %lld", i, d, (long long)t->shape[d], (long long)e.shape[d]);
   if (t->dtype.bits / 8 != dtype_size(e.dtype) || t->dtype.lanes != 1) fail("argument %d: dtype width mismatch", i);
+  // the reference's NDArray copy checks the full DLDataType (code 0 int, 1 uint, 2 float), not only the width
+  if (t->dtype.code != dl_code(e.dtype))
+    fail("argument %d: dtype code %d (0 int, 1 uint, 2 float), expected %d", i, (int)t->dtype.code, dl_code(e.dtype));
   if (t->device.device_type != tkbDLCPU && t->device.device_type != tkbDLCUDA && t->device.device_type != tkbDLCUDAHost)
     fail("argument %d: unsupported device type %d", i, t->device.device_type);
 }
 
-static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_args, cudaStream_t s) {
+static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_args, cudaStream_t s, int mode) {
   if (!rt->initialized) fail("The module has not been initialized");
+  if (mode < 0 || mode > 2) fail("trace mode must be 0, 1 or 2");
   Graph& g = rt->g;
   const int n_in = (int)g.input_eids.size(), n_out = (int)g.heads.size();
   if (n_args != n_in + n_out) fail("Found mismatch in the number of provided data entries and required.");
@@ -1568,8 +1665,13 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
   c.rt = rt;
   c.s = s;
   c.ws = get_workspace(rt, s);
+  c.mode = mode;
+  c.time_tc = rt->time_tc.load();
   c.in_ptr.resize(n_in);
   c.ws->tc_used = 0;
+  c.ws->trace_mode = 0;  // until this run has been enqueued completely
+  c.ws->payload_on_host = c.ws->dups_filled = false;
+  ++c.ws->chain_epoch;
   const long long before = g_launches;
   // inputs: device tensors are used in place, host tensors are staged (H2D on the caller's stream)
   for (int i = 0; i < n_in; ++i) {
@@ -1584,13 +1686,13 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
       c.in_ptr[i] = stage;
     }
   }
-  if (rt->trace_mode > 0) ensure_trace_buffers(rt, c.ws);
+  if (mode > 0) ensure_trace_buffers(rt, c.ws, mode);
   size_t rec = 0;
   for (size_t si = 0; si < rt->steps.size(); ++si) {
     rt->steps[si].fn(c);
     const int nid = rt->steps[si].nid;
     const bool last_of_node = si + 1 == rt->steps.size() || rt->steps[si + 1].nid != nid;
-    if (rt->trace_mode > 0 && nid >= 0 && last_of_node) {
+    if (mode > 0 && nid >= 0 && last_of_node) {
       // records are grouped per node in node order; nodes without steps (reshape aliases) in between
       size_t hi = rec;
       while (hi < rt->trace_recs.size() && rt->trace_recs[hi].nid <= nid) ++hi;
@@ -1598,7 +1700,7 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
       rec = hi;
     }
   }
-  if (rt->trace_mode > 0 && rec < rt->trace_recs.size()) trace_node(c, rec, rt->trace_recs.size());
+  if (mode > 0 && rec < rt->trace_recs.size()) trace_node(c, rec, rt->trace_recs.size());
   trace_join(c);
   bool host_out = false;
   for (int j = 0; j < n_out; ++j) {
@@ -1612,21 +1714,74 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
   }
   CUDA_OK(cudaGetLastError());
   if (host_out) CUDA_OK(cudaStreamSynchronize(s));  // host results are valid on return, like the reference
-  c.ws->trace_valid = rt->trace_mode >= 2;
+  c.ws->trace_mode = mode;
+  c.ws->payload_on_host = mode >= 2;
+  c.ws->in_ptr = c.in_ptr;
+  rt->launches += g_launches - before;
+  std::lock_guard<std::mutex> lk(rt->ws_mu);
   rt->last_stream = s;
-  {
-    std::lock_guard<std::mutex> lk(rt->ws_mu);
-    rt->launches += g_launches - before;
+}
+
+// Copy `bytes` from src to dst with up to `nthreads` host threads (the repeated records of a ResNet-18 batch-64 trace
+// are ~250 MB: one thread moves that in ~25 ms, eight in ~5).
+static void parallel_copy(const std::vector<std::array<long long, 3>>& jobs, uint8_t* base, int nthreads) {
+  const long long chunk = 4ll << 20;
+  std::vector<std::array<long long, 3>> parts;
+  for (auto& j : jobs)
+    for (long long o = 0; o < j[2]; o += chunk) parts.push_back({j[0] + o, j[1] + o, std::min(chunk, j[2] - o)});
+  if (parts.empty()) return;
+  nthreads = std::max(1, std::min<int>(nthreads, (int)parts.size()));
+  std::atomic<size_t> next{0};
+  auto work = [&] {
+    for (size_t i = next.fetch_add(1); i < parts.size(); i = next.fetch_add(1))
+      memcpy(base + parts[i][0], base + parts[i][1], (size_t)parts[i][2]);
+  };
+  std::vector<std::thread> th;
+  for (int t = 1; t < nthreads; ++t) th.emplace_back(work);
+  work();
+  for (auto& t : th) t.join();
+}
+
+// Make ws->trace_host the complete serialized blob of the last run on this workspace.  Mode 2 runs already streamed
+// every distinct activation to its payload offset; after a mode 1 run (device-resident capture) the read-out happens
+// here, from the ring / arena, which stay valid until the next run on the same stream.
+static void finish_trace_blob(tkb_runtime* rt, Workspace* ws) {
+  if (ws->trace_mode < 1) fail("no trace captured: run with trace mode 1 or 2 (tkb_trace_enable / tkb_run_traced) first");
+  ensure_trace_stream(ws);
+  if (!ws->payload_on_host) {
+    ensure_trace_host(rt, ws);
+    for (size_t i = 0; i < rt->trace_recs.size(); ++i) {
+      if (rt->trace_dup_of[i] >= 0) continue;
+      int r = rt->trace_recs[i].eid;
+      while (rt->ent[r].alias_of >= 0) r = rt->ent[r].alias_of;
+      if (rt->ent[r].is_const) continue;
+      CUDA_OK(cudaMemcpyAsync(ws->trace_host + rt->trace_host_off[i], trace_src(rt, ws, ws->in_ptr, i),
+                              (size_t)rt->ent[rt->trace_recs[i].eid].bytes(), cudaMemcpyDeviceToHost, ws->side));
+    }
+    ws->payload_on_host = true;
+    ws->dups_filled = false;
+  }
+  CUDA_OK(cudaStreamSynchronize(ws->side));
+  if (!ws->dups_filled) {
+    std::vector<std::array<long long, 3>> jobs;
+    for (size_t i = 0; i < rt->trace_recs.size(); ++i) {
+      const int d = rt->trace_dup_of[i];
+      if (d < 0) continue;
+      int r = rt->trace_recs[i].eid;
+      while (rt->ent[r].alias_of >= 0) r = rt->ent[r].alias_of;
+      if (rt->ent[r].is_const) continue;  // written when the buffer was allocated
+      jobs.push_back({rt->trace_host_off[i], rt->trace_host_off[d], rt->ent[rt->trace_recs[i].eid].bytes()});
+    }
+    int nt = (int)std::thread::hardware_concurrency();
+    if (const char* e = getenv("TKB_BLOB_THREADS")) nt = atoi(e);
+    parallel_copy(jobs, ws->trace_host, std::max(1, std::min(nt, 16)));
+    ws->dups_filled = true;
   }
 }
 
 // ------------------------------------------------------------------------------------------------
 // serialisation: dmlc stream encoding (u64 length prefixes, 3rdparty/dmlc-core serializer.h:128-193)
 // ------------------------------------------------------------------------------------------------
-static void put_u64(std::vector<uint8_t>& b, uint64_t v) { for (int i = 0; i < 8; ++i) b.push_back((uint8_t)(v >> (8 * i))); }
-static void put_i32(std::vector<uint8_t>& b, int32_t v) { for (int i = 0; i < 4; ++i) b.push_back((uint8_t)((uint32_t)v >> (8 * i))); }
-static void put_str(std::vector<uint8_t>& b, const std::string& s) { put_u64(b, s.size()); b.insert(b.end(), s.begin(), s.end()); }
-
 struct Reader {
   const uint8_t* p;
   size_t n, pos = 0;
@@ -1645,49 +1800,6 @@ struct Reader {
     return s;
   }
 };
-
-static void dl_dtype(int dt, uint8_t* code, uint8_t* bits) {
-  switch (dt) {
-    case kI8: *code = 0; *bits = 8; break;
-    case kU8: *code = 1; *bits = 8; break;
-    case kI16: *code = 0; *bits = 16; break;
-    case kI32: *code = 0; *bits = 32; break;
-    case kI64: *code = 0; *bits = 64; break;
-    default: *code = 2; *bits = 32; break;
-  }
-}
-
-// NDArray-list blob: src/runtime/file_utils.cc:210-229 (SaveParams) + include/tvm/runtime/ndarray.h:449-494
-// (SaveDLTensor): magic, reserved, names, count, then per tensor {magic, reserved, DLDevice(cpu,0), ndim,
-// dtype, shape[i64], nbytes(i64), data}.
-static void serialize_trace(tkb_runtime* rt, Workspace* ws, std::vector<uint8_t>& out) {
-  out.clear();
-  out.reserve((size_t)rt->trace_host_bytes + rt->trace_recs.size() * 128 + 64);
-  put_u64(out, 0xF7E58D4F05049CB7ull);
-  put_u64(out, 0);
-  put_u64(out, rt->trace_recs.size());
-  for (auto& r : rt->trace_recs) put_str(out, r.name);
-  put_u64(out, rt->trace_recs.size());
-  for (size_t i = 0; i < rt->trace_recs.size(); ++i) {
-    const Entry& e = rt->ent[rt->trace_recs[i].eid];
-    put_u64(out, 0xDD5E40F096B4A13Full);
-    put_u64(out, 0);
-    put_i32(out, 1);  // kDLCPU
-    put_i32(out, 0);
-    put_i32(out, (int32_t)e.shape.size());
-    uint8_t code, bits;
-    dl_dtype(e.dtype, &code, &bits);
-    out.push_back(code);
-    out.push_back(bits);
-    out.push_back(1);
-    out.push_back(0);  // lanes = 1 (u16 LE)
-    for (auto d : e.shape) put_u64(out, (uint64_t)d);
-    const long long bytes = e.bytes();
-    put_u64(out, (uint64_t)bytes);
-    const uint8_t* src = ws->trace_host + rt->trace_host_off[i];
-    out.insert(out.end(), src, src + bytes);
-  }
-}
 
 static tkb_runtime* create_impl(const std::string& symbol, const std::string& json, const std::vector<std::string>& names) {
   std::unique_ptr<tkb_runtime> rt(new tkb_runtime());
@@ -1745,19 +1857,33 @@ int tkb_create(const char* symbol, const char* graph_json, const char* const* co
   TKB_CATCH
 }
 
-int tkb_free(tkb_handle h) {
-  TKB_TRY
-  if (!h) return 0;
+static void destroy_workspaces(tkb_handle h) {
   for (auto& kv : h->ws) {
     Workspace* w = kv.second.get();
+    if (w->side) cudaStreamSynchronize(w->side);
     if (w->arena) cudaFree(w->arena);
     if (w->trace_ring) cudaFree(w->trace_ring);
     if (w->trace_host) cudaFreeHost(w->trace_host);
+    if (w->chain_flags) cudaFree(w->chain_flags);
     if (w->side) cudaStreamDestroy(w->side);
     if (w->ev) cudaEventDestroy(w->ev);
     if (w->ev_join) cudaEventDestroy(w->ev_join);
+    for (cudaEvent_t e : w->tc_events) cudaEventDestroy(e);
   }
+  h->ws.clear();
+}
+
+static void free_plan_allocs(tkb_handle h) {
   for (void* p : h->dev_allocs) cudaFree(p);
+  h->dev_allocs.clear();
+  for (auto& e : h->ent) e.dev_const = nullptr;  // uploaded constants were part of dev_allocs
+}
+
+int tkb_free(tkb_handle h) {
+  TKB_TRY
+  if (!h) return 0;
+  destroy_workspaces(h);
+  free_plan_allocs(h);
   delete h;
   TKB_CATCH
 }
@@ -1816,7 +1942,13 @@ int tkb_init(tkb_handle h, const tkb_DLTensor* const* consts, int n_consts) {
 
 int tkb_run(tkb_handle h, const tkb_DLTensor* const* args, int n_args, void* cuda_stream) {
   TKB_TRY
-  run_impl(h, args, n_args, (cudaStream_t)cuda_stream);
+  run_impl(h, args, n_args, (cudaStream_t)cuda_stream, h->trace_mode.load());
+  TKB_CATCH
+}
+
+int tkb_run_traced(tkb_handle h, const tkb_DLTensor* const* args, int n_args, void* cuda_stream, int trace_mode) {
+  TKB_TRY
+  run_impl(h, args, n_args, (cudaStream_t)cuda_stream, trace_mode);
   TKB_CATCH
 }
 
@@ -1831,7 +1963,9 @@ int tkb_packed_run(void* args, int* type_codes, int num_args, void* out_ret_valu
     if (type_codes[i] != 7 && type_codes[i] != 13) fail("Expect NDArray or DLTensor as inputs");
     ts.push_back((const tkb_DLTensor*)a[i].v_handle);  // an NDArray handle points at its DLTensor
   }
-  run_impl((tkb_handle)a[0].v_handle, ts.data(), (int)ts.size(), nullptr);
+  tkb_handle h = (tkb_handle)a[0].v_handle;
+  if (!h) fail("tkb_packed_run: null module handle");
+  run_impl(h, ts.data(), (int)ts.size(), nullptr, h->trace_mode.load());
   TKB_CATCH
 }
 
@@ -1842,14 +1976,15 @@ int tkb_set_option(tkb_handle h, const char* key, const char* value) {
     if (v != "auto" && v != "simt" && v != "tc" && v != "tc_explicit" && v != "tc_im2col")
       fail("conv_impl must be auto|simt|tc|tc_explicit|tc_im2col");
     if (h->initialized && v != h->conv_impl) {
+      // Re-planning is a configuration step like tkb_init: no run may be in flight.  The arena layout and every
+      // uploaded / repacked constant belong to the old plan: drop the workspaces (streams and events included) and
+      // the plan's device allocations before building the new one.
       h->conv_impl = v;
       std::lock_guard<std::mutex> guard(h->init_mu);
-      for (auto& kv : h->ws) {  // arena layout changes: drop the workspaces
-        cudaFree(kv.second->arena);
-        if (kv.second->trace_ring) cudaFree(kv.second->trace_ring);
-        if (kv.second->trace_host) cudaFreeHost(kv.second->trace_host);
-      }
-      h->ws.clear();
+      std::lock_guard<std::mutex> lk(h->ws_mu);
+      CUDA_OK(cudaDeviceSynchronize());
+      destroy_workspaces(h);
+      free_plan_allocs(h);
       build_plan(h);
     }
     h->conv_impl = v;
@@ -1861,7 +1996,7 @@ int tkb_set_option(tkb_handle h, const char* key, const char* value) {
   TKB_CATCH
 }
 
-int64_t tkb_launch_count(tkb_handle h) { return h->launches; }
+int64_t tkb_launch_count(tkb_handle h) { return h->launches.load(); }
 const char* tkb_plan_summary(tkb_handle h) { return h->plan_text.c_str(); }
 int tkb_work(tkb_handle h, int64_t* macs, int64_t* hbm_bytes) {
   if (macs) *macs = h->macs;
@@ -1869,11 +2004,19 @@ int tkb_work(tkb_handle h, int64_t* macs, int64_t* hbm_bytes) {
   return 0;
 }
 
-static Workspace* last_ws(tkb_handle h) {
+static Workspace* stream_ws(tkb_handle h, cudaStream_t s) {
   std::lock_guard<std::mutex> lk(h->ws_mu);
-  auto it = h->ws.find(h->last_stream);
-  if (it == h->ws.end()) fail("no run has been executed yet");
+  auto it = h->ws.find(s);
+  if (it == h->ws.end()) fail("no run has been executed on this stream yet");
   return it->second.get();
+}
+static Workspace* last_ws(tkb_handle h) {
+  cudaStream_t s;
+  {
+    std::lock_guard<std::mutex> lk(h->ws_mu);
+    s = h->last_stream;
+  }
+  return stream_ws(h, s);
 }
 
 int tkb_tc_time(tkb_handle h, double* ms, int* launches) {
@@ -1898,6 +2041,13 @@ int tkb_trace_enable(tkb_handle h, int mode) {
   TKB_CATCH
 }
 
+int tkb_trace_sync_on(tkb_handle h, void* cuda_stream) {
+  TKB_TRY
+  Workspace* ws = stream_ws(h, (cudaStream_t)cuda_stream);
+  if (ws->side) CUDA_OK(cudaStreamSynchronize(ws->side));
+  TKB_CATCH
+}
+
 int tkb_trace_sync(tkb_handle h) {
   TKB_TRY
   Workspace* ws = last_ws(h);
@@ -1905,15 +2055,33 @@ int tkb_trace_sync(tkb_handle h) {
   TKB_CATCH
 }
 
+int tkb_trace_blob_on(tkb_handle h, void* cuda_stream, const void** blob, size_t* len) {
+  TKB_TRY
+  Workspace* ws = stream_ws(h, (cudaStream_t)cuda_stream);
+  if (ws->trace_mode == 1) CUDA_OK(cudaStreamSynchronize((cudaStream_t)cuda_stream));  // the run itself must be complete
+  finish_trace_blob(h, ws);
+  *blob = ws->trace_host;
+  *len = (size_t)h->trace_host_bytes;
+  TKB_CATCH
+}
+
 int tkb_trace_blob(tkb_handle h, const void** blob, size_t* len) {
   TKB_TRY
-  Workspace* ws = last_ws(h);
-  if (!ws->trace_valid) fail("no trace captured: call tkb_trace_enable(h, 2) before tkb_run");
-  CUDA_OK(cudaStreamSynchronize(ws->side));
-  serialize_trace(h, ws, h->trace_blob_buf);
-  *blob = h->trace_blob_buf.data();
-  *len = h->trace_blob_buf.size();
+  cudaStream_t s;
+  {
+    std::lock_guard<std::mutex> lk(h->ws_mu);
+    s = h->last_stream;
+  }
+  if (tkb_trace_blob_on(h, (void*)s, blob, len) != 0) fail("%s", g_last_error.c_str());
   TKB_CATCH
+}
+
+static void write_file(const char* path, const void* data, size_t len) {
+  FILE* f = fopen(path, "wb");
+  if (!f) fail("cannot open %s for writing", path);
+  const size_t w = fwrite(data, 1, len, f);
+  fclose(f);
+  if (w != len) fail("short write to %s", path);
 }
 
 int tkb_trace_save(tkb_handle h, const char* path) {
@@ -1921,21 +2089,120 @@ int tkb_trace_save(tkb_handle h, const char* path) {
   const void* blob;
   size_t len;
   if (tkb_trace_blob(h, &blob, &len) != 0) fail("%s", g_last_error.c_str());
-  FILE* f = fopen(path, "wb");
-  if (!f) fail("cannot open %s for writing", path);
-  const size_t w = fwrite(blob, 1, len, f);
-  fclose(f);
-  if (w != len) fail("short write to %s", path);
+  write_file(path, blob, len);
+  TKB_CATCH
+}
+
+// Debug-executor-compatible dump of the last run (python/tvm/contrib/debugger/debug_result.py): the reference's
+// DebugResult writes (i) output_tensors.params = save_tensors({"{name}____topo-index:{i}____output-num:{j}": array}) over
+// ALL nodes of the graph, parameters included (:114-149), and (ii) _tvmdbg_graph_dump.json = the graph with, per node,
+// "inputs" replaced by the producers' names, "op" = "param" or the function name, attrs["T"] = "type: <dtype>" and
+// "shape" (:74-90, :191-202).  Same files here, from the tachikoma JSON graph and the captured trace.
+static std::string json_escape(const std::string& in) {
+  std::string o;
+  for (char ch : in) {
+    if (ch == '"' || ch == '\\') { o.push_back('\\'); o.push_back(ch); }
+    else if (ch == '\n') o += "\\n";
+    else o.push_back(ch);
+  }
+  return o;
+}
+
+int tkb_trace_dump_debug(tkb_handle h, const char* dir) {
+  TKB_TRY
+  if (!dir) fail("tkb_trace_dump_debug: null directory");
+  Workspace* ws = last_ws(h);
+  {
+    cudaStream_t s;
+    { std::lock_guard<std::mutex> lk(h->ws_mu); s = h->last_stream; }
+    if (ws->trace_mode == 1) CUDA_OK(cudaStreamSynchronize(s));
+  }
+  finish_trace_blob(h, ws);
+  const Graph& g = h->g;
+  auto root_of = [&](int eid) { while (h->ent[eid].alias_of >= 0) eid = h->ent[eid].alias_of; return eid; };
+  std::unordered_map<int, size_t> rec_of_root;  // root entry -> a trace record holding its bytes
+  for (size_t i = 0; i < h->trace_recs.size(); ++i) rec_of_root.emplace(root_of(h->trace_recs[i].eid), i);
+  // ---- output_tensors.params ----
+  std::vector<uint8_t> out;
+  std::vector<std::pair<std::string, int>> keys;  // (key, eid)
+  for (size_t nid = 0; nid < g.nodes.size(); ++nid)
+    for (uint32_t j = 0; j < g.node_row_ptr[nid + 1] - g.node_row_ptr[nid]; ++j)
+      keys.emplace_back(g.nodes[nid].name + "____topo-index:" + std::to_string(nid) + "____output-num:" + std::to_string(j),
+                        (int)g.eid((uint32_t)nid, j));
+  put_u64(out, 0xF7E58D4F05049CB7ull);
+  put_u64(out, 0);
+  put_u64(out, keys.size());
+  for (auto& k : keys) put_str(out, k.first);
+  put_u64(out, keys.size());
+  for (auto& k : keys) {
+    const Entry& e = h->ent[k.second];
+    const Entry& re = h->ent[root_of(k.second)];
+    const uint8_t* src = nullptr;
+    if (re.is_const) src = re.host.data();
+    else {
+      auto it = rec_of_root.find(root_of(k.second));
+      if (it == rec_of_root.end()) fail("tkb_trace_dump_debug: entry %d (%s) is not part of the trace", k.second, k.first.c_str());
+      src = ws->trace_host + h->trace_host_off[it->second];
+    }
+    put_u64(out, 0xDD5E40F096B4A13Full);
+    put_u64(out, 0);
+    put_i32(out, 1);
+    put_i32(out, 0);
+    put_i32(out, (int32_t)e.shape.size());
+    uint8_t code, bits;
+    dl_dtype(e.dtype, &code, &bits);
+    out.push_back(code); out.push_back(bits); out.push_back(1); out.push_back(0);
+    for (auto d : e.shape) put_u64(out, (uint64_t)d);
+    put_u64(out, (uint64_t)e.bytes());
+    out.insert(out.end(), src, src + e.bytes());
+  }
+  write_file((std::string(dir) + "/output_tensors.params").c_str(), out.data(), out.size());
+  // ---- _tvmdbg_graph_dump.json ----
+  std::ostringstream js;
+  auto shape_str = [](const std::vector<int64_t>& shp) {
+    std::string o = "[";
+    for (size_t i = 0; i < shp.size(); ++i) o += (i ? ", " : "") + std::to_string(shp[i]);
+    return o + "]";
+  };
+  js << "{\n    \"nodes\": [";
+  for (size_t nid = 0; nid < g.nodes.size(); ++nid) {
+    const GNode& n = g.nodes[nid];
+    js << (nid ? "," : "") << "\n        {\n            \"op\": \"" << json_escape(n.op_type == "kernel" ? n.name : std::string("param"))
+       << "\",\n            \"name\": \"" << json_escape(n.name) << "\",\n            \"inputs\": [";
+    for (size_t i = 0; i < n.inputs.size(); ++i) js << (i ? ", " : "") << "\"" << json_escape(g.nodes[n.inputs[i][0]].name) << "\"";
+    js << "],\n            \"attrs\": {";
+    for (auto& kv : n.attrs) {
+      js << "\n                \"" << json_escape(kv.first) << "\": [";
+      for (size_t i = 0; i < kv.second.size(); ++i) js << (i ? ", " : "") << "\"" << json_escape(kv.second[i]) << "\"";
+      js << "],";
+    }
+    js << "\n                \"num_inputs\": \"" << n.inputs.size() << "\",\n                \"num_outputs\": \"" << n.num_outputs
+       << "\",\n                \"T\": \"type: " << (n.dtypes.empty() ? "" : n.dtypes[0]) << "\"\n            },\n            \"shape\": "
+       << (n.shapes.empty() ? "[]" : shape_str(n.shapes[0])) << "\n        }";
+  }
+  js << "\n    ],\n    \"arg_nodes\": [";
+  for (size_t i = 0; i < g.arg_nodes.size(); ++i) js << (i ? ", " : "") << g.arg_nodes[i];
+  js << "],\n    \"node_row_ptr\": [";
+  for (size_t i = 0; i < g.node_row_ptr.size(); ++i) js << (i ? ", " : "") << g.node_row_ptr[i];
+  js << "],\n    \"heads\": [";
+  for (size_t i = 0; i < g.heads.size(); ++i) js << (i ? ", " : "") << "[" << g.heads[i][0] << ", " << g.heads[i][1] << ", " << g.heads[i][2] << "]";
+  js << "],\n    \"attrs\": {\n        \"shape\": [\"list_shape\", [";
+  for (size_t e = 0; e < h->ent.size(); ++e) js << (e ? ", " : "") << shape_str(h->ent[e].shape);
+  js << "]],\n        \"dltype\": [\"list_str\", [";
+  {
+    size_t e = 0;
+    for (size_t nid = 0; nid < g.nodes.size(); ++nid)
+      for (auto& d : g.nodes[nid].dtypes) js << (e++ ? ", " : "") << "\"" << d << "\"";
+  }
+  js << "]]\n    },\n    \"symbol\": \"" << json_escape(h->symbol) << "\"\n}\n";
+  const std::string text = js.str();
+  write_file((std::string(dir) + "/_tvmdbg_graph_dump.json").c_str(), text.data(), text.size());
   TKB_CATCH
 }
 
 int64_t tkb_trace_d2h_bytes(tkb_handle h) { return h->trace_d2h_bytes; }
 
-int64_t tkb_trace_bytes(tkb_handle h) {
-  int64_t n = 0;
-  for (auto& r : h->trace_recs) n += h->ent[r.eid].bytes();
-  return n;
-}
+int64_t tkb_trace_bytes(tkb_handle h) { return h->trace_host_bytes; }
 
 void tkb_fixed_point_multiplier_shift(double multiplier, int32_t* significand, int32_t* exponent) {
   fixed_point_multiplier_shift(multiplier, significand, exponent);

@@ -71,6 +71,12 @@ def load_library():
     L.tkb_num_outputs.argtypes = [H]
     L.tkb_init.argtypes = [H, ctypes.POINTER(ctypes.POINTER(DLTensor)), ctypes.c_int]
     L.tkb_run.argtypes = [H, ctypes.POINTER(ctypes.POINTER(DLTensor)), ctypes.c_int, ctypes.c_void_p]
+    L.tkb_run_traced.argtypes = [H, ctypes.POINTER(ctypes.POINTER(DLTensor)), ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
+    L.tkb_trace_sync_on.argtypes = [H, ctypes.c_void_p]
+    L.tkb_trace_blob_on.argtypes = [H, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t)]
+    L.tkb_trace_dump_debug.argtypes = [H, ctypes.c_char_p]
+    L.tkb_packed_run.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.c_int, ctypes.c_void_p,
+                                 ctypes.POINTER(ctypes.c_int), ctypes.c_void_p]
     L.tkb_set_option.argtypes = [H, ctypes.c_char_p, ctypes.c_char_p]
     L.tkb_launch_count.restype = ctypes.c_int64
     L.tkb_launch_count.argtypes = [H]
@@ -196,10 +202,33 @@ class TachikomaJSONRuntime:
         _check(self._lib.tkb_init(self._h, arr, len(args)))
         return 0
 
-    def run(self, *tensors, stream=None):
-        """``<symbol>``(inputs..., outputs...): outputs are caller-allocated."""
+    def run(self, *tensors, stream=None, trace_mode=None):
+        """``<symbol>``(inputs..., outputs...): outputs are caller-allocated.  ``trace_mode`` (0/1/2) overrides the
+        handle's default trace mode for this call only (per-stream trace state, see tkb_run_traced)."""
         args, arr = _tensor_array(tensors)
-        _check(self._lib.tkb_run(self._h, arr, len(args), ctypes.c_void_p(stream or 0)))
+        if trace_mode is None:
+            _check(self._lib.tkb_run(self._h, arr, len(args), ctypes.c_void_p(stream or 0)))
+        else:
+            _check(self._lib.tkb_run_traced(self._h, arr, len(args), ctypes.c_void_p(stream or 0), int(trace_mode)))
+
+    def packed_run(self, *tensors):
+        """Call through the TVMBackendPackedCFunc-shaped entry (include/tvm/runtime/c_backend_api.h:49-51):
+        args[0] = module handle (kTVMOpaqueHandle), args[1..] = DLTensor* (kTVMDLTensorHandle)."""
+        args, _ = _tensor_array(tensors)
+
+        class TVMValue(ctypes.Union):
+            _fields_ = [("v_int64", ctypes.c_int64), ("v_float64", ctypes.c_double), ("v_handle", ctypes.c_void_p)]
+
+        n = len(args) + 1
+        vals = (TVMValue * n)()
+        codes = (ctypes.c_int * n)()
+        vals[0].v_handle = self._h
+        codes[0] = 3
+        for i, a in enumerate(args):
+            vals[i + 1].v_handle = ctypes.cast(ctypes.pointer(a.t), ctypes.c_void_p)
+            codes[i + 1] = 7
+        ret, rcode = TVMValue(), ctypes.c_int(0)
+        _check(self._lib.tkb_packed_run(vals, codes, n, ctypes.byref(ret), ctypes.byref(rcode), None))
 
     # -- persistence (json_runtime.h:105-135) ------------------------------------------------------
     def save_to_binary(self):
@@ -240,13 +269,29 @@ class TachikomaJSONRuntime:
     def trace_enable(self, mode):
         _check(self._lib.tkb_trace_enable(self._h, int(mode)))
 
-    def trace_sync(self):
-        _check(self._lib.tkb_trace_sync(self._h))
+    def trace_sync(self, stream=None):
+        if stream is None:
+            _check(self._lib.tkb_trace_sync(self._h))
+        else:
+            _check(self._lib.tkb_trace_sync_on(self._h, ctypes.c_void_p(stream)))
 
-    def trace_blob(self):
+    def trace_blob_view(self, stream=None):
+        """(address, length) of the serialized trace in the runtime's pinned buffer: no copy.  Valid until the next
+        traced run on the same stream."""
         p, n = ctypes.c_void_p(), ctypes.c_size_t()
-        _check(self._lib.tkb_trace_blob(self._h, ctypes.byref(p), ctypes.byref(n)))
-        return ctypes.string_at(p.value, n.value)
+        if stream is None:
+            _check(self._lib.tkb_trace_blob(self._h, ctypes.byref(p), ctypes.byref(n)))
+        else:
+            _check(self._lib.tkb_trace_blob_on(self._h, ctypes.c_void_p(stream), ctypes.byref(p), ctypes.byref(n)))
+        return p.value, n.value
+
+    def trace_blob(self, stream=None):
+        p, n = self.trace_blob_view(stream)
+        return ctypes.string_at(p, n)
+
+    def trace_dump_debug(self, directory):
+        """Write output_tensors.params + _tvmdbg_graph_dump.json (debug_result.py:25, :114-149, :191-202)."""
+        _check(self._lib.tkb_trace_dump_debug(self._h, str(directory).encode()))
 
     def trace_save(self, path):
         _check(self._lib.tkb_trace_save(self._h, path.encode()))

@@ -80,31 +80,37 @@ def load_trace(blob):
     return out
 
 
-def concat_traces(blobs, sample_offsets=None):
+def const_record_names(graph_json):
+    """Names of the trace records whose tensor is produced by a ``const`` node of the tachikoma JSON graph
+    (weights, bias, scales, zero points): ``{op}____topo-index:{nid}____input-num:{i}`` for every kernel-node input
+    that points at a const node (schema: src/runtime/contrib/json/json_node.h:116-129)."""
+    import json
+    nodes = json.loads(graph_json)["nodes"]
+    out = set()
+    for nid, n in enumerate(nodes):
+        if n.get("op") != "kernel":
+            continue
+        for i, ref in enumerate(n.get("inputs", [])):
+            if nodes[ref[0]].get("op") == "const":
+                out.add("%s____topo-index:%d____input-num:%d" % (n["name"], nid, i))
+    return out
+
+
+def concat_traces(blobs, sample_offsets=None, graph_json=None):
     """Join per-rank trace blobs (rank order) into one blob.  Record keys get the suffix
     ``____rank:{r}____sample-offset:{o}`` so that every record stays addressable and carries the global
-    index of its first sample; constants (identical on all ranks) are kept from rank 0 only."""
+    index of its first sample.  With ``graph_json`` (the module's graph, identical on all ranks) the records of
+    CONSTANT tensors are kept from rank 0 only; which records those are is read from the graph (their producing
+    node is a ``const`` node), never inferred from input position or byte equality: two ranks that happen to see
+    identical activations keep all their activation records.  Without ``graph_json`` nothing is dropped."""
     blobs = list(blobs)
     if sample_offsets is None:
         sample_offsets = [0] * len(blobs)
-    merged = []
-    seen_const = {}
+    consts = const_record_names(graph_json) if graph_json is not None else set()
+    out = []
     for r, blob in enumerate(blobs):
         for name, arr in load_trace(blob):
-            key = "%s____rank:%d____sample-offset:%d" % (name, r, sample_offsets[r])
-            merged.append((key, arr, name, r))
-    # drop records of ranks > 0 that are byte-identical to rank 0's record of the same name (weights, scales)
-    rank0 = {name: arr for _, arr, name, r in merged if r == 0}
-    out = []
-    for key, arr, name, r in merged:
-        if r > 0 and name in rank0 and rank0[name].shape == arr.shape and rank0[name].dtype == arr.dtype \
-                and name.find("input-num:0") < 0 and np.array_equal(rank0[name], arr) and _is_param(name, seen_const):
-            continue
-        out.append((key, arr))
+            if r > 0 and name in consts:
+                continue
+            out.append(("%s____rank:%d____sample-offset:%d" % (name, r, sample_offsets[r]), arr))
     return save_trace(out)
-
-
-def _is_param(name, cache):
-    # inputs 1.. of a node are its parameters (weights, bias, scales, zero points) unless they are activations;
-    # byte-equality with rank 0 (checked by the caller) is the actual criterion, this only excludes outputs.
-    return "____output-num:" not in name

@@ -86,7 +86,10 @@ const char* tkb_last_error(void);
 /* Known keys: "conv_impl" = "auto" (tensor cores where they pay) | "simt" (CUDA-core kernels only) | "tc" (tensor
  *                           cores wherever supported) | "tc_im2col" (as "tc" without the halo-reuse convolution
  *                           kernel: TMA-im2col implicit GEMM) | "tc_explicit" (as "tc" with an explicit im2col
- *                           matrix) -- all routes produce identical bits, the last two exist for A/B tests;
+ *                           matrix) | "tc_chain_all" / "tc_chain_siblings" / "tc_chain_split" (as "tc" with consecutive
+ *                           layers merged into chained persistent launches, csrc/kernels_tc_chain.cu: dependent layers
+ *                           too / layers reading the same activation / every layer, a launch per dependency) -- all
+ *                           routes produce identical bits, everything after "tc" exists for A/B tests;
  *             "time_tc"   = "0"|"1" (bracket every tcgen05 launch with CUDA events, see tkb_tc_time). */
 int tkb_set_option(tkb_handle h, const char* key, const char* value);
 /* Number of kernels this library launched on behalf of h since creation (bench.py "gpu_launches"). */
@@ -140,6 +143,9 @@ int tkb_probe_int8_shape(int iters, int n, int commit_every, double* tops, void*
 /* Measurement aid: enqueue a device busy-wait of about `microseconds` on the stream, so that a host can queue a
  * whole step behind it and per-kernel CUDA events then see device time only. */
 int tkb_spin(double microseconds, void* cuda_stream);
+/* Debug counters of the chained tcgen05 launches since the last reset: out8[0] = work items that had to wait for a
+ * dependency, out8[1] = cycles waited (summed over CTAs); tools/chain_probe.py prints them. */
+int tkb_debug_chain_stats(uint64_t* out8, int reset);
 /* Library build info: "sm_100a;<n kernels>;..." */
 const char* tkb_version(void);
 

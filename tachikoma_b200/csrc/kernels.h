@@ -103,6 +103,31 @@ bool tc_halo_supported(const ConvGeom& g, int N);
 void tc_halo_tile_config(const ConvGeom& g, int N, int* bn, int* bk);
 int launch_tc_halo(const TcArgs& a, cudaStream_t s);
 int launch_tc(const TcArgs& a, cudaStream_t s);
+
+// ---- chained launch (kernels_tc_chain.cu): several consecutive fast-epilogue layers in ONE persistent kernel, tiles of
+// layer k+1 gated per image on layer k's completion counters.  A layer is a TcArgs of the implicit-conv (implicit == 1)
+// or plain-GEMM (implicit == 0) form with weights packed for (bn, tc_chain_bk()).
+#define TKB_CHAIN_MAX_SEG 16
+struct TcChainLayer {
+  TcArgs a;
+  int rows_per_img;     // output rows (pixels) per image: the granularity of the completion counters
+  int dep_a, dep_sum;   // index of the layer (in this chain) that produces the A operand / the residual, or -1
+};
+int tc_chain_bk(const TcArgs& a);
+bool tc_chain_supported(const TcArgs& a, int bn);
+int tc_chain_flag_ints(const TcChainLayer* layers, int n);   // ints of device memory for the claim counter + counters
+int tc_chain_item_count(const TcChainLayer* layers, int n, int bn);  // entries of the work list
+size_t tc_chain_state_bytes();
+}  // namespace tkb
+#include <vector>
+namespace tkb {
+// Encode the launch state (tensor maps, per-layer parameters) into `state`; `flags` / `tgt_dev`: device arrays of
+// tc_chain_flag_ints() ints (flags zeroed before every launch; tgt_dev filled by the caller from *tgt_host);
+// `items_dev`: device array of tc_chain_item_count() ints filled by the caller from *items_host (the work list).
+int tc_chain_build(const TcChainLayer* layers, int n, int bn, int* flags, int* tgt_dev, std::vector<int>* tgt_host,
+                   const int* items_dev, std::vector<int>* items_host, void* state);
+int launch_tc_chain(const void* state, int bn, cudaStream_t s);
+void tc_chain_stats(unsigned long long* out, bool reset);  // debug counters of the chained kernel (see g_chain_stats)
 int probe_int8_peak(int iters, double* tops, cudaStream_t s);
 int probe_int8_shape(int iters, int n, int commit_every, double* tops, cudaStream_t s);
 

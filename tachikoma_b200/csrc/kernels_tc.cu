@@ -104,6 +104,23 @@ static bool make_tmap_im2col(CUtensorMap* tm, const void* base, const ConvGeom& 
   return true;
 }
 
+bool make_tmap_im2col_pub(CUtensorMap* tm, const void* base, const ConvGeom& g, int bk) { return make_tmap_im2col(tm, base, g, bk); }
+bool make_tmap_3d_pub(CUtensorMap* tm, const void* base, long long k, long long rows, long long batch, int box_rows, int bk) {
+  return make_tmap_3d(tm, base, k, rows, batch, box_rows, bk);
+}
+
+// 2-D uint8 map of an output matrix [rows][n] for TMA stores of 128 x 128 tiles out of a 128-byte-swizzled staging buffer
+bool make_tmap_out_pub(CUtensorMap* tm, const void* base, long long n, long long rows) {
+  EncodeTiledFn fn = encode_tiled();
+  if (!fn || (n & 15)) return false;
+  cuuint64_t dims[2] = {(cuuint64_t)n, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)n};
+  cuuint32_t box[2] = {128, (cuuint32_t)BM};
+  cuuint32_t estr[2] = {1, 1};
+  return fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 bool tc_gemm_supported(int M, int N, int K) { return M > 0 && N > 0 && K > 0 && (K % 16) == 0; }
 
 bool tc_implicit_conv_supported(const ConvGeom& g) {

@@ -82,7 +82,22 @@ struct RunCtx;
 struct Step {
   std::function<void(RunCtx&)> fn;
   std::string desc;
-  int nid = -1;  // JSON node this step belongs to (-1: boundary conversion)
+  int nid = -1;   // JSON node this step belongs to (-1: boundary conversion)
+  int cand = -1;  // index into tkb_runtime::chain_cands: a tcgen05 layer that may be merged into a chained launch
+};
+
+// A tcgen05 convolution / GEMM step in the form the chained launch (kernels_tc_chain.cu) takes.
+struct ChainCand {
+  TcArgs ta;
+  int x_eid, y_eid, sum_eid, phys, rows_per_img, bn;
+  std::string name;
+};
+struct ChainPlan {
+  std::vector<int> cands;           // indices into chain_cands, execution order
+  std::vector<int> dep_a, dep_sum;  // per layer: producing layer inside the chain or -1
+  int bn = 128;
+  int flag_off = 0, flag_ints = 0;  // slice of the workspace's counter array
+  int item_off = 0, item_count = 0; // slice of the workspace's work-list array
 };
 
 struct TraceRec {
@@ -111,8 +126,8 @@ struct Workspace {
   bool payload_on_host = false;     // first occurrence of every traced tensor has been copied into trace_host
   bool dups_filled = false;         // repeated records (a tensor that is also a consumer's input) have been filled in
   std::vector<void*> in_ptr;        // device pointers of the last run's graph inputs (deferred read-out, mode 1)
-  int* chain_flags = nullptr;       // device: per-(layer, image) completion counters of the chained tcgen05 launches
-  unsigned chain_epoch = 0;         // runs executed on this workspace (the counters are never reset)
+  int* chain_flags = nullptr;       // device: [counters of all chains | their targets]; the first half is zeroed per run
+  std::vector<std::vector<uint8_t>> chain_state;  // per chain: encoded launch parameters (tensor maps point into arena)
 };
 
 }  // namespace tkb
@@ -143,6 +158,12 @@ struct tkb_runtime {
   std::string plan_text;
   std::atomic<long long> launches{0};
   long long macs = 0, hbm_bytes = 0;
+  std::vector<tkb::ChainCand> chain_cands;
+  std::vector<tkb::ChainPlan> chains;
+  int chain_flag_ints = 0;                      // counters of all chains (the workspace allocates twice this: + targets)
+  int chain_item_ints = 0;                      // work-list entries of all chains (allocated behind the targets)
+  bool chain_enabled = true;
+  int chain_policy = 0;                         // 0 off, 1 sibling layers, 2 dependent layers merged, 3 every layer / split
   cudaStream_t last_stream = nullptr;           // guarded by ws_mu; only the stream-less convenience calls read it
 };
 
@@ -198,11 +219,12 @@ struct Planner {
     rt->dev_allocs.push_back(d);
     return d;
   }
-  void add_step(const std::string& desc, std::function<void(RunCtx&)> fn) {
+  void add_step(const std::string& desc, std::function<void(RunCtx&)> fn, int cand = -1) {
     Step s;
     s.fn = std::move(fn);
     s.desc = desc;
     s.nid = cur_nid;
+    s.cand = cand;
     rt->steps.push_back(std::move(s));
     plan << "  [" << cur_nid << "] " << desc << "\n";
   }
@@ -746,6 +768,21 @@ static std::vector<uint8_t> repack_ohwi(const Entry& w, const std::string& layou
   return out;
 }
 
+// Another tensor-core composite (convolution / dense) reads the same activation as node `nid`: the two are independent
+// and can share one chained launch (a residual block's 3x3 convolution and its 1x1 projection; Q / K / V projections).
+static bool has_sibling_composite(const Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  if (n.inputs.empty()) return false;
+  const uint32_t x = P.g.eid(n.inputs[0]);
+  for (size_t j = 0; j < P.g.nodes.size(); ++j) {
+    const GNode& m = P.g.nodes[j];
+    if ((int)j == nid || m.op_type != "kernel" || m.inputs.empty()) continue;
+    if (m.name != "tachikoma.qnn.conv2d" && m.name != "tachikoma.qnn.dense") continue;
+    if (P.g.eid(m.inputs[0]) == x) return true;
+  }
+  return false;
+}
+
 static void plan_conv(Planner& P, int nid, bool composite) {
   const GNode& n = P.g.nodes[nid];
   const int x_eid = (int)P.g.eid(n.inputs[0]), w_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
@@ -811,7 +848,8 @@ static void plan_conv(Planner& P, int nid, bool composite) {
   const bool direct = g.KH == 1 && g.KW == 1 && g.sh == 1 && g.sw == 1 && !(g.pt | g.pl | g.pb | g.pr) && (g.C % 16) == 0;
   const bool tc_ok = P.rt->conv_impl != "simt" && g.groups == 1 && all_zero(ci.zp_w) &&
                      (g.zp_a == 0 || ci.bias_eid < 0) && M >= 1;
-  const bool force_tc = P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col";
+  const bool force_tc = P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" ||
+                        P.rt->conv_impl == "tc_nochain" || P.rt->conv_impl.rfind("tc_chain", 0) == 0;
   const bool use_tc = tc_ok && (force_tc || M * g.O >= 4096);
   // "Kernel view" of the convolution.  A few-channel convolution whose input still lives in logical NCHW
   // form (the network stem) is rewritten as a 1 x KW convolution over the vertically unfolded tensor
@@ -885,7 +923,19 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     ta.g = g;
     if (composite && !ci.float_mode)
       build_fast_epi(P, ci, bias2, abs_row_sums(wk.data(), g.O, K, g.w_dtype), g.O, Y.dtype, &ta.f);
-    bool halo = implicit && ta.f.enabled && P.rt->conv_impl != "tc_im2col" && tc_halo_supported(g, g.O);
+    // Chained launch (kernels_tc_chain.cu): layers with >= 96 output channels in the implicit-GEMM / plain-GEMM form
+    // become candidates; form_chains() merges consecutive candidates into one persistent launch.
+    const int chain_bn = 128;
+    bool chain = P.rt->chain_enabled && composite && !ci.float_mode && ta.f.enabled && !unfold && !from_nchw &&
+                 (P.rt->chain_policy != 1 || has_sibling_composite(P, nid)) &&
+                 (direct || implicit) && ci.bias_eid < 0 && g.O >= 96 && !P.ent[P.root(x_eid)].is_input &&
+                 (ci.sum_eid < 0 || !P.ent[P.root(ci.sum_eid)].is_input);
+    if (chain) {
+      TcArgs probe = ta;
+      probe.e = epi;
+      chain = tc_chain_supported(probe, chain_bn);
+    }
+    bool halo = !chain && implicit && ta.f.enabled && P.rt->conv_impl != "tc_im2col" && tc_halo_supported(g, g.O);
     if (halo) ta.implicit = 3;
     // Stride-2 stem over the unfolded tensor: two horizontally adjacent 32-byte pixels of X3 form one 64-byte
     // "pair pixel", output column q reads pair pixels q .. q + ceil(KW/2) - 1: a stride-1 1 x ceil(KW/2)
@@ -909,7 +959,8 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     }
     const int Kw = ta.K;  // row length of wp
     {  // constant weights: pre-tile into the swizzled shared-memory image (one bulk copy per tile at run time)
-      tc_tile_config(ta, &ta.pack_bn, &ta.pack_bk);
+      if (chain) { ta.pack_bn = chain_bn; ta.pack_bk = tc_chain_bk(ta); }
+      else tc_tile_config(ta, &ta.pack_bn, &ta.pack_bk);
       std::vector<uint8_t> packed(tc_pack_weights(wp.data(), g.O, Kw, ta.pack_bn, ta.pack_bk, nullptr));
       tc_pack_weights(wp.data(), g.O, Kw, ta.pack_bn, ta.pack_bk, packed.data());
       ta.w = P.dev_upload(packed.data(), packed.size());
@@ -927,6 +978,19 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 %s M=%lld N=%d K=%d (%dx%d s%d p%d) epi=%s", n.name.c_str(),
              direct ? "GEMM" : (unfold ? (halo ? "halo-reuse conv over pixel pairs of the vertically unfolded NCHW input" : "conv as windowed-row GEMM over vertically unfolded NCHW input") : halo ? "halo-reuse conv (TMA patch, resident weights)" : implicit ? "implicit-GEMM conv (TMA im2col)" : (from_nchw ? "GEMM + explicit im2col from NCHW" : "GEMM + explicit im2col")), M, g.O, Kp, g.KH,
              g.KW, g.sh, g.pt, ta.f.enabled ? "fast" : (epi.mode == kEpiInt ? "int" : (epi.mode == kEpiFloat ? "float" : "raw")));
+    if (chain) {
+      ChainCand cc;
+      cc.ta = ta;
+      cc.ta.e = epi;
+      cc.x_eid = x_eid; cc.y_eid = y_eid; cc.sum_eid = sum_eid; cc.phys = phys;
+      cc.rows_per_img = g.OH * g.OW;
+      cc.bn = chain_bn;
+      cc.name = n.name;
+      P.rt->chain_cands.push_back(cc);
+      P.add_step(std::string(desc) + " [chain candidate]", [](RunCtx&) { fail("internal: chain candidate executed outside its chain"); },
+                 (int)P.rt->chain_cands.size() - 1);
+      return;
+    }
     P.add_step(desc, [=](RunCtx& c) {
       TcArgs t = ta;
       t.e = epi;
@@ -1041,7 +1105,7 @@ static void plan_dense(Planner& P, int nid, bool composite) {
   const int bias_eid = ci.bias_eid, sum_eid = ci.sum_eid, xd = X.dtype, wd = Wt.dtype;
   const bool foldable = zpx == 0 || (Wt.is_const && bias_eid < 0);
   const bool use_tc = P.rt->conv_impl != "simt" && tc_gemm_supported((int)M, N, K) && zpw == 0 && foldable &&
-                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" || M * N >= 4096);
+                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_nochain" || P.rt->conv_impl.rfind("tc_chain", 0) == 0 || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" || M * N >= 4096);
   char desc[256];
   if (use_tc) {
     std::vector<int32_t> bias2;
@@ -1063,6 +1127,33 @@ static void plan_dense(Planner& P, int nid, bool composite) {
     if (composite && !ci.float_mode && Wt.is_const)
       build_fast_epi(P, ci, bias2, abs_row_sums(Wt.host.data(), N, K, wd), N, Y.dtype, &ta.f);
     const void* wpacked = nullptr;
+    const int chain_bn = 128;
+    bool chain = P.rt->chain_enabled && composite && !ci.float_mode && ta.f.enabled && Wt.is_const && bias_eid < 0 && N >= 96 &&
+                 (P.rt->chain_policy != 1 || has_sibling_composite(P, nid)) &&
+                 M >= 128 && !P.ent[P.root(x_eid)].is_input && (sum_eid < 0 || !P.ent[P.root(sum_eid)].is_input);
+    if (chain) {
+      TcArgs probe = ta;
+      probe.e = epi;
+      chain = tc_chain_supported(probe, chain_bn);
+    }
+    if (chain) {
+      ta.pack_bn = chain_bn; ta.pack_bk = tc_chain_bk(ta);
+      std::vector<uint8_t> packed(tc_pack_weights(Wt.host.data(), N, K, ta.pack_bn, ta.pack_bk, nullptr));
+      tc_pack_weights(Wt.host.data(), N, K, ta.pack_bn, ta.pack_bk, packed.data());
+      ta.w = P.dev_upload(packed.data(), packed.size());
+      ta.w_packed = 1;
+      ChainCand cc;
+      cc.ta = ta;
+      cc.ta.e = epi;
+      cc.x_eid = x_eid; cc.y_eid = y_eid; cc.sum_eid = sum_eid; cc.phys = kLogical;
+      cc.rows_per_img = 128;  // a dense row depends on the same row of its input only: 128-row blocks are the "images"
+      cc.bn = chain_bn;
+      cc.name = n.name;
+      P.rt->chain_cands.push_back(cc);
+      snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 GEMM M=%lld N=%d K=%d epi=fast [chain candidate]", n.name.c_str(), M, N, K);
+      P.add_step(desc, [](RunCtx&) { fail("internal: chain candidate executed outside its chain"); }, (int)P.rt->chain_cands.size() - 1);
+      return;
+    }
     if (Wt.is_const) {
       tc_tile_config(ta, &ta.pack_bn, &ta.pack_bk);
       std::vector<uint8_t> packed(tc_pack_weights(Wt.host.data(), N, K, ta.pack_bn, ta.pack_bk, nullptr));
@@ -1120,7 +1211,7 @@ static void plan_batch_matmul(Planner& P, int nid) {
   init_epi(epi);
   const int xd = X.dtype, wd = Wt.dtype;
   const bool use_tc = P.rt->conv_impl != "simt" && tc_gemm_supported(M, N, K) && zpx == 0 && zpw == 0 &&
-                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" || (long long)B * M * N >= 4096);
+                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_nochain" || P.rt->conv_impl.rfind("tc_chain", 0) == 0 || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" || (long long)B * M * N >= 4096);
   char desc[256];
   snprintf(desc, sizeof(desc), "qnn.batch_matmul -> %s B=%d M=%d N=%d K=%d", use_tc ? "tcgen05 i8 GEMM" : "CUDA-core GEMM", B, M, N, K);
   P.add_step(desc, [=](RunCtx& c) {
@@ -1408,12 +1499,136 @@ static void dl_dtype(int dt, uint8_t* code, uint8_t* bits) {
 static int dl_code(int dt) { return dt == kU8 ? 1 : (dt == kF32 ? 2 : 0); }
 
 // ------------------------------------------------------------------------------------------------
+// chained tcgen05 launches: merge runs of consecutive candidate steps (see kernels_tc_chain.cu)
+// ------------------------------------------------------------------------------------------------
+static void run_chain(RunCtx& c, int id) {
+  tkb_runtime* rt = c.rt;
+  Workspace* ws = c.ws;
+  const ChainPlan& ch = rt->chains[id];
+  if (ws->chain_state.size() != rt->chains.size()) ws->chain_state.assign(rt->chains.size(), {});
+  std::vector<uint8_t>& state = ws->chain_state[id];
+  if (state.empty()) {
+    // First run on this stream: the operands live at fixed offsets of this workspace's arena, so the tensor maps and
+    // per-layer parameters are encoded once and reused by every later run.
+    std::vector<TcChainLayer> layers(ch.cands.size());
+    for (size_t i = 0; i < ch.cands.size(); ++i) {
+      const ChainCand& cc = rt->chain_cands[ch.cands[i]];
+      TcChainLayer& L = layers[i];
+      L.a = cc.ta;
+      L.a.a = c.ptr(cc.x_eid, cc.phys);
+      L.a.y = c.ptr(cc.y_eid, cc.phys);
+      L.a.e.sum = cc.sum_eid >= 0 ? c.ptr(cc.sum_eid, cc.phys) : nullptr;
+      L.rows_per_img = cc.rows_per_img;
+      L.dep_a = ch.dep_a[i];
+      L.dep_sum = ch.dep_sum[i];
+    }
+    std::vector<int> tgt, items;
+    std::vector<uint8_t> st(tc_chain_state_bytes());
+    int* flags = ws->chain_flags + ch.flag_off;
+    int* tgt_dev = ws->chain_flags + rt->chain_flag_ints + ch.flag_off;
+    int* items_dev = ws->chain_flags + 2 * rt->chain_flag_ints + ch.item_off;
+    if (tc_chain_build(layers.data(), (int)layers.size(), ch.bn, flags, tgt_dev, &tgt, items_dev, &items, st.data()) != 0)
+      fail("internal: could not encode the chained tcgen05 launch %d", id);
+    if ((int)tgt.size() != ch.flag_ints || (int)items.size() != ch.item_count) fail("internal: chain %d layout mismatch", id);
+    CUDA_OK(cudaMemcpyAsync(tgt_dev, tgt.data(), tgt.size() * sizeof(int), cudaMemcpyHostToDevice, c.s));
+    CUDA_OK(cudaMemcpyAsync(items_dev, items.data(), items.size() * sizeof(int), cudaMemcpyHostToDevice, c.s));
+    CUDA_OK(cudaStreamSynchronize(c.s));  // tgt / items are locals; one-time cost
+    state.swap(st);
+  }
+  c.tc_mark();
+  if (launch_tc_chain(state.data(), ch.bn, c.s) != 0) fail("chained tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+  c.tc_mark();
+}
+
+static void form_chains(tkb_runtime* rt, Planner& P) {
+  rt->chains.clear();
+  rt->chain_flag_ints = 0;
+  rt->chain_item_ints = 0;
+  std::vector<Step> out;
+  auto nimg_of = [&](int cand) {
+    const ChainCand& cc = rt->chain_cands[cand];
+    return (cc.ta.M + cc.rows_per_img - 1) / cc.rows_per_img;
+  };
+  size_t i = 0;
+  while (i < rt->steps.size()) {
+    if (rt->steps[i].cand < 0) { out.push_back(std::move(rt->steps[i])); ++i; continue; }
+    ChainPlan ch;
+    ch.bn = rt->chain_cands[rt->steps[i].cand].bn;
+    const int nimg0 = nimg_of(rt->steps[i].cand);
+    // Which layers share a launch (TKB_CHAIN_POLICY / conv_impl): 1 (default) = only layers that read the same
+    // activation (a residual block's 3x3 convolution and its 1x1 projection, the Q / K / V projections): they are
+    // independent, fill the SMs together and nothing ever waits; every other layer keeps its single-layer kernel.
+    // 3 = every eligible layer runs on the chained kernel, a new launch at every dependency; 2 (conv_impl
+    // "tc_chain_all") = dependent layers are merged too (per-image completion counters): measured slower on ResNet-18,
+    // where a dependent step is bounded by one tile's latency (operands streamed at the SM's L2 bandwidth + epilogue +
+    // publish), not by the launch boundary -- see profiles/r02_notes.md.
+    size_t j = i;
+    while (j < rt->steps.size() && rt->steps[j].cand >= 0 && (int)(j - i) < TKB_CHAIN_MAX_SEG &&
+           rt->chain_cands[rt->steps[j].cand].bn == ch.bn && nimg_of(rt->steps[j].cand) == nimg0) {
+      const ChainCand& cj = rt->chain_cands[rt->steps[j].cand];
+      bool depends = false;
+      for (int m : ch.cands) {
+        const ChainCand& pm = rt->chain_cands[m];
+        depends = depends || P.root(pm.y_eid) == P.root(cj.x_eid) || (cj.sum_eid >= 0 && P.root(pm.y_eid) == P.root(cj.sum_eid));
+      }
+      if (depends && rt->chain_policy != 2) break;
+      ch.cands.push_back(rt->steps[j].cand);
+      ++j;
+    }
+    std::vector<TcChainLayer> layers(ch.cands.size());
+    for (size_t k = 0; k < ch.cands.size(); ++k) {
+      const ChainCand& cc = rt->chain_cands[ch.cands[k]];
+      int da = -1, ds = -1;
+      for (size_t m = 0; m < k; ++m) {
+        const ChainCand& pm = rt->chain_cands[ch.cands[m]];
+        if (P.root(pm.y_eid) == P.root(cc.x_eid)) da = (int)m;
+        if (cc.sum_eid >= 0 && P.root(pm.y_eid) == P.root(cc.sum_eid)) ds = (int)m;
+      }
+      ch.dep_a.push_back(da);
+      ch.dep_sum.push_back(ds);
+      layers[k].a = cc.ta;
+      layers[k].rows_per_img = cc.rows_per_img;
+    }
+    ch.flag_ints = tc_chain_flag_ints(layers.data(), (int)layers.size());
+    ch.flag_off = rt->chain_flag_ints;
+    rt->chain_flag_ints += ch.flag_ints;
+    ch.item_count = tc_chain_item_count(layers.data(), (int)layers.size(), ch.bn);
+    if (ch.item_count < 0) fail("internal: chained launch with too many tiles");
+    ch.item_off = rt->chain_item_ints;
+    rt->chain_item_ints += ch.item_count;
+    const int id = (int)rt->chains.size();
+    Step st;
+    st.nid = rt->steps[j - 1].nid;
+    st.desc = "chained tcgen05 launch " + std::to_string(id);
+    st.fn = [id](RunCtx& c) { run_chain(c, id); };
+    P.plan << "  chain " << id << ": " << ch.cands.size() << " layers in one persistent launch (BN=" << ch.bn << "):";
+    for (size_t k = 0; k < ch.cands.size(); ++k) {
+      const ChainCand& cc = rt->chain_cands[ch.cands[k]];
+      P.plan << " [" << k << "] M=" << cc.ta.M << " N=" << cc.ta.N << " K=" << cc.ta.K << " dep=" << ch.dep_a[k] << "/" << ch.dep_sum[k];
+    }
+    P.plan << "\n";
+    rt->chains.push_back(std::move(ch));
+    out.push_back(std::move(st));
+    i = j;
+  }
+  rt->steps.swap(out);
+}
+
+// ------------------------------------------------------------------------------------------------
 // BuildEngine (tachikoma_json_runtime.cc:240-290): walk the nodes, dispatch on the operator name
 // ------------------------------------------------------------------------------------------------
 static void build_plan(tkb_runtime* rt) {
   Planner P(rt);
   Graph& g = rt->g;
   rt->steps.clear();
+  rt->chain_cands.clear();
+  // Chained launches are an opt-in experiment (conv_impl "tc_chain_all" / "tc_chain_siblings" / "tc_chain_split", or
+  // TKB_CHAIN_POLICY=2/1/3 with "tc"): bit-exact, but on B200 slower than the single-layer kernels for every network
+  // of BASELINE.json (profiles/r02_notes.md), so the default plan does not use them.
+  rt->chain_policy = rt->conv_impl == "tc_chain_all" ? 2 : (rt->conv_impl == "tc_chain_siblings" ? 1 : (rt->conv_impl == "tc_chain_split" ? 3 : 0));
+  if (const char* cpol = getenv("TKB_CHAIN_POLICY")) rt->chain_policy = atoi(cpol);
+  if (rt->chain_policy < 0 || rt->chain_policy > 3) rt->chain_policy = 0;
+  rt->chain_enabled = rt->chain_policy != 0 && rt->conv_impl != "simt" && rt->conv_impl != "tc_nochain" && !getenv("TKB_NO_CHAIN");
   rt->arena_bytes = 0;
   rt->macs = rt->hbm_bytes = 0;
   rt->trace_recs.clear();
@@ -1456,6 +1671,7 @@ static void build_plan(tkb_runtime* rt) {
   // graph outputs are delivered in the logical layout
   P.cur_nid = -1;
   for (auto& h : g.heads) P.need((int)g.eid(h), kLogical);
+  form_chains(rt, P);
   // trace staging plan: tensors that exist in logical layout are copied in place; NHWC-physical ones
   // are permuted into a device ring first
   // Every tensor is staged ONCE per run: an activation appears as the output of its producer and again as
@@ -1671,7 +1887,7 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
   c.ws->tc_used = 0;
   c.ws->trace_mode = 0;  // until this run has been enqueued completely
   c.ws->payload_on_host = c.ws->dups_filled = false;
-  ++c.ws->chain_epoch;
+
   const long long before = g_launches;
   // inputs: device tensors are used in place, host tensors are staged (H2D on the caller's stream)
   for (int i = 0; i < n_in; ++i) {
@@ -1685,6 +1901,11 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
       CUDA_OK(cudaMemcpyAsync(stage, p, e.bytes(), cudaMemcpyHostToDevice, s));
       c.in_ptr[i] = stage;
     }
+  }
+  if (rt->chain_flag_ints > 0) {  // completion counters of the chained launches: one memset ahead of the first kernel
+    if (!c.ws->chain_flags)  // [counters | targets | work lists]
+      CUDA_OK(cudaMalloc((void**)&c.ws->chain_flags, ((size_t)rt->chain_flag_ints * 2 + rt->chain_item_ints) * sizeof(int)));
+    CUDA_OK(cudaMemsetAsync(c.ws->chain_flags, 0, (size_t)rt->chain_flag_ints * sizeof(int), s));
   }
   if (mode > 0) ensure_trace_buffers(rt, c.ws, mode);
   size_t rec = 0;
@@ -1973,8 +2194,9 @@ int tkb_set_option(tkb_handle h, const char* key, const char* value) {
   TKB_TRY
   const std::string k = key, v = value;
   if (k == "conv_impl") {
-    if (v != "auto" && v != "simt" && v != "tc" && v != "tc_explicit" && v != "tc_im2col")
-      fail("conv_impl must be auto|simt|tc|tc_explicit|tc_im2col");
+    if (v != "auto" && v != "simt" && v != "tc" && v != "tc_explicit" && v != "tc_im2col" && v != "tc_nochain" && v != "tc_chain_all" &&
+        v != "tc_chain_siblings" && v != "tc_chain_split")
+      fail("conv_impl must be auto|simt|tc|tc_nochain|tc_chain_all|tc_chain_siblings|tc_chain_split|tc_explicit|tc_im2col");
     if (h->initialized && v != h->conv_impl) {
       // Re-planning is a configuration step like tkb_init: no run may be in flight.  The arena layout and every
       // uploaded / repacked constant belong to the old plan: drop the workspaces (streams and events included) and
@@ -2206,6 +2428,13 @@ int64_t tkb_trace_bytes(tkb_handle h) { return h->trace_host_bytes; }
 
 void tkb_fixed_point_multiplier_shift(double multiplier, int32_t* significand, int32_t* exponent) {
   fixed_point_multiplier_shift(multiplier, significand, exponent);
+}
+
+int tkb_debug_chain_stats(uint64_t* out8, int reset) {
+  TKB_TRY
+  CUDA_OK(cudaDeviceSynchronize());
+  tc_chain_stats((unsigned long long*)out8, reset != 0);
+  TKB_CATCH
 }
 
 int tkb_spin(double microseconds, void* cuda_stream) {

@@ -52,6 +52,7 @@ struct TcKernelParams {
   int dbg;                // timing experiments only (TKB_DBG): 1 = no epilogue work, 2 = no B loads, 4 = no A loads
   EpiParams e;            // generic epilogue (any rounding / compute dtype / float mode / raw int32)
   FastEpi f;              // host-folded fixed-point epilogue (default QNN configuration)
+  static constexpr bool kChain = false;  // single-layer launch: the residual was written by an EARLIER kernel (ld.global.nc is safe)
 };
 
 // Device timeline of CTA 0 (TKB_TIMELINE=1, tools/conv_probe.py): slot -> clock64.  0 entry, 1 prologue done,
@@ -60,7 +61,8 @@ struct TcKernelParams {
 // first tile's k-groups (GEMM kernel) / of the CTA's tiles (halo kernel).
 // Compiled in only with -DTKB_TIMELINE (TKB_BUILD_TIMELINE=1 python -m tachikoma_b200.build --force): the stamps
 // cost ~2 % of a ResNet-18 step even when disabled at run time (hot-loop instructions, instruction cache).
-__device__ __forceinline__ void tl_stamp(const TcKernelParams& p, int slot) {
+template <class P>
+__device__ __forceinline__ void tl_stamp(const P& p, int slot) {
   if (p.tl != nullptr && blockIdx.x == 0) p.tl[slot] = clock64();
 }
 #ifdef TKB_TIMELINE
@@ -133,6 +135,13 @@ __device__ __forceinline__ uint4 ldg_nc_16(const void* p) {
   asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
   return v;
 }
+// Coherent 16-byte load (L2, not the non-coherent path): for data another CTA of the SAME launch has written and
+// published with a release at gpu scope (chained layers: the residual of layer k is the output of layer k-2).
+__device__ __forceinline__ uint4 ldg_cg_16(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
 
 // ---- epilogue -------------------------------------------------------------------------------------
 // MODE selects the inlined hot path of the epilogue warps; everything unusual (ragged N tails, outputs
@@ -187,31 +196,35 @@ __device__ __forceinline__ int32_t fast_requant_raw(int32_t a, const int4& t) {
 }
 
 // one element, any configuration
+template <class P>
 static __device__ __noinline__ void epi_slow_elem(int32_t acc, int col, long long idx, const int32_t* drow,
-                                           const TcKernelParams* p, int mode) {
+                                           const P* p, int mode) {
   if (drow) acc = (int32_t)((uint32_t)acc + (uint32_t)__ldg(drow + col));
-  int32_t v;
+  int32_t v = 0;
   if (mode_is_fast(mode)) {
     const FastEpi& f = p->f;
     v = fast_requant(acc, __ldg(f.tabA + col), f.lo, f.hi);
     if (mode_is_sum(mode)) {
-      const int32_t b = (int32_t)(((const uint8_t*)p->sum)[idx] ^ (uint8_t)f.sum_xor);
+      const int32_t b = (int32_t)(((const volatile uint8_t*)p->sum)[idx] ^ (uint8_t)f.sum_xor);
       v = min(max(fast_side(v, f.lhs) + fast_side(b, f.rhs), f.sum_lo), f.sum_hi);
     }
   } else {
-    v = epilogue_one(acc, col, idx, p->e);
+    if constexpr (!P::kChain) v = epilogue_one(acc, col, idx, p->e);
   }
   store_from_i32(p->y, p->e.out_dtype, idx, v);
 }
 
 // 32 columns of one output row.  r: raw TMEM accumulators; ncols: valid columns (1..32); col0: absolute
 // first column; idx0: linear output index of (row, col0); tab_addr: shared address of this chunk's table.
-template <int MODE, bool AL8 = false>
-__device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const TcKernelParams& p, uint32_t tab_addr,
+template <int MODE, bool AL8 = false, class P = TcKernelParams>
+__device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const P& p, uint32_t tab_addr,
                                                bool row_valid, int ncols, int col0, long long idx0,
                                                const int32_t* drow, bool vec_ok) {
   if (!row_valid) return;
-  const bool hot = MODE != kModeGeneric && ncols == 32 && vec_ok && drow == nullptr;
+  // Rows whose window overlaps the padding add their border class's per-channel delta first (runtime.cu border_plan).
+  // The fast modes do that inside the hot path (chained launches: a quarter to a half of the pixels of a 14x14 / 7x7
+  // feature map are border pixels); the single-layer kernels keep sending those rows through the out-of-line path.
+  const bool hot = MODE != kModeGeneric && ncols == 32 && vec_ok && (drow == nullptr || (P::kChain && mode_is_fast(MODE)));
   if (!hot) {
 #pragma unroll
     for (int j = 0; j < 32; ++j)
@@ -232,7 +245,8 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const Tc
     const FastEpi& f = p.f;
     uint32_t sraw[8];
     if constexpr (mode_is_sum(MODE)) {
-      const uint4 s0 = ldg_nc_16((const uint8_t*)p.sum + idx0), s1 = ldg_nc_16((const uint8_t*)p.sum + idx0 + 16);
+      const uint4 s0 = P::kChain ? ldg_cg_16((const uint8_t*)p.sum + idx0) : ldg_nc_16((const uint8_t*)p.sum + idx0);
+      const uint4 s1 = P::kChain ? ldg_cg_16((const uint8_t*)p.sum + idx0 + 16) : ldg_nc_16((const uint8_t*)p.sum + idx0 + 16);
       sraw[0] = s0.x ^ f.sum_xor; sraw[1] = s0.y ^ f.sum_xor; sraw[2] = s0.z ^ f.sum_xor; sraw[3] = s0.w ^ f.sum_xor;
       sraw[4] = s1.x ^ f.sum_xor; sraw[5] = s1.y ^ f.sum_xor; sraw[6] = s1.z ^ f.sum_xor; sraw[7] = s1.w ^ f.sum_xor;
     }
@@ -260,10 +274,15 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const Tc
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         uint32_t word = 0;
+        int4 dv = make_int4(0, 0, 0, 0);
+        if constexpr (P::kChain) {
+          if (drow != nullptr) dv = __ldg((const int4*)(drow + col0) + i);
+        }
+        const int32_t dl[4] = {dv.x, dv.y, dv.z, dv.w};
 #pragma unroll
         for (int jj = 0; jj < 4; ++jj) {
           const int j = 4 * i + jj;
-          int32_t y = fast_requant((int32_t)r[j], lds128(tab_addr + j * 16), f.lo, f.hi);
+          int32_t y = fast_requant((int32_t)(r[j] + (uint32_t)dl[jj]), lds128(tab_addr + j * 16), f.lo, f.hi);
           if constexpr (mode_is_sum(MODE)) {
             const int32_t b = (int32_t)((sraw[i] >> (8 * jj)) & 0xFFu);
             y = min(max(fast_side(y, f.lhs) + fast_side(b, f.rhs), f.sum_lo), f.sum_hi);
@@ -288,8 +307,8 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const Tc
 
 // Drain one accumulator stage: the calling epilogue warp owns TMEM lanes 32*q .. +31 and columns
 // [cbeg0, cbeg0 + cspan) of the tile; `row` is the output row (pixel) of this lane.
-template <int BN, int MODE, bool AL8 = false>
-__device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t tmem_base, uint32_t lt, int q, int cbeg0, int cspan,
+template <int BN, int MODE, bool AL8 = false, class P = TcKernelParams>
+__device__ __forceinline__ void epi_drain_tile(const P& p, uint32_t tmem_base, uint32_t lt, int q, int cbeg0, int cspan,
                                                int lane, int row, bool row_valid, int b, int n0, uint32_t tab_base,
                                                bool vec_ok, uint64_t* tempty, uint64_t* tfull) {
   const long long row_off = ((long long)b * p.M + row) * p.N;
@@ -330,7 +349,7 @@ __device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[as]);
     }
-    epilogue_chunk<MODE, AL8>(ra, p, tab_base + c * 16, row_valid, min(32, cend - c), n0 + c, row_off + n0 + c, drow, vec_ok);
+    epilogue_chunk<MODE, AL8, P>(ra, p, tab_base + c * 16, row_valid, min(32, cend - c), n0 + c, row_off + n0 + c, drow, vec_ok);
     if (!more_b) break;
     tmem_ld_wait32(rb);
     const bool more_a = c + 64 < cend;
@@ -340,7 +359,7 @@ __device__ __forceinline__ void epi_drain_tile(const TcKernelParams& p, uint32_t
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[as]);
     }
-    epilogue_chunk<MODE, AL8>(rb, p, tab_base + (c + 32) * 16, row_valid, min(32, cend - c - 32), n0 + c + 32,
+    epilogue_chunk<MODE, AL8, P>(rb, p, tab_base + (c + 32) * 16, row_valid, min(32, cend - c - 32), n0 + c + 32,
                          row_off + n0 + c + 32, drow, vec_ok);
     if (!more_a) break;
   }

@@ -411,6 +411,30 @@ def test_models_bit_exact_with_trace(name, kw, impl):
     assert mod.launch_count() > 0
 
 
+@pytest.mark.parametrize("impl", ["tc_chain_all", "tc_chain_siblings", "tc_chain_split"])
+@pytest.mark.parametrize("name,kw", [MODEL_CASES[2], MODEL_CASES[4], ("resnet18", dict(batch=4, image=224))], ids=["resnet18-64px", "bert", "resnet18-224px"])
+def test_chained_launches_bit_exact_with_trace(name, kw, impl):
+    """Chained persistent tcgen05 launches (csrc/kernels_tc_chain.cu): layers merged into one kernel with per-image
+    completion counters, dynamic work claiming, TMA-store epilogue.  An opt-in experiment (slower than the single-layer
+    kernels on B200), kept bit-exact: output and serialized trace equal the oracle's."""
+    func = models.MODELS[name](**kw)
+    x = models.synthetic_input(name, kw["batch"])
+    if "image" in kw:
+        x = np.ascontiguousarray(x[:, :, :kw["image"], :kw["image"]])
+    if name == "bert_encoder":
+        x = np.random.default_rng(1).integers(0, 256, (kw["batch"] * kw["seq"], kw["hidden"])).astype("uint8")
+    out, mod, (js, consts, ins) = run_gpu(func, {"data": x}, conv_impl=impl, trace=True)
+    if name == "resnet18":
+        assert "chained tcgen05 launch" in mod.plan_summary() or "chain 0" in mod.plan_summary()
+    outs, recs = interp.run_json(js, consts, ins, want_trace=True)
+    np.testing.assert_equal(out, outs[0])
+    assert mod.trace_blob() == interp.save_ndarray_list(recs)
+    for _ in range(3):  # counters are re-zeroed every run
+        out2 = np.zeros_like(out)
+        mod.run(*ins, out2)
+        np.testing.assert_equal(out2, outs[0])
+
+
 def test_gpu_trace_passes_record_by_record_replay():
     """the GPU-produced trace is a valid witness -- every record re-computed on the oracle
     from the recorded inputs alone, chain and constants checked (oracle/replay.py)."""

@@ -169,6 +169,74 @@ def qnn_add(a, b, sa, zpa, sb, zpb, so, zpo):
     return out
 
 
+def _sc(v):
+    return np.float32(np.asarray(v, dtype=np.float32).reshape(-1)[0])
+
+
+def _zp(v):
+    return int(np.asarray(v).reshape(-1)[0])
+
+
+def qnn_mul(a, b, sa, zpa, sb, zpb, so, zpo):
+    """src/relay/qnn/op/mul.cc:66-101 (per-tensor form): Q' = (int32(a) - zp_a) * (int32(b) - zp_b) with int32
+    wrap-around, then Requantize(Q', scale = float32(sa) * float32(sb), zp 0 -> output qparams, dtype of the inputs)."""
+    a, b = np.ascontiguousarray(a), np.ascontiguousarray(b)
+    with np.errstate(over="ignore"):
+        qa = a.astype(np.int32) - np.int32(_zp(zpa))
+        qb = b.astype(np.int32) - np.int32(_zp(zpb))
+        prod = (qa.astype(np.int64) * qb.astype(np.int64)).astype(np.int32)  # two's-complement wrap of the int32 multiply
+    new_scale = np.float32(_sc(sa) * _sc(sb))
+    return requantize(prod, new_scale, 0, _sc(so), _zp(zpo), -1, "None", "None", str(a.dtype))
+
+
+def qnn_concatenate(tensors, scales, zps, so, zpo, axis):
+    """src/relay/qnn/op/concatenate.cc:138-213: requantize every input whose qparams differ from the output's
+    (IsEqualScalar on the float32 scale and the int32 zero point), keep its dtype, then concatenate."""
+    outs = []
+    for t, s_, z_ in zip(tensors, scales, zps):
+        t = np.ascontiguousarray(t)
+        if _sc(s_) != _sc(so) or _zp(z_) != _zp(zpo):
+            t = requantize(t, _sc(s_), _zp(z_), _sc(so), _zp(zpo), -1, "None", "None", str(t.dtype))
+        outs.append(t)
+    return np.ascontiguousarray(np.concatenate(outs, axis=axis))
+
+
+def _axis_split(shape, axis):
+    nd = len(shape)
+    if nd == 0:
+        return 1, 1, 1
+    ax = axis + nd if axis < 0 else axis
+    return int(np.prod(shape[:ax], dtype=np.int64)), int(shape[ax]), int(np.prod(shape[ax + 1:], dtype=np.int64))
+
+
+def quantize(data, scale, zp, axis=-1, out_dtype="int8"):
+    shape0 = np.asarray(data).shape  # ascontiguousarray turns rank 0 into rank 1
+    data = np.ascontiguousarray(data, dtype=np.float32).reshape(shape0)
+    sc = np.ascontiguousarray(np.asarray(scale, dtype=np.float32).reshape(-1))
+    z = np.ascontiguousarray(np.asarray(zp, dtype=np.int32).reshape(-1))
+    outer, C, inner = _axis_split(data.shape, axis)
+    if sc.size == 1 and z.size == 1:
+        outer, C, inner = outer * C * inner, 1, 1
+    out = np.empty(data.shape, dtype=out_dtype)
+    L = ctypes.c_int64
+    lib().tko_quantize(_p(data), L(outer), L(C), L(inner), _p(sc), _p(z), int(sc.size), int(z.size), DT[out_dtype], _p(out))
+    return out
+
+
+def dequantize(data, scale, zp, axis=-1):
+    shape0 = np.asarray(data).shape
+    data = np.ascontiguousarray(data).reshape(shape0)
+    sc = np.ascontiguousarray(np.asarray(scale, dtype=np.float32).reshape(-1))
+    z = np.ascontiguousarray(np.asarray(zp, dtype=np.int32).reshape(-1))
+    outer, C, inner = _axis_split(data.shape, axis)
+    if sc.size == 1 and z.size == 1:
+        outer, C, inner = outer * C * inner, 1, 1
+    out = np.empty(data.shape, dtype=np.float32)
+    L = ctypes.c_int64
+    lib().tko_dequantize(_p(data), DT[str(data.dtype)], L(outer), L(C), L(inner), _p(sc), _p(z), int(sc.size), int(z.size), _p(out))
+    return out
+
+
 def pool2d(data, pool_size, strides, padding, layout="NCHW", is_avg=False, count_include_pad=False):
     data = np.ascontiguousarray(data)
     N, C, H, W = [data.shape[layout.index(ch)] for ch in "NCHW"]
@@ -234,6 +302,15 @@ def eval_op(op, attrs, args):
                           attrs["out_dtype"])
     if op == "qnn.add":
         return qnn_add(*args[:8])
+    if op == "qnn.mul":
+        return qnn_mul(*args[:8])
+    if op == "qnn.concatenate":
+        n = int(attrs["num_inputs"])
+        return qnn_concatenate(args[:n], args[n:2 * n], args[2 * n:3 * n], args[3 * n], args[3 * n + 1], int(attrs["axis"]))
+    if op == "qnn.quantize":
+        return quantize(args[0], args[1], args[2], int(attrs.get("axis", -1)), attrs["out_dtype"])
+    if op == "qnn.dequantize":
+        return dequantize(args[0], args[1], args[2], int(attrs.get("axis", -1)))
     if op == "nn.bias_add":
         ax = attrs.get("axis", 1)
         shp = [1] * args[0].ndim
@@ -398,7 +475,13 @@ def _eval_json_node(node, ins):
         return ins[0].reshape(node["attrs"]["shape"][0][0])
     if op == "transpose":
         return eval_op(op, dict(axes=[int(x) for x in a["axes"]]), ins)
-    return eval_op(op, {}, ins)  # qnn.dense, qnn.batch_matmul, qnn.add, add, nn.batch_flatten
+    if op == "qnn.concatenate":
+        return eval_op(op, dict(axis=int(g("axis")), num_inputs=(len(ins) - 2) // 3), ins)
+    if op == "qnn.quantize":
+        return eval_op(op, dict(axis=int(g("axis", -1)), out_dtype=node["attrs"]["dtype"][0][0]), ins)
+    if op == "qnn.dequantize":
+        return eval_op(op, dict(axis=int(g("axis", -1))), ins)
+    return eval_op(op, {}, ins)  # qnn.dense, qnn.batch_matmul, qnn.add, qnn.mul, add, nn.batch_flatten
 
 
 def run_json(graph_json, consts, inputs, want_trace=False):

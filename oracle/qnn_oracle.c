@@ -396,6 +396,39 @@ void tko_dnnl_float_epilogue(const int32_t* acc, int64_t outer, int64_t C, int64
   }
 }
 
+/* qnn.quantize, src/relay/qnn/op/quantize.cc:113-150 (QuantizeLower): in float32,
+ *   clip(round(x / scale) + float(zp), qmin, qmax) -> cast to out_dtype
+ * round = tir.round = llvm.round (half away from zero: src/target/llvm/intrin_rule_llvm.cc:82-84).
+ * Layout [outer][C][inner]; n_q = 1 (per tensor) or C (per channel on the axis). */
+void tko_quantize(const float* in, int64_t outer, int64_t C, int64_t inner, const float* scale,
+                  const int32_t* zp, int n_scale, int n_zp, int out_dtype, void* out) {
+  int64_t lo, hi;
+  dtype_range(out_dtype, &lo, &hi);
+  const int64_t total = outer * C * inner;
+#pragma omp parallel for schedule(static) if (total > 65536)
+  for (int64_t idx = 0; idx < total; ++idx) {
+    const int64_t c = (idx / inner) % C;
+    float v = in[idx] / (n_scale == 1 ? scale[0] : scale[c]);
+    v = roundf(v);
+    v = v + (float)(n_zp == 1 ? zp[0] : zp[c]);
+    v = v < (float)lo ? (float)lo : (v > (float)hi ? (float)hi : v);
+    store_int(out, out_dtype, idx, (int64_t)v);
+  }
+}
+
+/* qnn.dequantize, src/relay/qnn/op/dequantize.cc:95-127 (DequantizeLower):
+ *   float32(int32(x) - zp) * scale   (int32 subtraction wraps, float32 multiply) */
+void tko_dequantize(const void* in, int in_dtype, int64_t outer, int64_t C, int64_t inner,
+                    const float* scale, const int32_t* zp, int n_scale, int n_zp, float* out) {
+  const int64_t total = outer * C * inner;
+#pragma omp parallel for schedule(static) if (total > 65536)
+  for (int64_t idx = 0; idx < total; ++idx) {
+    const int64_t c = (idx / inner) % C;
+    const int32_t t = wrap32((int64_t)(int32_t)load_int(in, in_dtype, idx) - (int64_t)(n_zp == 1 ? zp[0] : zp[c]));
+    out[idx] = (float)t * (n_scale == 1 ? scale[0] : scale[c]);
+  }
+}
+
 /* Thread control for the timed CPU-baseline legs of bench.py: launchers such as torchrun export
  * OMP_NUM_THREADS=1, which would silently turn the "all host cores" baseline into a single-thread one. */
 int tko_set_threads(int n) {

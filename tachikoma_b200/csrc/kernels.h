@@ -36,6 +36,18 @@ void launch_requantize(const void* x, int x_dtype, void* y, int y_dtype, long lo
                        const RqParams& p, cudaStream_t s);
 void launch_qnn_add(const void* a, const void* b, void* y, int dtype, long long n, const EpiParams& e,
                     cudaStream_t s);
+// qnn.mul (per tensor): y = requantize((a - zpa) * (b - zpb)) with rq built for scale_a * scale_b -> output qparams
+void launch_qnn_mul(const void* a, const void* b, void* y, int dtype, long long n, int32_t zpa, int32_t zpb,
+                    const RqParams& rq, cudaStream_t s);
+// qnn.quantize / qnn.dequantize over [outer][C][inner]; parameters per tensor (n == 1: scale0 / zp0) or per channel
+// (device arrays of C entries)
+void launch_quantize(const float* x, void* y, int y_dtype, long long outer, int C, long long inner, const float* scale,
+                     const int32_t* zp, float scale0, int32_t zp0, int n_scale, int n_zp, int32_t lo, int32_t hi, cudaStream_t s);
+void launch_dequantize(const void* x, int x_dtype, float* y, long long outer, int C, long long inner, const float* scale,
+                       const int32_t* zp, float scale0, int32_t zp0, int n_scale, int n_zp, cudaStream_t s);
+// qnn.concatenate: copy (requant == 0) or requantize one input [outer][row_in] into rows of row_out elements at `off`
+void launch_concat_piece(const void* x, void* y, int dtype, long long outer, long long row_in, long long row_out, long long off,
+                         const RqParams& rq, int requant, cudaStream_t s);
 void launch_clip(const void* x, void* y, int dtype, long long n, double lo, double hi, cudaStream_t s);
 void launch_cast(const void* x, int x_dtype, void* y, int y_dtype, long long n, cudaStream_t s);
 // y = x + b[c] (int32 wrap / same dtype) over [outer][C][inner]; b has C elements of dtype b_dtype

@@ -427,6 +427,189 @@ void launch_qnn_add(const void* a, const void* b, void* y, int dtype, long long 
   ++g_launches;
 }
 
+// ---- qnn.mul (src/relay/qnn/op/mul.cc:66-101, per-tensor form) ----------------------------------------------------
+// Q' = (int32(a) - zp_a) * (int32(b) - zp_b) in the int32 ring, requantized from scale_a * scale_b (float32 product,
+// computed on the host) to the output qparams with the default UPWARD / int64 lowering; output dtype = input dtype.
+// 8-bit tensors: 16 elements per thread, 128-bit loads and stores.
+__device__ __forceinline__ int32_t qnn_mul_one(int32_t a, int32_t b, int32_t zpa, int32_t zpb, const RqParams& rq) {
+  const int32_t qa = (int32_t)((uint32_t)a - (uint32_t)zpa), qb = (int32_t)((uint32_t)b - (uint32_t)zpb);
+  return requantize_one((int32_t)((uint32_t)qa * (uint32_t)qb), 0, rq);
+}
+
+__global__ void __launch_bounds__(256) qnn_mul8_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ y,
+                                                       int dtype, long long nv, int32_t zpa, int32_t zpb, RqParams rq) {
+  for (long long i = blockIdx.x * 256LL + threadIdx.x; i < nv; i += (long long)gridDim.x * 256) {
+    const uint4 va = __ldg(a + i), vb = __ldg(b + i);
+    const uint32_t pa[4] = {va.x, va.y, va.z, va.w}, pb[4] = {vb.x, vb.y, vb.z, vb.w};
+    uint32_t po[4];
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      uint32_t o = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t ba = (pa[w] >> (8 * k)) & 0xFF, bb = (pb[w] >> (8 * k)) & 0xFF;
+        const int32_t xa = dtype == kU8 ? (int32_t)ba : (int32_t)(int8_t)ba, xb = dtype == kU8 ? (int32_t)bb : (int32_t)(int8_t)bb;
+        o |= ((uint32_t)qnn_mul_one(xa, xb, zpa, zpb, rq) & 0xFF) << (8 * k);
+      }
+      po[w] = o;
+    }
+    y[i] = make_uint4(po[0], po[1], po[2], po[3]);
+  }
+}
+
+__global__ void qnn_mul_kernel(const void* __restrict__ a, const void* __restrict__ b, void* __restrict__ y, int dtype,
+                               long long n, int32_t zpa, int32_t zpb, RqParams rq) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    store_from_i32(y, dtype, i, qnn_mul_one(load_as_i32(a, dtype, i), load_as_i32(b, dtype, i), zpa, zpb, rq));
+}
+
+void launch_qnn_mul(const void* a, const void* b, void* y, int dtype, long long n, int32_t zpa, int32_t zpb,
+                    const RqParams& rq, cudaStream_t s) {
+  if (n == 0) return;
+  if ((dtype == kU8 || dtype == kI8) && (n & 15) == 0 && ((((uintptr_t)a) | ((uintptr_t)b) | ((uintptr_t)y)) & 15) == 0) {
+    const long long nv = n >> 4;
+    const int nb = (int)std::min<long long>((nv + 255) / 256, 148LL * 8);
+    qnn_mul8_kernel<<<nb, 256, 0, s>>>((const uint4*)a, (const uint4*)b, (uint4*)y, dtype, nv, zpa, zpb, rq);
+  } else {
+    qnn_mul_kernel<<<blocks_for(n, 256), 256, 0, s>>>(a, b, y, dtype, n, zpa, zpb, rq);
+  }
+  ++g_launches;
+}
+
+// ---- qnn.quantize / qnn.dequantize (src/relay/qnn/op/quantize.cc:113-150, dequantize.cc:95-127) ----------------------
+// float32 arithmetic exactly as the reference lowers it: x / scale (IEEE division), tir.round = llvm.round (half away from
+// zero), + float(zp), clip to the output dtype's range, cast; and float32(int32(x) - zp) * scale.  Layout
+// [outer][C][inner] with per-tensor (n == 1) or per-channel (n == C) parameters; four elements per thread where the
+// inner extent allows (128-bit float accesses, 32-bit packed 8-bit accesses).
+struct QParams {
+  const float* scale;
+  const int32_t* zp;
+  float scale0;
+  int32_t zp0;
+  int n_scale, n_zp;
+};
+
+__device__ __forceinline__ int32_t quantize_one(float x, float sc, int32_t zp, int32_t lo, int32_t hi) {
+  float v = roundf(__fdiv_rn(x, sc));
+  v = __fadd_rn(v, (float)zp);
+  v = fminf(fmaxf(v, (float)lo), (float)hi);
+  return (int32_t)v;
+}
+
+__global__ void quantize_kernel(const float* __restrict__ x, void* __restrict__ y, int y_dtype, long long total, int C,
+                                long long inner, QParams q, int32_t lo, int32_t hi, int vec4) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  if (vec4) {  // inner % 4 == 0: the four elements share a channel
+    for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < total / 4; v += stride) {
+      const long long i = v * 4;
+      const int c = (int)((i / inner) % C);
+      const float sc = q.n_scale == 1 ? q.scale0 : q.scale[c];
+      const int32_t zp = q.n_zp == 1 ? q.zp0 : q.zp[c];
+      const float4 f = __ldg((const float4*)x + v);
+      const int32_t r0 = quantize_one(f.x, sc, zp, lo, hi), r1 = quantize_one(f.y, sc, zp, lo, hi);
+      const int32_t r2 = quantize_one(f.z, sc, zp, lo, hi), r3 = quantize_one(f.w, sc, zp, lo, hi);
+      if (y_dtype == kU8 || y_dtype == kI8)
+        ((uint32_t*)y)[v] = (uint32_t)(r0 & 0xFF) | ((uint32_t)(r1 & 0xFF) << 8) | ((uint32_t)(r2 & 0xFF) << 16) | ((uint32_t)(r3 & 0xFF) << 24);
+      else if (y_dtype == kI32) ((int4*)y)[v] = make_int4(r0, r1, r2, r3);
+      else { store_from_i32(y, y_dtype, i, r0); store_from_i32(y, y_dtype, i + 1, r1); store_from_i32(y, y_dtype, i + 2, r2); store_from_i32(y, y_dtype, i + 3, r3); }
+    }
+    return;
+  }
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c = (int)((i / inner) % C);
+    store_from_i32(y, y_dtype, i, quantize_one(x[i], q.n_scale == 1 ? q.scale0 : q.scale[c], q.n_zp == 1 ? q.zp0 : q.zp[c], lo, hi));
+  }
+}
+
+__global__ void dequantize_kernel(const void* __restrict__ x, int x_dtype, float* __restrict__ y, long long total, int C,
+                                  long long inner, QParams q, int vec4) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  if (vec4) {
+    for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < total / 4; v += stride) {
+      const long long i = v * 4;
+      const int c = (int)((i / inner) % C);
+      const float sc = q.n_scale == 1 ? q.scale0 : q.scale[c];
+      const uint32_t zp = (uint32_t)(q.n_zp == 1 ? q.zp0 : q.zp[c]);
+      int32_t t[4];
+      if (x_dtype == kU8 || x_dtype == kI8) {
+        const uint32_t w = __ldg((const uint32_t*)x + v);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) t[k] = x_dtype == kU8 ? (int32_t)((w >> (8 * k)) & 0xFF) : (int32_t)(int8_t)((w >> (8 * k)) & 0xFF);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) t[k] = load_as_i32(x, x_dtype, i + k);
+      }
+      ((float4*)y)[v] = make_float4(__fmul_rn((float)(int32_t)((uint32_t)t[0] - zp), sc), __fmul_rn((float)(int32_t)((uint32_t)t[1] - zp), sc),
+                                    __fmul_rn((float)(int32_t)((uint32_t)t[2] - zp), sc), __fmul_rn((float)(int32_t)((uint32_t)t[3] - zp), sc));
+    }
+    return;
+  }
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c = (int)((i / inner) % C);
+    const int32_t t = (int32_t)((uint32_t)load_as_i32(x, x_dtype, i) - (uint32_t)(q.n_zp == 1 ? q.zp0 : q.zp[c]));
+    y[i] = __fmul_rn((float)t, q.n_scale == 1 ? q.scale0 : q.scale[c]);
+  }
+}
+
+static QParams make_qparams(const float* scale, const int32_t* zp, float scale0, int32_t zp0, int n_scale, int n_zp) {
+  QParams q;
+  q.scale = scale; q.zp = zp; q.scale0 = scale0; q.zp0 = zp0; q.n_scale = n_scale; q.n_zp = n_zp;
+  return q;
+}
+
+void launch_quantize(const float* x, void* y, int y_dtype, long long outer, int C, long long inner, const float* scale,
+                     const int32_t* zp, float scale0, int32_t zp0, int n_scale, int n_zp, int32_t lo, int32_t hi, cudaStream_t s) {
+  const long long total = outer * C * inner;
+  if (total == 0) return;
+  const int vec4 = (inner % 4 == 0) && ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0;
+  quantize_kernel<<<blocks_for(vec4 ? total / 4 : total, 256), 256, 0, s>>>(x, y, y_dtype, total, C, inner,
+                                                                          make_qparams(scale, zp, scale0, zp0, n_scale, n_zp), lo, hi, vec4);
+  ++g_launches;
+}
+
+void launch_dequantize(const void* x, int x_dtype, float* y, long long outer, int C, long long inner, const float* scale,
+                       const int32_t* zp, float scale0, int32_t zp0, int n_scale, int n_zp, cudaStream_t s) {
+  const long long total = outer * C * inner;
+  if (total == 0) return;
+  const int vec4 = (inner % 4 == 0) && ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0;
+  dequantize_kernel<<<blocks_for(vec4 ? total / 4 : total, 256), 256, 0, s>>>(x, x_dtype, y, total, C, inner,
+                                                                            make_qparams(scale, zp, scale0, zp0, n_scale, n_zp), vec4);
+  ++g_launches;
+}
+
+// ---- qnn.concatenate (src/relay/qnn/op/concatenate.cc:138-213): one piece [outer][Ci][inner] into [outer][Ctot][inner] at
+// channel offset coff, requantized to the output qparams when its own differ (rq.skip == 0), same dtype.  16-byte copies
+// when Ci * inner and the offsets allow.
+__global__ void concat_piece_kernel(const void* __restrict__ x, void* __restrict__ y, int dtype, long long outer, long long row_in,
+                                    long long row_out, long long off, RqParams rq, int requant, int vec16) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  if (vec16) {  // rows and offsets are multiples of 16 bytes, no requantize
+    const long long rv = row_in * dtype_size(dtype) / 16, ov = row_out * dtype_size(dtype) / 16, offv = off * dtype_size(dtype) / 16;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < outer * rv; i += stride) {
+      const long long o = i / rv, r = i - o * rv;
+      ((uint4*)y)[o * ov + offv + r] = __ldg((const uint4*)x + i);
+    }
+    return;
+  }
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < outer * row_in; i += stride) {
+    const long long o = i / row_in, r = i - o * row_in;
+    int32_t v = load_as_i32(x, dtype, i);
+    if (requant) v = requantize_one(v, 0, rq);
+    store_from_i32(y, dtype, o * row_out + off + r, v);
+  }
+}
+
+void launch_concat_piece(const void* x, void* y, int dtype, long long outer, long long row_in, long long row_out, long long off,
+                         const RqParams& rq, int requant, cudaStream_t s) {
+  if (outer * row_in == 0) return;
+  const int es = dtype_size(dtype);
+  const int vec16 = !requant && (row_in * es) % 16 == 0 && (row_out * es) % 16 == 0 && (off * es) % 16 == 0 &&
+                    ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0;
+  const long long work = vec16 ? outer * row_in * es / 16 : outer * row_in;
+  concat_piece_kernel<<<blocks_for(work, 256), 256, 0, s>>>(x, y, dtype, outer, row_in, row_out, off, rq, requant, vec16);
+  ++g_launches;
+}
+
 __global__ void clip_kernel(const void* __restrict__ x, void* __restrict__ y, int dtype, long long n, double lo,
                             double hi) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {

@@ -1300,6 +1300,110 @@ static void plan_qnn_add(Planner& P, int nid) {
   });
 }
 
+// qnn.mul, per-tensor form (src/relay/qnn/op/mul.cc:66-101)
+static void plan_qnn_mul(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int a_eid = (int)P.g.eid(n.inputs[0]), b_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& A = P.ent[a_eid];
+  if (A.shape != P.ent[b_eid].shape || A.dtype != P.ent[b_eid].dtype) fail("Unsupported op: qnn.mul with broadcasting operands");
+  if (A.dtype == kF32 || A.dtype == kI64) fail("Unsupported op: qnn.mul on non-integer tensors");
+  auto sa = P.cfloats((int)P.g.eid(n.inputs[2]), "lhs_scale"), sb = P.cfloats((int)P.g.eid(n.inputs[4]), "rhs_scale");
+  if (sa.size() != 1 || sb.size() != 1) fail("Unsupported op: qnn.mul with per-channel scales");
+  const int32_t zpa = P.cints((int)P.g.eid(n.inputs[3]), "lhs_zero_point")[0], zpb = P.cints((int)P.g.eid(n.inputs[5]), "rhs_zero_point")[0];
+  const float so = P.cfloats((int)P.g.eid(n.inputs[6]), "output_scale")[0];
+  const int32_t zpo = P.cints((int)P.g.eid(n.inputs[7]), "output_zero_point")[0];
+  const float new_scale = sa[0] * sb[0];  // float32 product, mul.cc:91-93
+  const int dt = A.dtype;
+  RqParams rq = make_rq(P, {new_scale}, {0}, so, zpo, kUpward, kInt64, dt, 1);
+  const int phys = (P.preferred(a_eid) == kNHWC || P.preferred(b_eid) == kNHWC) && A.shape.size() == 4 &&
+                           !P.ent[P.root(a_eid)].is_const && !P.ent[P.root(b_eid)].is_const ? kNHWC : kLogical;
+  P.need(a_eid, phys);
+  P.need(b_eid, phys);
+  P.produce(y_eid, phys);
+  const long long cnt = numel(A.shape);
+  P.rt->hbm_bytes += 3 * A.bytes();
+  P.add_step("qnn.mul -> vectorised elementwise kernel", [=](RunCtx& c) {
+    launch_qnn_mul(c.ptr(a_eid, phys), c.ptr(b_eid, phys), c.ptr(y_eid, phys), dt, cnt, zpa, zpb, rq, c.s);
+  });
+}
+
+// qnn.quantize / qnn.dequantize at the float edges of a graph (quantize.cc:113-150, dequantize.cc:95-127)
+static void plan_quantize(Planner& P, int nid, bool dequant) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[x_eid];
+  const Entry& Y = P.ent[y_eid];
+  if (dequant ? (X.dtype == kF32 || X.dtype == kI64 || Y.dtype != kF32) : (X.dtype != kF32 || Y.dtype == kF32 || Y.dtype == kI64))
+    fail("Unsupported op: %s from dtype %d to dtype %d", n.name.c_str(), X.dtype, Y.dtype);
+  auto scl = P.cfloats((int)P.g.eid(n.inputs[1]), "scale");
+  auto zps = P.cints((int)P.g.eid(n.inputs[2]), "zero_point");
+  long long outer, inner;
+  int C;
+  axis_split(X, (int)n.i64("axis", -1), kLogical, &outer, &C, &inner);
+  if (scl.size() == 1 && zps.size() == 1) { outer *= (long long)C * inner; C = 1; inner = 1; }
+  if ((scl.size() != 1 && (int)scl.size() != C) || (zps.size() != 1 && (int)zps.size() != C))
+    fail("%s: %d scales / %d zero points for an axis of %d", n.name.c_str(), (int)scl.size(), (int)zps.size(), C);
+  const float* scl_dev = scl.size() > 1 ? (const float*)P.dev_upload(scl.data(), scl.size() * 4) : nullptr;
+  const int32_t* zp_dev = zps.size() > 1 ? (const int32_t*)P.dev_upload(zps.data(), zps.size() * 4) : nullptr;
+  const float s0 = scl[0];
+  const int32_t z0 = zps[0];
+  const int ns = (int)scl.size(), nz = (int)zps.size(), xdt = X.dtype, ydt = Y.dtype;
+  int32_t lo, hi;
+  dtype_range(ydt, &lo, &hi);
+  P.need(x_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->hbm_bytes += X.bytes() + Y.bytes();
+  if (dequant)
+    P.add_step("qnn.dequantize -> vectorised elementwise kernel", [=](RunCtx& c) {
+      launch_dequantize(c.ptr(x_eid, kLogical), xdt, (float*)c.ptr(y_eid, kLogical), outer, C, inner, scl_dev, zp_dev, s0, z0, ns, nz, c.s);
+    });
+  else
+    P.add_step("qnn.quantize -> vectorised elementwise kernel", [=](RunCtx& c) {
+      launch_quantize((const float*)c.ptr(x_eid, kLogical), c.ptr(y_eid, kLogical), ydt, outer, C, inner, scl_dev, zp_dev, s0, z0, ns, nz, lo, hi, c.s);
+    });
+}
+
+// qnn.concatenate (concatenate.cc:138-213): inputs = n tensors, n scales, n zero points, output scale, output zero point
+static void plan_qnn_concatenate(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int y_eid = (int)P.g.eid(nid, 0);
+  const Entry& Y = P.ent[y_eid];
+  if (n.inputs.size() < 5 || (n.inputs.size() - 2) % 3 != 0) fail("qnn.concatenate: expected n tensors, n scales, n zero points, 2 output parameters");
+  const int cnt = (int)(n.inputs.size() - 2) / 3;
+  const int rank = (int)Y.shape.size();
+  int axis = (int)n.i64("axis", 0);
+  if (axis < 0) axis += rank;
+  if (axis < 0 || axis >= rank) fail("qnn.concatenate: axis out of range");
+  if (Y.dtype == kF32 || Y.dtype == kI64) fail("Unsupported op: qnn.concatenate on non-integer tensors");
+  const float so = P.cfloats((int)P.g.eid(n.inputs[3 * cnt]), "output_scale")[0];
+  const int32_t zpo = P.cints((int)P.g.eid(n.inputs[3 * cnt + 1]), "output_zero_point")[0];
+  long long outer = 1, inner = 1;
+  for (int i = 0; i < axis; ++i) outer *= Y.shape[i];
+  for (int i = axis + 1; i < rank; ++i) inner *= Y.shape[i];
+  const long long row_out = Y.shape[axis] * inner;
+  P.produce(y_eid, kLogical);
+  long long off = 0;
+  const int dt = Y.dtype;
+  for (int i = 0; i < cnt; ++i) {
+    const int x_eid = (int)P.g.eid(n.inputs[i]);
+    const Entry& X = P.ent[x_eid];
+    if (X.dtype != dt || (int)X.shape.size() != rank) fail("qnn.concatenate: inputs must share dtype and rank");
+    for (int d = 0; d < rank; ++d)
+      if (d != axis && X.shape[d] != Y.shape[d]) fail("qnn.concatenate: input %d does not match the output shape", i);
+    const float si = P.cfloats((int)P.g.eid(n.inputs[cnt + i]), "input_scale")[0];
+    const int32_t zi = P.cints((int)P.g.eid(n.inputs[2 * cnt + i]), "input_zero_point")[0];
+    const int requant = !(si == so && zi == zpo);  // IsEqualScalar on both, concatenate.cc:186-187
+    RqParams rq = make_rq(P, {si}, {zi}, so, zpo, kUpward, kInt64, dt, 1);
+    const long long row_in = X.shape[axis] * inner, o = off;
+    P.need(x_eid, kLogical);
+    P.rt->hbm_bytes += 2 * X.bytes();
+    P.add_step("qnn.concatenate piece " + std::to_string(i) + (requant ? " -> requantize into the output slice" : " -> copy into the output slice"),
+               [=](RunCtx& c) { launch_concat_piece(c.ptr(x_eid, kLogical), c.ptr(y_eid, kLogical), dt, outer, row_in, row_out, o, rq, requant, c.s); });
+    off += row_in;
+  }
+  if (off != row_out) fail("qnn.concatenate: the inputs do not fill the output along axis %d", axis);
+}
+
 static void plan_unary(Planner& P, int nid) {  // clip, cast
   const GNode& n = P.g.nodes[nid];
   const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
@@ -1649,6 +1753,10 @@ static void build_plan(tkb_runtime* rt) {
     else if (op == "qnn.batch_matmul") plan_batch_matmul(P, (int)nid);
     else if (op == "qnn.requantize") plan_requantize(P, (int)nid);
     else if (op == "qnn.add") plan_qnn_add(P, (int)nid);
+    else if (op == "qnn.mul") plan_qnn_mul(P, (int)nid);
+    else if (op == "qnn.quantize") plan_quantize(P, (int)nid, false);
+    else if (op == "qnn.dequantize") plan_quantize(P, (int)nid, true);
+    else if (op == "qnn.concatenate") plan_qnn_concatenate(P, (int)nid);
     else if (op == "clip" || op == "cast") plan_unary(P, (int)nid);
     else if (op == "nn.bias_add" || op == "add") plan_add(P, (int)nid);
     else if (op == "nn.max_pool2d" || op == "nn.avg_pool2d" || op == "nn.global_avg_pool2d") plan_pool(P, (int)nid);

@@ -19,7 +19,8 @@ import numpy as np
 
 __all__ = [
     "Expr", "Var", "Constant", "Call", "Function", "var", "const", "post_order",
-    "qnn_conv2d", "qnn_dense", "qnn_batch_matmul", "qnn_requantize", "qnn_add", "bias_add", "add",
+    "qnn_conv2d", "qnn_dense", "qnn_batch_matmul", "qnn_requantize", "qnn_add", "qnn_mul", "qnn_concatenate",
+    "qnn_quantize", "qnn_dequantize", "bias_add", "add",
     "clip", "cast", "max_pool2d", "avg_pool2d", "global_avg_pool2d", "pad", "reshape",
     "batch_flatten", "transpose",
 ]
@@ -180,6 +181,50 @@ def qnn_add(lhs, rhs, lhs_scale, lhs_zero_point, rhs_scale, rhs_zero_point, outp
     args = [lhs, rhs, _c(lhs_scale, "float32"), _c(lhs_zero_point, "int32"), _c(rhs_scale, "float32"),
             _c(rhs_zero_point, "int32"), _c(output_scale, "float32"), _c(output_zero_point, "int32")]
     return Call("qnn.add", args, dict(lhs_axis=int(lhs_axis), rhs_axis=int(rhs_axis)), lhs.shape, lhs.dtype)
+
+
+def qnn_mul(lhs, rhs, lhs_scale, lhs_zero_point, rhs_scale, rhs_zero_point, output_scale,
+            output_zero_point, lhs_axis=-1, rhs_axis=-1):
+    """tvm.relay.qnn.op.mul (src/relay/qnn/op/mul.cc:43-101): (Qa - zp_a) * (Qb - zp_b) in int32, requantized from
+    the float32 product of the two scales to the output qparams; output dtype = input dtype.  Per-tensor form."""
+    assert lhs.shape == rhs.shape and lhs.dtype == rhs.dtype
+    args = [lhs, rhs, _c(lhs_scale, "float32"), _c(lhs_zero_point, "int32"), _c(rhs_scale, "float32"),
+            _c(rhs_zero_point, "int32"), _c(output_scale, "float32"), _c(output_zero_point, "int32")]
+    return Call("qnn.mul", args, dict(lhs_axis=int(lhs_axis), rhs_axis=int(rhs_axis)), lhs.shape, lhs.dtype)
+
+
+def qnn_concatenate(data, input_scales, input_zero_points, output_scale, output_zero_point, axis):
+    """tvm.relay.qnn.op.concatenate (src/relay/qnn/op/concatenate.cc:138-213): every input whose (scale, zero point)
+    differs from the output's is requantized to them (same dtype), then nn.concatenate.  Arguments of the call: the n
+    tensors, their n scales, their n zero points, output scale, output zero point (the tuples flattened, as the JSON
+    serializer does)."""
+    data = list(data)
+    n = len(data)
+    assert n >= 1 and len(input_scales) == n and len(input_zero_points) == n
+    rank = len(data[0].shape)
+    ax = axis + rank if axis < 0 else axis
+    oshape = list(data[0].shape)
+    oshape[ax] = sum(d.shape[ax] for d in data)
+    for d in data:
+        assert d.dtype == data[0].dtype and len(d.shape) == rank
+        assert all(d.shape[i] == oshape[i] for i in range(rank) if i != ax)
+    args = data + [_c(s, "float32") for s in input_scales] + [_c(z, "int32") for z in input_zero_points] + \
+        [_c(output_scale, "float32"), _c(output_zero_point, "int32")]
+    return Call("qnn.concatenate", args, dict(axis=int(axis), num_inputs=n), oshape, data[0].dtype)
+
+
+def qnn_quantize(data, output_scale, output_zero_point, axis=-1, out_dtype="int8"):
+    """tvm.relay.qnn.op.quantize (src/relay/qnn/op/quantize.cc:113-150): clip(round(x / scale) + zp, qmin, qmax)
+    in float32, cast to out_dtype; scale / zero point scalar or per-``axis`` vectors."""
+    assert data.dtype == "float32"
+    return Call("qnn.quantize", [data, _c(output_scale, "float32"), _c(output_zero_point, "int32")],
+                dict(axis=int(axis), out_dtype=out_dtype), data.shape, out_dtype)
+
+
+def qnn_dequantize(data, input_scale, input_zero_point, axis=-1):
+    """tvm.relay.qnn.op.dequantize (src/relay/qnn/op/dequantize.cc:95-127): float32(int32(x) - zp) * scale."""
+    return Call("qnn.dequantize", [data, _c(input_scale, "float32"), _c(input_zero_point, "int32")],
+                dict(axis=int(axis)), data.shape, "float32")
 
 
 def bias_add(data, bias, axis=1):

@@ -8,7 +8,8 @@ TVM itself cannot be imported here, so a small shim ``tvm`` package is installed
 ``sys.modules`` whose ``relay.*`` constructors build ``tachikoma_b200.relay`` expressions.  The
 reference test files
     tests/python/relay/test_op_qnn_requantize.py, test_op_qnn_dense.py, test_op_qnn_add.py,
-    tests/python/relay/test_op_qnn_batch_matmul.py, test_op_qnn_conv2d.py
+    tests/python/relay/test_op_qnn_batch_matmul.py, test_op_qnn_conv2d.py,
+    tests/python/relay/test_op_qnn_mul.py, test_op_qnn_concatenate.py, test_op_qnn_quantize.py, test_op_qnn_dequantize.py
 are then executed unmodified.  Whenever a test compares a QNN graph's output with a golden
 (``np.testing.assert_equal``) the triple (graph, inputs, golden) is captured.  For the conv2d
 property tests the golden is the test's own *reference function* (int32 nn.conv2d over
@@ -33,7 +34,9 @@ from tachikoma_b200 import relay as R  # noqa: E402
 
 REF_TESTS = "/root/reference/tests/python/relay"
 FILES = ["test_op_qnn_requantize.py", "test_op_qnn_dense.py", "test_op_qnn_add.py",
-         "test_op_qnn_batch_matmul.py", "test_op_qnn_conv2d.py"]
+         "test_op_qnn_batch_matmul.py", "test_op_qnn_conv2d.py",
+         # round 2; appended so that the cases above keep their indices and random draws
+         "test_op_qnn_mul.py", "test_op_qnn_concatenate.py", "test_op_qnn_quantize.py", "test_op_qnn_dequantize.py"]
 
 CASES, SKIPPED = [], []
 CURRENT = {"name": ""}
@@ -111,6 +114,21 @@ def to_ir(e, memo):
         r = R.qnn_batch_matmul(a[0], a[1], a[2], a[3], a[4], a[5], **at)
     elif e.op == "qnn.add":
         r = R.qnn_add(*a, **at)
+    elif e.op == "qnn.mul":
+        r = R.qnn_mul(*a, **at)
+    elif e.op == "qnn.concatenate":
+        n = at["num_inputs"]
+        r = R.qnn_concatenate(a[:n], a[n:2 * n], a[2 * n:3 * n], a[3 * n], a[3 * n + 1], at["axis"])
+    elif e.op == "qnn.quantize":
+        for z in a[1:3]:
+            if not isinstance(z, R.Constant):
+                raise Unsupported("non-constant qnn parameter")
+        r = R.qnn_quantize(a[0], a[1], a[2], **at)
+    elif e.op == "qnn.dequantize":
+        for z in a[1:3]:
+            if not isinstance(z, R.Constant):
+                raise Unsupported("non-constant qnn parameter")
+        r = R.qnn_dequantize(a[0], a[1], a[2], **at)
     elif e.op == "qnn.conv2d":
         for z in a[2:6]:
             if not isinstance(z, R.Constant):
@@ -118,6 +136,10 @@ def to_ir(e, memo):
         r = R.qnn_conv2d(a[0], a[1], a[2], a[3], a[4], a[5], **at)
     elif e.op == "nn.bias_add":
         r = R.bias_add(a[0], a[1], **at)
+    elif e.op in ("multiply", "add", "subtract") and all(isinstance(x, R.Constant) for x in a):
+        # constant expressions used as quantization parameters (test_op_qnn_conv2d.py:446-448): what FoldConstant does
+        fn = {"multiply": np.multiply, "add": np.add, "subtract": np.subtract}[e.op]
+        r = R.Constant(fn(a[0].data, a[1].data).astype(a[0].data.dtype))
     else:
         raise Unsupported(f"op {e.op} in qnn graph")
     memo[id(e)] = r
@@ -187,7 +209,7 @@ def np_eval(e, env, memo):
 class Sentinel:
     def __init__(self, func, inputs):
         self.func, self.inputs = func, inputs
-        self.dtype = func.body.dtype  # tests assert res.dtype == expected
+        self.dtype = np.dtype(func.body.dtype)  # tests assert res.dtype == expected (a string or a numpy type)
 
     def numpy(self):
         return self
@@ -353,7 +375,31 @@ def install_shim():
         finally:
             RQ_CFG.update(old)
 
-    qop = types.SimpleNamespace(requantize=q_requantize, dense=q_dense, batch_matmul=q_bmm, add=q_add,
+    def q_mul(lhs, rhs, lhs_scale, lhs_zero_point, rhs_scale, rhs_zero_point, output_scale, output_zero_point,
+              lhs_axis=-1, rhs_axis=-1):
+        return S("qnn.mul", [lhs, rhs, lhs_scale, lhs_zero_point, rhs_scale, rhs_zero_point, output_scale,
+                             output_zero_point], dict(lhs_axis=lhs_axis, rhs_axis=rhs_axis))
+
+    def q_concatenate(data, input_scales, input_zero_points, output_scale, output_zero_point, axis):
+        if isinstance(data, S):  # a call that yields a tuple (relay.split): not expressible in the mini IR
+            raise Unsupported("qnn.concatenate over a tuple-valued call")
+        data = list(data)
+        return S("qnn.concatenate", data + list(input_scales) + list(input_zero_points) + [output_scale, output_zero_point],
+                 dict(axis=int(axis), num_inputs=len(data)))
+
+    def q_quantize(data, output_scale, output_zero_point, axis=-1, out_dtype="int8"):
+        return S("qnn.quantize", [data, output_scale, output_zero_point], dict(axis=int(axis), out_dtype=out_dtype))
+
+    def q_dequantize(data, input_scale, input_zero_point, axis=-1):
+        return S("qnn.dequantize", [data, input_scale, input_zero_point], dict(axis=int(axis)))
+
+    def r_split(*a, **k):
+        raise Unsupported("relay.split (tuple-valued call)")
+    relay.split = r_split
+    relay.TensorType = lambda shape, dtype="float32": ("TensorType", tuple(shape), dtype)
+
+    qop = types.SimpleNamespace(requantize=q_requantize, dense=q_dense, batch_matmul=q_bmm, add=q_add, mul=q_mul,
+                                concatenate=q_concatenate, quantize=q_quantize, dequantize=q_dequantize,
                                 conv2d=q_conv2d, requantize_config=requantize_config)
     relay.qnn = types.SimpleNamespace(op=qop, transform=types.SimpleNamespace(CanonicalizeOps=ident))
 
@@ -379,6 +425,14 @@ def install_shim():
     contrib.graph_executor = ge
     tvm.contrib = contrib
     tvm.testing = types.SimpleNamespace(main=lambda: None)
+    tvm.__path__ = []  # "import tvm.topi.testing" needs tvm to look like a package
+    topi = types.ModuleType("tvm.topi")
+    topi_testing = types.ModuleType("tvm.topi.testing")
+    topi.testing = topi_testing
+    tvm.topi = topi
+    tvm.ir = types.SimpleNamespace(IRModule=IRModule)
+    sys.modules["tvm.topi"] = topi
+    sys.modules["tvm.topi.testing"] = topi_testing
     for name, mod in {"tvm": tvm, "tvm.relay": relay, "tvm.te": tvm.te, "tvm.relay.testing": testing,
                       "tvm.relay.testing.temp_op_attr": toa, "tvm.contrib": contrib,
                       "tvm.contrib.graph_executor": ge, "tvm.relay.transform": types.ModuleType("tvm.relay.transform")}.items():

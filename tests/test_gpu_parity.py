@@ -711,6 +711,83 @@ def test_c1_c2_batch_256_trace_equals_oracle(name):
     _full_size_trace_check(name, 256)
 
 
+# ---- qnn.mul / qnn.concatenate / qnn.quantize / qnn.dequantize beyond the reference's literals
+@pytest.mark.parametrize("dt", ["uint8", "int8"])
+@pytest.mark.parametrize("shape", [(2, 16, 14, 14), (3, 5, 7), (4096,)])
+def test_qnn_mul_vs_oracle(shape, dt):
+    rng = np.random.default_rng(len(shape))
+    lo, hi = (0, 256) if dt == "uint8" else (-128, 128)
+    a, b = rng.integers(lo, hi, shape).astype(dt), rng.integers(lo, hi, shape).astype(dt)
+    va, vb = R.var("a", shape, dt), R.var("b", shape, dt)
+    for (sa, za, sb, zb, so, zo) in [(0.0156863, 127 + lo, 0.0117647, 85 + lo, 0.0235294, 128 + lo), (0.5, lo, 0.25, lo, 0.125, lo),
+                                     (0.004, 3 + lo, 0.004, 250 + lo, 0.00001, 7 + lo)]:  # the last one saturates
+        func = R.Function([va, vb], R.qnn_mul(va, vb, np.float32(sa), za, np.float32(sb), zb, np.float32(so), zo))
+        ref, _ = interp.run_expr(func, {"a": a, "b": b})
+        out, mod, _ = run_gpu(func, {"a": a, "b": b})
+        assert "qnn.mul" in mod.plan_summary()
+        np.testing.assert_equal(out, ref)
+
+
+@pytest.mark.parametrize("axis", [0, 1, -1])
+def test_qnn_concatenate_vs_oracle(axis):
+    rng = np.random.default_rng(5 + axis)
+    shapes = [(2, 16, 6, 4), (2, 16, 6, 4), (2, 16, 6, 4)]
+    xs = [rng.integers(0, 256, sh).astype("uint8") for sh in shapes]
+    vs = [R.var("x%d" % i, sh, "uint8") for i, sh in enumerate(shapes)]
+    # one input shares the output qparams (plain copy), two are requantized
+    e = R.qnn_concatenate(vs, [np.float32(0.5), np.float32(0.25), np.float32(0.7)], [3, 9, 128], np.float32(0.25), 9, axis)
+    func = R.Function(vs, e)
+    ins = {"x%d" % i: x for i, x in enumerate(xs)}
+    ref, _ = interp.run_expr(func, ins)
+    out, mod, _ = run_gpu(func, ins)
+    assert "copy into the output slice" in mod.plan_summary() and "requantize into the output slice" in mod.plan_summary()
+    np.testing.assert_equal(out, ref)
+
+
+@pytest.mark.parametrize("out_dtype", ["uint8", "int8", "int32"])
+def test_quantize_dequantize_vs_oracle(out_dtype):
+    """Float edges of a graph: ties (x / scale exactly .5: llvm.round goes away from zero), saturation, per-channel."""
+    rng = np.random.default_rng(11)
+    x = (rng.standard_normal((2, 6, 5, 8)) * 40).astype("float32")
+    x.reshape(-1)[:8] = [0.25, -0.25, 0.75, -0.75, 1.25, -1.25, 1e9, -1e9]  # ties at scale 0.5, and saturation
+    d = R.var("d", x.shape, "float32")
+    zp = 0 if out_dtype != "uint8" else 120
+    for scale, z, axis in [(np.float32(0.5), zp, -1),
+                           (np.array([0.5, 0.25, 0.125, 1.0, 2.0, 0.3], "float32"), np.array([zp] * 6, "int32") + np.arange(6, dtype="int32"), 1)]:
+        q = R.qnn_quantize(d, scale, z, axis=axis, out_dtype=out_dtype)
+        func = R.Function([d], q)
+        ref, _ = interp.run_expr(func, {"d": x})
+        out, _, _ = run_gpu(func, {"d": x})
+        np.testing.assert_equal(out, ref)
+        qv = R.var("q", x.shape, out_dtype)
+        f2 = R.Function([qv], R.qnn_dequantize(qv, scale, z, axis=axis))
+        ref2, _ = interp.run_expr(f2, {"q": ref})
+        out2, _, _ = run_gpu(f2, {"q": ref})
+        assert out2.dtype == np.float32
+        np.testing.assert_equal(out2, ref2)  # float32 bit patterns: the reference's single multiply, no fused ops
+
+
+def test_float_edges_around_the_integer_chain():
+    """quantize -> qnn.conv2d composite -> dequantize: a graph with float edges is ingested whole and its trace holds the
+    float32 records too."""
+    rng = np.random.default_rng(2)
+    x = rng.standard_normal((2, 16, 12, 12)).astype("float32")
+    d = R.var("d", x.shape, "float32")
+    q = R.qnn_quantize(d, np.float32(0.05), 128, out_dtype="uint8")
+    w = rng.integers(-127, 128, (32, 16, 3, 3)).astype("int8")
+    e = R.qnn_conv2d(q, R.const(w), 128, 0, np.float32(0.05), np.float32(0.01), (3, 3), 32, padding=(1, 1))
+    e = R.bias_add(e, R.const(rng.integers(-1000, 1000, 32).astype("int32")))
+    e = R.qnn_requantize(e, np.float32(0.0005), 0, np.float32(0.1), 0, axis=1, out_dtype="int32")
+    e = R.cast(R.clip(e, 0.0, 255.0), "uint8")
+    e = R.qnn_dequantize(e, np.float32(0.1), 0)
+    func = R.Function([d], e)
+    ref, _ = interp.run_expr(func, {"d": x})
+    out, mod, (js, consts, ins) = run_gpu(func, {"d": x}, conv_impl="tc", trace=True)
+    np.testing.assert_equal(out, ref)
+    _, recs = interp.run_json(js, consts, ins, want_trace=True)
+    assert mod.trace_blob() == interp.save_ndarray_list(recs)
+
+
 def test_int8_peak_probe_runs():
     tops = RT.probe_int8_peak(2000)
     assert tops > 100.0, tops

@@ -239,6 +239,92 @@ __global__ void __launch_bounds__(256) dwconv3x3_nhwc_kernel(const uint8_t* __re
   }
 }
 
+// 3 x 3 depthwise, 16 channels per thread: 128-bit loads and stores (north_star: "coalesced 128-bit vectorised loads").
+// One thread owns 16 consecutive channels of NV vertically adjacent outputs of one column.  It walks the NV*S + 2
+// input rows once: per row three 128-bit loads (left / centre / right pixel; neighbouring threads of the block read the
+// same lines, so two of the three hit L1), the same PRMT byte transposition + dp4a as the 4-channel kernel above per
+// 32-bit word, accumulated straight into the outputs the row belongs to (no row buffer: 16 * NV accumulators).  The
+// per-channel epilogue constants are loaded once and used for all NV outputs.  Taps outside the image read the zero
+// point (see dwconv_nhwc_kernel for the identity that makes this exact).
+template <bool AU, bool WU, int S, int NV>
+__global__ void __launch_bounds__(128) dwconv3x3_v16_kernel(const uint8_t* __restrict__ x, const uint32_t* __restrict__ wrow,
+                                                            void* __restrict__ y, ConvGeom g, FastEpi f) {
+  constexpr int ROWS = (NV - 1) * S + 3;
+  const int cg = g.C >> 4;
+  const int t = blockIdx.x * 128 + threadIdx.x;
+  if (t >= g.OW * cg) return;
+  const int ox = t / cg, c0 = (t - ox * cg) * 16;
+  const int oy0 = blockIdx.y * NV, n = blockIdx.z;
+  const uint32_t zp4 = (uint32_t)(g.zp_a & 0xFF) * 0x01010101u;
+  const uint8_t* img = x + (long long)n * g.H * g.W * g.C + c0;
+  int xoff[3];
+  bool xin[3];
+#pragma unroll
+  for (int q = 0; q < 3; ++q) {
+    const int ix = ox * S - g.pl + q;
+    xin[q] = ix >= 0 && ix < g.W;
+    xoff[q] = ix * g.C;
+  }
+  // row-packed weights of this thread's 16 channels: wv[r][word] = 4 channels x {w(r,0), w(r,1), w(r,2), 0}
+  uint4 wv[3][4];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) wv[r][k] = __ldg((const uint4*)(wrow + (long long)r * g.C + c0 + 4 * k));
+  int32_t acc[NV][16];
+#pragma unroll
+  for (int o = 0; o < NV; ++o)
+#pragma unroll
+    for (int c = 0; c < 16; ++c) acc[o][c] = 0;
+#pragma unroll
+  for (int j = 0; j < ROWS; ++j) {
+    const int iy = oy0 * S - g.pt + j;
+    const bool yin = iy >= 0 && iy < g.H;
+    const uint8_t* row = img + (long long)iy * g.W * g.C;
+    uint4 p[3];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) p[q] = (yin && xin[q]) ? __ldg((const uint4*)(row + xoff[q])) : make_uint4(zp4, zp4, zp4, zp4);
+    const uint32_t p0[4] = {p[0].x, p[0].y, p[0].z, p[0].w}, p1[4] = {p[1].x, p[1].y, p[1].z, p[1].w}, p2[4] = {p[2].x, p[2].y, p[2].z, p[2].w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {  // 4 channels: three pixel words -> one word per channel holding its three taps
+      const uint32_t a = __byte_perm(p0[k], p1[k], 0x5140), b = __byte_perm(p0[k], p1[k], 0x7362);
+      const uint32_t c2 = __byte_perm(p2[k], p2[k], 0x5140), d = __byte_perm(p2[k], p2[k], 0x7362);
+      const uint32_t tr[4] = {__byte_perm(a, c2, 0x5410), __byte_perm(a, c2, 0x7632), __byte_perm(b, d, 0x5410), __byte_perm(b, d, 0x7632)};
+#pragma unroll
+      for (int o = 0; o < NV; ++o) {
+        const int r = j - o * S;  // filter row this input row is for output o (compile time)
+        if (r < 0 || r > 2) continue;
+        const uint32_t ww[4] = {wv[r][k].x, wv[r][k].y, wv[r][k].z, wv[r][k].w};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[o][4 * k + c] = dp4a_mixed<AU, WU>(tr[c], ww[c], acc[o][4 * k + c]);
+      }
+    }
+  }
+  // folded requantize + clamp (FastEpi, epilogue.cuh); the zero-point correction is already inside the table
+  uint32_t out[NV][4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+#pragma unroll
+    for (int o = 0; o < NV; ++o) out[o][k] = 0;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int4 tb = __ldg(f.tabA + c0 + 4 * k + c);
+      const long long cc = ((long long)tb.w << 32) | (unsigned long long)(uint32_t)tb.z;
+#pragma unroll
+      for (int o = 0; o < NV; ++o) {
+        const int32_t v = (int32_t)(((long long)acc[o][4 * k + c] * (long long)tb.x + cc) >> 32) >> tb.y;
+        out[o][k] |= (uint32_t)(min(max(v, f.lo), f.hi) & 0xFF) << (8 * c);
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 0; o < NV; ++o) {
+    const int oy = oy0 + o;
+    if (oy >= g.OH) break;
+    *(uint4*)((uint8_t*)y + (((long long)n * g.OH + oy) * g.OW + ox) * g.C + c0) = make_uint4(out[o][0], out[o][1], out[o][2], out[o][3]);
+  }
+}
+
 bool dwconv_nhwc_supported(const ConvGeom& g) {
   return g.groups == g.C && g.O == g.C && (g.C % 16) == 0 && g.N <= 65535 && g.OH <= 65535 && g.zp_w == nullptr &&
          g.zp_w0 == 0 && g.KH * g.KW <= 49;
@@ -247,6 +333,25 @@ bool dwconv_nhwc_supported(const ConvGeom& g) {
 void launch_dwconv_nhwc(const void* x, const void* w_tap, const void* w_row3, const int32_t* corr, void* y,
                         const ConvGeom& g, const EpiParams& e, const FastEpi& f, cudaStream_t s) {
   if ((long long)g.N * g.OH * g.OW == 0) return;
+  if (w_row3 && g.KH == 3 && g.KW == 3 && g.dh == 1 && g.dw == 1 && g.sh == g.sw && (g.sh == 1 || g.sh == 2) &&
+      f.enabled && !f.has_sum && (e.out_dtype == kU8 || e.out_dtype == kI8) && !getenv("TKB_DW_OLD") &&
+      ((((uintptr_t)x) | ((uintptr_t)y) | ((uintptr_t)w_row3)) & 15) == 0) {
+    const uint8_t* xp = (const uint8_t*)x;
+    const uint32_t* wp = (const uint32_t*)w_row3;
+    const bool au = g.a_dtype == kU8, wu = g.w_dtype == kU8;
+    constexpr int NV1 = 4, NV2 = 2;  // outputs per thread: stride 1 walks 6 rows for 4 outputs, stride 2 walks 5 for 2
+    const int nv = g.sh == 1 ? NV1 : NV2;
+    dim3 grid((unsigned)((g.OW * (g.C / 16) + 127) / 128), (unsigned)((g.OH + nv - 1) / nv), (unsigned)g.N);
+#define TKB_DW16(AU_, WU_)                                                                                 \
+  if (au == AU_ && wu == WU_) {                                                                            \
+    if (g.sh == 1) dwconv3x3_v16_kernel<AU_, WU_, 1, NV1><<<grid, 128, 0, s>>>(xp, wp, y, g, f);            \
+    else dwconv3x3_v16_kernel<AU_, WU_, 2, NV2><<<grid, 128, 0, s>>>(xp, wp, y, g, f);                      \
+  }
+    TKB_DW16(true, true) TKB_DW16(true, false) TKB_DW16(false, true) TKB_DW16(false, false)
+#undef TKB_DW16
+    ++g_launches;
+    return;
+  }
   if (w_row3 && g.KH == 3 && g.KW == 3 && g.dh == 1 && g.dw == 1 && g.sh == g.sw && (g.sh == 1 || g.sh == 2) &&
       g.OH <= 131070) {
     dim3 grid((unsigned)((g.OW * (g.C / 4) + 255) / 256), (unsigned)((g.OH + 1) / 2), (unsigned)g.N);

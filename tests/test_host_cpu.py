@@ -197,3 +197,33 @@ def test_trace_replay_models(name, kw):
         x = np.ascontiguousarray(x[:, :, :kw["image"], :kw["image"]])
     js, consts, recs = _oracle_trace(func, {"data": x})
     assert replay.verify_trace(js, interp.save_ndarray_list(recs), consts) == []
+
+
+def test_serialize_matches_json_fixtures():
+    """The JSON contract of both epilogue modes is pinned byte for byte: key order of the graph
+    (json_node.h / graph_executor.cc Load), attribute nesting, constant names, ArgPacker tag order."""
+    f, _ = _small_graph()
+    gold = os.path.join(ROOT, "tests", "golden")
+    for mode, name in (("int", "json_fixture_int.json"), ("dnnl_float", "json_fixture_dnnl_float.json")):
+        _, js, names, _ = T.serialize(T.partition_for_tachikoma(f, mode=mode))
+        want = open(os.path.join(gold, name)).read()
+        assert js == want, f"serialize() drifted from tests/golden/{name}"
+        g = json.loads(js)
+        assert list(g) == ["nodes", "arg_nodes", "heads", "node_row_ptr"]
+        kern = [n for n in g["nodes"] if n["op"] == "kernel"][0]
+        a = kern["attrs"]
+        assert all(isinstance(v, list) and isinstance(v[0], list) and all(isinstance(s, str) for s in v[0])
+                   for k, v in a.items() if k not in ("shape", "dtype", "num_inputs", "num_outputs")), "attributes are [[str, ...]]"
+        assert a["num_outputs"] == "1" and a["num_inputs"] == str(len(kern["inputs"]))
+        consts = [n["name"] for n in g["nodes"] if n["op"] == "const"]
+        assert consts == names
+        if mode == "dnnl_float":
+            order = ["bias_idx", "sum_idx", "o_scl_idx", "act_scl_idx", "sum_scl_idx", "dst_zp_idx"]
+            assert [int(a[t][0][0]) for t in order] == list(range(2, 8))
+            assert a["activation"] == [["clip", "8", "9", "10"]]
+        else:
+            order = ["bias_idx", "sum_idx", "src_zp_idx", "wgh_zp_idx", "src_scl_idx", "wgh_scl_idx", "rq_in_scl_idx",
+                     "rq_in_zp_idx", "rq_out_scl_idx", "rq_out_zp_idx", "sum_lhs_scl_idx", "sum_lhs_zp_idx",
+                     "sum_rhs_scl_idx", "sum_rhs_zp_idx", "sum_out_scl_idx", "sum_out_zp_idx"]
+            assert [int(a[t][0][0]) for t in order] == list(range(2, 18))
+            assert a["clip_a_max"] == [["%.17g" % 255.0]] and a["cast_dtype"] == [["uint8"]]

@@ -146,6 +146,35 @@ int tkb_spin(double microseconds, void* cuda_stream);
 /* Debug counters of the chained tcgen05 launches since the last reset: out8[0] = work items that had to wait for a
  * dependency, out8[1] = cycles waited (summed over CTAs); tools/chain_probe.py prints them. */
 int tkb_debug_chain_stats(uint64_t* out8, int reset);
+/* --- allocation-free entry point --------------------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * One qnn.conv2d (integer semantics of src/relay/qnn/op/convolution.cc, groups == 1):
+ *   out[n,o,p,q] = sum_{c,r,s} (data[n,c,p*sh-pt+r*dh,q*sw-pl+s*dw] - input_zero_point) * (weight[o,c,r,s] - kernel_zero_point)
+ * (int32, wrapping; taps outside the image contribute 0), computed as the runtime's explicit-im2col variant: the
+ * [N*OH*OW][Kp] column matrix (Kp = C*KH*KW rounded up to 16) is staged in a file-scope static __device__ array of
+ * TKB_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit, then multiplied with the weights.
+ * `data` (NCHW, int8 or uint8), `weight` (OIHW, int8 or uint8) and `out` (NCHW int32) are DEVICE pointers of the
+ * current device; dtypes are DLPack codes (0 = int, 1 = uint; 8 bits).  The call allocates nothing (no cudaMalloc /
+ * cudaFree / allocating library routine) and only enqueues work on `cuda_stream`.
+ * Errors (-1, tkb_last_error): N*OH*OW*Kp > TKB_NOALLOC_SCRATCH_BYTES, Kp > TKB_NOALLOC_MAX_K, kernel sides > 255,
+ * non-positive sizes, bad dtype codes.
+ * ALL calls on a device share the one scratch array, which keeps the previous call's contents (each call overwrites
+ * the part it uses before reading it; nothing relies on zeros): calls that overlap on the GPU (two streams or two
+ * host threads of one process) race and must be serialized by the caller.  Each process has its own copy. */
+#define TKB_NOALLOC_SCRATCH_BYTES (16 << 20)
+#define TKB_NOALLOC_MAX_K 12288
+typedef struct {
+  int n, c, h, w;                                 /* data [n][c][h][w] */
+  int o, kh, kw;                                  /* weight [o][c][kh][kw] */
+  int stride_h, stride_w, dilation_h, dilation_w;
+  int pad_top, pad_left, pad_bottom, pad_right;
+  int data_dtype_code, weight_dtype_code;         /* 0 = int8, 1 = uint8 */
+  int32_t input_zero_point, kernel_zero_point;
+} tkb_conv2d_desc;
+int tkb_qnn_conv2d_noalloc(const tkb_conv2d_desc* desc, const void* data, const void* weight, int32_t* out,
+                           void* cuda_stream);
+
 /* Library build info: "sm_100a;<n kernels>;..." */
 const char* tkb_version(void);
 

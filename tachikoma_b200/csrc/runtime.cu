@@ -34,6 +34,7 @@
 namespace tkb {
 
 static thread_local std::string g_last_error;
+void set_last_error(const std::string& msg) { g_last_error = msg; }  // for entry points in other files (noalloc.cu)
 
 struct Error : std::runtime_error {
   using std::runtime_error::runtime_error;

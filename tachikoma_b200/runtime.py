@@ -323,6 +323,29 @@ def probe_int8_peak(iters=2000):
     return t.value
 
 
+class Conv2dDesc(ctypes.Structure):
+    """tkb_conv2d_desc (include/tkb200.h)."""
+    _fields_ = [(k, ctypes.c_int) for k in
+                ("n", "c", "h", "w", "o", "kh", "kw", "stride_h", "stride_w", "dilation_h", "dilation_w", "pad_top",
+                 "pad_left", "pad_bottom", "pad_right", "data_dtype_code", "weight_dtype_code")] + \
+               [("input_zero_point", ctypes.c_int32), ("kernel_zero_point", ctypes.c_int32)]
+
+
+#: static scratch of tkb_qnn_conv2d_noalloc (TKB_NOALLOC_SCRATCH_BYTES / TKB_NOALLOC_MAX_K in include/tkb200.h)
+NOALLOC_SCRATCH_BYTES = 16 << 20
+NOALLOC_MAX_K = 12288
+
+
+def qnn_conv2d_noalloc(desc, data_ptr, weight_ptr, out_ptr, stream=None):
+    """tkb_qnn_conv2d_noalloc: one qnn.conv2d on DEVICE pointers, no allocation inside the call (no counterpart in the
+    reference; for callers that cannot cudaMalloc).  All calls share one static scratch array: serialize them."""
+    L = load_library()
+    L.tkb_qnn_conv2d_noalloc.argtypes = [ctypes.POINTER(Conv2dDesc), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                         ctypes.c_void_p]
+    _check(L.tkb_qnn_conv2d_noalloc(ctypes.byref(desc), ctypes.c_void_p(data_ptr), ctypes.c_void_p(weight_ptr),
+                                    ctypes.c_void_p(out_ptr), ctypes.c_void_p(stream) if stream else None))
+
+
 def create_executor(func, params=None, mode="int", conv_impl="auto"):
     """Partition + codegen + create + init in one call; returns (module, run) where
     ``run(**inputs) -> numpy array`` uses host buffers (the reference's graph-executor usage)."""

@@ -8,7 +8,7 @@ pooling is done on int32 (apply_with_upcast, qnn_torch.py:587-590).  Explicit ze
 expressed through the convolution's padding attribute, which is what the reference's SimplifyExpr
 (FoldExplicitPadding) leaves after partition_for_tachikoma (tests/python/contrib/test_tachikoma.py:88).
 
-Output scales are calibrated once on one seeded sample with a float simulation (torch CPU conv used
+Output scales are calibrated once on one seeded sample with a float simulation (numpy float32 convolution used
 as a calculator only) and rounded to 4 significant digits, so that activations keep spanning the
 uint8 range through the whole depth instead of collapsing to the zero point.
 """
@@ -27,15 +27,50 @@ def _round_sig(x, sig=4):
     return round(x, sig - int(floor(log10(abs(x)))) - 1)
 
 
+def _std(a):
+    """Sample standard deviation (n - 1) in float64 of a float32 array."""
+    return float(np.std(a.astype(np.float64), ddof=1))
+
+
+def _windows(x, k, stride, pad, fill):
+    """[N, C, OH, OW, k, k] strided view of the (padded) NCHW array."""
+    if pad:
+        x = np.pad(x, ((0, 0), (0, 0), (pad, pad), (pad, pad)), constant_values=fill)
+    v = np.lib.stride_tricks.sliding_window_view(x, (k, k), axis=(2, 3))
+    return v[:, :, ::stride, ::stride]
+
+
+def _conv2d_f32(x, w, stride, pad, groups):
+    """float32 NCHW / OIHW convolution for calibration (numpy only: the package uses torch for buffers, never for math)."""
+    n, c = x.shape[:2]
+    o, cg, kh, kw = w.shape
+    v = _windows(x, kh, stride, pad, 0.0)                       # [N, C, OH, OW, kh, kw]
+    oh, ow = v.shape[2:4]
+    if groups == c and cg == 1:                                  # depthwise (multiplier o // c)
+        m = o // c
+        out = np.einsum("nchwrs,cmrs->ncmhw", v, w.reshape(c, m, kh, kw), optimize=True)
+        return out.reshape(n, o, oh, ow).astype(np.float32)
+    og = o // groups
+    out = np.empty((n, o, oh, ow), np.float32)
+    for g in range(groups):
+        cols = v[:, g * cg:(g + 1) * cg].transpose(0, 2, 3, 1, 4, 5).reshape(n * oh * ow, cg * kh * kw)
+        res = cols @ w[g * og:(g + 1) * og].reshape(og, -1).T     # [N*OH*OW, og]
+        out[:, g * og:(g + 1) * og] = res.reshape(n, oh, ow, og).transpose(0, 3, 1, 2)
+    return out
+
+
+def _pool2d_f32(x, k, stride, pad, kind):
+    v = _windows(x, k, stride, pad, -np.inf if kind == "max" else 0.0)
+    return (v.max(axis=(4, 5)) if kind == "max" else v.mean(axis=(4, 5), dtype=np.float32)).astype(np.float32)
+
+
 class _Builder:
     """Tracks (expr, scale, zero_point) and a float shadow activation used for calibration."""
 
     def __init__(self, seed, calib_input, in_scale, in_zp):
         self.rng = np.random.default_rng(seed)
         self.n_layers = 0
-        import torch
-        self.torch = torch
-        self.shadow = torch.from_numpy(calib_input.astype(np.float32))  # quantized values as floats
+        self.shadow = calib_input.astype(np.float32)  # quantized values as floats
 
     def weights(self, shape, k):
         w = self.rng.integers(-127, 128, size=shape).astype(np.int8)
@@ -45,25 +80,22 @@ class _Builder:
 
     def _calibrate(self, acc, s_x, s_w, relu, ch_axis):
         """acc: float tensor of int32 accumulators (+bias).  Returns (s_out, zp_out, next shadow)."""
-        torch = self.torch
-        shp = [1] * acc.dim()
+        shp = [1] * acc.ndim
         shp[ch_axis] = -1
-        real = acc * torch.from_numpy((s_x * s_w).astype(np.float32)).reshape(shp)
-        std = float(real.std()) + 1e-12
+        real = acc * (s_x * s_w).astype(np.float32).reshape(shp)
+        std = _std(real) + 1e-12
         zp_out = 0 if relu else 128
         s_out = _round_sig(std / (50.0 if relu else 40.0))
-        q = torch.floor(real / s_out + 0.5) + zp_out
-        q = torch.clamp(q, float(zp_out if relu else 0), 255.0)
+        q = np.floor(real / np.float32(s_out) + np.float32(0.5)) + np.float32(zp_out)
+        q = np.clip(q, float(zp_out if relu else 0), 255.0).astype(np.float32)
         return np.float32(s_out), zp_out, q
 
     def conv(self, x, s_x, zp_x, oc, ksize, stride=1, pad=0, groups=1, relu=True, residual=None):
         """x: expr NCHW uint8.  residual: (expr, scale, zp, shadow) joined with qnn.add + relu."""
-        torch = self.torch
         ic = x.shape[1]
         w, s_w, b = self.weights((oc, ic // groups, ksize, ksize), ksize * ksize * ic // groups)
-        acc = torch.nn.functional.conv2d(
-            torch.nn.functional.pad(self.shadow - zp_x, (pad, pad, pad, pad)), torch.from_numpy(w.astype(np.float32)),
-            stride=stride, groups=groups) + torch.from_numpy(b.astype(np.float32)).reshape(1, -1, 1, 1)
+        acc = _conv2d_f32(self.shadow - np.float32(zp_x), w.astype(np.float32), stride, pad, groups) \
+            + b.astype(np.float32).reshape(1, -1, 1, 1)
         s_out, zp_out, q = self._calibrate(acc, s_x, s_w, relu and residual is None, 1)
         e = R.qnn_conv2d(x, R.const(w), zp_x, 0, np.float32(s_x), R.const(s_w), (ksize, ksize), oc,
                          strides=(stride, stride), padding=(pad, pad), groups=groups)
@@ -74,22 +106,21 @@ class _Builder:
         self.shadow = q
         if residual is not None:
             r_e, r_s, r_zp, r_shadow = residual
-            real = (q - zp_out) * float(s_out) + (r_shadow - r_zp) * float(r_s)
-            so = np.float32(_round_sig(float(real.std()) / 50.0))
+            real = (q - np.float32(zp_out)) * np.float32(s_out) + (r_shadow - np.float32(r_zp)) * np.float32(r_s)
+            so = np.float32(_round_sig(_std(real) / 50.0))
             zo = 0
             e = R.qnn_add(e, r_e, s_out, zp_out, np.float32(r_s), r_zp, so, zo)
             e = R.clip(e, float(zo), 255.0)
-            self.shadow = torch.clamp(torch.floor(real / float(so) + 0.5) + zo, float(zo), 255.0)
+            self.shadow = np.clip(np.floor(real / so + np.float32(0.5)) + zo, float(zo), 255.0).astype(np.float32)
             s_out, zp_out = so, zo
         self.n_layers += 1
         return e, s_out, zp_out
 
     def dense(self, x, s_x, zp_x, units, relu=True):
-        torch = self.torch
         k = x.shape[-1]
         w, s_w, b = self.weights((units, k), k)
-        acc = (self.shadow - zp_x) @ torch.from_numpy(w.astype(np.float32)).T + torch.from_numpy(b.astype(np.float32))
-        s_out, zp_out, q = self._calibrate(acc, s_x, s_w, relu, acc.dim() - 1)
+        acc = (self.shadow - np.float32(zp_x)) @ w.astype(np.float32).T + b.astype(np.float32)
+        s_out, zp_out, q = self._calibrate(acc, s_x, s_w, relu, acc.ndim - 1)
         e = R.qnn_dense(x, R.const(w), zp_x, 0, np.float32(s_x), R.const(s_w), units)
         e = R.bias_add(e, R.const(b), axis=1 if len(x.shape) == 2 else -1)
         e = R.qnn_requantize(e, R.const((np.float32(s_x) * s_w).astype(np.float32)), 0, s_out, zp_out, axis=-1,
@@ -100,7 +131,7 @@ class _Builder:
         return e, s_out, zp_out
 
     def max_pool(self, x, k, stride, pad):
-        self.shadow = self.torch.nn.functional.max_pool2d(self.shadow, k, stride, pad)
+        self.shadow = _pool2d_f32(self.shadow, k, stride, pad, "max")
         return R.max_pool2d(x, (k, k), (stride, stride), (pad, pad))
 
     def avg_pool_upcast(self, x, k=None, stride=None):
@@ -108,10 +139,10 @@ class _Builder:
         e = R.cast(x, "int32")
         if k is None:
             e = R.global_avg_pool2d(e)
-            self.shadow = self.torch.trunc(self.shadow.mean(dim=(2, 3), keepdim=True))
+            self.shadow = np.trunc(self.shadow.mean(axis=(2, 3), keepdims=True, dtype=np.float32))
         else:
             e = R.avg_pool2d(e, (k, k), (stride, stride))
-            self.shadow = self.torch.trunc(self.torch.nn.functional.avg_pool2d(self.shadow, k, stride))
+            self.shadow = np.trunc(_pool2d_f32(self.shadow, k, stride, 0, "avg"))
         return R.cast(e, "uint8")
 
 
@@ -196,10 +227,10 @@ def mobilenetv2(batch=128, seed=0, image=224, num_classes=1000):
             if st == 1 and ic == c:
                 # linear bottleneck joined with quantized::add (no relu): qnn.add -> clip(0, 255)
                 y, ys, yzp = b.conv(y, ys, yzp, c, 1, relu=False)
-                real = (b.shadow - yzp) * float(ys) + (ident_shadow - ident_zp) * float(ident_s)
-                so, zo = np.float32(_round_sig(float(real.std()) / 40.0)), 128
+                real = (b.shadow - np.float32(yzp)) * np.float32(ys) + (ident_shadow - np.float32(ident_zp)) * np.float32(ident_s)
+                so, zo = np.float32(_round_sig(_std(real) / 40.0)), 128
                 y = R.qnn_add(y, ident, ys, yzp, np.float32(ident_s), ident_zp, so, zo)
-                b.shadow = b.torch.clamp(b.torch.floor(real / float(so) + 0.5) + zo, 0.0, 255.0)
+                b.shadow = np.clip(np.floor(real / so + np.float32(0.5)) + zo, 0.0, 255.0).astype(np.float32)
                 ys, yzp = so, zo
             else:
                 y, ys, yzp = b.conv(y, ys, yzp, c, 1, relu=False)
@@ -219,29 +250,28 @@ def bert_encoder(batch=8, seed=0, seq=128, hidden=768, heads=12, ffn=3072, layer
     qnn.dense -> qnn.add residual -> FFN qnn.dense x2 -> qnn.add residual.  Softmax and LayerNorm are float
     operators outside the integer path and are not modelled: P is the
     requantized, clipped score matrix, which keeps every integer operator at its BERT-base shape."""
-    import torch
     rng = np.random.default_rng(seed)
     d = hidden // heads
     x = R.var("data", (batch * seq, hidden), "uint8")
-    shadow = torch.from_numpy(_input((2 * seq, hidden), 7).astype(np.float32))  # calibration sample: 2 sequences
+    shadow = _input((2 * seq, hidden), 7).astype(np.float32)  # calibration sample: 2 sequences
     cb = 2
 
     def calib(real, kind):
-        std = float(real.std()) + 1e-12
+        std = _std(real) + 1e-12
         if kind == "i8":
             s_out = np.float32(_round_sig(std / 40.0))
-            return s_out, 0, torch.clamp(torch.floor(real / float(s_out) + 0.5), -128.0, 127.0)
+            return s_out, 0, np.clip(np.floor(real / s_out + np.float32(0.5)), -128.0, 127.0).astype(np.float32)
         zp = 0 if kind == "relu" else 128
         s_out = np.float32(_round_sig(std / (50.0 if kind == "relu" else 40.0)))
-        return s_out, zp, torch.clamp(torch.floor(real / float(s_out) + 0.5) + zp, 0.0, 255.0)
+        return s_out, zp, np.clip(np.floor(real / s_out + np.float32(0.5)) + zp, 0.0, 255.0).astype(np.float32)
 
     def dense(e, sh, s_x, zp_x, units, kind):
         k = e.shape[-1]
         w = rng.integers(-127, 128, size=(units, k)).astype(np.int8)
         s_w = (rng.uniform(0.5, 1.5, size=units) / (127.0 * np.sqrt(k))).astype(np.float32)
         b = rng.integers(-(1 << 12), 1 << 12, size=units).astype(np.int32)
-        acc = (sh - zp_x) @ torch.from_numpy(w.astype(np.float32)).T + torch.from_numpy(b.astype(np.float32))
-        real = acc * torch.from_numpy((np.float32(s_x) * s_w).astype(np.float32))
+        acc = (sh - np.float32(zp_x)) @ w.astype(np.float32).T + b.astype(np.float32)
+        real = acc * (np.float32(s_x) * s_w).astype(np.float32)
         s_out, zp_out, q = calib(real, kind)
         y = R.qnn_dense(e, R.const(w), zp_x, 0, np.float32(s_x), R.const(s_w), units)
         y = R.bias_add(y, R.const(b), axis=1)
@@ -255,11 +285,11 @@ def bert_encoder(batch=8, seed=0, seq=128, hidden=768, heads=12, ffn=3072, layer
 
     def split_heads(e, sh, nb):  # [nb*seq, hidden] -> [nb*heads, seq, d]
         e = R.reshape(R.transpose(R.reshape(e, (nb, seq, heads, d)), (0, 2, 1, 3)), (nb * heads, seq, d))
-        sh = sh.reshape(cb, seq, heads, d).permute(0, 2, 1, 3).reshape(cb * heads, seq, d)
+        sh = sh.reshape(cb, seq, heads, d).transpose(0, 2, 1, 3).reshape(cb * heads, seq, d)
         return e, sh
 
     def bmm(a, a_sh, s_a, b_, b_sh, s_b, kind):
-        real = (a_sh @ b_sh.transpose(1, 2)) * float(s_a) * float(s_b)
+        real = (a_sh @ b_sh.transpose(0, 2, 1)) * np.float32(s_a) * np.float32(s_b)
         s_out, zp_out, q = calib(real, kind)
         y = R.qnn_batch_matmul(a, b_, 0, 0, np.float32(s_a), np.float32(s_b))
         y = R.qnn_requantize(y, np.float32(np.float32(s_a) * np.float32(s_b)), 0, s_out, zp_out, axis=-1, out_dtype="int32")
@@ -270,10 +300,10 @@ def bert_encoder(batch=8, seed=0, seq=128, hidden=768, heads=12, ffn=3072, layer
         return y, s_out, zp_out, q
 
     def residual(a, a_sh, s_a, zp_a, b_, b_sh, s_b, zp_b):
-        real = (a_sh - zp_a) * float(s_a) + (b_sh - zp_b) * float(s_b)
-        so, zo = np.float32(_round_sig(float(real.std()) / 40.0)), 128
+        real = (a_sh - np.float32(zp_a)) * np.float32(s_a) + (b_sh - np.float32(zp_b)) * np.float32(s_b)
+        so, zo = np.float32(_round_sig(_std(real) / 40.0)), 128
         y = R.clip(R.qnn_add(a, b_, np.float32(s_a), zp_a, np.float32(s_b), zp_b, so, zo), 0.0, 255.0)
-        return y, so, zo, torch.clamp(torch.floor(real / float(so) + 0.5) + zo, 0.0, 255.0)
+        return y, so, zo, np.clip(np.floor(real / so + np.float32(0.5)) + zo, 0.0, 255.0).astype(np.float32)
 
     e, s, zp = x, IN_SCALE, IN_ZP
     for _ in range(layers):
@@ -284,10 +314,10 @@ def bert_encoder(batch=8, seed=0, seq=128, hidden=768, heads=12, ffn=3072, layer
         k, k_sh = split_heads(k, k_sh, batch)
         v, v_sh = split_heads(v, v_sh, batch)
         p, s_p, _, p_sh = bmm(q, q_sh, s_q, k, k_sh, s_k, "relu")            # [B*h, S, S] uint8, zero point 0
-        vt, vt_sh = R.transpose(v, (0, 2, 1)), v_sh.transpose(1, 2)           # [B*h, d, S]
+        vt, vt_sh = R.transpose(v, (0, 2, 1)), v_sh.transpose(0, 2, 1)        # [B*h, d, S]
         c, s_c, _, c_sh = bmm(p, p_sh, s_p, vt, vt_sh, s_v, "i8")            # [B*h, S, d]
         c = R.reshape(R.transpose(R.reshape(c, (batch, heads, seq, d)), (0, 2, 1, 3)), (batch * seq, hidden))
-        c_sh = c_sh.reshape(cb, heads, seq, d).permute(0, 2, 1, 3).reshape(cb * seq, hidden)
+        c_sh = c_sh.reshape(cb, heads, seq, d).transpose(0, 2, 1, 3).reshape(cb * seq, hidden)
         o, s_o, zp_o, o_sh = dense(c, c_sh, s_c, 0, hidden, "u8")
         e, s, zp, shadow = residual(o, o_sh, s_o, zp_o, e, shadow, s, zp)
         f, s_f, zp_f, f_sh = dense(e, shadow, s, zp, ffn, "relu")

@@ -287,10 +287,55 @@ def legalize_qnn_for_tachikoma(func, mode="dnnl_float"):
     return R.Function(func.params, visit(func.body), func.attrs)
 
 
+#: tachikoma.py:711-723 (IsComputeIntensiveGraph) plus the QNN forms the integer path offloads
+COMPUTE_INTENSIVE_OPS = {
+    "nn.conv1d", "nn.conv2d", "nn.conv2d_transpose", "nn.conv3d", "nn.conv3d_transpose", "nn.dense", "nn.layer_norm",
+    "nn.batch_matmul", "nn.global_avg_pool2d", "qnn.conv2d", "qnn.dense", "qnn.batch_matmul",
+    "tachikoma.qnn.conv2d", "tachikoma.qnn.dense",
+}
+
+
+def is_valid_subgraph(body):
+    """tachikoma.py:739-741: a subgraph is worth offloading only if it holds a compute-intensive operator."""
+    return any(isinstance(e, R.Call) and e.op in COMPUTE_INTENSIVE_OPS for e in R.post_order(body))
+
+
 def prune_tachikoma_subgraphs(func):
-    """Reference: tachikoma.py:744-793 removes offloaded subgraphs that are too small to pay for the
-    boundary crossing.  The CUDA runtime always takes the whole function, so this is the identity."""
+    """tachikoma.py:744-793 reverts offloaded subgraphs without a compute-intensive operator to TVM, and does nothing
+    when the module holds a single subgraph (:775-777).  partition_for_tachikoma here always produces exactly one
+    subgraph (the whole function, or an error), so the faithful behaviour is the reference's early return; the
+    validity check is still evaluated so that a caller can log what the reference would have pruned."""
+    if not is_valid_subgraph(func.body):
+        logger.info("subgraph without a compute-intensive operator kept (single-subgraph module, tachikoma.py:775)")
     return func
+
+
+def _float_rewrite(func, name, pattern_ops, target):
+    """The reference's DFPatternCallback rewrites below work on FLOAT graphs.  On a graph without the pattern's
+    operators a rewrite is the identity (what `rewrite(callback, expr)` returns when nothing matches), which is the
+    case for every integer QNN graph; a graph that does hold them would end in operators the CUDA runtime rejects,
+    so it fails here with the runtime's own message instead of at init."""
+    present = sorted({e.op for e in R.post_order(func.body) if isinstance(e, R.Call)} & set(pattern_ops))
+    if present:
+        raise ValueError(f"Unsupported op: {target} ({name} matches float operators {present}; the tachikoma CUDA "
+                         "runtime executes the integer QNN path only)")
+    return func
+
+
+def rewrite_layer_norm(func):
+    """tachikoma.py:796-857: mean/subtract/power/mean/add/sqrt/divide/multiply/add -> nn.layer_norm."""
+    return _float_rewrite(func, "rewrite_layer_norm", ("mean", "variance", "power", "sqrt", "rsqrt"), "nn.layer_norm")
+
+
+def rewrite_dense_bias_gelu_reshape_last(func):
+    """tachikoma.py:860-951: nn.dense -> reshape -> add [-> erf GELU] reordered so that the reshape comes last."""
+    return _float_rewrite(func, "rewrite_dense_bias_gelu_reshape_last", ("nn.dense", "erf"), "nn.dense")
+
+
+def rewrite_resnetv1(func):
+    """tachikoma.py:954-1119: moves the stride of a ResNet-v1 downsample block's 1x1 convolutions forward (float
+    nn.conv2d / nn.relu graphs)."""
+    return _float_rewrite(func, "rewrite_resnetv1", ("nn.conv2d", "nn.relu"), "nn.conv2d")
 
 
 def partition_for_tachikoma(func, params=None, mode="int", symbol="tvmgen_default_tachikoma_main_0"):

@@ -148,6 +148,16 @@ def test_product_never_imports_oracle():
                 assert "oracle" not in src.replace("test oracle", ""), f"{fn} mentions the oracle"
 
 
+def test_torch_is_buffer_plumbing_only():
+    """PyTorch appears in the package only where device buffers / streams are handled (runtime.py); model building,
+    partitioning, serialization and the trace reader are numpy only."""
+    pkg = os.path.join(ROOT, "tachikoma_b200")
+    for fn in os.listdir(pkg):
+        if fn.endswith(".py") and fn != "runtime.py":
+            src = open(os.path.join(pkg, fn)).read()
+            assert not re.search(r"^\s*(import torch|from torch)", src, re.M), f"{fn} imports torch"
+
+
 # ---- trace reader / verifier (SURVEY section 8 row N1): record-by-record replay on the oracle ---------------
 def _oracle_trace(func, ins):
     part = T.partition_for_tachikoma(func)
@@ -227,3 +237,18 @@ def test_serialize_matches_json_fixtures():
                      "sum_rhs_scl_idx", "sum_rhs_zp_idx", "sum_out_scl_idx", "sum_out_zp_idx"]
             assert [int(a[t][0][0]) for t in order] == list(range(2, 18))
             assert a["clip_a_max"] == [["%.17g" % 255.0]] and a["cast_dtype"] == [["uint8"]]
+
+
+def test_wrapper_surface_of_the_reference_module():
+    """python/tvm/relay/op/contrib/tachikoma.py names: present, identity on integer graphs
+    (a DFPattern rewrite that matches nothing returns its input), loud on the float graphs they were written for."""
+    f, _ = _small_graph()
+    for fn in (T.rewrite_layer_norm, T.rewrite_dense_bias_gelu_reshape_last, T.rewrite_resnetv1, T.prune_tachikoma_subgraphs):
+        assert fn(f) is f
+    assert T.is_valid_subgraph(f.body)
+    x = R.var("x", (1, 4), "uint8")
+    assert not T.is_valid_subgraph(R.clip(x, 0.0, 9.0))
+    fl = R.Function([x], R.Call("nn.relu", [x], {}, x.shape, "float32"))
+    with pytest.raises(ValueError, match="Unsupported op: nn.conv2d"):
+        T.rewrite_resnetv1(fl)
+    assert T.get_optimal_layout_for_conv("NCHW", "OIHW") == "NHWC,OHWI,NHWC"

@@ -15,7 +15,8 @@ Legs (all timed with CUDA events on the launching stream, barrier + synchronize 
   value          input resident in HBM, every operator's tensors captured on the device in their logical layout
                  (trace mode 1: readable afterwards through tkb_trace_blob, verified below)
   e2e            pinned HOST input -> C ABI -> logits + every distinct traced tensor in pinned host memory
-                 (trace mode 2: H2D and D2H inside the timed region)
+                 (trace mode 2: H2D and D2H inside the timed region), two batches in flight on two streams;
+                 config.trace_to_host_e2e_one_batch_in_flight is the strictly serial form (run, wait for the trace, run)
   e2e_serialized as e2e, plus the complete NDArray-list blob (repeated records filled in) every step
   sustained      >= 2 s of back-to-back `value` steps (clocks / power under real load)
 After the timed legs the run PROVES what it timed: the serialized trace of the first and of the last end-to-end step
@@ -357,6 +358,41 @@ def main():
     last_blob = mod.trace_blob() if not args.no_verify else None  # the LAST timed step's trace, still in the pinned buffer
     last_logits = out_host.numpy().copy()
 
+    # (iii-b) the same end-to-end work with TWO batches in flight: the caller alternates two streams (each has its own
+    # workspace and pinned blob, include/tkb200.h), tkb_run returns once the logits are on the host, and the trace of
+    # batch i keeps streaming to the host while batch i+1 is uploaded and computed.  Before a stream is reused the
+    # caller waits for that stream's previous trace (tkb_trace_sync_on): every trace is complete in pinned host memory
+    # before its buffer is overwritten, which is when a consumer would read it.
+    pipe_streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    pipe_out = [torch.empty(out_shape, dtype=out_dt).pin_memory() for _ in range(2)]
+    pipe_warm = max(2, args.warmup)
+
+    def pipe_step(i):
+        k = i % 2
+        sk = pipe_streams[k].cuda_stream
+        if i - 2 >= -pipe_warm:
+            mod.trace_sync(stream=sk)
+        mod.run(xs_host[k], pipe_out[k], stream=sk, trace_mode=2)
+
+    for i in range(-pipe_warm, 0):
+        pipe_step(i)
+    for st in pipe_streams:
+        mod.trace_sync(stream=st.cuda_stream)
+    barrier()
+    p0 = torch.cuda.Event(enable_timing=True)
+    p_end = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    p0.record(pipe_streams[0])
+    pipe_streams[1].wait_event(p0)
+    for i in range(args.steps):
+        pipe_step(i)
+    for k in range(2):
+        p_end[k].record(pipe_streams[k])  # ordered after the run's trace transfer (the run joins its trace stream)
+    barrier()
+    ms_e2e_pipe = max_over_ranks(max(p0.elapsed_time(p_end[0]), p0.elapsed_time(p_end[1])))
+    k_last = (args.steps - 1) % 2
+    pipe_blob = mod.trace_blob(stream=pipe_streams[k_last].cuda_stream) if not args.no_verify else None
+    pipe_logits = pipe_out[k_last].numpy().copy()
+
     # (iv) as (iii) plus the complete serialized blob every step (repeated records filled by the parallel host copy)
     def e2e_blob_step(i):
         mod.run(xs_host[i % 2], out_host, stream=stream, trace_mode=2)
@@ -426,6 +462,8 @@ def main():
                      verify_against_oracle(args.model, args.batch, graph_json, consts, xs_np[0], first["logits"], first["blob"])]
         problems += ["last e2e step: " + p for p in
                      verify_against_oracle(args.model, args.batch, graph_json, consts, xs_np[1], last_logits, last_blob)]
+        problems += ["last pipelined e2e step: " + p for p in
+                     verify_against_oracle(args.model, args.batch, graph_json, consts, xs_np[k_last], pipe_logits, pipe_blob)]
         problems += ["device-resident trace: " + p for p in
                      verify_against_oracle(args.model, args.batch, graph_json, consts, xs_np[0], logits_dev, blob_dev)]
     bad = max_over_ranks(float(len(problems) > 0)) > 0
@@ -446,9 +484,10 @@ def main():
     except Exception:
         pass
     traffic, traffic_src = _ncu_traffic()
-    e2e_value = rate(ms_e2e)
+    e2e_serial = rate(ms_e2e)
+    e2e_value = rate(ms_e2e_pipe)
     d2h_step = int(trace_d2h + np.prod(out_shape) * out_host.element_size())
-    e2e_gbs = world * d2h_step * args.steps / (ms_e2e * 1e-3) / 1e9
+    e2e_gbs = world * d2h_step * args.steps / (ms_e2e_pipe * 1e-3) / 1e9
     per_sorted = sorted(per_value)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -462,6 +501,10 @@ def main():
                           "config.trace_readout_ms and the streamed form is e2e",
             "compute_only": rate(ms_compute),
             "trace_to_host_e2e": e2e_value,
+            "trace_to_host_e2e_one_batch_in_flight": e2e_serial,
+            "e2e_mode": "two batches in flight on two caller streams (double-buffered workspaces and pinned blobs); each "
+                        "trace is complete in pinned host memory before its stream is reused",
+            "e2e_d2h_gbs_one_batch_in_flight": world * d2h_step * args.steps / (ms_e2e * 1e-3) / 1e9,
             "e2e_serialized_blob": rate(ms_e2e_blob),
             "trace_readout_ms": readout_ms,
             "sustained_value": total_images * sus_steps / (ms_sus * 1e-3), "sustained_steps": sus_steps,
@@ -471,7 +514,8 @@ def main():
             "l2": "no explicit flush: each step streams its whole activation arena (> 126 MB L2) through HBM",
             "conv_impl": args.conv_impl, "int8_macs_per_step": macs, "numa": numa,
             "verified": "first and last end-to-end step + the device-resident trace of the `value` leg vs the CPU oracle on "
-                        "the first 4 and last 4 images of the batch: logits and every serialized trace record"
+                        "the first 4 and last 4 images of the batch: logits and every serialized trace record; also the last "
+                        "step of the two-batches-in-flight e2e leg"
                         if not args.no_verify else "skipped (--no-verify)",
         },
         "e2e": {"value": e2e_value, "unit": UNIT,
@@ -481,7 +525,7 @@ def main():
                 "frac_of_pcie": e2e_gbs / d2h_gbs if d2h_gbs else None},
         "gpu_launches": int(launches),
         "roofline": {
-            "bound": "tensor", "kernel": "tcgen05.mma kind::i8 conv/dense kernels (tc_chain_kernel / tc_halo_kernel / tc_gemm_kernel); all %d launches of a step" % (tc_n // runs if runs else 0),
+            "bound": "tensor", "kernel": "tcgen05.mma kind::i8 conv/dense kernels (tc_halo_kernel / tc_gemm_kernel); all %d launches of a step" % (tc_n // runs if runs else 0),
             "achieved": achieved_tops,
             "peak": peak_tops, "unit": "TFLOP/s", "frac": achieved_tops / peak_tops if peak_tops else None, "traffic": traffic,
             "note": "int8 ops (2*MAC) counted as FLOPs; achieved = 2 * MACs of a step / summed CUDA-event time of the tcgen05 launches "

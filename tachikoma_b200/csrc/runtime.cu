@@ -2031,7 +2031,6 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
     }
   }
   if (mode > 0 && rec < rt->trace_recs.size()) trace_node(c, rec, rt->trace_recs.size());
-  trace_join(c);
   bool host_out = false;
   for (int j = 0; j < n_out; ++j) {
     const int eid = (int)g.eid(g.heads[j]);
@@ -2043,7 +2042,20 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
     host_out = host_out || !dev;
   }
   CUDA_OK(cudaGetLastError());
-  if (host_out) CUDA_OK(cudaStreamSynchronize(s));  // host results are valid on return, like the reference
+  // Host results are valid on return, like the reference's.  The trace is NOT waited for here: the side stream keeps
+  // copying after the call has returned (tkb_trace_sync / tkb_trace_blob wait for it), so a caller that alternates two
+  // streams overlaps one batch's trace transfer with the next batch's upload and compute.  The join comes after the
+  // output copies: everything enqueued on `s` later (the next run, which overwrites the arena and the ring) is still
+  // ordered after the trace work.
+  const bool side_busy = c.ws->side && c.ws->side_dirty;
+  if (host_out && side_busy) {
+    CUDA_OK(cudaEventRecord(c.ws->ev, s));
+    trace_join(c);
+    CUDA_OK(cudaEventSynchronize(c.ws->ev));
+  } else {
+    trace_join(c);
+    if (host_out) CUDA_OK(cudaStreamSynchronize(s));
+  }
   c.ws->trace_mode = mode;
   c.ws->payload_on_host = mode >= 2;
   c.ws->in_ptr = c.in_ptr;

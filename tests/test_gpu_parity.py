@@ -618,6 +618,34 @@ def test_two_threads_two_streams_different_trace_modes():
     assert not errors, errors
 
 
+def test_two_batches_in_flight_from_one_thread():
+    """What bench.py's e2e leg does: ONE host thread alternates two streams with host inputs and host outputs.  tkb_run
+    returns once the logits are on the host while the trace keeps streaming; before a stream is reused the caller waits
+    for that stream's trace (tkb_trace_sync_on).  Every batch's logits and every trace equal the oracle's."""
+    import torch
+    func = models.resnet18(batch=2, image=64, num_classes=100)
+    part, mod, js, consts = _module(func)
+    xs = [np.ascontiguousarray(models.synthetic_input("resnet18", 2, seed=21 + t)[:, :, :64, :64]) for t in range(3)]
+    want = []
+    for x in xs:
+        outs, recs = interp.run_json(js, consts, [x], want_trace=True)
+        want.append((outs[0], interp.save_ndarray_list(recs)))
+    streams = [torch.cuda.Stream() for _ in range(2)]
+    outs = [np.zeros(part.body.shape, dtype=part.body.dtype) for _ in range(2)]
+    fed = [None, None]
+    for i in range(9):
+        k, j = i % 2, i % 3
+        sk = streams[k].cuda_stream
+        if fed[k] is not None:  # the trace of the batch this stream ran before: complete, then checked, then overwritten
+            mod.trace_sync(stream=sk)
+            assert mod.trace_blob(stream=sk) == want[fed[k]][1], "trace of batch %d differs (step %d)" % (fed[k], i)
+        mod.run(xs[j], outs[k], stream=sk, trace_mode=2)
+        assert (outs[k] == want[j][0]).all(), "logits differ (step %d)" % i
+        fed[k] = j
+    for k in range(2):
+        assert mod.trace_blob(stream=streams[k].cuda_stream) == want[fed[k]][1]
+
+
 def test_device_resident_trace_deferred_readout():
     """Trace mode 1 (what bench.py's `value` runs): nothing crosses PCIe during the run; tkb_trace_blob afterwards reads
     the ring / arena out and the bytes equal the streamed (mode 2) trace and the oracle's."""

@@ -73,7 +73,10 @@ int tkb_num_outputs(tkb_handle h);
 int tkb_init(tkb_handle h, const tkb_DLTensor* const* consts, int n_consts);
 /* args = inputs (graph input order) followed by caller-allocated outputs; n_args must equal
  * #inputs + #outputs.  cuda_stream is a cudaStream_t (NULL = default stream).  Re-entrant from
- * several host threads provided each uses its own stream. */
+ * several host threads provided each uses its own stream.  With host outputs the call returns when the outputs are
+ * valid; a trace being streamed to the host (mode 2) may still be in flight then: tkb_trace_sync_on / tkb_trace_blob_on
+ * wait for it, and the next run on the same stream is ordered after it on the device.  Each stream has its own
+ * workspace and pinned trace buffer, so one host thread may keep two batches in flight by alternating two streams. */
 int tkb_run(tkb_handle h, const tkb_DLTensor* const* args, int n_args, void* cuda_stream);
 /* TVMBackendPackedCFunc-shaped entry: args[0] = module handle (void*), args[1..] = DLTensor*.
  * type codes: 3 = kTVMOpaqueHandle, 7 = kTVMDLTensorHandle, 13 = kTVMNDArrayHandle. */

@@ -554,6 +554,8 @@ inline int num_sms() {
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (sms <= 0) sms = 148;
+    // experiment knob: persistent grids of fewer CTAs leave SMs to whatever runs beside them (trace transposes)
+    if (const char* e = getenv("TKB_SMS")) { const int v = atoi(e); if (v > 0 && v < sms) sms = v; }
   }
   return sms;
 }

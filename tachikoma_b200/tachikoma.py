@@ -344,6 +344,8 @@ def partition_for_tachikoma(func, params=None, mode="int", symbol="tvmgen_defaul
     ``check_fully_annotated``, :1347-1364) and mark the function for the tachikoma compiler."""
     if params:
         func = R.bind_params(func, params)
+    from .frontend import fold_explicit_padding  # SimplifyExpr / FoldExplicitPadding, test_tachikoma.py:88
+    func = fold_explicit_padding(func)
     func = legalize_qnn_for_tachikoma(func, mode=mode)
     for e in R.post_order(func.body):
         if isinstance(e, R.Call) and not e.op.startswith("tachikoma.") and e.op not in SUPPORTED_OPS:

@@ -153,7 +153,8 @@ def test_torch_is_buffer_plumbing_only():
     partitioning, serialization and the trace reader are numpy only."""
     pkg = os.path.join(ROOT, "tachikoma_b200")
     for fn in os.listdir(pkg):
-        if fn.endswith(".py") and fn != "runtime.py":
+        # frontend.py reads TorchScript models (graph walk, packed-parameter unpacking): torch is its input format
+        if fn.endswith(".py") and fn not in ("runtime.py", "frontend.py"):
             src = open(os.path.join(pkg, fn)).read()
             assert not re.search(r"^\s*(import torch|from torch)", src, re.M), f"{fn} imports torch"
 

@@ -201,6 +201,57 @@ def qnn_concatenate(tensors, scales, zps, so, zpo, axis):
     return np.ascontiguousarray(np.concatenate(outs, axis=axis))
 
 
+def qnn_leaky_relu(x, alpha, s_in, zp_in, s_out, zp_out):
+    """src/relay/qnn/op/leaky_relu.cc:70-139: Q' = RequantizeOrUpcast(int32(x)) to the output qparams
+    (op_common.h:196-210); negative side (x < zp_in): FixedPointMultiply(Q', alpha) + FixedPointMultiply(zp_out, 1 - alpha)
+    (src/relay/qnn/utils.cc FixedPointMultiply -> fixed_point_multiply); ConvertDtype saturates to the input dtype."""
+    x = np.ascontiguousarray(x)
+    if x.size > 4096:  # elementwise: evaluate the distinct values once (the scalar fixed_point_multiply is a Python loop)
+        vals, inv = np.unique(x, return_inverse=True)
+        return qnn_leaky_relu(vals, alpha, s_in, zp_in, s_out, zp_out)[inv].reshape(x.shape)
+    x32 = x.astype(np.int32)
+    if _sc(s_in) != _sc(s_out) or _zp(zp_in) != _zp(zp_out):
+        q = requantize(x32, _sc(s_in), _zp(zp_in), _sc(s_out), _zp(zp_out), -1, "None", "None", "int32")
+    else:
+        q = x32
+    ma, sa_ = fixed_point_multiplier_shift(float(alpha))
+    mz, sz = fixed_point_multiplier_shift(1.0 - float(alpha))
+    prod = fixed_point_multiply(q, ma, sa_)
+    scaled_z = fixed_point_multiply(np.asarray([_zp(zp_out)], dtype=np.int32), mz, sz)[0]
+    neg = _wrap_add_i32(np.asarray(prod, dtype=np.int32), np.full(q.shape, scaled_z, dtype=np.int32))
+    out = np.where(x32 < np.int32(_zp(zp_in)), neg, q)
+    info = np.iinfo(x.dtype)
+    return np.clip(out, info.min, info.max).astype(x.dtype)
+
+
+_UNARY = None
+
+
+def _unary_funcs():
+    """python/tvm/relay/qnn/op/legalizations.py:74-86."""
+    global _UNARY
+    if _UNARY is None:
+        from scipy import special
+
+        def hardswish(x):
+            return x * np.clip(x + 3.0, 0.0, 6.0) / 6.0
+        _UNARY = {"qnn.sqrt": np.sqrt, "qnn.rsqrt": lambda a: 1 / np.sqrt(a), "qnn.exp": np.exp, "qnn.erf": special.erf,
+                  "qnn.sigmoid": lambda a: 1 / (1 + np.exp(-a)), "qnn.hardswish": hardswish, "qnn.tanh": np.tanh,
+                  "qnn.log": np.log, "qnn.abs": np.abs}
+    return _UNARY
+
+
+def qnn_unary(op, x, s_in, zp_in, s_out, zp_out):
+    """legalizations.py:54-71 + canonicalizations.py:31-160: the operator IS quantize(f(dequantize(.))) tabulated over
+    all 256 bit patterns of the input dtype; evaluated here element by element (no table) with the oracle's own
+    dequantize / quantize, f = the numpy function the reference registers, applied to the float32 dequantized values."""
+    x = np.ascontiguousarray(x)
+    with np.errstate(all="ignore"):
+        d = dequantize(x, _sc(s_in), _zp(zp_in))
+        f = np.asarray(_unary_funcs()[op](d), dtype=np.float32)
+    return quantize(f, _sc(s_out), _zp(zp_out), -1, str(x.dtype))
+
+
 def _axis_split(shape, axis):
     nd = len(shape)
     if nd == 0:
@@ -311,6 +362,14 @@ def eval_op(op, attrs, args):
         return quantize(args[0], args[1], args[2], int(attrs.get("axis", -1)), attrs["out_dtype"])
     if op == "qnn.dequantize":
         return dequantize(args[0], args[1], args[2], int(attrs.get("axis", -1)))
+    if op == "qnn.leaky_relu":
+        return qnn_leaky_relu(args[0], float(attrs["alpha"]), *args[1:5])
+    if op in _unary_funcs():
+        return qnn_unary(op, *args[:5])
+    if op == "reinterpret":
+        return np.ascontiguousarray(args[0]).view(attrs["dtype"])
+    if op == "take":  # 1-D table, axis 0, mode "fast" (indices are in range by construction)
+        return np.ascontiguousarray(np.asarray(args[0])[np.asarray(args[1]).astype(np.int64)])
     if op == "nn.bias_add":
         ax = attrs.get("axis", 1)
         shp = [1] * args[0].ndim
@@ -481,6 +540,10 @@ def _eval_json_node(node, ins):
         return eval_op(op, dict(axis=int(g("axis", -1)), out_dtype=node["attrs"]["dtype"][0][0]), ins)
     if op == "qnn.dequantize":
         return eval_op(op, dict(axis=int(g("axis", -1))), ins)
+    if op == "qnn.leaky_relu":
+        return eval_op(op, dict(alpha=float(g("alpha"))), ins)
+    if op == "reinterpret":
+        return eval_op(op, dict(dtype=node["attrs"]["dtype"][0][0]), ins)
     return eval_op(op, {}, ins)  # qnn.dense, qnn.batch_matmul, qnn.add, qnn.mul, add, nn.batch_flatten
 
 

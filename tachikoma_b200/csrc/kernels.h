@@ -48,6 +48,12 @@ void launch_dequantize(const void* x, int x_dtype, float* y, long long outer, in
 // qnn.concatenate: copy (requant == 0) or requantize one input [outer][row_in] into rows of row_out elements at `off`
 void launch_concat_piece(const void* x, void* y, int dtype, long long outer, long long row_in, long long row_out, long long off,
                          const RqParams& rq, int requant, cudaStream_t s);
+// take(table, 8-bit indices): y[i] = table[x[i]] for a table of `entries` <= 256 elements of `elem` = 1 / 2 / 4 bytes
+void launch_lut8(const void* x, const void* table, int entries, int elem, void* y, long long n, cudaStream_t s);
+// qnn.leaky_relu, per tensor (leaky_relu.cc:70-139)
+void launch_qnn_leaky_relu(const void* x, void* y, int dtype, long long n, const RqParams& rq, int identity, int32_t zp_in,
+                           int32_t m_alpha, int32_t s_alpha, int32_t scaled_z, int32_t lo, int32_t hi, cudaStream_t s);
+int32_t device_fixed_point_multiply(int32_t x, int32_t m, int32_t s);  // one value, synchronous (init time)
 void launch_clip(const void* x, void* y, int dtype, long long n, double lo, double hi, cudaStream_t s);
 void launch_cast(const void* x, int x_dtype, void* y, int y_dtype, long long n, cudaStream_t s);
 // y = x + b[c] (int32 wrap / same dtype) over [outer][C][inner]; b has C elements of dtype b_dtype

@@ -715,6 +715,82 @@ void launch_concat_piece(const void* x, void* y, int dtype, long long outer, lon
   ++g_launches;
 }
 
+// take(table, indices) with 8-bit indices (bit pattern read as uint8) and a table of at most 256 entries of 1, 2 or 4
+// bytes: the form the table-lookup unary QNN operators legalize to (python/tvm/relay/qnn/op/canonicalizations.py:106-160).
+// HBM-bound: 16 indices per thread, the table staged in shared memory.
+template <typename T>
+__global__ void lut8_kernel(const uint8_t* __restrict__ x, const T* __restrict__ table, int entries, T* __restrict__ y,
+                            long long n, int vec16) {
+  __shared__ T tab[256];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) tab[i] = i < entries ? table[i] : T(0);
+  __syncthreads();
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x, stride = (long long)gridDim.x * blockDim.x;
+  if (vec16) {
+    for (long long v = tid; v < n / 16; v += stride) {
+      const uint4 in = __ldg((const uint4*)x + v);
+      const uint32_t w[4] = {in.x, in.y, in.z, in.w};
+      if constexpr (sizeof(T) == 1) {
+        uint32_t o[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          o[k] = (uint32_t)tab[w[k] & 0xFF] | ((uint32_t)tab[(w[k] >> 8) & 0xFF] << 8) |
+                 ((uint32_t)tab[(w[k] >> 16) & 0xFF] << 16) | ((uint32_t)tab[w[k] >> 24] << 24);
+        ((uint4*)y)[v] = make_uint4(o[0], o[1], o[2], o[3]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) y[v * 16 + k] = tab[(w[k >> 2] >> (8 * (k & 3))) & 0xFF];
+      }
+    }
+  } else {
+    for (long long i = tid; i < n; i += stride) y[i] = tab[x[i]];
+  }
+}
+
+void launch_lut8(const void* x, const void* table, int entries, int elem, void* y, long long n, cudaStream_t s) {
+  if (n == 0) return;
+  const int vec16 = (n % 16 == 0) && ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0;
+  const int bl = blocks_for(vec16 ? n / 16 : n, 256);
+  if (elem == 1) lut8_kernel<uint8_t><<<bl, 256, 0, s>>>((const uint8_t*)x, (const uint8_t*)table, entries, (uint8_t*)y, n, vec16);
+  else if (elem == 2) lut8_kernel<uint16_t><<<bl, 256, 0, s>>>((const uint8_t*)x, (const uint16_t*)table, entries, (uint16_t*)y, n, vec16);
+  else lut8_kernel<uint32_t><<<bl, 256, 0, s>>>((const uint8_t*)x, (const uint32_t*)table, entries, (uint32_t*)y, n, vec16);
+  ++g_launches;
+}
+
+// qnn.leaky_relu (src/relay/qnn/op/leaky_relu.cc:70-139), element by element on any integer dtype up to 32 bits:
+//   q = RequantizeOrUpcast(int32(x));  x < zp_in ? fixed_point_multiply(q, alpha) + fixed_point_multiply(zp_out, 1 - alpha) : q;
+//   saturate to the dtype.  `rq.skip_mul`-style identity is passed as `identity`.
+__global__ void qnn_leaky_relu_kernel(const void* __restrict__ x, void* __restrict__ y, int dtype, long long n, RqParams rq,
+                                      int identity, int32_t zp_in, int32_t m_alpha, int32_t s_alpha, int32_t scaled_z,
+                                      int32_t lo, int32_t hi) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int32_t v = load_as_i32(x, dtype, i);
+    const int32_t q = identity ? v : requantize_one(v, 0, rq);
+    int32_t r = q;
+    if (v < zp_in) r = (int32_t)((uint32_t)fixed_point_multiply_upward(q, m_alpha, s_alpha) + (uint32_t)scaled_z);
+    store_from_i32(y, dtype, i, min(max(r, lo), hi));
+  }
+}
+
+void launch_qnn_leaky_relu(const void* x, void* y, int dtype, long long n, const RqParams& rq, int identity, int32_t zp_in,
+                           int32_t m_alpha, int32_t s_alpha, int32_t scaled_z, int32_t lo, int32_t hi, cudaStream_t s) {
+  if (n == 0) return;
+  qnn_leaky_relu_kernel<<<blocks_for(n, 256), 256, 0, s>>>(x, y, dtype, n, rq, identity, zp_in, m_alpha, s_alpha, scaled_z, lo, hi);
+  ++g_launches;
+}
+
+// fixed_point_multiply of ONE value on the device (used once at init for the leaky-relu zero-point term, so that host
+// and device cannot disagree on the rounding)
+__global__ void fixed_point_multiply_kernel(int32_t x, int32_t m, int32_t s, int32_t* out) { *out = fixed_point_multiply_upward(x, m, s); }
+int32_t device_fixed_point_multiply(int32_t x, int32_t m, int32_t s) {
+  int32_t* d = nullptr;
+  int32_t h = 0;
+  if (cudaMalloc(&d, 4) != cudaSuccess) return 0;
+  fixed_point_multiply_kernel<<<1, 1>>>(x, m, s, d);
+  cudaMemcpy(&h, d, 4, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  return h;
+}
+
 __global__ void clip_kernel(const void* __restrict__ x, void* __restrict__ y, int dtype, long long n, double lo,
                             double hi) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {

@@ -1557,6 +1557,71 @@ static void plan_reshape(Planner& P, int nid) {  // reshape, nn.batch_flatten: a
   P.plan << "  [" << nid << "] " << n.name << " -> alias of e" << P.root(x_eid) << " (no kernel)\n";
 }
 
+// reinterpret: same bytes under another dtype of the same width -> alias, no kernel
+static void plan_reinterpret(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  if (P.ent[x_eid].shape != P.ent[y_eid].shape || dtype_size(P.ent[x_eid].dtype) != dtype_size(P.ent[y_eid].dtype))
+    fail("Unsupported op: reinterpret between dtypes of different width");
+  P.need(x_eid, kLogical);
+  P.ent[y_eid].alias_of = P.root(x_eid);
+  P.plan << "  [" << nid << "] reinterpret -> alias of e" << P.root(x_eid) << " (no kernel)\n";
+}
+
+// take(table, indices, axis = 0, mode = "fast") with a constant 1-D table and 8-bit indices: what the table-lookup
+// unary QNN operators legalize to (python/tvm/relay/qnn/op/canonicalizations.py:106-160)
+static void plan_take(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int t_eid = (int)P.g.eid(n.inputs[0]), i_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& Tb = P.ent[P.root(t_eid)];
+  const Entry& I = P.ent[i_eid];
+  if (!Tb.is_const || Tb.shape.size() != 1 || Tb.shape[0] > 256 || n.i64("axis", 0) != 0 || n.i64("batch_dims", 0) != 0)
+    fail("Unsupported op: take other than a constant table of <= 256 entries along axis 0");
+  if (I.dtype != kU8) fail("Unsupported op: take with indices that are not uint8 (reinterpret first)");
+  if (Tb.shape[0] < 256 && n.str("mode", "fast") != "fast") fail("Unsupported op: take with a short table outside mode=fast");
+  const int elem = dtype_size(Tb.dtype), entries = (int)Tb.shape[0];
+  if (elem > 4 || Tb.dtype != P.ent[y_eid].dtype || P.ent[y_eid].shape != I.shape) fail("Unsupported op: take with this table dtype / shape");
+  const int phys = P.preferred(i_eid);
+  P.need(i_eid, phys);
+  P.need(t_eid, kLogical);
+  P.produce(y_eid, phys);
+  const long long cnt = numel(I.shape);
+  P.rt->hbm_bytes += I.bytes() + P.ent[y_eid].bytes();
+  P.add_step("take -> 256-entry table lookup kernel", [=](RunCtx& c) {
+    launch_lut8(c.ptr(i_eid, phys), c.ptr(t_eid, kLogical), entries, elem, c.ptr(y_eid, phys), cnt, c.s);
+  });
+}
+
+// qnn.leaky_relu (src/relay/qnn/op/leaky_relu.cc:70-139), per-tensor parameters
+static void plan_qnn_leaky_relu(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[x_eid];
+  if (X.dtype == kF32 || X.dtype == kI64 || X.dtype != P.ent[y_eid].dtype) fail("Unsupported op: qnn.leaky_relu on this dtype");
+  auto si = P.cfloats((int)P.g.eid(n.inputs[1]), "input_scale"), so = P.cfloats((int)P.g.eid(n.inputs[3]), "output_scale");
+  auto zi = P.cints((int)P.g.eid(n.inputs[2]), "input_zero_point"), zo = P.cints((int)P.g.eid(n.inputs[4]), "output_zero_point");
+  if (si.size() != 1 || so.size() != 1 || zi.size() != 1 || zo.size() != 1) fail("Unsupported op: qnn.leaky_relu with per-channel parameters");
+  const double alpha = n.f64("alpha", 0.0);
+  int32_t ma, sa, mz, sz;
+  fixed_point_multiplier_shift(alpha, &ma, &sa);        // GetFixedPointMultiplierShift(alpha)
+  fixed_point_multiplier_shift(1.0 - alpha, &mz, &sz);  // ... (1 - alpha)
+  const int32_t scaled_z = device_fixed_point_multiply(zo[0], mz, sz);
+  const int identity = si[0] == so[0] && zi[0] == zo[0];  // RequantizeOrUpcast, op_common.h:196-210
+  RqParams rq = make_rq(P, si, zi, so[0], zo[0], kUpward, kInt64, kI32, 1);
+  int32_t lo, hi;
+  dtype_range(X.dtype, &lo, &hi);
+  const int phys = P.preferred(x_eid);
+  P.need(x_eid, phys);
+  P.produce(y_eid, phys);
+  const long long cnt = numel(X.shape);
+  const int dt = X.dtype;
+  const int32_t zp_in = zi[0];
+  P.rt->hbm_bytes += 2 * X.bytes();
+  P.add_step("qnn.leaky_relu -> elementwise kernel", [=](RunCtx& c) {
+    launch_qnn_leaky_relu(c.ptr(x_eid, phys), c.ptr(y_eid, phys), dt, cnt, rq, identity, zp_in, ma, sa, scaled_z, lo, hi, c.s);
+  });
+}
+
 static void plan_transpose(Planner& P, int nid) {
   const GNode& n = P.g.nodes[nid];
   const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
@@ -1764,6 +1829,9 @@ static void build_plan(tkb_runtime* rt) {
     else if (op == "nn.pad") plan_pad(P, (int)nid);
     else if (op == "reshape" || op == "nn.batch_flatten") plan_reshape(P, (int)nid);
     else if (op == "transpose") plan_transpose(P, (int)nid);
+    else if (op == "reinterpret") plan_reinterpret(P, (int)nid);
+    else if (op == "take") plan_take(P, (int)nid);
+    else if (op == "qnn.leaky_relu") plan_qnn_leaky_relu(P, (int)nid);
     else fail("Unsupported op: %s", op.c_str());  // same message as tachikoma_json_runtime.cc:286
     // trace records of this node: inputs then outputs, in the logical layout
     auto add_rec = [&](const std::string& name, int eid) {

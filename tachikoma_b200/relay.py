@@ -227,6 +227,39 @@ def qnn_dequantize(data, input_scale, input_zero_point, axis=-1):
                 dict(axis=int(axis)), data.shape, "float32")
 
 
+#: LUT-based unary QNN operators (python/tvm/relay/qnn/op/legalizations.py:54-86)
+QNN_UNARY_OPS = ("qnn.sqrt", "qnn.rsqrt", "qnn.exp", "qnn.erf", "qnn.sigmoid", "qnn.hardswish", "qnn.tanh", "qnn.log",
+                 "qnn.abs")
+
+
+def qnn_unary(op, x, scale, zero_point, output_scale, output_zero_point):
+    """relay.qnn.op.{sqrt,rsqrt,exp,erf,sigmoid,hardswish,tanh,log,abs}(x, scale, zero_point, output_scale,
+    output_zero_point): 8-bit in, same dtype out; legalized to a 256-entry table lookup (legalizations.py:54-86)."""
+    assert op in QNN_UNARY_OPS and x.dtype in ("int8", "uint8")
+    return Call(op, [x, _c(scale, "float32"), _c(zero_point, "int32"), _c(output_scale, "float32"),
+                     _c(output_zero_point, "int32")], {}, x.shape, x.dtype)
+
+
+def qnn_leaky_relu(x, alpha, input_scale, input_zero_point, output_scale, output_zero_point):
+    """relay.qnn.op.leaky_relu (src/relay/qnn/op/leaky_relu.cc:70-139)."""
+    return Call("qnn.leaky_relu", [x, _c(input_scale, "float32"), _c(input_zero_point, "int32"),
+                                   _c(output_scale, "float32"), _c(output_zero_point, "int32")],
+                dict(alpha=float(alpha)), x.shape, x.dtype)
+
+
+def reinterpret(data, dtype):
+    """relay.reinterpret: same bits, other dtype of the same width."""
+    assert np.dtype(dtype).itemsize == np.dtype(data.dtype).itemsize
+    return Call("reinterpret", [data], dict(dtype=dtype), data.shape, dtype)
+
+
+def take(table, indices, axis=0, mode="fast"):
+    """relay.take(table, indices, axis=0, mode="fast") with a 1-D table: out[i...] = table[indices[i...]]."""
+    table = _c(table)
+    assert len(table.shape) == 1 and axis == 0
+    return Call("take", [table, indices], dict(axis=0, mode=mode, batch_dims=0), indices.shape, table.dtype)
+
+
 def bias_add(data, bias, axis=1):
     return Call("nn.bias_add", [data, _c(bias)], dict(axis=int(axis)), data.shape, data.dtype)
 

@@ -246,10 +246,74 @@ def _make_composite(m, mode):
 #: operators the CUDA runtime executes outside a composite (single-op JSON kernel nodes)
 SUPPORTED_OPS = {
     "qnn.conv2d", "qnn.dense", "qnn.batch_matmul", "qnn.requantize", "qnn.add", "qnn.mul", "qnn.concatenate",
-    "qnn.quantize", "qnn.dequantize", "nn.bias_add", "add", "clip",
+    "qnn.quantize", "qnn.dequantize", "qnn.leaky_relu", "reinterpret", "take", "nn.bias_add", "add", "clip",
     "cast", "nn.max_pool2d", "nn.avg_pool2d", "nn.global_avg_pool2d", "nn.pad", "reshape", "nn.batch_flatten",
     "transpose",
 }
+
+
+def _hardswish(x):
+    return x * np.clip(x + 3.0, 0.0, 6.0) / 6.0
+
+
+def _unary_float_funcs():
+    """python/tvm/relay/qnn/op/legalizations.py:68-86 (the numpy functions the reference registers)."""
+    from scipy import special
+    return {"qnn.sqrt": np.sqrt, "qnn.rsqrt": lambda a: 1 / np.sqrt(a), "qnn.exp": np.exp, "qnn.erf": special.erf,
+            "qnn.sigmoid": lambda a: 1 / (1 + np.exp(-a)), "qnn.hardswish": _hardswish, "qnn.tanh": np.tanh,
+            "qnn.log": np.log, "qnn.abs": np.abs}
+
+
+def create_integer_lookup_table(floating_point_func, input_scale, input_zero_point, output_scale, output_zero_point,
+                                in_dtype="uint8", out_dtype="uint8"):
+    """python/tvm/relay/qnn/op/canonicalizations.py:31-103: out[b] = quantize(f(dequantize(b))) for all 256 bit
+    patterns b of the input dtype, indexed by the pattern read as uint8.  dequantize = float32(int32(b) - zp) * scale
+    (dequantize.cc:95-127); quantize = clip(round(x / scale) + zp) in float32, round half away from zero
+    (quantize.cc:113-150)."""
+    if np.dtype(in_dtype).itemsize != 1 or np.dtype(out_dtype).itemsize != 1:
+        raise ValueError(f"Only 8-bit integer dtypes are supported, got {in_dtype} and {out_dtype}")
+    pat = np.arange(256, dtype=np.uint8).view(in_dtype)
+    with np.errstate(all="ignore"):
+        deq = (pat.astype(np.int32) - np.int32(input_zero_point)).astype(np.float32) * np.float32(input_scale)
+        f = np.asarray(floating_point_func(deq), dtype=np.float32)
+        v = (f / np.float32(output_scale)).astype(np.float32)
+        t = np.trunc(v)
+        r = np.where(np.isfinite(v), t + np.sign(v) * (np.abs(v - t) >= 0.5), v).astype(np.float32)
+        r = (r + np.float32(output_zero_point)).astype(np.float32)
+        info = np.iinfo(out_dtype)
+        r = np.where(r < info.min, info.min, np.where(r > info.max, info.max, r))
+        r = np.where(np.isnan(r), 0.0, r)  # undefined in the reference (float -> int cast of NaN)
+    return r.astype(np.int64).astype(out_dtype)
+
+
+def legalize_qnn_unary(func):
+    """relay.qnn.transform.Legalize for the table-lookup unary operators (legalizations.py:54-71,
+    canonicalizations.py:106-160): qnn.<f>(x, s_in, zp_in, s_out, zp_out) -> take(table, reinterpret(x, uint8))."""
+    funcs = None
+    memo = {}
+
+    def visit(e):
+        nonlocal funcs
+        if id(e) in memo:
+            return memo[id(e)]
+        out = e
+        if isinstance(e, R.Call):
+            args = [visit(x) for x in e.args]
+            if e.op in R.QNN_UNARY_OPS:
+                if not all(_is_const(a) and np.asarray(a.data).size == 1 for a in args[1:5]):
+                    raise ValueError(f"Unsupported op: {e.op} with non-scalar quantization parameters")
+                funcs = funcs or _unary_float_funcs()
+                sc = lambda a: np.asarray(a.data).reshape(-1)[0]
+                table = create_integer_lookup_table(funcs[e.op], np.float32(sc(args[1])), int(sc(args[2])),
+                                                    np.float32(sc(args[3])), int(sc(args[4])), e.args[0].dtype, e.dtype)
+                out = R.take(R.const(table), R.reinterpret(args[0], "uint8"), axis=0, mode="fast")
+            elif any(a is not b for a, b in zip(args, e.args)):
+                out = R.Call(e.op, args, dict(e.attrs), e.shape, e.dtype)
+        memo[id(e)] = out
+        return out
+
+    body = visit(func.body)
+    return func if body is func.body else R.Function(func.params, body, dict(func.attrs))
 
 
 def legalize_qnn_for_tachikoma(func, mode="dnnl_float"):
@@ -346,6 +410,7 @@ def partition_for_tachikoma(func, params=None, mode="int", symbol="tvmgen_defaul
         func = R.bind_params(func, params)
     from .frontend import fold_explicit_padding  # SimplifyExpr / FoldExplicitPadding, test_tachikoma.py:88
     func = fold_explicit_padding(func)
+    func = legalize_qnn_unary(func)  # relay.qnn.transform.Legalize: table-lookup unary operators
     func = legalize_qnn_for_tachikoma(func, mode=mode)
     for e in R.post_order(func.body):
         if isinstance(e, R.Call) and not e.op.startswith("tachikoma.") and e.op not in SUPPORTED_OPS:

@@ -9,7 +9,8 @@ TVM itself cannot be imported here, so a small shim ``tvm`` package is installed
 reference test files
     tests/python/relay/test_op_qnn_requantize.py, test_op_qnn_dense.py, test_op_qnn_add.py,
     tests/python/relay/test_op_qnn_batch_matmul.py, test_op_qnn_conv2d.py,
-    tests/python/relay/test_op_qnn_mul.py, test_op_qnn_concatenate.py, test_op_qnn_quantize.py, test_op_qnn_dequantize.py
+    tests/python/relay/test_op_qnn_mul.py, test_op_qnn_concatenate.py, test_op_qnn_quantize.py, test_op_qnn_dequantize.py,
+    tests/python/relay/test_op_qnn_leaky_relu.py, test_op_qnn_unary_elementwise.py
 are then executed unmodified.  Whenever a test compares a QNN graph's output with a golden
 (``np.testing.assert_equal``) the triple (graph, inputs, golden) is captured.  For the conv2d
 property tests the golden is the test's own *reference function* (int32 nn.conv2d over
@@ -36,7 +37,8 @@ REF_TESTS = "/root/reference/tests/python/relay"
 FILES = ["test_op_qnn_requantize.py", "test_op_qnn_dense.py", "test_op_qnn_add.py",
          "test_op_qnn_batch_matmul.py", "test_op_qnn_conv2d.py",
          # round 2; appended so that the cases above keep their indices and random draws
-         "test_op_qnn_mul.py", "test_op_qnn_concatenate.py", "test_op_qnn_quantize.py", "test_op_qnn_dequantize.py"]
+         "test_op_qnn_mul.py", "test_op_qnn_concatenate.py", "test_op_qnn_quantize.py", "test_op_qnn_dequantize.py",
+         "test_op_qnn_leaky_relu.py", "test_op_qnn_unary_elementwise.py"]
 
 CASES, SKIPPED = [], []
 CURRENT = {"name": ""}
@@ -129,6 +131,10 @@ def to_ir(e, memo):
             if not isinstance(z, R.Constant):
                 raise Unsupported("non-constant qnn parameter")
         r = R.qnn_dequantize(a[0], a[1], a[2], **at)
+    elif e.op == "qnn.leaky_relu":
+        r = R.qnn_leaky_relu(a[0], at["alpha"], a[1], a[2], a[3], a[4])
+    elif e.op in R.QNN_UNARY_OPS:
+        r = R.qnn_unary(e.op, *a[:5])
     elif e.op == "qnn.conv2d":
         for z in a[2:6]:
             if not isinstance(z, R.Constant):
@@ -311,6 +317,7 @@ def install_shim():
     tvm.transform = types.SimpleNamespace(PassContext=lambda **kw: contextlib.nullcontext())
 
     relay.var, relay.const = s_var, s_const
+    relay.Expr, relay.Call = S, S  # type annotations in the test files
     relay.Function = lambda params, body: Module(list(params), body)
 
     def free_vars(e):
@@ -398,10 +405,29 @@ def install_shim():
     relay.split = r_split
     relay.TensorType = lambda shape, dtype="float32": ("TensorType", tuple(shape), dtype)
 
-    qop = types.SimpleNamespace(requantize=q_requantize, dense=q_dense, batch_matmul=q_bmm, add=q_add, mul=q_mul,
+    def q_leaky_relu(x, alpha, input_scale, input_zero_point, output_scale, output_zero_point):
+        return S("qnn.leaky_relu", [x, input_scale, input_zero_point, output_scale, output_zero_point], dict(alpha=float(alpha)))
+
+    def q_unary(name):
+        def make(x, scale, zero_point, output_scale, output_zero_point):
+            return S("qnn." + name, [x, scale, zero_point, output_scale, output_zero_point])
+        return make
+
+    qop = types.SimpleNamespace(requantize=q_requantize, leaky_relu=q_leaky_relu,
+                                **{k: q_unary(k) for k in ("sqrt", "rsqrt", "exp", "erf", "sigmoid", "hardswish", "tanh",
+                                                           "log", "abs")}, dense=q_dense, batch_matmul=q_bmm, add=q_add, mul=q_mul,
                                 concatenate=q_concatenate, quantize=q_quantize, dequantize=q_dequantize,
                                 conv2d=q_conv2d, requantize_config=requantize_config)
-    relay.qnn = types.SimpleNamespace(op=qop, transform=types.SimpleNamespace(CanonicalizeOps=ident))
+    relay.qnn = types.SimpleNamespace(op=qop, transform=types.SimpleNamespace(CanonicalizeOps=ident, Legalize=ident))
+    leg = types.ModuleType("tvm.relay.qnn.op.legalizations")  # the test imports the reference's own hardswish_func
+
+    def hardswish_func(x):
+        x2 = np.clip(x + 3.0, 0.0, 6.0)
+        return x * x2 / 6.0
+    leg.hardswish_func = hardswish_func
+    for name in ("tvm.relay.qnn", "tvm.relay.qnn.op"):
+        sys.modules[name] = types.ModuleType(name)
+    sys.modules["tvm.relay.qnn.op.legalizations"] = leg
 
     def nn_conv2d(data, weight, strides=(1, 1), padding=(0, 0), dilation=(1, 1), groups=1, channels=None,
                   kernel_size=None, data_layout="NCHW", kernel_layout="OIHW", out_layout="", out_dtype=""):
@@ -424,7 +450,9 @@ def install_shim():
     ge.create = lambda graph, lib, device=None: Executor(graph, {})
     contrib.graph_executor = ge
     tvm.contrib = contrib
-    tvm.testing = types.SimpleNamespace(main=lambda: None)
+    tvm.testing = types.ModuleType("tvm.testing")
+    tvm.testing.main = lambda: None
+    sys.modules["tvm.testing"] = tvm.testing
     tvm.__path__ = []  # "import tvm.topi.testing" needs tvm to look like a package
     topi = types.ModuleType("tvm.topi")
     topi_testing = types.ModuleType("tvm.topi.testing")
@@ -458,11 +486,15 @@ def main():
         spec = importlib.util.spec_from_file_location("ref_" + fname[:-3], os.path.join(REF_TESTS, fname))
         mod = importlib.util.module_from_spec(spec)
         spec.loader.exec_module(mod)
-        for tname in [n for n in dir(mod) if n.startswith("test_")]:
+        tests = [(n, getattr(mod, n)) for n in dir(mod) if n.startswith("test_")]
+        for cname in [n for n in dir(mod) if n.startswith("Test") and isinstance(getattr(mod, n), type)]:  # pytest classes
+            obj = getattr(mod, cname)()
+            tests += [(cname + "::" + n, getattr(obj, n)) for n in dir(obj) if n.startswith("test_")]
+        for tname, tfn in tests:
             CURRENT["name"] = f"tests/python/relay/{fname}::{tname}"
             before = len(CASES)
             try:
-                getattr(mod, tname)()
+                tfn()
             except Unsupported as ex:
                 SKIPPED.append(dict(source=CURRENT["name"], why=str(ex), captured_before_skip=len(CASES) - before))
             except Exception as ex:  # the shim does not cover everything; say so

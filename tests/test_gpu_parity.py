@@ -828,3 +828,61 @@ def test_unsupported_op_fails_at_init_not_run():
     mod = RT.TachikomaJSONRuntime(sym, js, names)
     with pytest.raises(RT.TachikomaError, match="Unsupported op: nn.softmax"):
         mod.init(consts)
+
+
+# ---- N3, second part: qnn.leaky_relu and the table-lookup unary operators ------------------------------------------
+@pytest.mark.parametrize("dtype", ["uint8", "int8"])
+def test_table_lookup_unary_ops_on_gpu(dtype):
+    """qnn.{sqrt,rsqrt,exp,erf,sigmoid,hardswish,tanh,log,abs} -> take(table, reinterpret(x)) -> lut8_kernel: every bit
+    pattern, ragged and 16-byte-multiple sizes, equal to the oracle's element-by-element evaluation."""
+    rng = np.random.default_rng(5)
+    for shape in [(4, 64), (3, 5, 7), (2, 16, 12, 12)]:
+        x = rng.integers(0, 256, shape).astype(np.uint8).view(dtype)
+        x.reshape(-1)[:256] = np.arange(256, dtype=np.uint8).view(dtype)[:x.size]
+        for op in R.QNN_UNARY_OPS:
+            v = R.var("in_0", shape, dtype)
+            f = R.Function([v], R.qnn_unary(op, v, 0.05, 3, 0.02, 7 if dtype == "uint8" else -4))
+            want, _ = interp.run_expr(f, {"in_0": x})
+            out, mod, _ = run_gpu(f, {"in_0": x}, trace=True)
+            np.testing.assert_equal(out, want)
+            assert "table lookup" in mod.plan_summary()
+
+
+def test_unary_lut_inside_a_convolution_chain_on_gpu():
+    """conv -> requantize -> clip -> cast -> qnn.tanh -> conv: the lookup runs on the channels-last tensor between two
+    tensor-core convolutions; logits and trace equal the oracle's."""
+    rng = np.random.default_rng(6)
+    x = rng.integers(0, 256, (2, 16, 12, 12)).astype(np.uint8)
+    v = R.var("in_0", x.shape, "uint8")
+
+    def conv(e, oc, zp_in, s_in, s_out, zp_out):
+        w = R.const(rng.integers(-20, 20, (oc, e.shape[1], 3, 3)).astype("int8"))
+        c = R.qnn_conv2d(e, w, zp_in, 0, s_in, 0.01, (3, 3), oc, padding=(1, 1))
+        c = R.qnn_requantize(c, np.float32(s_in * 0.01), 0, s_out, zp_out, axis=1, out_dtype="int32")
+        return R.cast(R.clip(c, 0.0, 255.0), "uint8")
+    e = conv(v, 32, 128, 0.02, 0.05, 128)
+    e = R.qnn_unary("qnn.tanh", e, 0.05, 128, 1.0 / 128, 128)
+    e = conv(e, 16, 128, 1.0 / 128, 0.04, 0)
+    f = R.Function([v], e)
+    want, _ = interp.run_expr(f, {"in_0": x})
+    for impl in ("auto", "tc"):
+        out, mod, (js, consts, ins) = run_gpu(f, {"in_0": x}, conv_impl=impl, trace=True)
+        np.testing.assert_equal(out, want)
+        _, recs = interp.run_json(js, consts, ins, want_trace=True)
+        assert mod.trace_blob() == interp.save_ndarray_list(recs)
+
+
+@pytest.mark.parametrize("dtype", ["uint8", "int8"])
+def test_qnn_leaky_relu_on_gpu(dtype):
+    rng = np.random.default_rng(7)
+    for shape in [(1, 256), (3, 5, 7), (2, 16, 12, 12)]:
+        x = rng.integers(0, 256, shape).astype(np.uint8).view(dtype)
+        x.reshape(-1)[:256] = np.arange(256, dtype=np.uint8).view(dtype)[:x.size]
+        zi, zo = (60, 17) if dtype == "uint8" else (-20, 9)
+        for alpha, si, so, z_in, z_out in [(0.9, 0.125, 0.6, zi, zo), (0.1, 0.05, 0.05, zi, zi), (0.5, 0.2, 0.1, zi, zo),
+                                           (0.25, 0.25, 0.125, zi, zo)]:
+            v = R.var("in_0", shape, dtype)
+            f = R.Function([v], R.qnn_leaky_relu(v, alpha, si, z_in, so, z_out))
+            want, _ = interp.run_expr(f, {"in_0": x})
+            out, _, _ = run_gpu(f, {"in_0": x}, trace=True)
+            np.testing.assert_equal(out, want)

@@ -253,3 +253,38 @@ def test_wrapper_surface_of_the_reference_module():
     with pytest.raises(ValueError, match="Unsupported op: nn.conv2d"):
         T.rewrite_resnetv1(fl)
     assert T.get_optimal_layout_for_conv("NCHW", "OIHW") == "NHWC,OHWI,NHWC"
+
+
+@pytest.mark.parametrize("dtype", ["uint8", "int8"])
+def test_table_lookup_legalization_equals_elementwise_oracle(dtype):
+    """legalize_qnn_unary (product, numpy) builds take(table, reinterpret(x)); the oracle evaluates the un-legalized
+    operator element by element: same bytes for every bit pattern, also where f is undefined (sqrt / log of negatives)."""
+    x = np.arange(256, dtype=np.uint8).view(dtype).reshape(4, 64)
+    for op in R.QNN_UNARY_OPS:
+        for (si, zi, so, zo) in [(0.125, 0, 0.125, 0), (0.05, 3, 0.02, -4 if dtype == "int8" else 7), (0.3, 100 if dtype == "uint8" else -100, 0.01, 0)]:
+            v = R.var("x", x.shape, dtype)
+            f = R.Function([v], R.qnn_unary(op, v, si, zi, so, zo))
+            want, _ = interp.run_expr(f, {"x": x})
+            leg = T.legalize_qnn_unary(f)
+            ops = [e.op for e in R.post_order(leg.body) if isinstance(e, R.Call)]
+            assert ops == ["reinterpret", "take"], ops
+            got, _ = interp.run_expr(leg, {"x": x})
+            np.testing.assert_array_equal(got, want, err_msg=f"{op} {dtype} {(si, zi, so, zo)}")
+            part = T.partition_for_tachikoma(f)
+            _, js, _, consts = T.serialize(part)
+            outs, _ = interp.run_json(js, consts, [x])
+            np.testing.assert_array_equal(outs[0], want)
+
+
+def test_leaky_relu_oracle_matches_float_definition_within_one():
+    x = np.arange(256, dtype=np.uint8).reshape(1, 256)
+    v = R.var("x", x.shape, "uint8")
+    for alpha, si, zi, so, zo in [(0.9, 0.125, 60, 0.6, 17), (0.1, 0.05, 128, 0.05, 128), (0.25, 0.2, 10, 0.1, 3)]:
+        f = R.Function([v], R.qnn_leaky_relu(v, alpha, si, zi, so, zo))
+        got, _ = interp.run_expr(f, {"x": x})
+        d = (x.astype(np.float64) - zi) * si
+        want = np.clip(np.round(np.where(d < 0, alpha * d, d) / so + zo), 0, 255)
+        assert np.abs(got.astype(int) - want).max() <= 1
+        _, js, _, consts = T.serialize(T.partition_for_tachikoma(f))
+        outs, _ = interp.run_json(js, consts, [x])
+        np.testing.assert_array_equal(outs[0], got)

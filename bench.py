@@ -431,7 +431,7 @@ def main():
             dst.copy_(src, non_blocking=True)
         b.record()
         barrier()
-        return 4 * probe_bytes / (max_over_ranks(a.elapsed_time(b)) * 1e-3) / 1e9
+        return world * 4 * probe_bytes / (max_over_ranks(a.elapsed_time(b)) * 1e-3) / 1e9  # all ranks together
 
     d2h_gbs, h2d_gbs = copy_rate(ph, pd), copy_rate(pd, ph)
     del pd, ph

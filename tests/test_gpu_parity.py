@@ -886,3 +886,70 @@ def test_qnn_leaky_relu_on_gpu(dtype):
             want, _ = interp.run_expr(f, {"in_0": x})
             out, _, _ = run_gpu(f, {"in_0": x}, trace=True)
             np.testing.assert_equal(out, want)
+
+
+# ---- randomized sweep: conv / dense chains with every attribute drawn at random -----------------------------------
+def _random_chain(seed):
+    """One random fused chain: qnn.conv2d | qnn.dense (+ bias) -> requantize -> clip -> cast [-> qnn.add -> clip]."""
+    rng = np.random.default_rng(1000 + seed)
+    pick = lambda xs: xs[int(rng.integers(0, len(xs)))]
+    xdt, odt = pick(["uint8", "uint8", "int8"]), pick(["uint8", "uint8", "int8"])
+    xi, oi = np.iinfo(xdt), np.iinfo(odt)
+    zp_x = int(rng.integers(xi.min, xi.max + 1)) if rng.random() < 0.6 else 0
+    per_channel = rng.random() < 0.6
+    if seed % 4 == 3:  # dense
+        m, k, n = int(rng.integers(1, 70)), pick([1, 7, 16, 48, 100, 256]), pick([1, 5, 16, 64, 100])
+        x = rng.integers(xi.min, xi.max + 1, (m, k)).astype(xdt)
+        w = rng.integers(-127, 128, (n, k)).astype("int8")
+        v = R.var("in_0", x.shape, xdt)
+        sw = (rng.uniform(0.5, 1.5, n) / (127 * np.sqrt(k))).astype("float32") if per_channel else np.float32(0.7 / (127 * np.sqrt(k)))
+        e = R.qnn_dense(v, R.const(w), zp_x, 0, np.float32(0.05), R.const(sw) if per_channel else sw, n)
+        axis, oc, bshape = -1, n, (n,)
+    else:
+        kh, kw = pick([1, 1, 2, 3, 3, 5]), pick([1, 1, 2, 3, 3, 5])
+        dil, st = (pick([1, 1, 2]), pick([1, 1, 2])), (pick([1, 1, 2, 3]), pick([1, 1, 2, 3]))
+        pad = (int(rng.integers(0, 3)), int(rng.integers(0, 3)), int(rng.integers(0, 3)), int(rng.integers(0, 3)))
+        c = pick([1, 3, 4, 8, 16, 24, 32, 64, 96, 128])
+        groups = pick([1, 1, 1, c]) if c > 1 else 1
+        oc = pick([1, 4, 16, 32, 64, 100, 128, 192]) if groups == 1 else c * pick([1, 2])
+        h = int(rng.integers((kh - 1) * dil[0] + 1, (kh - 1) * dil[0] + 18))
+        wd = int(rng.integers((kw - 1) * dil[1] + 1, (kw - 1) * dil[1] + 18))
+        nb = int(rng.integers(1, 5))
+        x = rng.integers(xi.min, xi.max + 1, (nb, c, h, wd)).astype(xdt)
+        w = rng.integers(-127, 128, (oc, c // groups, kh, kw)).astype("int8")
+        kk = kh * kw * c // groups
+        sw = (rng.uniform(0.5, 1.5, oc) / (127 * np.sqrt(kk))).astype("float32") if per_channel else np.float32(0.7 / (127 * np.sqrt(kk)))
+        v = R.var("in_0", x.shape, xdt)
+        e = R.qnn_conv2d(v, R.const(w), zp_x, 0, np.float32(0.05), R.const(sw) if per_channel else sw, (kh, kw), oc,
+                         strides=st, padding=pad, dilation=dil, groups=groups)
+        axis, bshape = 1, (oc,)
+    if rng.random() < 0.7:
+        e = R.bias_add(e, R.const(rng.integers(-3000, 3000, bshape).astype("int32")), axis=axis)
+    rq_in = (np.float32(0.05) * np.asarray(sw, dtype=np.float32)).astype("float32")
+    zp_o = int(rng.integers(oi.min, oi.max + 1)) if rng.random() < 0.5 else 0
+    e = R.qnn_requantize(e, R.const(rq_in) if per_channel else np.float32(rq_in), 0, np.float32(pick([0.02, 0.05, 0.11])), zp_o,
+                         axis=axis, out_dtype="int32")
+    lo = float(pick([oi.min, oi.min, max(oi.min, zp_o)]))
+    e = R.cast(R.clip(e, lo, float(oi.max)), odt)
+    ins = {"in_0": x}
+    params = [v]
+    if rng.random() < 0.4:
+        r = R.var("in_1", e.shape, odt)
+        ins["in_1"] = rng.integers(oi.min, oi.max + 1, e.shape).astype(odt)
+        params.append(r)
+        e = R.qnn_add(e, r, np.float32(pick([0.02, 0.05])), zp_o, np.float32(pick([0.02, 0.03, 0.05])),
+                      int(rng.integers(oi.min, oi.max + 1)), np.float32(pick([0.02, 0.06])), int(rng.integers(oi.min, oi.max + 1)))
+        e = R.clip(e, float(oi.min), float(oi.max))
+    return R.Function(params, e), ins
+
+
+@pytest.mark.parametrize("seed", range(96))
+def test_randomized_chain_sweep(seed):
+    func, ins = _random_chain(seed)
+    want, _ = interp.run_expr(func, ins)
+    for impl in ("auto", "tc", "simt"):
+        out, mod, (js, consts, xs) = run_gpu(func, ins, conv_impl=impl, trace=(impl == "tc"))
+        np.testing.assert_equal(out, want, err_msg=f"seed {seed} impl {impl}: {mod.plan_summary()}")
+        if impl == "tc":
+            _, recs = interp.run_json(js, consts, xs, want_trace=True)
+            assert mod.trace_blob() == interp.save_ndarray_list(recs)

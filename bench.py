@@ -239,7 +239,8 @@ def verify_against_oracle(model, batch, graph_json, consts, x, logits, blob, sub
     for lo, hi in spans:
         n = hi - lo
         part, _, js, _, cs = build_model(model, n)
-        outs, want = interp.run_json(js, cs, [np.ascontiguousarray(x[lo:hi])], want_trace=True)
+        rin = x.shape[0] // batch  # input rows per unit of the batch (BERT: 128 token rows per sequence)
+        outs, want = interp.run_json(js, cs, [np.ascontiguousarray(x[lo * rin:hi * rin])], want_trace=True)
         k = logits.shape[0] // batch
         if not np.array_equal(np.asarray(outs[0]), logits[lo * k:hi * k]):
             problems.append("logits of images %d..%d differ from the oracle" % (lo, hi))

@@ -18,6 +18,9 @@ convert -> torch.jit.trace) runs on the integer path:
   aten::adaptive_avg_pool2d / aten::avg_pool2d / aten::mean on a quantized tensor:
                              cast(int32) -> pool -> cast(uint8)  (apply_with_upcast, :587-590)
   aten::max_pool2d, aten::flatten, aten::reshape / view, aten::relu (= clip(zp, 255), :599-602)
+  quantized::leaky_relu -> qnn.leaky_relu (:982-1012); quantized::hardswish -> qnn.hardswish (:1041-1078);
+  aten::sigmoid / aten::tanh on a quantized tensor -> qnn.sigmoid / qnn.tanh with torch's fixed output parameters
+  (:399-423); aten::hardtanh / relu6 -> clip with quantized bounds (:964-979)
 
 Input quantization parameters are not operands in TorchScript (they live in the QTensor); like the reference
 (:240-296, :426-526) they are found by walking back to the producing op's output scale / zero point, here simply
@@ -207,6 +210,21 @@ def from_torchscript(script_module, input_shapes, input_names=None):
             r = _Q(e, a[0].scale, a[0].zp)
         elif kind in ("aten::reshape", "aten::view"):
             r = _Q(R.reshape(a[0].expr, _ints(a[1])), a[0].scale, a[0].zp)
+        elif kind == "quantized::leaky_relu":  # (x, negative_slope, inplace, output_scale, output_zero_point), :982-1012
+            s_out, zp_out = np.float32(a[3]), int(a[4])
+            r = _Q(R.qnn_leaky_relu(a[0].expr, float(a[1]), np.float32(a[0].scale), int(a[0].zp), s_out, zp_out), s_out, zp_out)
+        elif kind == "quantized::hardswish":  # (x, output_scale, output_zero_point), :1041-1078
+            s_out, zp_out = np.float32(a[1]), int(a[2])
+            r = _Q(R.qnn_unary("qnn.hardswish", a[0].expr, np.float32(a[0].scale), int(a[0].zp), s_out, zp_out), s_out, zp_out)
+        elif kind in ("aten::sigmoid", "aten::tanh") and a[0].quantized:
+            # fixed output parameters of torch's quantized kernels (qsigmoid.cpp / qtanh.cpp; :399-423 for sigmoid)
+            s_out, zp_out = (np.float32(1.0 / 256), 0) if kind == "aten::sigmoid" else (np.float32(2.0 / 256), 128)
+            r = _Q(R.qnn_unary("qnn." + kind[6:], a[0].expr, np.float32(a[0].scale), int(a[0].zp), s_out, zp_out), s_out, zp_out)
+        elif kind in ("aten::hardtanh", "aten::hardtanh_", "aten::relu6", "aten::relu6_", "quantized::relu6") and a[0].quantized:
+            # clip in the quantized domain with quantized bounds (quantize_scalar, :964-979)
+            lo_f, hi_f = (float(a[1]), float(a[2])) if "hardtanh" in kind else (0.0, 6.0)
+            qs = lambda v: max(0, min(int(round(a[0].zp + v / float(a[0].scale))), 255))
+            r = _Q(R.clip(a[0].expr, float(qs(lo_f)), float(qs(hi_f))), a[0].scale, a[0].zp)
         elif kind in ("aten::relu", "aten::relu_"):
             if not a[0].quantized:
                 raise ValueError("Unsupported op: aten::relu on a float tensor")

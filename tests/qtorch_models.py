@@ -99,6 +99,33 @@ class MLP(nn.Module):
         tq.fuse_modules(self, [["f1", "r1"]], inplace=True)
 
 
+class ActNet(nn.Module):
+    """conv -> quantized::leaky_relu -> conv -> quantized::hardswish -> conv -> aten::sigmoid -> relu6 -> conv."""
+
+    def __init__(self):
+        super().__init__()
+        self.q, self.dq = tq.QuantStub(), tq.DeQuantStub()
+        self.c1 = nn.Conv2d(3, 8, 3, 1, 1)
+        self.a1 = nn.LeakyReLU(0.1)
+        self.c2 = nn.Conv2d(8, 8, 3, 1, 1)
+        self.a2 = nn.Hardswish()
+        self.c3 = nn.Conv2d(8, 8, 1)
+        self.a3 = nn.Sigmoid()
+        self.c4 = nn.Conv2d(8, 8, 1)
+        self.a4 = nn.ReLU6()
+        self.c5 = nn.Conv2d(8, 4, 1)
+
+    def forward(self, x):
+        x = self.a1(self.c1(self.q(x)))
+        x = self.a2(self.c2(x))
+        x = self.a3(self.c3(x))
+        x = self.a4(self.c4(x))
+        return self.dq(self.c5(x))
+
+    def fuse(self):
+        pass
+
+
 def build(cls, shape, seed=0, per_channel=True):
     """-> (traced ScriptModule, eager quantized module).  BatchNorm statistics are randomized so that folding matters."""
     torch.manual_seed(seed)

@@ -126,6 +126,27 @@ def test_linear_relu_model():
     assert d.max() <= 1.0 + 1e-3, d.max()
 
 
+def test_activation_model_leaky_relu_hardswish_sigmoid_relu6():
+    shape = (2, 3, 10, 10)
+    ts, eager = QM.build(QM.ActNet, shape, seed=2)
+    func = F.from_torchscript(ts, [shape], ["x"])
+    ops = _ops(func)
+    for op in ("qnn.leaky_relu", "qnn.hardswish", "qnn.sigmoid"):
+        assert op in ops
+    sig = [e for e in R.post_order(func.body) if isinstance(e, R.Call) and e.op == "qnn.sigmoid"][0]
+    assert float(np.asarray(sig.args[3].data).reshape(-1)[0]) == 1.0 / 256 and int(np.asarray(sig.args[4].data).reshape(-1)[0]) == 0
+    part = T.partition_for_tachikoma(func)
+    sym, js, names, consts = T.serialize(part)
+    kernels = [n["name"] for n in __import__("json").loads(js)["nodes"] if n["op"] == "kernel"]
+    assert kernels.count("take") == 2 and kernels.count("reinterpret") == 2 and "qnn.leaky_relu" in kernels
+    x = QM.sample(shape)
+    a, _ = interp.run_expr(func, {"x": x})
+    outs, _ = interp.run_json(js, consts, [x])
+    np.testing.assert_array_equal(outs[0], a)
+    d = _compare_with_torch(ts, func, shape, "x")
+    assert d.max() <= 2.0 + 1e-3 and (d <= 1.0 + 1e-3).mean() >= 0.95, (d.max(), (d <= 1.0 + 1e-3).mean())
+
+
 def test_importer_rejects_unknown_ops():
     class M(torch.nn.Module):
         def forward(self, x):

@@ -53,3 +53,11 @@ def test_imported_mlp_on_gpu():
     ts, _ = QM.build(QM.MLP, shape, seed=5)
     func = F.from_torchscript(ts, [shape], ["x"])
     _run(func, "x", QM.sample(shape), "auto")
+
+
+def test_imported_activation_model_on_gpu():
+    shape = (2, 3, 10, 10)
+    ts, _ = QM.build(QM.ActNet, shape, seed=2)
+    func = F.from_torchscript(ts, [shape], ["x"])
+    for impl in ("auto", "tc"):
+        _run(func, "x", QM.sample(shape), impl)

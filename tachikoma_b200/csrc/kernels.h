@@ -121,6 +121,11 @@ bool tc_halo_supported(const ConvGeom& g, int N);
 void tc_halo_tile_config(const ConvGeom& g, int N, int* bn, int* bk);
 int launch_tc_halo(const TcArgs& a, cudaStream_t s);
 int launch_tc(const TcArgs& a, cudaStream_t s);
+// cta_group::2 pair kernel (kernels_tc_pair.cu): 256 x BN tiles on two CTAs of a cluster, B halved per CTA; fast
+// epilogues, unpacked K-major weights, plain GEMM or im2col-mode implicit convolution
+bool tc_pair_supported(const TcArgs& a);
+int tc_pair_bn(const TcArgs& a);
+int launch_tc_pair(const TcArgs& a, cudaStream_t s);
 
 // ---- chained launch (kernels_tc_chain.cu): several consecutive fast-epilogue layers in ONE persistent kernel, tiles of
 // layer k+1 gated per image on layer k's completion counters.  A layer is a TcArgs of the implicit-conv (implicit == 1)

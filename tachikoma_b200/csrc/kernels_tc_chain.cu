@@ -54,6 +54,7 @@ struct ChainSeg {
   ChainEpiStub e;
   FastEpi f;
   static constexpr bool kChain = true;  // residuals may have been written by this launch: coherent loads
+  static constexpr bool kPair = false;
 };
 struct ChainParams {
   alignas(64) CUtensorMap tm[TKB_CHAIN_MAX_SEG];   // A operand (im2col-mode or tiled)

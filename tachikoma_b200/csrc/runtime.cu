@@ -850,7 +850,7 @@ static void plan_conv(Planner& P, int nid, bool composite) {
   const bool tc_ok = P.rt->conv_impl != "simt" && g.groups == 1 && all_zero(ci.zp_w) &&
                      (g.zp_a == 0 || ci.bias_eid < 0) && M >= 1;
   const bool force_tc = P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" ||
-                        P.rt->conv_impl == "tc_nochain" || P.rt->conv_impl.rfind("tc_chain", 0) == 0;
+                        P.rt->conv_impl == "tc_nochain" || P.rt->conv_impl == "tc_pair" || P.rt->conv_impl.rfind("tc_chain", 0) == 0;
   const bool use_tc = tc_ok && (force_tc || M * g.O >= 4096);
   // "Kernel view" of the convolution.  A few-channel convolution whose input still lives in logical NCHW
   // form (the network stem) is rewritten as a 1 x KW convolution over the vertically unfolded tensor
@@ -936,7 +936,17 @@ static void plan_conv(Planner& P, int nid, bool composite) {
       probe.e = epi;
       chain = tc_chain_supported(probe, chain_bn);
     }
-    bool halo = !chain && implicit && ta.f.enabled && P.rt->conv_impl != "tc_im2col" && tc_halo_supported(g, g.O);
+    // cta_group::2 pair kernel (kernels_tc_pair.cu): opt-in (conv_impl = tc_pair) for GEMM-shaped layers with >= 128
+    // output channels; takes precedence over the halo kernel where both apply
+    bool pair = false;
+    if (!chain && P.rt->conv_impl == "tc_pair" && composite && !ci.float_mode && ta.f.enabled && !unfold && !from_nchw &&
+        (direct || implicit) && ci.bias_eid < 0 && g.O % 128 == 0) {
+      TcArgs probe = ta;
+      probe.e = epi;
+      probe.w_packed = 0;
+      pair = tc_pair_supported(probe);
+    }
+    bool halo = !chain && !pair && implicit && ta.f.enabled && P.rt->conv_impl != "tc_im2col" && tc_halo_supported(g, g.O);
     if (halo) ta.implicit = 3;
     // Stride-2 stem over the unfolded tensor: two horizontally adjacent 32-byte pixels of X3 form one 64-byte
     // "pair pixel", output column q reads pair pixels q .. q + ceil(KW/2) - 1: a stride-1 1 x ceil(KW/2)
@@ -959,7 +969,10 @@ static void plan_conv(Planner& P, int nid, bool composite) {
       }
     }
     const int Kw = ta.K;  // row length of wp
-    {  // constant weights: pre-tile into the swizzled shared-memory image (one bulk copy per tile at run time)
+    if (pair) {  // the pair kernel reads the plain K-major weight matrix through a tensor map (half of the rows per CTA)
+      ta.w = P.dev_upload(wp.data(), wp.size());
+      ta.w_packed = 0;
+    } else {  // constant weights: pre-tile into the swizzled shared-memory image (one bulk copy per tile at run time)
       if (chain) { ta.pack_bn = chain_bn; ta.pack_bk = tc_chain_bk(ta); }
       else tc_tile_config(ta, &ta.pack_bn, &ta.pack_bk);
       std::vector<uint8_t> packed(tc_pack_weights(wp.data(), g.O, Kw, ta.pack_bn, ta.pack_bk, nullptr));
@@ -977,7 +990,7 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     if (unfold) scratch_off = P.arena_alloc((long long)g.N * g.OH * (g.W + g.pl + g.pr) * 32 + 256);
     else if (!direct && !implicit) scratch_off = P.arena_alloc(M * Kp);
     snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 %s M=%lld N=%d K=%d (%dx%d s%d p%d) epi=%s", n.name.c_str(),
-             direct ? "GEMM" : (unfold ? (halo ? "halo-reuse conv over pixel pairs of the vertically unfolded NCHW input" : "conv as windowed-row GEMM over vertically unfolded NCHW input") : halo ? "halo-reuse conv (TMA patch, resident weights)" : implicit ? "implicit-GEMM conv (TMA im2col)" : (from_nchw ? "GEMM + explicit im2col from NCHW" : "GEMM + explicit im2col")), M, g.O, Kp, g.KH,
+             pair ? (direct ? "cta_group::2 pair GEMM" : "cta_group::2 pair implicit-GEMM conv (TMA im2col)") : direct ? "GEMM" : (unfold ? (halo ? "halo-reuse conv over pixel pairs of the vertically unfolded NCHW input" : "conv as windowed-row GEMM over vertically unfolded NCHW input") : halo ? "halo-reuse conv (TMA patch, resident weights)" : implicit ? "implicit-GEMM conv (TMA im2col)" : (from_nchw ? "GEMM + explicit im2col from NCHW" : "GEMM + explicit im2col")), M, g.O, Kp, g.KH,
              g.KW, g.sh, g.pt, ta.f.enabled ? "fast" : (epi.mode == kEpiInt ? "int" : (epi.mode == kEpiFloat ? "float" : "raw")));
     if (chain) {
       ChainCand cc;
@@ -1011,7 +1024,7 @@ static void plan_conv(Planner& P, int nid, bool composite) {
       }
       t.y = c.ptr(y_eid, phys);
       c.tc_mark();
-      if (launch_tc(t, c.s) != 0) fail("tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+      if ((pair ? launch_tc_pair(t, c.s) : launch_tc(t, c.s)) != 0) fail("tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
       c.tc_mark();
     });
   } else if (P.rt->conv_impl != "simt" && phys == kNHWC && Cg == 1 && all_zero(ci.zp_w) && dwconv_nhwc_supported(g)) {
@@ -1106,7 +1119,7 @@ static void plan_dense(Planner& P, int nid, bool composite) {
   const int bias_eid = ci.bias_eid, sum_eid = ci.sum_eid, xd = X.dtype, wd = Wt.dtype;
   const bool foldable = zpx == 0 || (Wt.is_const && bias_eid < 0);
   const bool use_tc = P.rt->conv_impl != "simt" && tc_gemm_supported((int)M, N, K) && zpw == 0 && foldable &&
-                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_nochain" || P.rt->conv_impl.rfind("tc_chain", 0) == 0 || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" || M * N >= 4096);
+                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_nochain" || P.rt->conv_impl.rfind("tc_chain", 0) == 0 || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" || P.rt->conv_impl == "tc_pair" || M * N >= 4096);
   char desc[256];
   if (use_tc) {
     std::vector<int32_t> bias2;
@@ -1212,7 +1225,7 @@ static void plan_batch_matmul(Planner& P, int nid) {
   init_epi(epi);
   const int xd = X.dtype, wd = Wt.dtype;
   const bool use_tc = P.rt->conv_impl != "simt" && tc_gemm_supported(M, N, K) && zpx == 0 && zpw == 0 &&
-                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_nochain" || P.rt->conv_impl.rfind("tc_chain", 0) == 0 || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" || (long long)B * M * N >= 4096);
+                      (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_nochain" || P.rt->conv_impl.rfind("tc_chain", 0) == 0 || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" || P.rt->conv_impl == "tc_pair" || (long long)B * M * N >= 4096);
   char desc[256];
   snprintf(desc, sizeof(desc), "qnn.batch_matmul -> %s B=%d M=%d N=%d K=%d", use_tc ? "tcgen05 i8 GEMM" : "CUDA-core GEMM", B, M, N, K);
   P.add_step(desc, [=](RunCtx& c) {
@@ -2384,8 +2397,8 @@ int tkb_set_option(tkb_handle h, const char* key, const char* value) {
   const std::string k = key, v = value;
   if (k == "conv_impl") {
     if (v != "auto" && v != "simt" && v != "tc" && v != "tc_explicit" && v != "tc_im2col" && v != "tc_nochain" && v != "tc_chain_all" &&
-        v != "tc_chain_siblings" && v != "tc_chain_split")
-      fail("conv_impl must be auto|simt|tc|tc_nochain|tc_chain_all|tc_chain_siblings|tc_chain_split|tc_explicit|tc_im2col");
+        v != "tc_chain_siblings" && v != "tc_chain_split" && v != "tc_pair")
+      fail("conv_impl must be auto|simt|tc|tc_nochain|tc_chain_all|tc_chain_siblings|tc_chain_split|tc_explicit|tc_im2col|tc_pair");
     if (h->initialized && v != h->conv_impl) {
       // Re-planning is a configuration step like tkb_init: no run may be in flight.  The arena layout and every
       // uploaded / repacked constant belong to the old plan: drop the workspaces (streams and events included) and

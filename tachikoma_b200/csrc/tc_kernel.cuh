@@ -53,6 +53,7 @@ struct TcKernelParams {
   EpiParams e;            // generic epilogue (any rounding / compute dtype / float mode / raw int32)
   FastEpi f;              // host-folded fixed-point epilogue (default QNN configuration)
   static constexpr bool kChain = false;  // single-layer launch: the residual was written by an EARLIER kernel (ld.global.nc is safe)
+  static constexpr bool kPair = false;   // true in the cta_group::2 kernel: accumulator stages are released to the LEADER CTA's barrier
 };
 
 // Device timeline of CTA 0 (TKB_TIMELINE=1, tools/conv_probe.py): slot -> clock64.  0 entry, 1 prologue done,
@@ -305,6 +306,19 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const P&
   }
 }
 
+// Hand an accumulator stage back to the MMA issuer.  In the cta_group::2 kernel the issuer lives in the pair's leader CTA
+// (rank 0): both CTAs' epilogue warps arrive on ITS barrier, through the cluster address space, with cluster-scope release.
+template <class P>
+__device__ __forceinline__ void acc_release(uint64_t* bar) {
+  if constexpr (P::kPair) {
+    uint32_t ra;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(ra) : "r"(smem_u32(bar)));
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(ra) : "memory");
+  } else {
+    mbar_arrive(bar);
+  }
+}
+
 // Drain one accumulator stage: the calling epilogue warp owns TMEM lanes 32*q .. +31 and columns
 // [cbeg0, cbeg0 + cspan) of the tile; `row` is the output row (pixel) of this lane.
 template <int BN, int MODE, bool AL8 = false, class P = TcKernelParams>
@@ -328,13 +342,13 @@ __device__ __forceinline__ void epi_drain_tile(const P& p, uint32_t tmem_base, u
   if (cbeg >= cend) {  // nothing to drain for this warp (ragged N tail): just release the stage
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) mbar_arrive(&tempty[as]);
+    if (lane == 0) acc_release<P>(&tempty[as]);
     return;
   }
   if (p.dbg & 1) {
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) mbar_arrive(&tempty[as]);
+    if (lane == 0) acc_release<P>(&tempty[as]);
     return;
   }
   uint32_t ra[32], rb[32];
@@ -347,7 +361,7 @@ __device__ __forceinline__ void epi_drain_tile(const P& p, uint32_t tmem_base, u
     else {  // all TMEM reads of this warp are complete: hand the accumulator stage back to the MMA warp
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[as]);
+      if (lane == 0) acc_release<P>(&tempty[as]);
     }
     epilogue_chunk<MODE, AL8, P>(ra, p, tab_base + c * 16, row_valid, min(32, cend - c), n0 + c, row_off + n0 + c, drow, vec_ok);
     if (!more_b) break;
@@ -357,7 +371,7 @@ __device__ __forceinline__ void epi_drain_tile(const P& p, uint32_t tmem_base, u
     else {
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[as]);
+      if (lane == 0) acc_release<P>(&tempty[as]);
     }
     epilogue_chunk<MODE, AL8, P>(rb, p, tab_base + (c + 32) * 16, row_valid, min(32, cend - c - 32), n0 + c + 32,
                          row_off + n0 + c + 32, drow, vec_ok);

@@ -953,3 +953,45 @@ def test_randomized_chain_sweep(seed):
         if impl == "tc":
             _, recs = interp.run_json(js, consts, xs, want_trace=True)
             assert mod.trace_blob() == interp.save_ndarray_list(recs)
+
+
+# ---- cta_group::2 pair kernel (kernels_tc_pair.cu), opt-in through conv_impl = tc_pair ----------------------------
+PAIR_CASES = {
+    # name: (N, C, H, O, k, stride, pad, zp_in, with_sum)
+    "l3_3x3": (2, 256, 14, 256, 3, 1, 1, 0, False),
+    "l3_3x3_sum": (3, 256, 14, 256, 3, 1, 1, 0, True),
+    "l2_3x3_bn128": (4, 128, 28, 128, 3, 1, 1, 0, True),
+    "l4_3x3_partial_pair": (2, 512, 7, 512, 3, 1, 1, 0, False),
+    "l3_1x1_gemm": (2, 256, 14, 512, 1, 1, 0, 0, False),
+    "l3_3x3_s2": (2, 128, 28, 256, 3, 2, 1, 0, False),
+    "l3_1x1_s2": (2, 128, 28, 256, 1, 2, 0, 0, True),
+    "zp_border": (2, 128, 12, 128, 3, 1, 1, 7, False),
+    "many_tiles": (16, 128, 28, 256, 3, 1, 1, 0, True),
+}
+
+
+@pytest.mark.parametrize("name", list(PAIR_CASES))
+def test_pair_kernel_vs_oracle(name):
+    n, c, h, o, k, st, pad, zp, with_sum = PAIR_CASES[name]
+    rng = np.random.default_rng(11)
+    x = rng.integers(0, 256, (n, c, h, h)).astype("uint8")
+    w = rng.integers(-127, 128, (o, c, k, k)).astype("int8")
+    sw = (rng.uniform(0.5, 1.5, o) / (127 * np.sqrt(k * k * c))).astype("float32")
+    v = R.var("in_0", x.shape, "uint8")
+    # a leading max pool keeps the convolution's input channels-last inside the runtime (no boundary conversion in between)
+    e = R.max_pool2d(v, (1, 1), (1, 1), (0, 0))
+    e = R.qnn_conv2d(e, R.const(w), zp, 0, np.float32(0.02), R.const(sw), (k, k), o, strides=(st, st), padding=(pad, pad))
+    e = R.bias_add(e, R.const(rng.integers(-4000, 4000, o).astype("int32")))
+    e = R.qnn_requantize(e, R.const((np.float32(0.02) * sw).astype("float32")), 0, np.float32(0.03), 0, axis=1, out_dtype="int32")
+    e = R.cast(R.clip(e, 0.0, 255.0), "uint8")
+    ins, params = {"in_0": x}, [v]
+    if with_sum:
+        r = R.var("in_1", e.shape, "uint8")
+        ins["in_1"] = rng.integers(0, 256, e.shape).astype("uint8")
+        params.append(r)
+        e = R.clip(R.qnn_add(e, r, np.float32(0.03), 0, np.float32(0.05), 3, np.float32(0.04), 0), 0.0, 255.0)
+    f = R.Function(params, e)
+    want, _ = interp.run_expr(f, ins)
+    out, mod, _ = run_gpu(f, ins, conv_impl="tc_pair", trace=True)
+    assert "cta_group::2" in mod.plan_summary(), mod.plan_summary()
+    np.testing.assert_equal(out, want)

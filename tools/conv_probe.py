@@ -25,7 +25,7 @@ e2 = R.cast(R.clip(e2, 0.0, 255.0), "uint8")
 part = T.partition_for_tachikoma(R.Function([d2], e2))
 sym, js, names, consts = T.serialize(part)
 mod = RT.TachikomaJSONRuntime(sym, js, names)
-mod.set_option("conv_impl", "tc")
+mod.set_option("conv_impl", os.environ.get("TKB_IMPL", "tc"))
 mod.init(consts)
 xd = torch.from_numpy(np.ascontiguousarray(x.transpose(0, 2, 3, 1))).cuda()
 out = torch.empty(tuple(part.body.shape), dtype=torch.uint8, device="cuda")

@@ -91,7 +91,9 @@ const char* tkb_last_error(void);
  *                           kernel: TMA-im2col implicit GEMM) | "tc_explicit" (as "tc" with an explicit im2col
  *                           matrix) | "tc_chain_all" / "tc_chain_siblings" / "tc_chain_split" (as "tc" with consecutive
  *                           layers merged into chained persistent launches, csrc/kernels_tc_chain.cu: dependent layers
- *                           too / layers reading the same activation / every layer, a launch per dependency) -- all
+ *                           too / layers reading the same activation / every layer, a launch per dependency) |
+ *                           "tc_pair" (as "tc" with the cta_group::2 pair kernel, csrc/kernels_tc_pair.cu, for layers with
+ *                           a multiple of 128 output channels) -- all
  *                           routes produce identical bits, everything after "tc" exists for A/B tests;
  *             "time_tc"   = "0"|"1" (bracket every tcgen05 launch with CUDA events, see tkb_tc_time). */
 int tkb_set_option(tkb_handle h, const char* key, const char* value);

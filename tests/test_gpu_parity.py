@@ -474,6 +474,19 @@ def test_bert_base_layer_full_size():
     np.testing.assert_equal(out2, ref)
 
 
+def test_bert_base_all_twelve_layers():
+    """The whole BERT-base encoder stack (12 layers at seq 128, hidden 768, 12 heads, FFN 3072; two sequences): 72 dense and
+    24 batch_matmul launches on tcgen05, output and trace byte for byte the oracle's (bench.py times ONE layer and says
+    so in its workload string)."""
+    func = models.bert_encoder(batch=2, layers=12)
+    x = models.synthetic_input("bert_encoder", 2)
+    out, mod, (js, consts, ins) = run_gpu(func, {"data": x}, conv_impl="tc", trace=True)
+    assert mod.plan_summary().count("tcgen05") >= 96
+    want, recs = interp.run_json(js, consts, ins, want_trace=True)
+    np.testing.assert_equal(out, want[0])
+    assert mod.trace_blob() == interp.save_ndarray_list(recs)
+
+
 POOL_CASES = [
     # (n, h, w, c, k, stride, pad, dtype)
     (2, 16, 16, 64, 3, 2, 1, "uint8"), (3, 13, 9, 32, 3, 2, 1, "uint8"), (1, 7, 7, 16, 3, 2, 1, "int8"),

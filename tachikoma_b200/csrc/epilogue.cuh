@@ -232,6 +232,8 @@ struct FastSide {        // q' = hi32(int64(q << ls) * M + C) >> s1   (host-norm
 struct FastEpi {
   int enabled;
   const int4* tabA;      // [N] {M, T - 32, C_lo, C_hi}
+  const int4* tab_host;  // HOST copy of tabA (never dereferenced on the device): kernels with <= 64 output channels take the
+                         // table through their parameter block (constant bank) instead of shared memory
   int32_t lo, hi;        // merged clamp of the requantize out_dtype and the relay clip
   int has_sum;
   uint32_t sum_xor;      // 0x80808080 for an int8 residual (b = (u ^ 0x80) - 128, the -128 is folded into rhs.C)

@@ -23,7 +23,7 @@ static constexpr int MAX_A_STAGES = 8;
 // chunk, fully unrolled -- a straight line of UTCIMMAs with one uniform add per descriptor.  (The run-time loop
 // costs ~110 cycles per MMA on the single issuing thread -- LDCU / R2UR / UIMAD chains between the MMAs -- which
 // for N = 64 tiles is 3x the tensor pipe's own time per instruction; unrolled it is ~57.)
-template <int BN, int MODE, int KH_, int KW_, int BK_, bool SPLIT>
+template <int BN, int MODE, int KH_, int KW_, int BK_, bool SPLIT, bool CTAB = false>
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ TcKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -161,9 +161,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
                         (p.sum == nullptr || (((uintptr_t)p.sum) & 15) == 0) &&
                         (p.e.out_dtype == kU8 || p.e.out_dtype == kI8);
     const uint32_t tab_base = smem_u32(tab_s);
-    for (int i = et; i < BN; i += EPI_THREADS)
-      sts128(tab_base + i * 16, i < p.N ? __ldg(p.f.tabA + i) : make_int4(0, 0, 0, 0));
-    epi_bar_sync();
+    if constexpr (!CTAB) {  // CTAB: the constants are kernel parameters (p.ctab), nothing to stage
+      for (int i = et; i < BN; i += EPI_THREADS)
+        sts128(tab_base + i * 16, i < p.N ? __ldg(p.f.tabA + i) : make_int4(0, 0, 0, 0));
+      epi_bar_sync();
+    }
     const int m = q * 32 + lane;
     const int prow = m / p.hWp, pcol = m - prow * p.hWp;
     const bool slot_valid = prow < p.hR && pcol < p.OW;
@@ -174,7 +176,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
       const int n = tile / p.hTpi, oh = (tile % p.hTpi) * p.hR + prow;
       const bool row_valid = slot_valid && oh < p.OH;
       const int row = (n * p.OH + oh) * p.OW + pcol;
-      epi_drain_tile<BN, MODE>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, 0, 0, tab_base, vec_ok, tempty, tfull);
+      epi_drain_tile<BN, MODE, false, TcKernelParams, CTAB>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, 0, 0, tab_base, vec_ok,
+                                                            tempty, tfull);
       TKB_TL_IF(lt == 0 && warp == 2 && lane == 0, p, 7);
     }
     TKB_TL_IF(warp == 2 && lane == 0, p, 8);
@@ -242,11 +245,11 @@ void tc_halo_tile_config(const ConvGeom& g, int N, int* bn, int* bk) {
   if (halo_config(g, N, &c)) { *bn = c.bn; *bk = c.bk; }
 }
 
-template <int BN, int MODE, int KH_, int KW_, int BK_, bool SPLIT>
+template <int BN, int MODE, int KH_, int KW_, int BK_, bool SPLIT, bool CTAB = false>
 static int launch_halo_ts(const CUtensorMap& ta, TcKernelParams& p, int smem, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(tc_halo_kernel<BN, MODE, KH_, KW_, BK_, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
+    if (cudaFuncSetAttribute(tc_halo_kernel<BN, MODE, KH_, KW_, BK_, SPLIT, CTAB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
         cudaSuccess)
       return -1;
     attr_set = true;
@@ -265,7 +268,7 @@ static int launch_halo_ts(const CUtensorMap& ta, TcKernelParams& p, int smem, cu
   cfg.numAttrs = getenv("TKB_NO_PDL") ? 0 : 1;
   p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
   p.tl = timeline_buf();
-  if (cudaLaunchKernelEx(&cfg, tc_halo_kernel<BN, MODE, KH_, KW_, BK_, SPLIT>, ta, p) != cudaSuccess) return -1;
+  if (cudaLaunchKernelEx(&cfg, tc_halo_kernel<BN, MODE, KH_, KW_, BK_, SPLIT, CTAB>, ta, p) != cudaSuccess) return -1;
   timeline_print("tc_halo", p.tl, s);
   ++g_launches;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
@@ -276,7 +279,16 @@ template <int BN, int MODE, int KH_, int KW_, int BK_>
 static int launch_halo_t(const CUtensorMap& ta, TcKernelParams& p, int smem, cudaStream_t s) {
   if constexpr (BN == 64) {
     const long long tiles = (long long)(p.M / (p.OH * p.OW)) * p.hTpi;
-    if (tiles >= 2LL * num_sms()) return launch_halo_ts<BN, MODE, KH_, KW_, BK_, true>(ta, p, smem, s);
+    if (tiles >= 2LL * num_sms()) {
+      // exactly 64 output channels: per-channel constants through the parameter block (profiles/r02_notes.md section 7:
+      // the table's broadcast LDS.128 were half of the shared-memory data pipe's load in these kernels)
+      static const bool ctab_off = getenv("TKB_NO_CTAB") != nullptr;
+      if (p.N == 64 && p.f.tab_host != nullptr && !ctab_off) {
+        memcpy(p.ctab, p.f.tab_host, sizeof(p.ctab));
+        return launch_halo_ts<BN, MODE, KH_, KW_, BK_, true, true>(ta, p, smem, s);
+      }
+      return launch_halo_ts<BN, MODE, KH_, KW_, BK_, true>(ta, p, smem, s);
+    }
   }
   return launch_halo_ts<BN, MODE, KH_, KW_, BK_, false>(ta, p, smem, s);
 }

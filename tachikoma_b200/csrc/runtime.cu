@@ -19,6 +19,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <deque>
 #include <functional>
 #include <memory>
 #include <mutex>
@@ -141,6 +142,7 @@ struct tkb_runtime {
   std::vector<tkb::Entry> ent;
   std::vector<tkb::Step> steps;
   std::vector<void*> dev_allocs;  // freed in tkb_free
+  std::deque<std::vector<int32_t>> host_tabs;  // host copies of the folded epilogue tables (FastEpi.tab_host points into these)
   long long arena_bytes = 0;
   bool initialized = false;
   std::mutex init_mu, ws_mu;
@@ -674,6 +676,8 @@ static bool build_fast_epi(Planner& P, const CompositeInfo& ci, const std::vecto
   out->sat = has_sum ? 0 : sat_code(out_dtype, lo, hi);
   out->sum_sat = has_sum ? sat_code(out_dtype, out->sum_lo, out->sum_hi) : 0;
   out->tabA = (const int4*)P.dev_upload(tab.data(), tab.size() * 4);
+  P.rt->host_tabs.emplace_back(tab.begin(), tab.end());
+  out->tab_host = (const int4*)P.rt->host_tabs.back().data();
   out->enabled = 1;
   return true;
 }
@@ -2299,6 +2303,7 @@ static void destroy_workspaces(tkb_handle h) {
 static void free_plan_allocs(tkb_handle h) {
   for (void* p : h->dev_allocs) cudaFree(p);
   h->dev_allocs.clear();
+  h->host_tabs.clear();
   for (auto& e : h->ent) e.dev_const = nullptr;  // uploaded constants were part of dev_allocs
 }
 

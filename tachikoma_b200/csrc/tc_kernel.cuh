@@ -52,6 +52,8 @@ struct TcKernelParams {
   int dbg;                // timing experiments only (TKB_DBG): 1 = no epilogue work, 2 = no B loads, 4 = no A loads
   EpiParams e;            // generic epilogue (any rounding / compute dtype / float mode / raw int32)
   FastEpi f;              // host-folded fixed-point epilogue (default QNN configuration)
+  int4 ctab[64];          // copy of f.tabA for layers with exactly 64 output channels: read as constant-bank operands by the
+                          // CTAB epilogue (no shared-memory traffic for the per-channel constants)
   static constexpr bool kChain = false;  // single-layer launch: the residual was written by an EARLIER kernel (ld.global.nc is safe)
   static constexpr bool kPair = false;   // true in the cta_group::2 kernel: accumulator stages are released to the LEADER CTA's barrier
 };
@@ -217,7 +219,15 @@ static __device__ __noinline__ void epi_slow_elem(int32_t acc, int col, long lon
 
 // 32 columns of one output row.  r: raw TMEM accumulators; ncols: valid columns (1..32); col0: absolute
 // first column; idx0: linear output index of (row, col0); tab_addr: shared address of this chunk's table.
-template <int MODE, bool AL8 = false, class P = TcKernelParams>
+// Per-channel constants {M, T - 32, C_lo, C_hi} of column j of the chunk: from the shared-memory table, or (CT >= 0:
+// compile-time first column of the chunk) straight from the kernel parameters, i.e. as constant-bank operands.
+template <int CT, class P>
+__device__ __forceinline__ int4 tab_entry(const P& p, uint32_t tab_addr, int j) {
+  if constexpr (CT >= 0) return p.ctab[CT + j];
+  else return lds128(tab_addr + j * 16);
+}
+
+template <int MODE, bool AL8 = false, class P = TcKernelParams, int CT = -1>
 __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const P& p, uint32_t tab_addr,
                                                bool row_valid, int ncols, int col0, long long idx0,
                                                const int32_t* drow, bool vec_ok) {
@@ -261,7 +271,7 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const P&
 #pragma unroll
         for (int jj = 0; jj < 4; ++jj) {
           const int j = 4 * i + jj;
-          int32_t y = fast_requant_raw((int32_t)r[j], lds128(tab_addr + j * 16));
+          int32_t y = fast_requant_raw((int32_t)r[j], tab_entry<CT>(p, tab_addr, j));
           if constexpr (mode_is_sum(MODE)) {
             y = min(max(y, f.lo), f.hi);
             const int32_t b = (int32_t)((sraw[i] >> (8 * jj)) & 0xFFu);
@@ -283,7 +293,7 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const P&
 #pragma unroll
         for (int jj = 0; jj < 4; ++jj) {
           const int j = 4 * i + jj;
-          int32_t y = fast_requant((int32_t)(r[j] + (uint32_t)dl[jj]), lds128(tab_addr + j * 16), f.lo, f.hi);
+          int32_t y = fast_requant((int32_t)(r[j] + (uint32_t)dl[jj]), tab_entry<CT>(p, tab_addr, j), f.lo, f.hi);
           if constexpr (mode_is_sum(MODE)) {
             const int32_t b = (int32_t)((sraw[i] >> (8 * jj)) & 0xFFu);
             y = min(max(fast_side(y, f.lhs) + fast_side(b, f.rhs), f.sum_lo), f.sum_hi);
@@ -321,7 +331,7 @@ __device__ __forceinline__ void acc_release(uint64_t* bar) {
 
 // Drain one accumulator stage: the calling epilogue warp owns TMEM lanes 32*q .. +31 and columns
 // [cbeg0, cbeg0 + cspan) of the tile; `row` is the output row (pixel) of this lane.
-template <int BN, int MODE, bool AL8 = false, class P = TcKernelParams>
+template <int BN, int MODE, bool AL8 = false, class P = TcKernelParams, bool CTAB = false>
 __device__ __forceinline__ void epi_drain_tile(const P& p, uint32_t tmem_base, uint32_t lt, int q, int cbeg0, int cspan,
                                                int lane, int row, bool row_valid, int b, int n0, uint32_t tab_base,
                                                bool vec_ok, uint64_t* tempty, uint64_t* tfull) {
@@ -352,6 +362,20 @@ __device__ __forceinline__ void epi_drain_tile(const P& p, uint32_t tmem_base, u
     return;
   }
   uint32_t ra[32], rb[32];
+  if constexpr (CTAB) {
+    // 64-column tile owned entirely by this warp, N == 64: both chunks with compile-time column numbers
+    static_assert(BN == 64, "CTAB epilogue: 64-column tiles only");
+    tmem_ld32(t_addr, ra);
+    tmem_ld_wait32(ra);
+    tmem_ld32(t_addr + 32, rb);
+    epilogue_chunk<MODE, AL8, P, 0>(ra, p, 0, row_valid, 32, n0, row_off + n0, drow, vec_ok);
+    tmem_ld_wait32(rb);
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) acc_release<P>(&tempty[as]);
+    epilogue_chunk<MODE, AL8, P, 32>(rb, p, 0, row_valid, 32, n0 + 32, row_off + n0 + 32, drow, vec_ok);
+    return;
+  }
   tmem_ld32(t_addr + cbeg, ra);
 #pragma unroll 1
   for (int c = cbeg;; c += 64) {

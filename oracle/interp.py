@@ -169,6 +169,18 @@ def qnn_add(a, b, sa, zpa, sb, zpb, so, zpo):
     return out
 
 
+def qnn_subtract(a, b, sa, zpa, sb, zpb, so, zpo):
+    """src/relay/qnn/op/subtract.cc:40-93."""
+    a, b = np.ascontiguousarray(a), np.ascontiguousarray(b)
+    assert a.shape == b.shape and a.dtype == b.dtype
+    out = np.empty_like(a)
+    f = lambda v: ctypes.c_float(float(np.float32(np.asarray(v).reshape(-1)[0])))
+    z = lambda v: ctypes.c_int32(int(np.asarray(v).reshape(-1)[0]))
+    lib().tko_qnn_subtract(_p(a), _p(b), DT[str(a.dtype)], ctypes.c_int64(a.size), f(sa), z(zpa), f(sb), z(zpb),
+                           f(so), z(zpo), _p(out))
+    return out
+
+
 def _sc(v):
     return np.float32(np.asarray(v, dtype=np.float32).reshape(-1)[0])
 
@@ -355,6 +367,8 @@ def eval_op(op, attrs, args):
         return qnn_add(*args[:8])
     if op == "qnn.mul":
         return qnn_mul(*args[:8])
+    if op == "qnn.subtract":
+        return qnn_subtract(*args[:8])
     if op == "qnn.concatenate":
         n = int(attrs["num_inputs"])
         return qnn_concatenate(args[:n], args[n:2 * n], args[2 * n:3 * n], args[3 * n], args[3 * n + 1], int(attrs["axis"]))

@@ -309,6 +309,26 @@ void tko_qnn_add(const void* a, const void* b, int dtype, int64_t n, float sa, i
   }
 }
 
+/* qnn.subtract, src/relay/qnn/op/subtract.cc:40-93: both sides through RequantizeOrUpcast to the output qparams,
+ * Q_a' - Q_b' in int32, + zp_out (skipped when it is zero: adding zero changes nothing), saturate to the dtype. */
+void tko_qnn_subtract(const void* a, const void* b, int dtype, int64_t n, float sa, int32_t zpa,
+                      float sb, int32_t zpb, float so, int32_t zpo, void* out) {
+  int32_t Ma, Sa, Mb, Sb;
+  tko_fixed_point_multiplier_shift((double)sa / (double)so, &Ma, &Sa);
+  tko_fixed_point_multiplier_shift((double)sb / (double)so, &Mb, &Sb);
+  int64_t lo, hi;
+  dtype_range(dtype, &lo, &hi);
+#pragma omp parallel for schedule(static) if (n > 65536)
+  for (int64_t i = 0; i < n; ++i) {
+    int32_t qa = requantize_or_upcast((int32_t)load_int(a, dtype, i), sa, zpa, so, zpo, Ma, Sa);
+    int32_t qb = requantize_or_upcast((int32_t)load_int(b, dtype, i), sb, zpb, so, zpo, Mb, Sb);
+    int64_t y = wrap32((int64_t)wrap32((int64_t)qa - qb) + zpo);
+    if (y < lo) y = lo;
+    if (y > hi) y = hi;
+    store_int(out, dtype, i, y);
+  }
+}
+
 /* nn.max_pool2d / nn.avg_pool2d on integer tensors: include/tvm/topi/nn/pooling.h:384-389 (adaptive,
  * used by global pooling: is_avg == 2), :585-650 (windowed: is_avg == 1).  The window sum is reduced
  * IN THE TENSOR DTYPE (tvm::sum(temp(indices), daxis), :599; int32 after the frontend's upcast,

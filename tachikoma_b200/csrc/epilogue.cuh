@@ -46,6 +46,7 @@ struct EpiParams {
   RqParams lhs, rhs;  // RequantizeOrUpcast of each side; skip flags inside
   int lhs_identity, rhs_identity;
   int32_t sum_zp_out, sum_qmin, sum_qmax, sum_clip_lo, sum_clip_hi;
+  int sum_sub;  // 1: qnn.subtract (lhs' - rhs' + zp_out, subtract.cc:40-93) instead of qnn.add (lhs' + rhs' - zp_out)
   // float (oneDNN-style) mode
   const float* o_scl;  // [N] or [1]
   int n_oscl;
@@ -178,7 +179,8 @@ __device__ __forceinline__ void store_from_i32(void* p, int dt, long long i, int
 __device__ __forceinline__ int32_t qnn_add_one(int32_t a, int32_t b, int c, const EpiParams& e) {
   int32_t qa = e.lhs_identity ? a : requantize_one(a, c, e.lhs);
   int32_t qb = e.rhs_identity ? b : requantize_one(b, c, e.rhs);
-  int32_t y = (int32_t)((uint32_t)qa + (uint32_t)qb - (uint32_t)e.sum_zp_out);
+  int32_t y = e.sum_sub ? (int32_t)((uint32_t)qa - (uint32_t)qb + (uint32_t)e.sum_zp_out)
+                        : (int32_t)((uint32_t)qa + (uint32_t)qb - (uint32_t)e.sum_zp_out);
   return min(max(y, e.sum_qmin), e.sum_qmax);
 }
 

@@ -495,7 +495,7 @@ __global__ void __launch_bounds__(256) qnn_add_lut_kernel(const uint4* __restric
     const int32_t v = dtype == kU8 ? i : (int32_t)(int8_t)i;
     tl[i] = e.lhs_identity ? v : requantize_one(v, 0, e.lhs);
     const int32_t qb = e.rhs_identity ? v : requantize_one(v, 0, e.rhs);
-    tr[i] = (int32_t)((uint32_t)qb - (uint32_t)e.sum_zp_out);
+    tr[i] = e.sum_sub ? (int32_t)((uint32_t)e.sum_zp_out - (uint32_t)qb) : (int32_t)((uint32_t)qb - (uint32_t)e.sum_zp_out);
   }
   __syncthreads();
   for (long long i = blockIdx.x * 256LL + threadIdx.x; i < nv; i += (long long)gridDim.x * 256) {

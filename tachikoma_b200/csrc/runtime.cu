@@ -1298,7 +1298,8 @@ static void plan_qnn_add(Planner& P, int nid) {
   const GNode& n = P.g.nodes[nid];
   const int a_eid = (int)P.g.eid(n.inputs[0]), b_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
   const Entry& A = P.ent[a_eid];
-  if (A.shape != P.ent[b_eid].shape || A.dtype != P.ent[b_eid].dtype) fail("Unsupported op: qnn.add with broadcasting operands");
+  const bool sub = n.name == "qnn.subtract";  // subtract.cc:40-93: the same two requantizes, lhs' - rhs' + zp_out
+  if (A.shape != P.ent[b_eid].shape || A.dtype != P.ent[b_eid].dtype) fail("Unsupported op: %s with broadcasting operands", n.name.c_str());
   const int phys = (P.preferred(a_eid) == kNHWC || P.preferred(b_eid) == kNHWC) && A.shape.size() == 4 &&
                            !P.ent[P.root(a_eid)].is_const && !P.ent[P.root(b_eid)].is_const ? kNHWC : kLogical;
   EpiParams e;
@@ -1307,13 +1308,14 @@ static void plan_qnn_add(Planner& P, int nid) {
             P.cfloats((int)P.g.eid(n.inputs[4]), "rhs_scale")[0], P.cints((int)P.g.eid(n.inputs[5]), "rhs_zero_point")[0],
             P.cfloats((int)P.g.eid(n.inputs[6]), "output_scale")[0], P.cints((int)P.g.eid(n.inputs[7]), "output_zero_point")[0],
             A.dtype);
+  e.sum_sub = sub ? 1 : 0;
   P.need(a_eid, phys);
   P.need(b_eid, phys);
   P.produce(y_eid, phys);
   const long long cnt = numel(A.shape);
   const int dt = A.dtype;
   P.rt->hbm_bytes += 3 * A.bytes();
-  P.add_step("qnn.add -> vectorised elementwise kernel", [=](RunCtx& c) {
+  P.add_step(sub ? "qnn.subtract -> vectorised elementwise kernel" : "qnn.add -> vectorised elementwise kernel", [=](RunCtx& c) {
     launch_qnn_add(c.ptr(a_eid, phys), c.ptr(b_eid, phys), c.ptr(y_eid, phys), dt, cnt, e, c.s);
   });
 }
@@ -1835,7 +1837,7 @@ static void build_plan(tkb_runtime* rt) {
     else if (op == "qnn.dense") plan_dense(P, (int)nid, false);
     else if (op == "qnn.batch_matmul") plan_batch_matmul(P, (int)nid);
     else if (op == "qnn.requantize") plan_requantize(P, (int)nid);
-    else if (op == "qnn.add") plan_qnn_add(P, (int)nid);
+    else if (op == "qnn.add" || op == "qnn.subtract") plan_qnn_add(P, (int)nid);
     else if (op == "qnn.mul") plan_qnn_mul(P, (int)nid);
     else if (op == "qnn.quantize") plan_quantize(P, (int)nid, false);
     else if (op == "qnn.dequantize") plan_quantize(P, (int)nid, true);

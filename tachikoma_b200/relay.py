@@ -193,6 +193,16 @@ def qnn_mul(lhs, rhs, lhs_scale, lhs_zero_point, rhs_scale, rhs_zero_point, outp
     return Call("qnn.mul", args, dict(lhs_axis=int(lhs_axis), rhs_axis=int(rhs_axis)), lhs.shape, lhs.dtype)
 
 
+def qnn_subtract(lhs, rhs, lhs_scale, lhs_zero_point, rhs_scale, rhs_zero_point, output_scale,
+                 output_zero_point, lhs_axis=-1, rhs_axis=-1):
+    """tvm.relay.qnn.op.subtract (src/relay/qnn/op/subtract.cc:40-93): both sides requantized to the output qparams,
+    Q_a' - Q_b' + zp_out in int32, saturated to the input dtype."""
+    assert lhs.shape == rhs.shape and lhs.dtype == rhs.dtype
+    args = [lhs, rhs, _c(lhs_scale, "float32"), _c(lhs_zero_point, "int32"), _c(rhs_scale, "float32"),
+            _c(rhs_zero_point, "int32"), _c(output_scale, "float32"), _c(output_zero_point, "int32")]
+    return Call("qnn.subtract", args, dict(lhs_axis=int(lhs_axis), rhs_axis=int(rhs_axis)), lhs.shape, lhs.dtype)
+
+
 def qnn_concatenate(data, input_scales, input_zero_points, output_scale, output_zero_point, axis):
     """tvm.relay.qnn.op.concatenate (src/relay/qnn/op/concatenate.cc:138-213): every input whose (scale, zero point)
     differs from the output's is requantized to them (same dtype), then nn.concatenate.  Arguments of the call: the n

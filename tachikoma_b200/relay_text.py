@@ -313,8 +313,9 @@ def _build(op, a, at):
         return R.qnn_batch_matmul(*a[:6], out_dtype=at.get("out_dtype") or "int32")
     if op == "qnn.requantize":
         return R.qnn_requantize(*a[:5], **_pick(at, "axis", "rounding", "compute_dtype", "out_dtype"))
-    if op in ("qnn.add", "qnn.mul"):
-        return (R.qnn_add if op == "qnn.add" else R.qnn_mul)(*a[:8], **_pick(at, "lhs_axis", "rhs_axis"))
+    if op in ("qnn.add", "qnn.mul", "qnn.subtract"):
+        fn = {"qnn.add": R.qnn_add, "qnn.mul": R.qnn_mul, "qnn.subtract": R.qnn_subtract}[op]
+        return fn(*a[:8], **_pick(at, "lhs_axis", "rhs_axis"))
     if op == "qnn.concatenate":
         return R.qnn_concatenate(a[0], a[1], a[2], a[3], a[4], at["axis"])
     if op == "qnn.quantize":

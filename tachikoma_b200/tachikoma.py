@@ -245,7 +245,7 @@ def _make_composite(m, mode):
 
 #: operators the CUDA runtime executes outside a composite (single-op JSON kernel nodes)
 SUPPORTED_OPS = {
-    "qnn.conv2d", "qnn.dense", "qnn.batch_matmul", "qnn.requantize", "qnn.add", "qnn.mul", "qnn.concatenate",
+    "qnn.conv2d", "qnn.dense", "qnn.batch_matmul", "qnn.requantize", "qnn.add", "qnn.subtract", "qnn.mul", "qnn.concatenate",
     "qnn.quantize", "qnn.dequantize", "qnn.leaky_relu", "reinterpret", "take", "nn.bias_add", "add", "clip",
     "cast", "nn.max_pool2d", "nn.avg_pool2d", "nn.global_avg_pool2d", "nn.pad", "reshape", "nn.batch_flatten",
     "transpose",

@@ -10,7 +10,7 @@ reference test files
     tests/python/relay/test_op_qnn_requantize.py, test_op_qnn_dense.py, test_op_qnn_add.py,
     tests/python/relay/test_op_qnn_batch_matmul.py, test_op_qnn_conv2d.py,
     tests/python/relay/test_op_qnn_mul.py, test_op_qnn_concatenate.py, test_op_qnn_quantize.py, test_op_qnn_dequantize.py,
-    tests/python/relay/test_op_qnn_leaky_relu.py, test_op_qnn_unary_elementwise.py
+    tests/python/relay/test_op_qnn_leaky_relu.py, test_op_qnn_unary_elementwise.py, test_op_qnn_subtract.py
 are then executed unmodified.  Whenever a test compares a QNN graph's output with a golden
 (``np.testing.assert_equal``) the triple (graph, inputs, golden) is captured.  For the conv2d
 property tests the golden is the test's own *reference function* (int32 nn.conv2d over
@@ -38,7 +38,7 @@ FILES = ["test_op_qnn_requantize.py", "test_op_qnn_dense.py", "test_op_qnn_add.p
          "test_op_qnn_batch_matmul.py", "test_op_qnn_conv2d.py",
          # round 2; appended so that the cases above keep their indices and random draws
          "test_op_qnn_mul.py", "test_op_qnn_concatenate.py", "test_op_qnn_quantize.py", "test_op_qnn_dequantize.py",
-         "test_op_qnn_leaky_relu.py", "test_op_qnn_unary_elementwise.py"]
+         "test_op_qnn_leaky_relu.py", "test_op_qnn_unary_elementwise.py", "test_op_qnn_subtract.py"]
 
 CASES, SKIPPED = [], []
 CURRENT = {"name": ""}
@@ -118,6 +118,8 @@ def to_ir(e, memo):
         r = R.qnn_add(*a, **at)
     elif e.op == "qnn.mul":
         r = R.qnn_mul(*a, **at)
+    elif e.op == "qnn.subtract":
+        r = R.qnn_subtract(*a, **at)
     elif e.op == "qnn.concatenate":
         n = at["num_inputs"]
         r = R.qnn_concatenate(a[:n], a[n:2 * n], a[2 * n:3 * n], a[3 * n], a[3 * n + 1], at["axis"])
@@ -387,6 +389,11 @@ def install_shim():
         return S("qnn.mul", [lhs, rhs, lhs_scale, lhs_zero_point, rhs_scale, rhs_zero_point, output_scale,
                              output_zero_point], dict(lhs_axis=lhs_axis, rhs_axis=rhs_axis))
 
+    def q_subtract(lhs, rhs, lhs_scale, lhs_zero_point, rhs_scale, rhs_zero_point, output_scale, output_zero_point,
+                   lhs_axis=-1, rhs_axis=-1):
+        return S("qnn.subtract", [lhs, rhs, lhs_scale, lhs_zero_point, rhs_scale, rhs_zero_point, output_scale,
+                                  output_zero_point], dict(lhs_axis=lhs_axis, rhs_axis=rhs_axis))
+
     def q_concatenate(data, input_scales, input_zero_points, output_scale, output_zero_point, axis):
         if isinstance(data, S):  # a call that yields a tuple (relay.split): not expressible in the mini IR
             raise Unsupported("qnn.concatenate over a tuple-valued call")
@@ -413,7 +420,7 @@ def install_shim():
             return S("qnn." + name, [x, scale, zero_point, output_scale, output_zero_point])
         return make
 
-    qop = types.SimpleNamespace(requantize=q_requantize, leaky_relu=q_leaky_relu,
+    qop = types.SimpleNamespace(requantize=q_requantize, leaky_relu=q_leaky_relu, subtract=q_subtract,
                                 **{k: q_unary(k) for k in ("sqrt", "rsqrt", "exp", "erf", "sigmoid", "hardswish", "tanh",
                                                            "log", "abs")}, dense=q_dense, batch_matmul=q_bmm, add=q_add, mul=q_mul,
                                 concatenate=q_concatenate, quantize=q_quantize, dequantize=q_dequantize,

@@ -1008,3 +1008,18 @@ def test_pair_kernel_vs_oracle(name):
     out, mod, _ = run_gpu(f, ins, conv_impl="tc_pair", trace=True)
     assert "cta_group::2" in mod.plan_summary(), mod.plan_summary()
     np.testing.assert_equal(out, want)
+
+
+@pytest.mark.parametrize("dt", ["uint8", "int8"])
+def test_qnn_subtract_vs_oracle(dt):
+    """qnn.subtract (subtract.cc:40-93) over every pair of byte values, equal and different quantization parameters."""
+    info = np.iinfo(dt)
+    a = np.repeat(np.arange(info.min, info.max + 1), 256).astype(dt).reshape(256, 256)
+    b = np.tile(np.arange(info.min, info.max + 1), 256).astype(dt).reshape(256, 256)
+    for qp in [(0.5, 3, 0.25, 7, 0.3, 5), (0.2, 0, 0.2, 0, 0.2, 0), (0.1, 4, 0.3, 9, 0.1, 4), (0.37, -2 if dt == "int8" else 2, 0.11, 1, 0.5, 0)]:
+        x, y = R.var("in_0", a.shape, dt), R.var("in_1", b.shape, dt)
+        f = R.Function([x, y], R.qnn_subtract(x, y, *qp))
+        want, _ = interp.run_expr(f, {"in_0": a, "in_1": b})
+        out, mod, _ = run_gpu(f, {"in_0": a, "in_1": b}, trace=True)
+        np.testing.assert_equal(out, want)
+        assert "qnn.subtract" in mod.plan_summary()

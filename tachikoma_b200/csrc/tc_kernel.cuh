@@ -235,7 +235,11 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const P&
   // Rows whose window overlaps the padding add their border class's per-channel delta first (runtime.cu border_plan).
   // The fast modes do that inside the hot path (chained launches: a quarter to a half of the pixels of a 14x14 / 7x7
   // feature map are border pixels); the single-layer kernels keep sending those rows through the out-of-line path.
-  const bool hot = MODE != kModeGeneric && ncols == 32 && vec_ok && (drow == nullptr || (P::kChain && mode_is_fast(MODE)));
+  // Ragged chunks (N = 16, 24, 144, ...: MobileNetV2's projection layers) stay on the vector path when the valid columns
+  // are whole store vectors: all 32 values are computed (table entries beyond N are zero) and only the valid 16-byte
+  // (8-byte for AL8 kernels) pieces are stored.  Everything else goes element by element through the out-of-line path.
+  const bool ragged_ok = mode_is_fast(MODE) && ncols > 0 && (AL8 ? (ncols & 7) == 0 : (ncols & 15) == 0);
+  const bool hot = MODE != kModeGeneric && (ncols == 32 || ragged_ok) && vec_ok && (drow == nullptr || (P::kChain && mode_is_fast(MODE)));
   if (!hot) {
 #pragma unroll
     for (int j = 0; j < 32; ++j)
@@ -257,7 +261,8 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const P&
     uint32_t sraw[8];
     if constexpr (mode_is_sum(MODE)) {
       const uint4 s0 = P::kChain ? ldg_cg_16((const uint8_t*)p.sum + idx0) : ldg_nc_16((const uint8_t*)p.sum + idx0);
-      const uint4 s1 = P::kChain ? ldg_cg_16((const uint8_t*)p.sum + idx0 + 16) : ldg_nc_16((const uint8_t*)p.sum + idx0 + 16);
+      uint4 s1 = make_uint4(0, 0, 0, 0);  // a ragged chunk (16 valid columns) must not read past the row
+      if (ncols > 16) s1 = P::kChain ? ldg_cg_16((const uint8_t*)p.sum + idx0 + 16) : ldg_nc_16((const uint8_t*)p.sum + idx0 + 16);
       sraw[0] = s0.x ^ f.sum_xor; sraw[1] = s0.y ^ f.sum_xor; sraw[2] = s0.z ^ f.sum_xor; sraw[3] = s0.w ^ f.sum_xor;
       sraw[4] = s1.x ^ f.sum_xor; sraw[5] = s1.y ^ f.sum_xor; sraw[6] = s1.z ^ f.sum_xor; sraw[7] = s1.w ^ f.sum_xor;
     }
@@ -304,14 +309,15 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const P&
       }
     }
     uint8_t* dst8 = (uint8_t*)p.y + idx0;
-    if (!AL8 || (((uintptr_t)dst8) & 15) == 0) {
+    if ((!AL8 || (((uintptr_t)dst8) & 15) == 0) && (ncols & 15) == 0) {
       uint4* dst = (uint4*)dst8;
       dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
-      dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
-    } else {  // rows that are 8- but not 16-byte multiples (e.g. 1000 classes)
+      if (ncols == 32) dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    } else {  // rows that are 8- but not 16-byte multiples (e.g. 1000 classes), ragged chunks of 8 / 24 columns
       uint2* dst = (uint2*)dst8;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) dst[i] = make_uint2(w[2 * i], w[2 * i + 1]);
+      for (int i = 0; i < 4; ++i)
+        if (8 * i < ncols) dst[i] = make_uint2(w[2 * i], w[2 * i + 1]);
     }
   }
 }

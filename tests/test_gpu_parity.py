@@ -1023,3 +1023,37 @@ def test_qnn_subtract_vs_oracle(dt):
         out, mod, _ = run_gpu(f, {"in_0": a, "in_1": b}, trace=True)
         np.testing.assert_equal(out, want)
         assert "qnn.subtract" in mod.plan_summary()
+
+
+@pytest.mark.parametrize("oc", [8, 16, 24, 40, 48, 72, 144, 200])
+@pytest.mark.parametrize("with_sum", [False, True])
+def test_ragged_output_channels_on_the_vector_epilogue(oc, with_sum):
+    """Output-channel counts that are not multiples of 32 (MobileNetV2 projections: 16, 24, 144 ...): the last chunk of a
+    tile is stored as whole 16-byte (8-byte) vectors; 1x1 and 3x3 convolutions, uint8 and int8 outputs, many rows so that
+    every alignment of a 24-byte row occurs; also a channel count that still needs the element path (200 = 192 + 8 with a
+    residual)."""
+    rng = np.random.default_rng(oc)
+    for k, odt in ((1, "uint8"), (3, "int8")):
+        c = 32
+        x = rng.integers(0, 256, (3, c, 9, 11)).astype("uint8")
+        w = rng.integers(-127, 128, (oc, c, k, k)).astype("int8")
+        sw = (rng.uniform(0.5, 1.5, oc) / (127 * np.sqrt(k * k * c))).astype("float32")
+        v = R.var("in_0", x.shape, "uint8")
+        e = R.max_pool2d(v, (1, 1), (1, 1), (0, 0))
+        e = R.qnn_conv2d(e, R.const(w), 0, 0, np.float32(0.02), R.const(sw), (k, k), oc, padding=(k // 2, k // 2))
+        e = R.bias_add(e, R.const(rng.integers(-4000, 4000, oc).astype("int32")))
+        zo = 0 if odt == "uint8" else -3
+        e = R.qnn_requantize(e, R.const((np.float32(0.02) * sw).astype("float32")), 0, np.float32(0.03), zo, axis=1, out_dtype="int32")
+        info = np.iinfo(odt)
+        e = R.cast(R.clip(e, float(info.min), float(info.max)), odt)
+        ins, params = {"in_0": x}, [v]
+        if with_sum:
+            r = R.var("in_1", e.shape, odt)
+            ins["in_1"] = rng.integers(info.min, info.max + 1, e.shape).astype(odt)
+            params.append(r)
+            e = R.clip(R.qnn_add(e, r, np.float32(0.03), zo, np.float32(0.05), 3, np.float32(0.04), 1), float(info.min), float(info.max))
+        f = R.Function(params, e)
+        want, _ = interp.run_expr(f, ins)
+        for impl in ("tc", "tc_im2col"):
+            out, mod, _ = run_gpu(f, ins, conv_impl=impl, trace=True)
+            np.testing.assert_equal(out, want, err_msg=f"oc={oc} k={k} {odt} sum={with_sum} {impl}")

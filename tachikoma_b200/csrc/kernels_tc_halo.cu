@@ -23,8 +23,8 @@ static constexpr int MAX_A_STAGES = 8;
 // chunk, fully unrolled -- a straight line of UTCIMMAs with one uniform add per descriptor.  (The run-time loop
 // costs ~110 cycles per MMA on the single issuing thread -- LDCU / R2UR / UIMAD chains between the MMAs -- which
 // for N = 64 tiles is 3x the tensor pipe's own time per instruction; unrolled it is ~57.)
-template <int BN, int MODE, int KH_, int KW_, int BK_, bool SPLIT, bool CTAB = false>
-__global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_constant__ CUtensorMap tmA,
+template <int BN, int MODE, int KH_, int KW_, int BK_, bool SPLIT, bool CTAB = false, int EG = 2>
+__global__ void TKB_TC_BOUNDS(EG) tc_halo_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ TcKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -36,9 +36,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
   uint64_t* a_full = (uint64_t*)(tab_s + BN);
   uint64_t* a_empty = a_full + MAX_A_STAGES;
   uint64_t* tfull = a_empty + MAX_A_STAGES;
-  uint64_t* tempty = tfull + 2;
-  uint64_t* b_full = tempty + 2;
+  uint64_t* tempty = tfull + 4;
+  uint64_t* b_full = tempty + 4;
   uint32_t* tmem_ptr = (uint32_t*)(b_full + 1);
+  constexpr int AS = SPLIT ? EG : 2;  // accumulator stages (tc_kernel.cuh)
+  static_assert(AS * BN <= 512, "TMEM columns");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nimg = p.M / (p.OH * p.OW);
@@ -49,11 +51,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     for (int i = 0; i < p.a_stages; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], SPLIT ? EPI_GROUP_WARPS : EPI_WARPS); }
+    for (int i = 0; i < AS; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], SPLIT ? EPI_GROUP_WARPS : EG * EPI_GROUP_WARPS); }
     mbar_init(b_full, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<2 * BN>(tmem_ptr);
+  if (warp == 1) tmem_alloc<AS * BN>(tmem_ptr);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -97,8 +99,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
     const uint32_t a_base = smem_u32(smem_a), b_base = smem_u32(smem_b);
     mbar_wait(b_full, 0);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-      const uint32_t as = lt & 1;
-      mbar_wait(&tempty[as], ((lt >> 1) & 1) ^ 1);
+      const uint32_t as = lt % AS;
+      mbar_wait(&tempty[as], ((lt / AS) & 1) ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * BN;
       for (int cc = 0; cc < cchunks; ++cc) {
@@ -162,21 +164,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
                         (p.e.out_dtype == kU8 || p.e.out_dtype == kI8);
     const uint32_t tab_base = smem_u32(tab_s);
     if constexpr (!CTAB) {  // CTAB: the constants are kernel parameters (p.ctab), nothing to stage
-      for (int i = et; i < BN; i += EPI_THREADS)
+      for (int i = et; i < BN; i += EG * EPI_GROUP_THREADS)
         sts128(tab_base + i * 16, i < p.N ? __ldg(p.f.tabA + i) : make_int4(0, 0, 0, 0));
-      epi_bar_sync();
+      epi_bar_sync<EG>();
     }
     const int m = q * 32 + lane;
     const int prow = m / p.hWp, pcol = m - prow * p.hWp;
     const bool slot_valid = prow < p.hR && pcol < p.OW;
-    constexpr int tstep = SPLIT ? 2 : 1, cspan = SPLIT ? BN : BN / 2;
-    const int cbeg0 = SPLIT ? 0 : grp * (BN / 2);
+    constexpr int tstep = SPLIT ? EG : 1, cspan = SPLIT ? BN : (BN / EG < 32 ? 32 : BN / EG);
+    const int cbeg0 = SPLIT ? 0 : grp * cspan;
     uint32_t lt = SPLIT ? grp : 0;
     for (int tile = blockIdx.x + (int)lt * gridDim.x; tile < total_tiles; tile += tstep * gridDim.x, lt += tstep) {
       const int n = tile / p.hTpi, oh = (tile % p.hTpi) * p.hR + prow;
       const bool row_valid = slot_valid && oh < p.OH;
       const int row = (n * p.OH + oh) * p.OW + pcol;
-      epi_drain_tile<BN, MODE, false, TcKernelParams, CTAB>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, 0, 0, tab_base, vec_ok,
+      epi_drain_tile<BN, MODE, false, TcKernelParams, CTAB, AS, EG>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, 0, 0, tab_base, vec_ok,
                                                             tempty, tfull);
       TKB_TL_IF(lt == 0 && warp == 2 && lane == 0, p, 7);
     }
@@ -185,7 +187,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_halo_kernel(const __grid_con
   tc_fence_before();
   __syncthreads();
   TKB_TL_IF(threadIdx.x == 0, p, 9);
-  if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
+  if (warp == 1) tmem_dealloc<AS * BN>(tmem_base);
 }
 
 // ---- host side -------------------------------------------------------------------------------------
@@ -227,7 +229,7 @@ static bool halo_config(const ConvGeom& g, int N, HaloCfg* c) {
   c->a_slot = (px * c->bk + 1023) / 1024 * 1024;
   const int num_kb = g.KH * g.KW * (g.C / c->bk);
   const long long b_total = (long long)num_kb * c->bn * c->bk;
-  const int fixed = c->bn * 16 + (2 * MAX_A_STAGES + 5) * 8 + 16 + 1024;
+  const int fixed = c->bn * 16 + (2 * MAX_A_STAGES + 9) * 8 + 16 + 1024;
   const long long room = 227 * 1024 - fixed - b_total;
   if (room < 2LL * c->a_slot) return false;
   c->a_stages = (int)std::min<long long>(MAX_A_STAGES, room / c->a_slot);
@@ -245,11 +247,11 @@ void tc_halo_tile_config(const ConvGeom& g, int N, int* bn, int* bk) {
   if (halo_config(g, N, &c)) { *bn = c.bn; *bk = c.bk; }
 }
 
-template <int BN, int MODE, int KH_, int KW_, int BK_, bool SPLIT, bool CTAB = false>
+template <int BN, int MODE, int KH_, int KW_, int BK_, bool SPLIT, bool CTAB = false, int EG = 2>
 static int launch_halo_ts(const CUtensorMap& ta, TcKernelParams& p, int smem, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(tc_halo_kernel<BN, MODE, KH_, KW_, BK_, SPLIT, CTAB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
+    if (cudaFuncSetAttribute(tc_halo_kernel<BN, MODE, KH_, KW_, BK_, SPLIT, CTAB, EG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
         cudaSuccess)
       return -1;
     attr_set = true;
@@ -258,7 +260,7 @@ static int launch_halo_ts(const CUtensorMap& ta, TcKernelParams& p, int smem, cu
   if (tiles > 0x3fffffffLL) return -1;  // the kernel decodes tiles in 32-bit arithmetic
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(tiles < num_sms() ? tiles : num_sms()));
-  cfg.blockDim = dim3(TC_THREADS);
+  cfg.blockDim = dim3(tc_threads(EG));
   cfg.dynamicSmemBytes = smem;
   cfg.stream = s;
   cudaLaunchAttribute attr[1];
@@ -268,7 +270,7 @@ static int launch_halo_ts(const CUtensorMap& ta, TcKernelParams& p, int smem, cu
   cfg.numAttrs = getenv("TKB_NO_PDL") ? 0 : 1;
   p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
   p.tl = timeline_buf();
-  if (cudaLaunchKernelEx(&cfg, tc_halo_kernel<BN, MODE, KH_, KW_, BK_, SPLIT, CTAB>, ta, p) != cudaSuccess) return -1;
+  if (cudaLaunchKernelEx(&cfg, tc_halo_kernel<BN, MODE, KH_, KW_, BK_, SPLIT, CTAB, EG>, ta, p) != cudaSuccess) return -1;
   timeline_print("tc_halo", p.tl, s);
   ++g_launches;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;

@@ -24,6 +24,14 @@ static constexpr int EPI_GROUP_WARPS = 4;
 static constexpr int EPI_GROUP_THREADS = EPI_GROUP_WARPS * 32;
 static constexpr int EPI_THREADS = EPI_WARPS * 32;
 static constexpr int TC_THREADS = 64 + EPI_THREADS;
+// EG (template parameter of the single-layer kernels) = number of epilogue groups.  2: the default.  1: a 192-thread CTA
+// (producer, issuer, four epilogue warps) launched TWO per SM, for layers of very many tiles with a handful of MMAs each
+// (MobileNetV2's pointwise convolutions, K = 16 .. 96): there the limit is the ~860 cycles of mbarrier / commit round
+// trips per tile on the producer and issuer threads (profiles/r02_notes.md section 13), and two CTAs per SM run two such
+// chains side by side with the same eight epilogue warps per SM.  4 (sixteen epilogue warps, four accumulator stages)
+// was measured and is no faster anywhere: 18 warps cap the kernel at 96 registers and the epilogue is not latency bound.
+__host__ __device__ constexpr int tc_threads(int eg) { return 64 + eg * EPI_GROUP_THREADS; }
+#define TKB_TC_BOUNDS(EG) __launch_bounds__(tc_threads(EG), (EG) == 1 ? 2 : 1)
 
 struct TcKernelParams {
   void* y;
@@ -127,8 +135,9 @@ __device__ __forceinline__ void tmem_ld_wait32(uint32_t (&r)[32]) {
                :
                : "memory");
 }
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory"); }
-// named barrier of one epilogue group (ids 2 and 3)
+template <int EG = 2>
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(EG * EPI_GROUP_THREADS) : "memory"); }
+// named barrier of one epilogue group (ids 2 .. 2 + EG - 1)
 __device__ __forceinline__ void epi_group_sync(int grp) {
   asm volatile("bar.sync %0, %1;" ::"r"(2 + grp), "n"(EPI_GROUP_THREADS) : "memory");
 }
@@ -337,7 +346,7 @@ __device__ __forceinline__ void acc_release(uint64_t* bar) {
 
 // Drain one accumulator stage: the calling epilogue warp owns TMEM lanes 32*q .. +31 and columns
 // [cbeg0, cbeg0 + cspan) of the tile; `row` is the output row (pixel) of this lane.
-template <int BN, int MODE, bool AL8 = false, class P = TcKernelParams, bool CTAB = false>
+template <int BN, int MODE, bool AL8 = false, class P = TcKernelParams, bool CTAB = false, int AS = 2, int EG = 2>
 __device__ __forceinline__ void epi_drain_tile(const P& p, uint32_t tmem_base, uint32_t lt, int q, int cbeg0, int cspan,
                                                int lane, int row, bool row_valid, int b, int n0, uint32_t tab_base,
                                                bool vec_ok, uint64_t* tempty, uint64_t* tfull) {
@@ -348,8 +357,8 @@ __device__ __forceinline__ void epi_drain_tile(const P& p, uint32_t tmem_base, u
     const int cls = (int)p.cls_h[pp] * p.ncls_w + (int)p.cls_w[qq];
     if (cls) drow = p.delta + (long long)cls * p.N;
   }
-  const uint32_t as = lt & 1;
-  mbar_wait(&tfull[as], (lt >> 1) & 1);
+  const uint32_t as = lt % AS;  // AS accumulator stages of BN columns
+  mbar_wait(&tfull[as], (lt / AS) & 1);
   tc_fence_after();
   TKB_TL_IF(lt == 0 && q == 2 && lane == 0 && cbeg0 == 0, p, 6);
   const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
@@ -409,19 +418,22 @@ __device__ __forceinline__ void epi_drain_tile(const P& p, uint32_t tmem_base, u
   }
 }
 
-template <int BN, int MODE, bool SPLIT>
-__global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
+template <int BN, int MODE, bool SPLIT, int EG = 2>
+__global__ void TKB_TC_BOUNDS(EG) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
                                                          const __grid_constant__ CUtensorMap tmB,
                                                          const __grid_constant__ TcKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int a_bytes = BM * p.bk, b_bytes = BN * p.bk, sub_bytes = a_bytes + b_bytes, stage_bytes = p.kps * sub_bytes;
   int4* tab_s = (int4*)(smem + p.stages * stage_bytes);  // one table of BN entries per epilogue group
-  uint64_t* full = (uint64_t*)(tab_s + 2 * BN);
+  uint64_t* full = (uint64_t*)(tab_s + EG * BN);
   uint64_t* empty = full + MAX_STAGES;
   uint64_t* tfull = empty + MAX_STAGES;
-  uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_ptr = (uint32_t*)(tempty + 2);
+  uint64_t* tempty = tfull + 4;
+  uint32_t* tmem_ptr = (uint32_t*)(tempty + 4);
+  // accumulator stages: one per epilogue group when the groups take alternate tiles, else two
+  constexpr int AS = SPLIT ? EG : 2;
+  static_assert(AS * BN <= 512, "TMEM columns");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mtiles = p.win ? p.win_rows * p.win_qt : (p.M + BM - 1) / BM, ntiles = (p.N + BN - 1) / BN;
@@ -437,10 +449,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
     for (int i = 0; i < p.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], SPLIT ? EPI_GROUP_WARPS : EPI_WARPS); }
+    for (int i = 0; i < AS; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], SPLIT ? EPI_GROUP_WARPS : EG * EPI_GROUP_WARPS); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<2 * BN>(tmem_ptr);
+  if (warp == 1) tmem_alloc<AS * BN>(tmem_ptr);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -509,8 +521,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     const int kper = p.bk / UMMA_K;
     const uint32_t smem_base = smem_u32(smem);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-      const uint32_t as = lt & 1;
-      mbar_wait(&tempty[as], ((lt >> 1) & 1) ^ 1);
+      const uint32_t as = lt % AS;
+      mbar_wait(&tempty[as], ((lt / AS) & 1) ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * BN;
       for (int kb0 = 0; kb0 < num_kb; kb0 += p.kps) {
@@ -556,9 +568,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                                           : (p.e.out_dtype == kU8 || p.e.out_dtype == kI8));
     const uint32_t tab_base = smem_u32(tab_s) + grp * BN * 16;
     int tab_n0 = -1;
-    // tile split: group g takes the CTA's tiles g, g + 2, ...: exactly those whose accumulator is TMEM stage g
-    constexpr int tstep = SPLIT ? 2 : 1, cspan = SPLIT ? BN : BN / 2;
-    const int cbeg0 = SPLIT ? 0 : grp * (BN / 2);
+    // tile split: group g takes the CTA's tiles g, g + EG, ...: exactly those whose accumulator is TMEM stage g;
+    // column split: every group takes BN / EG columns (at least one 32-column chunk) of every tile
+    constexpr int tstep = SPLIT ? EG : 1, cspan = SPLIT ? BN : (BN / EG < 32 ? 32 : BN / EG);
+    const int cbeg0 = SPLIT ? 0 : grp * cspan;
     uint32_t lt = SPLIT ? grp : 0;
     for (int tile = blockIdx.x + (int)lt * gridDim.x; tile < total_tiles; tile += tstep * gridDim.x, lt += tstep) {
       const int nt = tile % ntiles;
@@ -580,7 +593,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         row_valid = qp < p.OW;
         row = (mt / p.win_qt) * p.OW + qp;
       }
-      epi_drain_tile<BN, MODE, AL8>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, b, n0, tab_base, vec_ok, tempty, tfull);
+      epi_drain_tile<BN, MODE, AL8, TcKernelParams, false, AS, EG>(p, tmem_base, lt, q, cbeg0, cspan, lane, row, row_valid, b, n0, tab_base, vec_ok,
+                                                               tempty, tfull);
       TKB_TL_IF(lt == 0 && warp == 2 && lane == 0, p, 7);
     }
     TKB_TL_IF(warp == 2 && lane == 0, p, 8);
@@ -588,7 +602,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
   tc_fence_before();
   __syncthreads();
   TKB_TL_IF(threadIdx.x == 0, p, 9);
-  if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
+  if (warp == 1) tmem_dealloc<AS * BN>(tmem_base);
 }
 
 inline int num_sms() {
@@ -607,11 +621,11 @@ inline int num_sms() {
 // SPLIT (epilogue partition, template parameter of the kernels): true = the two epilogue groups take alternate
 // TILES, all columns each (64-column tiles of CTAs that have several tiles: two tiles are in the epilogue at once);
 // false = both groups work on every tile, half of its columns each.
-template <int BN, int MODE, bool SPLIT>
+template <int BN, int MODE, bool SPLIT, int EG = 2>
 static int launch_ts(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s) {
   const int sub_bytes = (BM + BN) * p.bk;
-  const int fixed = 2 * BN * 16 + (2 * MAX_STAGES + 4) * 8 + 16 + 1024 /* alignment slack */;
-  const int budget = 227 * 1024 - fixed;
+  const int fixed = EG * BN * 16 + (2 * MAX_STAGES + 8) * 8 + 16 + 1024 /* alignment slack */;
+  const int budget = (EG == 1 ? 110 : 227) * 1024 - fixed;  // EG == 1: two CTAs share the SM's shared memory
   const int num_kb = p.implicit ? p.KH * p.KW * (p.C / p.bk) : (p.K + p.bk - 1) / p.bk;
   // Group k-blocks so that one mbarrier round trip (~100+ cycles on the single issuing thread for each of
   // wait / elect / commit) covers enough MMAs: stages of up to 64 KB, at least 3 of them.
@@ -628,7 +642,7 @@ static int launch_ts(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParam
   const int smem = stages * stage_bytes + fixed;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(tc_gemm_kernel<BN, MODE, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
+    if (cudaFuncSetAttribute(tc_gemm_kernel<BN, MODE, SPLIT, EG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
         cudaSuccess)
       return -1;
     attr_set = true;
@@ -636,11 +650,12 @@ static int launch_ts(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParam
   const long long mt_host = p.win ? (long long)p.win_rows * p.win_qt : (p.M + BM - 1) / BM;
   const long long tiles = mt_host * ((p.N + BN - 1) / BN) * p.batches;
   if (tiles > 0x3fffffffLL) return -1;  // the kernel decodes tiles in 32-bit arithmetic
-  const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  const int ctas = (EG == 1 ? 2 : 1) * num_sms();
+  const int grid = (int)(tiles < ctas ? tiles : ctas);
   p.idesc = idesc_i8(BM, BN, false, false) | (p.idesc & ((1u << 7) | (1u << 10)));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(TC_THREADS);
+  cfg.blockDim = dim3(tc_threads(EG));
   cfg.dynamicSmemBytes = smem;
   cfg.stream = s;
   cudaLaunchAttribute attr[1];
@@ -649,17 +664,31 @@ static int launch_ts(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParam
   cfg.attrs = attr;
   cfg.numAttrs = getenv("TKB_NO_PDL") ? 0 : 1;
   p.tl = timeline_buf();
-  if (cudaLaunchKernelEx(&cfg, tc_gemm_kernel<BN, MODE, SPLIT>, ta, tb, p) != cudaSuccess) return -1;
+  if (cudaLaunchKernelEx(&cfg, tc_gemm_kernel<BN, MODE, SPLIT, EG>, ta, tb, p) != cudaSuccess) return -1;
   timeline_print("tc_gemm", p.tl, s);
   ++g_launches;
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
+// experiment knob TKB_EG: 1 = two small CTAs per SM wherever instantiated, 2 = never; default: by tiles and MMAs per tile
+// (measured, MobileNetV2 batch 128: 16 -> 96 at 112x112 112.8 -> 93.4 us, 32 -> 16 62.5 -> 52.2 us, 96 -> 24 at 56x56
+// 23.8 -> 20.3 us; layers with two column tiles or ~10 tiles per SM get slower, so they keep the one-CTA form)
+inline int epi_groups_for(long long tiles_per_sm, int num_mma_per_tile, int ntiles) {
+  static const int forced = [] { const char* e = getenv("TKB_EG"); return e ? atoi(e) : 0; }();
+  if (forced == 1 || forced == 2) return forced;
+  return (tiles_per_sm >= 16 && num_mma_per_tile <= 4 && ntiles == 1) ? 1 : 2;
+}
+
 template <int BN, int MODE>
 static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParams& p, cudaStream_t s) {
+  const long long mt_host = p.win ? (long long)p.win_rows * p.win_qt : (p.M + BM - 1) / BM;
+  const long long tiles = mt_host * ((p.N + BN - 1) / BN) * p.batches;
+  if constexpr (mode_is_fast(MODE) && BN <= 128) {
+    const int num_kb = p.implicit ? p.KH * p.KW * (p.C / p.bk) : (p.K + p.bk - 1) / p.bk;
+    // (the saturating-pack variants spill in this configuration: explicit clamps, same results)
+    if (epi_groups_for(tiles / num_sms(), num_kb * (p.bk / UMMA_K), (p.N + BN - 1) / BN) == 1) return launch_ts<BN, (MODE & 3), false, 1>(ta, tb, p, s);
+  }
   if constexpr (BN == 64 && mode_is_fast(MODE)) {
-    const long long mt_host = p.win ? (long long)p.win_rows * p.win_qt : (p.M + BM - 1) / BM;
-    const long long tiles = mt_host * ((p.N + BN - 1) / BN) * p.batches;
     if (tiles >= 2LL * num_sms()) return launch_ts<BN, MODE, true>(ta, tb, p, s);
   }
   return launch_ts<BN, MODE, false>(ta, tb, p, s);

@@ -352,6 +352,19 @@ def _wrap_add_i32(a, b):
 
 def eval_op(op, attrs, args):
     """Evaluate one Relay operator on numpy inputs (constants included in ``args``)."""
+    # float32 half of the tachikoma op list (oracle/float_ops.py); integer tensors never take these branches
+    if not op.startswith("qnn.") and args and all(np.asarray(a).dtype == np.float32 for a in args):
+        from . import float_ops as F
+        if op in F.FLOAT_OPS:
+            return F.eval_float_op(op, attrs, args)
+        if op == "add":
+            return F.float_add(args[0], args[1])
+        if op == "nn.bias_add":
+            shp = [1] * np.asarray(args[0]).ndim
+            shp[attrs.get("axis", 1)] = -1
+            return F.float_add(args[0], np.asarray(args[1]).reshape(shp))
+        if op in ("nn.max_pool2d", "nn.avg_pool2d", "nn.global_avg_pool2d"):
+            return F.float_pool(op, attrs, args[0])
     if op == "qnn.conv2d":
         return conv2d(args[0], args[1], args[2], args[3], attrs["strides"], attrs["padding"], attrs["dilation"],
                       attrs["groups"], attrs["data_layout"], attrs["kernel_layout"], attrs.get("out_layout", ""))
@@ -517,10 +530,35 @@ def _plain_attrs(node):
     return a
 
 
+_FLOAT_ATTR_LISTS = ("strides", "padding", "dilation", "pool_size", "output_padding", "kernel_size")
+_FLOAT_ATTR_INTS = ("groups", "axis", "channels", "units", "transpose_a", "transpose_b", "count_include_pad", "ceil_mode",
+                    "center", "scale")
+_FLOAT_ATTR_FLOATS = ("epsilon", "alpha", "a_min", "a_max")
+
+
+def _float_attrs(node):
+    out = {}
+    for k, v in _plain_attrs(node).items():
+        if k in _FLOAT_ATTR_LISTS:
+            out[k] = [int(x) for x in v]
+        elif k in _FLOAT_ATTR_INTS:
+            out[k] = int(v[0])
+        elif k in _FLOAT_ATTR_FLOATS:
+            out[k] = float(v[0])
+        elif len(v) == 1:
+            out[k] = v[0]
+    return out
+
+
 def _eval_json_node(node, ins):
     op = node["name"]
     if op.startswith("tachikoma.qnn."):
         return _eval_composite(node, ins)
+    if ins and all(np.asarray(a).dtype == np.float32 for a in ins) and not op.startswith("qnn.") and op not in ("clip", "cast", "reshape", "transpose", "nn.pad", "nn.batch_flatten"):
+        from . import float_ops as F
+        if op.startswith("tachikoma."):
+            return F.eval_float_composite(op, _float_attrs(node), ins)
+        return eval_op(op, _float_attrs(node), ins)
     a = _plain_attrs(node)
     g = lambda k, d=None: a[k][0] if k in a else d
     if op == "qnn.conv2d":

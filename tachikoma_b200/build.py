@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SOURCES = ["runtime.cu", "kernels_simt.cu", "kernels_tc.cu", "kernels_tc_generic.cu", "kernels_tc_halo.cu",
-           "kernels_tc_chain.cu", "kernels_tc_pair.cu", "noalloc.cu"]
+           "kernels_tc_chain.cu", "kernels_tc_pair.cu", "noalloc.cu", "kernels_float.cu"]
 HEADERS = ["epilogue.cuh", "graph.h", "json.h", "kernels.h", "tc_ptx.cuh", "tc_kernel.cuh"]
 LIB = os.path.join(HERE, "libtkb200.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",

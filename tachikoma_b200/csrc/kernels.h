@@ -156,6 +156,28 @@ int probe_int8_shape(int iters, int n, int commit_every, double* tops, cudaStrea
 
 void launch_spin(double us, cudaStream_t s);  // device busy-wait (measurement aid)
 
+// ---- float32 operators of the float tachikoma patterns (kernels_float.cu) ------------------------------------------------
+enum FAct : int { kFActNone = 0, kFActRelu, kFActTanh, kFActSigmoid, kFActClip, kFActGelu, kFActSwish, kFActMish, kFActAbs,
+                  kFActExp, kFActLog, kFActSqrt, kFActRound, kFActLeakyRelu };
+// post-ops of a float primitive in the reference's order (tachikoma_json_runtime.cc:185-233): + bias[channel], + sum, activation
+struct FPost { int act; float a, b; const float* bias; const float* sum; };
+// NC[D]HW convolution / pooling geometry (1-D and 2-D operators are the D = 1 (and H = 1) cases)
+struct FConvGeom {
+  int N, C, D, H, W, O, OD, OH, OW, KD, KH, KW, sd, sh, sw, dd, dh, dw, pd, ph, pw, groups, transposed;
+};
+struct FBcast5 { long long shape[5], ls[5], rs[5]; };
+void launch_fconv(const float* x, const float* w, float* y, const FConvGeom& g, const FPost& post, cudaStream_t s);
+void launch_fgemm(const float* A, const float* B, float* C, int batch, int M, int N, int K, long long a_b, long long a_m,
+                  long long a_k, long long b_b, long long b_n, long long b_k, const FPost& post, cudaStream_t s);
+void launch_funary(const float* x, float* y, long long n, int act, float a, float b, cudaStream_t s);
+void launch_fbinary(const float* l, const float* r, float* y, const FBcast5& bc, int mul, cudaStream_t s);
+void launch_fbatchnorm(const float* x, float* y, long long outer, int C, long long inner, const float* gamma, const float* beta,
+                       const float* mean, const float* var, float eps, cudaStream_t s);
+void launch_flayernorm(const float* x, float* y, long long rows, int C, const float* gamma, const float* beta, float eps,
+                       cudaStream_t s);
+void launch_fsoftmax(const float* x, float* y, long long outer, int C, long long inner, cudaStream_t s);
+void launch_fpool(const float* x, float* y, const FConvGeom& g, int is_avg, int count_include_pad, cudaStream_t s);
+
 extern thread_local long long g_launches;  // kernels launched by this thread (summed per handle)
 
 }  // namespace tkb

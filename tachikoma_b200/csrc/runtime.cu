@@ -23,7 +23,9 @@
 #include <functional>
 #include <memory>
 #include <mutex>
+#include <map>
 #include <regex>
+#include <set>
 #include <sstream>
 #include <thread>
 #include <unordered_map>
@@ -1641,6 +1643,341 @@ static void plan_qnn_leaky_relu(Planner& P, int nid) {
   });
 }
 
+// ------------------------------------------------------------------------------------------------
+// float32 operators (the other half of the reference's op list, tachikoma_json_runtime.cc:240-290): plain fp32 kernels
+// (kernels_float.cu), always in the logical (NC[D]HW / row-major) layout of the JSON graph
+// ------------------------------------------------------------------------------------------------
+static bool name_has(const std::string& s, const char* sub) { return s.find(sub) != std::string::npos; }
+
+// post-ops from the composite's name, as ParseAttrs does with its regular expressions (:185-233)
+static FPost float_post_from_name(const GNode& n) {
+  FPost post = {kFActNone, 0.f, 0.f, nullptr, nullptr};
+  const std::string& op = n.name;
+  if (name_has(op, "_relu")) post.act = kFActRelu;
+  if (name_has(op, "_tanh")) post.act = kFActTanh;
+  if (name_has(op, "_clip")) { post.act = kFActClip; post.a = (float)n.f64("a_min"); post.b = (float)n.f64("a_max"); }
+  if (name_has(op, "_sigmoid")) post.act = kFActSigmoid;
+  if (name_has(op, "_swish")) post.act = kFActSwish;
+  if (name_has(op, "_gelu")) post.act = kFActGelu;
+  if (name_has(op, "_mish")) post.act = kFActMish;
+  return post;
+}
+
+static void require_f32(Planner& P, const GNode& n, std::initializer_list<int> eids) {
+  for (int e : eids)
+    if (P.ent[P.root(e)].dtype != kF32) fail("Unsupported op: %s on tensors that are not float32", n.name.c_str());
+}
+
+// bias (input 2 of *_bias* composites) and sum (last input of *_sum* composites): tachikoma_json_runtime.cc:231, :372-376
+static void float_bias_sum(Planner& P, const GNode& n, int channels, long long out_elems, int* bias_eid, int* sum_eid) {
+  *bias_eid = *sum_eid = -1;
+  if (name_has(n.name, "_bias")) {
+    if (n.inputs.size() < 3) fail("%s: missing bias input", n.name.c_str());
+    *bias_eid = (int)P.g.eid(n.inputs[2]);
+    if (numel(P.ent[P.root(*bias_eid)].shape) != channels) fail("%s: bias of %lld elements for %d channels", n.name.c_str(), numel(P.ent[P.root(*bias_eid)].shape), channels);
+  }
+  if (name_has(n.name, "_sum")) {
+    *sum_eid = (int)P.g.eid(n.inputs.back());
+    if (numel(P.ent[P.root(*sum_eid)].shape) != out_elems) fail("%s: sum operand must have the output's shape", n.name.c_str());
+  }
+}
+
+static void plan_float_conv(Planner& P, int nid, bool transposed) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), w_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[P.root(x_eid)];
+  const Entry& Wt = P.ent[P.root(w_eid)];
+  const Entry& Y = P.ent[y_eid];
+  require_f32(P, n, {x_eid, w_eid, y_eid});
+  const int sp = (int)X.shape.size() - 2;  // spatial rank
+  if (sp < 1 || sp > 3 || Wt.shape.size() != X.shape.size() || Y.shape.size() != X.shape.size()) fail("Unsupported op: %s on rank-%d data", n.name.c_str(), (int)X.shape.size());
+  static const char* dls[3] = {"NCW", "NCHW", "NCDHW"};
+  static const char* kls[3] = {"OIW", "OIHW", "OIDHW"};
+  static const char* tls[3] = {"IOW", "IOHW", "IODHW"};
+  const std::string dl = n.str("data_layout", dls[sp - 1]), kl = n.str("kernel_layout", transposed ? tls[sp - 1] : kls[sp - 1]);
+  std::string ol = n.str("out_layout", "");
+  if (ol.empty()) ol = dl;
+  // conv3d_transpose says OIDHW and means IODHW (the reference's own work-around, tachikoma_json_runtime.cc:420-423)
+  const bool kl_ok = transposed ? (kl == tls[sp - 1] || (sp == 3 && kl == "OIDHW")) : kl == kls[sp - 1];
+  if (dl != dls[sp - 1] || ol != dl || !kl_ok) fail("Unsupported op: %s with data_layout %s / kernel_layout %s / out_layout %s", n.name.c_str(), dl.c_str(), kl.c_str(), ol.c_str());
+  auto st = n.ints("strides"), di = n.ints("dilation"), pd = n.ints("padding");
+  if (st.empty()) st.assign(sp, 1);
+  if (di.empty()) di.assign(sp, 1);
+  if (pd.empty()) pd.assign(2 * sp, 0);
+  if ((int)pd.size() == sp) { auto q = pd; pd.insert(pd.end(), q.begin(), q.end()); }
+  if ((int)pd.size() == 1) pd.assign(2 * sp, pd[0]);
+  if ((int)st.size() != sp || (int)di.size() != sp || (int)pd.size() != 2 * sp) fail("%s: strides / dilation / padding do not match %d spatial axes", n.name.c_str(), sp);
+  FConvGeom g = {};
+  g.groups = (int)n.i64("groups", 1);
+  g.transposed = transposed ? 1 : 0;
+  g.N = (int)X.shape[0]; g.C = (int)X.shape[1]; g.O = (int)Y.shape[1];
+  int in[3] = {1, 1, 1}, out[3] = {1, 1, 1}, k[3] = {1, 1, 1}, s3[3] = {1, 1, 1}, d3[3] = {1, 1, 1}, p3[3] = {0, 0, 0}, pe[3] = {0, 0, 0};
+  for (int i = 0; i < sp; ++i) {
+    const int j = 3 - sp + i;
+    in[j] = (int)X.shape[2 + i]; out[j] = (int)Y.shape[2 + i]; k[j] = (int)Wt.shape[2 + i];
+    s3[j] = (int)st[i]; d3[j] = (int)di[i]; p3[j] = (int)pd[i]; pe[j] = (int)pd[sp + i];
+  }
+  g.D = in[0]; g.H = in[1]; g.W = in[2]; g.OD = out[0]; g.OH = out[1]; g.OW = out[2]; g.KD = k[0]; g.KH = k[1]; g.KW = k[2];
+  g.sd = s3[0]; g.sh = s3[1]; g.sw = s3[2]; g.dd = d3[0]; g.dh = d3[1]; g.dw = d3[2]; g.pd = p3[0]; g.ph = p3[1]; g.pw = p3[2];
+  if (g.groups < 1 || g.C % g.groups || g.O % g.groups) fail("%s: %d groups for %d -> %d channels", n.name.c_str(), g.groups, g.C, g.O);
+  if (transposed ? (Wt.shape[0] != g.C || Wt.shape[1] != g.O / g.groups) : (Wt.shape[0] != g.O || Wt.shape[1] != g.C / g.groups))
+    fail("%s: weight shape does not match %d -> %d channels in %d groups", n.name.c_str(), g.C, g.O, g.groups);
+  auto opad = n.ints("output_padding");
+  for (int j = 0; j < 3; ++j) {
+    const int i = j - (3 - sp);
+    const int op_ = transposed && i >= 0 && i < (int)opad.size() ? (int)opad[i] : 0;
+    const int want = transposed ? (in[j] - 1) * s3[j] - p3[j] - pe[j] + d3[j] * (k[j] - 1) + 1 + op_
+                                : (in[j] + p3[j] + pe[j] - d3[j] * (k[j] - 1) - 1) / s3[j] + 1;
+    if (i >= 0 && want != out[j]) fail("%s: output extent %d on spatial axis %d, expected %d", n.name.c_str(), out[j], i, want);
+  }
+  FPost post = float_post_from_name(n);
+  int bias_eid, sum_eid;
+  float_bias_sum(P, n, g.O, numel(Y.shape), &bias_eid, &sum_eid);
+  P.need(x_eid, kLogical); P.need(w_eid, kLogical);
+  if (bias_eid >= 0) P.need(bias_eid, kLogical);
+  if (sum_eid >= 0) P.need(sum_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->hbm_bytes += X.bytes() + Wt.bytes() + Y.bytes();
+  P.add_step(n.name + (transposed ? " -> fp32 direct transposed convolution" : " -> fp32 direct convolution"), [=](RunCtx& c) {
+    FPost q = post;
+    q.bias = bias_eid >= 0 ? (const float*)c.ptr(bias_eid, kLogical) : nullptr;
+    q.sum = sum_eid >= 0 ? (const float*)c.ptr(sum_eid, kLogical) : nullptr;
+    launch_fconv((const float*)c.ptr(x_eid, kLogical), (const float*)c.ptr(w_eid, kLogical), (float*)c.ptr(y_eid, kLogical), g, q, c.s);
+  });
+}
+
+static void plan_float_dense(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), w_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[P.root(x_eid)];
+  const Entry& Wt = P.ent[P.root(w_eid)];
+  const Entry& Y = P.ent[y_eid];
+  require_f32(P, n, {x_eid, w_eid, y_eid});
+  if (Wt.shape.size() != 2 || X.shape.empty() || X.shape.back() != Wt.shape[1]) fail("%s: data / weight shapes do not match", n.name.c_str());
+  const int K = (int)Wt.shape[1], N = (int)Wt.shape[0];
+  const int M = (int)(numel(X.shape) / K);
+  if (numel(Y.shape) != (long long)M * N) fail("%s: output shape mismatch", n.name.c_str());
+  FPost post = float_post_from_name(n);
+  int bias_eid, sum_eid;
+  float_bias_sum(P, n, N, numel(Y.shape), &bias_eid, &sum_eid);
+  P.need(x_eid, kLogical); P.need(w_eid, kLogical);
+  if (bias_eid >= 0) P.need(bias_eid, kLogical);
+  if (sum_eid >= 0) P.need(sum_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->hbm_bytes += X.bytes() + Wt.bytes() + Y.bytes();
+  P.add_step(n.name + " -> fp32 tiled GEMM", [=](RunCtx& c) {
+    FPost q = post;
+    q.bias = bias_eid >= 0 ? (const float*)c.ptr(bias_eid, kLogical) : nullptr;
+    q.sum = sum_eid >= 0 ? (const float*)c.ptr(sum_eid, kLogical) : nullptr;
+    launch_fgemm((const float*)c.ptr(x_eid, kLogical), (const float*)c.ptr(w_eid, kLogical), (float*)c.ptr(y_eid, kLogical), 1, M, N, K,
+                 0, K, 1, 0, K, 1, q, c.s);
+  });
+}
+
+// nn.batch_matmul on float32 (tachikoma_json_runtime.cc:504-548): [B,M,K] x [B,N,K]^T by default, either side transposable
+static void plan_float_batch_matmul(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), w_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[P.root(x_eid)];
+  const Entry& Wt = P.ent[P.root(w_eid)];
+  const Entry& Y = P.ent[y_eid];
+  require_f32(P, n, {x_eid, w_eid, y_eid});
+  if (X.shape.size() != 3 || Wt.shape.size() != 3 || Y.shape.size() != 3) fail("%s: operands must have rank 3", n.name.c_str());
+  const bool ta = n.i64("transpose_a", 0) != 0, tb = n.i64("transpose_b", 1) != 0;
+  const int B = (int)Y.shape[0], M = (int)Y.shape[1], N = (int)Y.shape[2];
+  const int K = (int)(ta ? X.shape[1] : X.shape[2]);
+  if ((ta ? X.shape[2] : X.shape[1]) != M || (tb ? Wt.shape[1] : Wt.shape[2]) != N || (tb ? Wt.shape[2] : Wt.shape[1]) != K ||
+      (X.shape[0] != B && X.shape[0] != 1) || (Wt.shape[0] != B && Wt.shape[0] != 1))
+    fail("%s: operand shapes do not match", n.name.c_str());
+  const long long a_b = X.shape[0] == 1 ? 0 : (long long)M * K, b_b = Wt.shape[0] == 1 ? 0 : (long long)N * K;
+  const long long a_m = ta ? 1 : K, a_k = ta ? M : 1, b_n = tb ? K : 1, b_k = tb ? 1 : N;
+  P.need(x_eid, kLogical); P.need(w_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->hbm_bytes += X.bytes() + Wt.bytes() + Y.bytes();
+  P.add_step("nn.batch_matmul -> fp32 tiled GEMM (batched)", [=](RunCtx& c) {
+    FPost q = {kFActNone, 0.f, 0.f, nullptr, nullptr};
+    launch_fgemm((const float*)c.ptr(x_eid, kLogical), (const float*)c.ptr(w_eid, kLogical), (float*)c.ptr(y_eid, kLogical), B, M, N, K,
+                 a_b, a_m, a_k, b_b, b_n, b_k, q, c.s);
+  });
+}
+
+static void plan_float_unary(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[P.root(x_eid)];
+  require_f32(P, n, {x_eid, y_eid});
+  static const std::map<std::string, int> acts = {{"abs", kFActAbs}, {"exp", kFActExp}, {"log", kFActLog}, {"sqrt", kFActSqrt},
+      {"round", kFActRound}, {"nn.relu", kFActRelu}, {"nn.leaky_relu", kFActLeakyRelu}, {"tanh", kFActTanh},
+      {"sigmoid", kFActSigmoid}, {"clip", kFActClip}};
+  const int act = acts.at(n.name);
+  float a = 0.f, b = 0.f;
+  if (act == kFActClip) { a = (float)n.f64("a_min"); b = (float)n.f64("a_max"); }
+  if (act == kFActLeakyRelu) a = (float)n.f64("alpha", 0.01);
+  const long long cnt = numel(X.shape);
+  P.need(x_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->hbm_bytes += 2 * X.bytes();
+  P.add_step(n.name + " -> fp32 elementwise kernel", [=](RunCtx& c) {
+    launch_funary((const float*)c.ptr(x_eid, kLogical), (float*)c.ptr(y_eid, kLogical), cnt, act, a, b, c.s);
+  });
+}
+
+static void plan_float_binary(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int l_eid = (int)P.g.eid(n.inputs[0]), r_eid = (int)P.g.eid(n.inputs[1]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& L = P.ent[P.root(l_eid)];
+  const Entry& Rr = P.ent[P.root(r_eid)];
+  const Entry& Y = P.ent[y_eid];
+  require_f32(P, n, {l_eid, r_eid, y_eid});
+  const int rank = (int)Y.shape.size();
+  if (rank > 5 || (int)L.shape.size() > rank || (int)Rr.shape.size() > rank) fail("Unsupported op: %s of rank %d", n.name.c_str(), rank);
+  FBcast5 bc;
+  for (int d = 0; d < 5; ++d) { bc.shape[d] = 1; bc.ls[d] = bc.rs[d] = 0; }
+  auto fill = [&](const Entry& e, long long* strides) {
+    long long stride = 1;
+    for (int i = (int)e.shape.size() - 1, d = 4; i >= 0; --i, --d) {
+      const long long ext = e.shape[i], oext = Y.shape[rank - ((int)e.shape.size() - i)];
+      if (ext != oext && ext != 1) fail("%s: operand shapes do not broadcast", n.name.c_str());
+      strides[d] = ext == 1 ? 0 : stride;
+      stride *= ext;
+    }
+  };
+  for (int i = rank - 1, d = 4; i >= 0; --i, --d) bc.shape[d] = Y.shape[i];
+  fill(L, bc.ls);
+  fill(Rr, bc.rs);
+  const int mul = n.name == "multiply";
+  P.need(l_eid, kLogical); P.need(r_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->hbm_bytes += L.bytes() + Rr.bytes() + Y.bytes();
+  P.add_step(n.name + " -> fp32 broadcasting binary kernel", [=](RunCtx& c) {
+    launch_fbinary((const float*)c.ptr(l_eid, kLogical), (const float*)c.ptr(r_eid, kLogical), (float*)c.ptr(y_eid, kLogical), bc, mul, c.s);
+  });
+}
+
+// nn.batch_norm (inference; tachikoma_json_runtime.cc:550-596): output 0 only, axis = 1, center and scale
+static void plan_float_batch_norm(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  if (n.inputs.size() != 5) fail("nn.batch_norm: expected 5 inputs");
+  int e[5];
+  for (int i = 0; i < 5; ++i) e[i] = (int)P.g.eid(n.inputs[i]);
+  const int y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[P.root(e[0])];
+  require_f32(P, n, {e[0], e[1], e[2], e[3], e[4], y_eid});
+  if (n.i64("axis", 1) != 1 || !n.i64("center", 1) || !n.i64("scale", 1)) fail("Unimplemented BatchNorm case");  // the reference's ICHECK
+  if (X.shape.size() < 2) fail("nn.batch_norm: rank-%d data", (int)X.shape.size());
+  const int C = (int)X.shape[1];
+  for (int i = 1; i < 5; ++i) if (numel(P.ent[P.root(e[i])].shape) != C) fail("nn.batch_norm: statistics must have %d elements", C);
+  const long long outer = X.shape[0], inner = numel(X.shape) / (outer * C);
+  const float eps = (float)n.f64("epsilon", 1e-5);
+  for (int i = 0; i < 5; ++i) P.need(e[i], kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->hbm_bytes += 2 * X.bytes();
+  const int x = e[0], ga = e[1], be = e[2], me = e[3], va = e[4];
+  P.add_step("nn.batch_norm -> fp32 per-channel normalisation kernel", [=](RunCtx& c) {
+    launch_fbatchnorm((const float*)c.ptr(x, kLogical), (float*)c.ptr(y_eid, kLogical), outer, C, inner, (const float*)c.ptr(ga, kLogical),
+                      (const float*)c.ptr(be, kLogical), (const float*)c.ptr(me, kLogical), (const float*)c.ptr(va, kLogical), eps, c.s);
+  });
+}
+
+static void plan_float_layer_norm(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  if (n.inputs.size() != 3) fail("nn.layer_norm: expected 3 inputs");
+  const int x_eid = (int)P.g.eid(n.inputs[0]), g_eid = (int)P.g.eid(n.inputs[1]), b_eid = (int)P.g.eid(n.inputs[2]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[P.root(x_eid)];
+  require_f32(P, n, {x_eid, g_eid, b_eid, y_eid});
+  const int rank = (int)X.shape.size();
+  const int axis = (int)n.i64("axis", -1);
+  if ((axis != -1 && axis != rank - 1) || !n.i64("center", 1) || !n.i64("scale", 1)) fail("Unimplemented LayerNorm case");  // the reference's ICHECK
+  const int C = (int)X.shape.back();
+  if (numel(P.ent[P.root(g_eid)].shape) != C || numel(P.ent[P.root(b_eid)].shape) != C) fail("nn.layer_norm: gamma / beta must have %d elements", C);
+  const long long rows = numel(X.shape) / C;
+  const float eps = (float)n.f64("epsilon", 1e-5);
+  P.need(x_eid, kLogical); P.need(g_eid, kLogical); P.need(b_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->hbm_bytes += 2 * X.bytes();
+  P.add_step("nn.layer_norm -> fp32 warp-per-row kernel", [=](RunCtx& c) {
+    launch_flayernorm((const float*)c.ptr(x_eid, kLogical), (float*)c.ptr(y_eid, kLogical), rows, C, (const float*)c.ptr(g_eid, kLogical),
+                      (const float*)c.ptr(b_eid, kLogical), eps, c.s);
+  });
+}
+
+static void plan_float_softmax(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[P.root(x_eid)];
+  require_f32(P, n, {x_eid, y_eid});
+  const int rank = (int)X.shape.size();
+  int axis = (int)n.i64("axis", -1);
+  if (axis < 0) axis += rank;
+  if (axis < 0 || axis >= rank) fail("nn.softmax: axis %d of a rank-%d tensor", axis, rank);
+  long long outer = 1, inner = 1;
+  for (int i = 0; i < axis; ++i) outer *= X.shape[i];
+  for (int i = axis + 1; i < rank; ++i) inner *= X.shape[i];
+  const int C = (int)X.shape[axis];
+  P.need(x_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->hbm_bytes += 2 * X.bytes();
+  P.add_step("nn.softmax -> fp32 warp-per-vector kernel", [=](RunCtx& c) {
+    launch_fsoftmax((const float*)c.ptr(x_eid, kLogical), (float*)c.ptr(y_eid, kLogical), outer, C, inner, c.s);
+  });
+}
+
+// float max / average pooling, 2-D and 3-D (tachikoma_json_runtime.cc:641-701)
+static void plan_float_pool(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
+  const Entry& X = P.ent[P.root(x_eid)];
+  const Entry& Y = P.ent[y_eid];
+  require_f32(P, n, {x_eid, y_eid});
+  const int sp = (int)X.shape.size() - 2;
+  if (sp < 2 || sp > 3) fail("Unsupported op: %s on rank-%d data", n.name.c_str(), (int)X.shape.size());
+  const std::string lay = n.str("layout", sp == 2 ? "NCHW" : "NCDHW");
+  std::string ol = n.str("out_layout", "");
+  if (ol.empty()) ol = lay;
+  if (lay != (sp == 2 ? "NCHW" : "NCDHW") || ol != lay) fail("Unsupported op: %s with layout %s", n.name.c_str(), lay.c_str());
+  const bool global = name_has(n.name, "global");
+  const bool is_avg = name_has(n.name, "avg_pool");
+  std::vector<int64_t> ps, st, di, pd;
+  if (global) {
+    for (int i = 0; i < sp; ++i) ps.push_back(X.shape[2 + i]);
+    st.assign(sp, 1); di.assign(sp, 1); pd.assign(2 * sp, 0);
+  } else {
+    ps = n.ints("pool_size"); st = n.ints("strides"); di = n.ints("dilation"); pd = n.ints("padding");
+    if (di.empty()) di.assign(sp, 1);
+    if ((int)pd.size() == sp) { auto q = pd; pd.insert(pd.end(), q.begin(), q.end()); }
+    if ((int)pd.size() == 1) pd.assign(2 * sp, pd[0]);
+    if (n.i64("ceil_mode", 0)) fail("Unsupported op: pooling with ceil_mode");  // tachikoma.py:77-80 keeps these off the backend
+  }
+  if ((int)ps.size() != sp || (int)st.size() != sp || (int)di.size() != sp || (int)pd.size() != 2 * sp) fail("%s: pool_size / strides / padding do not match %d spatial axes", n.name.c_str(), sp);
+  FConvGeom g = {};
+  g.N = (int)X.shape[0]; g.C = (int)X.shape[1]; g.O = g.C; g.groups = 1;
+  int in[3] = {1, 1, 1}, out[3] = {1, 1, 1}, k[3] = {1, 1, 1}, s3[3] = {1, 1, 1}, d3[3] = {1, 1, 1}, p3[3] = {0, 0, 0};
+  for (int i = 0; i < sp; ++i) {
+    const int j = 3 - sp + i;
+    in[j] = (int)X.shape[2 + i]; out[j] = (int)Y.shape[2 + i]; k[j] = (int)ps[i]; s3[j] = (int)st[i]; d3[j] = (int)di[i]; p3[j] = (int)pd[i];
+    const int want = (in[j] + (int)pd[i] + (int)pd[sp + i] - d3[j] * (k[j] - 1) - 1) / s3[j] + 1;
+    if (want != out[j]) fail("%s: output extent %d on spatial axis %d, expected %d", n.name.c_str(), out[j], i, want);
+  }
+  g.D = in[0]; g.H = in[1]; g.W = in[2]; g.OD = out[0]; g.OH = out[1]; g.OW = out[2]; g.KD = k[0]; g.KH = k[1]; g.KW = k[2];
+  g.sd = s3[0]; g.sh = s3[1]; g.sw = s3[2]; g.dd = d3[0]; g.dh = d3[1]; g.dw = d3[2]; g.pd = p3[0]; g.ph = p3[1]; g.pw = p3[2];
+  const int cip = global ? 1 : (int)n.i64("count_include_pad", 0);
+  P.need(x_eid, kLogical);
+  P.produce(y_eid, kLogical);
+  P.rt->hbm_bytes += X.bytes() + Y.bytes();
+  P.add_step(n.name + " -> fp32 pooling kernel", [=](RunCtx& c) {
+    launch_fpool((const float*)c.ptr(x_eid, kLogical), (float*)c.ptr(y_eid, kLogical), g, is_avg ? 1 : 0, cip, c.s);
+  });
+}
+
+// Is this node one of the float operators?  (Every operand float32; integer graphs never get here.)
+static bool is_float_node(Planner& P, int nid) {
+  const GNode& n = P.g.nodes[nid];
+  if (P.ent[P.g.eid(nid, 0)].dtype != kF32) return false;
+  for (auto& in : n.inputs)
+    if (P.ent[P.root((int)P.g.eid(in))].dtype != kF32) return false;
+  return !n.inputs.empty();
+}
+
 static void plan_transpose(Planner& P, int nid) {
   const GNode& n = P.g.nodes[nid];
   const int x_eid = (int)P.g.eid(n.inputs[0]), y_eid = (int)P.g.eid(nid, 0);
@@ -1830,8 +2167,29 @@ static void build_plan(tkb_runtime* rt) {
     if (n.op_type != "kernel") continue;
     P.cur_nid = (int)nid;
     const std::string& op = n.name;
-    if (n.num_outputs != 1) fail("Unsupported op: %s with %u outputs", op.c_str(), n.num_outputs);
-    if (op == "tachikoma.qnn.conv2d") plan_conv(P, (int)nid, true);
+    if (n.num_outputs != 1 && op != "nn.batch_norm") fail("Unsupported op: %s with %u outputs", op.c_str(), n.num_outputs);
+    // float32 half of the op list, dispatched by name exactly as tachikoma_json_runtime.cc:255-285 does
+    static const std::set<std::string> float_unary = {"abs", "exp", "log", "sqrt", "round", "nn.relu", "nn.leaky_relu", "tanh", "sigmoid"};  // float clip: plan_unary
+    auto plan_float = [&]() -> bool {
+      if (name_has(op, "qnn.") || !is_float_node(P, (int)nid)) return false;
+      const bool deconv = name_has(op, "deconv1d") || name_has(op, "deconv2d") || name_has(op, "deconv3d") ||
+                          name_has(op, "conv1d_transpose") || name_has(op, "conv2d_transpose") || name_has(op, "conv3d_transpose");
+      const bool conv = name_has(op, "conv1d") || name_has(op, "conv2d") || name_has(op, "conv3d");
+      if (deconv) plan_float_conv(P, (int)nid, true);
+      else if (conv) plan_float_conv(P, (int)nid, false);
+      else if (name_has(op, "dense")) plan_float_dense(P, (int)nid);
+      else if (op == "nn.batch_norm") plan_float_batch_norm(P, (int)nid);
+      else if (op == "nn.max_pool2d" || op == "nn.max_pool3d" || op == "nn.avg_pool2d" || op == "nn.avg_pool3d" || op == "nn.global_avg_pool2d") plan_float_pool(P, (int)nid);
+      else if (float_unary.count(op)) plan_float_unary(P, (int)nid);
+      else if (op == "nn.softmax") plan_float_softmax(P, (int)nid);
+      else if (op == "add" || op == "multiply") plan_float_binary(P, (int)nid);
+      else if (op == "nn.layer_norm") plan_float_layer_norm(P, (int)nid);
+      else if (op == "nn.batch_matmul") plan_float_batch_matmul(P, (int)nid);
+      else return false;
+      return true;
+    };
+    if (plan_float()) {}
+    else if (op == "tachikoma.qnn.conv2d") plan_conv(P, (int)nid, true);
     else if (op == "tachikoma.qnn.dense") plan_dense(P, (int)nid, true);
     else if (op == "qnn.conv2d") plan_conv(P, (int)nid, false);
     else if (op == "qnn.dense") plan_dense(P, (int)nid, false);

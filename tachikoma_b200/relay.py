@@ -23,6 +23,9 @@ __all__ = [
     "qnn_quantize", "qnn_dequantize", "bias_add", "add",
     "clip", "cast", "max_pool2d", "avg_pool2d", "global_avg_pool2d", "pad", "reshape",
     "batch_flatten", "transpose",
+    "conv1d", "conv2d", "conv3d", "conv2d_transpose", "conv3d_transpose", "dense", "batch_matmul", "batch_norm", "layer_norm",
+    "softmax", "relu", "tanh", "sigmoid", "abs_", "exp", "log", "sqrt", "round_", "erf", "leaky_relu", "multiply", "divide",
+    "max_pool3d", "avg_pool3d",
 ]
 
 
@@ -342,6 +345,166 @@ def batch_flatten(data):
 def transpose(data, axes):
     axes = [int(a) for a in axes]
     return Call("transpose", [data], dict(axes=axes), [data.shape[a] for a in axes], data.dtype)
+
+
+# ----------------------------------------------------------------------------------------------
+# float32 operators of the tachikoma float patterns (python/tvm/relay/op/contrib/tachikoma.py:88-114): constructors with
+# relay.nn.* / relay.* signatures and type relations, default layouts NC[D]HW x OI[D]HW
+# ----------------------------------------------------------------------------------------------
+
+def _ntuple(v, n):
+    v = [int(v)] if isinstance(v, (int, np.integer)) else [int(x) for x in v]
+    return v * n if len(v) == 1 else v
+
+
+def _npad(p, n):
+    p = _ntuple(p, n)
+    if len(p) == n:  # (p_d, p_h, p_w) -> begin + end, as relay's GetPadding*
+        p = p + p
+    assert len(p) == 2 * n, p
+    return p
+
+
+def _conv_nd(op, sp, data, weight, strides, padding, dilation, groups, channels, kernel_size, data_layout, kernel_layout,
+             out_layout, out_dtype):
+    assert len(data.shape) == sp + 2 and len(weight.shape) == sp + 2, (op, data.shape, weight.shape)
+    st, di, pd = _ntuple(strides, sp), _ntuple(dilation, sp), _npad(padding, sp)
+    o = int(weight.shape[0])
+    assert weight.shape[1] * groups == data.shape[1], (op, data.shape, weight.shape, groups)
+    spatial = [(data.shape[2 + i] + pd[i] + pd[sp + i] - di[i] * (weight.shape[2 + i] - 1) - 1) // st[i] + 1 for i in range(sp)]
+    attrs = dict(strides=st, padding=pd, dilation=di, groups=int(groups), channels=int(channels if channels else o),
+                 kernel_size=[int(k) for k in (kernel_size if kernel_size is not None else weight.shape[2:])],
+                 data_layout=data_layout, kernel_layout=kernel_layout, out_layout=out_layout, out_dtype=out_dtype)
+    return Call(op, [data, weight], attrs, [data.shape[0], o] + spatial, data.dtype)
+
+
+def conv1d(data, weight, strides=1, padding=0, dilation=1, groups=1, channels=None, kernel_size=None, data_layout="NCW",
+           kernel_layout="OIW", out_layout="", out_dtype=""):
+    """relay.nn.conv1d (python/tvm/relay/op/nn/nn.py:30-117)."""
+    return _conv_nd("nn.conv1d", 1, data, weight, strides, padding, dilation, groups, channels, kernel_size, data_layout,
+                    kernel_layout, out_layout, out_dtype)
+
+
+def conv2d(data, weight, strides=(1, 1), padding=(0, 0), dilation=(1, 1), groups=1, channels=None, kernel_size=None,
+           data_layout="NCHW", kernel_layout="OIHW", out_layout="", out_dtype=""):
+    """relay.nn.conv2d (nn.py:120-227)."""
+    return _conv_nd("nn.conv2d", 2, data, weight, strides, padding, dilation, groups, channels, kernel_size, data_layout,
+                    kernel_layout, out_layout, out_dtype)
+
+
+def conv3d(data, weight, strides=(1, 1, 1), padding=(0, 0, 0), dilation=(1, 1, 1), groups=1, channels=None, kernel_size=None,
+           data_layout="NCDHW", kernel_layout="OIDHW", out_layout="", out_dtype=""):
+    """relay.nn.conv3d (nn.py:230-330)."""
+    return _conv_nd("nn.conv3d", 3, data, weight, strides, padding, dilation, groups, channels, kernel_size, data_layout,
+                    kernel_layout, out_layout, out_dtype)
+
+
+def _conv_transpose_nd(op, sp, data, weight, strides, padding, dilation, groups, channels, kernel_size, data_layout,
+                       kernel_layout, out_layout, output_padding, out_dtype):
+    assert len(data.shape) == sp + 2 and len(weight.shape) == sp + 2
+    st, di, pd, opad = _ntuple(strides, sp), _ntuple(dilation, sp), _npad(padding, sp), _ntuple(output_padding, sp)
+    assert weight.shape[0] == data.shape[1], (op, data.shape, weight.shape)
+    o = int(weight.shape[1]) * int(groups)
+    spatial = [(data.shape[2 + i] - 1) * st[i] - pd[i] - pd[sp + i] + di[i] * (weight.shape[2 + i] - 1) + 1 + opad[i] for i in range(sp)]
+    attrs = dict(strides=st, padding=pd, dilation=di, groups=int(groups), channels=int(channels if channels else o),
+                 kernel_size=[int(k) for k in (kernel_size if kernel_size is not None else weight.shape[2:])],
+                 data_layout=data_layout, kernel_layout=kernel_layout, out_layout=out_layout, output_padding=opad,
+                 out_dtype=out_dtype)
+    return Call(op, [data, weight], attrs, [data.shape[0], o] + spatial, data.dtype)
+
+
+def conv2d_transpose(data, weight, strides=(1, 1), padding=(0, 0), dilation=(1, 1), groups=1, channels=None, kernel_size=None,
+                     data_layout="NCHW", kernel_layout="IOHW", out_layout="", output_padding=(0, 0), out_dtype=""):
+    """relay.nn.conv2d_transpose (nn.py:515-590): weight is [in, out / groups, kh, kw]."""
+    return _conv_transpose_nd("nn.conv2d_transpose", 2, data, weight, strides, padding, dilation, groups, channels, kernel_size,
+                              data_layout, kernel_layout, out_layout, output_padding, out_dtype)
+
+
+def conv3d_transpose(data, weight, strides=(1, 1, 1), padding=(0, 0, 0), dilation=(1, 1, 1), groups=1, channels=None,
+                     kernel_size=None, data_layout="NCDHW", kernel_layout="OIDHW", out_layout="", output_padding=(0, 0, 0),
+                     out_dtype=""):
+    """relay.nn.conv3d_transpose (nn.py:430-512): the layout string says OIDHW, the tensor is [in, out / groups, d, h, w]
+    (the reference runtime's own work-around, tachikoma_json_runtime.cc:420-423)."""
+    return _conv_transpose_nd("nn.conv3d_transpose", 3, data, weight, strides, padding, dilation, groups, channels, kernel_size,
+                              data_layout, kernel_layout, out_layout, output_padding, out_dtype)
+
+
+def dense(data, weight, units=None, out_dtype=""):
+    """relay.nn.dense: weight is [units, in]."""
+    assert data.shape[-1] == weight.shape[1], (data.shape, weight.shape)
+    return Call("nn.dense", [data, weight], dict(units=int(units if units else weight.shape[0]), out_dtype=out_dtype),
+                tuple(data.shape[:-1]) + (weight.shape[0],), data.dtype)
+
+
+def batch_matmul(tensor_a, tensor_b, out_dtype="", transpose_a=False, transpose_b=True):
+    """relay.nn.batch_matmul (nn.py:2226): NT by default."""
+    m, k = (tensor_a.shape[2], tensor_a.shape[1]) if transpose_a else (tensor_a.shape[1], tensor_a.shape[2])
+    n, k2 = (tensor_b.shape[1], tensor_b.shape[2]) if transpose_b else (tensor_b.shape[2], tensor_b.shape[1])
+    assert k == k2, (tensor_a.shape, tensor_b.shape)
+    return Call("nn.batch_matmul", [tensor_a, tensor_b], dict(out_dtype=out_dtype, transpose_a=bool(transpose_a),
+                                                               transpose_b=bool(transpose_b)),
+                (max(tensor_a.shape[0], tensor_b.shape[0]), m, n), tensor_a.dtype)
+
+
+def batch_norm(data, gamma, beta, moving_mean, moving_var, axis=1, epsilon=1e-5, center=True, scale=True):
+    """relay.nn.batch_norm(...)[0] (nn.py:1963): the normalised tensor.  The reference's operator returns a 3-tuple of which
+    inference uses field 0 only; the JSON node still declares the three outputs (serialize())."""
+    return Call("nn.batch_norm", [data, _c(gamma), _c(beta), _c(moving_mean), _c(moving_var)],
+                dict(axis=int(axis), epsilon=float(epsilon), center=bool(center), scale=bool(scale)), data.shape, data.dtype)
+
+
+def layer_norm(data, gamma, beta, axis=-1, epsilon=1e-5, center=True, scale=True):
+    """relay.nn.layer_norm (nn.py:2112)."""
+    return Call("nn.layer_norm", [data, _c(gamma), _c(beta)],
+                dict(axis=int(axis), epsilon=float(epsilon), center=bool(center), scale=bool(scale)), data.shape, data.dtype)
+
+
+def softmax(data, axis=-1):
+    return Call("nn.softmax", [data], dict(axis=int(axis)), data.shape, data.dtype)
+
+
+def _unary(op):
+    def f(data):
+        return Call(op, [data], {}, data.shape, data.dtype)
+    f.__name__ = op.split(".")[-1]
+    f.__doc__ = f"relay.{op}"
+    return f
+
+
+relu, tanh, sigmoid, abs_, exp, log, sqrt, round_, erf = (_unary(o) for o in (
+    "nn.relu", "tanh", "sigmoid", "abs", "exp", "log", "sqrt", "round", "erf"))
+
+
+def leaky_relu(data, alpha=0.01):
+    return Call("nn.leaky_relu", [data], dict(alpha=float(alpha)), data.shape, data.dtype)
+
+
+def _binary(op):
+    def f(lhs, rhs):
+        rhs = _c(rhs, lhs.dtype)
+        return Call(op, [lhs, rhs], {}, np.broadcast_shapes(lhs.shape, rhs.shape), lhs.dtype)
+    f.__name__ = op
+    return f
+
+
+multiply, divide = _binary("multiply"), _binary("divide")
+
+
+def max_pool3d(data, pool_size=(1, 1, 1), strides=(1, 1, 1), dilation=(1, 1, 1), padding=(0, 0, 0), layout="NCDHW"):
+    return _pool3d("nn.max_pool3d", data, pool_size, strides, dilation, padding, layout, {})
+
+
+def avg_pool3d(data, pool_size=(1, 1, 1), strides=(1, 1, 1), dilation=(1, 1, 1), padding=(0, 0, 0), layout="NCDHW",
+               count_include_pad=False):
+    return _pool3d("nn.avg_pool3d", data, pool_size, strides, dilation, padding, layout, dict(count_include_pad=bool(count_include_pad)))
+
+
+def _pool3d(op, data, pool_size, strides, dilation, padding, layout, extra):
+    assert layout == "NCDHW" and len(data.shape) == 5
+    ps, st, di, pd = _ntuple(pool_size, 3), _ntuple(strides, 3), _ntuple(dilation, 3), _npad(padding, 3)
+    spatial = [(data.shape[2 + i] + pd[i] + pd[3 + i] - di[i] * (ps[i] - 1) - 1) // st[i] + 1 for i in range(3)]
+    return Call(op, [data], dict(pool_size=ps, strides=st, dilation=di, padding=pd, layout=layout, out_layout="",
+                                 ceil_mode=False, **extra), list(data.shape[:2]) + spatial, data.dtype)
 
 
 # ----------------------------------------------------------------------------------------------

@@ -44,9 +44,8 @@ _FLOAT_OPS = ["conv1d", "conv2d", "conv3d", "deconv2d", "deconv3d", "dense"]
 
 
 def pattern_table():
-    """Composite names in the reference's order (tachikoma.py:418-458).  Only the two QNN
-    composites are executable by this runtime; the float patterns are listed so that callers can see
-    the same table, and are rejected at init with the reference's own "Unsupported op" error."""
+    """Composite names in the reference's order (tachikoma.py:418-458): the two QNN composites (the tensor-core integer
+    path) and the float patterns (conv / deconv / dense [+ bias] [+ sum] [+ activation], executed as fp32 kernels)."""
     names = ["tachikoma.qnn.conv2d", "tachikoma.qnn.dense", "tachikoma.conv2d_bias_sum_relu",
              "tachikoma.conv2d_bias_sum"]
     for op in _FLOAT_OPS:
@@ -251,6 +250,14 @@ SUPPORTED_OPS = {
     "transpose",
 }
 
+#: float32 operators the CUDA runtime executes as single-operator nodes (tachikoma.py:88-114, float operands only)
+FLOAT_SUPPORTED_OPS = {
+    "nn.batch_norm", "nn.conv1d", "nn.conv2d", "nn.conv3d", "nn.conv2d_transpose", "nn.conv3d_transpose", "nn.dense",
+    "nn.max_pool2d", "nn.avg_pool2d", "nn.global_avg_pool2d", "nn.max_pool3d", "nn.avg_pool3d", "abs", "clip", "exp", "log",
+    "sqrt", "round", "nn.relu", "nn.leaky_relu", "tanh", "sigmoid", "nn.softmax", "add", "multiply", "nn.layer_norm",
+    "nn.batch_matmul",
+}
+
 
 def _hardswish(x):
     return x * np.clip(x + 3.0, 0.0, 6.0) / 6.0
@@ -351,6 +358,131 @@ def legalize_qnn_for_tachikoma(func, mode="dnnl_float"):
     return R.Function(func.params, visit(func.body), func.attrs)
 
 
+# ------------------------------------------------------------------------------------------------
+# float patterns (tachikoma.py:131-160 append_eltwise_ops, :163-187 make_conv_pattern, :190-213 conv_bias_sum[_relu],
+# :296-321 make_dense_pattern, :324-353 names): conv / deconv / dense [+ bias] [+ sum] [+ activation] -> one composite
+# ------------------------------------------------------------------------------------------------
+_FLOAT_ROOTS = {"nn.conv1d": "tachikoma.conv1d", "nn.conv2d": "tachikoma.conv2d", "nn.conv3d": "tachikoma.conv3d",
+                "nn.conv2d_transpose": "tachikoma.deconv2d", "nn.conv3d_transpose": "tachikoma.deconv3d",
+                "nn.dense": "tachikoma.dense"}
+
+
+def _is_call(e, op):
+    return isinstance(e, R.Call) and e.op == op
+
+
+def _strip_activation(e, users):
+    """Returns (inner, act, attrs, shared) if ``e`` is the last node of an activation sub-pattern over ``inner``; ``shared``
+    = how many users ``inner`` has inside the pattern.  Interior nodes must have no user outside the pattern."""
+    def n_users(x):
+        return len(users.get(id(x), []))
+
+    for op, act in (("nn.relu", "relu"), ("tanh", "tanh"), ("sigmoid", "sigmoid"), ("clip", "clip")):
+        if _is_call(e, op):
+            return e.args[0], act, ({"a_min": e.attrs["a_min"], "a_max": e.attrs["a_max"]} if act == "clip" else {}), 1
+    if _is_call(e, "multiply"):
+        a, b = e.args
+        # swish: multiply(op, sigmoid(op))
+        if _is_call(b, "sigmoid") and b.args[0] is a and n_users(b) == 1:
+            return a, "swish", {}, 2
+        # mish: multiply(op, tanh(log(add(exp(op), c))))
+        if _is_call(b, "tanh") and n_users(b) == 1 and _is_call(b.args[0], "log") and n_users(b.args[0]) == 1:
+            ad = b.args[0].args[0]
+            if _is_call(ad, "add") and n_users(ad) == 1 and _is_call(ad.args[0], "exp") and n_users(ad.args[0]) == 1 and \
+                    ad.args[0].args[0] is a and _is_const(ad.args[1]):
+                return a, "mish", {}, 2
+        # gelu: multiply(multiply(op, add(erf(divide(op, c1)), c2)), c3)
+        if _is_call(a, "multiply") and n_users(a) == 1 and _is_const(b):
+            x, added = a.args
+            if _is_call(added, "add") and n_users(added) == 1 and _is_const(added.args[1]) and _is_call(added.args[0], "erf") and \
+                    n_users(added.args[0]) == 1:
+                dv = added.args[0].args[0]
+                if _is_call(dv, "divide") and n_users(dv) == 1 and dv.args[0] is x and _is_const(dv.args[1]):
+                    return x, "gelu", {}, 2
+    return None
+
+
+def _match_float_chain(tail, users):
+    """Longest float pattern that ends at ``tail``; returns (name, root, bias, sum_src, extra_attrs) or None."""
+    if not isinstance(tail, R.Call) or tail.dtype != "float32":
+        return None
+
+    def n_users(x):
+        return len(users.get(id(x), []))
+
+    cands = []
+    st = _strip_activation(tail, users)
+    if st is not None:
+        cands.append(st)
+    cands.append((tail, None, {}, None))
+    for inner, act, extra, shared in cands:
+        cur = inner
+        if shared is not None and n_users(cur) != shared:
+            continue
+        # conv2d + bias + sum [+ relu] (tachikoma.py:190-213, predicate :251-264)
+        if act in (None, "relu") and _is_call(cur, "add") and cur.args[0].shape == cur.args[1].shape and \
+                _is_call(cur.args[0], "add") and n_users(cur.args[0]) == 1:
+            b = cur.args[0]
+            if _is_call(b.args[0], "nn.conv2d") and n_users(b.args[0]) == 1 and \
+                    int(np.prod(b.args[1].shape)) == b.args[0].attrs["channels"]:
+                name = "tachikoma.conv2d_bias_sum" + ("_relu" if act else "")
+                return name, b.args[0], b.args[1], cur.args[1], {}
+        bias = None
+        root = cur
+        if isinstance(cur, R.Call) and cur.op in ("add", "nn.bias_add"):
+            # add is commutative for the dataflow matcher: (root, bias) or (bias, root)
+            for r0, b0, first in ((cur.args[0], cur.args[1], True), (cur.args[1], cur.args[0], False)):
+                if not (isinstance(r0, R.Call) and r0.op in _FLOAT_ROOTS and n_users(r0) == 1) or (cur.op == "nn.bias_add" and not first):
+                    continue
+                ok = True
+                if "conv" in r0.op and act in (None, "relu"):
+                    # make_bias_add_pattren_predicate / add_checker (:267-293): evaluated when the pattern ends in the add
+                    # or in relu(add); it looks at args[0] / args[1] as written and accepts nn.conv2d with a bias of
+                    # `channels` elements only
+                    ok = first and r0.op == "nn.conv2d" and int(np.prod(b0.shape)) == r0.attrs["channels"]
+                if ok:
+                    bias, root = b0, r0
+                    break
+        if not (isinstance(root, R.Call) and root.op in _FLOAT_ROOTS):
+            continue
+        if root.dtype != "float32" or any(a.dtype != "float32" for a in root.args):
+            continue
+        if bias is None and root is not cur:
+            continue
+        name = _FLOAT_ROOTS[root.op] + ("_bias" if bias is not None else "") + (f"_{act}" if act else "")
+        return name, root, bias, None, extra  # a bare conv / dense is the pattern without bias and activation
+    return None
+
+
+def merge_float_composites(func):
+    """MergeComposite of the float rows of pattern_table() on the mini IR."""
+    users = _users(func.body)
+    memo = {}
+
+    def visit(e):
+        if id(e) in memo:
+            return memo[id(e)]
+        r = e
+        if isinstance(e, R.Call):
+            m = _match_float_chain(e, users)
+            if m is not None:
+                name, root, bias, sum_src, extra = m
+                args = [visit(root.args[0]), visit(root.args[1])]
+                if bias is not None:
+                    args.append(R.Constant(bias.data.reshape(-1)) if _is_const(bias) else visit(bias))
+                if sum_src is not None:
+                    args.append(visit(sum_src))
+                attrs = dict(root.attrs)
+                attrs.update(extra)
+                r = R.Call(name, args, attrs, e.shape, e.dtype)
+            else:
+                r = R.Call(e.op, [visit(a) for a in e.args], e.attrs, e.shape, e.dtype)
+        memo[id(e)] = r
+        return r
+
+    return R.Function(func.params, visit(func.body), func.attrs)
+
+
 #: tachikoma.py:711-723 (IsComputeIntensiveGraph) plus the QNN forms the integer path offloads
 COMPUTE_INTENSIVE_OPS = {
     "nn.conv1d", "nn.conv2d", "nn.conv2d_transpose", "nn.conv3d", "nn.conv3d_transpose", "nn.dense", "nn.layer_norm",
@@ -374,32 +506,8 @@ def prune_tachikoma_subgraphs(func):
     return func
 
 
-def _float_rewrite(func, name, pattern_ops, target):
-    """The reference's DFPatternCallback rewrites below work on FLOAT graphs.  On a graph without the pattern's
-    operators a rewrite is the identity (what `rewrite(callback, expr)` returns when nothing matches), which is the
-    case for every integer QNN graph; a graph that does hold them would end in operators the CUDA runtime rejects,
-    so it fails here with the runtime's own message instead of at init."""
-    present = sorted({e.op for e in R.post_order(func.body) if isinstance(e, R.Call)} & set(pattern_ops))
-    if present:
-        raise ValueError(f"Unsupported op: {target} ({name} matches float operators {present}; the tachikoma CUDA "
-                         "runtime executes the integer QNN path only)")
-    return func
-
-
-def rewrite_layer_norm(func):
-    """tachikoma.py:796-857: mean/subtract/power/mean/add/sqrt/divide/multiply/add -> nn.layer_norm."""
-    return _float_rewrite(func, "rewrite_layer_norm", ("mean", "variance", "power", "sqrt", "rsqrt"), "nn.layer_norm")
-
-
-def rewrite_dense_bias_gelu_reshape_last(func):
-    """tachikoma.py:860-951: nn.dense -> reshape -> add [-> erf GELU] reordered so that the reshape comes last."""
-    return _float_rewrite(func, "rewrite_dense_bias_gelu_reshape_last", ("nn.dense", "erf"), "nn.dense")
-
-
-def rewrite_resnetv1(func):
-    """tachikoma.py:954-1119: moves the stride of a ResNet-v1 downsample block's 1x1 convolutions forward (float
-    nn.conv2d / nn.relu graphs)."""
-    return _float_rewrite(func, "rewrite_resnetv1", ("nn.conv2d", "nn.relu"), "nn.conv2d")
+# rewrite_layer_norm, rewrite_dense_bias_gelu_reshape_last, rewrite_resnetv1 (tachikoma.py:796-1119): rewrites.py
+from .rewrites import rewrite_dense_bias_gelu_reshape_last, rewrite_layer_norm, rewrite_resnetv1  # noqa: E402,F401
 
 
 def partition_for_tachikoma(func, params=None, mode="int", symbol="tvmgen_default_tachikoma_main_0"):
@@ -412,8 +520,11 @@ def partition_for_tachikoma(func, params=None, mode="int", symbol="tvmgen_defaul
     func = fold_explicit_padding(func)
     func = legalize_qnn_unary(func)  # relay.qnn.transform.Legalize: table-lookup unary operators
     func = legalize_qnn_for_tachikoma(func, mode=mode)
+    func = merge_float_composites(func)
     for e in R.post_order(func.body):
         if isinstance(e, R.Call) and not e.op.startswith("tachikoma.") and e.op not in SUPPORTED_OPS:
+            if e.op in FLOAT_SUPPORTED_OPS and e.dtype == "float32" and all(a.dtype == "float32" for a in e.args):
+                continue
             logger.info("%s is not supported by the tachikoma CUDA runtime", e.op)
             raise ValueError(f"Unsupported op: {e.op}")
     func = prune_tachikoma_subgraphs(func)
@@ -481,6 +592,16 @@ def serialize(func, symbol=None):
         attrs["num_inputs"] = str(len(e.args))
         attrs["num_outputs"] = "1"
         add_node(dict(op="kernel", name=e.op, inputs=[entry[id(a)] for a in e.args], attrs=attrs), e)
+        if e.op == "nn.batch_norm":
+            # the operator is a 3-tuple (normalised data, moving mean, moving variance): the JSON node declares all three
+            # entries (codegen_json.h:203-224), inference reads entry 0 only (tachikoma_json_runtime.cc:556)
+            c = [int(e.args[1].shape[0])]
+            attrs["num_outputs"] = "3"
+            attrs["shape"] = [[list(e.shape), c, c]]
+            attrs["dtype"] = [[e.dtype] * 3]
+    row_ptr = [0]
+    for n in nodes:
+        row_ptr.append(row_ptr[-1] + int(n["attrs"].get("num_outputs", "1")))
     graph = dict(nodes=nodes, arg_nodes=[i for i, n in enumerate(nodes) if n["op"] != "kernel"],
-                 heads=[entry[id(func.body)]], node_row_ptr=list(range(len(nodes) + 1)))
+                 heads=[entry[id(func.body)]], node_row_ptr=row_ptr)
     return symbol, json.dumps(graph), const_names, consts

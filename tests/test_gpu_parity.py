@@ -835,8 +835,16 @@ def test_int8_peak_probe_runs():
 
 
 def test_unsupported_op_fails_at_init_not_run():
+    # an operator outside the reference's dispatch (tachikoma_json_runtime.cc:255-286): same message, at init
     xv = R.var("x", (1, 4), "float32")
-    part = R.Function([xv], R.Call("nn.softmax", [xv], {}, (1, 4), "float32"))
+    part = R.Function([xv], R.Call("nn.log_softmax", [xv], {}, (1, 4), "float32"))
+    sym, js, names, consts = T.serialize(part)
+    mod = RT.TachikomaJSONRuntime(sym, js, names)
+    with pytest.raises(RT.TachikomaError, match="Unsupported op: nn.log_softmax"):
+        mod.init(consts)
+    # a float operator on integer tensors is not the float path either
+    xi = R.var("x", (1, 4), "int32")
+    part = R.Function([xi], R.Call("nn.softmax", [xi], {"axis": -1}, (1, 4), "int32"))
     sym, js, names, consts = T.serialize(part)
     mod = RT.TachikomaJSONRuntime(sym, js, names)
     with pytest.raises(RT.TachikomaError, match="Unsupported op: nn.softmax"):

@@ -270,6 +270,27 @@ def fold_explicit_padding(func):
                     attrs = dict(e.attrs)
                     attrs["padding"] = [int(pw[2][0]), int(pw[3][0]), int(pw[2][1]), int(pw[3][1])]
                     out = R.Call(e.op, [visit(p.args[0])] + args[1:], attrs, e.shape, e.dtype)
+            # float operators (src/relay/transforms/fold_explicit_padding.cc:45-180): zero padding folds into
+            # nn.conv1d/2d/3d and into nn.avg_pool2d/3d (which then counts the padding), lowest-value padding into max pools
+            elif (e.op in ("nn.conv1d", "nn.conv2d", "nn.conv3d", "nn.avg_pool2d", "nn.avg_pool3d", "nn.max_pool2d", "nn.max_pool3d")
+                    and e.dtype == "float32" and isinstance(p, R.Call) and p.op == "nn.pad" and users.get(id(p), 0) == 1
+                    and p.attrs.get("pad_mode", "constant") == "constant" and isinstance(p.args[1], R.Constant)
+                    and e.attrs.get("data_layout", e.attrs.get("layout", "NC")).startswith("NC")):
+                pw = [list(map(int, w)) for w in p.attrs["pad_width"]]
+                sp = len(pw) - 2
+                pv = float(np.asarray(p.args[1].data).reshape(-1)[0])
+                is_max = "max_pool" in e.op
+                value_ok = (pv == float("-inf") or pv <= float(np.finfo(np.float32).min)) if is_max else pv == 0.0
+                old = [int(v) for v in e.attrs["padding"]]
+                if len(old) == sp:
+                    old = old + old
+                pool_ok = "pool" not in e.op or is_max or e.attrs.get("count_include_pad", False) or all(v == 0 for v in old)
+                if pw[0] == [0, 0] and pw[1] == [0, 0] and value_ok and pool_ok and len(old) == 2 * sp:
+                    attrs = dict(e.attrs)
+                    attrs["padding"] = [old[i] + pw[2 + i][0] for i in range(sp)] + [old[sp + i] + pw[2 + i][1] for i in range(sp)]
+                    if "avg_pool" in e.op:
+                        attrs["count_include_pad"] = True
+                    out = R.Call(e.op, [visit(p.args[0])] + args[1:], attrs, e.shape, e.dtype)
         memo[id(e)] = out
         return out
 

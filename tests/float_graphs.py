@@ -219,7 +219,7 @@ def other_cases():
 
 
 def all_cases():
-    return conv_cases() + dense_cases() + other_cases()
+    return conv_cases() + dense_cases() + other_cases() + pad_fold_cases()
 
 
 def inputs_for(func, seed=3):
@@ -232,3 +232,23 @@ def inputs_for(func, seed=3):
             v = np.abs(v) + np.float32(0.1)
         out[p.name] = v
     return out
+
+
+def pad_fold_cases():
+    """test_fuse_pad_avg_pool (test_tachikoma.py:1256-1270) and the convolution / max-pool forms of FoldExplicitPadding."""
+    rng = _rng(4)
+    cases = []
+    x = R.var("x", (1, 24, 17, 17))
+    p = R.pad(x, [[0, 0], [0, 0], [1, 1], [1, 1]])
+    cases.append(("pad_avg_pool", R.Function([x], R.avg_pool2d(p, (3, 3))), ["nn.avg_pool2d"]))
+    x = R.var("x", (1, 8, 9, 9))
+    p = R.pad(x, [[0, 0], [0, 0], [1, 2], [0, 1]])
+    cases.append(("pad_conv2d_relu", R.Function([x], R.relu(R.conv2d(p, _w(rng, (4, 8, 3, 3)), padding=(1, 1)))), ["tachikoma.conv2d_relu"]))
+    x = R.var("x", (1, 8, 9, 9))
+    p = R.pad(x, [[0, 0], [0, 0], [1, 1], [1, 1]], pad_value=float("-inf"))
+    cases.append(("pad_max_pool", R.Function([x], R.max_pool2d(p, (3, 3), (2, 2))), ["nn.max_pool2d"]))
+    # a non-zero pad value is not foldable into a convolution: the pad stays an operator
+    x = R.var("x", (1, 8, 9, 9))
+    p = R.pad(x, [[0, 0], [0, 0], [1, 1], [1, 1]], pad_value=0.5)
+    cases.append(("pad_kept_conv2d", R.Function([x], R.conv2d(p, _w(rng, (4, 8, 3, 3)))), ["nn.pad", "tachikoma.conv2d"]))
+    return cases

@@ -530,7 +530,10 @@ def main():
             "achieved": achieved_tops,
             "peak": peak_tops, "unit": "TFLOP/s", "frac": achieved_tops / peak_tops if peak_tops else None, "traffic": traffic,
             "note": "int8 ops (2*MAC) counted as FLOPs; achieved = 2 * MACs of a step / summed CUDA-event time of the tcgen05 launches "
-                    "(events on the launching stream around every launch, the host enqueues behind a device spin); peak = this run's "
+                    "(events on the launching stream around every run of consecutive tcgen05 launches -- layers that follow one another "
+                    "with no other kernel in between share one pair, so event cost and the loss of launch overlap an event between two "
+                    "kernels causes are not billed to them; TKB_TC_TIME_PER_LAUNCH=1 restores a pair per launch; the host enqueues "
+                    "behind a device spin); peak = this run's "
                     "tcgen05 kind::i8 issue-rate probe (MEASURED_PEAKS.json has no int8 entry; 2x its bf16 burst = %.0f); traffic = DRAM "
                     "bytes per launch from profiles/%s" % (2 * peaks.get("bf16_tflops", 0), traffic_src),
             "avg_launch_us": 1e3 * tc_ms / tc_n if tc_n else None, "launches_per_step": tc_n // runs if runs else None,

@@ -95,13 +95,16 @@ const char* tkb_last_error(void);
  *                           "tc_pair" (as "tc" with the cta_group::2 pair kernel, csrc/kernels_tc_pair.cu, for layers with
  *                           a multiple of 128 output channels) -- all
  *                           routes produce identical bits, everything after "tc" exists for A/B tests;
- *             "time_tc"   = "0"|"1" (bracket every tcgen05 launch with CUDA events, see tkb_tc_time). */
+ *             "time_tc"   = "0"|"1" (bracket every run of consecutive tcgen05 launches with CUDA events on the compute
+ *                           stream, see tkb_tc_time). */
 int tkb_set_option(tkb_handle h, const char* key, const char* value);
 /* Number of kernels this library launched on behalf of h since creation (bench.py "gpu_launches"). */
 int64_t tkb_launch_count(tkb_handle h);
 /* Human-readable plan: one line per kernel node with the kernel chosen and its algorithmic work. */
 const char* tkb_plan_summary(tkb_handle h);
-/* With option time_tc=1: summed device time (ms) and count of the tcgen05 GEMM launches of the last run. */
+/* With option time_tc=1: summed device time (ms) of the tcgen05 launches of the last run and their count.  Launches that
+ * follow one another with nothing else launched in between share one event pair (an event between two kernels costs
+ * 2-4 us and breaks their programmatic-dependent-launch overlap, which is not the kernels' time). */
 int tkb_tc_time(tkb_handle h, double* ms, int* launches);
 /* Total int8 multiply-accumulates and algorithmic HBM bytes of one run (roofline numerators). */
 int tkb_work(tkb_handle h, int64_t* macs, int64_t* hbm_bytes);

@@ -88,6 +88,7 @@ struct Step {
   std::string desc;
   int nid = -1;   // JSON node this step belongs to (-1: boundary conversion)
   int cand = -1;  // index into tkb_runtime::chain_cands: a tcgen05 layer that may be merged into a chained launch
+  bool is_tc = false;  // launches a tcgen05 layer (kernel timing: consecutive such steps form one timed run)
 };
 
 // A tcgen05 convolution / GEMM step in the form the chained launch (kernels_tc_chain.cu) takes.
@@ -126,6 +127,7 @@ struct Workspace {
   cudaEvent_t ev = nullptr;
   std::vector<cudaEvent_t> tc_events;  // begin/end pairs around tcgen05 GEMM launches (option time_tc)
   size_t tc_used = 0;
+  long long tc_launches = 0;           // tcgen05 launches inside the recorded runs
   int trace_mode = 0;               // trace mode of the LAST run on this stream (0 = nothing captured)
   bool payload_on_host = false;     // first occurrence of every traced tensor has been copied into trace_host
   bool dups_filled = false;         // repeated records (a tensor that is also a consumer's input) have been filled in
@@ -181,14 +183,35 @@ struct RunCtx {
   int mode = 0;               // trace mode of THIS call
   bool time_tc = false;
   std::vector<void*> in_ptr;  // device pointer of each graph input (logical layout)
-  void tc_mark() {  // records an event on the compute stream when kernel timing is on
-    if (!time_tc) return;
+  // Kernel timing (option time_tc): CUDA events on the compute stream around every RUN of consecutive tcgen05 launches.
+  // Back-to-back tensor-core layers (nothing else launched between them: ResNet's layer1 .. layer4) share one event pair,
+  // so the ~2-4 us an event pair costs per launch and the loss of the programmatic-dependent-launch overlap an event
+  // between two kernels causes are not billed to the kernels (they were a sixth of the sum with a pair per launch).
+  bool tc_pending = false;      // a run is open: its end event is recorded when something else is about to be launched
+  long long tc_launch_mark = 0;
+  void tc_record() {
     if (ws->tc_used == ws->tc_events.size()) {
       cudaEvent_t ev;
       cudaEventCreate(&ev);
       ws->tc_events.push_back(ev);
     }
     cudaEventRecord(ws->tc_events[ws->tc_used++], s);
+  }
+  void tc_flush() {  // close the open run (call before launching anything that is not a tcgen05 layer)
+    if (time_tc && tc_pending) { tc_record(); tc_pending = false; }
+  }
+  void tc_begin() {
+    if (!time_tc) return;
+    static const bool per_launch = getenv("TKB_TC_TIME_PER_LAUNCH") != nullptr;  // the old accounting, for comparison
+    if (tc_pending && g_launches == tc_launch_mark && !per_launch) return;       // continues the open run
+    tc_flush();
+    tc_record();
+  }
+  void tc_end() {
+    if (!time_tc) return;
+    tc_pending = true;
+    tc_launch_mark = g_launches;
+    ++ws->tc_launches;
   }
   void* ptr(int eid, int phys) const {
     const Entry* e = &rt->ent[eid];
@@ -230,6 +253,7 @@ struct Planner {
     s.desc = desc;
     s.nid = cur_nid;
     s.cand = cand;
+    s.is_tc = desc.find("tcgen05") != std::string::npos;
     rt->steps.push_back(std::move(s));
     plan << "  [" << cur_nid << "] " << desc << "\n";
   }
@@ -1019,19 +1043,21 @@ static void plan_conv(Planner& P, int nid, bool composite) {
       t.a = c.ptr(x_eid, (from_nchw || unfold) ? kLogical : phys);
       if (unfold) {
         void* x3 = c.ws->arena + scratch_off;
+        c.tc_flush();
         launch_unfold_rows_nchw(t.a, x3, g, c.s);
         t.a = x3;
       }
       if (!direct && !implicit && !unfold) {
         void* col = c.ws->arena + scratch_off;
+        c.tc_flush();
         if (from_nchw) launch_im2col_nchw(t.a, col, g, Kp, c.s);
         else launch_im2col(t.a, col, g, Kp, c.s);
         t.a = col;
       }
       t.y = c.ptr(y_eid, phys);
-      c.tc_mark();
+      c.tc_begin();
       if ((pair ? launch_tc_pair(t, c.s) : launch_tc(t, c.s)) != 0) fail("tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
-      c.tc_mark();
+      c.tc_end();
     });
   } else if (P.rt->conv_impl != "simt" && phys == kNHWC && Cg == 1 && all_zero(ci.zp_w) && dwconv_nhwc_supported(g)) {
     // depthwise: dedicated channels-last kernel (16 channels per thread), tap-major weights
@@ -1191,9 +1217,9 @@ static void plan_dense(Planner& P, int nid, bool composite) {
       t.a = c.ptr(x_eid, kLogical);
       t.w = wpacked ? wpacked : c.ptr(w_eid, kLogical);
       t.y = c.ptr(y_eid, kLogical);
-      c.tc_mark();
+      c.tc_begin();
       if (launch_tc(t, c.s) != 0) fail("tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
-      c.tc_mark();
+      c.tc_end();
     });
   } else {
     if (!ci.float_mode && ci.has_const_bias) epi.bias = (const int32_t*)P.dev_upload(ci.bias_host.data(), ci.bias_host.size() * 4);
@@ -1241,9 +1267,9 @@ static void plan_batch_matmul(Planner& P, int nid) {
       t.a = c.ptr(x_eid, kLogical); t.w = c.ptr(w_eid, kLogical); t.y = c.ptr(y_eid, kLogical);
       t.B = B; t.M = M; t.N = N; t.K = K; t.w_batched = wb; t.a_dtype = xd; t.w_dtype = wd;
       t.e = epi;
-      c.tc_mark();
+      c.tc_begin();
       if (launch_tc(t, c.s) != 0) fail("tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
-      c.tc_mark();
+      c.tc_end();
     } else {
       launch_gemm_simt(c.ptr(x_eid, kLogical), c.ptr(w_eid, kLogical), c.ptr(y_eid, kLogical), B, M, N, K, wb, xd, wd, zpx, zpw, epi, c.s);
     }
@@ -1554,7 +1580,11 @@ static void plan_pad(Planner& P, int nid) {
   auto pw = n.ints("pad_width");
   if ((int)pw.size() != 2 * rank) fail("nn.pad: pad_width must have 2*rank entries");
   const Entry& V = P.cst((int)P.g.eid(n.inputs[1]), "pad_value");
-  const int32_t value = V.dtype == kF32 ? (int32_t)((const float*)V.host.data())[0] : P.cints((int)P.g.eid(n.inputs[1]), "pad_value")[0];
+  int32_t value = V.dtype == kF32 ? (int32_t)((const float*)V.host.data())[0] : P.cints((int)P.g.eid(n.inputs[1]), "pad_value")[0];
+  if (X.dtype == kF32) {  // float tensors: the kernel writes the pad value's bit pattern
+    const float fv = V.dtype == kF32 ? ((const float*)V.host.data())[0] : (float)value;
+    memcpy(&value, &fv, 4);
+  }
   std::array<long long, 4> ishape = {1, 1, 1, 1}, before = {0, 0, 0, 0}, oshape = {1, 1, 1, 1};
   for (int i = 0; i < rank; ++i) {
     const int d = 4 - rank + i;
@@ -2061,9 +2091,9 @@ static void run_chain(RunCtx& c, int id) {
     CUDA_OK(cudaStreamSynchronize(c.s));  // tgt / items are locals; one-time cost
     state.swap(st);
   }
-  c.tc_mark();
+  c.tc_begin();
   if (launch_tc_chain(state.data(), ch.bn, c.s) != 0) fail("chained tcgen05 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
-  c.tc_mark();
+  c.tc_end();
 }
 
 static void form_chains(tkb_runtime* rt, Planner& P) {
@@ -2373,6 +2403,7 @@ static void trace_node(RunCtx& c, size_t lo, size_t hi) {
   }
   if (!any) return;
   cudaStream_t side = c.ws->side;
+  c.tc_flush();
   CUDA_OK(cudaEventRecord(c.ws->ev, c.s));
   CUDA_OK(cudaStreamWaitEvent(side, c.ws->ev, 0));
   c.ws->side_dirty = true;
@@ -2439,6 +2470,7 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
   c.time_tc = rt->time_tc.load();
   c.in_ptr.resize(n_in);
   c.ws->tc_used = 0;
+  c.ws->tc_launches = 0;
   c.ws->trace_mode = 0;  // until this run has been enqueued completely
   c.ws->payload_on_host = c.ws->dups_filled = false;
 
@@ -2464,6 +2496,7 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
   if (mode > 0) ensure_trace_buffers(rt, c.ws, mode);
   size_t rec = 0;
   for (size_t si = 0; si < rt->steps.size(); ++si) {
+    if (!rt->steps[si].is_tc) c.tc_flush();
     rt->steps[si].fn(c);
     const int nid = rt->steps[si].nid;
     const bool last_of_node = si + 1 == rt->steps.size() || rt->steps[si + 1].nid != nid;
@@ -2476,6 +2509,7 @@ static void run_impl(tkb_runtime* rt, const tkb_DLTensor* const* args, int n_arg
     }
   }
   if (mode > 0 && rec < rt->trace_recs.size()) trace_node(c, rec, rt->trace_recs.size());
+  c.tc_flush();
   bool host_out = false;
   for (int j = 0; j < n_out; ++j) {
     const int eid = (int)g.eid(g.heads[j]);
@@ -2819,7 +2853,7 @@ int tkb_tc_time(tkb_handle h, double* ms, int* launches) {
     total += t;
   }
   *ms = total;
-  *launches = (int)(ws->tc_used / 2);
+  *launches = (int)ws->tc_launches;
   TKB_CATCH
 }
 

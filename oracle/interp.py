@@ -445,6 +445,8 @@ def run_expr(func, inputs):
             assert id(e) in env, f"unbound var {e.name}"
         elif isinstance(e, R.Constant):
             env[id(e)] = e.data
+        elif e.op == "tuple":  # several outputs: the function returns the list of its fields
+            env[id(e)] = [env[id(a)] for a in e.args]
         else:
             env[id(e)] = eval_op(e.op, e.attrs, [env[id(a)] for a in e.args])
             assert tuple(env[id(e)].shape) == tuple(e.shape), (e.op, env[id(e)].shape, e.shape)

@@ -167,6 +167,7 @@ struct FConvGeom {
 };
 struct FBcast5 { long long shape[5], ls[5], rs[5]; };
 void launch_fconv(const float* x, const float* w, float* y, const FConvGeom& g, const FPost& post, cudaStream_t s);
+bool fconv_gemm_form(const FConvGeom& g);  // launch_fconv takes the implicit-GEMM kernel (else the direct one)
 void launch_fgemm(const float* A, const float* B, float* C, int batch, int M, int N, int K, long long a_b, long long a_m,
                   long long a_k, long long b_b, long long b_n, long long b_k, const FPost& post, cudaStream_t s);
 void launch_funary(const float* x, float* y, long long n, int act, float a, float b, cudaStream_t s);

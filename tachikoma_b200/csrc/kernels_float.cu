@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 
 #include "kernels.h"
 
@@ -96,9 +97,106 @@ __global__ void fconv_kernel(const float* __restrict__ x, const float* __restric
   }
 }
 
+// ---- convolution as an implicit GEMM: per group, Y[o][pixel] = sum_k W[o][k] * X[pixel][k] with k = (ci, kd, kh, kw) gathered
+// on the fly; 64 channels x 64 pixels x 16 k tiles, 4 x 4 outputs per thread, consecutive threads along the pixels (coalesced
+// gathers along W and coalesced stores into the NC[D]HW output).  Used when a group has at least 16 output channels; depthwise
+// and other thin groups keep the direct kernel.
+__global__ void __launch_bounds__(256) fconv_gemm_kernel(const float* __restrict__ x, const float* __restrict__ w, float* __restrict__ y,
+                                                         FConvGeom g, FPost post) {
+  __shared__ float Ws[16][64 + 1], Xs[16][64 + 1];
+  const int cg = g.C / g.groups, og = g.O / g.groups;
+  const int P = g.OD * g.OH * g.OW, KK = g.KD * g.KH * g.KW, K = cg * KK;
+  const long long pixels = (long long)g.N * P;
+  const int grp = blockIdx.z, o0 = blockIdx.y * 64;
+  const long long p0 = (long long)blockIdx.x * 64;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  // the pixel this thread gathers for (fixed over the k loop)
+  const int lr = threadIdx.x & 63, lk = threadIdx.x >> 6;  // lk: 0..3
+  const long long gp = p0 + lr;
+  const bool p_ok = gp < pixels;
+  int img = 0, id0 = 0, ih0 = 0, iw0 = 0;
+  if (p_ok) {
+    img = (int)(gp / P);
+    int r = (int)(gp - (long long)img * P);
+    const int ow = r % g.OW; r /= g.OW;
+    const int oh = r % g.OH;
+    const int od = r / g.OH;
+    id0 = od * g.sd - g.pd; ih0 = oh * g.sh - g.ph; iw0 = ow * g.sw - g.pw;
+  }
+  const float* xg = x + ((long long)img * g.C + (long long)grp * cg) * g.D * g.H * g.W;
+  const float* wg = w + (long long)grp * og * K;
+  float acc[4][4] = {};
+  for (int k0 = 0; k0 < K; k0 += 16) {
+    for (int i = threadIdx.x; i < 64 * 16; i += 256) {  // weights: consecutive threads along k (contiguous)
+      const int kk = i & 15, r = i >> 4;
+      Ws[kk][r] = (o0 + r < og && k0 + kk < K) ? __ldg(wg + (long long)(o0 + r) * K + k0 + kk) : 0.f;
+    }
+#pragma unroll
+    for (int pass = 0; pass < 4; ++pass) {  // gathered activations: consecutive threads along the pixels
+      const int kk = lk + 4 * pass, k = k0 + kk;
+      float v = 0.f;
+      if (p_ok && k < K) {
+        const int ci = k / KK;
+        int t = k - ci * KK;
+        const int kw = t % g.KW; t /= g.KW;
+        const int kh = t % g.KH;
+        const int kd = t / g.KH;
+        const int id = id0 + kd * g.dd, ih = ih0 + kh * g.dh, iw = iw0 + kw * g.dw;
+        if (id >= 0 && id < g.D && ih >= 0 && ih < g.H && iw >= 0 && iw < g.W)
+          v = __ldg(xg + (((long long)ci * g.D + id) * g.H + ih) * g.W + iw);
+      }
+      Xs[kk][lr] = v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      float av[4], bv[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { av[i] = Ws[kk][ty * 4 + i]; bv[i] = Xs[kk][tx * 4 + i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const long long q = p0 + tx * 4 + j;
+    if (q >= pixels) continue;
+    const int qi = (int)(q / P);
+    const int qr = (int)(q - (long long)qi * P);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int o = o0 + ty * 4 + i;
+      if (o >= og) continue;
+      const int oc = grp * og + o;
+      const long long idx = ((long long)qi * g.O + oc) * P + qr;
+      float v = acc[i][j];
+      if (post.bias) v += __ldg(post.bias + oc);
+      if (post.sum) v += __ldg(post.sum + idx);
+      y[idx] = f_act(v, post.act, post.a, post.b);
+    }
+  }
+}
+
+bool fconv_gemm_form(const FConvGeom& g) {
+  static const bool direct_only = getenv("TKB_FCONV_DIRECT") != nullptr;  // A/B knob (tools/fconv_probe.py)
+  const long long pixels = (long long)g.N * g.OD * g.OH * g.OW;
+  return !direct_only && !g.transposed && g.O / g.groups >= 16 && g.groups <= 65535 && (pixels + 63) / 64 < 0x7fffffffLL;
+}
+
 void launch_fconv(const float* x, const float* w, float* y, const FConvGeom& g, const FPost& post, cudaStream_t s) {
   const long long total = (long long)g.N * g.O * g.OD * g.OH * g.OW;
   if (total <= 0) return;
+  const int og = g.O / g.groups;
+  const long long pixels = (long long)g.N * g.OD * g.OH * g.OW;
+  if (fconv_gemm_form(g)) {
+    dim3 grid((unsigned)((pixels + 63) / 64), (unsigned)((og + 63) / 64), (unsigned)g.groups);
+    fconv_gemm_kernel<<<grid, 256, 0, s>>>(x, w, y, g, post);
+    ++g_launches;
+    return;
+  }
   const int threads = 256;
   const long long blocks = (total + threads - 1) / threads;
   fconv_kernel<<<(unsigned)(blocks < 148 * 32 ? blocks : 148 * 32), threads, 0, s>>>(x, w, y, g, post);

@@ -1768,7 +1768,7 @@ static void plan_float_conv(Planner& P, int nid, bool transposed) {
   if (sum_eid >= 0) P.need(sum_eid, kLogical);
   P.produce(y_eid, kLogical);
   P.rt->hbm_bytes += X.bytes() + Wt.bytes() + Y.bytes();
-  P.add_step(n.name + (transposed ? " -> fp32 direct transposed convolution" : " -> fp32 direct convolution"), [=](RunCtx& c) {
+  P.add_step(n.name + (transposed ? " -> fp32 direct transposed convolution" : fconv_gemm_form(g) ? " -> fp32 implicit-GEMM convolution (64x64x16 tiles)" : " -> fp32 direct convolution"), [=](RunCtx& c) {
     FPost q = post;
     q.bias = bias_eid >= 0 ? (const float*)c.ptr(bias_eid, kLogical) : nullptr;
     q.sum = sum_eid >= 0 ? (const float*)c.ptr(sum_eid, kLogical) : nullptr;

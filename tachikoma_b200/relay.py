@@ -18,7 +18,7 @@ from __future__ import annotations
 import numpy as np
 
 __all__ = [
-    "Expr", "Var", "Constant", "Call", "Function", "var", "const", "post_order",
+    "Expr", "Var", "Constant", "Call", "Function", "Tuple", "var", "const", "post_order",
     "qnn_conv2d", "qnn_dense", "qnn_batch_matmul", "qnn_requantize", "qnn_add", "qnn_mul", "qnn_concatenate",
     "qnn_quantize", "qnn_dequantize", "bias_add", "add",
     "clip", "cast", "max_pool2d", "avg_pool2d", "global_avg_pool2d", "pad", "reshape",
@@ -60,6 +60,14 @@ class Call(Expr):
 class Function:
     def __init__(self, params, body, attrs=None):
         self.params, self.body, self.attrs = list(params), body, dict(attrs or {})
+
+
+def Tuple(fields):
+    """relay.Tuple as a function body (several outputs, tests/python/contrib/test_tachikoma.py:640-650): a pseudo call that
+    the serializer turns into one graph head per field; it never becomes a node."""
+    fields = list(fields)
+    assert fields and all(isinstance(f, Expr) for f in fields)
+    return Call("tuple", fields, {}, fields[0].shape, fields[0].dtype)
 
 
 def var(name, shape, dtype="float32"):

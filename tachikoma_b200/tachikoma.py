@@ -522,6 +522,8 @@ def partition_for_tachikoma(func, params=None, mode="int", symbol="tvmgen_defaul
     func = legalize_qnn_for_tachikoma(func, mode=mode)
     func = merge_float_composites(func)
     for e in R.post_order(func.body):
+        if isinstance(e, R.Call) and e.op == "tuple" and e is func.body:
+            continue  # several outputs: one graph head per field
         if isinstance(e, R.Call) and not e.op.startswith("tachikoma.") and e.op not in SUPPORTED_OPS:
             if e.op in FLOAT_SUPPORTED_OPS and e.dtype == "float32" and all(a.dtype == "float32" for a in e.args):
                 continue
@@ -582,6 +584,10 @@ def serialize(func, symbol=None):
             continue
         if isinstance(e, R.Var):
             raise ValueError(f"free variable {e.name} is not a function parameter")
+        if isinstance(e, R.Call) and e.op == "tuple":
+            if e is not func.body:
+                raise ValueError("Unsupported op: tuple (only as the function body)")
+            continue
         if isinstance(e, R.Constant):
             name = f"tachikoma_{symbol}_const_{len(const_names)}"
             const_names.append(name)
@@ -603,5 +609,6 @@ def serialize(func, symbol=None):
     for n in nodes:
         row_ptr.append(row_ptr[-1] + int(n["attrs"].get("num_outputs", "1")))
     graph = dict(nodes=nodes, arg_nodes=[i for i, n in enumerate(nodes) if n["op"] != "kernel"],
-                 heads=[entry[id(func.body)]], node_row_ptr=row_ptr)
+                 heads=[entry[id(f)] for f in func.body.args] if getattr(func.body, "op", "") == "tuple" else [entry[id(func.body)]],
+                 node_row_ptr=row_ptr)
     return symbol, json.dumps(graph), const_names, consts

@@ -91,3 +91,25 @@ def test_float_oracle_known_answers():
     np.testing.assert_allclose(FO.activation(np.array([0.0, 1.0]), "gelu"), [0.0, 0.8413447460685429], rtol=1e-12)
     np.testing.assert_allclose(FO.activation(np.array([1.0]), "mish"), [0.8650983882673103], rtol=1e-12)
     np.testing.assert_array_equal(FO.eval_float_op("round", {}, [np.array([0.5, 1.5, 2.5, -0.5], np.float32)]), [0, 2, 2, -0])
+
+
+def test_multiple_outputs_become_graph_heads():
+    """test_tachikoma.py:640-650: out = Tuple((x + y, (x + y) + y)) -> two heads, no node for the tuple."""
+    x, y = R.var("x", (1, 3)), R.var("y", (1, 3))
+    z = R.add(x, y)
+    f = R.Function([x, y], R.Tuple([z, R.add(z, y)]))
+    part = T.partition_for_tachikoma(f)
+    sym, js, names, consts = T.serialize(part)
+    g = json.loads(js)
+    assert len(g["heads"]) == 2 and [n["name"] for n in g["nodes"] if n["op"] == "kernel"] == ["add", "add"]
+    xv, yv = np.float32([[1, 2, 3]]), np.float32([[10, 20, 30]])
+    want, _ = interp.run_expr(f, {"x": xv, "y": yv})
+    got, _ = interp.run_json(js, consts, [xv, yv])
+    assert len(got) == 2
+    np.testing.assert_array_equal(got[0], want[0])
+    np.testing.assert_array_equal(got[1], [[21, 42, 63]])
+    # an integer graph with two outputs: the convolution composite and its pooled copy
+    d = R.var("d", (1, 4, 6, 6), "uint8")
+    import pytest
+    with pytest.raises(ValueError, match="only as the function body"):
+        T.serialize(R.Function([x, y], R.add(R.Tuple([z, z]), y)))

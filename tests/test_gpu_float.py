@@ -95,3 +95,33 @@ def test_rewritten_float_graphs_on_gpu():
     want, _ = interp.run_expr(g, ins)
     np.testing.assert_allclose(out, want, rtol=1e-3, atol=1e-3)
     assert "tachikoma.dense_bias_gelu" in mod.plan_summary()
+
+
+def test_multiple_outputs_on_gpu():
+    """test_tachikoma.py:640-650 (test_multiple_outputs) plus an integer graph with two heads."""
+    from tachikoma_b200 import relay as R
+    x, y = R.var("x", (1, 3)), R.var("y", (1, 3))
+    z = R.add(x, y)
+    f = R.Function([x, y], R.Tuple([z, R.add(z, y)]))
+    sym, js, names, consts = T.serialize(T.partition_for_tachikoma(f))
+    mod = RT.TachikomaJSONRuntime(sym, js, names)
+    mod.init(consts)
+    xv, yv = np.float32([[1, 2, 3]]), np.float32([[10, 20, 30]])
+    o0, o1 = np.empty((1, 3), "float32"), np.empty((1, 3), "float32")
+    mod.run(xv, yv, o0, o1, trace_mode=2)
+    np.testing.assert_array_equal(o0, [[11, 22, 33]])
+    np.testing.assert_array_equal(o1, [[21, 42, 63]])
+    _, recs = interp.run_json(js, consts, [xv, yv], want_trace=True)
+    assert mod.trace_blob() == interp.save_ndarray_list(recs)
+    d = R.var("d", (2, 8, 10, 10), "uint8")
+    p = R.max_pool2d(d, (2, 2), (2, 2))
+    f = R.Function([d], R.Tuple([p, R.cast(p, "int32")]))
+    sym, js, names, consts = T.serialize(T.partition_for_tachikoma(f))
+    mod = RT.TachikomaJSONRuntime(sym, js, names)
+    mod.init(consts)
+    dv = np.random.default_rng(0).integers(0, 256, (2, 8, 10, 10)).astype("uint8")
+    o0, o1 = np.empty((2, 8, 5, 5), "uint8"), np.empty((2, 8, 5, 5), "int32")
+    mod.run(dv, o0, o1)
+    want, _ = interp.run_json(js, consts, [dv])
+    np.testing.assert_array_equal(o0, want[0])
+    np.testing.assert_array_equal(o1, want[1])

@@ -115,7 +115,7 @@ _TOKEN = re.compile(r"""
     (?P<ws>\s+)
   | (?P<meta>meta\[relay\.Constant\]\[\d+\])
   | (?P<str>"[^"]*")
-  | (?P<num>[-+]?(?:\d+\.\d*|\.\d+|\d+)(?:[eE][-+]?\d+)?(?:f64|f16|f|i64|i16|i8|u8)?)
+  | (?P<num>[-+]?(?:(?:\d+\.\d*|\.\d+|\d+)(?:[eE][-+]?\d+)?|inf|nan)(?:f64|f16|f|i64|i16|i8|u8)?(?![A-Za-z0-9_.]))
   | (?P<local>%[A-Za-z0-9_.]+)
   | (?P<glob>@[A-Za-z0-9_.]+)
   | (?P<name>[A-Za-z_][A-Za-z0-9_.]*)
@@ -180,9 +180,9 @@ class _Parser:
     # ---- literals ----
     @staticmethod
     def number(tok):
-        m = re.match(r"^([-+]?(?:\d+\.\d*|\.\d+|\d+)(?:[eE][-+]?\d+)?)(f64|f16|f|i64|i16|i8|u8)?$", tok)
+        m = re.match(r"^([-+]?(?:(?:\d+\.\d*|\.\d+|\d+)(?:[eE][-+]?\d+)?|inf|nan))(f64|f16|f|i64|i16|i8|u8)?$", tok)
         body, suf = m.group(1), m.group(2)
-        if suf in ("f", "f16", "f64") or (suf is None and re.search(r"[.eE]", body)):
+        if suf in ("f", "f16", "f64") or (suf is None and re.search(r"[.eE]|inf|nan", body)):
             dt = {"f": "float32", "f16": "float16", "f64": "float64", None: "float32"}[suf]
             return np.asarray(float(body), dtype=dt)
         dt = {None: "int32", "i64": "int64", "i16": "int16", "i8": "int8", "u8": "uint8"}[suf]
@@ -201,7 +201,7 @@ class _Parser:
         if kind == "num":  # attribute floats are doubles in the reference (the `f` suffix is only notation here)
             m = re.match(r"^(.*?)(f64|f16|f|i64|i16|i8|u8)?$", v)
             body, suf = m.group(1), m.group(2)
-            return float(body) if (suf in ("f", "f16", "f64") or re.search(r"[.eE]", body)) else int(body)
+            return float(body) if (suf in ("f", "f16", "f64") or re.search(r"[.eE]|inf|nan", body)) else int(body)
         if v in ("True", "False"):
             return v == "True"
         if v == "None":
@@ -357,6 +357,40 @@ def _build(op, a, at):
         return R.batch_flatten(a[0])
     if op == "transpose":
         return R.transpose(a[0], at["axes"])
+    # float operators of the tachikoma float patterns
+    conv_kw = ("strides", "padding", "dilation", "groups", "channels", "kernel_size", "data_layout", "kernel_layout", "out_layout")
+    if op in ("nn.conv1d", "nn.conv2d", "nn.conv3d"):
+        fn = {"nn.conv1d": R.conv1d, "nn.conv2d": R.conv2d, "nn.conv3d": R.conv3d}[op]
+        return fn(a[0], a[1], **_pick(at, *conv_kw), out_dtype=at.get("out_dtype") or "")
+    if op in ("nn.conv2d_transpose", "nn.conv3d_transpose"):
+        fn = R.conv2d_transpose if op == "nn.conv2d_transpose" else R.conv3d_transpose
+        return fn(a[0], a[1], **_pick(at, *conv_kw, "output_padding"), out_dtype=at.get("out_dtype") or "")
+    if op == "nn.dense":
+        return R.dense(a[0], a[1], at.get("units"), out_dtype=at.get("out_dtype") or "")
+    if op == "nn.batch_matmul":
+        return R.batch_matmul(a[0], a[1], out_dtype=at.get("out_dtype") or "", transpose_a=bool(at.get("transpose_a", False)),
+                              transpose_b=bool(at.get("transpose_b", True)))
+    if op == "nn.batch_norm":
+        return R.batch_norm(*a[:5], **_pick(at, "axis", "epsilon", "center", "scale"))
+    if op == "nn.layer_norm":
+        return R.layer_norm(*a[:3], **_pick(at, "axis", "epsilon", "center", "scale"))
+    if op == "nn.softmax":
+        return R.softmax(a[0], **_pick(at, "axis"))
+    if op == "nn.leaky_relu":
+        return R.leaky_relu(a[0], at.get("alpha", 0.01))
+    unary = {"nn.relu": R.relu, "tanh": R.tanh, "sigmoid": R.sigmoid, "abs": R.abs_, "exp": R.exp, "log": R.log, "sqrt": R.sqrt,
+             "round": R.round_, "erf": R.erf}
+    if op in unary:
+        return unary[op](a[0])
+    if op in ("multiply", "divide"):
+        return (R.multiply if op == "multiply" else R.divide)(a[0], a[1])
+    if op in ("nn.max_pool3d", "nn.avg_pool3d"):
+        if at.get("ceil_mode"):
+            raise ValueError("Unsupported op: %s with ceil_mode" % op)
+        kw = _pick(at, "pool_size", "strides", "dilation", "padding", "layout")
+        if op == "nn.avg_pool3d":
+            return R.avg_pool3d(a[0], count_include_pad=bool(at.get("count_include_pad", False)), **kw)
+        return R.max_pool3d(a[0], **kw)
     raise ValueError("Unsupported op: %s" % op)
 
 

@@ -96,9 +96,26 @@ def test_text_in_the_reference_printers_shape_parses_to_the_fused_chain():
 
 
 def test_parser_errors():
-    with pytest.raises(ValueError, match="Unsupported op: nn.softmax"):
-        RT_.fromtext("fn (%x: Tensor[(2, 3), float32]) { nn.softmax(%x, axis=1) }")
+    with pytest.raises(ValueError, match="Unsupported op: nn.log_softmax"):
+        RT_.fromtext("fn (%x: Tensor[(2, 3), float32]) { nn.log_softmax(%x, axis=1) }")
+    assert RT_.fromtext("fn (%x: Tensor[(2, 3), float32]) { nn.softmax(%x, axis=1) }").body.op == "nn.softmax"
     with pytest.raises(ValueError, match="only 0 constants given"):
         RT_.fromtext("fn (%x: Tensor[(2, 3), int32]) { add(%x, meta[relay.Constant][0]) }")
     with pytest.raises(ValueError, match="used before its definition"):
         RT_.fromtext("fn (%x: Tensor[(2, 3), int32]) { add(%x, %7) }")
+
+
+def test_float_graphs_round_trip_through_relay_text():
+    """Every float test graph (tests/float_graphs.py: convolutions 1-3D and transposed, dense, batch matmul, norms, softmax,
+    pools, activations incl. the gelu / swish / mish compositions, an -inf pad value) prints, parses back to the same text and
+    evaluates to the same values."""
+    import float_graphs as FG
+    from oracle import interp
+    for name, f, _ in FG.all_cases():
+        text, consts = RT_.astext(f)
+        g = RT_.fromtext(text, consts)
+        assert RT_.astext(g)[0] == text, name
+        ins = FG.inputs_for(f)
+        a, _ = interp.run_expr(f, ins)
+        b, _ = interp.run_expr(g, ins)
+        np.testing.assert_array_equal(a, b, err_msg=name)

@@ -155,6 +155,12 @@ __device__ __forceinline__ uint4 ldg_cg_16(const void* p) {
   return v;
 }
 
+__device__ __forceinline__ void stg256(void* p, const uint32_t (&w)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]),
+               "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+               : "memory");
+}
+
 // ---- epilogue -------------------------------------------------------------------------------------
 // MODE selects the inlined hot path of the epilogue warps; everything unusual (ragged N tails, outputs
 // whose rows are not 16-byte multiples, border rows that need the zero-point delta, the generic
@@ -318,7 +324,12 @@ __device__ __forceinline__ void epilogue_chunk(const uint32_t (&r)[32], const P&
       }
     }
     uint8_t* dst8 = (uint8_t*)p.y + idx0;
-    if ((!AL8 || (((uintptr_t)dst8) & 15) == 0) && (ncols & 15) == 0) {
+    if (ncols == 32 && (((uintptr_t)dst8) & 31) == 0) {
+      // one 256-bit store per lane (sm_100: STG.256): the lanes of a warp write 32 different rows, so every store
+      // instruction costs the LSU one wavefront per lane; two 128-bit stores cost twice that and write each 32-byte
+      // sector in two halves (profiles/r02_notes.md section 17)
+      stg256(dst8, w);
+    } else if ((!AL8 || (((uintptr_t)dst8) & 15) == 0) && (ncols & 15) == 0) {
       uint4* dst = (uint4*)dst8;
       dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
       if (ncols == 32) dst[1] = make_uint4(w[4], w[5], w[6], w[7]);

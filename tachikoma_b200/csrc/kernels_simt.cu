@@ -246,14 +246,48 @@ __global__ void __launch_bounds__(256) dwconv3x3_nhwc_kernel(const uint8_t* __re
 // 32-bit word, accumulated straight into the outputs the row belongs to (no row buffer: 16 * NV accumulators).  The
 // per-channel epilogue constants are loaded once and used for all NV outputs.  Taps outside the image read the zero
 // point (see dwconv_nhwc_kernel for the identity that makes this exact).
+// cvt.pack.sat: four int32 -> four saturated 8-bit values in one word (byte 0 = v0)
+template <bool UNSIGNED>
+__device__ __forceinline__ uint32_t dw_pack4_sat8(int32_t v0, int32_t v1, int32_t v2, int32_t v3) {
+  uint32_t t, d;
+  if (UNSIGNED) {
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(t) : "r"(v3), "r"(v2), "r"(0));
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(v1), "r"(v0), "r"(t));
+  } else {
+    asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(t) : "r"(v3), "r"(v2), "r"(0));
+    asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(v1), "r"(v0), "r"(t));
+  }
+  return d;
+}
+
+// (round 2, profiles/r02_notes.md section 18) The first version walked the rows one after the other -- three loads, wait,
+// compute -- with 168 registers (64 accumulators + 48 weight registers), i.e. 12 warps per SM each paying a full memory
+// latency per row: 1.2-1.9 TB/s.  Now the weights live in shared memory and ALL rows are requested before the first is
+// used, so a thread pays the latency once.
 template <bool AU, bool WU, int S, int NV>
 __global__ void __launch_bounds__(128) dwconv3x3_v16_kernel(const uint8_t* __restrict__ x, const uint32_t* __restrict__ wrow,
                                                             void* __restrict__ y, ConvGeom g, FastEpi f) {
   constexpr int ROWS = (NV - 1) * S + 3;
+  // Shared memory, both arrays laid out [item][channel group] so that the lanes of a warp (consecutive channel groups)
+  // read consecutive 16-byte words: the per-thread form (16 table entries 256 bytes apart from the next lane's) cost 32
+  // L1 wavefronts per load instruction and made the kernel L1-bound (ncu: L1/TEX throughput 87-89 %, DRAM 10-20 %).
+  //   dw_ws [3 rows][4 words][cg]: row-packed weights, one 32-bit lane = one channel's {w(r,0), w(r,1), w(r,2), 0}
+  //   dw_tab[16 channels][cg]    : folded requantize constants {M, T - 32, C_lo, C_hi}
+  extern __shared__ uint4 dw_ws[];
   const int cg = g.C >> 4;
+  int4* dw_tab = (int4*)(dw_ws + 12 * cg);
+  for (int i = threadIdx.x; i < 12 * cg; i += 128) {   // i = (r * 4 + k) * cg + group
+    const int grp = i % cg, rk = i / cg;
+    dw_ws[i] = __ldg((const uint4*)wrow + (rk >> 2) * (g.C >> 2) + grp * 4 + (rk & 3));
+  }
+  for (int i = threadIdx.x; i < 16 * cg; i += 128) {   // i = e * cg + group
+    const int grp = i % cg, e = i / cg;
+    dw_tab[i] = __ldg(f.tabA + grp * 16 + e);
+  }
+  __syncthreads();
   const int t = blockIdx.x * 128 + threadIdx.x;
   if (t >= g.OW * cg) return;
-  const int ox = t / cg, c0 = (t - ox * cg) * 16;
+  const int ox = t / cg, grp0 = t - ox * cg, c0 = grp0 * 16;
   const int oy0 = blockIdx.y * NV, n = blockIdx.z;
   const uint32_t zp4 = (uint32_t)(g.zp_a & 0xFF) * 0x01010101u;
   const uint8_t* img = x + (long long)n * g.H * g.W * g.C + c0;
@@ -265,26 +299,25 @@ __global__ void __launch_bounds__(128) dwconv3x3_v16_kernel(const uint8_t* __res
     xin[q] = ix >= 0 && ix < g.W;
     xoff[q] = ix * g.C;
   }
-  // row-packed weights of this thread's 16 channels: wv[r][word] = 4 channels x {w(r,0), w(r,1), w(r,2), 0}
-  uint4 wv[3][4];
-#pragma unroll
-  for (int r = 0; r < 3; ++r)
-#pragma unroll
-    for (int k = 0; k < 4; ++k) wv[r][k] = __ldg((const uint4*)(wrow + (long long)r * g.C + c0 + 4 * k));
-  int32_t acc[NV][16];
-#pragma unroll
-  for (int o = 0; o < NV; ++o)
-#pragma unroll
-    for (int c = 0; c < 16; ++c) acc[o][c] = 0;
+  uint4 p[ROWS][3];
 #pragma unroll
   for (int j = 0; j < ROWS; ++j) {
     const int iy = oy0 * S - g.pt + j;
     const bool yin = iy >= 0 && iy < g.H;
     const uint8_t* row = img + (long long)iy * g.W * g.C;
-    uint4 p[3];
 #pragma unroll
-    for (int q = 0; q < 3; ++q) p[q] = (yin && xin[q]) ? __ldg((const uint4*)(row + xoff[q])) : make_uint4(zp4, zp4, zp4, zp4);
-    const uint32_t p0[4] = {p[0].x, p[0].y, p[0].z, p[0].w}, p1[4] = {p[1].x, p[1].y, p[1].z, p[1].w}, p2[4] = {p[2].x, p[2].y, p[2].z, p[2].w};
+    for (int q = 0; q < 3; ++q) p[j][q] = (yin && xin[q]) ? __ldg((const uint4*)(row + xoff[q])) : make_uint4(zp4, zp4, zp4, zp4);
+  }
+  int32_t acc[NV][16];
+#pragma unroll
+  for (int o = 0; o < NV; ++o)
+#pragma unroll
+    for (int c = 0; c < 16; ++c) acc[o][c] = 0;
+  const uint4* wt = dw_ws + grp0;
+#pragma unroll
+  for (int j = 0; j < ROWS; ++j) {
+    const uint32_t p0[4] = {p[j][0].x, p[j][0].y, p[j][0].z, p[j][0].w}, p1[4] = {p[j][1].x, p[j][1].y, p[j][1].z, p[j][1].w},
+                   p2[4] = {p[j][2].x, p[j][2].y, p[j][2].z, p[j][2].w};
 #pragma unroll
     for (int k = 0; k < 4; ++k) {  // 4 channels: three pixel words -> one word per channel holding its three taps
       const uint32_t a = __byte_perm(p0[k], p1[k], 0x5140), b = __byte_perm(p0[k], p1[k], 0x7362);
@@ -294,26 +327,45 @@ __global__ void __launch_bounds__(128) dwconv3x3_v16_kernel(const uint8_t* __res
       for (int o = 0; o < NV; ++o) {
         const int r = j - o * S;  // filter row this input row is for output o (compile time)
         if (r < 0 || r > 2) continue;
-        const uint32_t ww[4] = {wv[r][k].x, wv[r][k].y, wv[r][k].z, wv[r][k].w};
+        const uint4 w4 = wt[(r * 4 + k) * cg];
+        const uint32_t ww[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
         for (int c = 0; c < 4; ++c) acc[o][4 * k + c] = dp4a_mixed<AU, WU>(tr[c], ww[c], acc[o][4 * k + c]);
       }
     }
   }
-  // folded requantize + clamp (FastEpi, epilogue.cuh); the zero-point correction is already inside the table
+  // folded requantize + clamp (FastEpi, epilogue.cuh); the zero-point correction is already inside the table.
+  // f.sat (1: the clamp is the uint8 range, 2: the int8 range): the saturating pack does the clamp, 2.5 instead of 6
+  // instructions per output.
   uint32_t out[NV][4];
+  if (f.sat) {
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < 4; ++k) {
+      int32_t v[NV][4];
 #pragma unroll
-    for (int o = 0; o < NV; ++o) out[o][k] = 0;
+      for (int c = 0; c < 4; ++c) {
+        const int4 tb = dw_tab[(4 * k + c) * cg + grp0];
+        const long long cc = ((long long)tb.w << 32) | (unsigned long long)(uint32_t)tb.z;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      const int4 tb = __ldg(f.tabA + c0 + 4 * k + c);
-      const long long cc = ((long long)tb.w << 32) | (unsigned long long)(uint32_t)tb.z;
+        for (int o = 0; o < NV; ++o) v[o][c] = (int32_t)(((long long)acc[o][4 * k + c] * (long long)tb.x + cc) >> 32) >> tb.y;
+      }
 #pragma unroll
-      for (int o = 0; o < NV; ++o) {
-        const int32_t v = (int32_t)(((long long)acc[o][4 * k + c] * (long long)tb.x + cc) >> 32) >> tb.y;
-        out[o][k] |= (uint32_t)(min(max(v, f.lo), f.hi) & 0xFF) << (8 * c);
+      for (int o = 0; o < NV; ++o) out[o][k] = f.sat == 1 ? dw_pack4_sat8<true>(v[o][0], v[o][1], v[o][2], v[o][3]) : dw_pack4_sat8<false>(v[o][0], v[o][1], v[o][2], v[o][3]);
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+#pragma unroll
+      for (int o = 0; o < NV; ++o) out[o][k] = 0;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int4 tb = dw_tab[(4 * k + c) * cg + grp0];
+        const long long cc = ((long long)tb.w << 32) | (unsigned long long)(uint32_t)tb.z;
+#pragma unroll
+        for (int o = 0; o < NV; ++o) {
+          const int32_t v = (int32_t)(((long long)acc[o][4 * k + c] * (long long)tb.x + cc) >> 32) >> tb.y;
+          out[o][k] |= (uint32_t)(min(max(v, f.lo), f.hi) & 0xFF) << (8 * c);
+        }
       }
     }
   }
@@ -344,8 +396,8 @@ void launch_dwconv_nhwc(const void* x, const void* w_tap, const void* w_row3, co
     dim3 grid((unsigned)((g.OW * (g.C / 16) + 127) / 128), (unsigned)((g.OH + nv - 1) / nv), (unsigned)g.N);
 #define TKB_DW16(AU_, WU_)                                                                                 \
   if (au == AU_ && wu == WU_) {                                                                            \
-    if (g.sh == 1) dwconv3x3_v16_kernel<AU_, WU_, 1, NV1><<<grid, 128, 0, s>>>(xp, wp, y, g, f);            \
-    else dwconv3x3_v16_kernel<AU_, WU_, 2, NV2><<<grid, 128, 0, s>>>(xp, wp, y, g, f);                      \
+    if (g.sh == 1) dwconv3x3_v16_kernel<AU_, WU_, 1, NV1><<<grid, 128, 28 * g.C, s>>>(xp, wp, y, g, f);     \
+    else dwconv3x3_v16_kernel<AU_, WU_, 2, NV2><<<grid, 128, 28 * g.C, s>>>(xp, wp, y, g, f);               \
   }
     TKB_DW16(true, true) TKB_DW16(true, false) TKB_DW16(false, true) TKB_DW16(false, false)
 #undef TKB_DW16

@@ -332,7 +332,7 @@ int launch_tc_halo(const TcArgs& a, cudaStream_t s) {
   const bool sum = a.f.has_sum != 0;
   // saturating-pack epilogue (kModeFastSat): spills at BN = 128 without the residual, so 64-column tiles only there
   const bool sat = a.f.sat && c.bn == 64, sum_sat = a.f.sum_sat != 0;
-  const bool k33 = g.KH == 3 && g.KW == 3, k14 = g.KH == 1 && g.KW == 4;
+  const bool k33 = g.KH == 3 && g.KW == 3, k14 = g.KH == 1 && g.KW == 4, k12 = g.KH == 1 && g.KW == 2;
 #define TKB_HALO(COND_, BN_, KH_, KW_, BK_)                                                        \
   if ((COND_) && c.bn == BN_ && (BK_ == 0 || c.bk == BK_))                                         \
     return sum ? (sum_sat ? launch_halo_t<BN_, kModeFastSumSat, KH_, KW_, BK_>(ta, p, c.smem, s)  \
@@ -341,6 +341,7 @@ int launch_tc_halo(const TcArgs& a, cudaStream_t s) {
                           : launch_halo_t<BN_, kModeFast, KH_, KW_, BK_>(ta, p, c.smem, s));
   TKB_HALO(k33, 64, 3, 3, 64) TKB_HALO(k33, 64, 3, 3, 128) TKB_HALO(k33, 128, 3, 3, 64) TKB_HALO(k33, 128, 3, 3, 128)
   TKB_HALO(k14, 64, 1, 4, 64)  // the stride-2 7x7 stem as a 1x4 convolution over pixel pairs of the unfolded input
+  TKB_HALO(k12, 64, 1, 2, 64)  // a stride-2 3x3 stem (MobileNetV2) in the same form: 1x2
   TKB_HALO(true, 64, 0, 0, 0) TKB_HALO(true, 128, 0, 0, 0) TKB_HALO(true, 256, 0, 0, 0)
 #undef TKB_HALO
   return -1;

@@ -687,7 +687,9 @@ static int launch_ts(const CUtensorMap& ta, const CUtensorMap& tb, TcKernelParam
 inline int epi_groups_for(long long tiles_per_sm, int num_mma_per_tile, int ntiles) {
   static const int forced = [] { const char* e = getenv("TKB_EG"); return e ? atoi(e) : 0; }();
   if (forced == 1 || forced == 2) return forced;
-  return (tiles_per_sm >= 16 && num_mma_per_tile <= 4 && ntiles == 1) ? 1 : 2;
+  static const int max_mma = [] { const char* e = getenv("TKB_EG_MMA"); return e ? atoi(e) : 4; }();      // tuning knobs
+  static const int min_tiles = [] { const char* e = getenv("TKB_EG_TILES"); return e ? atoi(e) : 16; }();
+  return (tiles_per_sm >= min_tiles && num_mma_per_tile <= max_mma && ntiles == 1) ? 1 : 2;
 }
 
 template <int BN, int MODE>

@@ -108,6 +108,10 @@ const char* tkb_plan_summary(tkb_handle h);
 int tkb_tc_time(tkb_handle h, double* ms, int* launches);
 /* Total int8 multiply-accumulates and algorithmic HBM bytes of one run (roofline numerators). */
 int tkb_work(tkb_handle h, int64_t* macs, int64_t* hbm_bytes);
+/* int8 multiply-accumulates of the plan's tcgen05 launches only (the launches tkb_tc_time times): depthwise and
+ * few-channel pointwise convolutions run on CUDA cores and are counted by tkb_work but not here.  No reference counterpart
+ * (measurement support for bench.py's roofline). */
+int64_t tkb_tc_macs(tkb_handle h);
 
 /* --- per-operator trace ------------------------------------------------------------------------
  * mode 0 = off;

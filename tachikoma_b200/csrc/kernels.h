@@ -26,6 +26,10 @@ void launch_conv2d_simt(const void* x, const void* w, void* y, const ConvGeom& g
 // depthwise convolution on dense channels-last 8-bit tensors; w_tap: [KH*KW][C] (tap-major), corr[c] = -zp_a*sum_taps w
 bool dwconv_nhwc_supported(const ConvGeom& g);
 // w_row3 (3x3 kernels, may be null): [3][C] words {w(r,0), w(r,1), w(r,2), 0} for the dp4a kernel
+// pointwise convolution with 8 / 16 / 24 / 32 input channels on CUDA cores (kernels_simt.cu pwconv_kernel); 0 on success
+bool pwconv_supported(int K, int N);
+int launch_pwconv(const void* x, const void* w, void* y, long long M, int N, int K, int a_dtype, int w_dtype, const FastEpi& f,
+                  cudaStream_t s);
 void launch_dwconv_nhwc(const void* x, const void* w_tap, const void* w_row3, const int32_t* corr, void* y,
                         const ConvGeom& g, const EpiParams& e, const FastEpi& f, cudaStream_t s);
 // Y[b,m,n] = sum_k (X[b,m,k]-zpx)(W[b?,n,k]-zpw); w_batched: W has a batch dim of B, else shared.

@@ -377,6 +377,130 @@ __global__ void __launch_bounds__(128) dwconv3x3_v16_kernel(const uint8_t* __res
   }
 }
 
+// ---- pointwise (1x1, stride 1, unpadded) convolution with very few input channels (8 .. 32): CUDA-core dp4a kernel -----------
+// MobileNetV2's 32 -> 16, 16 -> 96 and 24 -> 144 layers at 112x112 / 56x56 have one to two tcgen05 MMAs per 128-pixel tile; on
+// the tensor-core kernel they are bound by ~860 cycles of barrier round trips per tile (profiles/r02_notes.md section 13), at
+// a fifth of the memory roofline.  Here a thread owns 4 consecutive pixels x CB consecutive output channels: the pixels' input
+// bytes live in registers, weights and the folded requantize table are staged once per block in shared memory as
+// [item][channel block] (consecutive lanes = consecutive channel blocks read consecutive 16-byte words), and the CB outputs
+// of a pixel leave as one 8- or 16-byte store, the lanes of a warp covering contiguous bytes of the NHWC output.
+template <bool AU, bool WU, int KB, int CB>
+__global__ void __launch_bounds__(256) pwconv_kernel(const uint8_t* __restrict__ x, const uint32_t* __restrict__ w,
+                                                     uint8_t* __restrict__ y, long long M, int N, FastEpi f) {
+  constexpr int KW = KB / 4, KW4 = (KW + 3) / 4, PX = 4;  // input words per pixel, weight uint4 per channel, pixels per thread
+  extern __shared__ uint4 pw_smem[];
+  const int NB = N / CB;
+  uint4* ws = pw_smem;                           // [CB][KW4][NB]
+  int4* tab = (int4*)(pw_smem + CB * KW4 * NB);  // [CB][NB]
+  for (int i = threadIdx.x; i < CB * KW4 * NB; i += 256) {
+    const int nb = i % NB, r = i / NB, j = r % KW4, c = r / KW4;
+    ws[i] = __ldg((const uint4*)w + (long long)(nb * CB + c) * KW4 + j);
+  }
+  for (int i = threadIdx.x; i < CB * NB; i += 256) {
+    const int nb = i % NB, c = i / NB;
+    tab[i] = __ldg(f.tabA + nb * CB + c);
+  }
+  __syncthreads();
+  // A thread's 4 pixels are PS = 32 apart (pixel slot q -> pixels (q / 32) * 128 + q % 32 + 32 * i): for a given i the
+  // lanes of a warp then read / write neighbouring pixels, i.e. a contiguous stretch of memory per instruction.  (With 4
+  // consecutive pixels per thread every 16-byte load of a warp touched 32 different cache lines: L1-bound at 72 %.)
+  constexpr int PS = 32;
+  const long long slots = (M + PS * PX - 1) / (PS * PX) * PS, total = slots * NB;
+  for (long long t = (long long)blockIdx.x * 256 + threadIdx.x; t < total; t += (long long)gridDim.x * 256) {
+    const int nb = (int)(t % NB);
+    const long long q = t / NB;
+    const long long p0 = (q / PS) * (PS * PX) + (q % PS);
+    uint32_t xin[PX][KW];
+#pragma unroll
+    for (int p = 0; p < PX; ++p) {
+      const bool ok = p0 + (long long)p * PS < M;
+      const uint8_t* xp = x + (p0 + (long long)p * PS) * KB;
+      if constexpr (KB % 16 == 0) {
+#pragma unroll
+        for (int j = 0; j < KB / 16; ++j) {
+          const uint4 v = ok ? __ldg((const uint4*)xp + j) : make_uint4(0, 0, 0, 0);
+          xin[p][4 * j] = v.x; xin[p][4 * j + 1] = v.y; xin[p][4 * j + 2] = v.z; xin[p][4 * j + 3] = v.w;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < KB / 8; ++j) {
+          const uint2 v = ok ? __ldg((const uint2*)xp + j) : make_uint2(0, 0);
+          xin[p][2 * j] = v.x; xin[p][2 * j + 1] = v.y;
+        }
+      }
+    }
+    uint32_t out[PX][CB / 4];
+#pragma unroll
+    for (int c4 = 0; c4 < CB / 4; ++c4) {
+      int32_t v[PX][4];
+#pragma unroll
+      for (int cc = 0; cc < 4; ++cc) {
+        const int c = 4 * c4 + cc;
+        uint32_t ww[4 * KW4];
+#pragma unroll
+        for (int j = 0; j < KW4; ++j) {
+          const uint4 q = ws[(c * KW4 + j) * NB + nb];
+          ww[4 * j] = q.x; ww[4 * j + 1] = q.y; ww[4 * j + 2] = q.z; ww[4 * j + 3] = q.w;
+        }
+        const int4 tb = tab[c * NB + nb];
+        const long long add = ((long long)tb.w << 32) | (unsigned long long)(uint32_t)tb.z;
+#pragma unroll
+        for (int p = 0; p < PX; ++p) {
+          int32_t acc = 0;
+#pragma unroll
+          for (int k = 0; k < KW; ++k) acc = dp4a_mixed<AU, WU>(xin[p][k], ww[k], acc);
+          v[p][cc] = (int32_t)(((long long)acc * (long long)tb.x + add) >> 32) >> tb.y;
+        }
+      }
+#pragma unroll
+      for (int p = 0; p < PX; ++p) {
+        if (f.sat == 1) out[p][c4] = dw_pack4_sat8<true>(v[p][0], v[p][1], v[p][2], v[p][3]);
+        else if (f.sat == 2) out[p][c4] = dw_pack4_sat8<false>(v[p][0], v[p][1], v[p][2], v[p][3]);
+        else {
+          uint32_t word = 0;
+#pragma unroll
+          for (int cc = 0; cc < 4; ++cc) word |= (uint32_t)(min(max(v[p][cc], f.lo), f.hi) & 0xFF) << (8 * cc);
+          out[p][c4] = word;
+        }
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < PX; ++p) {
+      if (p0 + (long long)p * PS >= M) break;
+      uint8_t* dst = y + (p0 + (long long)p * PS) * N + nb * CB;
+      if constexpr (CB == 16) *(uint4*)dst = make_uint4(out[p][0], out[p][1], out[p][2], out[p][3]);
+      else *(uint2*)dst = make_uint2(out[p][0], out[p][1]);
+    }
+  }
+}
+
+bool pwconv_supported(int K, int N) { return (K == 8 || K == 16 || K == 24 || K == 32) && N % 8 == 0 && N >= 8 && N <= 1024; }
+
+// x: [M][K] bytes (NHWC pixels), w: [N][ceil(K/16)*16] bytes (rows zero-padded), y: [M][N] bytes
+int launch_pwconv(const void* x, const void* w, void* y, long long M, int N, int K, int a_dtype, int w_dtype, const FastEpi& f,
+                  cudaStream_t s) {
+  if (!pwconv_supported(K, N) || !f.enabled || f.has_sum || M <= 0) return -1;
+  if ((((uintptr_t)x) | ((uintptr_t)y) | ((uintptr_t)w)) & 15) return -1;
+  const int CB = N % 16 == 0 ? 16 : 8, NB = N / CB, KW4 = (K / 4 + 3) / 4;
+  const size_t smem = (size_t)(CB * KW4 * NB + CB * NB) * 16;
+  if (smem > 48 * 1024) return -1;
+  const long long total = ((M + 127) / 128) * 32 * NB, blocks = (total + 255) / 256;
+  const unsigned grid = (unsigned)(blocks < 148 * 8 ? blocks : 148 * 8);
+  const bool au = a_dtype == kU8, wu = w_dtype == kU8;
+#define TKB_PW(AU_, WU_, KB_, CB_)                                                                                        \
+  if (au == AU_ && wu == WU_ && K == KB_ && CB == CB_) {                                                                  \
+    pwconv_kernel<AU_, WU_, KB_, CB_><<<grid, 256, smem, s>>>((const uint8_t*)x, (const uint32_t*)w, (uint8_t*)y, M, N, f); \
+    ++g_launches;                                                                                                          \
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;                                                                     \
+  }
+#define TKB_PW_K(AU_, WU_) TKB_PW(AU_, WU_, 8, 16) TKB_PW(AU_, WU_, 8, 8) TKB_PW(AU_, WU_, 16, 16) TKB_PW(AU_, WU_, 16, 8) \
+  TKB_PW(AU_, WU_, 24, 16) TKB_PW(AU_, WU_, 24, 8) TKB_PW(AU_, WU_, 32, 16) TKB_PW(AU_, WU_, 32, 8)
+  TKB_PW_K(true, false) TKB_PW_K(true, true) TKB_PW_K(false, false) TKB_PW_K(false, true)
+#undef TKB_PW_K
+#undef TKB_PW
+  return -1;
+}
+
 bool dwconv_nhwc_supported(const ConvGeom& g) {
   return g.groups == g.C && g.O == g.C && (g.C % 16) == 0 && g.N <= 65535 && g.OH <= 65535 && g.zp_w == nullptr &&
          g.zp_w0 == 0 && g.KH * g.KW <= 49;

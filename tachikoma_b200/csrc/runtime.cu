@@ -165,6 +165,7 @@ struct tkb_runtime {
   std::string plan_text;
   std::atomic<long long> launches{0};
   long long macs = 0, hbm_bytes = 0;
+  long long tc_macs = 0;                       // MACs of the steps that run as tcgen05 launches (what tkb_tc_time times)
   std::vector<tkb::ChainCand> chain_cands;
   std::vector<tkb::ChainPlan> chains;
   int chain_flag_ints = 0;                      // counters of all chains (the workspace allocates twice this: + targets)
@@ -954,6 +955,29 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     ta.g = g;
     if (composite && !ci.float_mode)
       build_fast_epi(P, ci, bias2, abs_row_sums(wk.data(), g.O, K, g.w_dtype), g.O, Y.dtype, &ta.f);
+    // 1x1 convolution with 8 .. 32 input channels: one or two MMAs per 128-pixel tile make the tensor-core kernel
+    // barrier-bound (profiles/r02_notes.md sections 13, 20); the default plan runs these on the CUDA-core pointwise
+    // kernel.  conv_impl "tc" keeps the tcgen05 form (A/B, tests).
+    // (measured, MobileNetV2 batch 128: 32 -> 16 at 112x112 48.4 -> 26.0 us, 16 -> 96 91 -> 79.5 us, 24 -> 144 at 56x56
+    // 59 -> 42.5 us incl. the K-padding pass it no longer needs; at 28x28 the tensor-core kernel wins, 17.4 vs 21.3 us, hence
+    // the pixel-count threshold; TKB_PW_MIN_M overrides it, read at plan time so that tests can exercise small shapes)
+    static const bool pw_off = getenv("TKB_NO_PW") != nullptr;
+    const char* pw_min_env = getenv("TKB_PW_MIN_M");
+    const long long pw_min_m = pw_min_env ? atoll(pw_min_env) : (1LL << 18);
+    if (P.rt->conv_impl == "auto" && !pw_off && M >= pw_min_m && g.KH == 1 && g.KW == 1 && g.sh == 1 && g.sw == 1 && !(g.pt | g.pl | g.pb | g.pr) &&
+        !unfold && !from_nchw && pwconv_supported(Cg, g.O) && ta.f.enabled && !ta.f.has_sum && bias_eid < 0 && sum_eid < 0 &&
+        dtype_size(Y.dtype) == 1 && (int)wp.size() == g.O * ((Cg + 15) / 16 * 16)) {
+      void* wdev = P.dev_upload(wp.data(), wp.size());
+      const FastEpi fe = ta.f;
+      const int Kc = Cg, O = g.O, adt = g.a_dtype, wdt = g.w_dtype;
+      snprintf(desc, sizeof(desc), "%s -> CUDA-core pointwise conv (dp4a, 4 pixels x %d channels per thread) M=%lld N=%d K=%d epi=fast",
+               n.name.c_str(), O % 16 == 0 ? 16 : 8, M, O, Kc);
+      P.add_step(desc, [=](RunCtx& c) {
+        if (launch_pwconv(c.ptr(x_eid, phys), wdev, c.ptr(y_eid, phys), M, O, Kc, adt, wdt, fe, c.s) != 0)
+          fail("pointwise convolution launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+      });
+      return;
+    }
     // Chained launch (kernels_tc_chain.cu): layers with >= 96 output channels in the implicit-GEMM / plain-GEMM form
     // become candidates; form_chains() merges consecutive candidates into one persistent launch.
     const int chain_bn = 128;
@@ -1022,6 +1046,7 @@ static void plan_conv(Planner& P, int nid, bool composite) {
     snprintf(desc, sizeof(desc), "%s -> tcgen05 i8 %s M=%lld N=%d K=%d (%dx%d s%d p%d) epi=%s", n.name.c_str(),
              pair ? (direct ? "cta_group::2 pair GEMM" : "cta_group::2 pair implicit-GEMM conv (TMA im2col)") : direct ? "GEMM" : (unfold ? (halo ? "halo-reuse conv over pixel pairs of the vertically unfolded NCHW input" : "conv as windowed-row GEMM over vertically unfolded NCHW input") : halo ? "halo-reuse conv (TMA patch, resident weights)" : implicit ? "implicit-GEMM conv (TMA im2col)" : (from_nchw ? "GEMM + explicit im2col from NCHW" : "GEMM + explicit im2col")), M, g.O, Kp, g.KH,
              g.KW, g.sh, g.pt, ta.f.enabled ? "fast" : (epi.mode == kEpiInt ? "int" : (epi.mode == kEpiFloat ? "float" : "raw")));
+    P.rt->tc_macs += M * g.O * (long long)(g.KH * g.KW * Cg);
     if (chain) {
       ChainCand cc;
       cc.ta = ta;
@@ -1173,6 +1198,7 @@ static void plan_dense(Planner& P, int nid, bool composite) {
     if (composite && !ci.float_mode && Wt.is_const)
       build_fast_epi(P, ci, bias2, abs_row_sums(Wt.host.data(), N, K, wd), N, Y.dtype, &ta.f);
     const void* wpacked = nullptr;
+    P.rt->tc_macs += (long long)M * N * K;
     const int chain_bn = 128;
     bool chain = P.rt->chain_enabled && composite && !ci.float_mode && ta.f.enabled && Wt.is_const && bias_eid < 0 && N >= 96 &&
                  (P.rt->chain_policy != 1 || has_sibling_composite(P, nid)) &&
@@ -1259,6 +1285,7 @@ static void plan_batch_matmul(Planner& P, int nid) {
   const bool use_tc = P.rt->conv_impl != "simt" && tc_gemm_supported(M, N, K) && zpx == 0 && zpw == 0 &&
                       (P.rt->conv_impl == "tc" || P.rt->conv_impl == "tc_nochain" || P.rt->conv_impl.rfind("tc_chain", 0) == 0 || P.rt->conv_impl == "tc_explicit" || P.rt->conv_impl == "tc_im2col" || P.rt->conv_impl == "tc_pair" || (long long)B * M * N >= 4096);
   char desc[256];
+  if (use_tc) P.rt->tc_macs += (long long)B * M * N * K;
   snprintf(desc, sizeof(desc), "qnn.batch_matmul -> %s B=%d M=%d N=%d K=%d", use_tc ? "tcgen05 i8 GEMM" : "CUDA-core GEMM", B, M, N, K);
   P.add_step(desc, [=](RunCtx& c) {
     if (use_tc) {
@@ -2187,6 +2214,7 @@ static void build_plan(tkb_runtime* rt) {
   rt->chain_enabled = rt->chain_policy != 0 && rt->conv_impl != "simt" && rt->conv_impl != "tc_nochain" && !getenv("TKB_NO_CHAIN");
   rt->arena_bytes = 0;
   rt->macs = rt->hbm_bytes = 0;
+  rt->tc_macs = 0;
   rt->trace_recs.clear();
   for (auto& e : rt->ent) { e.off[0] = e.off[1] = -1; e.alias_of = -1; }
   for (uint32_t eid : g.input_eids) rt->ent[eid].off[kLogical] = P.arena_alloc(rt->ent[eid].bytes());  // H2D staging
@@ -2826,6 +2854,8 @@ int tkb_work(tkb_handle h, int64_t* macs, int64_t* hbm_bytes) {
   if (hbm_bytes) *hbm_bytes = h->hbm_bytes;
   return 0;
 }
+
+int64_t tkb_tc_macs(tkb_handle h) { return h ? h->tc_macs : 0; }
 
 static Workspace* stream_ws(tkb_handle h, cudaStream_t s) {
   std::lock_guard<std::mutex> lk(h->ws_mu);

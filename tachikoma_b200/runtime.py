@@ -259,6 +259,12 @@ class TachikomaJSONRuntime:
         self._lib.tkb_work(self._h, ctypes.byref(macs), ctypes.byref(hbm))
         return macs.value, hbm.value
 
+    def tc_macs(self):
+        """int8 MACs of the plan's tcgen05 launches (the ones tc_time() times)."""
+        self._lib.tkb_tc_macs.restype = ctypes.c_int64
+        self._lib.tkb_tc_macs.argtypes = [ctypes.c_void_p]
+        return int(self._lib.tkb_tc_macs(self._h))
+
     def tc_time(self):
         """(milliseconds, launches) of the tcgen05 GEMM kernels in the last run (needs option time_tc=1)."""
         ms, n = ctypes.c_double(), ctypes.c_int()

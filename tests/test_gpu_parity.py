@@ -1065,3 +1065,47 @@ def test_ragged_output_channels_on_the_vector_epilogue(oc, with_sum):
         for impl in ("tc", "tc_im2col"):
             out, mod, _ = run_gpu(f, ins, conv_impl=impl, trace=True)
             np.testing.assert_equal(out, want, err_msg=f"oc={oc} k={k} {odt} sum={with_sum} {impl}")
+
+
+# ---- pointwise convolutions with 8 .. 32 input channels: CUDA-core dp4a kernel in the default plan -----------------------------
+PW_CASES = {
+    # name: (n, ic, h, w, oc, zp_a, per_channel, relu, xdt, out_dt, clip)
+    "mbv2_32_16": (2, 32, 20, 20, 16, 0, True, False, "uint8", "uint8", None),
+    "mbv2_16_96": (2, 16, 20, 20, 96, 0, True, True, "uint8", "uint8", None),
+    "mbv2_24_144_zp": (1, 24, 17, 13, 144, 128, True, True, "uint8", "uint8", (0.0, 255.0)),
+    "k8_n8_ragged_pixels": (3, 8, 13, 17, 8, 3, False, True, "uint8", "uint8", None),     # 663 pixels: a partial pixel group
+    "k32_n24_s8": (3, 32, 9, 11, 24, 0, True, False, "int8", "int8", None),
+    "k16_n40_explicit_clamp": (1, 16, 12, 12, 40, 7, True, True, "uint8", "uint8", (20.0, 200.0)),
+    "k24_n1024": (1, 24, 6, 6, 1024, 0, True, False, "uint8", "int8", None),
+}
+
+
+@pytest.mark.parametrize("nhwc", [False, True], ids=["nchw", "nhwc"])
+@pytest.mark.parametrize("name", list(PW_CASES))
+def test_pointwise_few_channel_conv_vs_oracle(name, nhwc, monkeypatch):
+    monkeypatch.setenv("TKB_PW_MIN_M", "1")  # the default plan takes this kernel from 2^18 pixels up (read at plan time)
+    n, ic, h, w, oc, zp_a, pc, relu, xdt, odt, clip = PW_CASES[name]
+    func, args = _chain_conv(n, ic, h, w, oc, 1, 1, 0, 1, zp_a, pc, relu, False, seed=len(name) * 13 + oc, nhwc=nhwc, xdt=xdt,
+                             out_dt=odt, clip=clip)
+    ref, _ = interp.run_expr(func, args)
+    out, mod, (js, consts, ins) = run_gpu(func, args, conv_impl="auto", trace=True)
+    np.testing.assert_equal(out, ref)
+    want, recs = interp.run_json(js, consts, ins, want_trace=True)
+    assert mod.trace_blob() == interp.save_ndarray_list(recs)
+    out_tc, mod_tc, _ = run_gpu(func, args, conv_impl="tc")
+    np.testing.assert_equal(out_tc, ref)
+    assert "tcgen05" in mod_tc.plan_summary()
+    if nhwc:  # a graph input in logical NCHW form is gathered from NCHW instead (explicit im2col path)
+        assert "CUDA-core pointwise conv" in mod.plan_summary(), mod.plan_summary()
+
+
+def test_mobilenet_default_plan_uses_the_pointwise_kernel_and_matches_tc_plan(monkeypatch):
+    monkeypatch.setenv("TKB_PW_MIN_M", "1")
+    from tachikoma_b200 import models
+    func = models.mobilenetv2(batch=2, image=64, num_classes=100)
+    x = np.random.default_rng(3).integers(0, 256, (2, 3, 64, 64)).astype("uint8")
+    a, mod_a, _ = run_gpu(func, {"data": x}, conv_impl="auto", trace=True)
+    b, mod_b, _ = run_gpu(func, {"data": x}, conv_impl="tc", trace=True)
+    np.testing.assert_equal(a, b)
+    assert mod_a.trace_blob() == mod_b.trace_blob()
+    assert mod_a.plan_summary().count("CUDA-core pointwise conv") >= 3

@@ -110,7 +110,8 @@ class ClockSampler:
 
 SHAPES = {"mlp": "784-128-10 MLP (configs[0])", "lenet5": "LeNet-5 28x28 (configs[1])",
           "resnet18": "resnet18 224x224 (configs[2])", "mobilenetv2": "mobilenetv2 224x224 (configs[3])",
-          "bert_encoder": "BERT-base encoder, 1 of 12 layers, seq 128, hidden 768 (configs[4]; batch = sequences)"}
+          "bert_encoder": "BERT-base encoder, 1 of 12 layers, seq 128, hidden 768 (configs[4]; batch = sequences)",
+          "bert_base": "BERT-base encoder, all 12 layers, seq 128, hidden 768 (configs[4]; batch = sequences)"}
 
 
 def workload_string(model, batch):

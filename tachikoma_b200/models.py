@@ -152,7 +152,7 @@ def _input(shape, seed=1):
 
 def synthetic_input(name, batch, seed=1):
     shape = {"mlp": (batch, 784), "lenet5": (batch, 1, 28, 28), "resnet18": (batch, 3, 224, 224),
-             "mobilenetv2": (batch, 3, 224, 224), "bert_encoder": (batch * 128, 768)}[name]
+             "mobilenetv2": (batch, 3, 224, 224), "bert_encoder": (batch * 128, 768), "bert_base": (batch * 128, 768)}[name]
     return _input(shape, seed)
 
 
@@ -330,4 +330,10 @@ def bert_encoder(batch=8, seed=0, seq=128, hidden=768, heads=12, ffn=3072, layer
     return R.Function([x], e)
 
 
-MODELS = {"mlp": mlp, "lenet5": lenet5, "resnet18": resnet18, "mobilenetv2": mobilenetv2, "bert_encoder": bert_encoder}
+def bert_base(batch=8, seed=0):
+    """C5 at full depth: all 12 encoder layers of BERT-base (bert_encoder with layers=12)."""
+    return bert_encoder(batch=batch, seed=seed, layers=12)
+
+
+MODELS = {"mlp": mlp, "lenet5": lenet5, "resnet18": resnet18, "mobilenetv2": mobilenetv2, "bert_encoder": bert_encoder,
+          "bert_base": bert_base}

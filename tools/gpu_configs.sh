@@ -3,7 +3,7 @@
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 : > gpurun_out/configs.jsonl
-for cfg in "mlp 256" "lenet5 256" "resnet18 64" "mobilenetv2 128" "bert_encoder 8"; do
+for cfg in "mlp 256" "lenet5 256" "resnet18 64" "mobilenetv2 128" "bert_encoder 8" "bert_base 8"; do
   set -- $cfg
   timeout 600 python bench.py --model $1 --batch $2 --steps 20 --warmup 3 >> gpurun_out/configs.jsonl 2>> gpurun_out/configs.err || echo "{\"model\": \"$1\", \"failed\": true}" >> gpurun_out/configs.jsonl
 done

@@ -10,6 +10,30 @@ namespace tkb {
 
 thread_local long long g_launches = 0;
 
+// Programmatic dependent launch for the CUDA-core kernels that sit between tcgen05 layers (stem unfold, max pool, casts,
+// average pool, depthwise / pointwise convolutions, qnn.add): the kernel lets its successor start launching at once and
+// waits for its predecessor's memory before it touches any tensor, so launch latency and the neighbour's tail overlap as
+// they do between the tensor-core kernels (profiles/r02_notes.md section 17: worth ~2.3 us per boundary there).
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+template <typename... KArgs, typename... Args>
+static void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+  static const bool off = getenv("TKB_NO_PDL") != nullptr;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = off ? 0 : 1;
+  cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 static inline int blocks_for(long long n, int threads) {
   long long b = (n + threads - 1) / threads;
   const long long cap = 148LL * 32;  // grid-stride beyond 32 CTAs per SM
@@ -274,6 +298,7 @@ __global__ void __launch_bounds__(128) dwconv3x3_v16_kernel(const uint8_t* __res
   //   dw_ws [3 rows][4 words][cg]: row-packed weights, one 32-bit lane = one channel's {w(r,0), w(r,1), w(r,2), 0}
   //   dw_tab[16 channels][cg]    : folded requantize constants {M, T - 32, C_lo, C_hi}
   extern __shared__ uint4 dw_ws[];
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // (the constants below do not depend on the predecessor)
   const int cg = g.C >> 4;
   int4* dw_tab = (int4*)(dw_ws + 12 * cg);
   for (int i = threadIdx.x; i < 12 * cg; i += 128) {   // i = (r * 4 + k) * cg + group
@@ -284,6 +309,7 @@ __global__ void __launch_bounds__(128) dwconv3x3_v16_kernel(const uint8_t* __res
     const int grp = i % cg, e = i / cg;
     dw_tab[i] = __ldg(f.tabA + grp * 16 + e);
   }
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   __syncthreads();
   const int t = blockIdx.x * 128 + threadIdx.x;
   if (t >= g.OW * cg) return;
@@ -389,6 +415,7 @@ __global__ void __launch_bounds__(256) pwconv_kernel(const uint8_t* __restrict__
                                                      uint8_t* __restrict__ y, long long M, int N, FastEpi f) {
   constexpr int KW = KB / 4, KW4 = (KW + 3) / 4, PX = 4;  // input words per pixel, weight uint4 per channel, pixels per thread
   extern __shared__ uint4 pw_smem[];
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // (the constants below do not depend on the predecessor)
   const int NB = N / CB;
   uint4* ws = pw_smem;                           // [CB][KW4][NB]
   int4* tab = (int4*)(pw_smem + CB * KW4 * NB);  // [CB][NB]
@@ -400,6 +427,7 @@ __global__ void __launch_bounds__(256) pwconv_kernel(const uint8_t* __restrict__
     const int nb = i % NB, c = i / NB;
     tab[i] = __ldg(f.tabA + nb * CB + c);
   }
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   __syncthreads();
   // A thread's 4 pixels are PS = 32 apart (pixel slot q -> pixels (q / 32) * 128 + q % 32 + 32 * i): for a given i the
   // lanes of a warp then read / write neighbouring pixels, i.e. a contiguous stretch of memory per instruction.  (With 4
@@ -489,7 +517,7 @@ int launch_pwconv(const void* x, const void* w, void* y, long long M, int N, int
   const bool au = a_dtype == kU8, wu = w_dtype == kU8;
 #define TKB_PW(AU_, WU_, KB_, CB_)                                                                                        \
   if (au == AU_ && wu == WU_ && K == KB_ && CB == CB_) {                                                                  \
-    pwconv_kernel<AU_, WU_, KB_, CB_><<<grid, 256, smem, s>>>((const uint8_t*)x, (const uint32_t*)w, (uint8_t*)y, M, N, f); \
+    launch_pdl(pwconv_kernel<AU_, WU_, KB_, CB_>, dim3(grid), dim3(256), smem, s, (const uint8_t*)x, (const uint32_t*)w, (uint8_t*)y, M, N, f); \
     ++g_launches;                                                                                                          \
     return cudaGetLastError() == cudaSuccess ? 0 : -1;                                                                     \
   }
@@ -520,8 +548,8 @@ void launch_dwconv_nhwc(const void* x, const void* w_tap, const void* w_row3, co
     dim3 grid((unsigned)((g.OW * (g.C / 16) + 127) / 128), (unsigned)((g.OH + nv - 1) / nv), (unsigned)g.N);
 #define TKB_DW16(AU_, WU_)                                                                                 \
   if (au == AU_ && wu == WU_) {                                                                            \
-    if (g.sh == 1) dwconv3x3_v16_kernel<AU_, WU_, 1, NV1><<<grid, 128, 28 * g.C, s>>>(xp, wp, y, g, f);     \
-    else dwconv3x3_v16_kernel<AU_, WU_, 2, NV2><<<grid, 128, 28 * g.C, s>>>(xp, wp, y, g, f);               \
+    if (g.sh == 1) launch_pdl(dwconv3x3_v16_kernel<AU_, WU_, 1, NV1>, grid, dim3(128), (size_t)28 * g.C, s, xp, wp, y, g, f); \
+    else launch_pdl(dwconv3x3_v16_kernel<AU_, WU_, 2, NV2>, grid, dim3(128), (size_t)28 * g.C, s, xp, wp, y, g, f);          \
   }
     TKB_DW16(true, true) TKB_DW16(true, false) TKB_DW16(false, true) TKB_DW16(false, false)
 #undef TKB_DW16
@@ -665,6 +693,7 @@ __global__ void qnn_add_kernel(const void* __restrict__ a, const void* __restric
 // one ring add and the clamp -- the kernel is then HBM-bound instead of bound by two int64 fixed-point multiplies.
 __global__ void __launch_bounds__(256) qnn_add_lut_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
                                                           uint4* __restrict__ y, int dtype, long long nv, EpiParams e) {
+  pdl_enter();
   __shared__ int32_t tl[256], tr[256];
   {
     const int i = threadIdx.x;
@@ -699,7 +728,7 @@ void launch_qnn_add(const void* a, const void* b, void* y, int dtype, long long 
       ((((uintptr_t)a) | ((uintptr_t)b) | ((uintptr_t)y)) & 15) == 0) {
     const long long nv = n >> 4;
     const int nb = (int)std::min<long long>((nv + 255) / 256, 148LL * 8);
-    qnn_add_lut_kernel<<<nb, 256, 0, s>>>((const uint4*)a, (const uint4*)b, (uint4*)y, dtype, nv, e);
+    launch_pdl(qnn_add_lut_kernel, dim3(nb), dim3(256), 0, s, (const uint4*)a, (const uint4*)b, (uint4*)y, dtype, nv, e);
     ++g_launches;
     return;
   }
@@ -1005,6 +1034,7 @@ __global__ void cast_kernel(const void* __restrict__ x, int xd, void* __restrict
 // 8-bit -> 32-bit integer widening, 4 elements per thread (32-bit load, 128-bit store)
 template <bool SIGNED>
 __global__ void cast_8_to_32_kernel(const uint32_t* __restrict__ x, int4* __restrict__ y, unsigned n4) {
+  pdl_enter();
   const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n4) return;
   const uint32_t w = __ldg(x + i);
@@ -1013,6 +1043,7 @@ __global__ void cast_8_to_32_kernel(const uint32_t* __restrict__ x, int4* __rest
 }
 // 32-bit -> 8-bit truncation (LLVM trunc), 4 elements per thread
 __global__ void cast_32_to_8_kernel(const int4* __restrict__ x, uint32_t* __restrict__ y, unsigned n4) {
+  pdl_enter();
   const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n4) return;
   const int4 v = __ldg(x + i);
@@ -1025,13 +1056,13 @@ void launch_cast(const void* x, int x_dtype, void* y, int y_dtype, long long n, 
   if ((n & 3) == 0 && n / 4 < (1LL << 31) && ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0) {
     const unsigned n4 = (unsigned)(n / 4), nb = (n4 + 255) / 256;
     if (x8 && y_dtype == kI32) {
-      if (x_dtype == kI8) cast_8_to_32_kernel<true><<<nb, 256, 0, s>>>((const uint32_t*)x, (int4*)y, n4);
-      else cast_8_to_32_kernel<false><<<nb, 256, 0, s>>>((const uint32_t*)x, (int4*)y, n4);
+      if (x_dtype == kI8) launch_pdl(cast_8_to_32_kernel<true>, dim3(nb), dim3(256), 0, s, (const uint32_t*)x, (int4*)y, n4);
+      else launch_pdl(cast_8_to_32_kernel<false>, dim3(nb), dim3(256), 0, s, (const uint32_t*)x, (int4*)y, n4);
       ++g_launches;
       return;
     }
     if (x_dtype == kI32 && y8) {
-      cast_32_to_8_kernel<<<nb, 256, 0, s>>>((const int4*)x, (uint32_t*)y, n4);
+      launch_pdl(cast_32_to_8_kernel, dim3(nb), dim3(256), 0, s, (const int4*)x, (uint32_t*)y, n4);
       ++g_launches;
       return;
     }
@@ -1154,6 +1185,7 @@ __global__ void maxpool8_nhwc_kernel(const uint8_t* __restrict__ x, uint8_t* __r
 template <bool UNSIGNED>
 __global__ void __launch_bounds__(256) maxpool8_nhwc_3x3s2_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y,
                                                                   PoolArgs a) {
+  pdl_enter();
   const int cg = a.C >> 4;
   const int t = blockIdx.x * 256 + threadIdx.x;
   if (t >= a.OW * cg) return;
@@ -1198,6 +1230,7 @@ __global__ void __launch_bounds__(256) maxpool8_nhwc_3x3s2_kernel(const uint8_t*
 // (unrolled by 7) so several are in flight; sum wraps in int32 and the division truncates toward zero, as the
 // reference's topi pool (include/tvm/topi/nn/pooling.h:389, :624-650).
 __global__ void global_avgpool_nhwc_i32_kernel(const int32_t* __restrict__ x, int32_t* __restrict__ y, int HW, int C) {
+  pdl_enter();
   const int c = blockIdx.x * blockDim.x + threadIdx.x, n = blockIdx.y;
   if (c >= C) return;
   const int32_t* p = x + (long long)n * HW * C + c;
@@ -1232,8 +1265,8 @@ void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_incl
     const long long work = total / 16;
     if (KH == 3 && KW == 3 && sh == 2 && sw == 2 && pt <= 2 && pl <= 2 && N <= 65535 && a.OH <= 131070 && H >= 2 && W >= 2) {
       dim3 grid((unsigned)((a.OW * (C / 16) + 255) / 256), (unsigned)((a.OH + 1) / 2), (unsigned)N);
-      if (dtype == kU8) maxpool8_nhwc_3x3s2_kernel<true><<<grid, 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
-      else maxpool8_nhwc_3x3s2_kernel<false><<<grid, 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
+      if (dtype == kU8) launch_pdl(maxpool8_nhwc_3x3s2_kernel<true>, grid, dim3(256), 0, s, (const uint8_t*)x, (uint8_t*)y, a);
+      else launch_pdl(maxpool8_nhwc_3x3s2_kernel<false>, grid, dim3(256), 0, s, (const uint8_t*)x, (uint8_t*)y, a);
       ++g_launches;
       return;
     }
@@ -1245,7 +1278,7 @@ void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_incl
   if (is_avg && dtype == kI32 && dense_nhwc && KH == H && KW == W && pt + pb + pl + pr == 0 && N <= 65535 && H * W > 0) {
     // int32: the adaptive (is_avg == 2) and the windowed divisor are both H * W
     dim3 grid((unsigned)((C + 127) / 128), (unsigned)N);
-    global_avgpool_nhwc_i32_kernel<<<grid, 128, 0, s>>>((const int32_t*)x, (int32_t*)y, H * W, C);
+    launch_pdl(global_avgpool_nhwc_i32_kernel, grid, dim3(128), 0, s, (const int32_t*)x, (int32_t*)y, H * W, C);
     ++g_launches;
     return;
   }
@@ -1258,6 +1291,7 @@ void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_incl
 // per-operator trace and for subgraph outputs.  Requires C % 4 == 0, HW % 4 == 0, 4-byte aligned bases.
 __global__ void __launch_bounds__(256) nhwc_to_nchw8_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y, int HW, int C) {
   __shared__ uint8_t tile[64][68];
+  pdl_enter();
   const int n = blockIdx.z, hw0 = blockIdx.x * 64, c0 = blockIdx.y * 64;
   const uint8_t* xin = x + (long long)n * HW * C;
   uint8_t* yout = y + (long long)n * HW * C;
@@ -1287,7 +1321,7 @@ bool launch_nhwc_to_nchw8(const void* x, void* y, long long N, long long HW, lon
   if ((C & 3) || (HW & 3) || ((((uintptr_t)x) | ((uintptr_t)y)) & 3) || N > 65535 || (C + 63) / 64 > 65535) return false;
   if (N * HW * C == 0) return true;
   dim3 grid((unsigned)((HW + 63) / 64), (unsigned)((C + 63) / 64), (unsigned)N);
-  nhwc_to_nchw8_kernel<<<grid, 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, (int)HW, (int)C);
+  launch_pdl(nhwc_to_nchw8_kernel, grid, dim3(256), 0, s, (const uint8_t*)x, (uint8_t*)y, (int)HW, (int)C);
   ++g_launches;
   return true;
 }
@@ -1297,6 +1331,7 @@ bool launch_nhwc_to_nchw8(const void* x, void* y, long long N, long long HW, lon
 template <typename T>
 __global__ void __launch_bounds__(256) transpose_tile_kernel(const T* __restrict__ x, T* __restrict__ y, int A, int B) {
   __shared__ T tile[32][33];
+  pdl_enter();
   const long long base = (long long)blockIdx.z * A * B;
   const int a0 = blockIdx.x * 32, b0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
@@ -1316,9 +1351,9 @@ __global__ void __launch_bounds__(256) transpose_tile_kernel(const T* __restrict
 bool launch_transpose_tile(const void* x, void* y, int elem, long long N, long long A, long long B, cudaStream_t s) {
   if (N > 65535 || (B + 31) / 32 > 65535 || N * A * B == 0) return N * A * B == 0;
   dim3 grid((unsigned)((A + 31) / 32), (unsigned)((B + 31) / 32), (unsigned)N);
-  if (elem == 1) transpose_tile_kernel<uint8_t><<<grid, 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, (int)A, (int)B);
-  else if (elem == 2) transpose_tile_kernel<uint16_t><<<grid, 256, 0, s>>>((const uint16_t*)x, (uint16_t*)y, (int)A, (int)B);
-  else if (elem == 4) transpose_tile_kernel<uint32_t><<<grid, 256, 0, s>>>((const uint32_t*)x, (uint32_t*)y, (int)A, (int)B);
+  if (elem == 1) launch_pdl(transpose_tile_kernel<uint8_t>, grid, dim3(256), 0, s, (const uint8_t*)x, (uint8_t*)y, (int)A, (int)B);
+  else if (elem == 2) launch_pdl(transpose_tile_kernel<uint16_t>, grid, dim3(256), 0, s, (const uint16_t*)x, (uint16_t*)y, (int)A, (int)B);
+  else if (elem == 4) launch_pdl(transpose_tile_kernel<uint32_t>, grid, dim3(256), 0, s, (const uint32_t*)x, (uint32_t*)y, (int)A, (int)B);
   else return false;
   ++g_launches;
   return true;
@@ -1573,6 +1608,7 @@ __global__ void unfold_rows_nchw_kernel(const uint8_t* __restrict__ x, uint8_t* 
 template <int C_, int KH_>
 __global__ void __launch_bounds__(256) unfold_rows_nchw_vec_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y,
                                                                    ConvGeom g) {
+  pdl_enter();
   constexpr int CP = 32, KC = KH_ * C_, NG = (KC + 3) / 4;  // NG groups of 4 source lines -> output word NG-1 max
   __shared__ uint4 slab[8][32 * 9];                          // per warp: 32 lanes x (128 + 16) bytes
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1661,10 +1697,10 @@ void launch_unfold_rows_nchw(const void* x, void* y, const ConvGeom& g, cudaStre
     const long long nwarps = (long long)g.N * g.OH * ((g.W + 127) / 128);
     const int nbv = (int)std::min<long long>((nwarps + 7) / 8, 148LL * 64);
     bool done = true;
-    if (g.C == 3 && g.KH == 7) unfold_rows_nchw_vec_kernel<3, 7><<<nbv, 256, 0, s>>>(xi, yo, g);
-    else if (g.C == 3 && g.KH == 3) unfold_rows_nchw_vec_kernel<3, 3><<<nbv, 256, 0, s>>>(xi, yo, g);
-    else if (g.C == 1 && g.KH == 5) unfold_rows_nchw_vec_kernel<1, 5><<<nbv, 256, 0, s>>>(xi, yo, g);
-    else if (g.C == 1 && g.KH == 3) unfold_rows_nchw_vec_kernel<1, 3><<<nbv, 256, 0, s>>>(xi, yo, g);
+    if (g.C == 3 && g.KH == 7) launch_pdl(unfold_rows_nchw_vec_kernel<3, 7>, dim3(nbv), dim3(256), 0, s, xi, yo, g);
+    else if (g.C == 3 && g.KH == 3) launch_pdl(unfold_rows_nchw_vec_kernel<3, 3>, dim3(nbv), dim3(256), 0, s, xi, yo, g);
+    else if (g.C == 1 && g.KH == 5) launch_pdl(unfold_rows_nchw_vec_kernel<1, 5>, dim3(nbv), dim3(256), 0, s, xi, yo, g);
+    else if (g.C == 1 && g.KH == 3) launch_pdl(unfold_rows_nchw_vec_kernel<1, 3>, dim3(nbv), dim3(256), 0, s, xi, yo, g);
     else done = false;
     if (done) { ++g_launches; return; }
   }
@@ -1679,6 +1715,7 @@ void launch_unfold_rows_nchw(const void* x, void* y, const ConvGeom& g, cudaStre
 // 1x1 / stride-1 / unpadded convolution whose channel count is not a multiple of 16 (e.g. 24): the im2col matrix is
 // the activation matrix with every row zero-padded from C to Kp bytes; 8 bytes per thread, 32-bit indices.
 __global__ void pad_rows8_kernel(const uint2* __restrict__ x, uint2* __restrict__ a, unsigned total, int c8, int k8) {
+  pdl_enter();
   const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   const unsigned m = i / (unsigned)k8, ch = i - m * (unsigned)k8;
@@ -1690,7 +1727,7 @@ void launch_im2col(const void* x, void* a, const ConvGeom& g, int Kp, cudaStream
   if (g.KH == 1 && g.KW == 1 && g.sh == 1 && g.sw == 1 && !(g.pt | g.pl | g.pb | g.pr) && (g.C & 15) != 0 && (g.C & 7) == 0 &&
       (Kp & 7) == 0 && M * (Kp >> 3) < (1LL << 31) && M > 0 && ((((uintptr_t)x) | ((uintptr_t)a)) & 7) == 0) {
     const unsigned total = (unsigned)(M * (Kp >> 3));
-    pad_rows8_kernel<<<(total + 255) / 256, 256, 0, s>>>((const uint2*)x, (uint2*)a, total, g.C >> 3, Kp >> 3);
+    launch_pdl(pad_rows8_kernel, dim3((total + 255) / 256), dim3(256), 0, s, (const uint2*)x, (uint2*)a, total, g.C >> 3, Kp >> 3);
     ++g_launches;
     return;
   }

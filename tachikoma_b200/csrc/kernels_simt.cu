@@ -636,6 +636,7 @@ void launch_gemm_simt(const void* x, const void* w, void* y, int B, int M, int N
 
 __global__ void requantize_kernel(const void* __restrict__ x, int x_dtype, void* __restrict__ y, int y_dtype,
                                   long long total, int C, long long inner, RqParams p) {
+  pdl_enter();
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)((i / inner) % C);
@@ -650,13 +651,14 @@ void launch_requantize(const void* x, int x_dtype, void* y, int y_dtype, long lo
                        const RqParams& p, cudaStream_t s) {
   const long long total = outer * C * inner;
   if (total == 0) return;
-  requantize_kernel<<<blocks_for(total, 256), 256, 0, s>>>(x, x_dtype, y, y_dtype, total, C, inner, p);
+  launch_pdl(requantize_kernel, dim3(blocks_for(total, 256)), dim3(256), 0, s, x, x_dtype, y, y_dtype, total, C, inner, p);
   ++g_launches;
 }
 
 // qnn.add, HBM-bound: 16 bytes per thread per operand for the 8-bit dtypes.
 __global__ void qnn_add_kernel(const void* __restrict__ a, const void* __restrict__ b, void* __restrict__ y,
                                int dtype, long long n, EpiParams e) {
+  pdl_enter();
   const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const long long stride = (long long)gridDim.x * blockDim.x;
   if ((dtype == kU8 || dtype == kI8) && (n & 15) == 0 &&
@@ -733,7 +735,7 @@ void launch_qnn_add(const void* a, const void* b, void* y, int dtype, long long 
     return;
   }
   const long long work = (dtype == kU8 || dtype == kI8) && (n & 15) == 0 ? n >> 4 : n;
-  qnn_add_kernel<<<blocks_for(work, 256), 256, 0, s>>>(a, b, y, dtype, n, e);
+  launch_pdl(qnn_add_kernel, dim3(blocks_for(work, 256)), dim3(256), 0, s, a, b, y, dtype, n, e);
   ++g_launches;
 }
 
@@ -748,6 +750,7 @@ __device__ __forceinline__ int32_t qnn_mul_one(int32_t a, int32_t b, int32_t zpa
 
 __global__ void __launch_bounds__(256) qnn_mul8_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ y,
                                                        int dtype, long long nv, int32_t zpa, int32_t zpb, RqParams rq) {
+  pdl_enter();
   for (long long i = blockIdx.x * 256LL + threadIdx.x; i < nv; i += (long long)gridDim.x * 256) {
     const uint4 va = __ldg(a + i), vb = __ldg(b + i);
     const uint32_t pa[4] = {va.x, va.y, va.z, va.w}, pb[4] = {vb.x, vb.y, vb.z, vb.w};
@@ -769,6 +772,7 @@ __global__ void __launch_bounds__(256) qnn_mul8_kernel(const uint4* __restrict__
 
 __global__ void qnn_mul_kernel(const void* __restrict__ a, const void* __restrict__ b, void* __restrict__ y, int dtype,
                                long long n, int32_t zpa, int32_t zpb, RqParams rq) {
+  pdl_enter();
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     store_from_i32(y, dtype, i, qnn_mul_one(load_as_i32(a, dtype, i), load_as_i32(b, dtype, i), zpa, zpb, rq));
 }
@@ -779,9 +783,9 @@ void launch_qnn_mul(const void* a, const void* b, void* y, int dtype, long long 
   if ((dtype == kU8 || dtype == kI8) && (n & 15) == 0 && ((((uintptr_t)a) | ((uintptr_t)b) | ((uintptr_t)y)) & 15) == 0) {
     const long long nv = n >> 4;
     const int nb = (int)std::min<long long>((nv + 255) / 256, 148LL * 8);
-    qnn_mul8_kernel<<<nb, 256, 0, s>>>((const uint4*)a, (const uint4*)b, (uint4*)y, dtype, nv, zpa, zpb, rq);
+    launch_pdl(qnn_mul8_kernel, dim3(nb), dim3(256), 0, s, (const uint4*)a, (const uint4*)b, (uint4*)y, dtype, nv, zpa, zpb, rq);
   } else {
-    qnn_mul_kernel<<<blocks_for(n, 256), 256, 0, s>>>(a, b, y, dtype, n, zpa, zpb, rq);
+    launch_pdl(qnn_mul_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, s, a, b, y, dtype, n, zpa, zpb, rq);
   }
   ++g_launches;
 }
@@ -892,6 +896,7 @@ void launch_dequantize(const void* x, int x_dtype, float* y, long long outer, in
 // when Ci * inner and the offsets allow.
 __global__ void concat_piece_kernel(const void* __restrict__ x, void* __restrict__ y, int dtype, long long outer, long long row_in,
                                     long long row_out, long long off, RqParams rq, int requant, int vec16) {
+  pdl_enter();
   const long long stride = (long long)gridDim.x * blockDim.x;
   if (vec16) {  // rows and offsets are multiples of 16 bytes, no requantize
     const long long rv = row_in * dtype_size(dtype) / 16, ov = row_out * dtype_size(dtype) / 16, offv = off * dtype_size(dtype) / 16;
@@ -916,7 +921,7 @@ void launch_concat_piece(const void* x, void* y, int dtype, long long outer, lon
   const int vec16 = !requant && (row_in * es) % 16 == 0 && (row_out * es) % 16 == 0 && (off * es) % 16 == 0 &&
                     ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0;
   const long long work = vec16 ? outer * row_in * es / 16 : outer * row_in;
-  concat_piece_kernel<<<blocks_for(work, 256), 256, 0, s>>>(x, y, dtype, outer, row_in, row_out, off, rq, requant, vec16);
+  launch_pdl(concat_piece_kernel, dim3(blocks_for(work, 256)), dim3(256), 0, s, x, y, dtype, outer, row_in, row_out, off, rq, requant, vec16);
   ++g_launches;
 }
 
@@ -926,6 +931,7 @@ void launch_concat_piece(const void* x, void* y, int dtype, long long outer, lon
 template <typename T>
 __global__ void lut8_kernel(const uint8_t* __restrict__ x, const T* __restrict__ table, int entries, T* __restrict__ y,
                             long long n, int vec16) {
+  pdl_enter();
   __shared__ T tab[256];
   for (int i = threadIdx.x; i < 256; i += blockDim.x) tab[i] = i < entries ? table[i] : T(0);
   __syncthreads();
@@ -955,9 +961,9 @@ void launch_lut8(const void* x, const void* table, int entries, int elem, void* 
   if (n == 0) return;
   const int vec16 = (n % 16 == 0) && ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0;
   const int bl = blocks_for(vec16 ? n / 16 : n, 256);
-  if (elem == 1) lut8_kernel<uint8_t><<<bl, 256, 0, s>>>((const uint8_t*)x, (const uint8_t*)table, entries, (uint8_t*)y, n, vec16);
-  else if (elem == 2) lut8_kernel<uint16_t><<<bl, 256, 0, s>>>((const uint8_t*)x, (const uint16_t*)table, entries, (uint16_t*)y, n, vec16);
-  else lut8_kernel<uint32_t><<<bl, 256, 0, s>>>((const uint8_t*)x, (const uint32_t*)table, entries, (uint32_t*)y, n, vec16);
+  if (elem == 1) launch_pdl(lut8_kernel<uint8_t>, dim3(bl), dim3(256), 0, s, (const uint8_t*)x, (const uint8_t*)table, entries, (uint8_t*)y, n, vec16);
+  else if (elem == 2) launch_pdl(lut8_kernel<uint16_t>, dim3(bl), dim3(256), 0, s, (const uint8_t*)x, (const uint16_t*)table, entries, (uint16_t*)y, n, vec16);
+  else launch_pdl(lut8_kernel<uint32_t>, dim3(bl), dim3(256), 0, s, (const uint8_t*)x, (const uint32_t*)table, entries, (uint32_t*)y, n, vec16);
   ++g_launches;
 }
 
@@ -967,6 +973,7 @@ void launch_lut8(const void* x, const void* table, int entries, int elem, void* 
 __global__ void qnn_leaky_relu_kernel(const void* __restrict__ x, void* __restrict__ y, int dtype, long long n, RqParams rq,
                                       int identity, int32_t zp_in, int32_t m_alpha, int32_t s_alpha, int32_t scaled_z,
                                       int32_t lo, int32_t hi) {
+  pdl_enter();
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const int32_t v = load_as_i32(x, dtype, i);
     const int32_t q = identity ? v : requantize_one(v, 0, rq);
@@ -979,7 +986,7 @@ __global__ void qnn_leaky_relu_kernel(const void* __restrict__ x, void* __restri
 void launch_qnn_leaky_relu(const void* x, void* y, int dtype, long long n, const RqParams& rq, int identity, int32_t zp_in,
                            int32_t m_alpha, int32_t s_alpha, int32_t scaled_z, int32_t lo, int32_t hi, cudaStream_t s) {
   if (n == 0) return;
-  qnn_leaky_relu_kernel<<<blocks_for(n, 256), 256, 0, s>>>(x, y, dtype, n, rq, identity, zp_in, m_alpha, s_alpha, scaled_z, lo, hi);
+  launch_pdl(qnn_leaky_relu_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, s, x, y, dtype, n, rq, identity, zp_in, m_alpha, s_alpha, scaled_z, lo, hi);
   ++g_launches;
 }
 
@@ -998,6 +1005,7 @@ int32_t device_fixed_point_multiply(int32_t x, int32_t m, int32_t s) {
 
 __global__ void clip_kernel(const void* __restrict__ x, void* __restrict__ y, int dtype, long long n, double lo,
                             double hi) {
+  pdl_enter();
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     if (dtype == kF32) {
       float v = ((const float*)x)[i];
@@ -1013,11 +1021,12 @@ __global__ void clip_kernel(const void* __restrict__ x, void* __restrict__ y, in
 
 void launch_clip(const void* x, void* y, int dtype, long long n, double lo, double hi, cudaStream_t s) {
   if (n == 0) return;
-  clip_kernel<<<blocks_for(n, 256), 256, 0, s>>>(x, y, dtype, n, lo, hi);
+  launch_pdl(clip_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, s, x, y, dtype, n, lo, hi);
   ++g_launches;
 }
 
 __global__ void cast_kernel(const void* __restrict__ x, int xd, void* __restrict__ y, int yd, long long n) {
+  pdl_enter();
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     if (xd == kF32) {
       float v = ((const float*)x)[i];
@@ -1067,12 +1076,13 @@ void launch_cast(const void* x, int x_dtype, void* y, int y_dtype, long long n, 
       return;
     }
   }
-  cast_kernel<<<blocks_for(n, 256), 256, 0, s>>>(x, x_dtype, y, y_dtype, n);
+  launch_pdl(cast_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, s, x, x_dtype, y, y_dtype, n);
   ++g_launches;
 }
 
 __global__ void bias_add_kernel(const void* __restrict__ x, const void* __restrict__ b, void* __restrict__ y,
                                 int dtype, long long total, int C, long long inner) {
+  pdl_enter();
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)((i / inner) % C);
@@ -1085,19 +1095,20 @@ void launch_bias_add(const void* x, const void* b, void* y, int dtype, long long
                      cudaStream_t s) {
   const long long total = outer * C * inner;
   if (total == 0) return;
-  bias_add_kernel<<<blocks_for(total, 256), 256, 0, s>>>(x, b, y, dtype, total, C, inner);
+  launch_pdl(bias_add_kernel, dim3(blocks_for(total, 256)), dim3(256), 0, s, x, b, y, dtype, total, C, inner);
   ++g_launches;
 }
 
 __global__ void add_same_kernel(const void* __restrict__ a, const void* __restrict__ b, void* __restrict__ y,
                                 int dtype, long long n) {
+  pdl_enter();
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     store_from_i32(y, dtype, i, (int32_t)((uint32_t)load_as_i32(a, dtype, i) + (uint32_t)load_as_i32(b, dtype, i)));
 }
 
 void launch_add_same(const void* a, const void* b, void* y, int dtype, long long n, cudaStream_t s) {
   if (n == 0) return;
-  add_same_kernel<<<blocks_for(n, 256), 256, 0, s>>>(a, b, y, dtype, n);
+  launch_pdl(add_same_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, s, a, b, y, dtype, n);
   ++g_launches;
 }
 
@@ -1113,6 +1124,7 @@ struct PoolArgs {
 // Thread order follows the output's fastest-varying dimension so that stores coalesce for both
 // channels-last and NCHW tensors.
 __global__ void pool2d_kernel(const void* __restrict__ x, void* __restrict__ y, PoolArgs a) {
+  pdl_enter();
   const long long total = (long long)a.N * a.C * a.OH * a.OW;
   const bool c_fast = a.ys[1] == 1;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
@@ -1153,6 +1165,7 @@ __global__ void pool2d_kernel(const void* __restrict__ x, void* __restrict__ y, 
 // pixel (128-bit loads / stores, byte-wise SIMD max), threads of a warp cover consecutive channel groups.
 template <bool UNSIGNED>
 __global__ void maxpool8_nhwc_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y, PoolArgs a) {
+  pdl_enter();
   const int cg = a.C >> 4;
   const long long total = (long long)a.N * a.OH * a.OW * cg;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
@@ -1270,8 +1283,8 @@ void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_incl
       ++g_launches;
       return;
     }
-    if (dtype == kU8) maxpool8_nhwc_kernel<true><<<blocks_for(work, 256), 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
-    else maxpool8_nhwc_kernel<false><<<blocks_for(work, 256), 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, a);
+    if (dtype == kU8) launch_pdl(maxpool8_nhwc_kernel<true>, dim3(blocks_for(work, 256)), dim3(256), 0, s, (const uint8_t*)x, (uint8_t*)y, a);
+    else launch_pdl(maxpool8_nhwc_kernel<false>, dim3(blocks_for(work, 256)), dim3(256), 0, s, (const uint8_t*)x, (uint8_t*)y, a);
     ++g_launches;
     return;
   }
@@ -1282,7 +1295,7 @@ void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_incl
     ++g_launches;
     return;
   }
-  pool2d_kernel<<<blocks_for(total, 256), 256, 0, s>>>(x, y, a);
+  launch_pdl(pool2d_kernel, dim3(blocks_for(total, 256)), dim3(256), 0, s, x, y, a);
   ++g_launches;
 }
 
@@ -1379,6 +1392,7 @@ struct Perm4 { long long shape[4], istr[4]; };
 // plain gather with coalesced stores.
 template <typename T>
 __global__ void permute4_kernel(const T* __restrict__ x, T* __restrict__ y, Perm4 p) {
+  pdl_enter();
   const long long total = p.shape[0] * p.shape[1] * p.shape[2] * p.shape[3];
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
@@ -1398,10 +1412,10 @@ void launch_permute4(const void* x, void* y, int elem, const long long* out_shap
   for (int i = 0; i < 4; ++i) { p.shape[i] = out_shape[i]; p.istr[i] = in_strides[i]; total *= out_shape[i]; }
   if (total == 0) return;
   const int bl = blocks_for(total, 256);
-  if (elem == 1) permute4_kernel<uint8_t><<<bl, 256, 0, s>>>((const uint8_t*)x, (uint8_t*)y, p);
-  else if (elem == 2) permute4_kernel<uint16_t><<<bl, 256, 0, s>>>((const uint16_t*)x, (uint16_t*)y, p);
-  else if (elem == 8) permute4_kernel<uint64_t><<<bl, 256, 0, s>>>((const uint64_t*)x, (uint64_t*)y, p);
-  else permute4_kernel<uint32_t><<<bl, 256, 0, s>>>((const uint32_t*)x, (uint32_t*)y, p);
+  if (elem == 1) launch_pdl(permute4_kernel<uint8_t>, dim3(bl), dim3(256), 0, s, (const uint8_t*)x, (uint8_t*)y, p);
+  else if (elem == 2) launch_pdl(permute4_kernel<uint16_t>, dim3(bl), dim3(256), 0, s, (const uint16_t*)x, (uint16_t*)y, p);
+  else if (elem == 8) launch_pdl(permute4_kernel<uint64_t>, dim3(bl), dim3(256), 0, s, (const uint64_t*)x, (uint64_t*)y, p);
+  else launch_pdl(permute4_kernel<uint32_t>, dim3(bl), dim3(256), 0, s, (const uint32_t*)x, (uint32_t*)y, p);
   ++g_launches;
 }
 

@@ -66,6 +66,9 @@ void launch_bias_add(const void* x, const void* b, void* y, int dtype, long long
 void launch_add_same(const void* a, const void* b, void* y, int dtype, long long n, cudaStream_t s);
 // pooling with explicit element strides (n,c,h,w) for input and output; is_avg: 0 max, 1 windowed average,
 // 2 adaptive / global average (divisor cast to the tensor dtype, include/tvm/topi/nn/pooling.h:384-389)
+// cast(8-bit -> int32) -> global average pool -> cast(-> 8-bit) in one launch over channels-last data [N][HW][C], C % 4 == 0;
+// cast_out (the int32 copy of x, [N][HW][C]) may be nullptr
+void launch_upcast_gap(const void* x, int x_dtype, void* cast_out, void* pooled, void* out8, int N, int HW, int C, cudaStream_t s);
 void launch_pool2d(const void* x, void* y, int dtype, int is_avg, int count_include_pad, int N, int C, int H, int W,
                    int KH, int KW, int sh, int sw, int pt, int pl, int pb, int pr, const long long* xs,
                    const long long* ys, cudaStream_t s);

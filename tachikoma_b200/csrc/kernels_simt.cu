@@ -1242,6 +1242,50 @@ __global__ void __launch_bounds__(256) maxpool8_nhwc_3x3s2_kernel(const uint8_t*
 // Global average pool of a dense channels-last int32 tensor: one thread per (n, c), the HW loads are independent
 // (unrolled by 7) so several are in flight; sum wraps in int32 and the division truncates toward zero, as the
 // reference's topi pool (include/tvm/topi/nn/pooling.h:389, :624-650).
+// cast(8-bit -> int32) -> nn.global_avg_pool2d -> cast(int32 -> 8-bit), the frontend's apply_with_upcast form
+// (python/tvm/relay/frontend/qnn_torch.py:587-590), in one launch: a thread owns 4 channels of one image, sums the
+// H * W pixels in 32-bit wrap-around arithmetic, divides truncating (the int32 lowering, pooling.h:389) and writes the
+// pooled int32 value and its truncating 8-bit cast.  The int32 copy of the input (the first cast's output) is written
+// only when a trace wants it (cast_out != nullptr).  Same integers as the three separate kernels.
+template <bool SIGNED>
+__global__ void __launch_bounds__(128) upcast_gap_kernel(const uint32_t* __restrict__ x, int4* __restrict__ cast_out,
+                                                         int4* __restrict__ pooled, uint32_t* __restrict__ out8, int HW, int C4) {
+  pdl_enter();
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, n = blockIdx.y;
+  if (c >= C4) return;
+  const uint32_t* p = x + (long long)n * HW * C4 + c;
+  int4* co = cast_out ? cast_out + (long long)n * HW * C4 + c : nullptr;
+  uint32_t s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+  auto acc = [&](uint32_t w, int i) {
+    int4 v;
+    if (SIGNED) v = make_int4((int8_t)(w & 0xFF), (int8_t)((w >> 8) & 0xFF), (int8_t)((w >> 16) & 0xFF), (int8_t)(w >> 24));
+    else v = make_int4((int)(w & 0xFF), (int)((w >> 8) & 0xFF), (int)((w >> 16) & 0xFF), (int)(w >> 24));
+    s0 += (uint32_t)v.x; s1 += (uint32_t)v.y; s2 += (uint32_t)v.z; s3 += (uint32_t)v.w;
+    if (co) co[(long long)i * C4] = v;
+  };
+  int i = 0;
+  for (; i + 7 <= HW; i += 7) {
+    uint32_t w[7];
+#pragma unroll
+    for (int j = 0; j < 7; ++j) w[j] = __ldg(p + (long long)(i + j) * C4);
+#pragma unroll
+    for (int j = 0; j < 7; ++j) acc(w[j], i + j);
+  }
+  for (; i < HW; ++i) acc(__ldg(p + (long long)i * C4), i);
+  const int4 q = make_int4((int32_t)s0 / HW, (int32_t)s1 / HW, (int32_t)s2 / HW, (int32_t)s3 / HW);
+  pooled[(long long)n * C4 + c] = q;
+  out8[(long long)n * C4 + c] = ((uint32_t)q.x & 0xFF) | (((uint32_t)q.y & 0xFF) << 8) | (((uint32_t)q.z & 0xFF) << 16) | ((uint32_t)q.w << 24);
+}
+
+void launch_upcast_gap(const void* x, int x_dtype, void* cast_out, void* pooled, void* out8, int N, int HW, int C, cudaStream_t s) {
+  if (N <= 0 || HW <= 0 || C <= 0) return;
+  const int C4 = C / 4;
+  dim3 grid((C4 + 127) / 128, N);
+  if (x_dtype == kI8) launch_pdl(upcast_gap_kernel<true>, grid, dim3(128), 0, s, (const uint32_t*)x, (int4*)cast_out, (int4*)pooled, (uint32_t*)out8, HW, C4);
+  else launch_pdl(upcast_gap_kernel<false>, grid, dim3(128), 0, s, (const uint32_t*)x, (int4*)cast_out, (int4*)pooled, (uint32_t*)out8, HW, C4);
+  ++g_launches;
+}
+
 __global__ void global_avgpool_nhwc_i32_kernel(const int32_t* __restrict__ x, int32_t* __restrict__ y, int HW, int C) {
   pdl_enter();
   const int c = blockIdx.x * blockDim.x + threadIdx.x, n = blockIdx.y;

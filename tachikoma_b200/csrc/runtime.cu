@@ -1700,6 +1700,48 @@ static void plan_qnn_leaky_relu(Planner& P, int nid) {
   });
 }
 
+// cast(8-bit -> int32) -> nn.global_avg_pool2d -> cast(-> 8-bit), each with a single consumer (the frontend's
+// apply_with_upcast tail of ResNet / MobileNet): one launch instead of three.  Returns the two nodes whose work the step of
+// `nid` already does (the main loop only emits their trace records), or an empty list if the pattern is not there.
+static std::vector<int> plan_upcast_gap(Planner& P, int nid) {
+  static const bool off = getenv("TKB_NO_GAP_FUSION") != nullptr;
+  Graph& g = P.g;
+  auto sole_consumer = [&](int producer) -> int {
+    int found = -1, count = 0;
+    for (size_t k = 0; k < g.nodes.size(); ++k)
+      for (auto& in : g.nodes[k].inputs)
+        if ((int)in[0] == producer && in[1] == 0) { found = (int)k; ++count; }
+    for (auto& h : g.heads)
+      if ((int)h[0] == producer) ++count;
+    return count == 1 ? found : -1;
+  };
+  const GNode& c1 = g.nodes[nid];
+  if (off || c1.name != "cast" || c1.inputs.size() != 1) return {};
+  const int pool_nid = sole_consumer(nid);
+  if (pool_nid < 0 || g.nodes[pool_nid].name != "nn.global_avg_pool2d") return {};
+  const int c2_nid = sole_consumer(pool_nid);
+  if (c2_nid < 0 || g.nodes[c2_nid].name != "cast") return {};
+  const int x_eid = (int)g.eid(c1.inputs[0]), e1 = (int)g.eid((uint32_t)nid, 0), e2 = (int)g.eid((uint32_t)pool_nid, 0), e3 = (int)g.eid((uint32_t)c2_nid, 0);
+  const Entry& X = P.ent[P.root(x_eid)];
+  const std::string lay = g.nodes[pool_nid].str("layout", "NCHW");
+  if (X.shape.size() != 4 || (X.dtype != kU8 && X.dtype != kI8) || P.ent[e1].dtype != kI32 || P.ent[e2].dtype != kI32 ||
+      (P.ent[e3].dtype != kU8 && P.ent[e3].dtype != kI8) || (lay != "NCHW" && lay != "NHWC"))
+    return {};
+  const int N = (int)X.shape[0], C = (int)X.shape[lay.find('C')], HW = (int)(X.shape[lay.find('H')] * X.shape[lay.find('W')]);
+  if (C % 4 != 0 || N > 65535 || HW <= 0) return {};
+  const int phys = lay == "NCHW" ? kNHWC : kLogical;  // channels-last in memory either way
+  P.need(x_eid, phys);
+  P.produce(e1, phys);
+  P.produce(e2, phys);
+  P.produce(e3, phys);
+  const int xdt = X.dtype;
+  P.rt->hbm_bytes += X.bytes() + P.ent[e2].bytes() + P.ent[e3].bytes();
+  P.add_step("cast -> nn.global_avg_pool2d -> cast in one launch (int32 copy of the input written for traces only)", [=](RunCtx& c) {
+    launch_upcast_gap(c.ptr(x_eid, phys), xdt, c.mode > 0 ? c.ptr(e1, phys) : nullptr, c.ptr(e2, phys), c.ptr(e3, phys), N, HW, C, c.s);
+  });
+  return {pool_nid, c2_nid};
+}
+
 // ------------------------------------------------------------------------------------------------
 // float32 operators (the other half of the reference's op list, tachikoma_json_runtime.cc:240-290): plain fp32 kernels
 // (kernels_float.cu), always in the logical (NC[D]HW / row-major) layout of the JSON graph
@@ -2220,6 +2262,7 @@ static void build_plan(tkb_runtime* rt) {
   for (uint32_t eid : g.input_eids) rt->ent[eid].off[kLogical] = P.arena_alloc(rt->ent[eid].bytes());  // H2D staging
   P.plan << "plan for " << rt->symbol << " (conv_impl=" << rt->conv_impl << ")\n";
   static const std::regex conv_pat(".*conv2d.*"), dense_pat(".*dense.*");
+  std::set<int> fused_nodes;
   for (size_t nid = 0; nid < g.nodes.size(); ++nid) {
     const GNode& n = g.nodes[nid];
     if (n.op_type != "kernel") continue;
@@ -2246,7 +2289,10 @@ static void build_plan(tkb_runtime* rt) {
       else return false;
       return true;
     };
-    if (plan_float()) {}
+    std::vector<int> fused_tail;
+    if (fused_nodes.count((int)nid)) {}  // its work is part of an earlier node's fused step (plan_upcast_gap)
+    else if (op == "cast" && !(fused_tail = plan_upcast_gap(P, (int)nid)).empty()) fused_nodes.insert(fused_tail.begin(), fused_tail.end());
+    else if (plan_float()) {}
     else if (op == "tachikoma.qnn.conv2d") plan_conv(P, (int)nid, true);
     else if (op == "tachikoma.qnn.dense") plan_dense(P, (int)nid, true);
     else if (op == "qnn.conv2d") plan_conv(P, (int)nid, false);

@@ -1109,3 +1109,40 @@ def test_mobilenet_default_plan_uses_the_pointwise_kernel_and_matches_tc_plan(mo
     np.testing.assert_equal(a, b)
     assert mod_a.trace_blob() == mod_b.trace_blob()
     assert mod_a.plan_summary().count("CUDA-core pointwise conv") >= 3
+
+
+@pytest.mark.parametrize("dtype", ["uint8", "int8"])
+@pytest.mark.parametrize("layout", ["NCHW", "NHWC"])
+def test_upcast_global_average_pool_tail_in_one_launch(dtype, layout):
+    """cast -> nn.global_avg_pool2d -> cast (qnn_torch.py:587-590) fused by the planner; not fused when the int32 tensor has a
+    second consumer.  Sums above 8 bits, negative means (truncation toward zero), traces."""
+    rng = np.random.default_rng(11)
+    shape = (3, 20, 7, 5) if layout == "NCHW" else (3, 7, 5, 20)
+    lo, hi = (0, 256) if dtype == "uint8" else (-128, 128)
+    x = rng.integers(lo, hi, shape).astype(dtype)
+    v = R.var("x", shape, dtype)
+    up = R.cast(v, "int32")
+    tail = R.cast(R.global_avg_pool2d(up, layout=layout), dtype)
+    f = R.Function([v], tail)
+    ref, _ = interp.run_expr(f, {"x": x})
+    out, mod, (js, consts, ins) = run_gpu(f, {"x": x}, trace=True)
+    np.testing.assert_equal(out, ref)
+    plan = mod.plan_summary()
+    assert "in one launch" in plan and "pooling kernel" not in plan and "cast -> elementwise" not in plan
+    _, recs = interp.run_json(js, consts, ins, want_trace=True)
+    assert mod.trace_blob() == interp.save_ndarray_list(recs)
+    # untraced run of the same module: same output (the int32 copy is not written then)
+    out2 = np.empty_like(out)
+    mod.run(x, out2, trace_mode=0)
+    np.testing.assert_equal(out2, ref)
+    # two consumers of the int32 tensor: three separate kernels
+    g = R.Function([v], R.Tuple([tail, up]))
+    part = T.partition_for_tachikoma(g)
+    sym, js2, names, consts2 = T.serialize(part)
+    m2 = RT.TachikomaJSONRuntime(sym, js2, names)
+    m2.init(consts2)
+    o0, o1 = np.empty(tail.shape, dtype), np.empty(shape, "int32")
+    m2.run(x, o0, o1)
+    np.testing.assert_equal(o0, ref)
+    np.testing.assert_equal(o1, x.astype("int32"))
+    assert "in one launch" not in m2.plan_summary()

@@ -113,3 +113,32 @@ def test_multiple_outputs_become_graph_heads():
     import pytest
     with pytest.raises(ValueError, match="only as the function body"):
         T.serialize(R.Function([x, y], R.add(R.Tuple([z, z]), y)))
+
+
+def float_fixture_graph():
+    x = R.var("x", (1, 4, 6, 6))
+    y = R.var("y", (1, 8, 4, 4))
+    w = R.const(np.arange(8 * 4 * 3 * 3, dtype="float32").reshape(8, 4, 3, 3) / 100)
+    b = R.const(np.arange(8, dtype="float32").reshape(8, 1, 1))
+    c = R.relu(R.add(R.add(R.conv2d(x, w), b), y))
+    c = R.clip(R.conv2d(c, R.const(np.ones((4, 8, 1, 1), "float32"))), 0.0, 6.0)
+    bn = R.batch_norm(c, np.ones(4, "float32"), np.zeros(4, "float32"), np.zeros(4, "float32"), np.ones(4, "float32"))
+    return R.Function([x, y], R.softmax(bn, axis=1))
+
+
+def test_float_serialization_matches_the_json_fixture():
+    """tests/golden/json_fixture_float.json pins the JSON of a float subgraph: composite names, inputs in the composite call's
+    argument order (data, weight, bias, sum: codegen.cc:516-524), the root call's attributes plus the clip's a_min / a_max on a
+    `_clip` composite (codegen.cc:531-536), the three declared outputs of nn.batch_norm and node_row_ptr."""
+    import os
+    f = float_fixture_graph()
+    _, js, names, consts = T.serialize(T.partition_for_tachikoma(f))
+    want = open(os.path.join(os.path.dirname(__file__), "golden", "json_fixture_float.json")).read()
+    assert js == want, "serialize() drifted from tests/golden/json_fixture_float.json"
+    g = json.loads(js)
+    kern = {n["name"]: n for n in g["nodes"] if n["op"] == "kernel"}
+    assert list(kern) == ["tachikoma.conv2d_bias_sum_relu", "tachikoma.conv2d_clip", "nn.batch_norm", "nn.softmax"]
+    assert kern["tachikoma.conv2d_bias_sum_relu"]["attrs"]["num_inputs"] == "4"
+    assert kern["tachikoma.conv2d_clip"]["attrs"]["a_min"] == [["0"]] and kern["tachikoma.conv2d_clip"]["attrs"]["a_max"] == [["6"]]
+    assert kern["tachikoma.conv2d_clip"]["attrs"]["kernel_size"] == [["1", "1"]]
+    assert kern["nn.batch_norm"]["attrs"]["num_outputs"] == "3"

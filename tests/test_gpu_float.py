@@ -125,3 +125,23 @@ def test_multiple_outputs_on_gpu():
     want, _ = interp.run_json(js, consts, [dv])
     np.testing.assert_array_equal(o0, want[0])
     np.testing.assert_array_equal(o1, want[1])
+
+
+def test_float_json_fixture_graph_on_gpu():
+    """The graph behind tests/golden/json_fixture_float.json (conv + bias + sum + relu, conv + clip, nn.batch_norm with its
+    three declared outputs, softmax) runs from exactly that JSON text."""
+    import os
+    from test_float_cpu import float_fixture_graph
+    f = float_fixture_graph()
+    sym, js, names, consts = T.serialize(T.partition_for_tachikoma(f))
+    assert js == open(os.path.join(os.path.dirname(__file__), "golden", "json_fixture_float.json")).read()
+    mod = RT.TachikomaJSONRuntime(sym, js, names)
+    mod.init(consts)
+    ins = FG.inputs_for(f)
+    out = np.empty((1, 4, 4, 4), "float32")
+    mod.run(ins["x"], ins["y"], out, trace_mode=2)
+    want, _ = interp.run_expr(f, ins)
+    np.testing.assert_allclose(out, want, rtol=1e-3, atol=1e-3)
+    got = interp.load_ndarray_list(mod.trace_blob())
+    _, recs = interp.run_json(js, consts, [ins["x"], ins["y"]], want_trace=True)
+    assert [r[0] for r in got] == [r[0] for r in recs]

@@ -1,6 +1,6 @@
 """Locate the first trace record of the small ResNet-18 that differs from the oracle (chained launch debugging)."""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # repo root (this checker lives under tests/: it uses the oracle)
 import numpy as np
 from oracle import interp
 from tachikoma_b200 import models, runtime as RT, tachikoma as T, trace as TR
